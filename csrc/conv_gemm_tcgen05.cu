@@ -1,0 +1,761 @@
+// tcgen05 / TMEM / TMA GEMM and implicit-GEMM convolution for sm_100a.
+//
+// One warp-specialised kernel covers the five GEMM-shaped hot ops of the CNN
+// zoo (reference call sites: tf.nn.conv2d / conv2d gradients / xw_plus_b at
+// scripts/tf_cnn_benchmarks/convnet_builder_legacy.py:123-141,318 and
+// tf.gradients at benchmark_cnn.py:3104; there they are cuDNN / cuBLAS calls):
+//
+//   GEMM_TN : C[M,N] = A[M,K] * B[N,K]^T             (FC fprop / dgrad, 1x1 conv)
+//   GEMM_NT : C[M,N] = A[K,M]^T * B[K,N]             (FC wgrad)
+//   FPROP   : y = conv(x, w)       A = im2col(x) via TMA im2col mode, B = w[Cout][R*S*C]
+//   DGRAD   : dx = conv^T(dy, w)   A = im2col(dy), B = w read in place, MN-major, taps flipped
+//   WGRAD   : dw = x^T (*) dy      A = dy (MN-major), B = im2col(x) (MN-major), split over pixels
+//
+// Layout: activations NHWC fp16, filters OHWI (= [Cout][R][S][C]) fp16, fp32
+// accumulation in TMEM. Tile = 128 x BN (BN in {64,128,256}), K-block = 64
+// fp16 = one 128-byte swizzled row. Roles per CTA (192 threads):
+//   warp 0 : TMA producer (one elected lane)
+//   warp 1 : TMEM allocator + tcgen05.mma issuer (one elected lane)
+//   warps 2-5 : epilogue (tcgen05.ld -> bias/ReLU -> global), one TMEM lane quarter each
+#include "kfb_common.cuh"
+#include "../include/kfb200.h"
+
+#include <stdarg.h>
+#include <string.h>
+
+namespace kfb {
+
+// ---------------------------------------------------------------------------
+// error string
+// ---------------------------------------------------------------------------
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+enum GemmMode : int { GEMM_TN = 0, GEMM_NT = 1, FPROP = 2, DGRAD = 3, WGRAD = 4 };
+
+struct GemmParams {
+  int mode;
+  int M, N;           // logical output extent (rows, cols) of one split
+  int num_kb;         // total number of 64-wide K blocks
+  int kb_per_split;   // K blocks handled by one blockIdx.z
+  // im2col geometry (FPROP / DGRAD: pixel = output row; WGRAD: pixel = K index)
+  int P, Q;           // im2col pixel grid (rows x cols) per image
+  int lower_h, lower_w;
+  int stride_h, stride_w;
+  int R, S;           // filter taps
+  int CB;             // 64-wide channel blocks per tap (FPROP/DGRAD)
+  int Ck;             // K extent per tap in elements (FPROP: C, DGRAD: Cout)
+  int Cn;             // WGRAD: channels per tap (N extent per tap)
+  int NCB;            // WGRAD: BN-wide channel blocks per tap
+  // epilogue
+  void* out;
+  long long ldc;           // elements between output rows
+  long long split_stride;  // elements between split-K slices
+  const float* bias;
+  int relu;
+  int out_fp32;
+  // optional row scatter (strided dgrad of a 1x1 conv): row (n,p,q) -> (n, p*sh, q*sw)
+  int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw;
+};
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;
+constexpr int kThreads = 192;
+constexpr int kTileABytes = kBlockM * kBlockK * 2;  // 16 KiB
+
+template <int BN>
+struct TileCfg {
+  static constexpr int kTileBBytes = BN * kBlockK * 2;
+  static constexpr int kStageBytes = kTileABytes + kTileBBytes;
+  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 3 : 4);
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int kTmemCols = BN < 32 ? 32 : BN;
+};
+
+template <int BN, int MODE>
+__global__ void __launch_bounds__(kThreads, 2)
+    gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
+                        const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  using Cfg = TileCfg<BN>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr uint32_t kAMajor = (MODE == GEMM_NT || MODE == WGRAD) ? kMajorMN : kMajorK;
+  constexpr uint32_t kBMajor = (MODE == GEMM_NT || MODE == WGRAD || MODE == DGRAD) ? kMajorMN
+                                                                                   : kMajorK;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kTileABytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full_bar = empty_bar + kStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int m0 = blockIdx.x * kBlockM;
+  int n0 = blockIdx.y * BN;  // first logical column of this tile
+  int wg_tap = 0, wg_cn = 0;
+  if (MODE == WGRAD) {
+    wg_tap = blockIdx.y / p.NCB;
+    wg_cn = blockIdx.y % p.NCB;
+    n0 = wg_cn * BN;  // channel offset within the tap
+  }
+  const int kb_begin = blockIdx.z * p.kb_per_split;
+  int kb_end = kb_begin + p.kb_per_split;
+  if (kb_end > p.num_kb) kb_end = p.num_kb;
+  const int my_kb = kb_end - kb_begin;  // may be <= 0 for a trailing split: writes zeros
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    mbar_fence_init();
+    fence_proxy_async_smem();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_smem, Cfg::kTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0 && my_kb > 0) {
+      // im2col start coordinates of this tile's first pixel (FPROP/DGRAD)
+      int px_n = 0, px_h = 0, px_w = 0;
+      if (MODE == FPROP || MODE == DGRAD) {
+        const int pq = p.P * p.Q;
+        px_n = m0 / pq;
+        const int rem = m0 - px_n * pq;
+        const int pp = rem / p.Q;
+        px_h = p.lower_h + pp * p.stride_h;
+        px_w = p.lower_w + (rem - pp * p.Q) * p.stride_w;
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem_a + stage * kTileABytes;
+        uint8_t* sb = smem_b + stage * Cfg::kTileBBytes;
+        mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+        if (MODE == GEMM_TN) {
+          tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBlockK, m0);
+          tma_load_2d(sb, &tmB, &full_bar[stage], kb * kBlockK, n0);
+        } else if (MODE == GEMM_NT) {
+#pragma unroll
+          for (int j = 0; j < kBlockM / 64; ++j)
+            tma_load_2d(sa + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, kb * kBlockK);
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)
+            tma_load_2d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * kBlockK);
+        } else if (MODE == FPROP) {
+          const int tap = kb / p.CB;
+          const int cb = kb - tap * p.CB;
+          const int r = tap / p.S;
+          const int s = tap - r * p.S;
+          tma_load_im2col_4d(sa, &tmA, &full_bar[stage], cb * kBlockK, px_w, px_h, px_n,
+                             static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+          tma_load_2d(sb, &tmB, &full_bar[stage], tap * p.Ck + cb * kBlockK, n0);
+        } else if (MODE == DGRAD) {
+          const int tap = kb / p.CB;
+          const int cb = kb - tap * p.CB;
+          const int r = tap / p.S;
+          const int s = tap - r * p.S;
+          tma_load_im2col_4d(sa, &tmA, &full_bar[stage], cb * kBlockK, px_w, px_h, px_n,
+                             static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+          const int wtap = (p.R - 1 - r) * p.S + (p.S - 1 - s);
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)
+            tma_load_3d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, wtap, cb * kBlockK);
+        } else {  // WGRAD
+          const int r = wg_tap / p.S;
+          const int s = wg_tap - r * p.S;
+          const int pix = kb * kBlockK;
+          const int pq = p.P * p.Q;
+          const int n_img = pix / pq;
+          const int rem = pix - n_img * pq;
+          const int pp = rem / p.Q;
+          const int h = p.lower_h + pp * p.stride_h;
+          const int w = p.lower_w + (rem - pp * p.Q) * p.stride_w;
+#pragma unroll
+          for (int j = 0; j < kBlockM / 64; ++j)
+            tma_load_2d(sa + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, pix);
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)
+            tma_load_im2col_4d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, w, h, n_img,
+                               static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+        }
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0 && my_kb > 0) {
+      constexpr uint32_t idesc = make_idesc_f16(kBlockM, BN, kAMajor, kBMajor);
+      // K-major: 8-row groups 1024 B apart; +32 B per UMMA_K(16) inside the swizzle atom.
+      // MN-major: 64-element column groups 8192 B apart (LBO), 8-row K groups 1024 B apart
+      //           (SBO); +2048 B per UMMA_K(16 rows).
+      constexpr uint32_t a_lbo = (kAMajor == kMajorK) ? 16 : 8192;
+      constexpr uint32_t b_lbo = (kBMajor == kMajorK) ? 16 : 8192;
+      constexpr uint32_t a_kstep = (kAMajor == kMajorK) ? 32 : 2048;
+      constexpr uint32_t b_kstep = (kBMajor == kMajorK) ? 32 : 2048;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < my_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem_a + stage * kTileABytes);
+        const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kTileBBytes);
+#pragma unroll
+        for (int k = 0; k < kBlockK / 16; ++k) {
+          const uint64_t da = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
+          const uint64_t db = make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, 1024);
+          umma_f16_ss(tmem_base, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full_bar);
+    }
+  } else {
+    // ===================== epilogue =====================
+    const int quarter = warp & 3;
+    const int row = m0 + quarter * 32 + lane;
+    if (my_kb > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    // output row address
+    long long row_off = row;
+    if (p.sc_P > 0) {
+      const int pq = p.sc_P * p.sc_Q;
+      const int n_img = row / pq;
+      const int rem = row - n_img * pq;
+      const int pp = rem / p.sc_Q;
+      const int qq = rem - pp * p.sc_Q;
+      row_off = (static_cast<long long>(n_img) * p.sc_H + static_cast<long long>(pp) * p.sc_sh) *
+                    p.sc_W +
+                static_cast<long long>(qq) * p.sc_sw;
+    }
+    int col_mem0 = n0;       // first memory column of this tile
+    int n_limit = p.N - n0;  // number of valid columns in this tile
+    if (MODE == WGRAD) {
+      col_mem0 = wg_tap * p.Cn + n0;
+      n_limit = p.Cn - n0;
+    }
+    const bool row_ok = row < p.M;
+    const long long base =
+        static_cast<long long>(blockIdx.z) * p.split_stride + row_off * p.ldc + col_mem0;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      if (c * 32 >= n_limit) break;  // warp-uniform
+      uint32_t v[32];
+      if (my_kb > 0) {
+        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + c * 32, v);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0u;
+      }
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int col = c * 32 + j;
+          if (col < n_limit) f[j] += __ldg(p.bias + n0 + col);
+        }
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+      }
+      if (!row_ok) continue;
+      const bool full = (c * 32 + 32 <= n_limit);
+      if (p.out_fp32) {
+        float* o = reinterpret_cast<float*>(p.out) + base + c * 32;
+        if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c * 32 + j < n_limit) o[j] = f[j];
+        }
+      } else {
+        __half* o = reinterpret_cast<__half*>(p.out) + base + c * 32;
+        if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 u;
+            u.x = pack_half2(f[j], f[j + 1]);
+            u.y = pack_half2(f[j + 2], f[j + 3]);
+            u.z = pack_half2(f[j + 4], f[j + 5]);
+            u.w = pack_half2(f[j + 6], f[j + 7]);
+            *reinterpret_cast<uint4*>(o + j) = u;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c * 32 + j < n_limit) o[j] = __float2half_rn(f[j]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Deterministic split-K reduction: out[i] = (accumulate ? out[i] : 0) + sum_z ws[z][i]
+// ---------------------------------------------------------------------------
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out,
+                                     long long n, int splits, int accumulate, float scale) {
+  const long long i4 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+  if (i4 >= n) return;
+  if (i4 + 4 <= n) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int z = 0; z < splits; ++z) {
+      const float4 v = *reinterpret_cast<const float4*>(ws + static_cast<long long>(z) * n + i4);
+      acc.x += v.x;
+      acc.y += v.y;
+      acc.z += v.z;
+      acc.w += v.w;
+    }
+    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+    float4* o = reinterpret_cast<float4*>(out + i4);
+    if (accumulate) {
+      const float4 old = *o;
+      acc.x += old.x; acc.y += old.y; acc.z += old.z; acc.w += old.w;
+    }
+    *o = acc;
+  } else {
+    for (long long i = i4; i < n; ++i) {
+      float acc = 0.f;
+      for (int z = 0; z < splits; ++z) acc += ws[static_cast<long long>(z) * n + i];
+      acc *= scale;
+      out[i] = accumulate ? out[i] + acc : acc;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Host: tensor-map encoding through the driver entry point (no -lcuda needed)
+// ---------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*PFN_encodeIm2col)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                     const cuuint64_t*, const cuuint64_t*, const int*, const int*,
+                                     cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                     CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled g_encodeTiled = nullptr;
+static PFN_encodeIm2col g_encodeIm2col = nullptr;
+
+static int load_driver_fns() {
+  if (g_encodeTiled && g_encodeIm2col) return 0;
+  cudaDriverEntryPointQueryResult q;
+  void* fn = nullptr;
+  KFB_CHECK_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+  KFB_REQUIRE(fn != nullptr && q == cudaDriverEntryPointSuccess,
+              "cuTensorMapEncodeTiled not available from the driver");
+  g_encodeTiled = reinterpret_cast<PFN_encodeTiled>(fn);
+  fn = nullptr;
+  KFB_CHECK_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &q));
+  KFB_REQUIRE(fn != nullptr && q == cudaDriverEntryPointSuccess,
+              "cuTensorMapEncodeIm2col not available from the driver");
+  g_encodeIm2col = reinterpret_cast<PFN_encodeIm2col>(fn);
+  return 0;
+}
+
+// fp16 tensor, rank 2 or 3 (dims innermost first), 128B swizzle, zero OOB fill.
+static int encode_tiled(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims,
+                        const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box) {
+  cuuint64_t gdim[5];
+  cuuint64_t gstr[4];
+  cuuint32_t bx[5];
+  cuuint32_t es[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+  }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
+  CUresult r = g_encodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, rank, const_cast<void*>(ptr),
+                             gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  KFB_REQUIRE(r == CUDA_SUCCESS,
+              "cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu,%llu,%llu] box [%u,%u,%u] "
+              "stride0 %llu ptr %p",
+              (int)r, rank, (unsigned long long)dims[0], (unsigned long long)dims[1],
+              (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], box[1], rank > 2 ? box[2] : 0,
+              (unsigned long long)strides_bytes[0], ptr);
+  return 0;
+}
+
+// NHWC fp16 activation viewed as {C, W, H, N}; im2col traversal.
+static int encode_im2col(CUtensorMap* m, const void* ptr, int N, int H, int W, int C, int lower_w,
+                         int lower_h, int upper_w, int upper_h, int channels_per_pixel,
+                         int pixels_per_column, int stride_w, int stride_h) {
+  cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t gstr[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lower[2] = {lower_w, lower_h};
+  int upper[2] = {upper_w, upper_h};
+  cuuint32_t es[4] = {1, (cuuint32_t)stride_w, (cuuint32_t)stride_h, 1};
+  CUresult r = g_encodeIm2col(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(ptr), gdim,
+                              gstr, lower, upper, (cuuint32_t)channels_per_pixel,
+                              (cuuint32_t)pixels_per_column, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  KFB_REQUIRE(r == CUDA_SUCCESS,
+              "cuTensorMapEncodeIm2col failed (%d): NHWC [%d,%d,%d,%d] lower [%d,%d] upper "
+              "[%d,%d] cpp %d ppc %d stride [%d,%d]",
+              (int)r, N, H, W, C, lower_w, lower_h, upper_w, upper_h, channels_per_pixel,
+              pixels_per_column, stride_w, stride_h);
+  return 0;
+}
+
+template <int BN, int MODE>
+static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
+                      dim3 grid, cudaStream_t stream) {
+  using Cfg = TileCfg<BN>;
+  static bool attr_set[16] = {false};  // per device
+  int dev = 0;
+  KFB_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 16 && !attr_set[dev]) {
+    KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::kSmemBytes));
+    attr_set[dev] = true;
+  }
+  gemm_tcgen05_kernel<BN, MODE><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int MODE>
+static int launch_mode(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
+                       dim3 grid, cudaStream_t stream) {
+  switch (bn) {
+    case 64: return launch_cfg<64, MODE>(tmA, tmB, p, grid, stream);
+    case 128: return launch_cfg<128, MODE>(tmA, tmB, p, grid, stream);
+    case 256: return launch_cfg<256, MODE>(tmA, tmB, p, grid, stream);
+  }
+  set_error("unsupported BN %d", bn);
+  return 2;
+}
+
+static int pick_bn(int n) { return n <= 64 ? 64 : (n <= 128 ? 128 : 256); }
+
+static int g_sm_count = 0;
+static int sm_count() {
+  if (g_sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sm_count <= 0) g_sm_count = 148;
+  }
+  return g_sm_count;
+}
+
+static void init_params(GemmParams* p) { memset(p, 0, sizeof(*p)); }
+
+}  // namespace kfb
+
+using namespace kfb;
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+extern "C" const char* kfb_last_error(void) { return kfb::g_err; }
+
+extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, int K,
+                           long long lda, long long ldb, long long ldc, const float* bias,
+                           int relu, int out_fp32, void* stream) {
+  KFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tn: bad shape %d %d %d", M, N, K);
+  KFB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tn: lda/ldb must be multiples of 8 elements");
+  if (load_driver_fns()) return 1;
+  const int bn = pick_bn(N);
+  CUtensorMap tmA, tmB;
+  uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * 2};
+  uint32_t ba[2] = {64, 128};
+  if (encode_tiled(&tmA, A, 2, da, sa, ba)) return 1;
+  uint64_t db[2] = {(uint64_t)K, (uint64_t)N}, sb[1] = {(uint64_t)ldb * 2};
+  uint32_t bb[2] = {64, (uint32_t)bn};
+  if (encode_tiled(&tmB, B, 2, db, sb, bb)) return 1;
+  GemmParams p;
+  init_params(&p);
+  p.mode = GEMM_TN;
+  p.M = M;
+  p.N = N;
+  p.num_kb = (K + 63) / 64;
+  p.kb_per_split = p.num_kb;
+  p.out = C;
+  p.ldc = ldc;
+  p.bias = bias;
+  p.relu = relu;
+  p.out_fp32 = out_fp32;
+  dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);
+  return launch_mode<GEMM_TN>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
+}
+
+// C[M,N] (fp32) = A[K,M]^T * B[K,N]; split over K into `workspace` then reduced.
+extern "C" int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N, int K,
+                           long long lda, long long ldb, long long ldc, float* workspace,
+                           long long workspace_bytes, int accumulate, float scale, void* stream) {
+  KFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_nt: bad shape %d %d %d", M, N, K);
+  KFB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_nt: lda/ldb must be multiples of 8 elements");
+  KFB_REQUIRE(ldc == N, "gemm_nt: output must be dense (ldc == N)");
+  if (load_driver_fns()) return 1;
+  const int bn = pick_bn(N);
+  CUtensorMap tmA, tmB;
+  uint64_t da[2] = {(uint64_t)M, (uint64_t)K}, sa[1] = {(uint64_t)lda * 2};
+  uint32_t bx[2] = {64, 64};
+  if (encode_tiled(&tmA, A, 2, da, sa, bx)) return 1;
+  uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)ldb * 2};
+  if (encode_tiled(&tmB, B, 2, db, sb, bx)) return 1;
+  GemmParams p;
+  init_params(&p);
+  p.mode = GEMM_NT;
+  p.M = M;
+  p.N = N;
+  p.num_kb = (K + 63) / 64;
+  const int tiles = ((M + 127) / 128) * ((N + bn - 1) / bn);
+  int splits = (2 * sm_count() + tiles - 1) / tiles;
+  if (splits > p.num_kb) splits = p.num_kb;
+  const long long slice = (long long)M * N;
+  long long max_splits = workspace_bytes / (slice * 4);
+  if (splits > max_splits) splits = (int)max_splits;
+  KFB_REQUIRE(splits >= 1, "gemm_nt: workspace too small (%lld bytes for %lld-element slices)",
+              workspace_bytes, slice);
+  p.kb_per_split = (p.num_kb + splits - 1) / splits;
+  splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.out = workspace;
+  p.ldc = N;
+  p.split_stride = slice;
+  p.out_fp32 = 1;
+  dim3 grid((M + 127) / 128, (N + bn - 1) / bn, splits);
+  if (launch_mode<GEMM_NT>(bn, tmA, tmB, p, grid, (cudaStream_t)stream)) return 1;
+  const long long n4 = (slice + 3) / 4;
+  splitk_reduce_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      workspace, C, slice, splits, accumulate, scale);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int check_conv(const kfb_conv_desc* d, const char* who) {
+  KFB_REQUIRE(d != nullptr, "%s: null descriptor", who);
+  KFB_REQUIRE(d->c % 8 == 0 && d->k % 8 == 0, "%s: C (%d) and Cout (%d) must be multiples of 8",
+              who, d->c, d->k);
+  KFB_REQUIRE(d->n > 0 && d->h > 0 && d->w > 0 && d->p > 0 && d->q > 0, "%s: bad geometry", who);
+  const int up_h = d->pad_h_hi - (d->r - 1), up_w = d->pad_w_hi - (d->s - 1);
+  KFB_REQUIRE(d->pad_h_lo <= 127 && d->pad_w_lo <= 127 && up_h >= -128 && up_w >= -128,
+              "%s: padding/filter exceed the TMA im2col corner range", who);
+  KFB_REQUIRE((d->h + d->pad_h_lo + d->pad_h_hi - d->r) / d->stride_h + 1 == d->p &&
+                  (d->w + d->pad_w_lo + d->pad_w_hi - d->s) / d->stride_w + 1 == d->q,
+              "%s: output size (%d,%d) inconsistent with geometry", who, d->p, d->q);
+  return 0;
+}
+
+// y[N,P,Q,ldy>=K] = conv(x[N,H,W,C], w[K,R,S,C]) (+bias) (ReLU)
+extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void* w, void* y,
+                              long long ldy, const float* bias, int relu, void* stream) {
+  if (check_conv(d, "conv_fprop")) return 2;
+  if (load_driver_fns()) return 1;
+  const int M = d->n * d->p * d->q;
+  const int bn = pick_bn(d->k);
+  CUtensorMap tmA, tmB;
+  if (encode_im2col(&tmA, x, d->n, d->h, d->w, d->c, -d->pad_w_lo, -d->pad_h_lo,
+                    d->pad_w_hi - (d->s - 1), d->pad_h_hi - (d->r - 1), 64, 128, d->stride_w,
+                    d->stride_h))
+    return 1;
+  const uint64_t Kt = (uint64_t)d->r * d->s * d->c;
+  uint64_t db[2] = {Kt, (uint64_t)d->k}, sb[1] = {Kt * 2};
+  uint32_t bb[2] = {64, (uint32_t)bn};
+  if (encode_tiled(&tmB, w, 2, db, sb, bb)) return 1;
+  GemmParams p;
+  init_params(&p);
+  p.mode = FPROP;
+  p.M = M;
+  p.N = d->k;
+  p.R = d->r;
+  p.S = d->s;
+  p.CB = (d->c + 63) / 64;
+  p.Ck = d->c;
+  p.num_kb = d->r * d->s * p.CB;
+  p.kb_per_split = p.num_kb;
+  p.P = d->p;
+  p.Q = d->q;
+  p.lower_h = -d->pad_h_lo;
+  p.lower_w = -d->pad_w_lo;
+  p.stride_h = d->stride_h;
+  p.stride_w = d->stride_w;
+  p.out = y;
+  p.ldc = ldy;
+  p.bias = bias;
+  p.relu = relu;
+  dim3 grid((M + 127) / 128, (d->k + bn - 1) / bn, 1);
+  return launch_mode<FPROP>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
+}
+
+// dx[N,H,W,C] = conv^T(dy[N,P,Q,lddy>=K], w[K,R,S,C]).
+// stride 1: implicit GEMM over dy with flipped taps.
+// stride > 1: only 1x1 un-padded filters (the ResNet-v1 / projection case): GEMM + row scatter
+// into a dx the caller has zero-filled.
+extern "C" int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void* w, void* dx,
+                              void* stream) {
+  if (check_conv(d, "conv_dgrad")) return 2;
+  if (load_driver_fns()) return 1;
+  const bool strided = d->stride_h != 1 || d->stride_w != 1;
+  KFB_REQUIRE(!strided || (d->r == 1 && d->s == 1 && d->pad_h_lo == 0 && d->pad_w_lo == 0),
+              "conv_dgrad: strided dgrad is only implemented for 1x1 un-padded filters");
+  const int bn = pick_bn(d->c);
+  CUtensorMap tmA, tmB;
+  GemmParams p;
+  init_params(&p);
+  p.mode = DGRAD;
+  p.N = d->c;
+  p.R = d->r;
+  p.S = d->s;
+  p.CB = (d->k + 63) / 64;
+  p.Ck = d->k;
+  p.num_kb = d->r * d->s * p.CB;
+  p.kb_per_split = p.num_kb;
+  p.stride_h = 1;
+  p.stride_w = 1;
+  p.out = dx;
+  p.ldc = d->c;
+  int M;
+  if (!strided) {
+    // dx pixel (h,w) gathers dy at (h + pad_lo - r, w + pad_lo - s): an fprop over dy with
+    // padding (R-1-pad_lo) and flipped taps.
+    M = d->n * d->h * d->w;
+    const int plo_h = d->r - 1 - d->pad_h_lo, plo_w = d->s - 1 - d->pad_w_lo;
+    // upper padding such that the output extent is exactly H x W
+    const int phi_h = d->h - d->p + d->r - 1 - plo_h, phi_w = d->w - d->q + d->s - 1 - plo_w;
+    KFB_REQUIRE(plo_h >= 0 && plo_w >= 0 && phi_h >= 0 && phi_w >= 0,
+                "conv_dgrad: unsupported padding");
+    if (encode_im2col(&tmA, dy, d->n, d->p, d->q, d->k, -plo_w, -plo_h, phi_w - (d->s - 1),
+                      phi_h - (d->r - 1), 64, 128, 1, 1))
+      return 1;
+    p.P = d->h;
+    p.Q = d->w;
+    p.lower_h = -plo_h;
+    p.lower_w = -plo_w;
+  } else {
+    M = d->n * d->p * d->q;
+    if (encode_im2col(&tmA, dy, d->n, d->p, d->q, d->k, 0, 0, 0, 0, 64, 128, 1, 1)) return 1;
+    p.P = d->p;
+    p.Q = d->q;
+    p.sc_P = d->p;
+    p.sc_Q = d->q;
+    p.sc_H = d->h;
+    p.sc_W = d->w;
+    p.sc_sh = d->stride_h;
+    p.sc_sw = d->stride_w;
+  }
+  p.M = M;
+  uint64_t db[3] = {(uint64_t)d->c, (uint64_t)d->r * d->s, (uint64_t)d->k};
+  uint64_t sb[2] = {(uint64_t)d->c * 2, (uint64_t)d->r * d->s * d->c * 2};
+  uint32_t bb[3] = {64, 1, 64};
+  if (encode_tiled(&tmB, w, 3, db, sb, bb)) return 1;
+  dim3 grid((M + 127) / 128, (d->c + bn - 1) / bn, 1);
+  return launch_mode<DGRAD>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
+}
+
+extern "C" long long kfb_conv_wgrad_workspace_bytes(const kfb_conv_desc* d) {
+  // enough for the split count picked below (<= 2*SMs/tiles + 1 slices, at least 1)
+  const long long slice = (long long)d->k * d->r * d->s * d->c * 4;
+  const int bn = pick_bn(d->c);
+  const int tiles = ((d->k + 127) / 128) * d->r * d->s * ((d->c + bn - 1) / bn);
+  int splits = (2 * 148 + tiles - 1) / tiles;
+  if (splits < 1) splits = 1;
+  return slice * splits;
+}
+
+// dw[K,R,S,C] (fp32) (+)= scale * sum_pixels dy[pix,K]^T * im2col(x)[pix,(r,s,C)]
+extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void* dy,
+                              long long lddy, float* dw, float* workspace,
+                              long long workspace_bytes, int accumulate, float scale,
+                              void* stream) {
+  if (check_conv(d, "conv_wgrad")) return 2;
+  if (load_driver_fns()) return 1;
+  const int pixels = d->n * d->p * d->q;
+  const int bn = pick_bn(d->c);
+  CUtensorMap tmA, tmB;
+  uint64_t da[2] = {(uint64_t)d->k, (uint64_t)pixels}, sa[1] = {(uint64_t)lddy * 2};
+  uint32_t bx[2] = {64, 64};
+  if (encode_tiled(&tmA, dy, 2, da, sa, bx)) return 1;
+  if (encode_im2col(&tmB, x, d->n, d->h, d->w, d->c, -d->pad_w_lo, -d->pad_h_lo,
+                    d->pad_w_hi - (d->s - 1), d->pad_h_hi - (d->r - 1), 64, 64, d->stride_w,
+                    d->stride_h))
+    return 1;
+  GemmParams p;
+  init_params(&p);
+  p.mode = WGRAD;
+  p.M = d->k;
+  p.N = d->r * d->s * d->c;
+  p.R = d->r;
+  p.S = d->s;
+  p.Cn = d->c;
+  p.NCB = (d->c + bn - 1) / bn;
+  p.num_kb = (pixels + 63) / 64;
+  p.P = d->p;
+  p.Q = d->q;
+  p.lower_h = -d->pad_h_lo;
+  p.lower_w = -d->pad_w_lo;
+  p.stride_h = d->stride_h;
+  p.stride_w = d->stride_w;
+  const int tiles = ((d->k + 127) / 128) * d->r * d->s * p.NCB;
+  int splits = (2 * sm_count() + tiles - 1) / tiles;
+  if (splits > p.num_kb) splits = p.num_kb;
+  const long long slice = (long long)d->k * d->r * d->s * d->c;
+  const long long max_splits = workspace_bytes / (slice * 4);
+  if (splits > max_splits) splits = (int)max_splits;
+  KFB_REQUIRE(splits >= 1, "conv_wgrad: workspace too small (%lld bytes, slice %lld elements)",
+              workspace_bytes, slice);
+  p.kb_per_split = (p.num_kb + splits - 1) / splits;
+  splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.out = workspace;
+  p.ldc = (long long)d->r * d->s * d->c;
+  p.split_stride = slice;
+  p.out_fp32 = 1;
+  dim3 grid((d->k + 127) / 128, d->r * d->s * p.NCB, splits);
+  if (launch_mode<WGRAD>(bn, tmA, tmB, p, grid, (cudaStream_t)stream)) return 1;
+  const long long n4 = (slice + 3) / 4;
+  splitk_reduce_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      workspace, dw, slice, splits, accumulate, scale);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,89 @@
+"""ctypes binding to the in-tree CUDA library (``_lib/libkfb200.so``).
+
+The library is built by ``kf_benchmarks_b200.build`` (plain ``nvcc`` for
+``sm_100a``) and exposes a C ABI declared in ``include/kfb200.h``. Tensors are
+handed over as raw device pointers plus the current CUDA stream, so there is no
+dependency on torch's C++ headers and the ``.so`` is visible in the process's
+map when it is used.
+
+On a machine with a GPU a missing library is a hard error: the ops in
+``kf_benchmarks_b200.ops`` never fall back to PyTorch math on CUDA tensors.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_lib",
+                         "libkfb200.so")
+_lib = None
+_lock = threading.Lock()
+
+# number of kernel launches issued through this binding (bench.py reports it)
+launch_count = 0
+
+
+class KfbError(RuntimeError):
+    pass
+
+
+class ConvDesc(ctypes.Structure):
+    """Mirror of ``kfb_conv_desc`` in include/kfb200.h."""
+    _fields_ = [(name, ctypes.c_int) for name in (
+        "n", "h", "w", "c", "k", "r", "s", "pad_h_lo", "pad_h_hi", "pad_w_lo", "pad_w_hi",
+        "stride_h", "stride_w", "p", "q")]
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_LIB_PATH)
+
+
+def load():
+    """Load the shared library once; raise KfbError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(_LIB_PATH):
+            raise KfbError(
+                f"native library not built: {_LIB_PATH} (run `python -m kf_benchmarks_b200.build`)")
+        lib = ctypes.CDLL(_LIB_PATH)
+        lib.kfb_last_error.restype = ctypes.c_char_p
+        _lib = lib
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().kfb_last_error().decode("utf-8", "replace")
+        raise KfbError(f"{what} failed (rc={rc}): {msg}")
+
+
+def call(name: str, *args) -> None:
+    """Call ``kfb_<name>`` and raise on a non-zero return code."""
+    global launch_count
+    fn = getattr(load(), "kfb_" + name)
+    rc = fn(*args)
+    launch_count += 1
+    check(rc, name)
+
+
+def ptr(t) -> ctypes.c_void_p:
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def stream_ptr() -> ctypes.c_void_p:
+    import torch
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+i32 = ctypes.c_int
+i64 = ctypes.c_longlong
+f32 = ctypes.c_float
