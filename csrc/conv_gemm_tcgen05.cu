@@ -7,6 +7,7 @@
 //
 //   GEMM_TN : C[M,N] = A[M,K] * B[N,K]^T             (FC fprop / dgrad, 1x1 conv)
 //   GEMM_NT : C[M,N] = A[K,M]^T * B[K,N]             (FC wgrad)
+//   GEMM_NN : C[M,N] = A[M,K] * B[K,N]               (FC dgrad; B read MN-major in place)
 //   FPROP   : y = conv(x, w)       A = im2col(x) via TMA im2col mode, B = w[Cout][R*S*C]
 //   DGRAD   : dx = conv^T(dy, w)   A = im2col(dy), B = w read in place, MN-major, taps flipped
 //   WGRAD   : dw = x^T (*) dy      A = dy (MN-major), B = im2col(x) (MN-major), split over pixels
@@ -36,7 +37,7 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-enum GemmMode : int { GEMM_TN = 0, GEMM_NT = 1, FPROP = 2, DGRAD = 3, WGRAD = 4 };
+enum GemmMode : int { GEMM_TN = 0, GEMM_NT = 1, FPROP = 2, DGRAD = 3, WGRAD = 4, GEMM_NN = 5 };
 
 struct GemmParams {
   int mode;
@@ -59,8 +60,11 @@ struct GemmParams {
   const float* bias;
   int relu;
   int out_fp32;
-  // optional row scatter (strided dgrad of a 1x1 conv): row (n,p,q) -> (n, p*sh, q*sw)
-  int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw;
+  int accumulate;          // out += result (gradient accumulation for fan-out tensors)
+  // optional row scatter (strided dgrad): row (n,i,j) -> (n, h0 + i*sh, w0 + j*sw) of H x W
+  int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw, sc_h0, sc_w0;
+  // DGRAD: filter tap visited at (r, s) of this launch's (sub-)filter
+  int wt_r0, wt_rstep, wt_s0, wt_sstep, wt_S;
 };
 
 constexpr int kBlockM = 128;
@@ -84,8 +88,8 @@ __global__ void __launch_bounds__(kThreads, 2)
   using Cfg = TileCfg<BN>;
   constexpr int kStages = Cfg::kStages;
   constexpr uint32_t kAMajor = (MODE == GEMM_NT || MODE == WGRAD) ? kMajorMN : kMajorK;
-  constexpr uint32_t kBMajor = (MODE == GEMM_NT || MODE == WGRAD || MODE == DGRAD) ? kMajorMN
-                                                                                   : kMajorK;
+  constexpr uint32_t kBMajor =
+      (MODE == GEMM_NT || MODE == WGRAD || MODE == DGRAD || MODE == GEMM_NN) ? kMajorMN : kMajorK;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -155,6 +159,11 @@ __global__ void __launch_bounds__(kThreads, 2)
         if (MODE == GEMM_TN) {
           tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBlockK, m0);
           tma_load_2d(sb, &tmB, &full_bar[stage], kb * kBlockK, n0);
+        } else if (MODE == GEMM_NN) {
+          tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBlockK, m0);
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)
+            tma_load_2d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * kBlockK);
         } else if (MODE == GEMM_NT) {
 #pragma unroll
           for (int j = 0; j < kBlockM / 64; ++j)
@@ -177,7 +186,8 @@ __global__ void __launch_bounds__(kThreads, 2)
           const int s = tap - r * p.S;
           tma_load_im2col_4d(sa, &tmA, &full_bar[stage], cb * kBlockK, px_w, px_h, px_n,
                              static_cast<uint16_t>(s), static_cast<uint16_t>(r));
-          const int wtap = (p.R - 1 - r) * p.S + (p.S - 1 - s);
+          const int wtap = (p.wt_r0 + p.wt_rstep * (p.R - 1 - r)) * p.wt_S +
+                           (p.wt_s0 + p.wt_sstep * (p.S - 1 - s));
 #pragma unroll
           for (int j = 0; j < BN / 64; ++j)
             tma_load_3d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, wtap, cb * kBlockK);
@@ -253,9 +263,10 @@ __global__ void __launch_bounds__(kThreads, 2)
       const int rem = row - n_img * pq;
       const int pp = rem / p.sc_Q;
       const int qq = rem - pp * p.sc_Q;
-      row_off = (static_cast<long long>(n_img) * p.sc_H + static_cast<long long>(pp) * p.sc_sh) *
+      row_off = (static_cast<long long>(n_img) * p.sc_H + p.sc_h0 +
+                 static_cast<long long>(pp) * p.sc_sh) *
                     p.sc_W +
-                static_cast<long long>(qq) * p.sc_sw;
+                p.sc_w0 + static_cast<long long>(qq) * p.sc_sw;
     }
     int col_mem0 = n0;       // first memory column of this tile
     int n_limit = p.N - n0;  // number of valid columns in this tile
@@ -297,18 +308,34 @@ __global__ void __launch_bounds__(kThreads, 2)
         float* o = reinterpret_cast<float*>(p.out) + base + c * 32;
         if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+          for (int j = 0; j < 32; j += 4) {
+            float4 r = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+            if (p.accumulate) {
+              const float4 old = *reinterpret_cast<const float4*>(o + j);
+              r.x += old.x; r.y += old.y; r.z += old.z; r.w += old.w;
+            }
+            *reinterpret_cast<float4*>(o + j) = r;
+          }
         } else {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
-            if (c * 32 + j < n_limit) o[j] = f[j];
+            if (c * 32 + j < n_limit) o[j] = p.accumulate ? o[j] + f[j] : f[j];
         }
       } else {
         __half* o = reinterpret_cast<__half*>(p.out) + base + c * 32;
         if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
           for (int j = 0; j < 32; j += 8) {
+            if (p.accumulate) {
+              const uint4 old = *reinterpret_cast<const uint4*>(o + j);
+              const __half2* oh = reinterpret_cast<const __half2*>(&old);
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                const float2 of = __half22float2(oh[t]);
+                f[j + 2 * t] += of.x;
+                f[j + 2 * t + 1] += of.y;
+              }
+            }
             uint4 u;
             u.x = pack_half2(f[j], f[j + 1]);
             u.y = pack_half2(f[j + 2], f[j + 3]);
@@ -319,7 +346,8 @@ __global__ void __launch_bounds__(kThreads, 2)
         } else {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
-            if (c * 32 + j < n_limit) o[j] = __float2half_rn(f[j]);
+            if (c * 32 + j < n_limit)
+              o[j] = __float2half_rn(p.accumulate ? __half2float(o[j]) + f[j] : f[j]);
         }
       }
     }
@@ -530,6 +558,36 @@ extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, 
   return launch_mode<GEMM_TN>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
 }
 
+// C[M,N] (+)= A[M,K] * B[K,N]; B is read in place as an MN-major operand.
+extern "C" int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, int K,
+                           long long lda, long long ldb, long long ldc, int out_fp32,
+                           int accumulate, void* stream) {
+  KFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_nn: bad shape %d %d %d", M, N, K);
+  KFB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_nn: lda/ldb must be multiples of 8 elements");
+  if (load_driver_fns()) return 1;
+  const int bn = pick_bn(N);
+  CUtensorMap tmA, tmB;
+  uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * 2};
+  uint32_t ba[2] = {64, 128};
+  if (encode_tiled(&tmA, A, 2, da, sa, ba)) return 1;
+  uint64_t db[2] = {(uint64_t)N, (uint64_t)K}, sb[1] = {(uint64_t)ldb * 2};
+  uint32_t bb[2] = {64, 64};
+  if (encode_tiled(&tmB, B, 2, db, sb, bb)) return 1;
+  GemmParams p;
+  init_params(&p);
+  p.mode = GEMM_NN;
+  p.M = M;
+  p.N = N;
+  p.num_kb = (K + 63) / 64;
+  p.kb_per_split = p.num_kb;
+  p.out = C;
+  p.ldc = ldc;
+  p.out_fp32 = out_fp32;
+  p.accumulate = accumulate;
+  dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);
+  return launch_mode<GEMM_NN>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
+}
+
 // C[M,N] (fp32) = A[K,M]^T * B[K,N]; split over K into `workspace` then reduced.
 extern "C" int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N, int K,
                            long long lda, long long ldb, long long ldc, float* workspace,
@@ -629,69 +687,101 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   return launch_mode<FPROP>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
 }
 
-// dx[N,H,W,C] = conv^T(dy[N,P,Q,lddy>=K], w[K,R,S,C]).
-// stride 1: implicit GEMM over dy with flipped taps.
-// stride > 1: only 1x1 un-padded filters (the ResNet-v1 / projection case): GEMM + row scatter
-// into a dx the caller has zero-filled.
+// dx[N,H,W,C] (+)= conv^T(dy[N,P,Q,K], w[K,R,S,C]).
+// The transposed convolution is decomposed by output phase (h mod stride_h, w mod stride_w):
+// every phase is a stride-1 correlation of dy with the sub-filter of taps r = r0 + stride*t,
+// gathered by TMA im2col over dy and scattered to the phase's pixels of dx. Stride 1 is the
+// single-phase case. Phases without any tap (e.g. 1x1 filters with stride 2) stay zero: without
+// `accumulate` the caller zero-fills dx first (kfb_conv_dgrad_needs_zero_fill tells).
+static int dgrad_phase_taps(int R, int stride, int pad_lo, int phase, int* r0, int* nR,
+                            int* base) {
+  *r0 = (phase + pad_lo) % stride;
+  *nR = *r0 < R ? (R - *r0 + stride - 1) / stride : 0;
+  *base = (phase + pad_lo - *r0) / stride;
+  return 0;
+}
+
+extern "C" int kfb_conv_dgrad_needs_zero_fill(const kfb_conv_desc* d) {
+  for (int ph = 0; ph < d->stride_h; ++ph)
+    for (int pw = 0; pw < d->stride_w; ++pw) {
+      int r0, nR, bh, s0, nS, bw;
+      dgrad_phase_taps(d->r, d->stride_h, d->pad_h_lo, ph, &r0, &nR, &bh);
+      dgrad_phase_taps(d->s, d->stride_w, d->pad_w_lo, pw, &s0, &nS, &bw);
+      if (nR == 0 || nS == 0) return 1;
+      // pixels of dx beyond the last window also receive nothing but are covered by OOB zeros
+    }
+  return 0;
+}
+
 extern "C" int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void* w, void* dx,
-                              void* stream) {
+                              int accumulate, void* stream) {
   if (check_conv(d, "conv_dgrad")) return 2;
   if (load_driver_fns()) return 1;
-  const bool strided = d->stride_h != 1 || d->stride_w != 1;
-  KFB_REQUIRE(!strided || (d->r == 1 && d->s == 1 && d->pad_h_lo == 0 && d->pad_w_lo == 0),
-              "conv_dgrad: strided dgrad is only implemented for 1x1 un-padded filters");
   const int bn = pick_bn(d->c);
-  CUtensorMap tmA, tmB;
-  GemmParams p;
-  init_params(&p);
-  p.mode = DGRAD;
-  p.N = d->c;
-  p.R = d->r;
-  p.S = d->s;
-  p.CB = (d->k + 63) / 64;
-  p.Ck = d->k;
-  p.num_kb = d->r * d->s * p.CB;
-  p.kb_per_split = p.num_kb;
-  p.stride_h = 1;
-  p.stride_w = 1;
-  p.out = dx;
-  p.ldc = d->c;
-  int M;
-  if (!strided) {
-    // dx pixel (h,w) gathers dy at (h + pad_lo - r, w + pad_lo - s): an fprop over dy with
-    // padding (R-1-pad_lo) and flipped taps.
-    M = d->n * d->h * d->w;
-    const int plo_h = d->r - 1 - d->pad_h_lo, plo_w = d->s - 1 - d->pad_w_lo;
-    // upper padding such that the output extent is exactly H x W
-    const int phi_h = d->h - d->p + d->r - 1 - plo_h, phi_w = d->w - d->q + d->s - 1 - plo_w;
-    KFB_REQUIRE(plo_h >= 0 && plo_w >= 0 && phi_h >= 0 && phi_w >= 0,
-                "conv_dgrad: unsupported padding");
-    if (encode_im2col(&tmA, dy, d->n, d->p, d->q, d->k, -plo_w, -plo_h, phi_w - (d->s - 1),
-                      phi_h - (d->r - 1), 64, 128, 1, 1))
-      return 1;
-    p.P = d->h;
-    p.Q = d->w;
-    p.lower_h = -plo_h;
-    p.lower_w = -plo_w;
-  } else {
-    M = d->n * d->p * d->q;
-    if (encode_im2col(&tmA, dy, d->n, d->p, d->q, d->k, 0, 0, 0, 0, 64, 128, 1, 1)) return 1;
-    p.P = d->p;
-    p.Q = d->q;
-    p.sc_P = d->p;
-    p.sc_Q = d->q;
-    p.sc_H = d->h;
-    p.sc_W = d->w;
-    p.sc_sh = d->stride_h;
-    p.sc_sw = d->stride_w;
-  }
-  p.M = M;
+  CUtensorMap tmB;
   uint64_t db[3] = {(uint64_t)d->c, (uint64_t)d->r * d->s, (uint64_t)d->k};
   uint64_t sb[2] = {(uint64_t)d->c * 2, (uint64_t)d->r * d->s * d->c * 2};
   uint32_t bb[3] = {64, 1, 64};
   if (encode_tiled(&tmB, w, 3, db, sb, bb)) return 1;
-  dim3 grid((M + 127) / 128, (d->c + bn - 1) / bn, 1);
-  return launch_mode<DGRAD>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
+  const bool strided = d->stride_h != 1 || d->stride_w != 1;
+  for (int ph = 0; ph < d->stride_h; ++ph) {
+    for (int pw = 0; pw < d->stride_w; ++pw) {
+      int r0, nR, base_h, s0, nS, base_w;
+      dgrad_phase_taps(d->r, d->stride_h, d->pad_h_lo, ph, &r0, &nR, &base_h);
+      dgrad_phase_taps(d->s, d->stride_w, d->pad_w_lo, pw, &s0, &nS, &base_w);
+      const int Hp = (d->h - ph + d->stride_h - 1) / d->stride_h;  // dx rows of this phase
+      const int Wp = (d->w - pw + d->stride_w - 1) / d->stride_w;
+      if (nR == 0 || nS == 0 || Hp <= 0 || Wp <= 0) continue;
+      // dy row read for dx row index i and sub-tap t' (flipped): i + lower_h + t'
+      const int lower_h = base_h - (nR - 1), lower_w = base_w - (nS - 1);
+      const int upper_h = Hp - d->p + lower_h, upper_w = Wp - d->q + lower_w;
+      KFB_REQUIRE(lower_h >= -128 && lower_w >= -128 && upper_h <= 127 && upper_w <= 127 &&
+                      lower_h <= 127 && lower_w <= 127 && upper_h >= -128 && upper_w >= -128,
+                  "conv_dgrad: geometry exceeds the TMA im2col corner range");
+      CUtensorMap tmA;
+      if (encode_im2col(&tmA, dy, d->n, d->p, d->q, d->k, lower_w, lower_h, upper_w, upper_h, 64,
+                        128, 1, 1))
+        return 1;
+      GemmParams p;
+      init_params(&p);
+      p.mode = DGRAD;
+      p.M = d->n * Hp * Wp;
+      p.N = d->c;
+      p.R = nR;
+      p.S = nS;
+      p.CB = (d->k + 63) / 64;
+      p.Ck = d->k;
+      p.num_kb = nR * nS * p.CB;
+      p.kb_per_split = p.num_kb;
+      p.P = Hp;
+      p.Q = Wp;
+      p.lower_h = lower_h;
+      p.lower_w = lower_w;
+      p.stride_h = 1;
+      p.stride_w = 1;
+      p.wt_r0 = r0;
+      p.wt_rstep = d->stride_h;
+      p.wt_s0 = s0;
+      p.wt_sstep = d->stride_w;
+      p.wt_S = d->s;
+      p.out = dx;
+      p.ldc = d->c;
+      p.accumulate = accumulate;
+      if (strided) {
+        p.sc_P = Hp;
+        p.sc_Q = Wp;
+        p.sc_H = d->h;
+        p.sc_W = d->w;
+        p.sc_sh = d->stride_h;
+        p.sc_sw = d->stride_w;
+        p.sc_h0 = ph;
+        p.sc_w0 = pw;
+      }
+      dim3 grid((p.M + 127) / 128, (d->c + bn - 1) / bn, 1);
+      if (launch_mode<DGRAD>(bn, tmA, tmB, p, grid, (cudaStream_t)stream)) return 1;
+    }
+  }
+  return 0;
 }
 
 extern "C" long long kfb_conv_wgrad_workspace_bytes(const kfb_conv_desc* d) {

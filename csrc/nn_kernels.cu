@@ -1,0 +1,1111 @@
+// Memory-bound layer kernels for sm_100a: batch-norm (stats / finalize / fused
+// apply+ReLU+residual, backward reduce + apply), pooling, spatial mean,
+// bias/ReLU backward, strided copies (concat / split), explicit im2col for
+// tiny-C stems, dropout, LRN and the fused softmax-cross-entropy(+top-k).
+//
+// All tensors are NHWC fp16 viewed as [rows = N*H*W][C] with an explicit row
+// stride (ld) so producers can write straight into channel slices of a concat
+// buffer. Channel counts must be multiples of 8 (16-byte vectors).
+// Reference behaviour: ConvNetBuilder.batch_norm / mpool / apool / spatial_mean /
+// dropout / lrn (T/convnet_builder_legacy.py:228-468) and CNNModel.loss_function /
+// accuracy_function (T/models/model.py:285-312).
+#include "kfb_common.cuh"
+#include "../include/kfb200.h"
+
+namespace kfb {
+
+struct alignas(16) Half8 {
+  __half2 h[4];
+};
+
+__device__ __forceinline__ void load8(const __half* p, float (&f)[8]) {
+  const Half8 v = *reinterpret_cast<const Half8*>(p);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __half22float2(v.h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ void store8(__half* p, const float (&f)[8]) {
+  Half8 v;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v.h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+  *reinterpret_cast<Half8*>(p) = v;
+}
+
+constexpr int kRedThreads = 256;
+
+// Generic per-channel two-value reduction over rows.
+//   MODE 0 (bn stats)      : a = x,            b = x*x
+//   MODE 1 (bn backward)   : g = dy*(mask>0);  a = g, b = g * (x - mean) * rstd
+//   MODE 2 (bias backward) : g = dy*(mask>0);  a = g (b unused); also writes g to dz
+// Stage 1 writes partial[block][2][C]; stage 2 (finalize kernels) folds the blocks in a
+// fixed order, so results are run-to-run deterministic.
+template <int MODE>
+__global__ void __launch_bounds__(kRedThreads)
+    channel_reduce_kernel(const __half* __restrict__ x, long long ldx,
+                          const __half* __restrict__ dy, long long lddy,
+                          const __half* __restrict__ mask, long long ldm,
+                          const float* __restrict__ mean_rstd,  // [2][C] (MODE 1)
+                          __half* __restrict__ dz, long long lddz, long long rows, int C,
+                          float* __restrict__ partial) {
+  extern __shared__ float red[];  // [kRedThreads][16] worst case handled by looping
+  const int vpr = C >> 3;         // vectors per row
+  // thread -> (row lane, channel vector); channel vectors beyond 256 are looped
+  const int cv_per_pass = vpr < kRedThreads ? vpr : kRedThreads;
+  const int row_lanes = kRedThreads / cv_per_pass;
+  const int tv = threadIdx.x % cv_per_pass;
+  const int tr = threadIdx.x / cv_per_pass;
+  const long long rows_per_block = (rows + gridDim.x - 1) / gridDim.x;
+  const long long r_begin = blockIdx.x * rows_per_block;
+  long long r_end = r_begin + rows_per_block;
+  if (r_end > rows) r_end = rows;
+
+  for (int cv0 = 0; cv0 < vpr; cv0 += cv_per_pass) {
+    const int cv = cv0 + tv;
+    float a[8], b[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = b[i] = 0.f;
+    float mu[8], rs[8];
+    if (MODE == 1 && cv < vpr && tr < row_lanes) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        mu[i] = mean_rstd[cv * 8 + i];
+        rs[i] = mean_rstd[C + cv * 8 + i];
+      }
+    }
+    if (cv < vpr && tr < row_lanes) {
+      for (long long r = r_begin + tr; r < r_end; r += row_lanes) {
+        if (MODE == 0) {
+          float v[8];
+          load8(x + r * ldx + cv * 8, v);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            a[i] += v[i];
+            b[i] += v[i] * v[i];
+          }
+        } else {
+          float g[8];
+          load8(dy + r * lddy + cv * 8, g);
+          if (mask != nullptr) {
+            float m[8];
+            load8(mask + r * ldm + cv * 8, m);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = m[i] > 0.f ? g[i] : 0.f;
+          }
+          if (MODE == 1) {
+            float v[8];
+            load8(x + r * ldx + cv * 8, v);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              a[i] += g[i];
+              b[i] += g[i] * (v[i] - mu[i]) * rs[i];
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] += g[i];
+            if (dz != nullptr) store8(dz + r * lddz + cv * 8, g);
+          }
+        }
+      }
+    }
+    // fold the row lanes through shared memory (fixed order)
+    __syncthreads();
+    float* mine = red + threadIdx.x * 16;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      mine[i] = a[i];
+      mine[8 + i] = b[i];
+    }
+    __syncthreads();
+    if (tr == 0 && cv < vpr) {
+      float sa[8], sb[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) sa[i] = sb[i] = 0.f;
+      for (int l = 0; l < row_lanes; ++l) {
+        const float* o = red + (l * cv_per_pass + tv) * 16;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          sa[i] += o[i];
+          sb[i] += o[8 + i];
+        }
+      }
+      float* pa = partial + static_cast<long long>(blockIdx.x) * 2 * C + cv * 8;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        pa[i] = sa[i];
+        pa[C + i] = sb[i];
+      }
+    }
+  }
+}
+
+// BN forward finalize: mean/var from partial sums, moving-average update, and the
+// per-channel affine (scale, shift) the apply kernel uses.
+__global__ void bn_finalize_kernel(const float* __restrict__ partial, int nblocks, int C,
+                                   float inv_count, float unbias, float eps, float decay,
+                                   const float* __restrict__ gamma,  // may be null (no scale)
+                                   const float* __restrict__ beta, float* __restrict__ moving_mean,
+                                   float* __restrict__ moving_var,
+                                   float* __restrict__ mean_rstd,     // [2][C] saved for bwd
+                                   float* __restrict__ scale_shift,   // [2][C]
+                                   int update_moving) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f, ss = 0.f;
+  for (int b = 0; b < nblocks; ++b) {
+    s += partial[static_cast<long long>(b) * 2 * C + c];
+    ss += partial[static_cast<long long>(b) * 2 * C + C + c];
+  }
+  const float mean = s * inv_count;
+  float var = ss * inv_count - mean * mean;
+  var = var < 0.f ? 0.f : var;
+  const float rstd = rsqrtf(var + eps);
+  mean_rstd[c] = mean;
+  mean_rstd[C + c] = rstd;
+  const float g = gamma ? gamma[c] : 1.f;
+  const float sc = g * rstd;
+  scale_shift[c] = sc;
+  scale_shift[C + c] = beta[c] - mean * sc;
+  if (update_moving) {
+    moving_mean[c] = moving_mean[c] * decay + mean * (1.f - decay);
+    moving_var[c] = moving_var[c] * decay + var * unbias * (1.f - decay);
+  }
+}
+
+// Inference-mode affine from the moving statistics.
+__global__ void bn_inference_affine_kernel(int C, float eps, const float* __restrict__ gamma,
+                                           const float* __restrict__ beta,
+                                           const float* __restrict__ moving_mean,
+                                           const float* __restrict__ moving_var,
+                                           float* __restrict__ scale_shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float sc = (gamma ? gamma[c] : 1.f) * rsqrtf(moving_var[c] + eps);
+  scale_shift[c] = sc;
+  scale_shift[C + c] = beta[c] - moving_mean[c] * sc;
+}
+
+// y = act(x * scale + shift (+ residual)); act = ReLU if relu.
+__global__ void __launch_bounds__(256)
+    bn_apply_kernel(const __half* __restrict__ x, long long ldx,
+                    const float* __restrict__ scale_shift, const __half* __restrict__ res,
+                    long long ldr, __half* __restrict__ y, long long ldy, long long rows, int C,
+                    int relu) {
+  const int vpr = C >> 3;
+  const long long total = rows * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    float v[8];
+    load8(x + r * ldx + cv * 8, v);
+    const float4 s0 = *reinterpret_cast<const float4*>(scale_shift + cv * 8);
+    const float4 s1 = *reinterpret_cast<const float4*>(scale_shift + cv * 8 + 4);
+    const float4 b0 = *reinterpret_cast<const float4*>(scale_shift + C + cv * 8);
+    const float4 b1 = *reinterpret_cast<const float4*>(scale_shift + C + cv * 8 + 4);
+    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    const float sh[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], sc[k], sh[k]);
+    if (res != nullptr) {
+      float rr[8];
+      load8(res + r * ldr + cv * 8, rr);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] += rr[k];
+    }
+    if (relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+    }
+    store8(y + r * ldy + cv * 8, v);
+  }
+}
+
+// BN backward finalize: dgamma/dbeta (optionally accumulated into the gradient arena) and
+// the per-channel coefficients of the apply pass.
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblocks, int C,
+                                       float inv_count, const float* __restrict__ gamma,
+                                       const float* __restrict__ mean_rstd,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                       int accumulate, float grad_scale,
+                                       float* __restrict__ coef /* [3][C]: k, c1, c2 */) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float db = 0.f, dg = 0.f;
+  for (int b = 0; b < nblocks; ++b) {
+    db += partial[static_cast<long long>(b) * 2 * C + c];
+    dg += partial[static_cast<long long>(b) * 2 * C + C + c];
+  }
+  if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + dg * grad_scale;
+  if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + db * grad_scale;
+  const float rstd = mean_rstd[C + c];
+  coef[c] = (gamma ? gamma[c] : 1.f) * rstd;
+  coef[C + c] = db * inv_count;
+  coef[2 * C + c] = dg * inv_count;
+}
+
+// dz = k * (g - c1 - xhat * c2), g = dy * (mask > 0); optionally d_res (+)= g.
+__global__ void __launch_bounds__(256)
+    bn_bwd_apply_kernel(const __half* __restrict__ dy, long long lddy,
+                        const __half* __restrict__ mask, long long ldm,
+                        const __half* __restrict__ x, long long ldx,
+                        const float* __restrict__ mean_rstd, const float* __restrict__ coef,
+                        __half* __restrict__ dz, long long lddz, __half* __restrict__ dres,
+                        long long lddr, int dres_accumulate, long long rows, int C) {
+  const int vpr = C >> 3;
+  const long long total = rows * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    float g[8], v[8];
+    load8(dy + r * lddy + cv * 8, g);
+    if (mask != nullptr) {
+      float m[8];
+      load8(mask + r * ldm + cv * 8, m);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = m[k] > 0.f ? g[k] : 0.f;
+    }
+    load8(x + r * ldx + cv * 8, v);
+    float out[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = cv * 8 + k;
+      const float xhat = (v[k] - mean_rstd[c]) * mean_rstd[C + c];
+      out[k] = coef[c] * (g[k] - coef[C + c] - xhat * coef[2 * C + c]);
+    }
+    store8(dz + r * lddz + cv * 8, out);
+    if (dres != nullptr) {
+      if (dres_accumulate) {
+        float o[8];
+        load8(dres + r * lddr + cv * 8, o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] += o[k];
+      }
+      store8(dres + r * lddr + cv * 8, g);
+    }
+  }
+}
+
+// Fold bias-gradient partials: db[c] (+)= scale * sum_b partial[b][0][c]
+__global__ void colsum_finalize_kernel(const float* __restrict__ partial, int nblocks, int C,
+                                       float* __restrict__ out, int accumulate, float scale) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f;
+  for (int b = 0; b < nblocks; ++b) s += partial[static_cast<long long>(b) * 2 * C + c];
+  out[c] = (accumulate ? out[c] : 0.f) + s * scale;
+}
+
+// ---------------------------------------------------------------------------
+// Elementwise: out = act(a (+ b)); act: 0 none, 1 relu. Also used for grad accumulation.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    add_act_kernel(const __half* __restrict__ a, long long lda, const __half* __restrict__ b,
+                   long long ldb, __half* __restrict__ y, long long ldy, long long rows, int C,
+                   int relu) {
+  const int vpr = C >> 3;
+  const long long total = rows * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    float v[8];
+    load8(a + r * lda + cv * 8, v);
+    if (b != nullptr) {
+      float w[8];
+      load8(b + r * ldb + cv * 8, w);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] += w[k];
+    }
+    if (relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+    }
+    store8(y + r * ldy + cv * 8, v);
+  }
+}
+
+// dx (+)= dy * (mask > 0)
+__global__ void __launch_bounds__(256)
+    relu_bwd_kernel(const __half* __restrict__ dy, long long lddy, const __half* __restrict__ mask,
+                    long long ldm, __half* __restrict__ dx, long long lddx, int accumulate,
+                    long long rows, int C) {
+  const int vpr = C >> 3;
+  const long long total = rows * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    float g[8];
+    load8(dy + r * lddy + cv * 8, g);
+    if (mask != nullptr) {
+      float m[8];
+      load8(mask + r * ldm + cv * 8, m);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = m[k] > 0.f ? g[k] : 0.f;
+    }
+    if (accumulate) {
+      float o[8];
+      load8(dx + r * lddx + cv * 8, o);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += o[k];
+    }
+    store8(dx + r * lddx + cv * 8, g);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Pooling (NHWC). Max pooling stores the arg-max tap (uint8) for the backward pass.
+// Average pooling divides by the number of in-bounds taps (TF 'SAME' semantics).
+// ---------------------------------------------------------------------------
+struct PoolGeom {
+  int n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w;
+};
+
+__global__ void __launch_bounds__(256)
+    pool_fwd_kernel(const __half* __restrict__ x, long long ldx, __half* __restrict__ y,
+                    long long ldy, unsigned char* __restrict__ argmax, PoolGeom g, int is_max) {
+  const int vpr = g.c >> 3;
+  const long long total = static_cast<long long>(g.n) * g.p * g.q * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % vpr);
+    long long t = i / vpr;
+    const int q = static_cast<int>(t % g.q);
+    t /= g.q;
+    const int p = static_cast<int>(t % g.p);
+    const int n = static_cast<int>(t / g.p);
+    const int h0 = p * g.sh - g.pad_h, w0 = q * g.sw - g.pad_w;
+    float acc[8];
+    int arg[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      acc[k] = is_max ? -65504.f : 0.f;
+      arg[k] = 0;
+    }
+    int count = 0;
+    for (int r = 0; r < g.kh; ++r) {
+      const int hh = h0 + r;
+      if (hh < 0 || hh >= g.h) continue;
+      for (int s = 0; s < g.kw; ++s) {
+        const int ww = w0 + s;
+        if (ww < 0 || ww >= g.w) continue;
+        float v[8];
+        load8(x + ((static_cast<long long>(n) * g.h + hh) * g.w + ww) * ldx + cv * 8, v);
+        if (is_max) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (v[k] > acc[k] || count == 0) {
+              acc[k] = v[k];
+              arg[k] = r * g.kw + s;
+            }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += v[k];
+        }
+        ++count;
+      }
+    }
+    if (!is_max) {
+      const float inv = count > 0 ? 1.f / count : 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] *= inv;
+    }
+    const long long orow = (static_cast<long long>(n) * g.p + p) * g.q + q;
+    store8(y + orow * ldy + cv * 8, acc);
+    if (is_max && argmax != nullptr) {
+      uint2 packed;
+      packed.x = arg[0] | (arg[1] << 8) | (arg[2] << 16) | (arg[3] << 24);
+      packed.y = arg[4] | (arg[5] << 8) | (arg[6] << 16) | (arg[7] << 24);
+      *reinterpret_cast<uint2*>(argmax + orow * g.c + cv * 8) = packed;
+    }
+  }
+}
+
+// Gather formulation: one thread per input vector visits the output windows that cover it.
+__global__ void __launch_bounds__(256)
+    pool_bwd_kernel(const __half* __restrict__ dy, long long lddy,
+                    const unsigned char* __restrict__ argmax, __half* __restrict__ dx,
+                    long long lddx, int accumulate, PoolGeom g, int is_max) {
+  const int vpr = g.c >> 3;
+  const long long total = static_cast<long long>(g.n) * g.h * g.w * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % vpr);
+    long long t = i / vpr;
+    const int ww = static_cast<int>(t % g.w);
+    t /= g.w;
+    const int hh = static_cast<int>(t % g.h);
+    const int n = static_cast<int>(t / g.h);
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    // output rows p with p*sh - pad <= hh < p*sh - pad + kh
+    int p_lo = (hh + g.pad_h - g.kh + g.sh) / g.sh;
+    if (hh + g.pad_h - g.kh + 1 <= 0) p_lo = 0;
+    int p_hi = (hh + g.pad_h) / g.sh;
+    if (p_hi >= g.p) p_hi = g.p - 1;
+    int q_lo = (ww + g.pad_w - g.kw + g.sw) / g.sw;
+    if (ww + g.pad_w - g.kw + 1 <= 0) q_lo = 0;
+    int q_hi = (ww + g.pad_w) / g.sw;
+    if (q_hi >= g.q) q_hi = g.q - 1;
+    for (int p = p_lo; p <= p_hi; ++p) {
+      const int r = hh - (p * g.sh - g.pad_h);
+      if (r < 0 || r >= g.kh) continue;
+      for (int q = q_lo; q <= q_hi; ++q) {
+        const int s = ww - (q * g.sw - g.pad_w);
+        if (s < 0 || s >= g.kw) continue;
+        const long long orow = (static_cast<long long>(n) * g.p + p) * g.q + q;
+        float d[8];
+        load8(dy + orow * lddy + cv * 8, d);
+        if (is_max) {
+          const uint2 packed = *reinterpret_cast<const uint2*>(argmax + orow * g.c + cv * 8);
+          const int tap = r * g.kw + s;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const unsigned a = ((k < 4 ? packed.x : packed.y) >> (8 * (k & 3))) & 0xffu;
+            if (static_cast<int>(a) == tap) acc[k] += d[k];
+          }
+        } else {
+          // number of in-bounds taps of window (p, q)
+          const int h0 = p * g.sh - g.pad_h, w0 = q * g.sw - g.pad_w;
+          const int hc = min(h0 + g.kh, g.h) - max(h0, 0);
+          const int wc = min(w0 + g.kw, g.w) - max(w0, 0);
+          const float inv = 1.f / static_cast<float>(hc * wc);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += d[k] * inv;
+        }
+      }
+    }
+    __half* o = dx + ((static_cast<long long>(n) * g.h + hh) * g.w + ww) * lddx + cv * 8;
+    if (accumulate) {
+      float old[8];
+      load8(o, old);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += old[k];
+    }
+    store8(o, acc);
+  }
+}
+
+// y[n][c] = mean over hw of x[n][hw][c]
+__global__ void __launch_bounds__(256)
+    spatial_mean_fwd_kernel(const __half* __restrict__ x, long long ldx, __half* __restrict__ y,
+                            long long ldy, int n, int hw, int C) {
+  const int vpr = C >> 3;
+  const long long total = static_cast<long long>(n) * vpr;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int cv = static_cast<int>(i % vpr);
+  const long long img = i / vpr;
+  float acc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+  for (int j = 0; j < hw; ++j) {
+    float v[8];
+    load8(x + (img * hw + j) * ldx + cv * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] += v[k];
+  }
+  const float inv = 1.f / hw;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) acc[k] *= inv;
+  store8(y + img * ldy + cv * 8, acc);
+}
+
+__global__ void __launch_bounds__(256)
+    spatial_mean_bwd_kernel(const __half* __restrict__ dy, long long lddy, __half* __restrict__ dx,
+                            long long lddx, int accumulate, int n, int hw, int C) {
+  const int vpr = C >> 3;
+  const long long total = static_cast<long long>(n) * hw * vpr;
+  const float inv = 1.f / hw;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % vpr);
+    const long long row = i / vpr;
+    const long long img = row / hw;
+    float d[8];
+    load8(dy + img * lddy + cv * 8, d);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) d[k] *= inv;
+    __half* o = dx + row * lddx + cv * 8;
+    if (accumulate) {
+      float old[8];
+      load8(o, old);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) d[k] += old[k];
+    }
+    store8(o, d);
+  }
+}
+
+// Strided 2-D copy of 16-byte vectors (concat / split / pad). accumulate: dst += src.
+__global__ void __launch_bounds__(256)
+    copy2d_kernel(const __half* __restrict__ src, long long lds, __half* __restrict__ dst,
+                  long long ldd, long long rows, int C, int accumulate) {
+  const int vpr = C >> 3;
+  const long long total = rows * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    if (accumulate) {
+      float a[8], b[8];
+      load8(src + r * lds + cv * 8, a);
+      load8(dst + r * ldd + cv * 8, b);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a[k] += b[k];
+      store8(dst + r * ldd + cv * 8, a);
+    } else {
+      *reinterpret_cast<uint4*>(dst + r * ldd + cv * 8) =
+          *reinterpret_cast<const uint4*>(src + r * lds + cv * 8);
+    }
+  }
+}
+
+// Explicit im2col for convolutions whose input channel count is not a multiple of 8
+// (image stems, C = 1 or 3): col[row][(r*S+s)*C + c], zero padded to kpad columns.
+__global__ void __launch_bounds__(256)
+    im2col_small_c_kernel(const __half* __restrict__ x, __half* __restrict__ col, int n, int h,
+                          int w, int c, int p, int q, int kh, int kw, int sh, int sw, int pad_h,
+                          int pad_w, int kpad) {
+  const int vpr = kpad >> 3;
+  const long long total = static_cast<long long>(n) * p * q * vpr;
+  const int ktot = kh * kw * c;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int kv = static_cast<int>(i % vpr);
+    long long t = i / vpr;
+    const int qq = static_cast<int>(t % q);
+    t /= q;
+    const int pp = static_cast<int>(t % p);
+    const int nn = static_cast<int>(t / p);
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = kv * 8 + j;
+      float val = 0.f;
+      if (k < ktot) {
+        const int cc = k % c;
+        const int tap = k / c;
+        const int s = tap % kw, r = tap / kw;
+        const int hh = pp * sh - pad_h + r, ww = qq * sw - pad_w + s;
+        if (hh >= 0 && hh < h && ww >= 0 && ww < w)
+          val = __half2float(x[((static_cast<long long>(nn) * h + hh) * w + ww) * c + cc]);
+      }
+      v[j] = val;
+    }
+    store8(col + (i / vpr) * kpad + kv * 8, v);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Philox-4x32-10 (counter-based RNG) for dropout masks and synthetic inputs.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32(uint4 ctr, uint2 key) {
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += 0x9E3779B9u;
+    key.y += 0xBB67AE85u;
+  }
+  return ctr;
+}
+__device__ __forceinline__ float u01(uint32_t r) { return (r >> 8) * (1.0f / 16777216.0f); }
+
+// y = x * mask / keep, mask regenerated from (seed, offset) in backward (same kernel).
+__global__ void __launch_bounds__(256)
+    dropout_kernel(const __half* __restrict__ x, __half* __restrict__ y, long long nvec,
+                   float keep_prob, unsigned long long seed, unsigned long long offset) {
+  const float inv_keep = 1.f / keep_prob;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    const unsigned long long cnt = offset + static_cast<unsigned long long>(i);
+    const uint4 r0 = philox4x32(
+        make_uint4(static_cast<uint32_t>(cnt), static_cast<uint32_t>(cnt >> 32), 0u, 0u), key);
+    const uint4 r1 = philox4x32(
+        make_uint4(static_cast<uint32_t>(cnt), static_cast<uint32_t>(cnt >> 32), 1u, 0u), key);
+    const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+    float v[8];
+    load8(x + i * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = u01(rr[k]) < keep_prob ? v[k] * inv_keep : 0.f;
+    store8(y + i * 8, v);
+  }
+}
+
+// Synthetic images: truncated normal(mean, std) clipped at 2 sigma (resampled), fp16.
+// T/models/model.py:220-237 (tf.truncated_normal mean 127 stddev 60).
+__global__ void __launch_bounds__(256)
+    synth_images_kernel(__half* __restrict__ out, long long n, float mean, float stddev,
+                        unsigned long long seed) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+    float z = 0.f;
+    for (uint32_t attempt = 0; attempt < 8; ++attempt) {
+      const uint4 r = philox4x32(
+          make_uint4(static_cast<uint32_t>(i), static_cast<uint32_t>(i >> 32), attempt, 7u), key);
+      const float u1 = fmaxf(u01(r.x), 1e-7f), u2 = u01(r.y);
+      const float rad = sqrtf(-2.f * __logf(u1));
+      float s, c;
+      __sincosf(6.28318530718f * u2, &s, &c);
+      z = rad * c;
+      if (fabsf(z) <= 2.f) break;
+      z = rad * s;
+      if (fabsf(z) <= 2.f) break;
+      z = fminf(fmaxf(z, -2.f), 2.f);
+    }
+    out[i] = __float2half_rn(mean + stddev * z);
+  }
+}
+
+// Labels uniform in [lo, hi)
+__global__ void synth_labels_kernel(int* __restrict__ out, int n, int lo, int hi,
+                                    unsigned long long seed) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint2 key = make_uint2(static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+  const uint4 r = philox4x32(make_uint4(static_cast<uint32_t>(i), 0u, 0u, 11u), key);
+  out[i] = lo + static_cast<int>(r.x % static_cast<uint32_t>(hi - lo));
+}
+
+// ---------------------------------------------------------------------------
+// Local response normalisation across channels (T/convnet_builder_legacy.py:462-468).
+// y = x / (bias + alpha * sum_{|j-c|<=radius} x_j^2)^beta
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    lrn_fwd_kernel(const __half* __restrict__ x, __half* __restrict__ y, long long rows, int C,
+                   int radius, float bias, float alpha, float beta) {
+  const long long total = rows * C;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / C;
+    const int c = static_cast<int>(i - r * C);
+    float ss = 0.f;
+    const int lo = max(c - radius, 0), hi = min(c + radius, C - 1);
+    for (int j = lo; j <= hi; ++j) {
+      const float v = __half2float(x[r * C + j]);
+      ss += v * v;
+    }
+    const float d = bias + alpha * ss;
+    y[i] = __float2half_rn(__half2float(x[i]) * __powf(d, -beta));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    lrn_bwd_kernel(const __half* __restrict__ x, const __half* __restrict__ dy,
+                   __half* __restrict__ dx, int accumulate, long long rows, int C, int radius,
+                   float bias, float alpha, float beta) {
+  const long long total = rows * C;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / C;
+    const int c = static_cast<int>(i - r * C);
+    const float xc = __half2float(x[i]);
+    // dx_c = dy_c * d_c^-beta - 2 alpha beta x_c * sum_{j: |j-c|<=radius} dy_j x_j d_j^(-beta-1)
+    float acc = 0.f, own = 0.f;
+    const int lo = max(c - radius, 0), hi = min(c + radius, C - 1);
+    for (int j = lo; j <= hi; ++j) {
+      float ss = 0.f;
+      const int l2 = max(j - radius, 0), h2 = min(j + radius, C - 1);
+      for (int k = l2; k <= h2; ++k) {
+        const float v = __half2float(x[r * C + k]);
+        ss += v * v;
+      }
+      const float d = bias + alpha * ss;
+      const float dyj = __half2float(dy[r * C + j]);
+      if (j == c) own = dyj * __powf(d, -beta);
+      acc += dyj * __half2float(x[r * C + j]) * __powf(d, -beta - 1.f);
+    }
+    float g = own - 2.f * alpha * beta * xc * acc;
+    if (accumulate) g += __half2float(dx[i]);
+    dx[i] = __float2half_rn(g);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Softmax cross-entropy with sparse labels, fused with the backward gradient, the
+// loss-scale multiply and top-1 / top-5 hits. One warp per row.
+//   loss_row[r] = logsumexp(z) - z[label]
+//   dlogits[r]  = (softmax(z) - onehot) * grad_scale       (fp16, row stride lddl)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    softmax_xent_kernel(const float* __restrict__ logits, long long ldl,
+                        const int* __restrict__ labels, int rows, int classes,
+                        float grad_scale, const float* __restrict__ dyn_scale,
+                        __half* __restrict__ dlogits, long long lddl,
+                        float* __restrict__ loss_rows, int* __restrict__ top1,
+                        int* __restrict__ top5) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const float* z = logits + static_cast<long long>(warp) * ldl;
+  const int label = labels[warp];
+  float m = -INFINITY;
+  for (int j = lane; j < classes; j += 32) m = fmaxf(m, z[j]);
+  m = warp_max(m);
+  float s = 0.f;
+  for (int j = lane; j < classes; j += 32) s += __expf(z[j] - m);
+  s = warp_sum(s);
+  const float zl = (label >= 0 && label < classes) ? z[label] : 0.f;
+  const float lse = m + __logf(s);
+  // rank of the label logit = number of classes strictly greater (tf.nn.in_top_k counts ties
+  // as hits)
+  float greater = 0.f;
+  for (int j = lane; j < classes; j += 32) greater += (z[j] > zl) ? 1.f : 0.f;
+  greater = warp_sum(greater);
+  if (lane == 0) {
+    loss_rows[warp] = lse - zl;
+    if (top1) top1[warp] = greater < 1.f ? 1 : 0;
+    if (top5) top5[warp] = greater < 5.f ? 1 : 0;
+  }
+  if (dlogits != nullptr) {
+    if (dyn_scale != nullptr) grad_scale *= *dyn_scale;
+    const float inv = 1.f / s;
+    __half* d = dlogits + static_cast<long long>(warp) * lddl;
+    for (int j = lane; j < lddl; j += 32) {
+      float g = 0.f;
+      if (j < classes) g = (__expf(z[j] - m) * inv - (j == label ? 1.f : 0.f)) * grad_scale;
+      d[j] = __float2half_rn(g);
+    }
+  }
+}
+
+// out[0] = sum(loss_rows)/rows ; out[1] = sum(top1) ; out[2] = sum(top5)  (single block)
+__global__ void loss_finalize_kernel(const float* __restrict__ loss_rows,
+                                     const int* __restrict__ top1, const int* __restrict__ top5,
+                                     int rows, float* __restrict__ out) {
+  __shared__ float sh[3][32];
+  float a = 0.f, b = 0.f, c = 0.f;
+  for (int i = threadIdx.x; i < rows; i += blockDim.x) {
+    a += loss_rows[i];
+    if (top1) b += top1[i];
+    if (top5) c += top5[i];
+  }
+  a = warp_sum(a);
+  b = warp_sum(b);
+  c = warp_sum(c);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) {
+    sh[0][w] = a;
+    sh[1][w] = b;
+    sh[2][w] = c;
+  }
+  __syncthreads();
+  if (w == 0) {
+    const int nw = blockDim.x >> 5;
+    a = l < nw ? sh[0][l] : 0.f;
+    b = l < nw ? sh[1][l] : 0.f;
+    c = l < nw ? sh[2][l] : 0.f;
+    a = warp_sum(a);
+    b = warp_sum(b);
+    c = warp_sum(c);
+    if (l == 0) {
+      out[0] = a / rows;
+      out[1] = b;
+      out[2] = c;
+    }
+  }
+}
+
+// fp32 -> fp16 cast (weight shadow refresh when the optimizer is not the fused one)
+__global__ void __launch_bounds__(256)
+    cast_f32_f16_kernel(const float* __restrict__ in, __half* __restrict__ out, long long n) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[i] = __float2half_rn(in[i]);
+}
+
+// dst[r][0..cols) = src[r][0..cols) for arbitrary cols / strides (flatten into padded rows).
+__global__ void __launch_bounds__(256)
+    copy_rows_kernel(const __half* __restrict__ src, long long lds, __half* __restrict__ dst,
+                     long long ldd, long long rows, long long cols, int accumulate) {
+  const long long total = rows * cols;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / cols;
+    const long long c = i - r * cols;
+    const __half v = src[r * lds + c];
+    __half* o = dst + r * ldd + c;
+    *o = accumulate ? __float2half_rn(__half2float(*o) + __half2float(v)) : v;
+  }
+}
+
+static inline int grid_for(long long work_items, int threads = 256, int max_blocks = 148 * 16) {
+  long long b = (work_items + threads - 1) / threads;
+  if (b < 1) b = 1;
+  if (b > max_blocks) b = max_blocks;
+  return static_cast<int>(b);
+}
+
+static inline int reduce_blocks(long long rows, int C) {
+  // enough blocks to fill the machine, but each block should own >= 64 rows
+  long long b = rows / 64;
+  const long long cap = 148 * 4;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+}  // namespace kfb
+
+using namespace kfb;
+
+#define KFB_REQ_C8(C, who) KFB_REQUIRE((C) > 0 && (C) % 8 == 0, who ": C (%d) must be a multiple of 8", (C))
+
+extern "C" int kfb_reduce_blocks(long long rows, int C) { return reduce_blocks(rows, C); }
+
+// scratch must hold kfb_reduce_blocks(rows,C) * 2 * C floats.
+extern "C" int kfb_bn_forward_train(const void* x, long long ldx, long long rows, int C,
+                                    const float* gamma, const float* beta, float* moving_mean,
+                                    float* moving_var, float eps, float decay, int update_moving,
+                                    float* mean_rstd, float* scale_shift, float* scratch,
+                                    const void* residual, long long ldr, int relu, void* y,
+                                    long long ldy, void* stream) {
+  KFB_REQ_C8(C, "bn_forward_train");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nb = reduce_blocks(rows, C);
+  channel_reduce_kernel<0><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
+      (const __half*)x, ldx, nullptr, 0, nullptr, 0, nullptr, nullptr, 0, rows, C, scratch);
+  const float unbias = rows > 1 ? (float)((double)rows / (double)(rows - 1)) : 1.f;
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, nb, C, (float)(1.0 / (double)rows),
+                                                     unbias, eps, decay, gamma, beta, moving_mean,
+                                                     moving_var, mean_rstd, scale_shift,
+                                                     update_moving);
+  bn_apply_kernel<<<grid_for(rows * (C / 8)), 256, 0, st>>>(
+      (const __half*)x, ldx, scale_shift, (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
+      relu);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_bn_forward_inference(const void* x, long long ldx, long long rows, int C,
+                                        const float* gamma, const float* beta,
+                                        const float* moving_mean, const float* moving_var,
+                                        float eps, float* scale_shift, const void* residual,
+                                        long long ldr, int relu, void* y, long long ldy,
+                                        void* stream) {
+  KFB_REQ_C8(C, "bn_forward_inference");
+  cudaStream_t st = (cudaStream_t)stream;
+  bn_inference_affine_kernel<<<(C + 127) / 128, 128, 0, st>>>(C, eps, gamma, beta, moving_mean,
+                                                             moving_var, scale_shift);
+  bn_apply_kernel<<<grid_for(rows * (C / 8)), 256, 0, st>>>(
+      (const __half*)x, ldx, scale_shift, (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
+      relu);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Backward of y = act(bn(x) (+ residual)). `mask` is y when act = ReLU (else null).
+// coef: 3*C floats of scratch; scratch: kfb_reduce_blocks * 2 * C floats.
+extern "C" int kfb_bn_backward(const void* dy, long long lddy, const void* mask, long long ldm,
+                               const void* x, long long ldx, long long rows, int C,
+                               const float* gamma, const float* mean_rstd, float* dgamma,
+                               float* dbeta, int accumulate_param_grads, float grad_scale,
+                               float* coef, float* scratch, void* dz, long long lddz, void* dres,
+                               long long lddr, int dres_accumulate, void* stream) {
+  KFB_REQ_C8(C, "bn_backward");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nb = reduce_blocks(rows, C);
+  channel_reduce_kernel<1><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
+      (const __half*)x, ldx, (const __half*)dy, lddy, (const __half*)mask, ldm, mean_rstd,
+      nullptr, 0, rows, C, scratch);
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(
+      scratch, nb, C, (float)(1.0 / (double)rows), gamma, mean_rstd, dgamma, dbeta,
+      accumulate_param_grads, grad_scale, coef);
+  bn_bwd_apply_kernel<<<grid_for(rows * (C / 8)), 256, 0, st>>>(
+      (const __half*)dy, lddy, (const __half*)mask, ldm, (const __half*)x, ldx, mean_rstd, coef,
+      (__half*)dz, lddz, (__half*)dres, lddr, dres_accumulate, rows, C);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// dz = dy * (mask > 0) (dz may be null or alias dy); dbias (+)= scale * colsum(dz).
+extern "C" int kfb_bias_act_backward(const void* dy, long long lddy, const void* mask,
+                                     long long ldm, long long rows, int C, void* dz,
+                                     long long lddz, float* dbias, int accumulate, float scale,
+                                     float* scratch, void* stream) {
+  KFB_REQ_C8(C, "bias_act_backward");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nb = reduce_blocks(rows, C);
+  channel_reduce_kernel<2><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
+      nullptr, 0, (const __half*)dy, lddy, (const __half*)mask, ldm, nullptr, (__half*)dz, lddz,
+      rows, C, scratch);
+  if (dbias != nullptr)
+    colsum_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, nb, C, dbias, accumulate,
+                                                           scale);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_add_act(const void* a, long long lda, const void* b, long long ldb, void* y,
+                           long long ldy, long long rows, int C, int relu, void* stream) {
+  KFB_REQ_C8(C, "add_act");
+  add_act_kernel<<<grid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)a, lda, (const __half*)b, ldb, (__half*)y, ldy, rows, C, relu);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_relu_backward(const void* dy, long long lddy, const void* mask, long long ldm,
+                                 void* dx, long long lddx, int accumulate, long long rows, int C,
+                                 void* stream) {
+  KFB_REQ_C8(C, "relu_backward");
+  relu_bwd_kernel<<<grid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)dy, lddy, (const __half*)mask, ldm, (__half*)dx, lddx, accumulate, rows, C);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int fill_pool(PoolGeom* g, int n, int h, int w, int c, int p, int q, int kh, int kw, int sh,
+                     int sw, int pad_h, int pad_w) {
+  KFB_REQ_C8(c, "pool");
+  KFB_REQUIRE(kh * kw <= 255, "pool: window %dx%d too large", kh, kw);
+  *g = PoolGeom{n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w};
+  return 0;
+}
+
+extern "C" int kfb_pool_forward(const void* x, long long ldx, void* y, long long ldy,
+                                unsigned char* argmax, int n, int h, int w, int c, int p, int q,
+                                int kh, int kw, int sh, int sw, int pad_h, int pad_w, int is_max,
+                                void* stream) {
+  PoolGeom g;
+  if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
+  pool_fwd_kernel<<<grid_for((long long)n * p * q * (c / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)x, ldx, (__half*)y, ldy, argmax, g, is_max);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_pool_backward(const void* dy, long long lddy, const unsigned char* argmax,
+                                 void* dx, long long lddx, int accumulate, int n, int h, int w,
+                                 int c, int p, int q, int kh, int kw, int sh, int sw, int pad_h,
+                                 int pad_w, int is_max, void* stream) {
+  PoolGeom g;
+  if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
+  pool_bwd_kernel<<<grid_for((long long)n * h * w * (c / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)dy, lddy, argmax, (__half*)dx, lddx, accumulate, g, is_max);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_spatial_mean_forward(const void* x, long long ldx, void* y, long long ldy, int n,
+                                        int hw, int C, void* stream) {
+  KFB_REQ_C8(C, "spatial_mean_forward");
+  const long long total = (long long)n * (C / 8);
+  spatial_mean_fwd_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)x, ldx, (__half*)y, ldy, n, hw, C);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_spatial_mean_backward(const void* dy, long long lddy, void* dx, long long lddx,
+                                         int accumulate, int n, int hw, int C, void* stream) {
+  KFB_REQ_C8(C, "spatial_mean_backward");
+  spatial_mean_bwd_kernel<<<grid_for((long long)n * hw * (C / 8)), 256, 0,
+                            (cudaStream_t)stream>>>((const __half*)dy, lddy, (__half*)dx, lddx,
+                                                    accumulate, n, hw, C);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_copy2d(const void* src, long long lds, void* dst, long long ldd, long long rows,
+                          int C, int accumulate, void* stream) {
+  KFB_REQ_C8(C, "copy2d");
+  copy2d_kernel<<<grid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)src, lds, (__half*)dst, ldd, rows, C, accumulate);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_copy_rows(const void* src, long long lds, void* dst, long long ldd,
+                             long long rows, long long cols, int accumulate, void* stream) {
+  copy_rows_kernel<<<grid_for(rows * cols), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)src, lds, (__half*)dst, ldd, rows, cols, accumulate);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_im2col_small_c(const void* x, void* col, int n, int h, int w, int c, int p,
+                                  int q, int kh, int kw, int sh, int sw, int pad_h, int pad_w,
+                                  int kpad, void* stream) {
+  KFB_REQUIRE(kpad % 8 == 0 && kpad >= kh * kw * c, "im2col_small_c: bad kpad %d", kpad);
+  im2col_small_c_kernel<<<grid_for((long long)n * p * q * (kpad / 8)), 256, 0,
+                          (cudaStream_t)stream>>>((const __half*)x, (__half*)col, n, h, w, c, p,
+                                                  q, kh, kw, sh, sw, pad_h, pad_w, kpad);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_dropout(const void* x, void* y, long long n, float keep_prob,
+                           unsigned long long seed, unsigned long long offset, void* stream) {
+  KFB_REQUIRE(n % 8 == 0, "dropout: element count must be a multiple of 8");
+  KFB_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "dropout: bad keep_prob %f", keep_prob);
+  dropout_kernel<<<grid_for(n / 8), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)x, (__half*)y, n / 8, keep_prob, seed, offset);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_synth_images(void* out, long long n, float mean, float stddev,
+                                unsigned long long seed, void* stream) {
+  synth_images_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>((__half*)out, n, mean,
+                                                                     stddev, seed);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_synth_labels(int* out, int n, int lo, int hi, unsigned long long seed,
+                                void* stream) {
+  KFB_REQUIRE(hi > lo, "synth_labels: empty range");
+  synth_labels_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(out, n, lo, hi, seed);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_lrn_forward(const void* x, void* y, long long rows, int C, int radius,
+                               float bias, float alpha, float beta, void* stream) {
+  lrn_fwd_kernel<<<grid_for(rows * C), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)x, (__half*)y, rows, C, radius, bias, alpha, beta);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_lrn_backward(const void* x, const void* dy, void* dx, int accumulate,
+                                long long rows, int C, int radius, float bias, float alpha,
+                                float beta, void* stream) {
+  lrn_bwd_kernel<<<grid_for(rows * C), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)x, (const __half*)dy, (__half*)dx, accumulate, rows, C, radius, bias, alpha,
+      beta);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// out3 = {mean loss, #top1 hits, #top5 hits}; loss_rows/top1/top5 are per-row scratch outputs.
+extern "C" int kfb_softmax_xent(const float* logits, long long ldl, const int* labels, int rows,
+                                int classes, float grad_scale, const float* dyn_scale,
+                                void* dlogits, long long lddl, float* loss_rows, int* top1,
+                                int* top5, float* out3, void* stream) {
+  KFB_REQUIRE(rows > 0 && classes > 0, "softmax_xent: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int warps_per_block = 8;
+  softmax_xent_kernel<<<(rows + warps_per_block - 1) / warps_per_block, 256, 0, st>>>(
+      logits, ldl, labels, rows, classes, grad_scale, dyn_scale, (__half*)dlogits, lddl,
+      loss_rows, top1, top5);
+  if (out3 != nullptr) loss_finalize_kernel<<<1, 256, 0, st>>>(loss_rows, top1, top5, rows, out3);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_cast_f32_f16(const float* in, void* out, long long n, void* stream) {
+  cast_f32_f16_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(in, (__half*)out, n);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

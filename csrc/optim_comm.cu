@@ -1,0 +1,575 @@
+// Gradient-path kernels for sm_100a: fused optimizers on the flat parameter arena and the
+// peer-to-peer (NVLink 5 / NVSwitch) collectives that replace the reference's gradient
+// replication stack:
+//
+//   * kfb_optimizer_step       - unscale + weight decay + clip + finite-skip + SGD / Nesterov
+//                                momentum / RMSProp / Adam on the fp32 master, fp16 re-emit
+//                                (T/benchmark_cnn.py:1172-1190, 2787-2808, 3110-3120)
+//   * kfb_allreduce_update     - ONE kernel per bucket: two-shot all-reduce over mapped peer
+//                                arenas (reduce-scatter by P2P loads, all-gather by P2P
+//                                stores) fused with the optimizer epilogue above
+//                                (replaces T/batch_allreduce.py + T/allreduce.py:280-324,
+//                                hvd.allreduce T/benchmark_cnn.py:3122-3130, KungFu
+//                                SynchronousSGDOptimizer T/benchmark_cnn.py:1193-1195)
+//   * kfb_sma_update           - KungFu SynchronousAveraging: all-reduce-average the *model*,
+//                                blend, then apply the local gradient (:1199-1201)
+//   * kfb_pair_average_update  - KungFu PairAveraging / AD-PSGD: pull one peer's published
+//                                model straight from its HBM, blend 1/2, apply the local
+//                                gradient, publish (:1196-1198)
+//   * kfb_broadcast_pull       - initial variable broadcast from rank 0 (T/variable_mgr.py:342-356)
+//   * kfb_device_barrier       - flag barrier in symmetric memory (kungfu.run_barrier)
+//   * kfb_check_finite / kfb_loss_scale_update - auto loss-scale state machine
+//                                (T/variable_mgr_util.py:51-139)
+//
+// Synchronisation protocol: every rank owns a flag page in symmetric memory. Flags only ever
+// grow (per-call sequence numbers), are written with st.release.sys after a system fence and
+// polled with ld.acquire.sys, so there is no reset race. Waits are bounded (trap after 20 s).
+#include "kfb_common.cuh"
+#include "../include/kfb200.h"
+
+namespace kfb {
+
+constexpr int kMaxRanks = 8;
+// flag page layout (uint32 words): [kind][src_rank], kinds below; one extra block counter row
+enum FlagKind : int { FLAG_READY = 0, FLAG_REDUCED = 1, FLAG_DONE = 2, FLAG_BARRIER = 3,
+                      FLAG_KINDS = 4 };
+constexpr int kCounterWord = FLAG_KINDS * kMaxRanks;  // grid arrival counters live after flags
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+struct HyperParams {
+  int opt;             // 0 sgd, 1 momentum (Nesterov, TF ApplyMomentum), 2 rmsprop, 3 adam
+  float lr;
+  float momentum;      // momentum / rmsprop momentum / adam beta1
+  float decay;         // rmsprop decay / adam beta2
+  float epsilon;
+  float weight_decay;  // L2 coefficient: g += wd * w
+  float grad_scale;    // multiplies the (reduced) gradient: 1/loss_scale, 1/N for means
+  float clip;          // elementwise clip (<= 0: off)
+  float adam_t;        // step count for Adam bias correction
+};
+
+// dyn (optional, device memory): {lr, grad_scale, adam_t, unused}. Lets a captured CUDA graph
+// see per-step values.
+__device__ __forceinline__ void resolve_dyn(HyperParams& h, const float* dyn) {
+  if (dyn != nullptr) {
+    h.lr = dyn[0];
+    h.grad_scale = dyn[1];
+    h.adam_t = dyn[2];
+  }
+}
+
+__device__ __forceinline__ float apply_update(const HyperParams& h, float w, float g_raw, float* m,
+                                              float* v, long long i) {
+  float g = g_raw * h.grad_scale + h.weight_decay * w;
+  if (h.clip > 0.f) g = fminf(fmaxf(g, -h.clip), h.clip);
+  switch (h.opt) {
+    case 0:
+      return w - h.lr * g;
+    case 1: {
+      const float acc = m[i] * h.momentum + g;
+      m[i] = acc;
+      return w - h.lr * (g + h.momentum * acc);
+    }
+    case 2: {
+      const float ms = h.decay * v[i] + (1.f - h.decay) * g * g;
+      v[i] = ms;
+      const float mom = h.momentum * m[i] + h.lr * g * rsqrtf(ms + h.epsilon);
+      m[i] = mom;
+      return w - mom;
+    }
+    default: {
+      const float b1 = h.momentum, b2 = h.decay;
+      const float mm = b1 * m[i] + (1.f - b1) * g;
+      const float vv = b2 * v[i] + (1.f - b2) * g * g;
+      m[i] = mm;
+      v[i] = vv;
+      const float lr_t = h.lr * sqrtf(1.f - __powf(b2, h.adam_t)) / (1.f - __powf(b1, h.adam_t));
+      return w - lr_t * mm / (sqrtf(vv) + h.epsilon);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Local fused optimizer over [0, n)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    optimizer_step_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m,
+                          float* __restrict__ v, __half* __restrict__ w16, long long n,
+                          HyperParams h, const float* __restrict__ dyn,
+                          const int* __restrict__ skip_flag) {
+  if (skip_flag != nullptr && *skip_flag != 0) return;
+  resolve_dyn(h, dyn);
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float nw = apply_update(h, w[i], g[i], m, v, i);
+    w[i] = nw;
+    if (w16 != nullptr) w16[i] = __float2half_rn(nw);
+  }
+}
+
+// flag[0] |= any non-finite in g[0..n)
+__global__ void __launch_bounds__(256)
+    check_finite_kernel(const float* __restrict__ g, long long n, int* __restrict__ flag) {
+  int bad = 0;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float x = g[i];
+    bad |= !(fabsf(x) <= 3.4028234e38f);
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
+}
+
+// state = {loss_scale, normal_steps}; dyn[1] (grad_scale) is refreshed to base_grad_scale/scale.
+// Skip flag set: halve, reset counter. Else count up to inc_every clean steps, then double
+// (same transitions as T/variable_mgr_util.py:51-88).
+__global__ void loss_scale_update_kernel(float* state, int* flag, int inc_every, float* dyn,
+                                         float base_grad_scale) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  float scale = state[0];
+  float steps = state[1];
+  if (*flag != 0) {
+    scale *= 0.5f;
+    steps = 0.f;
+  } else if (steps < static_cast<float>(inc_every)) {
+    steps += 1.f;
+  } else {
+    scale *= 2.f;
+    steps = 0.f;
+  }
+  state[0] = scale;
+  state[1] = steps;
+  if (dyn != nullptr) dyn[1] = base_grad_scale / scale;
+}
+
+// ---------------------------------------------------------------------------
+// Peer context (passed by value)
+// ---------------------------------------------------------------------------
+struct PeerCtx {
+  int rank, nranks;
+  float* src[kMaxRanks];      // per-rank source arena (gradients, or weights for SMA)
+  float* reduced[kMaxRanks];  // per-rank landing buffer for reduced shards
+  uint32_t* flags[kMaxRanks]; // per-rank flag page
+};
+
+__device__ __forceinline__ void wait_flags(const PeerCtx& c, int kind, uint32_t seq) {
+  // thread t < nranks polls the flag written by rank t into MY page
+  if (threadIdx.x < c.nranks) {
+    const uint32_t* f = c.flags[c.rank] + kind * kMaxRanks + threadIdx.x;
+    const uint64_t t0 = globaltimer_ns();
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(f) - seq) < 0) {
+      if ((++spins & 0xfff) == 0 && globaltimer_ns() - t0 > 20000000000ull) {
+        printf("kfb: rank %d timed out waiting for flag kind %d from rank %d (want %u have %u)\n",
+               c.rank, kind, (int)threadIdx.x, seq, ld_acquire_sys(f));
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// All threads have issued their stores; publish `seq` of `kind` to every rank once the whole
+// grid has arrived. counter_slot selects one of the arrival counters in my flag page.
+__device__ __forceinline__ void grid_arrive_and_signal(const PeerCtx& c, int kind, uint32_t seq,
+                                                       int counter_slot) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* counter = c.flags[c.rank] + kCounterWord + counter_slot;
+    const uint32_t prev = atomicAdd(counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *counter = 0;  // all blocks have arrived; nobody touches it again in this launch
+      __threadfence_system();
+      for (int r = 0; r < c.nranks; ++r)
+        st_release_sys(c.flags[r] + kind * kMaxRanks + c.rank, seq);
+    }
+  }
+}
+
+// MODE 0: gradient all-reduce + optimizer. MODE 1: SMA (source = weights).
+template <int MODE>
+__global__ void __launch_bounds__(512)
+    allreduce_update_kernel(PeerCtx c, long long offset, long long count, uint32_t seq,
+                            float* __restrict__ w, const float* __restrict__ g_local,
+                            float* __restrict__ m, float* __restrict__ v,
+                            __half* __restrict__ w16, HyperParams h,
+                            const float* __restrict__ dyn, const int* __restrict__ skip_flag,
+                            float sma_alpha) {
+  resolve_dyn(h, dyn);
+  const int n = c.nranks;
+  // --- announce: my source data for [offset, offset+count) is final ---
+  if (blockIdx.x == 0 && threadIdx.x < n)
+    st_release_sys(c.flags[threadIdx.x] + FLAG_READY * kMaxRanks + c.rank, seq);
+  wait_flags(c, FLAG_READY, seq);
+
+  // --- phase 1: reduce my shard from every peer, push the result to every rank ---
+  const long long per = ((count + n - 1) / n + 3) & ~3ll;  // shard length, multiple of 4
+  const long long s_begin = offset + per * c.rank;
+  long long s_end = s_begin + per;
+  if (s_end > offset + count) s_end = offset + count;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  const float inv_n = 1.f / static_cast<float>(n);
+  for (long long i = s_begin + tid * 4; i < s_end; i += nthreads * 4) {
+    if (i + 4 <= s_end) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < n) {
+          const float4 x = *reinterpret_cast<const float4*>(c.src[r] + i);
+          acc.x += x.x;
+          acc.y += x.y;
+          acc.z += x.z;
+          acc.w += x.w;
+        }
+      }
+      if (MODE == 1) {
+        acc.x *= inv_n; acc.y *= inv_n; acc.z *= inv_n; acc.w *= inv_n;
+      }
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r)
+        if (r < n) *reinterpret_cast<float4*>(c.reduced[r] + i) = acc;
+    } else {
+      for (long long j = i; j < s_end; ++j) {
+        float acc = 0.f;
+        for (int r = 0; r < n; ++r) acc += c.src[r][j];
+        if (MODE == 1) acc *= inv_n;
+        for (int r = 0; r < n; ++r) c.reduced[r][j] = acc;
+      }
+    }
+  }
+  grid_arrive_and_signal(c, FLAG_REDUCED, seq, 0);
+  wait_flags(c, FLAG_REDUCED, seq);
+
+  // --- phase 2: every rank applies the identical update to its full replica ---
+  const bool skip = (skip_flag != nullptr && *skip_flag != 0);
+  if (!skip) {
+    const float* red = c.reduced[c.rank];
+    for (long long i = offset + tid; i < offset + count; i += nthreads) {
+      float nw;
+      if (MODE == 0) {
+        nw = apply_update(h, w[i], red[i], m, v, i);
+      } else {
+        // SMA: w <- (1-a) w + a * avg(w); then the local gradient step
+        const float blended = (1.f - sma_alpha) * w[i] + sma_alpha * red[i];
+        nw = apply_update(h, blended, g_local[i], m, v, i);
+      }
+      w[i] = nw;
+      if (w16 != nullptr) w16[i] = __float2half_rn(nw);
+    }
+  }
+  // --- done: peers may overwrite their sources / my landing buffer only after everyone is
+  //     through phase 2 (SMA reads w as a source in the next call) ---
+  grid_arrive_and_signal(c, FLAG_DONE, seq, 1);
+  wait_flags(c, FLAG_DONE, seq);
+}
+
+// Pull `count` floats at `offset` from rank `root`'s arena into mine (+ fp16 shadow).
+__global__ void __launch_bounds__(512)
+    broadcast_pull_kernel(PeerCtx c, int root, long long offset, long long count, uint32_t seq,
+                          float* __restrict__ dst, __half* __restrict__ dst16) {
+  if (blockIdx.x == 0 && threadIdx.x < c.nranks)
+    st_release_sys(c.flags[threadIdx.x] + FLAG_READY * kMaxRanks + c.rank, seq);
+  wait_flags(c, FLAG_READY, seq);
+  const float* src = c.src[root];
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = offset + tid; i < offset + count; i += nthreads) {
+    const float x = src[i];
+    if (c.rank != root) dst[i] = x;
+    if (dst16 != nullptr) dst16[i] = __float2half_rn(x);
+  }
+  grid_arrive_and_signal(c, FLAG_DONE, seq, 1);
+  wait_flags(c, FLAG_DONE, seq);
+}
+
+__global__ void device_barrier_kernel(PeerCtx c, uint32_t seq) {
+  if (threadIdx.x < c.nranks) {
+    __threadfence_system();
+    st_release_sys(c.flags[threadIdx.x] + FLAG_BARRIER * kMaxRanks + c.rank, seq);
+  }
+  wait_flags(c, FLAG_BARRIER, seq);
+}
+
+// flag <- OR over ranks of flag (auto loss scale: every rank must take the same skip decision,
+// T/variable_mgr.py:321-332). Each rank posts its value into every page, then reads all.
+__global__ void flag_or_kernel(PeerCtx c, uint32_t seq, int* __restrict__ flag) {
+  constexpr int kPostWord = kCounterWord + 8;  // [src_rank] words after the arrival counters
+  if (threadIdx.x < c.nranks) {
+    *reinterpret_cast<volatile uint32_t*>(c.flags[threadIdx.x] + kPostWord + c.rank) =
+        static_cast<uint32_t>(*flag != 0);
+    __threadfence_system();
+    st_release_sys(c.flags[threadIdx.x] + FLAG_BARRIER * kMaxRanks + c.rank, seq);
+  }
+  wait_flags(c, FLAG_BARRIER, seq);
+  if (threadIdx.x == 0) {
+    uint32_t any = 0;
+    for (int r = 0; r < c.nranks; ++r)
+      any |= *reinterpret_cast<volatile uint32_t*>(c.flags[c.rank] + kPostWord + r);
+    *flag = any ? 1 : 0;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// PairAveraging (AD-PSGD). Each rank publishes its model into a ring of 3 snapshot buffers
+// guarded by {begin, end} version words (a seqlock): version k lives in slot k % 3. A reader
+// picks the peer's newest complete version, reads it, and re-checks `begin`: the slot can only
+// have been overwritten if the writer began version k+3 meanwhile.
+// ---------------------------------------------------------------------------
+struct PairCtx {
+  const float* peer_pub;       // peer's publish ring base (3 * stride floats)
+  const uint32_t* peer_ver;    // peer's {begin, end}
+  float* my_pub;               // my publish ring
+  uint32_t* my_ver;            // my {begin, end}
+  long long stride;            // floats per slot
+};
+
+__global__ void __launch_bounds__(512)
+    pair_average_kernel(PairCtx pc, long long count, float* __restrict__ w,
+                        const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                        __half* __restrict__ w16, HyperParams h, const float* __restrict__ dyn,
+                        uint32_t my_next_version, int has_peer, int* __restrict__ torn_counter) {
+  resolve_dyn(h, dyn);
+  __shared__ uint32_t s_ver;
+  if (threadIdx.x == 0) s_ver = has_peer ? ld_acquire_sys(pc.peer_ver + 1) : 0u;
+  __syncthreads();
+  const uint32_t ver = s_ver;
+  const bool blend = has_peer && ver > 0;  // version 0 = nothing published yet
+  const float* peer = pc.peer_pub + static_cast<long long>(ver % 3u) * pc.stride;
+  float* mine = pc.my_pub + static_cast<long long>(my_next_version % 3u) * pc.stride;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  // every block announces `begin` before its own first store into the slot
+  if (threadIdx.x == 0) st_release_sys(pc.my_ver, my_next_version);
+  __syncthreads();
+  for (long long i = tid; i < count; i += nthreads) {
+    float wi = w[i];
+    if (blend) wi = 0.5f * (wi + peer[i]);
+    const float nw = apply_update(h, wi, g[i], m, v, i);
+    w[i] = nw;
+    if (w16 != nullptr) w16[i] = __float2half_rn(nw);
+    mine[i] = nw;
+  }
+  if (blend && threadIdx.x == 0) {
+    const uint32_t begin_now = ld_acquire_sys(pc.peer_ver);
+    if (begin_now >= ver + 3u) atomicAdd(torn_counter, 1);
+  }
+  // publish: all blocks' stores must be visible before `end` moves
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* counter = pc.my_ver + 2;
+    const uint32_t prev = atomicAdd(counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *counter = 0;
+      __threadfence_system();
+      st_release_sys(pc.my_ver + 1, my_next_version);  // end
+    }
+  }
+}
+
+static int fill_peer_ctx(PeerCtx* c, int rank, int nranks, void* const* src, void* const* reduced,
+                         void* const* flags) {
+  KFB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks && rank >= 0 && rank < nranks,
+              "peer ctx: bad rank %d / %d", rank, nranks);
+  c->rank = rank;
+  c->nranks = nranks;
+  for (int r = 0; r < kMaxRanks; ++r) {
+    c->src[r] = r < nranks ? (float*)src[r] : nullptr;
+    c->reduced[r] = (r < nranks && reduced) ? (float*)reduced[r] : nullptr;
+    c->flags[r] = r < nranks ? (uint32_t*)flags[r] : nullptr;
+  }
+  return 0;
+}
+
+static HyperParams make_hyper(const kfb_hyper* hp) {
+  HyperParams h;
+  h.opt = hp->opt;
+  h.lr = hp->lr;
+  h.momentum = hp->momentum;
+  h.decay = hp->decay;
+  h.epsilon = hp->epsilon;
+  h.weight_decay = hp->weight_decay;
+  h.grad_scale = hp->grad_scale;
+  h.clip = hp->clip;
+  h.adam_t = hp->adam_t;
+  return h;
+}
+
+}  // namespace kfb
+
+using namespace kfb;
+
+extern "C" int kfb_flag_page_bytes(void) { return 4096; }
+
+extern "C" int kfb_optimizer_step(float* w, const float* g, float* m, float* v, void* w16,
+                                  long long n, const kfb_hyper* hp, const float* dyn,
+                                  const int* skip_flag, void* stream) {
+  KFB_REQUIRE(hp != nullptr && hp->opt >= 0 && hp->opt <= 3, "optimizer_step: bad optimizer");
+  long long blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  optimizer_step_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      w, g, m, v, (__half*)w16, n, make_hyper(hp), dyn, skip_flag);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_check_finite(const float* g, long long n, int* flag, void* stream) {
+  long long blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  check_finite_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(g, n, flag);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_loss_scale_update(float* state, int* flag, int inc_every, float* dyn,
+                                     float base_grad_scale, void* stream) {
+  loss_scale_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(state, flag, inc_every, dyn,
+                                                               base_grad_scale);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// mode 0: gradient all-reduce (+optimizer); mode 1: SMA (src = weight arenas, g_local = my grads)
+extern "C" int kfb_allreduce_update(int mode, int rank, int nranks, void* const* src,
+                                    void* const* reduced, void* const* flags, long long offset,
+                                    long long count, unsigned seq, float* w, const float* g_local,
+                                    float* m, float* v, void* w16, const kfb_hyper* hp,
+                                    const float* dyn, const int* skip_flag, float sma_alpha,
+                                    int blocks, void* stream) {
+  KFB_REQUIRE(hp != nullptr, "allreduce_update: null hyper");
+  KFB_REQUIRE(offset % 4 == 0, "allreduce_update: offset must be a multiple of 4 floats");
+  PeerCtx c;
+  if (fill_peer_ctx(&c, rank, nranks, src, reduced, flags)) return 2;
+  if (blocks <= 0) blocks = 32;
+  if (blocks > 128) blocks = 128;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == 0)
+    allreduce_update_kernel<0><<<blocks, 512, 0, st>>>(c, offset, count, seq, w, g_local, m, v,
+                                                       (__half*)w16, make_hyper(hp), dyn,
+                                                       skip_flag, sma_alpha);
+  else
+    allreduce_update_kernel<1><<<blocks, 512, 0, st>>>(c, offset, count, seq, w, g_local, m, v,
+                                                       (__half*)w16, make_hyper(hp), dyn,
+                                                       skip_flag, sma_alpha);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_broadcast_pull(int rank, int nranks, void* const* src, void* const* flags,
+                                  int root, long long offset, long long count, unsigned seq,
+                                  float* dst, void* dst16, int blocks, void* stream) {
+  PeerCtx c;
+  if (fill_peer_ctx(&c, rank, nranks, src, nullptr, flags)) return 2;
+  if (blocks <= 0) blocks = 64;
+  broadcast_pull_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(c, root, offset, count, seq,
+                                                                  dst, (__half*)dst16);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_device_barrier(int rank, int nranks, void* const* flags, unsigned seq,
+                                  void* stream) {
+  PeerCtx c;
+  if (fill_peer_ctx(&c, rank, nranks, flags, nullptr, flags)) return 2;
+  device_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(c, seq);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_flag_or(int rank, int nranks, void* const* flags, unsigned seq, int* flag,
+                           void* stream) {
+  PeerCtx c;
+  if (fill_peer_ctx(&c, rank, nranks, flags, nullptr, flags)) return 2;
+  flag_or_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(c, seq, flag);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_pair_average_update(const float* peer_pub, const unsigned* peer_ver,
+                                       float* my_pub, unsigned* my_ver, long long stride,
+                                       long long count, float* w, const float* g, float* m,
+                                       float* v, void* w16, const kfb_hyper* hp, const float* dyn,
+                                       unsigned my_next_version, int has_peer, int* torn_counter,
+                                       int blocks, void* stream) {
+  KFB_REQUIRE(hp != nullptr, "pair_average_update: null hyper");
+  PairCtx pc;
+  pc.peer_pub = peer_pub;
+  pc.peer_ver = peer_ver;
+  pc.my_pub = my_pub;
+  pc.my_ver = my_ver;
+  pc.stride = stride;
+  if (blocks <= 0) blocks = 64;
+  pair_average_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(
+      pc, count, w, g, m, v, (__half*)w16, make_hyper(hp), dyn, my_next_version, has_peer,
+      torn_counter);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Symmetric-memory runtime: device allocations exported over CUDA IPC.
+// ---------------------------------------------------------------------------
+extern "C" int kfb_symm_alloc(long long bytes, void** out) {
+  KFB_REQUIRE(bytes > 0 && out != nullptr, "symm_alloc: bad arguments");
+  void* p = nullptr;
+  KFB_CHECK_CUDA(cudaMalloc(&p, (size_t)bytes));
+  KFB_CHECK_CUDA(cudaMemset(p, 0, (size_t)bytes));
+  KFB_CHECK_CUDA(cudaDeviceSynchronize());
+  *out = p;
+  return 0;
+}
+
+extern "C" int kfb_symm_free(void* p) {
+  KFB_CHECK_CUDA(cudaFree(p));
+  return 0;
+}
+
+extern "C" int kfb_ipc_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
+
+extern "C" int kfb_ipc_get_handle(void* p, void* handle_out) {
+  cudaIpcMemHandle_t h;
+  KFB_CHECK_CUDA(cudaIpcGetMemHandle(&h, p));
+  memcpy(handle_out, &h, sizeof(h));
+  return 0;
+}
+
+extern "C" int kfb_ipc_open(const void* handle, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  void* p = nullptr;
+  KFB_CHECK_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *out = p;
+  return 0;
+}
+
+extern "C" int kfb_ipc_close(void* p) {
+  KFB_CHECK_CUDA(cudaIpcCloseMemHandle(p));
+  return 0;
+}
+
+extern "C" int kfb_enable_peer_access(int peer_device) {
+  int dev = 0;
+  KFB_CHECK_CUDA(cudaGetDevice(&dev));
+  if (peer_device == dev) return 0;
+  int can = 0;
+  KFB_CHECK_CUDA(cudaDeviceCanAccessPeer(&can, dev, peer_device));
+  KFB_REQUIRE(can, "device %d cannot access peer %d", dev, peer_device);
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    return 0;
+  }
+  KFB_CHECK_CUDA(e);
+  return 0;
+}

@@ -37,6 +37,10 @@ int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, int K, long
                 long long ldb, long long ldc, const float* bias, int relu, int out_fp32,
                 void* stream);
 
+/* C[M,N] (+)= A[M,K] * B[K,N]; B is consumed in place as an MN-major operand (FC dgrad). */
+int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
+                long long ldb, long long ldc, int out_fp32, int accumulate, void* stream);
+
 /* C[M,N] (fp32) (+)= scale * A[K,M]^T * B[K,N]; K is split across CTAs into `workspace`
  * (fp32 slices of M*N) and reduced in a fixed order. FC weight gradient. */
 int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N, int K, long long lda,
@@ -47,15 +51,153 @@ int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N, int K, lon
 int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void* w, void* y, long long ldy,
                    const float* bias, int relu, void* stream);
 
-/* dx = conv^T(dy, w) (autodiff of the above, T/benchmark_cnn.py:3104). For stride > 1 only
- * 1x1 un-padded filters are supported and dx must be zero-filled by the caller. */
-int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void* w, void* dx, void* stream);
+/* dx (+)= conv^T(dy, w) (autodiff of the above, T/benchmark_cnn.py:3104). Strided convolutions
+ * run one launch per output phase. When kfb_conv_dgrad_needs_zero_fill(d) is non-zero some
+ * pixels of dx receive no contribution and, without `accumulate`, the caller zero-fills dx
+ * first. */
+int kfb_conv_dgrad_needs_zero_fill(const kfb_conv_desc* d);
+int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void* w, void* dx,
+                   int accumulate, void* stream);
 
 /* dw (fp32, OHWI) (+)= scale * x^T (*) dy, split over pixels into `workspace`. */
 long long kfb_conv_wgrad_workspace_bytes(const kfb_conv_desc* d);
 int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void* dy, long long lddy,
                    float* dw, float* workspace, long long workspace_bytes, int accumulate,
                    float scale, void* stream);
+
+/* ------------------------------------------------------------------ */
+/* Memory-bound layer kernels (csrc/nn_kernels.cu). Tensors are viewed */
+/* as [rows][C] fp16 with an explicit row stride; C % 8 == 0.          */
+/* ------------------------------------------------------------------ */
+
+/* Number of stage-1 blocks the per-channel reductions use; scratch buffers passed to the
+ * entry points below must hold kfb_reduce_blocks(rows, C) * 2 * C floats. */
+int kfb_reduce_blocks(long long rows, int C);
+
+/* Training-mode batch norm fused with ReLU and residual add:
+ * y = act(gamma * (x - mean) * rstd + beta (+ residual)); updates the moving statistics.
+ * T/convnet_builder_legacy.py:393-459 (fused_batch_norm + assign_moving_average). */
+int kfb_bn_forward_train(const void* x, long long ldx, long long rows, int C, const float* gamma,
+                         const float* beta, float* moving_mean, float* moving_var, float eps,
+                         float decay, int update_moving, float* mean_rstd, float* scale_shift,
+                         float* scratch, const void* residual, long long ldr, int relu, void* y,
+                         long long ldy, void* stream);
+int kfb_bn_forward_inference(const void* x, long long ldx, long long rows, int C,
+                             const float* gamma, const float* beta, const float* moving_mean,
+                             const float* moving_var, float eps, float* scale_shift,
+                             const void* residual, long long ldr, int relu, void* y,
+                             long long ldy, void* stream);
+/* Backward of the fused op above: dgamma/dbeta, dz (grad wrt x) and optionally the residual
+ * gradient. `mask` is the forward output when ReLU was applied. coef: 3*C floats. */
+int kfb_bn_backward(const void* dy, long long lddy, const void* mask, long long ldm, const void* x,
+                    long long ldx, long long rows, int C, const float* gamma,
+                    const float* mean_rstd, float* dgamma, float* dbeta,
+                    int accumulate_param_grads, float grad_scale, float* coef, float* scratch,
+                    void* dz, long long lddz, void* dres, long long lddr, int dres_accumulate,
+                    void* stream);
+/* dz = dy * (mask > 0); dbias (+)= scale * column sums of dz (conv/FC bias + ReLU backward). */
+int kfb_bias_act_backward(const void* dy, long long lddy, const void* mask, long long ldm,
+                          long long rows, int C, void* dz, long long lddz, float* dbias,
+                          int accumulate, float scale, float* scratch, void* stream);
+int kfb_add_act(const void* a, long long lda, const void* b, long long ldb, void* y, long long ldy,
+                long long rows, int C, int relu, void* stream);
+int kfb_relu_backward(const void* dy, long long lddy, const void* mask, long long ldm, void* dx,
+                      long long lddx, int accumulate, long long rows, int C, void* stream);
+/* Max / average pooling, NHWC (T/convnet_builder_legacy.py:228-286). argmax: uint8 [N,P,Q,C]. */
+int kfb_pool_forward(const void* x, long long ldx, void* y, long long ldy, unsigned char* argmax,
+                     int n, int h, int w, int c, int p, int q, int kh, int kw, int sh, int sw,
+                     int pad_h, int pad_w, int is_max, void* stream);
+int kfb_pool_backward(const void* dy, long long lddy, const unsigned char* argmax, void* dx,
+                      long long lddx, int accumulate, int n, int h, int w, int c, int p, int q,
+                      int kh, int kw, int sh, int sw, int pad_h, int pad_w, int is_max,
+                      void* stream);
+int kfb_spatial_mean_forward(const void* x, long long ldx, void* y, long long ldy, int n, int hw,
+                             int C, void* stream);
+int kfb_spatial_mean_backward(const void* dy, long long lddy, void* dx, long long lddx,
+                              int accumulate, int n, int hw, int C, void* stream);
+/* Strided 2-D copy / accumulate (concat, split). */
+int kfb_copy2d(const void* src, long long lds, void* dst, long long ldd, long long rows, int C,
+               int accumulate, void* stream);
+/* Row copy with arbitrary column count / strides (flatten into 8-padded rows). */
+int kfb_copy_rows(const void* src, long long lds, void* dst, long long ldd, long long rows,
+                  long long cols, int accumulate, void* stream);
+/* Explicit im2col for stems whose input channel count is not a multiple of 8. */
+int kfb_im2col_small_c(const void* x, void* col, int n, int h, int w, int c, int p, int q, int kh,
+                       int kw, int sh, int sw, int pad_h, int pad_w, int kpad, void* stream);
+/* Philox dropout; the backward pass calls it again on dy with the same (seed, offset). */
+int kfb_dropout(const void* x, void* y, long long n, float keep_prob, unsigned long long seed,
+                unsigned long long offset, void* stream);
+/* Synthetic inputs generated on the device (T/models/model.py:220-237). */
+int kfb_synth_images(void* out, long long n, float mean, float stddev, unsigned long long seed,
+                     void* stream);
+int kfb_synth_labels(int* out, int n, int lo, int hi, unsigned long long seed, void* stream);
+int kfb_lrn_forward(const void* x, void* y, long long rows, int C, int radius, float bias,
+                    float alpha, float beta, void* stream);
+int kfb_lrn_backward(const void* x, const void* dy, void* dx, int accumulate, long long rows,
+                     int C, int radius, float bias, float alpha, float beta, void* stream);
+/* Sparse softmax cross-entropy, mean loss, fused gradient (x grad_scale) and top-1/top-5 hits
+ * (T/models/model.py:285-312, loss-scale multiply of T/benchmark_cnn.py:3102-3103).
+ * out3 = {mean loss, #top-1 hits, #top-5 hits}. dyn_scale (device, optional) multiplies
+ * grad_scale (device-resident loss scale). */
+int kfb_softmax_xent(const float* logits, long long ldl, const int* labels, int rows, int classes,
+                     float grad_scale, const float* dyn_scale, void* dlogits, long long lddl,
+                     float* loss_rows, int* top1, int* top5, float* out3, void* stream);
+int kfb_cast_f32_f16(const float* in, void* out, long long n, void* stream);
+
+/* ------------------------------------------------------------------ */
+/* Optimizers, P2P collectives, symmetric memory (csrc/optim_comm.cu)  */
+/* ------------------------------------------------------------------ */
+
+typedef struct {
+  int opt;            /* 0 sgd, 1 momentum (Nesterov), 2 rmsprop, 3 adam */
+  float lr;
+  float momentum;     /* momentum | rmsprop momentum | adam beta1 */
+  float decay;        /* rmsprop decay | adam beta2 */
+  float epsilon;
+  float weight_decay; /* g += weight_decay * w (the L2 term of T/benchmark_cnn.py:3068-3099) */
+  float grad_scale;   /* multiplies the reduced gradient (1/loss_scale, 1/N for mean modes) */
+  float clip;         /* elementwise clip_by_value bound, <= 0 disables */
+  float adam_t;       /* step count for Adam bias correction */
+} kfb_hyper;
+
+/* Fused optimizer over a flat arena; dyn (device, optional) = {lr, grad_scale, adam_t, -}
+ * overrides the by-value fields; skip_flag (device, optional) != 0 skips the update. */
+int kfb_optimizer_step(float* w, const float* g, float* m, float* v, void* w16, long long n,
+                       const kfb_hyper* hp, const float* dyn, const int* skip_flag, void* stream);
+int kfb_check_finite(const float* g, long long n, int* flag, void* stream);
+int kfb_loss_scale_update(float* state, int* flag, int inc_every, float* dyn,
+                          float base_grad_scale, void* stream);
+
+/* Two-shot P2P all-reduce over mapped peer arenas fused with the optimizer (mode 0), or
+ * SynchronousAveraging of the model (mode 1). src / reduced / flags are host arrays of
+ * nranks device pointers (peer mappings); seq must increase by one per collective call and
+ * be identical on every rank. */
+int kfb_flag_page_bytes(void);
+int kfb_allreduce_update(int mode, int rank, int nranks, void* const* src, void* const* reduced,
+                         void* const* flags, long long offset, long long count, unsigned seq,
+                         float* w, const float* g_local, float* m, float* v, void* w16,
+                         const kfb_hyper* hp, const float* dyn, const int* skip_flag,
+                         float sma_alpha, int blocks, void* stream);
+int kfb_broadcast_pull(int rank, int nranks, void* const* src, void* const* flags, int root,
+                       long long offset, long long count, unsigned seq, float* dst, void* dst16,
+                       int blocks, void* stream);
+int kfb_device_barrier(int rank, int nranks, void* const* flags, unsigned seq, void* stream);
+int kfb_flag_or(int rank, int nranks, void* const* flags, unsigned seq, int* flag, void* stream);
+/* PairAveraging (AD-PSGD): blend with one peer's published model, local step, publish. */
+int kfb_pair_average_update(const float* peer_pub, const unsigned* peer_ver, float* my_pub,
+                            unsigned* my_ver, long long stride, long long count, float* w,
+                            const float* g, float* m, float* v, void* w16, const kfb_hyper* hp,
+                            const float* dyn, unsigned my_next_version, int has_peer,
+                            int* torn_counter, int blocks, void* stream);
+
+/* Symmetric memory over CUDA IPC (cudaMalloc'd, zero-filled). */
+int kfb_symm_alloc(long long bytes, void** out);
+int kfb_symm_free(void* p);
+int kfb_ipc_handle_bytes(void);
+int kfb_ipc_get_handle(void* p, void* handle_out);
+int kfb_ipc_open(const void* handle, void** out);
+int kfb_ipc_close(void* p);
+int kfb_enable_peer_access(int peer_device);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,558 @@
+"""BenchmarkCNN: the benchmark driver (training loop, evaluation, logging, checkpoints).
+
+Capabilities and text output follow the reference driver (T/benchmark_cnn.py:1233-2391):
+the same flag-combination rules, header block, ``images/sec: m +/- u (jitter = j)`` step
+lines, ``total images/sec`` footer and returned stats dict. What differs is the
+machinery: one process per GPU, a static kernel schedule instead of ``sess.run``,
+CUDA-event timing (max over ranks for the totals) instead of host wall-clock, and the
+fused NVLink update kernels instead of TF's gradient-aggregation graph.
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from . import ckpt as ckpt_lib
+from . import datasets, lr as lr_mod
+from .constants import BenchmarkMode
+from .models import model_config
+from .nn.params import ParameterStore
+from .parallel import comm as comm_lib
+from .parallel.strategy import UpdateEngine, reduction_semantics
+from .params import IGNORED_ON_B200, UNSUPPORTED_WHEN_SET, make_params
+from .utils import log_util
+from .utils.log_util import log_fn  # noqa: F401  (re-exported, monkey-patchable via log_util)
+
+_NUM_STEPS_TO_PROFILE = 10
+
+
+def _log(msg: str) -> None:
+    log_util.log_fn(msg)
+
+
+def get_mode_from_params(params) -> str:
+    if params.forward_only and params.eval:
+        raise ValueError("Only one of forward_only and eval parameters is true")
+    if params.eval:
+        return BenchmarkMode.EVAL
+    if params.forward_only:
+        return BenchmarkMode.FORWARD_ONLY
+    if (params.eval_during_training_every_n_steps or params.eval_during_training_every_n_epochs or
+            params.eval_during_training_at_specified_steps or
+            params.eval_during_training_at_specified_epochs):
+        return BenchmarkMode.TRAIN_AND_EVAL
+    return BenchmarkMode.TRAIN
+
+
+def setup(params):
+    """Process-level setup (T/benchmark_cnn.py:3356-3395): thread counts, unsupported-flag
+    checks. Returns the (possibly adjusted) params."""
+    for name, why in UNSUPPORTED_WHEN_SET.items():
+        if getattr(params, name):
+            raise ValueError("--%s: %s" % (name, why))
+    if params.num_intra_threads:
+        torch.set_num_threads(int(params.num_intra_threads))
+    return params
+
+
+class BenchmarkCNN:
+    def __init__(self, params, dataset=None, model=None):
+        self.params = params
+        p = params
+        self.dataset = dataset or datasets.create_dataset(p.data_dir, p.data_name)
+        self.model = model or model_config.get_model_config(p.model, self.dataset, p)
+        a = p.autotune_threshold if p.autotune_threshold else 1
+        self.num_warmup_batches = (p.num_warmup_batches if p.num_warmup_batches is not None
+                                   else max(10, 5 * a * a))
+        self.num_gpus = p.num_gpus
+        self.device_kind = p.device.lower()
+        self._validate()
+        if p.batch_size > 0:
+            self.model.set_batch_size(p.batch_size)
+        self.mode = get_mode_from_params(p)
+        # ---- process model: one rank per device --------------------------------
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", str(self.rank)))
+        if p.variable_update in ("kungfu", "horovod"):
+            self.num_workers = self.world      # num_gpus == 1 per worker
+            self.replicas_per_worker = 1
+        else:
+            self.num_workers = 1
+            self.replicas_per_worker = max(self.world, 1)
+            if self.world > 1 and self.world != p.num_gpus:
+                raise ValueError("launched %d ranks but --num_gpus=%d" % (self.world, p.num_gpus))
+        self.batch_size_per_device = self.model.get_batch_size()
+        self.batch_size = self.batch_size_per_device * self.num_gpus  # per worker, as reference
+        if self.device_kind == "gpu":
+            if not torch.cuda.is_available():
+                raise RuntimeError("--device=gpu but no CUDA device is visible "
+                                   "(use --device=cpu --data_format=NHWC for the CPU path)")
+            idx = self.local_rank
+            if p.gpu_indices:
+                idx = [int(x) for x in p.gpu_indices.split(",")][self.local_rank]
+            self.device = torch.device("cuda", idx)
+            torch.cuda.set_device(self.device)
+        else:
+            self.device = torch.device("cpu")
+        self.enable_auto_loss_scale = p.use_fp16 and p.fp16_enable_auto_loss_scale
+        self.num_batches, self.num_epochs = lr_mod.get_num_batches_and_epochs(
+            p, self.batch_size * self.num_workers,
+            self.dataset.num_examples_per_epoch("train"))
+        self.eval_steps = self._eval_schedule()
+        self.comm = None
+        self.store = None
+        self.executor = None
+        self.engine = None
+        self.global_step = 0
+        self.seed = p.tf_random_seed
+        if p.variable_update in ("kungfu", "horovod"):
+            self.seed += self.rank  # T/benchmark_cnn.py:2625-2636
+
+    # ------------------------------------------------------------------ validation
+    def _validate(self) -> None:
+        """Flag-combination rules of T/benchmark_cnn.py:1268-1352."""
+        p = self.params
+        if p.device.lower() == "cpu" and p.data_format == "NCHW" and not p.mkl:
+            raise ValueError("device=cpu requires that data_format=NHWC")
+        if ((p.num_epochs_per_decay or p.learning_rate_decay_factor) and
+                not (p.init_learning_rate is not None and p.num_epochs_per_decay and
+                     p.learning_rate_decay_factor)):
+            raise ValueError("If one of num_epochs_per_decay or learning_rate_decay_factor is "
+                             "set, both must be set and learning_rate must be set")
+        if (p.minimum_learning_rate and
+                not (p.init_learning_rate is not None and p.num_epochs_per_decay and
+                     p.learning_rate_decay_factor)):
+            raise ValueError("minimum_learning_rate requires learning_rate, "
+                             "num_epochs_per_decay, and learning_rate_decay_factor to be set")
+        if (p.use_fp16 and p.fp16_vars and "replicated" in p.variable_update and
+                p.all_reduce_spec and "nccl" in p.all_reduce_spec):
+            raise ValueError("fp16 variables are not supported with NCCL")
+        if p.use_fp16 and p.fp16_vars and p.gradient_repacking:
+            raise ValueError("--fp16_vars cannot be used with --gradient_repacking")
+        if p.variable_update == "horovod" and p.num_gpus > 1:
+            raise ValueError("Horovod benchmarks require num_gpus=1 on each worker")
+        if p.variable_update == "horovod" and p.job_name:
+            raise ValueError("job_name should not be specified for Horovod.")
+        if p.variable_update == "kungfu" and p.num_gpus > 1:
+            raise ValueError("KungFu benchmarks require num_gpus=1 on each worker")
+        if p.variable_update == "kungfu" and p.job_name:
+            raise ValueError("job_name should not be specified for KungFu.")
+        if p.use_fp16 and p.fp16_enable_auto_loss_scale:
+            if p.all_reduce_spec and "nccl" in p.all_reduce_spec:
+                raise ValueError("Automatic loss scaling is not supported with NCCL.")
+            if p.variable_update not in ("parameter_server", "replicated", "independent"):
+                raise ValueError("Automatic loss scaling is not supported with "
+                                 "variable_update=%s." % p.variable_update)
+            if p.staged_vars:
+                raise ValueError("Automatic loss scaling is not supported with staged_vars.")
+        if p.debugger is not None and p.debugger != "cli" and ":" not in p.debugger:
+            raise ValueError('--debugger must be "cli" or in the form host:port')
+        if p.hierarchical_copy and p.num_gpus <= 1:
+            raise ValueError("--hierarchical_copy requires --num_gpus to be greater than 1")
+        if p.save_model_secs and p.save_model_steps:
+            raise ValueError("At most one of --save_model_secs and --save_model_steps can be "
+                             "specified")
+        ev = [bool(p.eval_during_training_every_n_steps),
+              bool(p.eval_during_training_every_n_epochs),
+              bool(p.eval_during_training_at_specified_steps),
+              bool(p.eval_during_training_at_specified_epochs)]
+        if ev.count(True) > 1:
+            raise ValueError("At most one flag with --eval_during_training_* prefix must be "
+                             "specified.")
+        if any(ev):
+            if p.eval:
+                raise ValueError("At most one of --eval and --eval_during_training_* must be "
+                                 "specified")
+            if p.forward_only:
+                raise ValueError("At most one of --forward_only and --eval_during_training_* "
+                                 "must be specified")
+            if p.job_name:
+                raise ValueError("--eval_during_training_* is not yet supported in distributed "
+                                 "mode.")
+            if p.staged_vars:
+                raise ValueError("--eval_during_training_* is not currently compatible with "
+                                 "staged_vars")
+        if p.stop_at_top_1_accuracy and not any(ev):
+            raise ValueError("--stop_at_top_1_accuracy is only supported with "
+                             "--eval_during_training_*")
+        if p.forward_only and p.freeze_when_forward_only:
+            if p.train_dir is not None:
+                raise ValueError("In forward_only mode, when --freeze_when_forward_only is True, "
+                                 "--train_dir should not be specified")
+        elif p.trt_mode:
+            raise ValueError("--trt_mode should not be specified if one of --forward_only and "
+                             "--freeze_when_forward_only is set to False")
+        if p.staged_vars and p.variable_update != "parameter_server":
+            raise ValueError("staged_vars for now is only supported with "
+                             "variable_update=parameter_server")
+        if p.all_reduce_spec:
+            from .parallel import allreduce_spec
+            allreduce_spec.parse_all_reduce_spec(p.all_reduce_spec)  # syntax check
+
+    def _eval_schedule(self):
+        p = self.params
+        per_epoch = self.dataset.num_examples_per_epoch("train") / float(
+            self.batch_size * max(self.num_workers, 1))
+        if p.eval_during_training_every_n_steps:
+            n = p.eval_during_training_every_n_steps
+            return set(range(n, self.num_batches + 1, n))
+        if p.eval_during_training_every_n_epochs:
+            n = max(int(p.eval_during_training_every_n_epochs * per_epoch), 1)
+            return set(range(n, self.num_batches + 1, n))
+        if p.eval_during_training_at_specified_steps:
+            return set(int(x) for x in p.eval_during_training_at_specified_steps)
+        if p.eval_during_training_at_specified_epochs:
+            return set(max(int(float(x) * per_epoch), 1)
+                       for x in p.eval_during_training_at_specified_epochs)
+        return set()
+
+    # ------------------------------------------------------------------ info
+    def print_info(self) -> None:
+        """T/benchmark_cnn.py:1633-1666."""
+        p = self.params
+        if self.rank != 0:
+            return
+        _log("Model:       %s" % self.model.get_model_name())
+        subset = "validation" if p.eval else "train"
+        ds = self.dataset.name + (" (synthetic)" if self.dataset.use_synthetic_gpu_inputs() else "")
+        _log("Dataset:     %s" % ds)
+        _log("Mode:        %s" % self.mode)
+        _log("SingleSess:  %s" % False)
+        _log("Batch size:  %s global" % (self.batch_size * self.num_workers))
+        _log("             %s per device" % self.batch_size_per_device)
+        if p.batch_group_size > 1:
+            _log("             %d batches per prepocessing group" % p.batch_group_size)
+        _log("Num batches: %d" % self.num_batches)
+        _log("Num epochs:  %.2f" % self.num_epochs)
+        kind = "gpu" if self.device_kind == "gpu" else "cpu"
+        _log("Devices:     %s" % ["/%s:%d" % (kind, i) for i in range(self.num_gpus)])
+        _log("Data format: %s" % ("NHWC" if True else p.data_format))
+        _log("Optimizer:   %s" % p.optimizer)
+        _log("Variables:   %s" % p.variable_update)
+        if p.variable_update in ("replicated", "distributed_all_reduce", "collective_all_reduce"):
+            _log("AllReduce:   %s" % p.all_reduce_spec)
+        if p.variable_update == "kungfu":
+            _log("KungFu option: %s" % p.kungfu_option)
+        _log("==========")
+        for name in IGNORED_ON_B200:
+            from . import flags
+            if getattr(p, name) != flags.param_specs[name].default_value:
+                _log("note: --%s has no effect on the B200-native runtime" % name)
+
+    # ------------------------------------------------------------------ build
+    def _build(self, phase_train: bool) -> None:
+        p = self.params
+        _log_rank0 = _log if self.rank == 0 else (lambda *_: None)
+        _log_rank0("Generating training model" if phase_train else "Generating model")
+        nclass = self.dataset.num_classes
+        self.nclass = nclass
+        self.graph = self.model.build_graph(nclass, phase_train=phase_train,
+                                            batch_size=self.batch_size_per_device)
+        self.comm = comm_lib.create_comm(p, self.device)
+        self.store = ParameterStore(self.graph, self.device,
+                                    fp16_shadow=self.device.type == "cuda",
+                                    allocator=self.comm.allocator())
+        _log_rank0("Initializing graph")
+        self.store.initialize(self.seed)
+        if self.device.type == "cuda":
+            from .nn.executor_cuda import CudaExecutor
+            self.executor = CudaExecutor(self.graph, self.store, nclass,
+                                         aux_weight=self.model.aux_loss_weight,
+                                         dropout_seed=4321 + self.rank)
+        else:
+            from .nn.executor_ref import RefExecutor
+            self.executor = RefExecutor(self.graph, self.store, nclass,
+                                        aux_weight=self.model.aux_loss_weight,
+                                        dropout_seed=4321 + self.rank)
+        self.engine = UpdateEngine(p, self.store, self.comm, self.model, seed=self.seed)
+        self.input_source = self._make_input_source(phase_train)
+
+    def _make_input_source(self, train: bool):
+        from .data import inputs
+        return inputs.create_input_source(self.params, self.dataset, self.model,
+                                          self.batch_size_per_device, self.device, self.nclass,
+                                          seed=self.seed, rank=self.rank,
+                                          world=max(self.world, 1), train=train)
+
+    # ------------------------------------------------------------------ run
+    def run(self) -> Dict:
+        """Runs the benchmark and returns the stats dict (T/benchmark_cnn.py:1726-1755)."""
+        try:
+            if self.params.eval:
+                return self._run_eval()
+            return self._benchmark_train()
+        finally:
+            if self.comm is not None:
+                self.comm.close()
+
+    def _examples_per_step(self) -> int:
+        """Batch size the LR schedule sees (T/benchmark_cnn.py:2757-2765)."""
+        if self.params.variable_update in ("kungfu", "horovod", "collective_all_reduce"):
+            return self.batch_size * self.num_workers
+        return self.batch_size
+
+    def _maybe_restore(self) -> None:
+        p = self.params
+        if not p.train_dir:
+            return
+        try:
+            path, step = ckpt_lib.latest_checkpoint(p.train_dir)
+        except ckpt_lib.CheckpointNotFoundException:
+            return
+        arrays = ckpt_lib.load_arrays(path)
+        self.store.from_tf_arrays(arrays, strict=False)
+        self.global_step = int(arrays.get("global_step", step))
+        if self.rank == 0:
+            _log("Restored checkpoint %s (global_step %d)" % (path, self.global_step))
+
+    def _save(self) -> None:
+        p = self.params
+        if not p.train_dir or self.rank != 0:
+            return
+        extra = {"global_step": np.asarray(self.global_step, dtype=np.int64)}
+        if self.engine is not None and (self.engine.auto_loss_scale or self.engine.loss_scale != 1):
+            extra["loss_scale"] = np.asarray(self.engine.loss_scale, dtype=np.float32)
+            extra["loss_scale_normal_steps"] = np.asarray(self.engine.loss_scale_normal_steps,
+                                                          dtype=np.int64)
+        path = ckpt_lib.save_checkpoint(p.train_dir, self.global_step, self.store, extra,
+                                        max_to_keep=p.max_ckpts_to_keep,
+                                        opt_slots=self._opt_slot_arrays())
+        _log("Saved checkpoint %s" % path)
+
+    def _opt_slot_arrays(self):
+        names = {"momentum": {"m": "Momentum"}, "rmsprop": {"v": "RMSProp", "m": "RMSProp_1"},
+                 "adam": {"m": "Adam", "v": "Adam_1"}, "sgd": {}}[self.params.optimizer]
+        out = {}
+        for key, suffix in names.items():
+            if key in self.store.opt_slots:
+                out[suffix] = self.store.opt_slots[key]
+        return out
+
+    def _step(self, train: bool = True, backward: bool = True) -> None:
+        """One step on this rank: inputs -> forward -> loss/backward -> exchange + update."""
+        ex, eng = self.executor, self.engine
+        images, labels = self.input_source.next_batch()
+        ex.set_inputs(images, labels)
+        ex.forward(train)
+        if not backward:
+            ex.loss_backward(backward=False)
+            return
+        lr = eng.learning_rate(self.global_step, self._examples_per_step(),
+                               self.dataset.num_examples_per_epoch("train"))
+        eng.begin_step(lr)
+        ex.loss_backward(loss_scale=eng.loss_scale, on_grads_ready=eng.on_grads_ready)
+        eng.finish_step()
+        self.global_step += 1
+
+    def _benchmark_train(self) -> Dict:
+        p = self.params
+        forward_only = bool(p.forward_only)
+        self._build(phase_train=not forward_only)
+        self._maybe_restore()
+        self.engine.broadcast_initial_variables()
+        rank0 = self.rank == 0
+        cuda = self.device.type == "cuda"
+        profiler = None
+        if p.tfprof_file or p.trace_file:
+            from .utils import profile as profile_lib
+            profiler = profile_lib.StepProfiler(p, self.device)
+        if rank0:
+            _log("Running warm up")
+        step_train_times: List[float] = []
+        loop_start = None
+        display = max(int(p.display_every), 1)
+        accuracy_cols = bool(p.print_training_accuracy or forward_only)
+        last_save_time = time.time()
+        ev_start = ev_end = None
+        pending = []  # (event_start, event_end) of steps whose time has not been read yet
+        n_done = 0
+        stop_early = False
+        for local_step in range(-self.num_warmup_batches, self.num_batches):
+            if local_step == 0:
+                self._sync()
+                self.comm.barrier()
+                if rank0:
+                    _log("Done warm up")
+                    _log(log_util.header_line(accuracy_cols, p.loss_type_to_report))
+                loop_start = time.time()
+            if profiler is not None:
+                profiler.before_step(local_step)
+            if cuda:
+                ev_start, ev_end = torch.cuda.Event(enable_timing=True), \
+                    torch.cuda.Event(enable_timing=True)
+                ev_start.record()
+            else:
+                t0 = time.time()
+            self._step(train=not forward_only, backward=not forward_only)
+            if cuda:
+                ev_end.record()
+                if p.sync_on_finish:
+                    ev_end.synchronize()
+            else:
+                step_time = time.time() - t0
+            if profiler is not None:
+                profiler.after_step(local_step)
+            if local_step < 0:
+                continue
+            n_done += 1
+            if cuda:
+                pending.append((ev_start, ev_end))
+            else:
+                step_train_times.append(step_time)
+            step1 = local_step + 1
+            if step1 == 1 or step1 % display == 0 or step1 == self.num_batches:
+                if cuda:
+                    ev_end.synchronize()
+                    step_train_times.extend(s.elapsed_time(e) / 1e3 for s, e in pending)
+                    pending = []
+                if (step1 == 1 or step1 % display == 0) and rank0:
+                    loss, t1, t5 = self.executor.read_loss()
+                    loss = self._reported_loss(loss)
+                    n = self.batch_size_per_device
+                    _log(log_util.step_line(
+                        step1, self.batch_size, step_train_times, loss,
+                        t1 / n if accuracy_cols else None, t5 / n if accuracy_cols else None))
+            if p.save_model_steps and step1 % p.save_model_steps == 0:
+                self._save()
+            elif p.save_model_secs and time.time() - last_save_time >= p.save_model_secs:
+                self._save()
+                last_save_time = time.time()
+            if step1 in self.eval_steps:
+                acc = self._eval_during_training()
+                if p.stop_at_top_1_accuracy and acc["top_1_accuracy"] >= p.stop_at_top_1_accuracy:
+                    if rank0:
+                        _log("Stopping, as eval accuracy at least %s was reached" %
+                             p.stop_at_top_1_accuracy)
+                    stop_early = True
+            if stop_early:
+                break
+        self._sync()
+        if cuda and pending:
+            step_train_times.extend(s.elapsed_time(e) / 1e3 for s, e in pending)
+        # device-timed total: sum of this rank's step times, max over ranks
+        local_elapsed = float(np.sum(step_train_times)) if step_train_times else 0.0
+        elapsed = self.comm.max_over_ranks(local_elapsed)
+        num_steps = n_done
+        total_replicas = self.num_workers * self.replicas_per_worker \
+            if p.variable_update not in ("kungfu", "horovod") else self.num_workers
+        images_per_sec = (total_replicas * num_steps * self.batch_size_per_device /
+                          elapsed) if elapsed > 0 else 0.0
+        loss, t1, t5 = self.executor.read_loss()
+        loss = self._reported_loss(loss)
+        if rank0:
+            _log("-" * 64)
+            _log("total images/sec: %.2f" % images_per_sec)
+            _log("-" * 64)
+        if profiler is not None:
+            profiler.finish()
+        if p.train_dir and not forward_only:
+            self._save()
+        if self.engine.algo == "pair" and hasattr(self.engine, "torn") and rank0:
+            torn = int(self.engine.torn.item())
+            if torn:
+                _log("PairAveraging: %d model pulls raced with a publish" % torn)
+        stats = {
+            "num_workers": self.num_workers, "num_steps": num_steps,
+            "average_wall_time": elapsed / max(num_steps, 1),
+            "images_per_sec": images_per_sec, "last_average_loss": loss,
+            "loss_scale": self.engine.loss_scale, "skipped_steps": self.engine.skipped_steps,
+        }
+        if p.benchmark_log_dir and rank0:
+            from .utils import benchmark_logger
+            benchmark_logger.write(p, stats, self)
+        return stats
+
+    def _reported_loss(self, base_loss: float) -> float:
+        """total_loss adds the L2 term (T/benchmark_cnn.py:3068-3099); it is only evaluated
+        when a loss is reported, never inside the timed kernels."""
+        p = self.params
+        if p.loss_type_to_report == "base_loss" or not p.weight_decay or p.forward_only:
+            return base_loss
+        w = self.store.w32
+        l2 = 0.5 * float((w.double() ** 2).sum().item())
+        return base_loss + p.weight_decay * l2
+
+    def _sync(self) -> None:
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+
+    # ------------------------------------------------------------------ eval
+    def _eval_batches(self) -> int:
+        p = self.params
+        if p.num_eval_batches and p.num_eval_epochs:
+            raise ValueError("At most one of --num_eval_batches and --num_eval_epochs may be "
+                             "specified.")
+        if p.num_eval_epochs:
+            return max(int(p.num_eval_epochs * self.dataset.num_examples_per_epoch("validation") /
+                           (self.batch_size * self.num_workers)), 1)
+        return p.num_eval_batches or p.num_batches or 100
+
+    def _eval_once(self, num_batches: int, source=None) -> Dict:
+        """T/benchmark_cnn.py:1864-1923."""
+        src = source or self.input_source
+        top1 = top5 = 0
+        total = 0
+        loss_sum = 0.0
+        self._sync()
+        start = time.time()
+        for step in range(num_batches):
+            images, labels = src.next_batch()
+            self.executor.set_inputs(images, labels)
+            self.executor.forward(False)
+            self.executor.loss_backward(backward=False)
+            loss, t1, t5 = self.executor.read_loss()
+            top1 += t1
+            top5 += t5
+            loss_sum += loss
+            total += self.batch_size_per_device
+            if (step + 1) % max(self.params.display_every, 1) == 0 and self.rank == 0:
+                dt = time.time() - start
+                _log("%i\t%.1f examples/sec" % (step + 1, total / max(dt, 1e-9)))
+        dt = time.time() - start
+        acc1, acc5 = top1 / max(total, 1), top5 / max(total, 1)
+        if self.rank == 0:
+            _log("Accuracy @ 1 = %.4f Accuracy @ 5 = %.4f [%d examples]" % (acc1, acc5, total))
+        return {"top_1_accuracy": acc1, "top_5_accuracy": acc5, "num_examples": total,
+                "eval_average_loss": loss_sum / max(num_batches, 1),
+                "images_per_sec": total / max(dt, 1e-9)}
+
+    def _eval_during_training(self) -> Dict:
+        from .data import inputs
+        src = inputs.create_input_source(self.params, self.dataset, self.model,
+                                         self.batch_size_per_device, self.device, self.nclass,
+                                         seed=self.seed + 1, rank=self.rank,
+                                         world=max(self.world, 1), train=False)
+        return self._eval_once(self._eval_batches(), src)
+
+    def _run_eval(self) -> Dict:
+        """T/benchmark_cnn.py:1757-1794."""
+        p = self.params
+        self._build(phase_train=False)
+        result = {}
+        while True:
+            path, step = ckpt_lib.latest_checkpoint(p.train_dir)
+            self.store.from_tf_arrays(ckpt_lib.load_arrays(path), strict=False)
+            self.global_step = step
+            result = self._eval_once(self._eval_batches())
+            if self.rank == 0:
+                _log("-" * 64)
+                _log("total images/sec: %.2f" % result["images_per_sec"])
+                _log("-" * 64)
+            if p.eval_interval_secs <= 0:
+                break
+            time.sleep(p.eval_interval_secs)
+        return result
+
+
+def run_from_kwargs(**kwargs) -> Dict:
+    """Library entry: ``run_from_kwargs(model='resnet50', batch_size=64, ...)``."""
+    params = setup(make_params(**kwargs))
+    bench = BenchmarkCNN(params)
+    bench.print_info()
+    return bench.run()

@@ -1,0 +1,105 @@
+"""Checkpoints: save / resume and export in the reference's variable-name layout.
+
+The reference saves ``train_dir/model.ckpt-<global_step>`` through ``tf.train.Saver`` plus a
+``checkpoint`` state file (T/benchmark_cnn.py:2076-2082,2373-2378) and loads the newest or a
+named one (``load_checkpoint`` :905-950). TensorFlow is not available on this image, so the
+tensors are stored as one ``.npz`` per checkpoint whose *keys are the reference's TF variable
+names* (``v0/cg/conv0/conv2d/kernel`` ..., HWIO / [in,out] layouts, fp32, plus ``global_step``,
+``loss_scale``, ``loss_scale_normal_steps`` and ``<var>/Momentum`` style optimizer slots) -
+``tools/export_tf_checkpoint.py`` turns such a file into a real TF bundle wherever TensorFlow
+is installed. The ``checkpoint`` state file uses TF's text format with relative paths so a
+moved ``train_dir`` still resolves.
+"""
+from __future__ import annotations
+
+import os
+import re
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+
+_SUFFIX = ".npz"
+
+
+class CheckpointNotFoundException(Exception):
+    pass
+
+
+def _state_path(train_dir: str) -> str:
+    return os.path.join(train_dir, "checkpoint")
+
+
+def _write_state(train_dir: str, names) -> None:
+    with open(_state_path(train_dir), "w") as f:
+        f.write('model_checkpoint_path: "%s"\n' % names[-1])
+        for n in names:
+            f.write('all_model_checkpoint_paths: "%s"\n' % n)
+
+
+def _read_state(train_dir: str):
+    path = _state_path(train_dir)
+    if not os.path.exists(path):
+        return []
+    names = []
+    with open(path) as f:
+        for line in f:
+            m = re.match(r'all_model_checkpoint_paths: "(.*)"', line.strip())
+            if m:
+                names.append(m.group(1))
+    return names
+
+
+def save_checkpoint(train_dir: str, global_step: int, store, extra: Optional[Dict] = None,
+                    max_to_keep: int = 5, opt_slots: Optional[Dict] = None) -> str:
+    os.makedirs(train_dir, exist_ok=True)
+    arrays = store.to_tf_arrays("v0/")
+    if opt_slots:
+        from .nn.params import _native_to_tf
+        for suffix, arena in opt_slots.items():
+            for p in store.graph.params.values():
+                if not p.trainable:
+                    continue
+                s = store.slots[p.name]
+                t = arena[s.offset:s.offset + s.numel].view(p.shape).detach().float().cpu()
+                arrays["v0/%s/%s" % (p.name, suffix)] = _native_to_tf(p, t).numpy()
+    for k, v in (extra or {}).items():
+        arrays[k] = np.asarray(v)
+    name = "model.ckpt-%d" % global_step
+    tmp = os.path.join(train_dir, name + ".tmp" + _SUFFIX)
+    np.savez(tmp, **arrays)
+    os.replace(tmp, os.path.join(train_dir, name + _SUFFIX))
+    names = [n for n in _read_state(train_dir) if n != name] + [name]
+    while max_to_keep and len(names) > max_to_keep:
+        old = names.pop(0)
+        try:
+            os.remove(os.path.join(train_dir, old + _SUFFIX))
+        except OSError:
+            pass
+    _write_state(train_dir, names)
+    return os.path.join(train_dir, name)
+
+
+def latest_checkpoint(path: str) -> Tuple[str, int]:
+    """Resolves a directory (newest checkpoint) or an explicit ``.../model.ckpt-N`` path and
+    returns (path without suffix, global step) - the rules of T/benchmark_cnn.py:905-950."""
+    if path is None:
+        raise CheckpointNotFoundException("No checkpoint directory given")
+    m = re.match(r".*ckpt-(\d+)$", path[:-len(_SUFFIX)] if path.endswith(_SUFFIX) else path)
+    if m:
+        base = path[:-len(_SUFFIX)] if path.endswith(_SUFFIX) else path
+        if not os.path.exists(base + _SUFFIX):
+            raise CheckpointNotFoundException("No checkpoint file found at %s" % base)
+        return base, int(m.group(1))
+    names = _read_state(path)
+    if not names:
+        raise CheckpointNotFoundException("No checkpoint file found in dir:`%s`" % path)
+    name = os.path.basename(names[-1])
+    base = os.path.join(path, name)
+    if not os.path.exists(base + _SUFFIX):
+        raise CheckpointNotFoundException("No checkpoint file found at %s" % base)
+    return base, int(name.split("-")[-1])
+
+
+def load_arrays(base_path: str) -> Dict[str, np.ndarray]:
+    with np.load(base_path + _SUFFIX) as z:
+        return {k: z[k] for k in z.files}

@@ -1,0 +1,399 @@
+"""NetBuilder: the layer-builder API the model zoo is written against.
+
+It offers the same calls and bookkeeping as the reference's ``ConvNetBuilder``
+(T/convnet_builder_legacy.py:32-468): a running ``top_layer`` / ``top_size``,
+per-type name counters that are global to the network (``conv0, conv1, ...``,
+``affine0``, ``batchnorm0`` ...), the ``SAME_RESNET`` padding mode, inception
+columns with ``share``, and an auxiliary-head context. Instead of emitting TF ops
+it records nodes of ``nn.graph.Graph`` and fuses as it goes:
+
+* conv + bias + ReLU                -> one ``conv`` node (GEMM epilogue)
+* batch-norm + ReLU                 -> one ``bn`` node
+* batch-norm + residual add + ReLU  -> one ``bn`` node with a second input
+
+Variable names reproduce the reference's scopes so checkpoints can be exported
+in its layout.
+"""
+from __future__ import annotations
+
+import contextlib
+import math
+from collections import defaultdict
+from typing import List, Optional, Sequence, Tuple
+
+from .graph import Graph, Node, ParamSpec, TensorRef
+
+
+def _same_pad(in_size: int, k: int, stride: int) -> Tuple[int, int]:
+    out = -(-in_size // stride)
+    total = max((out - 1) * stride + k - in_size, 0)
+    return total // 2, total - total // 2
+
+
+def resolve_padding(mode: str, in_size: int, k: int, stride: int) -> Tuple[int, int]:
+    mode = mode.upper()
+    if mode == "VALID":
+        return 0, 0
+    if mode == "SAME":
+        return _same_pad(in_size, k, stride)
+    if mode == "SAME_RESNET":
+        if stride == 1:
+            return _same_pad(in_size, k, 1)
+        lo = (k - 1) // 2
+        return lo, k - 1 - lo
+    raise ValueError(f"unknown padding mode {mode!r}")
+
+
+def out_size(in_size: int, k: int, stride: int, pad: Tuple[int, int]) -> int:
+    return (in_size + pad[0] + pad[1] - k) // stride + 1
+
+
+class NetBuilder:
+    def __init__(self, graph: Graph, phase_train: bool = True):
+        self.graph = graph
+        self.phase_train = phase_train
+        self.top_layer: TensorRef = graph.input
+        self.top_size: int = graph.input.shape[-1]
+        self.counts = defaultdict(int)
+        self.use_batch_norm = False
+        self.batch_norm_config = {}  # decay / epsilon / scale overrides
+        self.aux_top_layer: Optional[TensorRef] = None
+        self.aux_top_size = 0
+        self._scopes: List[str] = ["cg"]
+        self.data_format = "NHWC"
+        self.channel_pos = "channels_last"
+
+    # -- naming ---------------------------------------------------------------
+    @contextlib.contextmanager
+    def scope(self, name: str):
+        self._scopes.append(name)
+        try:
+            yield
+        finally:
+            self._scopes.pop()
+
+    def _full(self, leaf: str) -> str:
+        return "/".join(self._scopes + [leaf])
+
+    @contextlib.contextmanager
+    def switch_to_aux_top_layer(self):
+        """T/convnet_builder_legacy.py:97-110."""
+        if self.aux_top_layer is None:
+            raise RuntimeError("Empty auxiliary top layer in the network.")
+        saved = (self.top_layer, self.top_size)
+        self.top_layer, self.top_size = self.aux_top_layer, self.aux_top_size
+        yield
+        self.aux_top_layer, self.aux_top_size = self.top_layer, self.top_size
+        self.top_layer, self.top_size = saved
+
+    # -- layers ---------------------------------------------------------------
+    def conv(self, num_out_channels, k_height, k_width, d_height=1, d_width=1, mode="SAME",
+             input_layer=None, num_channels_in=None, use_batch_norm=None, stddev=None,
+             activation="relu", bias=0.0, kernel_initializer=None) -> TensorRef:
+        """T/convnet_builder_legacy.py:143-226."""
+        if input_layer is None:
+            input_layer = self.top_layer
+        if num_channels_in is None:
+            num_channels_in = self.top_size
+        if len(input_layer.shape) != 4:
+            raise ValueError("conv expects an NHWC input")
+        n, h, w, c = input_layer.shape
+        if c != num_channels_in:
+            raise ValueError(f"conv: input has {c} channels, num_channels_in={num_channels_in}")
+        name = "conv" + str(self.counts["conv"])
+        self.counts["conv"] += 1
+        if use_batch_norm is None:
+            use_batch_norm = self.use_batch_norm
+        pad_h = resolve_padding(mode, h, k_height, d_height)
+        pad_w = resolve_padding(mode, w, k_width, d_width)
+        p = out_size(h, k_height, d_height, pad_h)
+        q = out_size(w, k_width, d_width, pad_w)
+        fan_in = k_height * k_width * c
+        fan_out = k_height * k_width * num_out_channels
+        if kernel_initializer is not None:
+            init = kernel_initializer
+        elif stddev is not None:
+            init = ("trunc_normal", float(stddev))
+        else:
+            init = ("glorot_uniform", fan_in, fan_out)
+        with self.scope(name):
+            params = {}
+            tf_shape = (k_height, k_width, c, num_out_channels)
+            if c % 8 == 0:
+                params["kernel"] = ParamSpec(self._full("conv2d/kernel"),
+                                             (num_out_channels, k_height, k_width, c), tf_shape,
+                                             "conv_kernel", True, init)
+            else:
+                # tiny-C stem: filters stored as rows of an explicit-im2col GEMM, K padded to 8
+                kpad = (fan_in + 7) // 8 * 8
+                params["kernel"] = ParamSpec(self._full("conv2d/kernel"),
+                                             (num_out_channels, kpad), tf_shape,
+                                             "conv_kernel_flat", True, init, logical_cols=fan_in,
+                                             conv_rsc=(k_height, k_width, c))
+            has_bias = (not use_batch_norm) and bias is not None
+            if has_bias:
+                params["biases"] = ParamSpec(self._full("biases"), (num_out_channels,),
+                                             (num_out_channels,), "bias", True,
+                                             ("const", float(bias)))
+            if activation not in ("relu", "linear", "tanh", None):
+                raise KeyError("Invalid activation type '%s'" % activation)
+            act = "linear" if activation is None else activation
+            node = self.graph.add_node(
+                "conv", self._full(""), [input_layer], (n, p, q, num_out_channels),
+                dict(kh=k_height, kw=k_width, sh=d_height, sw=d_width, pad_h=pad_h, pad_w=pad_w,
+                     activation="linear" if use_batch_norm else act, has_bias=has_bias),
+                params)
+            self.top_layer, self.top_size = node.output, num_out_channels
+            if use_batch_norm:
+                self.batch_norm(**self.batch_norm_config)
+                if act == "relu":
+                    self.relu()
+                elif act == "tanh":
+                    self.tanh()
+        return self.top_layer
+
+    def batch_norm(self, input_layer=None, decay=0.999, scale=False, epsilon=0.001) -> TensorRef:
+        """T/convnet_builder_legacy.py:433-459 (defaults decay .999, eps 1e-3, no scale)."""
+        if input_layer is None:
+            input_layer = self.top_layer
+        else:
+            self.top_size = None
+        name = "batchnorm" + str(self.counts["batchnorm"])
+        self.counts["batchnorm"] += 1
+        c = input_layer.shape[-1]
+        with self.scope(name):
+            params = {"beta": ParamSpec(self._full("beta"), (c,), (c,), "beta", True, ("zeros",))}
+            if scale:
+                params["gamma"] = ParamSpec(self._full("gamma"), (c,), (c,), "gamma", True,
+                                            ("ones",))
+            params["moving_mean"] = ParamSpec(self._full("moving_mean"), (c,), (c,),
+                                              "moving_mean", False, ("zeros",))
+            params["moving_variance"] = ParamSpec(self._full("moving_variance"), (c,), (c,),
+                                                  "moving_variance", False, ("ones",))
+            node = self.graph.add_node(
+                "bn", self._full(""), [input_layer], input_layer.shape,
+                dict(decay=float(decay), epsilon=float(epsilon), scale=bool(scale), relu=False),
+                params)
+        self.top_layer = node.output
+        if self.top_size is None:
+            self.top_size = c
+        return self.top_layer
+
+    def relu(self, input_layer=None) -> TensorRef:
+        """ReLU on the top layer; folded into a preceding batch-norm when possible."""
+        x = self.top_layer if input_layer is None else input_layer
+        prod = x.producer
+        if (prod is not None and prod.op == "bn" and not prod.attrs["relu"] and
+                not x.consumers and x is not self.graph.logits):
+            prod.attrs["relu"] = True
+            self.top_layer = x
+            return x
+        node = self.graph.add_node("act", "relu%d" % self.counts["relu"], [x], x.shape,
+                                   dict(kind="relu"))
+        self.counts["relu"] += 1
+        self.top_layer = node.output
+        return self.top_layer
+
+    def tanh(self, input_layer=None) -> TensorRef:
+        x = self.top_layer if input_layer is None else input_layer
+        node = self.graph.add_node("act", "tanh%d" % self.counts["tanh"], [x], x.shape,
+                                   dict(kind="tanh"))
+        self.counts["tanh"] += 1
+        self.top_layer = node.output
+        return self.top_layer
+
+    def add(self, shortcut: TensorRef, res: TensorRef, relu: bool = False) -> TensorRef:
+        """``act(shortcut + res)``: the residual join of the ResNet blocks
+        (T/models/resnet_model_legacy.py:77). Folded into the batch-norm that produced ``res``
+        when that is legal."""
+        if shortcut.shape != res.shape:
+            raise ValueError(f"add: shapes differ {shortcut.shape} vs {res.shape}")
+        prod = res.producer
+        if (prod is not None and prod.op == "bn" and not prod.attrs["relu"] and
+                len(prod.inputs) == 1 and not res.consumers):
+            prod.inputs.append(shortcut)
+            shortcut.consumers.append(prod)
+            prod.attrs["relu"] = bool(relu)
+            self.top_layer = res
+        else:
+            node = self.graph.add_node("add", "add%d" % self.counts["add"], [shortcut, res],
+                                       res.shape, dict(relu=bool(relu)))
+            self.counts["add"] += 1
+            self.top_layer = node.output
+        self.top_size = res.shape[-1]
+        return self.top_layer
+
+    def _pool(self, kind, k_height, k_width, d_height, d_width, mode, input_layer,
+              num_channels_in) -> TensorRef:
+        """T/convnet_builder_legacy.py:228-286."""
+        if input_layer is None:
+            input_layer = self.top_layer
+        else:
+            self.top_size = num_channels_in
+        name = kind + str(self.counts[kind])
+        self.counts[kind] += 1
+        n, h, w, c = input_layer.shape
+        pad_h = resolve_padding(mode, h, k_height, d_height)
+        pad_w = resolve_padding(mode, w, k_width, d_width)
+        p = out_size(h, k_height, d_height, pad_h)
+        q = out_size(w, k_width, d_width, pad_w)
+        node = self.graph.add_node(
+            "pool", name, [input_layer], (n, p, q, c),
+            dict(kind="max" if kind == "mpool" else "avg", kh=k_height, kw=k_width, sh=d_height,
+                 sw=d_width, pad_h=pad_h, pad_w=pad_w))
+        self.top_layer = node.output
+        if self.top_size is None:
+            self.top_size = c
+        return self.top_layer
+
+    def mpool(self, k_height, k_width, d_height=2, d_width=2, mode="VALID", input_layer=None,
+              num_channels_in=None) -> TensorRef:
+        return self._pool("mpool", k_height, k_width, d_height, d_width, mode, input_layer,
+                          num_channels_in)
+
+    def apool(self, k_height, k_width, d_height=2, d_width=2, mode="VALID", input_layer=None,
+              num_channels_in=None) -> TensorRef:
+        return self._pool("apool", k_height, k_width, d_height, d_width, mode, input_layer,
+                          num_channels_in)
+
+    def reshape(self, shape: Sequence[int], input_layer=None) -> TensorRef:
+        """Only the flattening reshapes the zoo uses (``[-1, F]``) are supported."""
+        if input_layer is None:
+            input_layer = self.top_layer
+        shape = list(shape)
+        total = 1
+        for s in input_layer.shape[1:]:
+            total *= s
+        if len(shape) != 2 or shape[0] != -1 or shape[1] != total:
+            raise ValueError(f"reshape: unsupported target {shape} for input {input_layer.shape}")
+        node = self.graph.add_node("reshape", "reshape%d" % self.counts["reshape"], [input_layer],
+                                   (input_layer.shape[0], total))
+        self.counts["reshape"] += 1
+        self.top_layer, self.top_size = node.output, total
+        return self.top_layer
+
+    def affine(self, num_out_channels, input_layer=None, num_channels_in=None, bias=0.0,
+               stddev=None, activation="relu") -> TensorRef:
+        """T/convnet_builder_legacy.py:288-325."""
+        if input_layer is None:
+            input_layer = self.top_layer
+        if num_channels_in is None:
+            num_channels_in = self.top_size
+        if len(input_layer.shape) != 2 or input_layer.shape[1] != num_channels_in:
+            raise ValueError(f"affine: bad input {input_layer.shape} for in={num_channels_in}")
+        name = "affine" + str(self.counts["affine"])
+        self.counts["affine"] += 1
+        if activation not in ("relu", "linear", None):
+            raise KeyError("Invalid activation type '%s'" % activation)
+        act = "linear" if activation is None else activation
+        init_factor = 2.0 if act == "relu" else 1.0
+        std = stddev or math.sqrt(init_factor / num_channels_in)
+        with self.scope(name):
+            params = {
+                # native layout [out, in padded to 8]: K-major operand rows must be 16-byte
+                # multiples for TMA; the pad columns stay zero
+                "weights": ParamSpec(self._full("weights"),
+                                     (num_out_channels, (num_channels_in + 7) // 8 * 8),
+                                     (num_channels_in, num_out_channels), "fc_weight", True,
+                                     ("trunc_normal", float(std)),
+                                     logical_cols=num_channels_in),
+                "biases": ParamSpec(self._full("biases"), (num_out_channels,),
+                                    (num_out_channels,), "bias", True, ("const", float(bias))),
+            }
+            node = self.graph.add_node("affine", self._full(""), [input_layer],
+                                       (input_layer.shape[0], num_out_channels),
+                                       dict(activation=act), params)
+        self.top_layer, self.top_size = node.output, num_out_channels
+        return self.top_layer
+
+    def inception_module(self, name, cols, input_layer=None, in_size=None) -> TensorRef:
+        """T/convnet_builder_legacy.py:327-365."""
+        if input_layer is None:
+            input_layer = self.top_layer
+        if in_size is None:
+            in_size = self.top_size
+        name += str(self.counts[name])
+        self.counts[name] += 1
+        with self.scope(name):
+            col_layers, col_sizes = [], []
+            for c, col in enumerate(cols):
+                col_layers.append([])
+                col_sizes.append([])
+                for l, layer in enumerate(col):
+                    ltype, args = layer[0], layer[1:]
+                    kwargs = ({"input_layer": input_layer, "num_channels_in": in_size}
+                              if l == 0 else {})
+                    if ltype == "conv":
+                        self.conv(*args, **kwargs)
+                    elif ltype == "mpool":
+                        self.mpool(*args, **kwargs)
+                    elif ltype == "apool":
+                        self.apool(*args, **kwargs)
+                    elif ltype == "share":
+                        self.top_layer = col_layers[c - 1][l]
+                        self.top_size = col_sizes[c - 1][l]
+                    else:
+                        raise KeyError("Invalid layer type for inception module: '%s'" % ltype)
+                    col_layers[c].append(self.top_layer)
+                    col_sizes[c].append(self.top_size)
+            self.concat([layers[-1] for layers in col_layers])
+        return self.top_layer
+
+    def concat(self, layers: Sequence[TensorRef]) -> TensorRef:
+        base = layers[0].shape[:-1]
+        for t in layers:
+            if t.shape[:-1] != base:
+                raise ValueError("concat: spatial shapes differ")
+        total = sum(t.shape[-1] for t in layers)
+        node = self.graph.add_node("concat", "concat%d" % self.counts["concat"], list(layers),
+                                   tuple(base) + (total,))
+        self.counts["concat"] += 1
+        self.top_layer, self.top_size = node.output, total
+        return self.top_layer
+
+    def pad_channels(self, before: int, after: int, input_layer=None) -> TensorRef:
+        """Zero-pad the channel axis ("plan A" shortcut, T/models/resnet_model_legacy.py:239-247)."""
+        x = self.top_layer if input_layer is None else input_layer
+        node = self.graph.add_node("pad_channels", "pad%d" % self.counts["pad"], [x],
+                                   x.shape[:-1] + (x.shape[-1] + before + after,),
+                                   dict(before=before, after=after))
+        self.counts["pad"] += 1
+        self.top_layer, self.top_size = node.output, node.output.shape[-1]
+        return self.top_layer
+
+    def spatial_mean(self, keep_dims=False) -> TensorRef:
+        """T/convnet_builder_legacy.py:367-373."""
+        name = "spatial_mean" + str(self.counts["spatial_mean"])
+        self.counts["spatial_mean"] += 1
+        x = self.top_layer
+        n, h, w, c = x.shape
+        node = self.graph.add_node("spatial_mean", name, [x], (n, c))
+        self.top_layer = node.output
+        return self.top_layer
+
+    def dropout(self, keep_prob=0.5, input_layer=None) -> TensorRef:
+        """T/convnet_builder_legacy.py:375-390 (the counter is not advanced there either)."""
+        if input_layer is None:
+            input_layer = self.top_layer
+        else:
+            self.top_size = None
+        if not self.phase_train:
+            keep_prob = 1.0
+        node = self.graph.add_node("dropout", "dropout%d_%d" % (self.counts["dropout"],
+                                                               len(self.graph.nodes)),
+                                   [input_layer], input_layer.shape,
+                                   dict(keep_prob=float(keep_prob)))
+        self.top_layer = node.output
+        if self.top_size is None:
+            self.top_size = input_layer.shape[-1]
+        return self.top_layer
+
+    def lrn(self, depth_radius, bias, alpha, beta) -> TensorRef:
+        """T/convnet_builder_legacy.py:462-468."""
+        name = "lrn" + str(self.counts["lrn"])
+        self.counts["lrn"] += 1
+        node = self.graph.add_node("lrn", name, [self.top_layer], self.top_layer.shape,
+                                   dict(radius=int(depth_radius), bias=float(bias),
+                                        alpha=float(alpha), beta=float(beta)))
+        self.top_layer = node.output
+        return self.top_layer

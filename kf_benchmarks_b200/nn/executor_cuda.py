@@ -1,0 +1,616 @@
+"""CUDA executor: runs a ``Graph`` forward and backward with the hand-written sm_100a
+kernels of ``csrc/`` (no autograd, no cuDNN / cuBLAS, no Triton).
+
+Design (B200-first, not a translation of the TF graph executor the reference leans on):
+
+* every activation, gradient and scratch buffer is allocated once, up front - the step is a
+  fixed sequence of kernel launches on static addresses, so it can be captured in a CUDA
+  graph and nothing touches the allocator inside the timed loop (180 GB of HBM3e makes
+  keeping all activations resident the cheap option);
+* activations are NHWC fp16 ``[rows][C]``; flat tensors are rows padded to 8 columns so
+  every row is a 16-byte multiple (TMA requirement); pad columns stay zero;
+* convolutions / FC layers go through the tcgen05 implicit-GEMM kernel (fprop, dgrad,
+  wgrad); weight gradients land directly in the fp32 gradient arena of the
+  ``ParameterStore`` at the variable's offset, so the gradient exchange needs no packing;
+* backward visits nodes in reverse order; after each node the arena range whose gradients
+  just became final is reported through ``on_grads_ready(lo, hi)`` - the hook the
+  bucket scheduler of ``parallel/`` uses to overlap the fused all-reduce+SGD kernel with
+  the rest of the backward pass (reference: TF scheduling NcclAllReduce ops as their
+  inputs become ready).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Callable, Dict, List, Optional
+
+import torch
+
+from ..ops import native
+from ..ops.native import ConvDesc, f32, i32, i64, ptr
+from .graph import Graph, Node, TensorRef
+from .params import ParameterStore
+
+u64 = ctypes.c_ulonglong
+
+
+def _pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+class _Buf:
+    """A 2-D fp16 view [rows][cols] with row stride ld (elements)."""
+    __slots__ = ("t", "rows", "cols", "ld")
+
+    def __init__(self, t: torch.Tensor, rows: int, cols: int, ld: int):
+        self.t, self.rows, self.cols, self.ld = t, rows, cols, ld
+
+    @property
+    def p(self):
+        return ctypes.c_void_p(self.t.data_ptr())
+
+
+class CudaExecutor:
+    def __init__(self, graph: Graph, store: ParameterStore, nclass: int, aux_weight: float = 0.4,
+                 dropout_seed: int = 4321, need_input_grad: bool = False):
+        if not torch.cuda.is_available():
+            raise RuntimeError("CudaExecutor needs a CUDA device")
+        native.load()  # fail loudly if the extension is missing
+        self.graph = graph
+        self.store = store
+        self.device = store.device
+        self.nclass = nclass
+        self.aux_weight = aux_weight
+        self.dropout_seed = int(dropout_seed)
+        self.step_index = 0
+        self._stream = None
+        dev = self.device
+        n = graph.batch_size
+
+        # ---- buffers ------------------------------------------------------------
+        self.buf: Dict[int, _Buf] = {}
+        self.gbuf: Dict[int, _Buf] = {}
+        self._alias: Dict[int, int] = {}
+        h, w, c = graph.input.shape[1:]
+        self.images = torch.zeros((n, h, w, c), dtype=torch.float16, device=dev)
+        self.buf[graph.input.id] = _Buf(self.images, n * h * w, c, c)
+        self.labels = torch.zeros((n,), dtype=torch.int32, device=dev)
+        self.needs_grad = self._mark_needs_grad(need_input_grad)
+        for node in graph.nodes:
+            self._alloc_output(node)
+        # reductions / split-K scratch (sized below), loss outputs
+        self._scratch_need = 0
+        self._ws_need = 0
+        self.loss_rows = torch.zeros((2, n), dtype=torch.float32, device=dev)
+        self.top = torch.zeros((4, n), dtype=torch.int32, device=dev)
+        self.loss_out = torch.zeros((8,), dtype=torch.float32, device=dev)
+        self.loss_scale_dev = torch.ones((1,), dtype=torch.float32, device=dev)
+        self._per_node: Dict[int, dict] = {}
+        for node in graph.nodes:
+            self._prepare(node)
+        self.scratch = torch.zeros((max(self._scratch_need, 1024),), dtype=torch.float32,
+                                   device=dev)
+        self.workspace = torch.zeros((max(self._ws_need // 4, 1024),), dtype=torch.float32,
+                                     device=dev)
+        self._plan_grad_writes()
+
+    # ------------------------------------------------------------------ helpers
+    def _s(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _mark_needs_grad(self, need_input_grad: bool) -> Dict[int, bool]:
+        need = {self.graph.input.id: need_input_grad}
+        for node in self.graph.nodes:
+            has_param = any(p.trainable for p in node.params.values())
+            need[node.output.id] = has_param or any(need[t.id] for t in node.inputs)
+        return need
+
+    def _alloc_output(self, node: Node) -> None:
+        t = node.output
+        dev = self.device
+        if len(t.shape) == 4:
+            rows, cols = t.rows, t.shape[-1]
+            if cols % 8 != 0:
+                raise NotImplementedError(
+                    f"{node.name}: {cols} channels - the sm_100a kernels need channel counts "
+                    "that are multiples of 8 (use --device=cpu for this model)")
+            ld = cols
+        else:
+            rows, cols = t.shape[0], t.shape[1]
+            ld = _pad8(cols)
+        if node.op == "reshape":
+            src = self.buf[node.inputs[0].id]
+            if src.t.numel() == rows * ld and cols == ld:
+                # pure view of the same storage
+                self.buf[t.id] = _Buf(src.t.view(rows, ld), rows, cols, ld)
+                self._alias[t.id] = node.inputs[0].id
+                return
+        is_logits = t is self.graph.logits or t is self.graph.aux_logits
+        dt = torch.float32 if is_logits else torch.float16
+        if is_logits and node.op != "affine":
+            raise NotImplementedError("logits must come from an affine layer")
+        self.buf[t.id] = _Buf(torch.zeros((rows, ld), dtype=dt, device=dev), rows, cols, ld)
+
+    def _grad(self, t: TensorRef) -> _Buf:
+        """Gradient buffer of tensor t (allocated lazily, aliases follow reshape views)."""
+        if t.id in self._alias:
+            base = self._grad(self.graph.tensors[self._alias[t.id]])
+            b = self.buf[t.id]
+            g = _Buf(base.t.view(b.rows, b.ld), b.rows, b.cols, b.ld)
+            self.gbuf[t.id] = g
+            return g
+        if t.id not in self.gbuf:
+            b = self.buf[t.id]
+            self.gbuf[t.id] = _Buf(torch.zeros((b.rows, b.ld), dtype=torch.float16,
+                                               device=self.device), b.rows, b.cols, b.ld)
+        return self.gbuf[t.id]
+
+    def _root(self, tid: int) -> int:
+        while tid in self._alias:
+            tid = self._alias[tid]
+        return tid
+
+    def _plan_grad_writes(self) -> None:
+        """Static schedule of which backward contribution writes and which accumulates."""
+        written = set()
+        self._first: Dict[tuple, bool] = {}
+        for node in reversed(self.graph.nodes):
+            for idx, t in enumerate(node.inputs):
+                if not self.needs_grad.get(t.id, False):
+                    continue
+                root = self._root(t.id)
+                self._first[(id(node), idx)] = root not in written
+                written.add(root)
+        for t in self.graph.tensors:
+            if self.needs_grad.get(t.id, False) and (t.consumers or t is self.graph.logits or
+                                                     t is self.graph.aux_logits):
+                self._grad(t)
+
+    def _acc(self, node: Node, idx: int) -> int:
+        return 0 if self._first[(id(node), idx)] else 1
+
+    def _need_scratch(self, rows: int, c: int) -> None:
+        nb = native.load().kfb_reduce_blocks(ctypes.c_longlong(rows), ctypes.c_int(c))
+        self._scratch_need = max(self._scratch_need, nb * 2 * c)
+
+    # ------------------------------------------------------------------ per-node setup
+    def _prepare(self, node: Node) -> None:
+        info: dict = {}
+        a = node.attrs
+        st = self.store
+        dev = self.device
+        if node.op == "conv":
+            x = node.inputs[0]
+            n, h, w, c = x.shape
+            k = node.output.shape[-1]
+            spec = node.params["kernel"]
+            d = ConvDesc()
+            d.n, d.h, d.w, d.c = n, h, w, c
+            d.k, d.r, d.s = k, a["kh"], a["kw"]
+            d.pad_h_lo, d.pad_h_hi = a["pad_h"]
+            d.pad_w_lo, d.pad_w_hi = a["pad_w"]
+            d.stride_h, d.stride_w = a["sh"], a["sw"]
+            d.p, d.q = node.output.shape[1], node.output.shape[2]
+            info["desc"] = d
+            info["dgrad_zero_fill"] = bool(
+                native.load().kfb_conv_dgrad_needs_zero_fill(ctypes.byref(d)))
+            info["flat"] = spec.kind == "conv_kernel_flat"
+            if info["flat"]:
+                kpad = spec.shape[1]
+                info["kpad"] = kpad
+                info["col"] = torch.zeros((n * d.p * d.q, kpad), dtype=torch.float16, device=dev)
+                m_rows = n * d.p * d.q
+                self._ws_need = max(self._ws_need, self._nt_ws(k, kpad))
+            else:
+                fn = native.load().kfb_conv_wgrad_workspace_bytes
+                fn.restype = ctypes.c_longlong
+                self._ws_need = max(self._ws_need, int(fn(ctypes.byref(d))))
+            if a["activation"] == "tanh":
+                raise NotImplementedError("tanh epilogue is not built for the CUDA executor")
+            self._need_scratch(node.output.rows, k)
+        elif node.op == "bn":
+            c = node.output.shape[-1]
+            info["mean_rstd"] = torch.zeros((2 * c,), dtype=torch.float32, device=dev)
+            info["scale_shift"] = torch.zeros((2 * c,), dtype=torch.float32, device=dev)
+            info["coef"] = torch.zeros((3 * c,), dtype=torch.float32, device=dev)
+            self._need_scratch(node.output.rows, c)
+        elif node.op == "affine":
+            spec = node.params["weights"]
+            out, in_pad = spec.shape
+            self._ws_need = max(self._ws_need, self._nt_ws(out, in_pad))
+            self._need_scratch(node.output.shape[0], _pad8(out))
+        elif node.op == "pool":
+            if a["kind"] == "max":
+                o = node.output
+                info["argmax"] = torch.zeros((o.rows, o.shape[-1]), dtype=torch.uint8, device=dev)
+        elif node.op == "pad_channels":
+            if a["before"] % 8 or a["after"] % 8:
+                raise NotImplementedError("pad_channels: pads must be multiples of 8")
+        elif node.op == "lrn" or node.op == "dropout":
+            pass
+        self._per_node[id(node)] = info
+
+    @staticmethod
+    def _nt_ws(m: int, n: int) -> int:
+        bn = 64 if n <= 64 else (128 if n <= 128 else 256)
+        tiles = ((m + 127) // 128) * ((n + bn - 1) // bn)
+        splits = max(1, (2 * 148 + tiles - 1) // tiles)
+        return m * n * 4 * splits
+
+    # ------------------------------------------------------------------ inputs
+    def set_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+        """Copies a batch into the static input buffers (non-blocking from pinned memory)."""
+        self.images.copy_(images, non_blocking=True)
+        self.labels.copy_(labels, non_blocking=True)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, train: bool = True) -> None:
+        s = self._s()
+        for node in self.graph.nodes:
+            getattr(self, "_fwd_" + node.op)(node, train, s)
+
+    def _w16(self, name):
+        return ctypes.c_void_p(self.store.view(name, "w16").data_ptr())
+
+    def _w32(self, name):
+        return ctypes.c_void_p(self.store.view(name, "w32").data_ptr())
+
+    def _g32(self, name):
+        return ctypes.c_void_p(self.store.view(name, "grad").data_ptr())
+
+    def _fwd_conv(self, node, train, s):
+        info = self._per_node[id(node)]
+        a = node.attrs
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        bias = self._w32(node.params["biases"].name) if a["has_bias"] else None
+        relu = i32(1 if a["activation"] == "relu" else 0)
+        d = info["desc"]
+        kname = node.params["kernel"].name
+        if info["flat"]:
+            col = info["col"]
+            native.call("im2col_small_c", x.p, ptr(col), i32(d.n), i32(d.h), i32(d.w), i32(d.c),
+                        i32(d.p), i32(d.q), i32(d.r), i32(d.s), i32(d.stride_h), i32(d.stride_w),
+                        i32(d.pad_h_lo), i32(d.pad_w_lo), i32(info["kpad"]), s)
+            native.call("gemm_tn", ptr(col), self._w16(kname), y.p, i32(y.rows), i32(d.k),
+                        i32(info["kpad"]), i64(info["kpad"]), i64(info["kpad"]), i64(y.ld), bias,
+                        relu, i32(0), s)
+        else:
+            native.call("conv_fprop", ctypes.byref(d), x.p, self._w16(kname), y.p, i64(y.ld),
+                        bias, relu, s)
+
+    def _fwd_bn(self, node, train, s):
+        info = self._per_node[id(node)]
+        a = node.attrs
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        res = self.buf[node.inputs[1].id] if len(node.inputs) > 1 else None
+        gamma = self._w32(node.params["gamma"].name) if a["scale"] else None
+        beta = self._w32(node.params["beta"].name)
+        mm = ptr(self.store.view(node.params["moving_mean"].name))
+        mv = ptr(self.store.view(node.params["moving_variance"].name))
+        c = y.cols
+        if train:
+            native.call("bn_forward_train", x.p, i64(x.ld), i64(x.rows), i32(c), gamma, beta, mm,
+                        mv, f32(a["epsilon"]), f32(a["decay"]), i32(1), ptr(info["mean_rstd"]),
+                        ptr(info["scale_shift"]), ptr(self.scratch), res.p if res else None,
+                        i64(res.ld if res else 0), i32(int(a["relu"])), y.p, i64(y.ld), s)
+        else:
+            native.call("bn_forward_inference", x.p, i64(x.ld), i64(x.rows), i32(c), gamma, beta,
+                        mm, mv, f32(a["epsilon"]), ptr(info["scale_shift"]),
+                        res.p if res else None, i64(res.ld if res else 0), i32(int(a["relu"])),
+                        y.p, i64(y.ld), s)
+
+    def _fwd_act(self, node, train, s):
+        if node.attrs["kind"] != "relu":
+            raise NotImplementedError("only ReLU is built as a stand-alone activation")
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        native.call("add_act", x.p, i64(x.ld), None, i64(0), y.p, i64(y.ld), i64(x.rows),
+                    i32(_pad8(x.cols)), i32(1), s)
+
+    def _fwd_add(self, node, train, s):
+        a, b = self.buf[node.inputs[0].id], self.buf[node.inputs[1].id]
+        y = self.buf[node.output.id]
+        native.call("add_act", a.p, i64(a.ld), b.p, i64(b.ld), y.p, i64(y.ld), i64(a.rows),
+                    i32(_pad8(a.cols)), i32(int(node.attrs["relu"])), s)
+
+    def _pool_args(self, node):
+        a = node.attrs
+        n, h, w, c = node.inputs[0].shape
+        p, q = node.output.shape[1], node.output.shape[2]
+        return (i32(n), i32(h), i32(w), i32(c), i32(p), i32(q), i32(a["kh"]), i32(a["kw"]),
+                i32(a["sh"]), i32(a["sw"]), i32(a["pad_h"][0]), i32(a["pad_w"][0]),
+                i32(1 if a["kind"] == "max" else 0))
+
+    def _fwd_pool(self, node, train, s):
+        info = self._per_node[id(node)]
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        native.call("pool_forward", x.p, i64(x.ld), y.p, i64(y.ld), ptr(info.get("argmax")),
+                    *self._pool_args(node), s)
+
+    def _fwd_spatial_mean(self, node, train, s):
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        n, h, w, c = node.inputs[0].shape
+        native.call("spatial_mean_forward", x.p, i64(x.ld), y.p, i64(y.ld), i32(n), i32(h * w),
+                    i32(c), s)
+
+    def _fwd_reshape(self, node, train, s):
+        if node.output.id in self._alias:
+            return
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        per_row = y.cols
+        native.call("copy_rows", x.p, i64(per_row), y.p, i64(y.ld), i64(y.rows), i64(per_row),
+                    i32(0), s)
+
+    def _fwd_affine(self, node, train, s):
+        a = node.attrs
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        spec = node.params["weights"]
+        out, in_pad = spec.shape
+        native.call("gemm_tn", x.p, self._w16(spec.name), y.p, i32(x.rows), i32(out),
+                    i32(spec.logical_cols), i64(x.ld), i64(in_pad), i64(y.ld),
+                    self._w32(node.params["biases"].name),
+                    i32(1 if a["activation"] == "relu" else 0),
+                    i32(int(y.t.dtype == torch.float32)), s)
+
+    def _dropout_offset(self, node) -> int:
+        idx = self.graph.nodes.index(node)
+        return (self.step_index * 4096 + idx) * (1 << 32)
+
+    def _fwd_dropout(self, node, train, s):
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        kp = node.attrs["keep_prob"] if train else 1.0
+        native.call("dropout", x.p, y.p, i64(x.rows * x.ld), f32(kp), u64(self.dropout_seed),
+                    u64(self._dropout_offset(node)), s)
+
+    def _fwd_lrn(self, node, train, s):
+        a = node.attrs
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        native.call("lrn_forward", x.p, y.p, i64(x.rows), i32(x.cols), i32(a["radius"]),
+                    f32(a["bias"]), f32(a["alpha"]), f32(a["beta"]), s)
+
+    def _fwd_concat(self, node, train, s):
+        y = self.buf[node.output.id]
+        off = 0
+        for t in node.inputs:
+            x = self.buf[t.id]
+            native.call("copy2d", x.p, i64(x.ld), ctypes.c_void_p(y.t.data_ptr() + off * 2),
+                        i64(y.ld), i64(x.rows), i32(x.cols), i32(0), s)
+            off += x.cols
+
+    def _fwd_pad_channels(self, node, train, s):
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        off = node.attrs["before"]
+        native.call("copy2d", x.p, i64(x.ld), ctypes.c_void_p(y.t.data_ptr() + off * 2), i64(y.ld),
+                    i64(x.rows), i32(x.cols), i32(0), s)
+
+    # ------------------------------------------------------------------ loss + backward
+    def loss_backward(self, loss_scale: float = 1.0, backward: bool = True,
+                      on_grads_ready: Optional[Callable[[int, int], None]] = None,
+                      dyn_scale: Optional[torch.Tensor] = None) -> None:
+        """Softmax-xent (+0.4 aux) and the whole backward pass. Gradients of
+        ``loss * loss_scale`` land in ``store.grad``; ``dyn_scale`` (device scalar) multiplies
+        loss_scale for device-resident automatic loss scaling."""
+        s = self._s()
+        g = self.graph
+        n = g.batch_size
+        heads = [(g.logits, 1.0, 0)]
+        if g.aux_logits is not None:
+            heads.append((g.aux_logits, self.aux_weight, 1))
+        for t, weight, slot in heads:
+            lb = self.buf[t.id]
+            gb = self._grad(t) if backward else None
+            native.call("softmax_xent", lb.p, i64(lb.ld), ptr(self.labels), i32(n),
+                        i32(self.nclass), f32(loss_scale * weight / n), ptr(dyn_scale),
+                        gb.p if gb else None, i64(lb.ld), ptr(self.loss_rows[slot]),
+                        ptr(self.top[2 * slot]), ptr(self.top[2 * slot + 1]),
+                        ctypes.c_void_p(self.loss_out.data_ptr() + 16 * slot), s)
+        if not backward:
+            return
+        for node in reversed(g.nodes):
+            if not self.needs_grad[node.output.id]:
+                continue
+            getattr(self, "_bwd_" + node.op)(node, s)
+            if on_grads_ready is not None and node.params:
+                lo, hi = self.store.span([p.name for p in node.params.values() if p.trainable])
+                if hi > lo:
+                    on_grads_ready(lo, hi)
+        self.step_index += 1
+
+    def read_loss(self):
+        """(loss, top1 hits, top5 hits) of the last step; synchronises the stream."""
+        v = self.loss_out.tolist()
+        loss = v[0] + (self.aux_weight * v[4] if self.graph.aux_logits is not None else 0.0)
+        return loss, int(v[1]), int(v[2])
+
+    def _bias_act_bwd(self, node, gy: _Buf, y: _Buf, relu: bool, bias_name: Optional[str], s,
+                      cols: int) -> None:
+        """In place: gy <- gy * (y > 0); dbias <- column sums."""
+        if not relu and bias_name is None:
+            return
+        native.call("bias_act_backward", gy.p, i64(gy.ld), y.p if relu else None, i64(y.ld),
+                    i64(gy.rows), i32(cols), gy.p if relu else None, i64(gy.ld),
+                    self._g32(bias_name) if bias_name else None, i32(0), f32(1.0),
+                    ptr(self.scratch), s)
+
+    def _bwd_conv(self, node, s):
+        info = self._per_node[id(node)]
+        a = node.attrs
+        xin = node.inputs[0]
+        x, y = self.buf[xin.id], self.buf[node.output.id]
+        gy = self._grad(node.output)
+        d = info["desc"]
+        kname = node.params["kernel"].name
+        self._bias_act_bwd(node, gy, y, a["activation"] == "relu",
+                           node.params["biases"].name if a["has_bias"] else None, s, y.cols)
+        if info["flat"]:
+            if self.needs_grad[xin.id]:
+                raise NotImplementedError("input gradient of a tiny-C stem conv is not built")
+            col = info["col"]
+            native.call("gemm_nt", gy.p, ptr(col), self._g32(kname), i32(d.k), i32(info["kpad"]),
+                        i32(gy.rows), i64(gy.ld), i64(info["kpad"]), i64(info["kpad"]),
+                        ptr(self.workspace), i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
+            return
+        if self.needs_grad[xin.id]:
+            gx = self._grad(xin)
+            acc = self._acc(node, 0)
+            if info["dgrad_zero_fill"] and not acc:
+                gx.t.zero_()
+            native.call("conv_dgrad", ctypes.byref(d), gy.p, self._w16(kname), gx.p, i32(acc), s)
+        native.call("conv_wgrad", ctypes.byref(d), x.p, gy.p, i64(gy.ld), self._g32(kname),
+                    ptr(self.workspace), i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
+
+    def _bwd_bn(self, node, s):
+        info = self._per_node[id(node)]
+        a = node.attrs
+        zin = node.inputs[0]
+        z, y = self.buf[zin.id], self.buf[node.output.id]
+        gy = self._grad(node.output)
+        gamma = self._w32(node.params["gamma"].name) if a["scale"] else None
+        dgamma = self._g32(node.params["gamma"].name) if a["scale"] else None
+        dbeta = self._g32(node.params["beta"].name)
+        has_res = len(node.inputs) > 1
+        gres = self._grad(node.inputs[1]) if has_res and self.needs_grad[node.inputs[1].id] else None
+        res_acc = self._acc(node, 1) if gres is not None else 0
+        need_dz = self.needs_grad[zin.id]
+        if need_dz and self._acc(node, 0):
+            gz = self._tmp_like(z)
+        else:
+            gz = self._grad(zin) if need_dz else self._tmp_like(z)
+        native.call("bn_backward", gy.p, i64(gy.ld), y.p if a["relu"] else None, i64(y.ld), z.p,
+                    i64(z.ld), i64(z.rows), i32(z.cols), gamma, ptr(info["mean_rstd"]), dgamma,
+                    dbeta, i32(0), f32(1.0), ptr(info["coef"]), ptr(self.scratch), gz.p,
+                    i64(gz.ld), gres.p if gres else None, i64(gres.ld if gres else 0),
+                    i32(res_acc), s)
+        if need_dz and self._acc(node, 0):
+            gdst = self._grad(zin)
+            native.call("copy2d", gz.p, i64(gz.ld), gdst.p, i64(gdst.ld), i64(gz.rows),
+                        i32(gz.cols), i32(1), s)
+
+    _tmp: Dict[tuple, _Buf] = {}
+
+    def _tmp_like(self, b: _Buf) -> _Buf:
+        key = (self.device.index, b.rows, b.ld)
+        if key not in self._tmp:
+            self._tmp[key] = _Buf(torch.zeros((b.rows, b.ld), dtype=torch.float16,
+                                              device=self.device), b.rows, b.cols, b.ld)
+        t = self._tmp[key]
+        return _Buf(t.t, b.rows, b.cols, b.ld)
+
+    def _bwd_act(self, node, s):
+        xin = node.inputs[0]
+        if not self.needs_grad[xin.id]:
+            return
+        y, gy, gx = self.buf[node.output.id], self._grad(node.output), self._grad(xin)
+        native.call("relu_backward", gy.p, i64(gy.ld), y.p, i64(y.ld), gx.p, i64(gx.ld),
+                    i32(self._acc(node, 0)), i64(gy.rows), i32(_pad8(gy.cols)), s)
+
+    def _bwd_add(self, node, s):
+        y, gy = self.buf[node.output.id], self._grad(node.output)
+        for idx, t in enumerate(node.inputs):
+            if not self.needs_grad[t.id]:
+                continue
+            gx = self._grad(t)
+            native.call("relu_backward", gy.p, i64(gy.ld), y.p if node.attrs["relu"] else None,
+                        i64(y.ld), gx.p, i64(gx.ld), i32(self._acc(node, idx)), i64(gy.rows),
+                        i32(_pad8(gy.cols)), s)
+
+    def _bwd_pool(self, node, s):
+        xin = node.inputs[0]
+        if not self.needs_grad[xin.id]:
+            return
+        info = self._per_node[id(node)]
+        gy, gx = self._grad(node.output), self._grad(xin)
+        args = self._pool_args(node)
+        native.call("pool_backward", gy.p, i64(gy.ld), ptr(info.get("argmax")), gx.p, i64(gx.ld),
+                    i32(self._acc(node, 0)), *args, s)
+
+    def _bwd_spatial_mean(self, node, s):
+        xin = node.inputs[0]
+        if not self.needs_grad[xin.id]:
+            return
+        gy, gx = self._grad(node.output), self._grad(xin)
+        n, h, w, c = xin.shape
+        native.call("spatial_mean_backward", gy.p, i64(gy.ld), gx.p, i64(gx.ld),
+                    i32(self._acc(node, 0)), i32(n), i32(h * w), i32(c), s)
+
+    def _bwd_reshape(self, node, s):
+        xin = node.inputs[0]
+        if node.output.id in self._alias or not self.needs_grad[xin.id]:
+            return
+        gy, gx = self._grad(node.output), self._grad(xin)
+        native.call("copy_rows", gy.p, i64(gy.ld), gx.p, i64(gy.cols), i64(gy.rows), i64(gy.cols),
+                    i32(self._acc(node, 0)), s)
+
+    def _bwd_affine(self, node, s):
+        a = node.attrs
+        xin = node.inputs[0]
+        x, y = self.buf[xin.id], self.buf[node.output.id]
+        gy = self._grad(node.output)
+        spec = node.params["weights"]
+        out, in_pad = spec.shape
+        relu = a["activation"] == "relu"
+        self._bias_act_bwd(node, gy, y, relu, node.params["biases"].name, s, gy.ld)
+        if self.needs_grad[xin.id]:
+            gx = self._grad(xin)
+            native.call("gemm_nn", gy.p, self._w16(spec.name), gx.p, i32(gy.rows), i32(in_pad),
+                        i32(out), i64(gy.ld), i64(in_pad), i64(gx.ld), i32(0),
+                        i32(self._acc(node, 0)), s)
+        native.call("gemm_nt", gy.p, x.p, self._g32(spec.name), i32(out), i32(in_pad),
+                    i32(gy.rows), i64(gy.ld), i64(x.ld), i64(in_pad), ptr(self.workspace),
+                    i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
+
+    def _bwd_dropout(self, node, s):
+        xin = node.inputs[0]
+        if not self.needs_grad[xin.id]:
+            return
+        gy, gx = self._grad(node.output), self._grad(xin)
+        dst = gx if not self._acc(node, 0) else self._tmp_like(gy)
+        native.call("dropout", gy.p, dst.p, i64(gy.rows * gy.ld), f32(node.attrs["keep_prob"]),
+                    u64(self.dropout_seed), u64(self._dropout_offset(node)), s)
+        if dst is not gx:
+            native.call("copy2d", dst.p, i64(dst.ld), gx.p, i64(gx.ld), i64(gx.rows),
+                        i32(_pad8(gx.cols)), i32(1), s)
+
+    def _bwd_lrn(self, node, s):
+        xin = node.inputs[0]
+        if not self.needs_grad[xin.id]:
+            return
+        a = node.attrs
+        x, gy, gx = self.buf[xin.id], self._grad(node.output), self._grad(xin)
+        native.call("lrn_backward", x.p, gy.p, gx.p, i32(self._acc(node, 0)), i64(x.rows),
+                    i32(x.cols), i32(a["radius"]), f32(a["bias"]), f32(a["alpha"]),
+                    f32(a["beta"]), s)
+
+    def _bwd_concat(self, node, s):
+        gy = self._grad(node.output)
+        off = 0
+        for idx, t in enumerate(node.inputs):
+            cols = self.buf[t.id].cols
+            if self.needs_grad[t.id]:
+                gx = self._grad(t)
+                native.call("copy2d", ctypes.c_void_p(gy.t.data_ptr() + off * 2), i64(gy.ld),
+                            gx.p, i64(gx.ld), i64(gx.rows), i32(cols),
+                            i32(self._acc(node, idx)), s)
+            off += cols
+
+    def _bwd_pad_channels(self, node, s):
+        xin = node.inputs[0]
+        if not self.needs_grad[xin.id]:
+            return
+        gy, gx = self._grad(node.output), self._grad(xin)
+        off = node.attrs["before"]
+        native.call("copy2d", ctypes.c_void_p(gy.t.data_ptr() + off * 2), i64(gy.ld), gx.p,
+                    i64(gx.ld), i64(gx.rows), i32(gx.cols), i32(self._acc(node, 0)), s)
+
+    # ------------------------------------------------------------------ inspection
+    def logits(self) -> torch.Tensor:
+        b = self.buf[self.graph.logits.id]
+        return b.t[:, :b.cols]
+
+    def value(self, tensor_id: int) -> torch.Tensor:
+        b = self.buf[tensor_id]
+        t = self.graph.tensors[tensor_id]
+        return b.t[:, :b.cols].reshape(t.shape)
+
+    def grad_value(self, tensor_id: int) -> torch.Tensor:
+        b = self.gbuf[tensor_id]
+        t = self.graph.tensors[tensor_id]
+        return b.t[:, :b.cols].reshape(t.shape)

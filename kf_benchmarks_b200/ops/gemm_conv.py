@@ -137,17 +137,42 @@ def conv_fprop(x, w, d: ConvDesc, bias=None, relu=False, out=None, ldy=None):
     return out
 
 
-def conv_dgrad(dy, w, d: ConvDesc, out=None):
+def conv_dgrad(dy, w, d: ConvDesc, out=None, accumulate=False):
     _chk(dy, torch.float16, "dy")
     _chk(w, torch.float16, "w")
-    strided = d.stride_h != 1 or d.stride_w != 1
+    zero_fill = bool(native.load().kfb_conv_dgrad_needs_zero_fill(ctypes.byref(d)))
     if out is None:
-        alloc = torch.zeros if strided else torch.empty
+        alloc = torch.zeros if zero_fill else torch.empty
         out = alloc((d.n, d.h, d.w, d.c), device=dy.device, dtype=torch.float16)
-    elif strided:
+        accumulate = False
+    elif zero_fill and not accumulate:
         out.zero_()
-    native.call("conv_dgrad", ctypes.byref(d), ptr(dy), ptr(w), ptr(out), stream_ptr())
+    native.call("conv_dgrad", ctypes.byref(d), ptr(dy), ptr(w), ptr(out), i32(int(accumulate)),
+                stream_ptr())
     return out
+
+
+def gemm_nn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None,
+            out_dtype=torch.float16, accumulate: bool = False, k: Optional[int] = None,
+            n: Optional[int] = None) -> torch.Tensor:
+    """``a[M,K] @ b[K,N]`` with b read in place (MN-major operand)."""
+    _chk2d(a, "a")
+    _chk2d(b, "b")
+    m = a.shape[0]
+    k = a.shape[1] if k is None else k
+    n = b.shape[1] if n is None else n
+    if out is None:
+        out = torch.empty((m, n), device=a.device, dtype=out_dtype)
+        accumulate = False
+    native.call("gemm_nn", ptr(a), ptr(b), ptr(out), i32(m), i32(n), i32(k), i64(a.stride(0)),
+                i64(b.stride(0)), i64(out.stride(0)), i32(int(out.dtype == torch.float32)),
+                i32(int(accumulate)), stream_ptr())
+    return out
+
+
+def _chk2d(t: torch.Tensor, name: str):
+    if not t.is_cuda or t.dtype != torch.float16 or t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name}: expected 2-D CUDA fp16 with unit inner stride")
 
 
 def conv_wgrad(x, dy, d: ConvDesc, out=None, accumulate=False, scale=1.0, workspace=None):

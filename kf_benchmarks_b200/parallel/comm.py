@@ -1,0 +1,239 @@
+"""Communicators: how one rank (= one process = one GPU) talks to its peers.
+
+The reference reaches its peers through four external stacks (TF in-process NCCL /
+cross-device copies, TF collective ops over gRPC, Horovod, KungFu - SURVEY.md 2.4). Here
+there is one process model - a rank per GPU, rendezvous through ``torch.distributed`` for
+the plumbing only - and three interchangeable communicators:
+
+* ``P2PComm``   - the product path. Gradient / weight arenas, landing buffers and a flag
+  page are cudaMalloc'ed by the native runtime, exported over CUDA IPC and mapped by every
+  peer, so the fused kernels of ``csrc/optim_comm.cu`` read and write peer HBM directly
+  over NVLink 5 / NVSwitch.
+* ``TorchDistComm`` - ``torch.distributed`` all-reduce (NCCL on GPUs, gloo on CPU ranks)
+  followed by a separate update: the "only calls NCCL" baseline and the CPU-replica path.
+* ``SingleComm`` - world size 1.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import List, Optional
+
+import torch
+
+from ..ops import native
+from ..ops.native import f32, i32, i64, ptr
+
+
+class _CudaArray:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can wrap a raw device pointer."""
+
+    def __init__(self, addr: int, numel: int, typestr: str):
+        self.__cuda_array_interface__ = {
+            "shape": (numel,), "typestr": typestr, "data": (addr, False), "version": 3,
+            "strides": None,
+        }
+
+
+_TYPESTR = {torch.float32: "<f4", torch.float16: "<f2", torch.int32: "<i4", torch.uint8: "|u1"}
+
+
+def wrap_device_pointer(addr: int, numel: int, dtype: torch.dtype, device) -> torch.Tensor:
+    return torch.as_tensor(_CudaArray(addr, numel, _TYPESTR[dtype]), device=device)
+
+
+class Comm:
+    rank = 0
+    size = 1
+    kind = "single"
+
+    def barrier(self) -> None:
+        pass
+
+    def allgather_object(self, obj):
+        return [obj]
+
+    def allocator(self):
+        """Arena allocator handed to ParameterStore (None: plain torch allocation)."""
+        return None
+
+    def max_over_ranks(self, value: float) -> float:
+        return value
+
+    def close(self) -> None:
+        pass
+
+
+class SingleComm(Comm):
+    pass
+
+
+def init_process_group(backend: str) -> None:
+    import torch.distributed as dist
+    if dist.is_initialized():
+        return
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29511")
+    dist.init_process_group(backend=backend, rank=int(os.environ["RANK"]),
+                            world_size=int(os.environ["WORLD_SIZE"]))
+
+
+class TorchDistComm(Comm):
+    """torch.distributed plumbing; ``backend`` nccl (GPU baseline) or gloo (CPU replicas)."""
+
+    def __init__(self, backend: str, device):
+        import torch.distributed as dist
+        init_process_group(backend)
+        self.dist = dist
+        self.rank = dist.get_rank()
+        self.size = dist.get_world_size()
+        self.kind = backend
+        self.device = torch.device(device)
+
+    def barrier(self) -> None:
+        self.dist.barrier()
+
+    def allgather_object(self, obj):
+        out = [None] * self.size
+        self.dist.all_gather_object(out, obj)
+        return out
+
+    def all_reduce_(self, t: torch.Tensor) -> torch.Tensor:
+        self.dist.all_reduce(t)
+        return t
+
+    def broadcast_(self, t: torch.Tensor, src: int = 0) -> torch.Tensor:
+        self.dist.broadcast(t, src=src)
+        return t
+
+    def max_over_ranks(self, value: float) -> float:
+        t = torch.tensor([value], dtype=torch.float64,
+                         device=self.device if self.kind == "nccl" else "cpu")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+
+class P2PComm(Comm):
+    """Symmetric memory over CUDA IPC + the fused NVLink kernels.
+
+    Every allocation made through ``allocator()`` is symmetric: all ranks call it in the same
+    order with the same size, the handles are exchanged once, and ``peers(tensor)`` returns the
+    per-rank device pointers of that allocation as mapped into this process.
+    """
+    kind = "p2p"
+
+    def __init__(self, device, bootstrap_backend: str = "gloo"):
+        import torch.distributed as dist
+        init_process_group(bootstrap_backend)
+        self.dist = dist
+        self.rank = dist.get_rank()
+        self.size = dist.get_world_size()
+        if self.size > 8:
+            raise ValueError("P2PComm supports up to 8 ranks (one NVSwitch box)")
+        self.device = torch.device(device)
+        torch.cuda.set_device(self.device)
+        self.lib = native.load()
+        self._allocs = []  # (local_ptr, nbytes, [peer ptrs])
+        self._by_ptr = {}
+        self.seq = 0
+        flag_bytes = int(self.lib.kfb_flag_page_bytes())
+        self.flags = self.symm_alloc(flag_bytes // 4, torch.int32)
+        self._flag_ptrs = self._ptr_array(self.flags)
+        self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self.barrier()
+
+    # -- symmetric allocation -------------------------------------------------------
+    def symm_alloc(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        nbytes = max(int(numel) * torch.empty((), dtype=dtype).element_size(), 256)
+        p = ctypes.c_void_p()
+        native.check(self.lib.kfb_symm_alloc(ctypes.c_longlong(nbytes), ctypes.byref(p)),
+                     "symm_alloc")
+        hb = int(self.lib.kfb_ipc_handle_bytes())
+        handle = ctypes.create_string_buffer(hb)
+        native.check(self.lib.kfb_ipc_get_handle(p, handle), "ipc_get_handle")
+        handles = self.allgather_object(bytes(handle.raw))
+        peer_ptrs = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                peer_ptrs.append(p.value)
+                continue
+            q = ctypes.c_void_p()
+            native.check(self.lib.kfb_ipc_open(ctypes.create_string_buffer(h, hb),
+                                               ctypes.byref(q)), "ipc_open")
+            peer_ptrs.append(q.value)
+        t = wrap_device_pointer(p.value, int(numel), dtype, self.device)
+        self._allocs.append((p.value, nbytes, peer_ptrs))
+        self._by_ptr[p.value] = peer_ptrs
+        return t
+
+    def allocator(self):
+        return lambda n, dt: self.symm_alloc(n, dt)
+
+    def peers(self, t: torch.Tensor) -> List[int]:
+        """Per-rank pointers of the symmetric allocation `t` starts at."""
+        return self._by_ptr[t.data_ptr()]
+
+    def _ptr_array(self, t: torch.Tensor):
+        arr = (ctypes.c_void_p * 8)()
+        for r, a in enumerate(self.peers(t)):
+            arr[r] = a
+        return arr
+
+    def ptr_array(self, t: torch.Tensor):
+        return self._ptr_array(t)
+
+    # -- plumbing ----------------------------------------------------------------------
+    def allgather_object(self, obj):
+        out = [None] * self.size
+        self.dist.all_gather_object(out, obj)
+        return out
+
+    def barrier(self) -> None:
+        torch.cuda.synchronize(self.device)
+        self.dist.barrier()
+
+    def max_over_ranks(self, value: float) -> float:
+        t = torch.tensor([value], dtype=torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def next_seq(self) -> int:
+        self.seq += 1
+        return self.seq
+
+    def device_barrier(self, stream=None) -> None:
+        s = ctypes.c_void_p((stream or torch.cuda.current_stream(self.device)).cuda_stream)
+        native.call("device_barrier", i32(self.rank), i32(self.size), self._flag_ptrs,
+                    ctypes.c_uint(self.next_seq()), s)
+
+    def flag_or(self, flag: torch.Tensor, stream=None) -> None:
+        s = ctypes.c_void_p((stream or torch.cuda.current_stream(self.device)).cuda_stream)
+        native.call("flag_or", i32(self.rank), i32(self.size), self._flag_ptrs,
+                    ctypes.c_uint(self.next_seq()), ptr(flag), s)
+
+    def close(self) -> None:
+        try:
+            self.barrier()
+        except Exception:
+            pass
+        for local, _, peer_ptrs in self._allocs:
+            for r, a in enumerate(peer_ptrs):
+                if r != self.rank:
+                    self.lib.kfb_ipc_close(ctypes.c_void_p(a))
+        self._allocs = []
+
+
+def create_comm(params, device) -> Comm:
+    """Pick the communicator from the environment torchrun / our launcher set up."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world <= 1:
+        return SingleComm()
+    dev = torch.device(device)
+    impl = params.comm_impl
+    if dev.type == "cpu":
+        return TorchDistComm("gloo", dev)
+    if impl == "nccl":
+        return TorchDistComm("nccl", dev)
+    if impl == "gloo":
+        raise ValueError("--comm_impl=gloo needs --device=cpu")
+    return P2PComm(dev)

@@ -1,0 +1,379 @@
+"""Variable-update strategies: what happens to the gradients of a step.
+
+The reference has eight ``VariableMgr`` classes (T/variable_mgr.py:28-831) plus the
+Horovod and KungFu hooks; all of them are data parallelism. On one
+NVSwitch box they collapse onto five behaviours, each a single fused kernel per
+gradient bucket (``csrc/optim_comm.cu``):
+
+==========================  =========================================================
+variable_update             behaviour
+==========================  =========================================================
+independent                 local fused optimizer, no exchange
+replicated, horovod,        all-reduce **sum** fused with unscale + update
+ *_all_reduce                (ResNet divides its LR by num_gpus to compensate,
+                             T/models/resnet_model_legacy.py:311-328)
+parameter_server,           all-reduce **mean** fused with the update (reduce-to-owner +
+ distributed_replicated      broadcast collapse to an all-reduce on NVSwitch)
+kungfu sync_sgd             all-reduce mean (KungFu SynchronousSGDOptimizer)
+kungfu sma                  all-reduce-average of the *weights*, blend, local step
+kungfu async_sgd            pull one random peer's model, blend 1/2, local step (AD-PSGD)
+kungfu ada_sgd              sma until --ada_sgd_switch_step, then sync_sgd
+==========================  =========================================================
+
+Buckets are offset ranges of the flat arenas (``nn/params.py``); the CUDA executor reports
+ranges whose gradients are final during backward and every full bucket is launched on a
+high-priority stream at once, overlapping the exchange with the rest of backward.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from ..nn.params import ParameterStore
+from ..ops import native
+from ..ops.native import f32, i32, i64, ptr
+from ..ops import optim_ref
+from .comm import Comm, P2PComm, TorchDistComm
+
+OPT_IDS = {"sgd": 0, "momentum": 1, "rmsprop": 2, "adam": 3}
+
+
+class Hyper(ctypes.Structure):
+    """Mirror of ``kfb_hyper`` (include/kfb200.h)."""
+    _fields_ = [("opt", ctypes.c_int), ("lr", ctypes.c_float), ("momentum", ctypes.c_float),
+                ("decay", ctypes.c_float), ("epsilon", ctypes.c_float),
+                ("weight_decay", ctypes.c_float), ("grad_scale", ctypes.c_float),
+                ("clip", ctypes.c_float), ("adam_t", ctypes.c_float)]
+
+
+def reduction_semantics(params) -> Tuple[str, bool]:
+    """(algorithm, average) for a parameter set: algorithm in
+    {none, allreduce, sma, pair}."""
+    vu = params.variable_update
+    if vu == "independent":
+        return "none", False
+    if vu in ("replicated", "horovod", "distributed_all_reduce", "collective_all_reduce"):
+        return "allreduce", False
+    if vu in ("parameter_server", "distributed_replicated"):
+        return "allreduce", True
+    if vu == "kungfu":
+        opt = params.kungfu_option
+        if opt == "sync_sgd":
+            return "allreduce", True
+        if opt == "sma":
+            return "sma", True
+        if opt == "async_sgd":
+            return "pair", False
+        if opt == "ada_sgd":
+            return "ada", True
+    raise ValueError("unsupported variable_update=%s" % vu)
+
+
+def plan_buckets(total: int, bucket_elems: int, num_buckets: int = 0) -> List[Tuple[int, int]]:
+    """Split [0, total) into buckets: `num_buckets` equal parts (gradient_repacking) or
+    size-based. Boundaries are multiples of 128 elements (arena slot alignment)."""
+    if total <= 0:
+        return []
+    if num_buckets and num_buckets > 0:
+        per = -(-total // num_buckets)
+    else:
+        per = max(bucket_elems, 128)
+    per = (per + 127) // 128 * 128
+    out = []
+    lo = 0
+    while lo < total:
+        hi = min(lo + per, total)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+class UpdateEngine:
+    """Applies one step's gradients to the model according to the strategy."""
+
+    def __init__(self, params, store: ParameterStore, comm: Comm, model, seed: int = 1234):
+        self.params = params
+        self.store = store
+        self.comm = comm
+        self.model = model
+        self.algo, self.average = reduction_semantics(params)
+        if comm.size == 1 and self.algo != "none":
+            self.algo = "none"  # a single replica: nothing to exchange
+        self.device = store.device
+        self.cuda = self.device.type == "cuda"
+        self.opt = OPT_IDS[params.optimizer]
+        self.step_count = 0
+        n = store.num_trainable_padded
+        self.total = n
+        self.m = store.opt_slot("m") if self.opt != 0 else None
+        self.v = store.opt_slot("v") if self.opt in (2, 3) else None
+        self.loss_scale = self._initial_loss_scale()
+        self.auto_loss_scale = bool(params.use_fp16 and params.fp16_enable_auto_loss_scale)
+        self.loss_scale_normal_steps = 0
+        self.skipped_steps = 0
+        bucket_elems = max(int(params.bucket_bytes) // 4, 128)
+        self.buckets = plan_buckets(n, bucket_elems, params.gradient_repacking)
+        self._ready_hi = 0
+        self._launched = 0
+        self._rng = np.random.RandomState(seed + 7919 * comm.rank)
+        self.relaxed = params.variable_consistency == "relaxed"
+        if self.cuda:
+            self.skip_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._setup_comm_buffers()
+
+    # ------------------------------------------------------------------ setup
+    def _initial_loss_scale(self) -> float:
+        p = self.params
+        if not p.use_fp16 and self.device.type != "cuda":
+            return 1.0
+        if p.fp16_loss_scale is not None:
+            return float(p.fp16_loss_scale)
+        return float(self.model.get_fp16_loss_scale()) if (p.use_fp16 or self.cuda) else 1.0
+
+    def _setup_comm_buffers(self) -> None:
+        c = self.comm
+        self.reduced = None
+        if isinstance(c, P2PComm) and self.algo != "none":
+            st = self.store
+            self.reduced = c.symm_alloc(self.total, torch.float32)
+            self._grad_ptrs = c.ptr_array(st.grad)
+            self._w_ptrs = c.ptr_array(st.w32)
+            self._red_ptrs = c.ptr_array(self.reduced)
+            self._flag_ptrs = c.ptr_array(c.flags)
+            self.ready_event = torch.cuda.Event()
+            self.done_event = torch.cuda.Event()
+            if self.algo in ("pair", "ada"):
+                pass
+            if self.algo == "pair":
+                self.pub = c.symm_alloc(3 * self.total, torch.float32)
+                self.ver = c.symm_alloc(64, torch.int32)
+                self._pub_peers = c.peers(self.pub)
+                self._ver_peers = c.peers(self.ver)
+                self.torn = torch.zeros(1, dtype=torch.int32, device=self.device)
+                self.my_version = 0
+
+    # ------------------------------------------------------------------ per-step
+    def learning_rate(self, global_step: int, examples_per_step: int, num_examples: int) -> float:
+        from .. import lr as lr_mod
+        return lr_mod.get_learning_rate(self.params, global_step, num_examples, self.model,
+                                        examples_per_step)
+
+    def _hyper(self, lr: float) -> Hyper:
+        p = self.params
+        h = Hyper()
+        h.opt = self.opt
+        h.lr = lr
+        if self.opt == 1:
+            h.momentum = p.momentum
+        elif self.opt == 2:
+            h.momentum, h.decay, h.epsilon = p.rmsprop_momentum, p.rmsprop_decay, p.rmsprop_epsilon
+        elif self.opt == 3:
+            h.momentum, h.decay, h.epsilon = p.adam_beta1, p.adam_beta2, p.adam_epsilon
+        h.weight_decay = p.weight_decay or 0.0
+        scale = 1.0 / self.loss_scale
+        if self._effective_algo() == "allreduce" and self.average:
+            scale /= self.comm.size
+        h.grad_scale = scale
+        h.clip = p.gradient_clip if p.gradient_clip else 0.0
+        h.adam_t = float(self.step_count + 1)
+        return h
+
+    def begin_step(self, lr: float) -> None:
+        """Called before backward: arms the overlap scheduler."""
+        self._h = self._hyper(lr)
+        self._ready_hi = 0
+        self._launched = 0
+        if self.cuda and self.auto_loss_scale:
+            self.skip_flag.zero_()
+
+    def _effective_algo(self) -> str:
+        if self.algo != "ada":
+            return self.algo
+        return "sma" if self.step_count < self.params.ada_sgd_switch_step else "allreduce"
+
+    def on_grads_ready(self, lo: int, hi: int) -> None:
+        """Backward-completion callback: gradients of arena range [lo, hi) are final. Ranges
+        arrive in increasing offset order (the arena is laid out that way)."""
+        self._ready_hi = max(self._ready_hi, hi)
+        if not self._can_overlap():
+            return
+        while self._launched < len(self.buckets) and \
+                self.buckets[self._launched][1] <= self._ready_hi:
+            self._launch_bucket(self.buckets[self._launched], overlapped=True)
+            self._launched += 1
+
+    def _can_overlap(self) -> bool:
+        return (self.cuda and isinstance(self.comm, P2PComm) and
+                self._effective_algo() == "allreduce" and not self.auto_loss_scale and
+                not self.relaxed)
+
+    def finish_step(self) -> None:
+        """Called after backward: runs whatever has not been overlapped and makes the compute
+        stream wait for the update."""
+        algo = self._effective_algo()
+        if self.auto_loss_scale:
+            self._check_finite()
+        if not self.cuda or isinstance(self.comm, TorchDistComm):
+            self._finish_torch(algo)
+        elif algo == "none":
+            self._local_update(0, self.total)
+        elif algo == "pair":
+            self._pair_update()
+        else:
+            while self._launched < len(self.buckets):
+                self._launch_bucket(self.buckets[self._launched], overlapped=self._can_overlap())
+                self._launched += 1
+            if self._can_overlap():
+                self.done_event.record(self.comm.comm_stream)
+                torch.cuda.current_stream(self.device).wait_event(self.done_event)
+        if self.auto_loss_scale:
+            self._update_loss_scale()
+        self.step_count += 1
+
+    # ------------------------------------------------------------------ CUDA paths
+    def _s(self, stream=None):
+        return ctypes.c_void_p((stream or torch.cuda.current_stream(self.device)).cuda_stream)
+
+    def _ptr_at(self, t: Optional[torch.Tensor], off: int):
+        if t is None:
+            return None
+        return ctypes.c_void_p(t.data_ptr() + off * t.element_size())
+
+    def _local_update(self, lo: int, hi: int) -> None:
+        st = self.store
+        native.call("optimizer_step", self._ptr_at(st.w32, lo), self._ptr_at(st.grad, lo),
+                    self._ptr_at(self.m, lo), self._ptr_at(self.v, lo), self._ptr_at(st.w16, lo),
+                    i64(hi - lo), ctypes.byref(self._h), None,
+                    ptr(self.skip_flag) if self.auto_loss_scale else None, self._s())
+
+    def _launch_bucket(self, bucket, overlapped: bool) -> None:
+        lo, hi = bucket
+        st, c = self.store, self.comm
+        algo = self._effective_algo()
+        stream = None
+        if overlapped:
+            self.ready_event.record(torch.cuda.current_stream(self.device))
+            c.comm_stream.wait_event(self.ready_event)
+            stream = c.comm_stream
+        mode = 1 if algo == "sma" else 0
+        src = self._w_ptrs if mode == 1 else self._grad_ptrs
+        h = self._h
+        native.call("allreduce_update", i32(mode), i32(c.rank), i32(c.size), src, self._red_ptrs,
+                    self._flag_ptrs, i64(lo), i64(hi - lo), ctypes.c_uint(c.next_seq()),
+                    ptr(st.w32), ptr(st.grad), ptr(self.m), ptr(self.v), ptr(st.w16),
+                    ctypes.byref(h), None, ptr(self.skip_flag) if self.auto_loss_scale else None,
+                    f32(self.params.sma_alpha), i32(0), self._s(stream))
+
+    def _pair_update(self) -> None:
+        c, st = self.comm, self.store
+        peer = int(self._rng.randint(0, c.size - 1))
+        if peer >= c.rank:
+            peer += 1
+        self.my_version += 1
+        native.call("pair_average_update", ctypes.c_void_p(self._pub_peers[peer]),
+                    ctypes.c_void_p(self._ver_peers[peer]), ptr(self.pub), ptr(self.ver),
+                    i64(self.total), i64(self.total), ptr(st.w32), ptr(st.grad), ptr(self.m),
+                    ptr(self.v), ptr(st.w16), ctypes.byref(self._h), None,
+                    ctypes.c_uint(self.my_version), i32(1), ptr(self.torn), i32(0), self._s())
+
+    def _check_finite(self) -> None:
+        st = self.store
+        if self.cuda:
+            native.call("check_finite", ptr(st.grad), i64(self.total), ptr(self.skip_flag),
+                        self._s())
+            if isinstance(self.comm, P2PComm):
+                self.comm.flag_or(self.skip_flag)
+            elif isinstance(self.comm, TorchDistComm):
+                self.comm.all_reduce_(self.skip_flag)
+        else:
+            bad = 0 if bool(torch.isfinite(st.grad).all()) else 1
+            if isinstance(self.comm, TorchDistComm):
+                t = torch.tensor([bad], dtype=torch.int32)
+                self.comm.all_reduce_(t)
+                bad = int(t.item())
+            self._cpu_skip = bad != 0
+
+    def _update_loss_scale(self) -> None:
+        """Host mirror of the state machine (T/variable_mgr_util.py:51-88). The decision needs
+        the flag on the host; auto loss scaling therefore costs one small D2H per step."""
+        skipped = bool(self.skip_flag.item()) if self.cuda else self._cpu_skip
+        self.loss_scale, self.loss_scale_normal_steps = next_loss_scale(
+            self.loss_scale, self.loss_scale_normal_steps, skipped,
+            self.params.fp16_inc_loss_scale_every_n)
+        if skipped:
+            self.skipped_steps += 1
+
+    # ------------------------------------------------------------------ torch paths
+    def _finish_torch(self, algo: str) -> None:
+        """CPU replicas (gloo) and the NCCL comparison baseline: collective, then update."""
+        st, c = self.store, self.comm
+        h = self._h
+        skip = False
+        if self.auto_loss_scale:
+            skip = bool(self.skip_flag.item()) if self.cuda else self._cpu_skip
+        if algo == "allreduce":
+            c.all_reduce_(st.grad)
+        blend_src = None
+        if algo == "sma":
+            avg = st.w32.clone()
+            c.all_reduce_(avg)
+            avg /= c.size
+            blend_src = (avg, self.params.sma_alpha)
+        elif algo == "pair":
+            blend_src = (self._pair_pull_torch(), 0.5)
+        if skip:
+            return
+        if blend_src is not None:
+            other, a = blend_src
+            st.w32.mul_(1.0 - a).add_(other, alpha=a)
+        if self.cuda:
+            self._local_update(0, self.total)
+        else:
+            optim_ref.apply_update(h, st.w32, st.grad, self.m, self.v, st.w16)
+
+    def _pair_pull_torch(self) -> torch.Tensor:
+        """PairAveraging over torch.distributed: every rank draws a peer from a shared
+        permutation-free schedule; implemented as an all-gather of the models (baseline
+        quality - the product path reads the peer's HBM directly)."""
+        c, st = self.comm, self.store
+        peer = int(self._rng.randint(0, c.size - 1))
+        if peer >= c.rank:
+            peer += 1
+        models = [torch.empty_like(st.w32) for _ in range(c.size)]
+        c.dist.all_gather(models, st.w32)
+        return models[peer]
+
+    # ------------------------------------------------------------------ init-time collectives
+    def broadcast_initial_variables(self) -> None:
+        """Rank 0's variables (and BN statistics) become everyone's (T/variable_mgr.py:342-356,
+        hvd.broadcast_global_variables / kungfu broadcast, T/benchmark_cnn.py:2094-2100)."""
+        c, st = self.comm, self.store
+        if c.size == 1:
+            return
+        if isinstance(c, P2PComm):
+            w_ptrs = c.ptr_array(st.w32)
+            native.call("broadcast_pull", i32(c.rank), i32(c.size), w_ptrs, c.ptr_array(c.flags),
+                        i32(0), i64(0), i64(self.total), ctypes.c_uint(c.next_seq()),
+                        ptr(st.w32), ptr(st.w16), i32(0), self._s())
+            torch.cuda.synchronize(self.device)
+            # the (small) non-trainable state goes through the bootstrap group
+            state = st.state.cpu()
+            c.dist.broadcast(state, src=0)
+            st.state.copy_(state)
+        else:
+            c.broadcast_(st.w32, 0)
+            c.broadcast_(st.state, 0)
+            st.sync_shadow()
+        c.barrier()
+
+
+def next_loss_scale(scale: float, normal_steps: int, skipped: bool, inc_every_n: int):
+    """One transition of the automatic loss-scale state machine."""
+    if skipped:
+        return scale / 2.0, 0
+    if normal_steps < inc_every_n:
+        return scale, normal_steps + 1
+    return scale * 2.0, 0

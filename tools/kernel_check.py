@@ -53,6 +53,14 @@ case("fprop_3x3_s2_c64_k64", "fprop", n=2, h=56, w=56, c=64, k=64, r=3, s=3, str
      pad="SAME_RESNET")
 case("wgrad_3x3_s2_c64_k64", "wgrad", n=2, h=56, w=56, c=64, k=64, r=3, s=3, stride=2,
      pad="SAME_RESNET")
+case("dgrad_3x3_s2_c64_k64", "dgrad", n=2, h=56, w=56, c=64, k=64, r=3, s=3, stride=2,
+     pad="SAME_RESNET")
+case("dgrad_3x3_s2_valid_c64_k96_odd", "dgrad", n=2, h=35, w=35, c=64, k=96, r=3, s=3, stride=2,
+     pad="VALID")
+case("dgrad_3x3_s2_same_c32_k32", "dgrad", n=3, h=16, w=16, c=32, k=32, r=3, s=3, stride=2,
+     pad="SAME")
+case("dgrad_5x5_s2_same_c64_k64", "dgrad", n=2, h=15, w=15, c=64, k=64, r=5, s=5, stride=2,
+     pad="SAME")
 case("fprop_7x7_s2_c8_k64", "fprop", n=2, h=64, w=64, c=8, k=64, r=7, s=7, stride=2,
      pad="SAME_RESNET")
 case("fprop_big_3x3_c256", "fprop", n=32, h=14, w=14, c=256, k=256, r=3, s=3, stride=1, pad="SAME")
