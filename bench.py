@@ -1,0 +1,223 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 fp16 synthetic-ImageNet training images/sec on N B200s.
+
+Contract (driver): ``python bench.py --gpus N --steps K --warmup W`` (under torchrun for
+N > 1) prints ONE JSON line from rank 0. The metric/config are BASELINE.json's: ResNet-50
+v1, fp16 compute / fp32 master weights, batch 256 per GPU, synthetic ImageNet,
+``variable_update=replicated`` (fused P2P all-reduce + Nesterov-momentum SGD), device-timed,
+max over ranks. ``--impl reference`` reports that the TensorFlow/KungFu reference cannot be
+installed on this image.
+
+Timed region = exactly K full training steps (forward, loss, backward, gradient exchange,
+optimizer update, BN statistics) bracketed by barrier + synchronize on both sides and CUDA
+events on the launching stream. Every step touches > 5 GB of activations, far more than the
+126 MB L2, so no explicit L2 flush is needed between iterations.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# reference numbers that exist: RTX 3090, fp32, parameter_server
+_PUBLISHED = {1: 416.43, 2: 713.23}
+
+
+def _reference_arm(args) -> int:
+    """The reference is a TF 2.5 (compat.v1) + KungFu/Horovod program; neither TensorFlow nor
+    KungFu nor Horovod wheels exist in /opt/wheelhouse and the tree has no setup.py /
+    pyproject.toml, so `pip install /root/reference` cannot succeed."""
+    why = ("reference (tf_cnn_benchmarks fork) needs TensorFlow 2.5 + KungFu/Horovod; none are "
+           "installable offline on this image and the tree has no setup.py/pyproject.toml")
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    try:
+        sys.path.insert(0, ref_dir)
+        import tensorflow  # noqa: F401
+        why = "tensorflow imported but the reference run path is not wired on this image"
+    except Exception:
+        pass
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                smax.append(float(parts[2]))
+                power.append(float(parts[3]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def _timed_steps(bench, steps, torch, e2e: bool):
+    """K steps between barrier+sync on both sides; returns device ms (this rank)."""
+    dev = bench.device
+    torch.cuda.synchronize(dev)
+    bench.comm.barrier()
+    torch.cuda.synchronize(dev)
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    start.record()
+    last = None
+    for _ in range(steps):
+        bench._step(train=True, backward=True)
+        if e2e:
+            last = bench.executor.read_loss()  # device->host read of the step's result
+    end.record()
+    end.synchronize()
+    torch.cuda.synchronize(dev)
+    bench.comm.barrier()
+    wall = time.time() - t0
+    return start.elapsed_time(end), wall, last
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="resnet50")
+    ap.add_argument("--batch_size", type=int, default=256)
+    ap.add_argument("--variable_update", default="replicated")
+    ap.add_argument("--kungfu_option", default="sync_sgd")
+    ap.add_argument("--optimizer", default="momentum")
+    ap.add_argument("--comm_impl", default="p2p")
+    ap.add_argument("--no_e2e", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return _reference_arm(args)
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        from kf_benchmarks_b200.parallel import launcher
+        return launcher.launch_local([os.path.abspath(__file__)] + sys.argv[1:], args.gpus)
+
+    import torch
+    from kf_benchmarks_b200 import benchmark, params as params_lib
+    from kf_benchmarks_b200.data import inputs
+    from kf_benchmarks_b200.ops import native
+
+    warmup = max(args.warmup, 3)
+    kungfu = args.variable_update in ("kungfu", "horovod")
+    p = params_lib.make_params(
+        model=args.model, batch_size=args.batch_size, use_fp16=True,
+        variable_update=args.variable_update, kungfu_option=args.kungfu_option,
+        num_gpus=1 if kungfu else args.gpus, optimizer=args.optimizer,
+        comm_impl=args.comm_impl, num_batches=args.steps, num_warmup_batches=warmup,
+        data_format="NHWC")
+    p = benchmark.setup(p)
+    bench = benchmark.BenchmarkCNN(p)
+    rank = bench.rank
+    bench._build(phase_train=True)
+    bench.engine.broadcast_initial_variables()
+    for _ in range(warmup):
+        bench._step()
+    sampler = ClockSampler(bench.device.index or 0)
+    if rank == 0:
+        sampler.start()
+    launches0 = native.launch_count
+    ms, wall, _ = _timed_steps(bench, args.steps, torch, e2e=False)
+    launches = native.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_max = bench.comm.max_over_ranks(ms)
+    n_ranks = max(bench.world, 1)
+    global_batch = args.batch_size * n_ranks
+    value = global_batch * args.steps / (ms_max / 1e3)
+    loss = bench.executor.read_loss()[0]
+
+    e2e = None
+    if not args.no_e2e:
+        # same metric through the public step API with per-step H2D of the inputs from pinned
+        # host memory and a D2H read of the loss
+        src = inputs.SyntheticHostSource(args.batch_size, bench.model.image_size, 3, bench.nclass,
+                                         bench.device, seed=77 + rank, ring=3)
+        bench.input_source = src
+        for _ in range(2):
+            bench._step()
+        ms_e, _, last = _timed_steps(bench, args.steps, torch, e2e=True)
+        ms_e = bench.comm.max_over_ranks(ms_e)
+        e2e = {"value": global_batch * args.steps / (ms_e / 1e3), "unit": "images/sec",
+               "h2d_bytes_per_step": src.bytes_per_step * n_ranks,
+               "d2h_bytes_per_step": 32 * n_ranks, "ms_per_step": ms_e / args.steps}
+    if rank == 0:
+        pub = _PUBLISHED.get(n_ranks)
+        out = {
+            "metric": "ResNet-50 fp16 synthetic-ImageNet training images/sec "
+                      "(device-timed, max over ranks)",
+            "value": value, "unit": "images/sec", "n_gpus": n_ranks, "steps": args.steps,
+            "warmup": warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": (value / pub) if pub else None,
+            "dtype": "fp16", "data": "synthetic",
+            "config": {"model": args.model, "global_batch": global_batch, "seq_len": None,
+                       "image_size": bench.model.image_size,
+                       "parallelism": "dp%d" % n_ranks,
+                       "variable_update": args.variable_update, "optimizer": args.optimizer,
+                       "comm_impl": args.comm_impl if n_ranks > 1 else "none",
+                       "l2_hygiene": "per-step working set (>5 GB activations) exceeds the "
+                                     "126 MB L2; no explicit flush",
+                       "baseline_note": "vs_baseline divides by the reference's only published "
+                                        "numbers (RTX 3090, fp32, nan loss; BASELINE.md)"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "final_loss": loss, "wall_s_timed": wall,
+        }
+        print(json.dumps(out))
+    bench.comm.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
