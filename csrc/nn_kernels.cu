@@ -1104,6 +1104,70 @@ extern "C" int kfb_softmax_xent(const float* logits, long long ldl, const int* l
   return 0;
 }
 
+// ---------------------------------------------------------------------------
+// Allocation-free variant of kfb_softmax_xent.
+//
+// kfb_softmax_xent needs three per-row scratch arrays (row losses and the top-1 / top-5 hit
+// flags that the finalize kernel folds). Some callers have no way to provide them: code that
+// runs where cudaMalloc is off limits (inside a latency-critical serving or training loop
+// where the implicit device synchronisation of an allocation is not acceptable, inside a
+// region that is being stream-captured, or embedded in a host application that owns all device
+// memory and hands this library none). For those, the scratch lives in the fixed-size device
+// array below, which every GPU that loads this library keeps until the process exits
+// (kXentStaticMaxRows * 12 bytes = 48 KiB).
+//
+// In host code `g_xent_static_scratch` is only a host-side handle for the symbol, not a device
+// address; the per-device address is looked up with cudaGetSymbolAddress the first time the
+// entry point runs on a device (with that device current) and cached.
+// ---------------------------------------------------------------------------
+namespace kfb {
+constexpr int kXentStaticMaxRows = 4096;
+static __device__ __align__(256) unsigned char
+    g_xent_static_scratch[kXentStaticMaxRows * 3 * sizeof(float)];
+
+constexpr int kMaxDevices = 64;
+static unsigned char* g_xent_static_addr[kMaxDevices] = {nullptr};
+}  // namespace kfb
+
+extern "C" int kfb_softmax_xent_static_max_rows(void) { return kfb::kXentStaticMaxRows; }
+
+extern "C" int kfb_softmax_xent_static(const float* logits, long long ldl, const int* labels,
+                                       int rows, int classes, float grad_scale,
+                                       const float* dyn_scale, void* dlogits, long long lddl,
+                                       float* out3, void* stream) {
+  KFB_REQUIRE(rows > 0 && classes > 0, "softmax_xent_static: bad shape");
+  KFB_REQUIRE(rows <= kXentStaticMaxRows,
+              "softmax_xent_static: %d rows exceed the built-in scratch (max %d rows); use "
+              "kfb_softmax_xent with caller-provided scratch",
+              rows, kXentStaticMaxRows);
+  KFB_REQUIRE(out3 != nullptr, "softmax_xent_static: out3 is required");
+  int dev = -1;
+  KFB_CHECK_CUDA(cudaGetDevice(&dev));
+  KFB_REQUIRE(dev >= 0 && dev < kMaxDevices, "softmax_xent_static: device ordinal %d out of range",
+              dev);
+  if (g_xent_static_addr[dev] == nullptr) {
+    // one-time set-up for this device (the current one): resolve the symbol's device address
+    unsigned char* p = nullptr;
+    KFB_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_xent_static_scratch));
+    KFB_REQUIRE(p != nullptr, "softmax_xent_static: symbol address lookup returned null");
+    g_xent_static_addr[dev] = p;
+  }
+  unsigned char* base = g_xent_static_addr[dev];
+  float* loss_rows = reinterpret_cast<float*>(base);
+  int* top1 = reinterpret_cast<int*>(base + kXentStaticMaxRows * sizeof(float));
+  int* top5 = reinterpret_cast<int*>(base + 2 * kXentStaticMaxRows * sizeof(float));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int warps_per_block = 8;
+  // Rows [0, rows) of all three arrays are rewritten by the first kernel before the second
+  // one reads them, so nothing left over from an earlier call has to be cleared.
+  softmax_xent_kernel<<<(rows + warps_per_block - 1) / warps_per_block, 256, 0, st>>>(
+      logits, ldl, labels, rows, classes, grad_scale, dyn_scale, (__half*)dlogits, lddl,
+      loss_rows, top1, top5);
+  loss_finalize_kernel<<<1, 256, 0, st>>>(loss_rows, top1, top5, rows, out3);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int kfb_cast_f32_f16(const float* in, void* out, long long n, void* stream) {
   cast_f32_f16_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(in, (__half*)out, n);
   KFB_CHECK_CUDA(cudaGetLastError());

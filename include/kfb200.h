@@ -142,6 +142,21 @@ int kfb_lrn_backward(const void* x, const void* dy, void* dx, int accumulate, lo
 int kfb_softmax_xent(const float* logits, long long ldl, const int* labels, int rows, int classes,
                      float grad_scale, const float* dyn_scale, void* dlogits, long long lddl,
                      float* loss_rows, int* top1, int* top5, float* out3, void* stream);
+/* Allocation-free variant of kfb_softmax_xent (no counterpart in the reference; it exists for
+ * callers of this library that cannot allocate device memory: hot loops that must not hit the
+ * implicit synchronisation of cudaMalloc, code inside a stream capture, hosts that own the
+ * whole device heap). The per-row scratch lives in a 48 KiB static device array inside the
+ * library, so rows <= kfb_softmax_xent_static_max_rows() (4096); larger batches are rejected
+ * with an error. No cudaMalloc / cudaFree / allocating call is made. The first call on each
+ * device resolves the array's device address (cudaGetSymbolAddress) - make that first call
+ * before starting any stream capture. All calls share the one array: it keeps the previous
+ * call's contents (harmless - each call rewrites the rows it reads), and two calls that may
+ * run concurrently on the same GPU (different streams) race on it and must be serialised by
+ * the caller. out3 = {mean loss, #top-1 hits, #top-5 hits} as for kfb_softmax_xent. */
+int kfb_softmax_xent_static_max_rows(void);
+int kfb_softmax_xent_static(const float* logits, long long ldl, const int* labels, int rows,
+                            int classes, float grad_scale, const float* dyn_scale, void* dlogits,
+                            long long lddl, float* out3, void* stream);
 int kfb_cast_f32_f16(const float* in, void* out, long long n, void* stream);
 
 /* ------------------------------------------------------------------ */
