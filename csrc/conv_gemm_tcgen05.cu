@@ -249,13 +249,15 @@ __global__ void __launch_bounds__(kThreads, 2)
     }
   } else {
     // ===================== epilogue =====================
+    // TMEM -> registers (thread = row) -> bias/ReLU -> per-warp staging tile in shared memory
+    // (the pipeline buffers are free once tmem_full fires) -> global stores in which every
+    // instruction writes four full 128-byte row segments.
     const int quarter = warp & 3;
     const int row = m0 + quarter * 32 + lane;
     if (my_kb > 0) {
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
     }
-    // output row address
     long long row_off = row;
     if (p.sc_P > 0) {
       const int pq = p.sc_P * p.sc_Q;
@@ -268,88 +270,116 @@ __global__ void __launch_bounds__(kThreads, 2)
                     p.sc_W +
                 p.sc_w0 + static_cast<long long>(qq) * p.sc_sw;
     }
+    if (row >= p.M) row_off = -1;  // marks an invalid row
     int col_mem0 = n0;       // first memory column of this tile
     int n_limit = p.N - n0;  // number of valid columns in this tile
     if (MODE == WGRAD) {
       col_mem0 = wg_tap * p.Cn + n0;
       n_limit = p.Cn - n0;
     }
-    const bool row_ok = row < p.M;
-    const long long base =
-        static_cast<long long>(blockIdx.z) * p.split_stride + row_off * p.ldc + col_mem0;
+    if (n_limit > BN) n_limit = BN;
+    const long long base = static_cast<long long>(blockIdx.z) * p.split_stride + col_mem0;
+    constexpr int kStageRowBytes = 144;  // 128 B of payload + 16 B pad (bank-conflict free)
+    uint8_t* stage_buf = smem_a + quarter * (32 * kStageRowBytes);
+    const int esize = p.out_fp32 ? 4 : 2;
+    const int cols_per_chunk = 128 / esize;  // 32 (fp32) or 64 (fp16)
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      if (c * 32 >= n_limit) break;  // warp-uniform
-      uint32_t v[32];
-      if (my_kb > 0) {
-        tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + c * 32, v);
-        tmem_ld_wait();
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = 0u;
-      }
-      float f[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-      if (p.bias != nullptr) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int col = c * 32 + j;
-          if (col < n_limit) f[j] += __ldg(p.bias + n0 + col);
-        }
-      }
-      if (p.relu) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
-      }
-      if (!row_ok) continue;
-      const bool full = (c * 32 + 32 <= n_limit);
-      if (p.out_fp32) {
-        float* o = reinterpret_cast<float*>(p.out) + base + c * 32;
-        if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            float4 r = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-            if (p.accumulate) {
-              const float4 old = *reinterpret_cast<const float4*>(o + j);
-              r.x += old.x; r.y += old.y; r.z += old.z; r.w += old.w;
-            }
-            *reinterpret_cast<float4*>(o + j) = r;
-          }
+    for (int c0 = 0; c0 < BN; c0 += cols_per_chunk) {
+      if (c0 >= n_limit) break;  // warp-uniform
+      // ---- registers <- TMEM, epilogue math, -> staging row of this thread ----
+#pragma unroll 1
+      for (int h = 0; h < cols_per_chunk / 32; ++h) {
+        uint32_t v[32];
+        const int cc = c0 + h * 32;
+        if (my_kb > 0) {
+          tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cc, v);
+          tmem_ld_wait();
         } else {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c * 32 + j < n_limit) o[j] = p.accumulate ? o[j] + f[j] : f[j];
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
         }
-      } else {
-        __half* o = reinterpret_cast<__half*>(p.out) + base + c * 32;
-        if (full && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (cc + j < n_limit) f[j] += __ldg(p.bias + n0 + cc + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+        }
+        uint8_t* srow = stage_buf + lane * kStageRowBytes;
+        if (p.out_fp32) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(srow + j * 4) =
+                make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+        } else {
 #pragma unroll
           for (int j = 0; j < 32; j += 8) {
-            if (p.accumulate) {
-              const uint4 old = *reinterpret_cast<const uint4*>(o + j);
-              const __half2* oh = reinterpret_cast<const __half2*>(&old);
-#pragma unroll
-              for (int t = 0; t < 4; ++t) {
-                const float2 of = __half22float2(oh[t]);
-                f[j + 2 * t] += of.x;
-                f[j + 2 * t + 1] += of.y;
-              }
-            }
             uint4 u;
             u.x = pack_half2(f[j], f[j + 1]);
             u.y = pack_half2(f[j + 2], f[j + 3]);
             u.z = pack_half2(f[j + 4], f[j + 5]);
             u.w = pack_half2(f[j + 6], f[j + 7]);
-            *reinterpret_cast<uint4*>(o + j) = u;
+            *reinterpret_cast<uint4*>(srow + h * 64 + j * 2) = u;
           }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c * 32 + j < n_limit)
-              o[j] = __float2half_rn(p.accumulate ? __half2float(o[j]) + f[j] : f[j]);
         }
       }
+      __syncwarp();
+      // ---- staging -> global: lane handles 16-byte piece (lane % 8) of row it*4 + lane/8 ----
+      const int piece = lane & 7;
+      const int epp = 16 / esize;  // elements per piece
+      const int pcol = c0 + piece * epp;
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int r = it * 4 + (lane >> 3);
+        const long long ro = __shfl_sync(0xffffffffu, row_off, r);
+        if (ro < 0 || pcol >= n_limit) continue;
+        const uint8_t* sp = stage_buf + r * kStageRowBytes + piece * 16;
+        uint8_t* gp = reinterpret_cast<uint8_t*>(p.out) + (base + ro * p.ldc + pcol) * esize;
+        const bool vec_ok = (pcol + epp <= n_limit) && ((reinterpret_cast<uintptr_t>(gp) & 15) == 0);
+        if (p.out_fp32) {
+          float4 val = *reinterpret_cast<const float4*>(sp);
+          if (vec_ok) {
+            if (p.accumulate) {
+              const float4 old = *reinterpret_cast<const float4*>(gp);
+              val.x += old.x; val.y += old.y; val.z += old.z; val.w += old.w;
+            }
+            *reinterpret_cast<float4*>(gp) = val;
+          } else {
+            const float e[4] = {val.x, val.y, val.z, val.w};
+            float* go = reinterpret_cast<float*>(gp);
+            for (int j = 0; j < 4; ++j)
+              if (pcol + j < n_limit) go[j] = p.accumulate ? go[j] + e[j] : e[j];
+          }
+        } else {
+          uint4 val = *reinterpret_cast<const uint4*>(sp);
+          if (vec_ok) {
+            if (p.accumulate) {
+              const uint4 old = *reinterpret_cast<const uint4*>(gp);
+              __half2* a2 = reinterpret_cast<__half2*>(&val);
+              const __half2* o2 = reinterpret_cast<const __half2*>(&old);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 x = __half22float2(a2[j]), y = __half22float2(o2[j]);
+                a2[j] = __floats2half2_rn(x.x + y.x, x.y + y.y);
+              }
+            }
+            *reinterpret_cast<uint4*>(gp) = val;
+          } else {
+            const __half* e = reinterpret_cast<const __half*>(&val);
+            __half* go = reinterpret_cast<__half*>(gp);
+            for (int j = 0; j < 8; ++j)
+              if (pcol + j < n_limit)
+                go[j] = p.accumulate ? __float2half_rn(__half2float(go[j]) + __half2float(e[j]))
+                                     : e[j];
+          }
+        }
+      }
+      __syncwarp();
     }
   }
 

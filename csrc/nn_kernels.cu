@@ -141,6 +141,34 @@ __global__ void __launch_bounds__(kRedThreads)
   }
 }
 
+// Folds the stage-1 partials of channel c in a fixed order. Block = (32 channels, 8 lanes):
+// lane ty sums blocks ty, ty+8, ... (coalesced 128-byte rows), then lane 0 adds the 8 lane sums.
+constexpr int kFoldLanes = 8;
+__device__ __forceinline__ bool fold_partials(const float* __restrict__ partial, int nblocks,
+                                              int C, int c, float& s0, float& s1) {
+  __shared__ float sh[2][kFoldLanes][32];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  float a = 0.f, b = 0.f;
+  if (c < C) {
+    for (int blk = ty; blk < nblocks; blk += kFoldLanes) {
+      a += partial[static_cast<long long>(blk) * 2 * C + c];
+      b += partial[static_cast<long long>(blk) * 2 * C + C + c];
+    }
+  }
+  sh[0][ty][tx] = a;
+  sh[1][ty][tx] = b;
+  __syncthreads();
+  if (ty != 0 || c >= C) return false;
+  s0 = 0.f;
+  s1 = 0.f;
+#pragma unroll
+  for (int l = 0; l < kFoldLanes; ++l) {
+    s0 += sh[0][l][tx];
+    s1 += sh[1][l][tx];
+  }
+  return true;
+}
+
 // BN forward finalize: mean/var from partial sums, moving-average update, and the
 // per-channel affine (scale, shift) the apply kernel uses.
 __global__ void bn_finalize_kernel(const float* __restrict__ partial, int nblocks, int C,
@@ -151,13 +179,9 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partial, int nblock
                                    float* __restrict__ mean_rstd,     // [2][C] saved for bwd
                                    float* __restrict__ scale_shift,   // [2][C]
                                    int update_moving) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float s = 0.f, ss = 0.f;
-  for (int b = 0; b < nblocks; ++b) {
-    s += partial[static_cast<long long>(b) * 2 * C + c];
-    ss += partial[static_cast<long long>(b) * 2 * C + C + c];
-  }
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  float s, ss;
+  if (!fold_partials(partial, nblocks, C, c, s, ss)) return;
   const float mean = s * inv_count;
   float var = ss * inv_count - mean * mean;
   var = var < 0.f ? 0.f : var;
@@ -194,19 +218,23 @@ __global__ void __launch_bounds__(256)
                     long long ldr, __half* __restrict__ y, long long ldy, long long rows, int C,
                     int relu) {
   const int vpr = C >> 3;
-  const long long total = rows * vpr;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long r = i / vpr;
-    const int cv = static_cast<int>(i - r * vpr);
-    float v[8];
-    load8(x + r * ldx + cv * 8, v);
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cv >= vpr) return;
+  float sc[8], sh[8];
+  {
     const float4 s0 = *reinterpret_cast<const float4*>(scale_shift + cv * 8);
     const float4 s1 = *reinterpret_cast<const float4*>(scale_shift + cv * 8 + 4);
     const float4 b0 = *reinterpret_cast<const float4*>(scale_shift + C + cv * 8);
     const float4 b1 = *reinterpret_cast<const float4*>(scale_shift + C + cv * 8 + 4);
-    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-    const float sh[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    sc[0] = s0.x; sc[1] = s0.y; sc[2] = s0.z; sc[3] = s0.w;
+    sc[4] = s1.x; sc[5] = s1.y; sc[6] = s1.z; sc[7] = s1.w;
+    sh[0] = b0.x; sh[1] = b0.y; sh[2] = b0.z; sh[3] = b0.w;
+    sh[4] = b1.x; sh[5] = b1.y; sh[6] = b1.z; sh[7] = b1.w;
+  }
+  for (long long r = static_cast<long long>(blockIdx.y) * blockDim.y + threadIdx.y; r < rows;
+       r += static_cast<long long>(gridDim.y) * blockDim.y) {
+    float v[8];
+    load8(x + r * ldx + cv * 8, v);
 #pragma unroll
     for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], sc[k], sh[k]);
     if (res != nullptr) {
@@ -224,58 +252,64 @@ __global__ void __launch_bounds__(256)
 }
 
 // BN backward finalize: dgamma/dbeta (optionally accumulated into the gradient arena) and
-// the per-channel coefficients of the apply pass.
+// the per-channel coefficients of the apply pass, dz = A*g + B*x + D with
+//   A = gamma*rstd, B = -A*rstd*dgamma/M, D = A*(rstd*mean*dgamma/M - dbeta/M).
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblocks, int C,
                                        float inv_count, const float* __restrict__ gamma,
                                        const float* __restrict__ mean_rstd,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        int accumulate, float grad_scale,
-                                       float* __restrict__ coef /* [3][C]: k, c1, c2 */) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float db = 0.f, dg = 0.f;
-  for (int b = 0; b < nblocks; ++b) {
-    db += partial[static_cast<long long>(b) * 2 * C + c];
-    dg += partial[static_cast<long long>(b) * 2 * C + C + c];
-  }
+                                       float* __restrict__ coef /* [3][C]: A, B, D */) {
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  float db, dg;
+  if (!fold_partials(partial, nblocks, C, c, db, dg)) return;
   if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + dg * grad_scale;
   if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + db * grad_scale;
-  const float rstd = mean_rstd[C + c];
-  coef[c] = (gamma ? gamma[c] : 1.f) * rstd;
-  coef[C + c] = db * inv_count;
-  coef[2 * C + c] = dg * inv_count;
+  const float mean = mean_rstd[c], rstd = mean_rstd[C + c];
+  const float A = (gamma ? gamma[c] : 1.f) * rstd;
+  const float c1 = db * inv_count, c2 = dg * inv_count;
+  coef[c] = A;
+  coef[C + c] = -A * rstd * c2;
+  coef[2 * C + c] = A * (rstd * mean * c2 - c1);
 }
 
-// dz = k * (g - c1 - xhat * c2), g = dy * (mask > 0); optionally d_res (+)= g.
+// dz = A*g + B*x + D, g = dy * (mask > 0); optionally d_res (+)= g.
+__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+  f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
 __global__ void __launch_bounds__(256)
     bn_bwd_apply_kernel(const __half* __restrict__ dy, long long lddy,
                         const __half* __restrict__ mask, long long ldm,
                         const __half* __restrict__ x, long long ldx,
-                        const float* __restrict__ mean_rstd, const float* __restrict__ coef,
-                        __half* __restrict__ dz, long long lddz, __half* __restrict__ dres,
-                        long long lddr, int dres_accumulate, long long rows, int C) {
+                        const float* __restrict__ coef, __half* __restrict__ dz, long long lddz,
+                        __half* __restrict__ dres, long long lddr, int dres_accumulate,
+                        long long rows, int C) {
   const int vpr = C >> 3;
-  const long long total = rows * vpr;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long r = i / vpr;
-    const int cv = static_cast<int>(i - r * vpr);
+  // blockDim = (vx, vy): vx channel vectors x vy rows; channel coefficients live in registers
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cv >= vpr) return;
+  float A[8], B[8], D[8];
+  load8f(coef + cv * 8, A);
+  load8f(coef + C + cv * 8, B);
+  load8f(coef + 2 * C + cv * 8, D);
+  for (long long r = static_cast<long long>(blockIdx.y) * blockDim.y + threadIdx.y; r < rows;
+       r += static_cast<long long>(gridDim.y) * blockDim.y) {
     float g[8], v[8];
     load8(dy + r * lddy + cv * 8, g);
+    load8(x + r * ldx + cv * 8, v);
     if (mask != nullptr) {
       float m[8];
       load8(mask + r * ldm + cv * 8, m);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] = m[k] > 0.f ? g[k] : 0.f;
     }
-    load8(x + r * ldx + cv * 8, v);
     float out[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int c = cv * 8 + k;
-      const float xhat = (v[k] - mean_rstd[c]) * mean_rstd[C + c];
-      out[k] = coef[c] * (g[k] - coef[C + c] - xhat * coef[2 * C + c]);
-    }
+    for (int k = 0; k < 8; ++k) out[k] = fmaf(A[k], g[k], fmaf(B[k], v[k], D[k]));
     store8(dz + r * lddz + cv * 8, out);
     if (dres != nullptr) {
       if (dres_accumulate) {
@@ -292,10 +326,9 @@ __global__ void __launch_bounds__(256)
 // Fold bias-gradient partials: db[c] (+)= scale * sum_b partial[b][0][c]
 __global__ void colsum_finalize_kernel(const float* __restrict__ partial, int nblocks, int C,
                                        float* __restrict__ out, int accumulate, float scale) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float s = 0.f;
-  for (int b = 0; b < nblocks; ++b) s += partial[static_cast<long long>(b) * 2 * C + c];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  float s, unused;
+  if (!fold_partials(partial, nblocks, C, c, s, unused)) return;
   out[c] = (accumulate ? out[c] : 0.f) + s * scale;
 }
 
@@ -845,6 +878,22 @@ static inline int grid_for(long long work_items, int threads = 256, int max_bloc
   return static_cast<int>(b);
 }
 
+// 2-D launch shape for the per-row apply kernels: x = channel vectors, y = rows.
+static inline void apply_launch_shape(long long rows, int C, dim3* grid, dim3* block) {
+  const int vpr = C >> 3;
+  int vx = 1;
+  while (vx < vpr && vx < 256) vx <<= 1;  // power of two >= vpr (capped at 256)
+  if (vx > vpr && (vx >> 1) >= vpr) vx >>= 1;
+  const int vy = 256 / vx > 0 ? 256 / vx : 1;
+  const int gx = (vpr + vx - 1) / vx;
+  long long gy = (rows + vy - 1) / vy;
+  const long long cap = (148LL * 16 + gx - 1) / gx;
+  if (gy > cap) gy = cap;
+  if (gy < 1) gy = 1;
+  *grid = dim3((unsigned)gx, (unsigned)gy, 1);
+  *block = dim3((unsigned)vx, (unsigned)vy, 1);
+}
+
 static inline int reduce_blocks(long long rows, int C) {
   // enough blocks to fill the machine, but each block should own >= 64 rows
   long long b = rows / 64;
@@ -875,13 +924,14 @@ extern "C" int kfb_bn_forward_train(const void* x, long long ldx, long long rows
   channel_reduce_kernel<0><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
       (const __half*)x, ldx, nullptr, 0, nullptr, 0, nullptr, nullptr, 0, rows, C, scratch);
   const float unbias = rows > 1 ? (float)((double)rows / (double)(rows - 1)) : 1.f;
-  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, nb, C, (float)(1.0 / (double)rows),
-                                                     unbias, eps, decay, gamma, beta, moving_mean,
-                                                     moving_var, mean_rstd, scale_shift,
-                                                     update_moving);
-  bn_apply_kernel<<<grid_for(rows * (C / 8)), 256, 0, st>>>(
-      (const __half*)x, ldx, scale_shift, (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
-      relu);
+  bn_finalize_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(
+      scratch, nb, C, (float)(1.0 / (double)rows), unbias, eps, decay, gamma, beta, moving_mean,
+      moving_var, mean_rstd, scale_shift, update_moving);
+  dim3 ag, ab;
+  apply_launch_shape(rows, C, &ag, &ab);
+  bn_apply_kernel<<<ag, ab, 0, st>>>((const __half*)x, ldx, scale_shift,
+                                     (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
+                                     relu);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -896,9 +946,11 @@ extern "C" int kfb_bn_forward_inference(const void* x, long long ldx, long long 
   cudaStream_t st = (cudaStream_t)stream;
   bn_inference_affine_kernel<<<(C + 127) / 128, 128, 0, st>>>(C, eps, gamma, beta, moving_mean,
                                                              moving_var, scale_shift);
-  bn_apply_kernel<<<grid_for(rows * (C / 8)), 256, 0, st>>>(
-      (const __half*)x, ldx, scale_shift, (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
-      relu);
+  dim3 ag, ab;
+  apply_launch_shape(rows, C, &ag, &ab);
+  bn_apply_kernel<<<ag, ab, 0, st>>>((const __half*)x, ldx, scale_shift,
+                                     (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
+                                     relu);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -917,12 +969,14 @@ extern "C" int kfb_bn_backward(const void* dy, long long lddy, const void* mask,
   channel_reduce_kernel<1><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
       (const __half*)x, ldx, (const __half*)dy, lddy, (const __half*)mask, ldm, mean_rstd,
       nullptr, 0, rows, C, scratch);
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(
+  bn_bwd_finalize_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(
       scratch, nb, C, (float)(1.0 / (double)rows), gamma, mean_rstd, dgamma, dbeta,
       accumulate_param_grads, grad_scale, coef);
-  bn_bwd_apply_kernel<<<grid_for(rows * (C / 8)), 256, 0, st>>>(
-      (const __half*)dy, lddy, (const __half*)mask, ldm, (const __half*)x, ldx, mean_rstd, coef,
-      (__half*)dz, lddz, (__half*)dres, lddr, dres_accumulate, rows, C);
+  dim3 ag, ab;
+  apply_launch_shape(rows, C, &ag, &ab);
+  bn_bwd_apply_kernel<<<ag, ab, 0, st>>>((const __half*)dy, lddy, (const __half*)mask, ldm,
+                                         (const __half*)x, ldx, coef, (__half*)dz, lddz,
+                                         (__half*)dres, lddr, dres_accumulate, rows, C);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -939,8 +993,8 @@ extern "C" int kfb_bias_act_backward(const void* dy, long long lddy, const void*
       nullptr, 0, (const __half*)dy, lddy, (const __half*)mask, ldm, nullptr, (__half*)dz, lddz,
       rows, C, scratch);
   if (dbias != nullptr)
-    colsum_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, nb, C, dbias, accumulate,
-                                                           scale);
+    colsum_finalize_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(scratch, nb, C, dbias,
+                                                                           accumulate, scale);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
