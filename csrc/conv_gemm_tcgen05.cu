@@ -61,6 +61,7 @@ struct GemmParams {
   int relu;
   int out_fp32;
   int accumulate;          // out += result (gradient accumulation for fan-out tensors)
+  int stages;              // smem pipeline depth of this launch (1..kMaxStages)
   // optional row scatter (strided dgrad): row (n,i,j) -> (n, h0 + i*sh, w0 + j*sw) of H x W
   int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw, sc_h0, sc_w0;
   // DGRAD: filter tap visited at (r, s) of this launch's (sub-)filter
@@ -72,21 +73,26 @@ constexpr int kBlockK = 64;
 constexpr int kThreads = 192;
 constexpr int kTileABytes = kBlockM * kBlockK * 2;  // 16 KiB
 
+constexpr int kMaxStages = 4;
+
 template <int BN>
 struct TileCfg {
   static constexpr int kTileBBytes = BN * kBlockK * 2;
   static constexpr int kStageBytes = kTileABytes + kTileBBytes;
-  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 3 : 4);
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
   static constexpr int kTmemCols = BN < 32 ? 32 : BN;
+  // at least 2 A tiles' worth of bytes must exist: the epilogue stages through them
+  static constexpr int smem_bytes(int stages) {
+    const int pipe = stages * kStageBytes;
+    return (pipe < 2 * kTileABytes ? 2 * kTileABytes : pipe) + 1024 /*align*/ + 256 /*bars*/;
+  }
 };
 
 template <int BN, int MODE>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, 3)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                         const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   using Cfg = TileCfg<BN>;
-  constexpr int kStages = Cfg::kStages;
+  const int kStages = p.stages;
   constexpr uint32_t kAMajor = (MODE == GEMM_NT || MODE == WGRAD) ? kMajorMN : kMajorK;
   constexpr uint32_t kBMajor =
       (MODE == GEMM_NT || MODE == WGRAD || MODE == DGRAD || MODE == GEMM_NN) ? kMajorMN : kMajorK;
@@ -96,9 +102,11 @@ __global__ void __launch_bounds__(kThreads, 2)
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kTileABytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
-  uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* tmem_full_bar = empty_bar + kStages;
+  const int pipe_bytes = kStages * Cfg::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(
+      smem + (pipe_bytes < 2 * kTileABytes ? 2 * kTileABytes : pipe_bytes));
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* tmem_full_bar = empty_bar + kMaxStages;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
   const int warp = threadIdx.x >> 5;
@@ -329,54 +337,64 @@ __global__ void __launch_bounds__(kThreads, 2)
         }
       }
       __syncwarp();
-      // ---- staging -> global: lane handles 16-byte piece (lane % 8) of row it*4 + lane/8 ----
+      // ---- staging -> global: lane handles 16-byte piece (lane % 8) of row it*4 + lane/8.
+      //      All old-value loads of an accumulate are issued before the first store so eight
+      //      requests per lane are in flight. ----
       const int piece = lane & 7;
       const int epp = 16 / esize;  // elements per piece
       const int pcol = c0 + piece * epp;
+      const bool col_ok = pcol < n_limit;
+      const bool col_full = pcol + epp <= n_limit;
+      uint8_t* gps[8];
+      bool vec_ok[8], any_ok[8];
+      uint4 olds[8];
 #pragma unroll
       for (int it = 0; it < 8; ++it) {
         const int r = it * 4 + (lane >> 3);
         const long long ro = __shfl_sync(0xffffffffu, row_off, r);
-        if (ro < 0 || pcol >= n_limit) continue;
-        const uint8_t* sp = stage_buf + r * kStageRowBytes + piece * 16;
-        uint8_t* gp = reinterpret_cast<uint8_t*>(p.out) + (base + ro * p.ldc + pcol) * esize;
-        const bool vec_ok = (pcol + epp <= n_limit) && ((reinterpret_cast<uintptr_t>(gp) & 15) == 0);
-        if (p.out_fp32) {
-          float4 val = *reinterpret_cast<const float4*>(sp);
-          if (vec_ok) {
-            if (p.accumulate) {
-              const float4 old = *reinterpret_cast<const float4*>(gp);
-              val.x += old.x; val.y += old.y; val.z += old.z; val.w += old.w;
-            }
-            *reinterpret_cast<float4*>(gp) = val;
-          } else {
-            const float e[4] = {val.x, val.y, val.z, val.w};
-            float* go = reinterpret_cast<float*>(gp);
-            for (int j = 0; j < 4; ++j)
-              if (pcol + j < n_limit) go[j] = p.accumulate ? go[j] + e[j] : e[j];
-          }
-        } else {
-          uint4 val = *reinterpret_cast<const uint4*>(sp);
-          if (vec_ok) {
-            if (p.accumulate) {
-              const uint4 old = *reinterpret_cast<const uint4*>(gp);
+        gps[it] = reinterpret_cast<uint8_t*>(p.out) + (base + ro * p.ldc + pcol) * esize;
+        any_ok[it] = ro >= 0 && col_ok;
+        vec_ok[it] = any_ok[it] && col_full && ((reinterpret_cast<uintptr_t>(gps[it]) & 15) == 0);
+      }
+      if (p.accumulate) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+          if (vec_ok[it]) olds[it] = *reinterpret_cast<const uint4*>(gps[it]);
+      }
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        if (!any_ok[it]) continue;
+        const int r = it * 4 + (lane >> 3);
+        uint4 val = *reinterpret_cast<const uint4*>(stage_buf + r * kStageRowBytes + piece * 16);
+        if (vec_ok[it]) {
+          if (p.accumulate) {
+            if (p.out_fp32) {
+              float4* v4 = reinterpret_cast<float4*>(&val);
+              const float4* o4 = reinterpret_cast<const float4*>(&olds[it]);
+              v4->x += o4->x; v4->y += o4->y; v4->z += o4->z; v4->w += o4->w;
+            } else {
               __half2* a2 = reinterpret_cast<__half2*>(&val);
-              const __half2* o2 = reinterpret_cast<const __half2*>(&old);
+              const __half2* o2 = reinterpret_cast<const __half2*>(&olds[it]);
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const float2 x = __half22float2(a2[j]), y = __half22float2(o2[j]);
                 a2[j] = __floats2half2_rn(x.x + y.x, x.y + y.y);
               }
             }
-            *reinterpret_cast<uint4*>(gp) = val;
-          } else {
-            const __half* e = reinterpret_cast<const __half*>(&val);
-            __half* go = reinterpret_cast<__half*>(gp);
-            for (int j = 0; j < 8; ++j)
-              if (pcol + j < n_limit)
-                go[j] = p.accumulate ? __float2half_rn(__half2float(go[j]) + __half2float(e[j]))
-                                     : e[j];
           }
+          *reinterpret_cast<uint4*>(gps[it]) = val;
+        } else if (p.out_fp32) {
+          const float* e = reinterpret_cast<const float*>(&val);
+          float* go = reinterpret_cast<float*>(gps[it]);
+          for (int j = 0; j < 4; ++j)
+            if (pcol + j < n_limit) go[j] = p.accumulate ? go[j] + e[j] : e[j];
+        } else {
+          const __half* e = reinterpret_cast<const __half*>(&val);
+          __half* go = reinterpret_cast<__half*>(gps[it]);
+          for (int j = 0; j < 8; ++j)
+            if (pcol + j < n_limit)
+              go[j] = p.accumulate ? __float2half_rn(__half2float(go[j]) + __half2float(e[j]))
+                                   : e[j];
         }
       }
       __syncwarp();
@@ -514,10 +532,15 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gemm
   if (dev < 16 && !attr_set[dev]) {
     KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        Cfg::kSmemBytes));
+                                        Cfg::smem_bytes(kMaxStages)));
+    KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE>,
+                                        cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        cudaSharedmemCarveoutMaxShared));
     attr_set[dev] = true;
   }
-  gemm_tcgen05_kernel<BN, MODE><<<grid, kThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
+  KFB_REQUIRE(p.stages >= 1 && p.stages <= kMaxStages, "bad pipeline depth %d", p.stages);
+  gemm_tcgen05_kernel<BN, MODE><<<grid, kThreads, Cfg::smem_bytes(p.stages), stream>>>(tmA, tmB,
+                                                                                        p);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -534,7 +557,21 @@ static int launch_mode(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, c
   return 2;
 }
 
+// Tile width and pipeline depth. Two goals: (a) at least two CTAs per SM so the epilogue of one
+// tile overlaps the main loop of another (TMEM: 512 columns per SM, shared memory: ~227 KB);
+// (b) for short-K (memory-bound) problems, narrower tiles and a shallow pipeline so three or
+// four CTAs fit and enough stores are in flight.
 static int pick_bn(int n) { return n <= 64 ? 64 : (n <= 128 ? 128 : 256); }
+static int pick_bn_for(int n, int num_kb) {
+  int bn = pick_bn(n);
+  if (num_kb <= 2 && bn == 256) bn = 128;
+  return bn;
+}
+static int pick_stages(int bn, int kb_per_cta) {
+  int st = bn == 256 ? 2 : (bn == 128 ? 3 : 4);  // <= ~96 KB per CTA
+  if (kb_per_cta < st) st = kb_per_cta;
+  return st < 1 ? 1 : st;
+}
 
 static int g_sm_count = 0;
 static int sm_count() {
@@ -564,7 +601,7 @@ extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, 
   KFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tn: bad shape %d %d %d", M, N, K);
   KFB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tn: lda/ldb must be multiples of 8 elements");
   if (load_driver_fns()) return 1;
-  const int bn = pick_bn(N);
+  const int bn = pick_bn_for(N, (K + 63) / 64);
   CUtensorMap tmA, tmB;
   uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * 2};
   uint32_t ba[2] = {64, 128};
@@ -579,6 +616,7 @@ extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, 
   p.N = N;
   p.num_kb = (K + 63) / 64;
   p.kb_per_split = p.num_kb;
+  p.stages = pick_stages(bn, p.num_kb);
   p.out = C;
   p.ldc = ldc;
   p.bias = bias;
@@ -595,7 +633,7 @@ extern "C" int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, 
   KFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_nn: bad shape %d %d %d", M, N, K);
   KFB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_nn: lda/ldb must be multiples of 8 elements");
   if (load_driver_fns()) return 1;
-  const int bn = pick_bn(N);
+  const int bn = pick_bn_for(N, (K + 63) / 64);
   CUtensorMap tmA, tmB;
   uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, sa[1] = {(uint64_t)lda * 2};
   uint32_t ba[2] = {64, 128};
@@ -610,6 +648,7 @@ extern "C" int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, 
   p.N = N;
   p.num_kb = (K + 63) / 64;
   p.kb_per_split = p.num_kb;
+  p.stages = pick_stages(bn, p.num_kb);
   p.out = C;
   p.ldc = ldc;
   p.out_fp32 = out_fp32;
@@ -649,6 +688,7 @@ extern "C" int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N,
               workspace_bytes, slice);
   p.kb_per_split = (p.num_kb + splits - 1) / splits;
   splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.stages = pick_stages(bn, p.kb_per_split);
   p.out = workspace;
   p.ldc = N;
   p.split_stride = slice;
@@ -682,7 +722,7 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   if (check_conv(d, "conv_fprop")) return 2;
   if (load_driver_fns()) return 1;
   const int M = d->n * d->p * d->q;
-  const int bn = pick_bn(d->k);
+  const int bn = pick_bn_for(d->k, d->r * d->s * ((d->c + 63) / 64));
   CUtensorMap tmA, tmB;
   if (encode_im2col(&tmA, x, d->n, d->h, d->w, d->c, -d->pad_w_lo, -d->pad_h_lo,
                     d->pad_w_hi - (d->s - 1), d->pad_h_hi - (d->r - 1), 64, 128, d->stride_w,
@@ -703,6 +743,7 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   p.Ck = d->c;
   p.num_kb = d->r * d->s * p.CB;
   p.kb_per_split = p.num_kb;
+  p.stages = pick_stages(bn, p.num_kb);
   p.P = d->p;
   p.Q = d->q;
   p.lower_h = -d->pad_h_lo;
@@ -747,7 +788,6 @@ extern "C" int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void
                               int accumulate, void* stream) {
   if (check_conv(d, "conv_dgrad")) return 2;
   if (load_driver_fns()) return 1;
-  const int bn = pick_bn(d->c);
   CUtensorMap tmB;
   uint64_t db[3] = {(uint64_t)d->c, (uint64_t)d->r * d->s, (uint64_t)d->k};
   uint64_t sb[2] = {(uint64_t)d->c * 2, (uint64_t)d->r * d->s * d->c * 2};
@@ -783,6 +823,8 @@ extern "C" int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void
       p.Ck = d->k;
       p.num_kb = nR * nS * p.CB;
       p.kb_per_split = p.num_kb;
+      const int bn = pick_bn_for(d->c, p.num_kb);
+      p.stages = pick_stages(bn, p.num_kb);
       p.P = Hp;
       p.Q = Wp;
       p.lower_h = lower_h;
@@ -867,6 +909,7 @@ extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void*
               workspace_bytes, slice);
   p.kb_per_split = (p.num_kb + splits - 1) / splits;
   splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.stages = pick_stages(bn, p.kb_per_split);
   p.out = workspace;
   p.ldc = (long long)d->r * d->s * d->c;
   p.split_stride = slice;
