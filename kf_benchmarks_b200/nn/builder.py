@@ -312,6 +312,9 @@ class NetBuilder:
             input_layer = self.top_layer
         if in_size is None:
             in_size = self.top_size
+        # As in the reference, the counter that is bumped is the one of the *suffixed* name, so
+        # every module of a kind ends up as "<kind>0" (conv counters keep the variables unique).
+        # Reproduced on purpose: it defines the variable names of reference checkpoints.
         name += str(self.counts[name])
         self.counts[name] += 1
         with self.scope(name):

@@ -1,0 +1,63 @@
+"""all_reduce_spec grammar and bucket planning (T/allreduce.py:35-104,420-454;
+tests T/allreduce_test.py:32-300)."""
+import pytest
+
+from kf_benchmarks_b200.parallel import allreduce_spec as A
+from kf_benchmarks_b200.parallel.strategy import plan_buckets, reduction_semantics
+from kf_benchmarks_b200 import params as P
+
+
+def test_parse_general_int():
+    assert A.parse_general_int("64") == 64
+    assert A.parse_general_int("4k") == 4096 and A.parse_general_int("4K") == 4096
+    assert A.parse_general_int("2M") == 2 << 20 and A.parse_general_int("1G") == 1 << 30
+    with pytest.raises(ValueError):
+        A.parse_general_int("4q")
+
+
+def test_parse_all_reduce_spec():
+    assert A.parse_all_reduce_spec("nccl") == [A.AllReduceSpecTuple("nccl", 1, -1)]
+    assert A.parse_all_reduce_spec("xring#2") == [A.AllReduceSpecTuple("xring", 2, -1)]
+    spec = A.parse_all_reduce_spec("pscpu:32k:xring")
+    assert spec == [A.AllReduceSpecTuple("pscpu", 1, 32768), A.AllReduceSpecTuple("xring", 1, -1)]
+    spec = A.parse_all_reduce_spec("psgpu#4:1M:nccl/xring#2:64M:collective")
+    assert [s.alg for s in spec] == ["psgpu", "nccl/xring", "collective"]
+    assert [s.limit for s in spec] == [1 << 20, 64 << 20, -1]
+    for bad in ("nccl:abc:xring", "nccl:64k", "foo", "nccl:2M:xring:1M:pscpu"):
+        with pytest.raises(ValueError):
+            A.parse_all_reduce_spec(bad)
+
+
+def test_extract_ranges():
+    assert A.extract_ranges([]) == ([], [])
+    assert A.extract_ranges([1, 3, 4, 6, 7, 8, 9]) == ([[3, 4], [6, 9]], [1])
+    r, s = A.extract_ranges(list(range(10)), range_size_limit=3)
+    assert r == [[0, 4], [5, 9]] and s == []
+    groups, singles = A.small_tensor_groups([4, 4, 4000, 4, 4, 4, 9000, 4], 64, 10)
+    assert groups == [[0, 1], [3, 4, 5]] and singles == [7]
+
+
+def test_plan_buckets():
+    b = plan_buckets(1000, 256)
+    assert b[0] == (0, 256) and b[-1][1] == 1000 and all(lo % 128 == 0 for lo, _ in b)
+    b = plan_buckets(10_000, 999999, num_buckets=4)
+    assert len(b) == 4 and b[-1][1] == 10_000
+    assert plan_buckets(0, 128) == []
+    cover = []
+    for lo, hi in plan_buckets(25_600_000, 2 << 20):
+        cover.append(hi - lo)
+    assert sum(cover) == 25_600_000
+
+
+@pytest.mark.parametrize("vu,opt,expect", [
+    ("independent", "sync_sgd", ("none", False)),
+    ("replicated", "sync_sgd", ("allreduce", False)),     # sums, T/batch_allreduce.py:24-29
+    ("horovod", "sync_sgd", ("allreduce", False)),        # hvd.allreduce(average=False)
+    ("parameter_server", "sync_sgd", ("allreduce", True)),
+    ("kungfu", "sync_sgd", ("allreduce", True)),
+    ("kungfu", "sma", ("sma", True)),
+    ("kungfu", "async_sgd", ("pair", False)),
+    ("kungfu", "ada_sgd", ("ada", True)),
+])
+def test_reduction_semantics(vu, opt, expect):
+    assert reduction_semantics(P.make_params(variable_update=vu, kungfu_option=opt)) == expect

@@ -1,0 +1,96 @@
+"""Flag surface, parsing and validation (reference: T/flags.py, T/benchmark_cnn.py:114-636,
+959-1034,1268-1352; tests T/benchmark_cnn_test.py:1179-1234)."""
+import pytest
+
+from kf_benchmarks_b200 import benchmark, flags, params as P
+
+
+def test_all_reference_flags_present_with_defaults():
+    assert P.NUM_REFERENCE_FLAGS == 129
+    d = P.make_params()
+    assert d.model == "trivial" and d.num_gpus == 1 and d.display_every == 10
+    assert d.variable_update == "parameter_server" and d.kungfu_option == "sync_sgd"
+    assert d.optimizer == "sgd" and d.momentum == 0.9 and d.weight_decay == 4e-5
+    assert d.rmsprop_epsilon == 1.0 and d.adam_epsilon == 1e-8
+    assert d.data_format == "NCHW" and d.device == "gpu" and d.use_fp16 is False
+    assert d.fp16_inc_loss_scale_every_n == 1000 and d.max_ckpts_to_keep == 5
+    assert d.eval_dir == "/tmp/tf_cnn_benchmarks/eval" and d.tf_random_seed == 1234
+    assert d.compact_gradient_transfer is True and d.variable_consistency == "strong"
+    assert d.trt_max_workspace_size_bytes == 4 << 30
+
+
+def test_parse_styles_and_aliases():
+    p = P.make_params_from_flags(["--model=resnet50", "--batch_size", "256", "--use_fp16",
+                                  "--nodistortions", "--kungfu_strategy=sma",
+                                  "--variable_update=kungfu", "--gradient_clip=1.5",
+                                  "--eval_during_training_at_specified_steps=3,7"])
+    assert (p.model, p.batch_size, p.use_fp16, p.distortions) == ("resnet50", 256, True, False)
+    assert p.kungfu_option == "sma" and p.gradient_clip == 1.5
+    assert p.eval_during_training_at_specified_steps == ["3", "7"]
+    p = P.make_params_from_flags(["--use_fp16=false", "--xla=true"])
+    assert p.use_fp16 is False and p.xla is True
+
+
+def test_positional_arguments_are_rejected():
+    with pytest.raises(flags.FlagError):
+        P.make_params_from_flags(["--distortions", "False"])
+    with pytest.raises(flags.FlagError):
+        P.make_params_from_flags(["--no_such_flag=1"])
+
+
+def test_bounds_and_enums():
+    with pytest.raises(ValueError):
+        P.make_params(gradient_repacking=-1)
+    with pytest.raises(ValueError):
+        P.make_params(gpu_memory_frac_for_testing=1.5)
+    with pytest.raises(ValueError):
+        P.make_params(optimizer="lamb")
+    with pytest.raises(ValueError):
+        P.make_params(variable_update="magic")
+    with pytest.raises(ValueError):
+        P.make_params(not_a_param=1)
+    assert P.make_params(kungfu_option="ada_sgd").kungfu_option == "ada_sgd"
+
+
+def test_remove_param_fields():
+    p = P.remove_param_fields(P.make_params(), ["model", "xla"])
+    assert not hasattr(p, "model") and hasattr(p, "batch_size")
+
+
+@pytest.mark.parametrize("kw", [
+    dict(device="cpu", data_format="NCHW"),
+    dict(num_epochs_per_decay=2.0),
+    dict(minimum_learning_rate=0.1),
+    dict(variable_update="horovod", num_gpus=2),
+    dict(variable_update="kungfu", num_gpus=2),
+    dict(use_fp16=True, fp16_vars=True, gradient_repacking=2),
+    dict(use_fp16=True, fp16_enable_auto_loss_scale=True, variable_update="kungfu"),
+    dict(hierarchical_copy=True, num_gpus=1),
+    dict(save_model_secs=10, save_model_steps=5),
+    dict(eval_during_training_every_n_steps=1, eval_during_training_every_n_epochs=1.0),
+    dict(eval_during_training_every_n_steps=1, forward_only=True),
+    dict(stop_at_top_1_accuracy=0.5),
+    dict(staged_vars=True, variable_update="replicated"),
+    dict(trt_mode="FP16"),
+    dict(debugger="nonsense"),
+    dict(all_reduce_spec="bogus_alg"),
+])
+def test_invalid_combinations_raise(kw):
+    base = dict(device="cpu", data_format="NHWC")
+    base.update(kw)
+    with pytest.raises(ValueError):
+        benchmark.BenchmarkCNN(P.make_params(**base))
+
+
+def test_unsupported_features_fail_loudly_in_setup():
+    for kw in (dict(xla=True), dict(job_name="worker")):
+        with pytest.raises(ValueError):
+            benchmark.setup(P.make_params(**kw))
+
+
+def test_warmup_default_and_batch_sizes():
+    b = benchmark.BenchmarkCNN(P.make_params(device="cpu", data_format="NHWC", model="resnet50"))
+    assert b.num_warmup_batches == 10 and b.batch_size_per_device == 64 and b.num_batches == 100
+    b = benchmark.BenchmarkCNN(P.make_params(device="cpu", data_format="NHWC", autotune_threshold=3,
+                                             batch_size=8, num_gpus=1))
+    assert b.num_warmup_batches == 45 and b.batch_size == 8

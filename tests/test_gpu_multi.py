@@ -1,0 +1,50 @@
+"""Multi-GPU: fused P2P kernels and the overlapped all-reduce training step. Needs >= 2 GPUs
+(skipped on a single-GPU box); ranks are real processes, one per GPU."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+def _launch(n, args, timeout=600):
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    cmd = [sys.executable, "-m", "kf_benchmarks_b200.parallel.launcher", "-np", str(n), "--"] + args
+    return subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=timeout)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+def test_p2p_kernels_match_host_simulation():
+    n = min(_ngpu(), 8)
+    res = _launch(n, [os.path.join(ROOT, "tools", "p2p_check.py")])
+    assert res.returncode == 0 and "P2P_CHECK ALL PASS" in res.stdout, res.stdout[-4000:]
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+@pytest.mark.parametrize("mode", [
+    ["--variable_update=replicated", "--num_gpus=2"],
+    ["--variable_update=kungfu", "--kungfu_option=sync_sgd"],
+    ["--variable_update=kungfu", "--kungfu_option=sma"],
+    ["--variable_update=kungfu", "--kungfu_option=async_sgd"],
+])
+def test_two_gpu_training_modes_run(mode):
+    args = ["-m", "kf_benchmarks_b200.cli", "--model=resnet20", "--data_name=cifar10",
+            "--batch_size=64", "--use_fp16", "--optimizer=momentum", "--num_batches=12",
+            "--num_warmup_batches=2", "--display_every=4", "--init_learning_rate=0.05"] + mode
+    res = _launch(2, args)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    assert "total images/sec:" in res.stdout
+    losses = [float(l.split("\t")[-1]) for l in res.stdout.splitlines()
+              if "images/sec:" in l and l[0].isdigit()]
+    assert losses and all(x == x and x < 20 for x in losses), res.stdout[-2000:]

@@ -1,0 +1,200 @@
+"""End-to-end update semantics on CPU, checked against an independent re-simulation.
+
+Follows the reference's strongest test idea (VariableUpdateTest, T/benchmark_cnn_test.py:
+1236-1365 with the oracle of T/test_util.py:365-443): run the real driver, then recompute
+every step by hand - per-rank gradients from the reference executor, the mode's reduction
+rule (replicated sums, parameter_server / KungFu S-SGD average, SMA averages models,
+PairAveraging blends with the peer), the TF optimizer formulas - and compare the variables.
+Multi-rank cases run as real processes over gloo (ranks sharing this box), like the
+reference's spawn-N-local-processes harness (T/benchmark_cnn_distributed_test.py:161-256).
+"""
+import json
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from kf_benchmarks_b200 import benchmark, datasets, params as P
+from kf_benchmarks_b200.data import inputs
+from kf_benchmarks_b200.models import model_config
+from kf_benchmarks_b200.nn.executor_ref import RefExecutor
+from kf_benchmarks_b200.nn.params import ParameterStore
+from kf_benchmarks_b200.ops import optim_ref
+from kf_benchmarks_b200.parallel.strategy import UpdateEngine
+from kf_benchmarks_b200.parallel.comm import SingleComm
+from kf_benchmarks_b200.utils import log_util
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BASE = dict(model="trivial", data_name="cifar10", device="cpu", data_format="NHWC", batch_size=4,
+            num_batches=3, num_warmup_batches=0, display_every=1, weight_decay=1e-3,
+            init_learning_rate=0.05)
+
+
+class _Sim:
+    """Independent simulation of `world` replicas."""
+
+    def __init__(self, kw, world):
+        self.kw, self.world = kw, world
+        self.p = P.make_params(**kw)
+        ds = datasets.create_dataset(None, "cifar10")
+        self.model = model_config.get_model_config(self.p.model, ds, self.p)
+        self.model.set_batch_size(self.p.batch_size)
+        self.g = self.model.build_graph(ds.num_classes, batch_size=self.p.batch_size)
+        per_rank_seed = self.p.variable_update in ("kungfu", "horovod")
+        self.stores, self.srcs, self.slots = [], [], []
+        for r in range(world):
+            st = ParameterStore(self.g, "cpu", fp16_shadow=False)
+            st.initialize(self.p.tf_random_seed + (r if per_rank_seed else 0))
+            self.stores.append(st)
+            seed = self.p.tf_random_seed + (r if per_rank_seed else 0)
+            self.srcs.append(inputs.SyntheticHostSource(
+                self.p.batch_size, 32, 3, ds.num_classes, "cpu", seed * 1000003 + r,
+                dtype=torch.float32))
+            self.slots.append((torch.zeros_like(st.w32), torch.zeros_like(st.w32)))
+        # every mode starts from rank 0's variables (broadcast at start)
+        for st in self.stores[1:]:
+            st.w32.copy_(self.stores[0].w32)
+            st.state.copy_(self.stores[0].state)
+        self.engine = UpdateEngine(self.p, self.stores[0], SingleComm(), self.model)
+        self.nclass = ds.num_classes
+
+    def grads(self, r):
+        ex = RefExecutor(self.g, self.stores[r], self.nclass)
+        ex.set_inputs(*self.srcs[r].next_batch())
+        ex.forward(True)
+        ex.loss_backward(1.0)
+        return self.stores[r].grad.clone()
+
+    def step(self, k):
+        p, n = self.p, self.world
+        h = self.engine._hyper(p.init_learning_rate)
+        h.adam_t = float(k + 1)
+        h.grad_scale = 1.0
+        gs = [self.grads(r) for r in range(n)]
+        vu, opt = p.variable_update, p.kungfu_option
+        if vu == "independent" or n == 1:
+            red = gs
+        elif vu in ("replicated", "horovod"):
+            red = [sum(gs)] * n
+        elif vu == "parameter_server" or (vu == "kungfu" and opt == "sync_sgd"):
+            red = [sum(gs) / n] * n
+        else:
+            red = gs
+        if vu == "kungfu" and opt == "sma" and n > 1:
+            avg = sum(st.w32 for st in self.stores) / n
+            for st in self.stores:
+                st.w32.mul_(1 - p.sma_alpha).add_(avg, alpha=p.sma_alpha)
+        if vu == "kungfu" and opt == "async_sgd" and n == 2:
+            w0, w1 = self.stores[0].w32.clone(), self.stores[1].w32.clone()
+            self.stores[0].w32.copy_(0.5 * (w0 + w1))
+            self.stores[1].w32.copy_(0.5 * (w0 + w1))
+        for r in range(n):
+            m, v = self.slots[r]
+            optim_ref.apply_update(h, self.stores[r].w32, red[r], m, v)
+
+
+def _run_single(kw):
+    lines = []
+    old = log_util.log_fn
+    log_util.log_fn = lines.append
+    try:
+        bench = benchmark.BenchmarkCNN(benchmark.setup(P.make_params(**kw)))
+        bench.print_info()
+        stats = bench.run()
+    finally:
+        log_util.log_fn = old
+    return bench, stats, lines
+
+
+@pytest.mark.parametrize("extra", [
+    dict(optimizer="sgd"), dict(optimizer="momentum"), dict(optimizer="rmsprop"),
+    dict(optimizer="adam"), dict(optimizer="momentum", gradient_clip=1e-3),
+    dict(optimizer="sgd", variable_update="replicated"),
+    dict(optimizer="sgd", variable_update="independent"),
+])
+def test_single_process_matches_simulation(extra):
+    kw = dict(BASE)
+    kw.update(extra)
+    bench, stats, lines = _run_single(kw)
+    sim = _Sim(kw, 1)
+    for k in range(kw["num_batches"]):
+        sim.step(k)
+    assert torch.allclose(bench.store.w32, sim.stores[0].w32, rtol=1e-5, atol=1e-6)
+    # log format: header, 3 step lines, totals
+    steps = [l for l in lines if re.match(r"^\d+\timages/sec: ", l)]
+    assert len(steps) == 3 and any(l.startswith("total images/sec: ") for l in lines)
+    assert "Step\tImg/sec\ttotal_loss" in lines and "Model:       trivial" in lines
+    assert stats["num_steps"] == 3 and stats["images_per_sec"] > 0
+
+
+def _spawn(kw, world, tmp_path, launcher_np=None):
+    out = str(tmp_path)
+    cmd = [sys.executable, "-m", "kf_benchmarks_b200.parallel.launcher", "-np", str(world), "--",
+           os.path.join(ROOT, "tests", "helpers", "rank_worker.py"), json.dumps(kw), out]
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2")
+    env.pop("RANK", None)
+    env.pop("WORLD_SIZE", None)
+    res = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    return [np.load(os.path.join(out, "rank%d.npz" % r)) for r in range(world)]
+
+
+@pytest.mark.parametrize("extra", [
+    dict(variable_update="replicated", num_gpus=2, optimizer="momentum"),
+    dict(variable_update="parameter_server", num_gpus=2, optimizer="sgd"),
+    dict(variable_update="independent", num_gpus=2, optimizer="sgd"),
+    dict(variable_update="kungfu", kungfu_option="sync_sgd", optimizer="momentum"),
+    dict(variable_update="kungfu", kungfu_option="sma", optimizer="sgd"),
+    dict(variable_update="kungfu", kungfu_option="async_sgd", optimizer="sgd"),
+    dict(variable_update="horovod", optimizer="sgd"),
+])
+def test_two_ranks_match_simulation(extra, tmp_path):
+    kw = dict(BASE)
+    kw.update(extra)
+    results = _spawn(kw, 2, tmp_path)
+    sim = _Sim(kw, 2)
+    for k in range(kw["num_batches"]):
+        sim.step(k)
+    for r in range(2):
+        assert np.allclose(results[r]["w"], sim.stores[r].w32.numpy(), rtol=2e-5, atol=2e-6), \
+            "rank %d diverges from the simulation" % r
+    synced = extra["variable_update"] in ("replicated", "parameter_server", "horovod") or \
+        extra.get("kungfu_option") == "sync_sgd"
+    same = np.array_equal(results[0]["w"], results[1]["w"])
+    assert same == synced      # synchronous modes keep replicas bit-identical, others do not
+
+
+def test_resume_from_checkpoint(tmp_path):
+    kw = dict(BASE, optimizer="momentum", train_dir=str(tmp_path / "ckpt"), num_batches=2)
+    bench, _, lines = _run_single(kw)
+    assert os.path.exists(os.path.join(kw["train_dir"], "model.ckpt-2.npz"))
+    bench2, _, lines2 = _run_single(kw)
+    assert any("Restored checkpoint" in l for l in lines2)
+    assert bench2.global_step == 4
+    assert os.path.exists(os.path.join(kw["train_dir"], "model.ckpt-4.npz"))
+
+
+def test_eval_and_eval_during_training(tmp_path):
+    kw = dict(BASE, train_dir=str(tmp_path / "ckpt"), num_batches=2,
+              eval_during_training_every_n_steps=1, num_eval_batches=2)
+    _, _, lines = _run_single(kw)
+    acc = [l for l in lines if l.startswith("Accuracy @ 1 = ")]
+    assert len(acc) == 2 and re.match(
+        r"^Accuracy @ 1 = \d\.\d{4} Accuracy @ 5 = \d\.\d{4} \[8 examples\]$", acc[0])
+    kw = dict(BASE, train_dir=str(tmp_path / "ckpt"), eval=True, num_batches=3)
+    kw.pop("init_learning_rate")
+    _, res, lines = _run_single(kw)
+    assert res["num_examples"] == 12 and 0.0 <= res["top_1_accuracy"] <= res["top_5_accuracy"]
+
+
+def test_forward_only_and_loss_reporting():
+    _, stats, lines = _run_single(dict(BASE, forward_only=True))
+    assert any(l.endswith("top_1_accuracy\ttop_5_accuracy") for l in lines)
+    b1, s1, _ = _run_single(dict(BASE, loss_type_to_report="base_loss", num_batches=1))
+    b2, s2, _ = _run_single(dict(BASE, loss_type_to_report="total_loss", num_batches=1))
+    l2 = 0.5 * float((b2.store.w32.double() ** 2).sum()) * BASE["weight_decay"]
+    assert s2["last_average_loss"] == pytest.approx(s1["last_average_loss"] + l2, rel=1e-4)
