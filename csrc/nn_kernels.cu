@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(kRedThreads)
                           const __half* __restrict__ dy, long long lddy,
                           const __half* __restrict__ mask, long long ldm,
                           const float* __restrict__ mean_rstd,  // [2][C] (MODE 1)
+                          const float* __restrict__ relu_affine,  // [2][C] or null (MODE 1)
                           __half* __restrict__ dz, long long lddz, long long rows, int C,
                           float* __restrict__ partial) {
   extern __shared__ float red[];  // [kRedThreads][16] worst case handled by looping
@@ -67,17 +68,44 @@ __global__ void __launch_bounds__(kRedThreads)
     float a[8], b[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) a[i] = b[i] = 0.f;
-    float mu[8], rs[8];
-    if (MODE == 1 && cv < vpr && tr < row_lanes) {
+    // MODE 1 per-channel constants. The ReLU mask of y = relu(x*sc + sh) is recomputed from x
+    // as (x > thr) xor (sc < 0) with thr = -sh/sc, so y does not have to be re-read.
+    float mu[8], thr[8];
+    unsigned neg_bits = 0;
+    const bool recompute_mask = MODE == 1 && relu_affine != nullptr;
+    const bool active = cv < vpr && tr < row_lanes;
+    if (MODE == 1 && active) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         mu[i] = mean_rstd[cv * 8 + i];
-        rs[i] = mean_rstd[C + cv * 8 + i];
+        thr[i] = 0.f;
+        if (recompute_mask) {
+          const float sc = relu_affine[cv * 8 + i], sh = relu_affine[C + cv * 8 + i];
+          if (sc > 0.f) {
+            thr[i] = -sh / sc;
+          } else if (sc < 0.f) {
+            thr[i] = -sh / sc;
+            neg_bits |= 1u << i;
+          } else {
+            thr[i] = sh > 0.f ? -INFINITY : INFINITY;  // constant output
+          }
+        }
       }
     }
-    if (cv < vpr && tr < row_lanes) {
-      for (long long r = r_begin + tr; r < r_end; r += row_lanes) {
-        if (MODE == 0) {
+    if (active) {
+      if (MODE == 0) {
+        long long r = r_begin + tr;
+        for (; r + row_lanes < r_end; r += 2 * row_lanes) {
+          float v0[8], v1[8];
+          load8(x + r * ldx + cv * 8, v0);
+          load8(x + (r + row_lanes) * ldx + cv * 8, v1);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            a[i] += v0[i] + v1[i];
+            b[i] += v0[i] * v0[i] + v1[i] * v1[i];
+          }
+        }
+        for (; r < r_end; r += row_lanes) {
           float v[8];
           load8(x + r * ldx + cv * 8, v);
 #pragma unroll
@@ -85,28 +113,56 @@ __global__ void __launch_bounds__(kRedThreads)
             a[i] += v[i];
             b[i] += v[i] * v[i];
           }
-        } else {
-          float g[8];
-          load8(dy + r * lddy + cv * 8, g);
-          if (mask != nullptr) {
-            float m[8];
-            load8(mask + r * ldm + cv * 8, m);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) g[i] = m[i] > 0.f ? g[i] : 0.f;
-          }
+        }
+      } else {
+        for (long long r = r_begin + tr; r < r_end; r += 2 * row_lanes) {
+          const bool two = r + row_lanes < r_end;
+          const long long r1 = two ? r + row_lanes : r;
+          float g0[8], g1[8], v0[8], v1[8], m0[8], m1[8];
+          load8(dy + r * lddy + cv * 8, g0);
+          load8(dy + r1 * lddy + cv * 8, g1);
           if (MODE == 1) {
-            float v[8];
-            load8(x + r * ldx + cv * 8, v);
+            load8(x + r * ldx + cv * 8, v0);
+            load8(x + r1 * ldx + cv * 8, v1);
+          }
+          if (mask != nullptr) {
+            load8(mask + r * ldm + cv * 8, m0);
+            load8(mask + r1 * ldm + cv * 8, m1);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-              a[i] += g[i];
-              b[i] += g[i] * (v[i] - mu[i]) * rs[i];
+              g0[i] = m0[i] > 0.f ? g0[i] : 0.f;
+              g1[i] = m1[i] > 0.f ? g1[i] : 0.f;
+            }
+          } else if (recompute_mask) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const bool ng = (neg_bits >> i) & 1u;
+              g0[i] = ((v0[i] > thr[i]) != ng) ? g0[i] : 0.f;
+              g1[i] = ((v1[i] > thr[i]) != ng) ? g1[i] : 0.f;
+            }
+          }
+          if (!two) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g1[i] = 0.f;
+          }
+          if (MODE == 1) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              a[i] += g0[i] + g1[i];
+              b[i] += g0[i] * (v0[i] - mu[i]) + g1[i] * (v1[i] - mu[i]);
             }
           } else {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] += g[i];
-            if (dz != nullptr) store8(dz + r * lddz + cv * 8, g);
+            for (int i = 0; i < 8; ++i) a[i] += g0[i] + g1[i];
+            if (dz != nullptr) {
+              store8(dz + r * lddz + cv * 8, g0);
+              if (two) store8(dz + r1 * lddz + cv * 8, g1);
+            }
           }
+        }
+        if (MODE == 1) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) b[i] *= mean_rstd[C + cv * 8 + i];
         }
       }
     }
@@ -285,17 +341,26 @@ __global__ void __launch_bounds__(256)
     bn_bwd_apply_kernel(const __half* __restrict__ dy, long long lddy,
                         const __half* __restrict__ mask, long long ldm,
                         const __half* __restrict__ x, long long ldx,
-                        const float* __restrict__ coef, __half* __restrict__ dz, long long lddz,
-                        __half* __restrict__ dres, long long lddr, int dres_accumulate,
-                        long long rows, int C) {
+                        const float* __restrict__ coef, const float* __restrict__ relu_affine,
+                        __half* __restrict__ dz, long long lddz, __half* __restrict__ dres,
+                        long long lddr, int dres_accumulate, long long rows, int C) {
   const int vpr = C >> 3;
   // blockDim = (vx, vy): vx channel vectors x vy rows; channel coefficients live in registers
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   if (cv >= vpr) return;
-  float A[8], B[8], D[8];
+  float A[8], B[8], D[8], thr[8];
+  unsigned neg_bits = 0;
   load8f(coef + cv * 8, A);
   load8f(coef + C + cv * 8, B);
   load8f(coef + 2 * C + cv * 8, D);
+  if (relu_affine != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float sc = relu_affine[cv * 8 + k], sh = relu_affine[C + cv * 8 + k];
+      thr[k] = sc != 0.f ? -sh / sc : (sh > 0.f ? -INFINITY : INFINITY);
+      if (sc < 0.f) neg_bits |= 1u << k;
+    }
+  }
   for (long long r = static_cast<long long>(blockIdx.y) * blockDim.y + threadIdx.y; r < rows;
        r += static_cast<long long>(gridDim.y) * blockDim.y) {
     float g[8], v[8];
@@ -306,6 +371,10 @@ __global__ void __launch_bounds__(256)
       load8(mask + r * ldm + cv * 8, m);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] = m[k] > 0.f ? g[k] : 0.f;
+    } else if (relu_affine != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        g[k] = ((v[k] > thr[k]) != (((neg_bits >> k) & 1u) != 0)) ? g[k] : 0.f;
     }
     float out[8];
 #pragma unroll
@@ -601,37 +670,46 @@ __global__ void __launch_bounds__(256)
 
 // Explicit im2col for convolutions whose input channel count is not a multiple of 8
 // (image stems, C = 1 or 3): col[row][(r*S+s)*C + c], zero padded to kpad columns.
+// TC/TKH/TKW > 0 make the filter geometry compile-time (cheap index arithmetic); 0 = runtime.
+template <int TC, int TKH, int TKW>
 __global__ void __launch_bounds__(256)
     im2col_small_c_kernel(const __half* __restrict__ x, __half* __restrict__ col, int n, int h,
-                          int w, int c, int p, int q, int kh, int kw, int sh, int sw, int pad_h,
-                          int pad_w, int kpad) {
+                          int w, int c_rt, int p, int q, int kh_rt, int kw_rt, int sh, int sw,
+                          int pad_h, int pad_w, int kpad_rt) {
+  const int c = TC > 0 ? TC : c_rt;
+  const int kh = TKH > 0 ? TKH : kh_rt;
+  const int kw = TKW > 0 ? TKW : kw_rt;
+  const int ktot = kh * kw * c;
+  const int kpad = TC > 0 ? ((TC * TKH * TKW + 7) / 8 * 8) : kpad_rt;
   const int vpr = kpad >> 3;
   const long long total = static_cast<long long>(n) * p * q * vpr;
-  const int ktot = kh * kw * c;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int kv = static_cast<int>(i % vpr);
-    long long t = i / vpr;
-    const int qq = static_cast<int>(t % q);
-    t /= q;
+    const long long row = i / vpr;
+    const int kv = static_cast<int>(i - row * vpr);
+    const int qq = static_cast<int>(row % q);
+    const long long t = row / q;
     const int pp = static_cast<int>(t % p);
     const int nn = static_cast<int>(t / p);
+    const int h0 = pp * sh - pad_h, w0 = qq * sw - pad_w;
+    const __half* xin = x + static_cast<long long>(nn) * h * w * c;
     float v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int k = kv * 8 + j;
       float val = 0.f;
       if (k < ktot) {
-        const int cc = k % c;
         const int tap = k / c;
-        const int s = tap % kw, r = tap / kw;
-        const int hh = pp * sh - pad_h + r, ww = qq * sw - pad_w + s;
+        const int cc = k - tap * c;
+        const int r = tap / kw;
+        const int s = tap - r * kw;
+        const int hh = h0 + r, ww = w0 + s;
         if (hh >= 0 && hh < h && ww >= 0 && ww < w)
-          val = __half2float(x[((static_cast<long long>(nn) * h + hh) * w + ww) * c + cc]);
+          val = __half2float(xin[(static_cast<long long>(hh) * w + ww) * c + cc]);
       }
       v[j] = val;
     }
-    store8(col + (i / vpr) * kpad + kv * 8, v);
+    store8(col + row * kpad + kv * 8, v);
   }
 }
 
@@ -922,7 +1000,8 @@ extern "C" int kfb_bn_forward_train(const void* x, long long ldx, long long rows
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = reduce_blocks(rows, C);
   channel_reduce_kernel<0><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
-      (const __half*)x, ldx, nullptr, 0, nullptr, 0, nullptr, nullptr, 0, rows, C, scratch);
+      (const __half*)x, ldx, nullptr, 0, nullptr, 0, nullptr, nullptr, nullptr, 0, rows, C,
+      scratch);
   const float unbias = rows > 1 ? (float)((double)rows / (double)(rows - 1)) : 1.f;
   bn_finalize_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(
       scratch, nb, C, (float)(1.0 / (double)rows), unbias, eps, decay, gamma, beta, moving_mean,
@@ -955,11 +1034,14 @@ extern "C" int kfb_bn_forward_inference(const void* x, long long ldx, long long 
   return 0;
 }
 
-// Backward of y = act(bn(x) (+ residual)). `mask` is y when act = ReLU (else null).
+// Backward of y = act(bn(x) (+ residual)). ReLU mask: `mask` = y when given; else, if
+// `relu_affine` (the forward scale/shift, [2][C]) is given and there was no residual, the mask
+// is recomputed from x (saves re-reading y twice); both null = no activation.
 // coef: 3*C floats of scratch; scratch: kfb_reduce_blocks * 2 * C floats.
 extern "C" int kfb_bn_backward(const void* dy, long long lddy, const void* mask, long long ldm,
-                               const void* x, long long ldx, long long rows, int C,
-                               const float* gamma, const float* mean_rstd, float* dgamma,
+                               const float* relu_affine, const void* x, long long ldx,
+                               long long rows, int C, const float* gamma,
+                               const float* mean_rstd, float* dgamma,
                                float* dbeta, int accumulate_param_grads, float grad_scale,
                                float* coef, float* scratch, void* dz, long long lddz, void* dres,
                                long long lddr, int dres_accumulate, void* stream) {
@@ -968,14 +1050,15 @@ extern "C" int kfb_bn_backward(const void* dy, long long lddy, const void* mask,
   const int nb = reduce_blocks(rows, C);
   channel_reduce_kernel<1><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
       (const __half*)x, ldx, (const __half*)dy, lddy, (const __half*)mask, ldm, mean_rstd,
-      nullptr, 0, rows, C, scratch);
+      mask ? nullptr : relu_affine, nullptr, 0, rows, C, scratch);
   bn_bwd_finalize_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(
       scratch, nb, C, (float)(1.0 / (double)rows), gamma, mean_rstd, dgamma, dbeta,
       accumulate_param_grads, grad_scale, coef);
   dim3 ag, ab;
   apply_launch_shape(rows, C, &ag, &ab);
   bn_bwd_apply_kernel<<<ag, ab, 0, st>>>((const __half*)dy, lddy, (const __half*)mask, ldm,
-                                         (const __half*)x, ldx, coef, (__half*)dz, lddz,
+                                         (const __half*)x, ldx, coef,
+                                         mask ? nullptr : relu_affine, (__half*)dz, lddz,
                                          (__half*)dres, lddr, dres_accumulate, rows, C);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -990,8 +1073,8 @@ extern "C" int kfb_bias_act_backward(const void* dy, long long lddy, const void*
   cudaStream_t st = (cudaStream_t)stream;
   const int nb = reduce_blocks(rows, C);
   channel_reduce_kernel<2><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
-      nullptr, 0, (const __half*)dy, lddy, (const __half*)mask, ldm, nullptr, (__half*)dz, lddz,
-      rows, C, scratch);
+      nullptr, 0, (const __half*)dy, lddy, (const __half*)mask, ldm, nullptr, nullptr,
+      (__half*)dz, lddz, rows, C, scratch);
   if (dbias != nullptr)
     colsum_finalize_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(scratch, nb, C, dbias,
                                                                            accumulate, scale);
@@ -1091,9 +1174,18 @@ extern "C" int kfb_im2col_small_c(const void* x, void* col, int n, int h, int w,
                                   int q, int kh, int kw, int sh, int sw, int pad_h, int pad_w,
                                   int kpad, void* stream) {
   KFB_REQUIRE(kpad % 8 == 0 && kpad >= kh * kw * c, "im2col_small_c: bad kpad %d", kpad);
-  im2col_small_c_kernel<<<grid_for((long long)n * p * q * (kpad / 8)), 256, 0,
-                          (cudaStream_t)stream>>>((const __half*)x, (__half*)col, n, h, w, c, p,
-                                                  q, kh, kw, sh, sw, pad_h, pad_w, kpad);
+  const int blocks = grid_for((long long)n * p * q * (kpad / 8), 256, 148 * 32);
+  cudaStream_t st = (cudaStream_t)stream;
+#define KFB_IM2COL(TC, TKH, TKW)                                                              \
+  im2col_small_c_kernel<TC, TKH, TKW><<<blocks, 256, 0, st>>>(                                \
+      (const __half*)x, (__half*)col, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w, kpad)
+  const bool tight = kpad == (kh * kw * c + 7) / 8 * 8;
+  if (tight && c == 3 && kh == 7 && kw == 7) KFB_IM2COL(3, 7, 7);
+  else if (tight && c == 3 && kh == 3 && kw == 3) KFB_IM2COL(3, 3, 3);
+  else if (tight && c == 3 && kh == 11 && kw == 11) KFB_IM2COL(3, 11, 11);
+  else if (tight && c == 3 && kh == 5 && kw == 5) KFB_IM2COL(3, 5, 5);
+  else KFB_IM2COL(0, 0, 0);
+#undef KFB_IM2COL
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

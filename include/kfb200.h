@@ -88,9 +88,11 @@ int kfb_bn_forward_inference(const void* x, long long ldx, long long rows, int C
                              const void* residual, long long ldr, int relu, void* y,
                              long long ldy, void* stream);
 /* Backward of the fused op above: dgamma/dbeta, dz (grad wrt x) and optionally the residual
- * gradient. `mask` is the forward output when ReLU was applied. coef: 3*C floats. */
-int kfb_bn_backward(const void* dy, long long lddy, const void* mask, long long ldm, const void* x,
-                    long long ldx, long long rows, int C, const float* gamma,
+ * gradient. ReLU mask: `mask` (the forward output) if given, else recomputed from x through
+ * `relu_affine` (the forward scale_shift; only valid without a residual). coef: 3*C floats. */
+int kfb_bn_backward(const void* dy, long long lddy, const void* mask, long long ldm,
+                    const float* relu_affine, const void* x, long long ldx, long long rows, int C,
+                    const float* gamma,
                     const float* mean_rstd, float* dgamma, float* dbeta,
                     int accumulate_param_grads, float grad_scale, float* coef, float* scratch,
                     void* dz, long long lddz, void* dres, long long lddr, int dres_accumulate,

@@ -39,6 +39,7 @@ class SyntheticDeviceSource(InputSource):
 
 class SyntheticHostSource(InputSource):
     """A small ring of pinned host batches; every step pays the H2D copy."""
+    host_resident = True
 
     def __init__(self, batch, image_size, depth, nclass, device, seed, ring=2,
                  dtype=torch.float16):

@@ -74,6 +74,14 @@ class CudaExecutor:
         self.images = torch.zeros((n, h, w, c), dtype=torch.float16, device=dev)
         self.buf[graph.input.id] = _Buf(self.images, n * h * w, c, c)
         self.labels = torch.zeros((n,), dtype=torch.int32, device=dev)
+        # host batches are prefetched into a second buffer on a copy stream (double buffering)
+        self._img_bufs = [self.images, None]
+        self._lab_bufs = [self.labels, None]
+        self._cur = 0
+        self._staged = False
+        self._copy_stream = None
+        self._ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self._free = [torch.cuda.Event(), torch.cuda.Event()]
         self.needs_grad = self._mark_needs_grad(need_input_grad)
         for node in graph.nodes:
             self._alloc_output(node)
@@ -237,16 +245,59 @@ class CudaExecutor:
         return m * n * 4 * splits
 
     # ------------------------------------------------------------------ inputs
+    def _bind_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+        self.images, self.labels = images, labels
+        b = self.buf[self.graph.input.id]
+        self.buf[self.graph.input.id] = _Buf(images, b.rows, b.cols, b.ld)
+
     def set_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
-        """Copies a batch into the static input buffers (non-blocking from pinned memory)."""
-        self.images.copy_(images, non_blocking=True)
-        self.labels.copy_(labels, non_blocking=True)
+        """Makes a batch the input of the next step. Device tensors of the right type are used
+        in place (the synthetic device source hands over the same cached buffers every step);
+        host tensors are copied on the compute stream (see stage_inputs for the overlapped
+        path)."""
+        ref = self._img_bufs[self._cur]
+        if (images.is_cuda and images.dtype == torch.float16 and images.is_contiguous() and
+                images.shape == ref.shape and labels.is_cuda and labels.dtype == torch.int32):
+            self._bind_inputs(images, labels)
+            return
+        img, lab = self._img_bufs[self._cur], self._lab_bufs[self._cur]
+        img.copy_(images, non_blocking=True)
+        lab.copy_(labels, non_blocking=True)
+        self._bind_inputs(img, lab)
+
+    def stage_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+        """Starts the host->device copy of the NEXT step's batch on a copy stream into the back
+        buffer; it overlaps the kernels of the step that is currently enqueued."""
+        b = 1 - self._cur
+        if self._img_bufs[b] is None:
+            self._img_bufs[b] = torch.zeros_like(self._img_bufs[self._cur])
+            self._lab_bufs[b] = torch.zeros_like(self._lab_bufs[self._cur])
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        cs = self._copy_stream
+        cs.wait_event(self._free[b])  # the forward pass that last read this buffer is done
+        with torch.cuda.stream(cs):
+            self._img_bufs[b].copy_(images, non_blocking=True)
+            self._lab_bufs[b].copy_(labels, non_blocking=True)
+            self._ready[b].record(cs)
+        self._staged = True
+
+    def has_staged_inputs(self) -> bool:
+        return self._staged
+
+    def use_staged_inputs(self) -> None:
+        b = 1 - self._cur
+        torch.cuda.current_stream(self.device).wait_event(self._ready[b])
+        self._cur = b
+        self._staged = False
+        self._bind_inputs(self._img_bufs[b], self._lab_bufs[b])
 
     # ------------------------------------------------------------------ forward
     def forward(self, train: bool = True) -> None:
         s = self._s()
         for node in self.graph.nodes:
             getattr(self, "_fwd_" + node.op)(node, train, s)
+        # the image buffer is only read by the forward pass (backward uses saved activations)
+        self._free[self._cur].record(torch.cuda.current_stream(self.device))
 
     def _w16(self, name):
         return ctypes.c_void_p(self.store.view(name, "w16").data_ptr())
@@ -474,7 +525,11 @@ class CudaExecutor:
             gz = self._tmp_like(z)
         else:
             gz = self._grad(zin) if need_dz else self._tmp_like(z)
-        native.call("bn_backward", gy.p, i64(gy.ld), y.p if a["relu"] else None, i64(y.ld), z.p,
+        # plain BN+ReLU: the mask is recomputed from z (no need to re-read y); with a residual
+        # the stored output is the only source of the mask
+        mask = y.p if (a["relu"] and has_res) else None
+        affine = ptr(info["scale_shift"]) if (a["relu"] and not has_res) else None
+        native.call("bn_backward", gy.p, i64(gy.ld), mask, i64(y.ld), affine, z.p,
                     i64(z.ld), i64(z.rows), i32(z.cols), gamma, ptr(info["mean_rstd"]), dgamma,
                     dbeta, i32(0), f32(1.0), ptr(info["coef"]), ptr(self.scratch), gz.p,
                     i64(gz.ld), gres.p if gres else None, i64(gres.ld if gres else 0),

@@ -63,7 +63,9 @@ def test_bn_forward_backward(rows, c, relu, res, scale):
     dres = torch.empty_like(x) if res else None
     dgamma = torch.zeros(c, device="cuda") if scale else None
     dbeta = torch.zeros(c, device="cuda")
-    native.call("bn_backward", ptr(dy), i64(c), ptr(y) if relu else None, i64(c), ptr(x), i64(c),
+    use_affine = relu and not res       # mask recomputed from x through the forward affine
+    native.call("bn_backward", ptr(dy), i64(c), ptr(y) if (relu and res) else None, i64(c),
+                ptr(ss) if use_affine else None, ptr(x), i64(c),
                 i64(rows), i32(c), ptr(gamma), ptr(mean_rstd), ptr(dgamma), ptr(dbeta), i32(0),
                 f32(1.0), ptr(coef), ptr(scratch), ptr(dz), i64(c), ptr(dres), i64(c), i32(0),
                 _s())
