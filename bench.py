@@ -126,12 +126,84 @@ def _timed_steps(bench, steps, torch, e2e: bool):
     return start.elapsed_time(end), wall, last
 
 
+def _standin_arm(args, torch) -> int:
+    """Same metric for the conventional PyTorch stand-in (cuDNN/cuBLAS autocast + NCCL +
+    torch.optim), see kf_benchmarks_b200/baseline/torch_standin.py. Labelled impl=standin: it is
+    neither the reference nor the product."""
+    import torch.distributed as dist
+    from kf_benchmarks_b200 import benchmark, datasets, lr as lr_mod, params as params_lib
+    from kf_benchmarks_b200.baseline.torch_standin import StandinTrainer
+    from kf_benchmarks_b200.models import model_config
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    kungfu = args.variable_update in ("kungfu", "horovod")
+    p = params_lib.make_params(model=args.model, batch_size=args.batch_size, use_fp16=True,
+                               variable_update=args.variable_update,
+                               kungfu_option=args.kungfu_option,
+                               num_gpus=1 if kungfu else args.gpus, optimizer=args.optimizer,
+                               data_format="NHWC")
+    ds = datasets.create_dataset(None, None)
+    model = model_config.get_model_config(args.model, ds, p)
+    model.set_batch_size(args.batch_size)
+    graph = model.build_graph(ds.num_classes, batch_size=args.batch_size)
+    tr = StandinTrainer(p, model, graph, ds.num_classes, dev, world, rank)
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    h = model.image_size
+    images = (torch.randn(args.batch_size, h, h, 3, device=dev, generator=gen) * 60 + 127).half()
+    labels = torch.randint(0, ds.num_classes - 1, (args.batch_size,), device=dev, generator=gen)
+    warmup = max(args.warmup, 3)
+    lr = lr_mod.get_learning_rate(p, 1000, ds.num_examples_per_epoch("train"), model,
+                                  args.batch_size * (world if kungfu else args.gpus))
+    for _ in range(warmup + 5):  # cudnn.benchmark needs a few extra steps
+        tr.step(images, labels, lr)
+
+    def sync():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+    sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        tr.step(images, labels, lr)
+    e1.record()
+    e1.synchronize()
+    sync()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    if rank == 0:
+        gb = args.batch_size * world
+        print(json.dumps({
+            "impl": "standin", "metric": "ResNet-50 fp16 synthetic-ImageNet training images/sec "
+            "(device-timed, max over ranks)", "value": gb * args.steps / (ms / 1e3),
+            "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "dtype": "fp16 autocast", "data": "synthetic",
+            "config": {"model": args.model, "global_batch": gb,
+                       "variable_update": args.variable_update, "optimizer": args.optimizer,
+                       "note": "PyTorch cuDNN/cuBLAS + NCCL stand-in (not the reference)"},
+            "final_loss": float(tr.last_loss)}))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "standin"])
     ap.add_argument("--model", default="resnet50")
     ap.add_argument("--batch_size", type=int, default=256)
     ap.add_argument("--variable_update", default="replicated")
@@ -151,6 +223,8 @@ def main() -> int:
     from kf_benchmarks_b200.data import inputs
     from kf_benchmarks_b200.ops import native
 
+    if args.impl == "standin":
+        return _standin_arm(args, torch)
     warmup = max(args.warmup, 3)
     kungfu = args.variable_update in ("kungfu", "horovod")
     p = params_lib.make_params(

@@ -1,0 +1,263 @@
+"""Real-data input pipelines: ImageNet TFRecords and CIFAR-10, on host threads, delivered to the
+device through a pinned double buffer (the executor prefetches the next batch on a copy stream).
+
+Image transforms follow the reference (T/preprocessing.py:130-307,653-737):
+
+* normalisation ``x / 127.5 - 1``;
+* ImageNet eval: resize so the short side covers 1.15x the target, centre crop;
+* ImageNet train: sample a distorted bounding box (object coverage >= 0.1, aspect ratio in
+  [3/4, 4/3], area in [0.05, 1], up to 100 attempts), crop, resize (bilinear / nearest / bicubic
+  / area, ``round_robin`` cycles through them by batch position), random horizontal flip,
+  optional colour distortion (brightness 32/255, saturation [0.5, 1.5], contrast [0.5, 1.5],
+  order alternating with batch position);
+* CIFAR-10 train: pad 4, random 32x32 crop, random flip; eval: centre crop / pad.
+
+A background ``ImageProducer`` keeps ``2 * batch_group_size`` batches staged
+(T/cnn_util.py:118-198); ``--datasets_repeat_cached_sample`` repeats one decoded sample to take
+IO out of a benchmark; workers start at different file offsets (``shift_ratio`` =
+rank / world, T/benchmark_cnn.py:3217-3221).
+"""
+from __future__ import annotations
+
+import glob
+import io
+import os
+import random
+from typing import List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from ..utils.cnn_util import ImageProducer
+from . import tfrecord
+from .inputs import InputSource
+
+_RESIZE = {"nearest": 0, "bilinear": 2, "bicubic": 3, "area": 4}  # PIL resample codes
+_ROUND_ROBIN = ["bilinear", "nearest", "bicubic", "area"]
+
+
+def normalized_image(img: np.ndarray) -> np.ndarray:
+    return img.astype(np.float32) * (1.0 / 127.5) - 1.0
+
+
+def get_image_resize_method(resize_method: str, batch_position: int = 0) -> str:
+    if resize_method == "round_robin":
+        return _ROUND_ROBIN[batch_position % len(_ROUND_ROBIN)]
+    if resize_method not in _RESIZE:
+        raise ValueError("Invalid resize_method %s" % resize_method)
+    return resize_method
+
+
+def _resize(img: np.ndarray, h: int, w: int, method: str) -> np.ndarray:
+    from PIL import Image
+    pil = Image.fromarray(img.astype(np.uint8))
+    return np.asarray(pil.resize((w, h), resample=_RESIZE[method]))
+
+
+def eval_image(img: np.ndarray, height: int, width: int, batch_position: int = 0,
+               resize_method: str = "bilinear") -> np.ndarray:
+    ih, iw = img.shape[:2]
+    ratio = max(height / float(ih), width / float(iw))
+    rh, rw = int(ih * ratio * 1.15), int(iw * ratio * 1.15)
+    out = _resize(img, rh, rw, get_image_resize_method(resize_method, batch_position))
+    top, left = (rh - height) // 2, (rw - width) // 2
+    return out[top:top + height, left:left + width]
+
+
+def sample_distorted_bounding_box(ih: int, iw: int, bbox: Optional[Tuple[float, ...]], rng,
+                                  min_object_covered=0.1, aspect=(0.75, 1.33), area=(0.05, 1.0),
+                                  max_attempts=100) -> Tuple[int, int, int, int]:
+    """(top, left, h, w) of a random crop; falls back to the whole image."""
+    if bbox is None:
+        bbox = (0.0, 0.0, 1.0, 1.0)  # ymin, xmin, ymax, xmax
+    by0, bx0, by1, bx1 = bbox
+    barea = max((by1 - by0) * (bx1 - bx0), 1e-6)
+    for _ in range(max_attempts):
+        a = rng.uniform(area[0], area[1]) * ih * iw
+        r = rng.uniform(aspect[0], aspect[1])
+        w = int(round((a * r) ** 0.5))
+        h = int(round((a / r) ** 0.5))
+        if w < 1 or h < 1 or w > iw or h > ih:
+            continue
+        top, left = rng.randint(0, ih - h), rng.randint(0, iw - w)
+        y0, x0, y1, x1 = top / ih, left / iw, (top + h) / ih, (left + w) / iw
+        inter = max(0.0, min(y1, by1) - max(y0, by0)) * max(0.0, min(x1, bx1) - max(x0, bx0))
+        if inter / barea >= min_object_covered:
+            return top, left, h, w
+    return 0, 0, ih, iw
+
+
+def distort_color(img: np.ndarray, batch_position: int, rng) -> np.ndarray:
+    """Brightness / saturation / contrast jitter on [0, 255] floats; the op order alternates with
+    the batch position (T/preprocessing.py:262-307)."""
+    x = img.astype(np.float32)
+
+    def brightness(v):
+        return v + rng.uniform(-32.0, 32.0)
+
+    def saturation(v):
+        g = v.mean(axis=2, keepdims=True)
+        return g + (v - g) * rng.uniform(0.5, 1.5)
+
+    def contrast(v):
+        m = v.mean(axis=(0, 1), keepdims=True)
+        return m + (v - m) * rng.uniform(0.5, 1.5)
+
+    ops = [brightness, saturation, contrast] if batch_position % 2 == 0 else \
+        [brightness, contrast, saturation]
+    for op in ops:
+        x = op(x)
+    return np.clip(x, 0.0, 255.0)
+
+
+def train_image(img: np.ndarray, height: int, width: int, bbox, batch_position: int,
+                resize_method: str, distortions: bool, rng, distort_colors: bool = True):
+    if distortions:
+        top, left, h, w = sample_distorted_bounding_box(img.shape[0], img.shape[1], bbox, rng)
+        img = img[top:top + h, left:left + w]
+        img = _resize(img, height, width, get_image_resize_method(resize_method, batch_position))
+        if rng.random() < 0.5:
+            img = img[:, ::-1]
+        if distort_colors:
+            img = distort_color(img, batch_position, rng)
+    else:
+        img = _resize(img, height, width, get_image_resize_method(resize_method, batch_position))
+    return np.ascontiguousarray(img)
+
+
+def decode_jpeg(buf: bytes) -> np.ndarray:
+    from PIL import Image
+    return np.asarray(Image.open(io.BytesIO(buf)).convert("RGB"))
+
+
+def parse_example_proto(record: bytes):
+    """(image bytes, label, bbox or None, text) - T/preprocessing.py:27-72."""
+    ex = tfrecord.parse_example(record)
+    label = int(ex["image/class/label"][0])
+    bbox = None
+    if ex.get("image/object/bbox/xmin"):
+        bbox = (float(ex["image/object/bbox/ymin"][0]), float(ex["image/object/bbox/xmin"][0]),
+                float(ex["image/object/bbox/ymax"][0]), float(ex["image/object/bbox/xmax"][0]))
+    text = ex.get("image/class/text", [b""])
+    return ex["image/encoded"][0], label, bbox, text[0] if text else b""
+
+
+class _BatchSource(InputSource):
+    """Common machinery: a producer thread filling pinned batches."""
+    host_resident = True
+
+    def __init__(self, params, batch, height, width, device, train, seed):
+        self.p = params
+        self.batch, self.h, self.w = batch, height, width
+        self.device = torch.device(device)
+        self.train = train
+        self.rng = random.Random(seed)
+        self.out_dtype = torch.float16 if self.device.type == "cuda" else torch.float32
+        self.producer = ImageProducer(self._make_batch, params.batch_group_size)
+        self.producer.start()
+        self.bytes_per_step = batch * height * width * 3 * (2 if self.out_dtype ==
+                                                            torch.float16 else 4) + batch * 4
+
+    def _next_example(self, position: int):
+        raise NotImplementedError
+
+    def _make_batch(self):
+        imgs = np.empty((self.batch, self.h, self.w, 3), dtype=np.float32)
+        labels = np.empty((self.batch,), dtype=np.int32)
+        for i in range(self.batch):
+            imgs[i], labels[i] = self._next_example(i)
+        t = torch.from_numpy(imgs).to(self.out_dtype)
+        lab = torch.from_numpy(labels)
+        if self.device.type == "cuda":
+            t, lab = t.pin_memory(), lab.pin_memory()
+        return t, lab
+
+    def next_batch(self):
+        return self.producer.get()
+
+    def close(self):
+        self.producer.done()
+
+
+class ImagenetSource(_BatchSource):
+    def __init__(self, params, dataset, batch, height, width, device, train, seed, rank, world):
+        subset = "train" if train else "validation"
+        files = sorted(glob.glob(dataset.tf_record_pattern(subset)))
+        if not files:
+            raise ValueError("Found no files in --data_dir matching: %s" %
+                             dataset.tf_record_pattern(subset))
+        shift = int(len(files) * (rank / float(max(world, 1))))
+        self.files = files[shift:] + files[:shift]       # shift_ratio = rank / world
+        self.records = self._record_iter()
+        self.cached = None
+        super().__init__(params, batch, height, width, device, train, seed * 7919 + rank)
+
+    def _record_iter(self):
+        while True:
+            order = list(self.files)
+            for path in order:
+                for rec in tfrecord.read_records(path):
+                    yield rec
+
+    def _next_example(self, position: int):
+        p = self.p
+        if p.datasets_repeat_cached_sample and self.cached is not None:
+            buf, label, bbox = self.cached
+        else:
+            buf, label, bbox, _ = parse_example_proto(next(self.records))
+            self.cached = (buf, label, bbox)
+        img = decode_jpeg(buf)
+        if self.train:
+            out = train_image(img, self.h, self.w, bbox, position, p.resize_method, p.distortions,
+                              self.rng)
+        else:
+            out = eval_image(img, self.h, self.w, position, p.resize_method)
+        return normalized_image(out), label
+
+
+class Cifar10Source(_BatchSource):
+    def __init__(self, params, dataset, batch, device, train, seed, rank, world):
+        self.images, self.labels = dataset.read_data_files("train" if train else "validation")
+        self.order = np.arange(len(self.labels))
+        self.pos = 0
+        self.np_rng = np.random.RandomState(seed * 7919 + rank)
+        if train:
+            self.np_rng.shuffle(self.order)
+        super().__init__(params, batch, 32, 32, device, train, seed * 7919 + rank)
+
+    def _next_example(self, position: int):
+        if self.pos >= len(self.order):
+            self.pos = 0
+            if self.train:
+                self.np_rng.shuffle(self.order)
+        idx = self.order[self.pos]
+        self.pos += 1
+        img = self.images[idx]
+        if self.train and self.p.distortions:
+            padded = np.zeros((40, 40, 3), dtype=img.dtype)
+            padded[4:36, 4:36] = img
+            top, left = self.rng.randint(0, 8), self.rng.randint(0, 8)
+            img = padded[top:top + 32, left:left + 32]
+            if self.rng.random() < 0.5:
+                img = img[:, ::-1]
+        return normalized_image(img), int(self.labels[idx])
+
+
+_PREPROCESSORS = {"imagenet": {"default": ImagenetSource}, "cifar10": {"default": Cifar10Source}}
+
+
+def get_preprocessor(dataset_name: str, name: str = "default"):
+    try:
+        return _PREPROCESSORS[dataset_name][name]
+    except KeyError:
+        raise ValueError("no input preprocessor %r for dataset %r" % (name, dataset_name))
+
+
+def create_real_data_source(params, dataset, model, batch, device, nclass, seed, rank, world,
+                            train) -> InputSource:
+    if dataset.name == "imagenet":
+        return ImagenetSource(params, dataset, batch, model.image_size, model.image_size, device,
+                              train, seed, rank, world)
+    if dataset.name == "cifar10":
+        return Cifar10Source(params, dataset, batch, device, train, seed, rank, world)
+    raise ValueError("no real-data pipeline for dataset %s" % dataset.name)

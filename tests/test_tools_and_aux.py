@@ -1,0 +1,67 @@
+"""all_reduce_benchmark, trace / profile outputs, benchmark logger (reference tests:
+T/all_reduce_benchmark_test.py:28-47, T/benchmark_cnn_test.py:656-675)."""
+import json
+import os
+import re
+import subprocess
+import sys
+
+from kf_benchmarks_b200 import benchmark, params as P
+from kf_benchmarks_b200.utils import log_util
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_all_reduce_benchmark_two_cpu_ranks():
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    cmd = [sys.executable, "-m", "kf_benchmarks_b200.parallel.launcher", "-np", "2", "--", "-m",
+           "kf_benchmarks_b200.all_reduce_benchmark", "--model=trivial", "--data_name=cifar10",
+           "--device=cpu", "--data_format=NHWC", "--num_batches=2", "--num_warmup_batches=1",
+           "--iters_per_step=2"]
+    res = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout + res.stderr
+    lines = [l for l in res.stdout.splitlines() if l.startswith("Average time per step:")]
+    assert lines and re.match(r"^Average time per step: [0-9.e-]+$", lines[-1])
+
+
+def test_trace_profile_and_benchmark_log(tmp_path):
+    kw = dict(model="trivial", data_name="cifar10", device="cpu", data_format="NHWC", batch_size=4,
+              num_batches=11, num_warmup_batches=3, trace_file=str(tmp_path / "trace.json"),
+              tfprof_file=str(tmp_path / "prof.txt"), benchmark_log_dir=str(tmp_path / "blog"),
+              benchmark_test_id="t1")
+    lines = []
+    old = log_util.log_fn
+    log_util.log_fn = lines.append
+    try:
+        benchmark.BenchmarkCNN(benchmark.setup(P.make_params(**kw))).run()
+    finally:
+        log_util.log_fn = old
+    assert any(l.startswith("Dumping trace to") for l in lines)
+    with open(kw["trace_file"]) as f:
+        trace = json.load(f)
+    assert "traceEvents" in trace and len(trace["traceEvents"]) > 0
+    assert os.path.getsize(kw["tfprof_file"]) > 0
+    with open(os.path.join(kw["benchmark_log_dir"], "benchmark_run.log")) as f:
+        info = json.load(f)
+    assert info["model_name"] == "trivial" and info["test_id"] == "t1"
+    with open(os.path.join(kw["benchmark_log_dir"], "metric.log")) as f:
+        metrics = [json.loads(l) for l in f]
+    assert {m["name"] for m in metrics} >= {"average_examples_per_sec", "last_average_loss"}
+
+
+def test_cli_entry_point_and_help():
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    res = subprocess.run([sys.executable, "-m", "kf_benchmarks_b200.cli", "--model=trivial",
+                          "--device=cpu", "--data_format=NHWC", "--data_name=cifar10",
+                          "--batch_size=4", "--num_batches=2", "--num_warmup_batches=0",
+                          "--display_every=1"], cwd=ROOT, env=env, capture_output=True, text=True,
+                         timeout=300)
+    assert res.returncode == 0, res.stderr
+    assert re.search(r"^total images/sec: \d+\.\d\d$", res.stdout, re.M)
+    res = subprocess.run([sys.executable, "-m", "kf_benchmarks_b200.cli", "--model", "trivial",
+                          "stray"], cwd=ROOT, env=env, capture_output=True, text=True, timeout=60)
+    assert res.returncode == 2 and "positional" in res.stderr
