@@ -62,6 +62,8 @@ struct GemmParams {
   int out_fp32;
   int accumulate;          // out += result (gradient accumulation for fan-out tensors)
   int stages;              // smem pipeline depth of this launch (1..kMaxStages)
+  int m_tiles, n_tiles, splits;  // tile space walked by the persistent CTAs
+  int wg_flat;             // WGRAD: N is the flattened (tap, channel) axis (C % 64 == 0)
   // optional row scatter (strided dgrad): row (n,i,j) -> (n, h0 + i*sh, w0 + j*sw) of H x W
   int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw, sc_h0, sc_w0;
   // DGRAD: filter tap visited at (r, s) of this launch's (sub-)filter
@@ -70,25 +72,34 @@ struct GemmParams {
 
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;
-constexpr int kThreads = 192;
 constexpr int kTileABytes = kBlockM * kBlockK * 2;  // 16 KiB
-
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 8;
+constexpr int kStageRowBytes = 144;                 // 128 B payload + 16 B pad (conflict free)
+constexpr int kSmemBudget = 227 * 1024;
 
 template <int BN>
 struct TileCfg {
   static constexpr int kTileBBytes = BN * kBlockK * 2;
   static constexpr int kStageBytes = kTileABytes + kTileBBytes;
-  static constexpr int kTmemCols = BN < 32 ? 32 : BN;
-  // at least 2 A tiles' worth of bytes must exist: the epilogue stages through them
-  static constexpr int smem_bytes(int stages) {
-    const int pipe = stages * kStageBytes;
-    return (pipe < 2 * kTileABytes ? 2 * kTileABytes : pipe) + 1024 /*align*/ + 256 /*bars*/;
-  }
+  static constexpr int kTmemCols = 2 * BN;  // two accumulator stages (power of two >= 128)
+  // Narrow tiles are picked for short-K, store-bound problems: give them eight epilogue warps
+  // (two per TMEM lane quarter, interleaving column chunks); 256-wide tiles keep four and a
+  // deeper smem ring instead.
+  static constexpr int kEpiWarps = BN == 256 ? 4 : 8;
+  static constexpr int kThreads = 64 + 32 * kEpiWarps;
+  static constexpr int kStagingBytes = kEpiWarps * 32 * kStageRowBytes;
+  static constexpr int kFixedBytes = kStagingBytes + 1024 /*align*/ + 512 /*barriers*/;
+  static constexpr int kMaxFit = (kSmemBudget - kFixedBytes) / kStageBytes;
+  static constexpr int max_stages() { return kMaxFit > kMaxStages ? kMaxStages : kMaxFit; }
+  static constexpr int smem_bytes(int stages) { return stages * kStageBytes + kFixedBytes; }
 };
 
+// Persistent kernel: one CTA per SM walks the tile list (m fastest, then n, then split).
+// Three pipelines run concurrently: TMA -> smem ring (full/empty mbarriers), MMA -> TMEM
+// accumulator pair (tmem_full/tmem_empty), and the epilogue draining accumulator `a` while the
+// MMA warp already fills accumulator `a^1` for the next tile.
 template <int BN, int MODE>
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                         const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   using Cfg = TileCfg<BN>;
@@ -102,28 +113,17 @@ __global__ void __launch_bounds__(kThreads, 3)
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kTileABytes;
-  const int pipe_bytes = kStages * Cfg::kStageBytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(
-      smem + (pipe_bytes < 2 * kTileABytes ? 2 * kTileABytes : pipe_bytes));
+  uint8_t* staging = smem + kStages * Cfg::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
   uint64_t* empty_bar = full_bar + kMaxStages;
-  uint64_t* tmem_full_bar = empty_bar + kMaxStages;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint64_t* tmem_full_bar = empty_bar + kMaxStages;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;       // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-
-  const int m0 = blockIdx.x * kBlockM;
-  int n0 = blockIdx.y * BN;  // first logical column of this tile
-  int wg_tap = 0, wg_cn = 0;
-  if (MODE == WGRAD) {
-    wg_tap = blockIdx.y / p.NCB;
-    wg_cn = blockIdx.y % p.NCB;
-    n0 = wg_cn * BN;  // channel offset within the tap
-  }
-  const int kb_begin = blockIdx.z * p.kb_per_split;
-  int kb_end = kb_begin + p.kb_per_split;
-  if (kb_end > p.num_kb) kb_end = p.num_kb;
-  const int my_kb = kb_end - kb_begin;  // may be <= 0 for a trailing split: writes zeros
+  const int tiles_mn = p.m_tiles * p.n_tiles;
+  const int total_tiles = tiles_mn * p.splits;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -132,7 +132,10 @@ __global__ void __launch_bounds__(kThreads, 3)
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(tmem_full_bar, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full_bar[a], 1);
+      mbar_init(&tmem_empty_bar[a], Cfg::kEpiWarps);  // one arrive per epilogue warp
+    }
     mbar_fence_init();
     fence_proxy_async_smem();
   }
@@ -146,86 +149,138 @@ __global__ void __launch_bounds__(kThreads, 3)
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0 && my_kb > 0) {
-      // im2col start coordinates of this tile's first pixel (FPROP/DGRAD)
-      int px_n = 0, px_h = 0, px_w = 0;
-      if (MODE == FPROP || MODE == DGRAD) {
-        const int pq = p.P * p.Q;
-        px_n = m0 / pq;
-        const int rem = m0 - px_n * pq;
-        const int pp = rem / p.Q;
-        px_h = p.lower_h + pp * p.stride_h;
-        px_w = p.lower_w + (rem - pp * p.Q) * p.stride_w;
-      }
+    if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = kb_begin; kb < kb_end; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sa = smem_a + stage * kTileABytes;
-        uint8_t* sb = smem_b + stage * Cfg::kTileBBytes;
-        mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-        if (MODE == GEMM_TN) {
-          tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBlockK, m0);
-          tma_load_2d(sb, &tmB, &full_bar[stage], kb * kBlockK, n0);
-        } else if (MODE == GEMM_NN) {
-          tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBlockK, m0);
-#pragma unroll
-          for (int j = 0; j < BN / 64; ++j)
-            tma_load_2d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * kBlockK);
-        } else if (MODE == GEMM_NT) {
-#pragma unroll
-          for (int j = 0; j < kBlockM / 64; ++j)
-            tma_load_2d(sa + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, kb * kBlockK);
-#pragma unroll
-          for (int j = 0; j < BN / 64; ++j)
-            tma_load_2d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * kBlockK);
-        } else if (MODE == FPROP) {
-          const int tap = kb / p.CB;
-          const int cb = kb - tap * p.CB;
-          const int r = tap / p.S;
-          const int s = tap - r * p.S;
-          tma_load_im2col_4d(sa, &tmA, &full_bar[stage], cb * kBlockK, px_w, px_h, px_n,
-                             static_cast<uint16_t>(s), static_cast<uint16_t>(r));
-          tma_load_2d(sb, &tmB, &full_bar[stage], tap * p.Ck + cb * kBlockK, n0);
-        } else if (MODE == DGRAD) {
-          const int tap = kb / p.CB;
-          const int cb = kb - tap * p.CB;
-          const int r = tap / p.S;
-          const int s = tap - r * p.S;
-          tma_load_im2col_4d(sa, &tmA, &full_bar[stage], cb * kBlockK, px_w, px_h, px_n,
-                             static_cast<uint16_t>(s), static_cast<uint16_t>(r));
-          const int wtap = (p.wt_r0 + p.wt_rstep * (p.R - 1 - r)) * p.wt_S +
-                           (p.wt_s0 + p.wt_sstep * (p.S - 1 - s));
-#pragma unroll
-          for (int j = 0; j < BN / 64; ++j)
-            tma_load_3d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, wtap, cb * kBlockK);
-        } else {  // WGRAD
-          const int r = wg_tap / p.S;
-          const int s = wg_tap - r * p.S;
-          const int pix = kb * kBlockK;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int z = tile / tiles_mn;
+        const int rem_t = tile - z * tiles_mn;
+        const int n_blk = rem_t / p.m_tiles;
+        const int m0 = (rem_t - n_blk * p.m_tiles) * kBlockM;
+        const int n0 = n_blk * BN;
+        const int kb_begin = z * p.kb_per_split;
+        int kb_end = kb_begin + p.kb_per_split;
+        if (kb_end > p.num_kb) kb_end = p.num_kb;
+        // im2col start coordinates of this tile's first pixel (FPROP/DGRAD)
+        int px_n = 0, px_h = 0, px_w = 0;
+        if (MODE == FPROP || MODE == DGRAD) {
           const int pq = p.P * p.Q;
-          const int n_img = pix / pq;
-          const int rem = pix - n_img * pq;
+          px_n = m0 / pq;
+          const int rem = m0 - px_n * pq;
           const int pp = rem / p.Q;
-          const int h = p.lower_h + pp * p.stride_h;
-          const int w = p.lower_w + (rem - pp * p.Q) * p.stride_w;
-#pragma unroll
-          for (int j = 0; j < kBlockM / 64; ++j)
-            tma_load_2d(sa + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, pix);
-#pragma unroll
-          for (int j = 0; j < BN / 64; ++j)
-            tma_load_im2col_4d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, w, h, n_img,
-                               static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+          px_h = p.lower_h + pp * p.stride_h;
+          px_w = p.lower_w + (rem - pp * p.Q) * p.stride_w;
         }
-        if (++stage == kStages) {
-          stage = 0;
-          phase ^= 1;
+        // ---- per-tile constants and incremental counters (no divisions inside the K loop) ----
+        // FPROP/DGRAD: kb -> (r, s, cb)
+        int it_r = 0, it_s = 0, it_cb = 0;
+        if (MODE == FPROP || MODE == DGRAD) {
+          const int tap = kb_begin / p.CB;
+          it_cb = kb_begin - tap * p.CB;
+          it_r = tap / p.S;
+          it_s = tap - it_r * p.S;
+        }
+        // WGRAD: pixel cursor (n, row, col) of the K block, and the (tap, channel) of each
+        // 64-wide column block of this n-tile
+        int wg_n = 0, wg_p = 0, wg_q = 0;
+        int wg_c0[BN / 64], wg_r[BN / 64], wg_s[BN / 64];
+        if (MODE == WGRAD) {
+          const int pix = kb_begin * kBlockK;
+          const int pq = p.P * p.Q;
+          wg_n = pix / pq;
+          const int rem = pix - wg_n * pq;
+          wg_p = rem / p.Q;
+          wg_q = rem - wg_p * p.Q;
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j) {
+            int tap, c0;
+            if (p.wg_flat) {
+              const int nn = n0 + 64 * j;  // flattened (tap * C + c), C % 64 == 0
+              tap = nn / p.Cn;
+              c0 = nn - tap * p.Cn;
+              if (tap >= p.R * p.S) {      // past the end: out-of-bounds channels read as zeros
+                tap = 0;
+                c0 = p.Cn;
+              }
+            } else {
+              tap = n_blk / p.NCB;
+              c0 = (n_blk - tap * p.NCB) * BN + 64 * j;
+            }
+            wg_c0[j] = c0;
+            wg_r[j] = tap / p.S;
+            wg_s[j] = tap - wg_r[j] * p.S;
+          }
+        }
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem_a + stage * kTileABytes;
+          uint8_t* sb = smem_b + stage * Cfg::kTileBBytes;
+          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          if (MODE == GEMM_TN) {
+            tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBlockK, m0);
+            tma_load_2d(sb, &tmB, &full_bar[stage], kb * kBlockK, n0);
+          } else if (MODE == GEMM_NN) {
+            tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBlockK, m0);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * kBlockK);
+          } else if (MODE == GEMM_NT) {
+#pragma unroll
+            for (int j = 0; j < kBlockM / 64; ++j)
+              tma_load_2d(sa + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, kb * kBlockK);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, kb * kBlockK);
+          } else if (MODE == FPROP || MODE == DGRAD) {
+            tma_load_im2col_4d(sa, &tmA, &full_bar[stage], it_cb * kBlockK, px_w, px_h, px_n,
+                               static_cast<uint16_t>(it_s), static_cast<uint16_t>(it_r));
+            if (MODE == FPROP) {
+              tma_load_2d(sb, &tmB, &full_bar[stage],
+                          (it_r * p.S + it_s) * p.Ck + it_cb * kBlockK, n0);
+            } else {
+              const int wtap = (p.wt_r0 + p.wt_rstep * (p.R - 1 - it_r)) * p.wt_S +
+                               (p.wt_s0 + p.wt_sstep * (p.S - 1 - it_s));
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_3d(sb + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, wtap,
+                            it_cb * kBlockK);
+            }
+            if (++it_cb == p.CB) {
+              it_cb = 0;
+              if (++it_s == p.S) {
+                it_s = 0;
+                ++it_r;
+              }
+            }
+          } else {  // WGRAD: K = pixels; N = (tap, channel) flattened or one tap per n-tile
+            const int h = p.lower_h + wg_p * p.stride_h;
+            const int w = p.lower_w + wg_q * p.stride_w;
+#pragma unroll
+            for (int j = 0; j < kBlockM / 64; ++j)
+              tma_load_2d(sa + j * 8192, &tmA, &full_bar[stage], m0 + 64 * j, kb * kBlockK);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_im2col_4d(sb + j * 8192, &tmB, &full_bar[stage], wg_c0[j], w, h, wg_n,
+                                 static_cast<uint16_t>(wg_s[j]), static_cast<uint16_t>(wg_r[j]));
+            wg_q += kBlockK;  // advance the pixel cursor by one K block
+            while (wg_q >= p.Q) {
+              wg_q -= p.Q;
+              if (++wg_p == p.P) {
+                wg_p = 0;
+                ++wg_n;
+              }
+            }
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0 && my_kb > 0) {
+    if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_f16(kBlockM, BN, kAMajor, kBMajor);
       // K-major: 8-row groups 1024 B apart; +32 B per UMMA_K(16) inside the swizzle atom.
       // MN-major: 64-element column groups 8192 B apart (LBO), 8-row K groups 1024 B apart
@@ -236,168 +291,202 @@ __global__ void __launch_bounds__(kThreads, 3)
       constexpr uint32_t b_kstep = (kBMajor == kMajorK) ? 32 : 2048;
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < my_kb; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int z = tile / tiles_mn;
+        const int kb_begin = z * p.kb_per_split;
+        int kb_end = kb_begin + p.kb_per_split;
+        if (kb_end > p.num_kb) kb_end = p.num_kb;
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem_a + stage * kTileABytes);
-        const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kTileBBytes);
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem_a + stage * kTileABytes);
+          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kTileBBytes);
 #pragma unroll
-        for (int k = 0; k < kBlockK / 16; ++k) {
-          const uint64_t da = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
-          const uint64_t db = make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, 1024);
-          umma_f16_ss(tmem_base, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t da = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
+            const uint64_t db = make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, 1024);
+            umma_f16_ss(tmem_d, da, db, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
-        umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
-        if (++stage == kStages) {
-          stage = 0;
-          phase ^= 1;
-        }
+        umma_commit(&tmem_full_bar[acc]);
       }
-      umma_commit(tmem_full_bar);
     }
   } else {
     // ===================== epilogue =====================
     // TMEM -> registers (thread = row) -> bias/ReLU -> per-warp staging tile in shared memory
-    // (the pipeline buffers are free once tmem_full fires) -> global stores in which every
-    // instruction writes four full 128-byte row segments.
-    const int quarter = warp & 3;
-    const int row = m0 + quarter * 32 + lane;
-    if (my_kb > 0) {
-      mbar_wait(tmem_full_bar, 0);
-      tc_fence_after();
-    }
-    long long row_off = row;
-    if (p.sc_P > 0) {
-      const int pq = p.sc_P * p.sc_Q;
-      const int n_img = row / pq;
-      const int rem = row - n_img * pq;
-      const int pp = rem / p.sc_Q;
-      const int qq = rem - pp * p.sc_Q;
-      row_off = (static_cast<long long>(n_img) * p.sc_H + p.sc_h0 +
-                 static_cast<long long>(pp) * p.sc_sh) *
-                    p.sc_W +
-                p.sc_w0 + static_cast<long long>(qq) * p.sc_sw;
-    }
-    if (row >= p.M) row_off = -1;  // marks an invalid row
-    int col_mem0 = n0;       // first memory column of this tile
-    int n_limit = p.N - n0;  // number of valid columns in this tile
-    if (MODE == WGRAD) {
-      col_mem0 = wg_tap * p.Cn + n0;
-      n_limit = p.Cn - n0;
-    }
-    if (n_limit > BN) n_limit = BN;
-    const long long base = static_cast<long long>(blockIdx.z) * p.split_stride + col_mem0;
-    constexpr int kStageRowBytes = 144;  // 128 B of payload + 16 B pad (bank-conflict free)
-    uint8_t* stage_buf = smem_a + quarter * (32 * kStageRowBytes);
+    // -> global stores in which every instruction writes four full 128-byte row segments.
+    const int quarter = warp & 3;                  // TMEM lanes this warp may read
+    const int epi = warp - 2;                      // 0 .. kEpiWarps-1
+    constexpr int kColSplit = Cfg::kEpiWarps / 4;  // warps sharing a lane quarter
+    const int col_part = epi / 4;                  // which interleaved set of chunks is mine
+    uint8_t* stage_buf = staging + epi * (32 * kStageRowBytes);
     const int esize = p.out_fp32 ? 4 : 2;
     const int cols_per_chunk = 128 / esize;  // 32 (fp32) or 64 (fp16)
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int z = tile / tiles_mn;
+      const int rem_t = tile - z * tiles_mn;
+      const int n_blk = rem_t / p.m_tiles;
+      const int m0 = (rem_t - n_blk * p.m_tiles) * kBlockM;
+      int n0 = n_blk * BN;
+      int col_mem0 = n0;       // first memory column of this tile
+      int n_limit = p.N - n0;  // number of valid columns in this tile
+      if (MODE == WGRAD && !p.wg_flat) {
+        const int tap = n_blk / p.NCB;
+        n0 = (n_blk - tap * p.NCB) * BN;
+        col_mem0 = tap * p.Cn + n0;
+        n_limit = p.Cn - n0;
+      }
+      if (n_limit > BN) n_limit = BN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      const int row = m0 + quarter * 32 + lane;
+      long long row_off = row;
+      if (p.sc_P > 0) {
+        const int pq = p.sc_P * p.sc_Q;
+        const int n_img = row / pq;
+        const int rem = row - n_img * pq;
+        const int pp = rem / p.sc_Q;
+        const int qq = rem - pp * p.sc_Q;
+        row_off = (static_cast<long long>(n_img) * p.sc_H + p.sc_h0 +
+                   static_cast<long long>(pp) * p.sc_sh) *
+                      p.sc_W +
+                  p.sc_w0 + static_cast<long long>(qq) * p.sc_sw;
+      }
+      if (row >= p.M) row_off = -1;  // marks an invalid row
+      const long long base = static_cast<long long>(z) * p.split_stride + col_mem0;
+      mbar_wait(&tmem_full_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t tmem_acc = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
+      const int c_step = cols_per_chunk * kColSplit;
+      const int c_first = col_part * cols_per_chunk;
+      if (c_first >= n_limit || c_first >= BN) {
+        // nothing to read for this warp in this tile: release the accumulator right away
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+      }
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += cols_per_chunk) {
-      if (c0 >= n_limit) break;  // warp-uniform
-      // ---- registers <- TMEM, epilogue math, -> staging row of this thread ----
+      for (int c0 = c_first; c0 < BN; c0 += c_step) {
+        if (c0 >= n_limit) break;  // warp-uniform
+        const bool last_chunk = (c0 + c_step >= BN) || (c0 + c_step >= n_limit);
+        // ---- registers <- TMEM, epilogue math, -> staging row of this thread ----
 #pragma unroll 1
-      for (int h = 0; h < cols_per_chunk / 32; ++h) {
-        uint32_t v[32];
-        const int cc = c0 + h * 32;
-        if (my_kb > 0) {
-          tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cc, v);
+        for (int h = 0; h < cols_per_chunk / 32; ++h) {
+          uint32_t v[32];
+          const int cc = c0 + h * 32;
+          tmem_ld_32x32b_x32(tmem_acc + cc, v);
           tmem_ld_wait();
-        } else {
+          float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = 0u;
-        }
-        float f[32];
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if (p.bias != nullptr) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        if (p.bias != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (cc + j < n_limit) f[j] += __ldg(p.bias + n0 + cc + j);
-        }
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
-        }
-        uint8_t* srow = stage_buf + lane * kStageRowBytes;
-        if (p.out_fp32) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<float4*>(srow + j * 4) =
-                make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            uint4 u;
-            u.x = pack_half2(f[j], f[j + 1]);
-            u.y = pack_half2(f[j + 2], f[j + 3]);
-            u.z = pack_half2(f[j + 4], f[j + 5]);
-            u.w = pack_half2(f[j + 6], f[j + 7]);
-            *reinterpret_cast<uint4*>(srow + h * 64 + j * 2) = u;
+            for (int j = 0; j < 32; ++j)
+              if (cc + j < n_limit) f[j] += __ldg(p.bias + n0 + cc + j);
           }
-        }
-      }
-      __syncwarp();
-      // ---- staging -> global: lane handles 16-byte piece (lane % 8) of row it*4 + lane/8.
-      //      All old-value loads of an accumulate are issued before the first store so eight
-      //      requests per lane are in flight. ----
-      const int piece = lane & 7;
-      const int epp = 16 / esize;  // elements per piece
-      const int pcol = c0 + piece * epp;
-      const bool col_ok = pcol < n_limit;
-      const bool col_full = pcol + epp <= n_limit;
-      uint8_t* gps[8];
-      bool vec_ok[8], any_ok[8];
-      uint4 olds[8];
+          if (p.relu) {
 #pragma unroll
-      for (int it = 0; it < 8; ++it) {
-        const int r = it * 4 + (lane >> 3);
-        const long long ro = __shfl_sync(0xffffffffu, row_off, r);
-        gps[it] = reinterpret_cast<uint8_t*>(p.out) + (base + ro * p.ldc + pcol) * esize;
-        any_ok[it] = ro >= 0 && col_ok;
-        vec_ok[it] = any_ok[it] && col_full && ((reinterpret_cast<uintptr_t>(gps[it]) & 15) == 0);
-      }
-      if (p.accumulate) {
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+          }
+          uint8_t* srow = stage_buf + lane * kStageRowBytes;
+          if (p.out_fp32) {
 #pragma unroll
-        for (int it = 0; it < 8; ++it)
-          if (vec_ok[it]) olds[it] = *reinterpret_cast<const uint4*>(gps[it]);
-      }
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<float4*>(srow + j * 4) =
+                  make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+          } else {
 #pragma unroll
-      for (int it = 0; it < 8; ++it) {
-        if (!any_ok[it]) continue;
-        const int r = it * 4 + (lane >> 3);
-        uint4 val = *reinterpret_cast<const uint4*>(stage_buf + r * kStageRowBytes + piece * 16);
-        if (vec_ok[it]) {
-          if (p.accumulate) {
-            if (p.out_fp32) {
-              float4* v4 = reinterpret_cast<float4*>(&val);
-              const float4* o4 = reinterpret_cast<const float4*>(&olds[it]);
-              v4->x += o4->x; v4->y += o4->y; v4->z += o4->z; v4->w += o4->w;
-            } else {
-              __half2* a2 = reinterpret_cast<__half2*>(&val);
-              const __half2* o2 = reinterpret_cast<const __half2*>(&olds[it]);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float2 x = __half22float2(a2[j]), y = __half22float2(o2[j]);
-                a2[j] = __floats2half2_rn(x.x + y.x, x.y + y.y);
-              }
+            for (int j = 0; j < 32; j += 8) {
+              uint4 u;
+              u.x = pack_half2(f[j], f[j + 1]);
+              u.y = pack_half2(f[j + 2], f[j + 3]);
+              u.z = pack_half2(f[j + 4], f[j + 5]);
+              u.w = pack_half2(f[j + 6], f[j + 7]);
+              *reinterpret_cast<uint4*>(srow + h * 64 + j * 2) = u;
             }
           }
-          *reinterpret_cast<uint4*>(gps[it]) = val;
-        } else if (p.out_fp32) {
-          const float* e = reinterpret_cast<const float*>(&val);
-          float* go = reinterpret_cast<float*>(gps[it]);
-          for (int j = 0; j < 4; ++j)
-            if (pcol + j < n_limit) go[j] = p.accumulate ? go[j] + e[j] : e[j];
-        } else {
-          const __half* e = reinterpret_cast<const __half*>(&val);
-          __half* go = reinterpret_cast<__half*>(gps[it]);
-          for (int j = 0; j < 8; ++j)
-            if (pcol + j < n_limit)
-              go[j] = p.accumulate ? __float2half_rn(__half2float(go[j]) + __half2float(e[j]))
-                                   : e[j];
         }
+        if (last_chunk) {
+          // this warp has read everything it needs from the accumulator: hand it back to the
+          // MMA warp before the (slow) global stores
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        }
+        __syncwarp();
+        // ---- staging -> global: lane handles 16-byte piece (lane % 8) of row i8*4 + lane/8.
+        //      All old-value loads of an accumulate are issued before the first store so eight
+        //      requests per lane are in flight. ----
+        const int piece = lane & 7;
+        const int epp = 16 / esize;  // elements per piece
+        const int pcol = c0 + piece * epp;
+        const bool col_ok = pcol < n_limit;
+        const bool col_full = pcol + epp <= n_limit;
+        uint8_t* gps[8];
+        bool vec_ok[8], any_ok[8];
+        uint4 olds[8];
+#pragma unroll
+        for (int i8 = 0; i8 < 8; ++i8) {
+          const int r = i8 * 4 + (lane >> 3);
+          const long long ro = __shfl_sync(0xffffffffu, row_off, r);
+          gps[i8] = reinterpret_cast<uint8_t*>(p.out) + (base + ro * p.ldc + pcol) * esize;
+          any_ok[i8] = ro >= 0 && col_ok;
+          vec_ok[i8] =
+              any_ok[i8] && col_full && ((reinterpret_cast<uintptr_t>(gps[i8]) & 15) == 0);
+        }
+        if (p.accumulate) {
+#pragma unroll
+          for (int i8 = 0; i8 < 8; ++i8)
+            if (vec_ok[i8]) olds[i8] = *reinterpret_cast<const uint4*>(gps[i8]);
+        }
+#pragma unroll
+        for (int i8 = 0; i8 < 8; ++i8) {
+          if (!any_ok[i8]) continue;
+          const int r = i8 * 4 + (lane >> 3);
+          uint4 val = *reinterpret_cast<const uint4*>(stage_buf + r * kStageRowBytes + piece * 16);
+          if (vec_ok[i8]) {
+            if (p.accumulate) {
+              if (p.out_fp32) {
+                float4* v4 = reinterpret_cast<float4*>(&val);
+                const float4* o4 = reinterpret_cast<const float4*>(&olds[i8]);
+                v4->x += o4->x; v4->y += o4->y; v4->z += o4->z; v4->w += o4->w;
+              } else {
+                __half2* a2 = reinterpret_cast<__half2*>(&val);
+                const __half2* o2 = reinterpret_cast<const __half2*>(&olds[i8]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float2 x = __half22float2(a2[j]), y = __half22float2(o2[j]);
+                  a2[j] = __floats2half2_rn(x.x + y.x, x.y + y.y);
+                }
+              }
+            }
+            *reinterpret_cast<uint4*>(gps[i8]) = val;
+          } else if (p.out_fp32) {
+            const float* e = reinterpret_cast<const float*>(&val);
+            float* go = reinterpret_cast<float*>(gps[i8]);
+            for (int j = 0; j < 4; ++j)
+              if (pcol + j < n_limit) go[j] = p.accumulate ? go[j] + e[j] : e[j];
+          } else {
+            const __half* e = reinterpret_cast<const __half*>(&val);
+            __half* go = reinterpret_cast<__half*>(gps[i8]);
+            for (int j = 0; j < 8; ++j)
+              if (pcol + j < n_limit)
+                go[j] = p.accumulate ? __float2half_rn(__half2float(go[j]) + __half2float(e[j]))
+                                     : e[j];
+          }
+        }
+        __syncwarp();
       }
-      __syncwarp();
     }
   }
 
@@ -522,9 +611,20 @@ static int encode_im2col(CUtensorMap* m, const void* ptr, int N, int H, int W, i
   return 0;
 }
 
+static int g_sm_count = 0;
+static int sm_count() {
+  if (g_sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sm_count <= 0) g_sm_count = 148;
+  }
+  return g_sm_count;
+}
+
 template <int BN, int MODE>
-static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
-                      dim3 grid, cudaStream_t stream) {
+static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams p, dim3 tiles,
+                      cudaStream_t stream) {
   using Cfg = TileCfg<BN>;
   static bool attr_set[16] = {false};  // per device
   int dev = 0;
@@ -532,15 +632,18 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gemm
   if (dev < 16 && !attr_set[dev]) {
     KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        Cfg::smem_bytes(kMaxStages)));
-    KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE>,
-                                        cudaFuncAttributePreferredSharedMemoryCarveout,
-                                        cudaSharedmemCarveoutMaxShared));
+                                        Cfg::smem_bytes(Cfg::max_stages())));
     attr_set[dev] = true;
   }
-  KFB_REQUIRE(p.stages >= 1 && p.stages <= kMaxStages, "bad pipeline depth %d", p.stages);
-  gemm_tcgen05_kernel<BN, MODE><<<grid, kThreads, Cfg::smem_bytes(p.stages), stream>>>(tmA, tmB,
-                                                                                        p);
+  p.stages = Cfg::max_stages();
+  p.m_tiles = (int)tiles.x;
+  p.n_tiles = (int)tiles.y;
+  p.splits = (int)tiles.z;
+  const long long total = (long long)tiles.x * tiles.y * tiles.z;
+  KFB_REQUIRE(total > 0 && total < (1ll << 31), "bad tile count %lld", total);
+  const int ctas = total < sm_count() ? (int)total : sm_count();
+  gemm_tcgen05_kernel<BN, MODE><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
+      tmA, tmB, p);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -557,33 +660,23 @@ static int launch_mode(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, c
   return 2;
 }
 
-// Tile width and pipeline depth. Two goals: (a) at least two CTAs per SM so the epilogue of one
-// tile overlaps the main loop of another (TMEM: 512 columns per SM, shared memory: ~227 KB);
-// (b) for short-K (memory-bound) problems, narrower tiles and a shallow pipeline so three or
-// four CTAs fit and enough stores are in flight.
+// Tile width: the widest tile that covers N (wider tiles amortise the A-operand smem reads);
+// short-K, wide-N problems keep 128-wide tiles so more tiles exist to balance across SMs.
 static int pick_bn(int n) { return n <= 64 ? 64 : (n <= 128 ? 128 : 256); }
 static int pick_bn_for(int n, int num_kb) {
   int bn = pick_bn(n);
   if (num_kb <= 2 && bn == 256) bn = 128;
   return bn;
 }
-static int pick_stages(int bn, int kb_per_cta) {
-  int st = bn == 256 ? 2 : (bn == 128 ? 3 : 4);  // <= ~96 KB per CTA
-  if (kb_per_cta < st) st = kb_per_cta;
-  return st < 1 ? 1 : st;
-}
 
-static int g_sm_count = 0;
-static int sm_count() {
-  if (g_sm_count == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-    if (g_sm_count <= 0) g_sm_count = 148;
-  }
-  return g_sm_count;
+// Split count such that tiles * splits fills k whole rounds of the persistent grid (k = 2 when
+// possible): a partial last round would leave most SMs idle for a full tile time.
+static int balanced_splits(int tiles, int num_kb, int sms) {
+  int splits = (2 * sms) / tiles;
+  if (splits < 1) splits = 1;
+  if (splits > num_kb) splits = num_kb;
+  return splits < 1 ? 1 : splits;
 }
-
 static void init_params(GemmParams* p) { memset(p, 0, sizeof(*p)); }
 
 }  // namespace kfb
@@ -616,7 +709,6 @@ extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, 
   p.N = N;
   p.num_kb = (K + 63) / 64;
   p.kb_per_split = p.num_kb;
-  p.stages = pick_stages(bn, p.num_kb);
   p.out = C;
   p.ldc = ldc;
   p.bias = bias;
@@ -648,7 +740,6 @@ extern "C" int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, 
   p.N = N;
   p.num_kb = (K + 63) / 64;
   p.kb_per_split = p.num_kb;
-  p.stages = pick_stages(bn, p.num_kb);
   p.out = C;
   p.ldc = ldc;
   p.out_fp32 = out_fp32;
@@ -679,8 +770,7 @@ extern "C" int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N,
   p.N = N;
   p.num_kb = (K + 63) / 64;
   const int tiles = ((M + 127) / 128) * ((N + bn - 1) / bn);
-  int splits = (2 * sm_count() + tiles - 1) / tiles;
-  if (splits > p.num_kb) splits = p.num_kb;
+  int splits = balanced_splits(tiles, p.num_kb, sm_count() < 148 ? sm_count() : 148);
   const long long slice = (long long)M * N;
   long long max_splits = workspace_bytes / (slice * 4);
   if (splits > max_splits) splits = (int)max_splits;
@@ -688,7 +778,6 @@ extern "C" int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N,
               workspace_bytes, slice);
   p.kb_per_split = (p.num_kb + splits - 1) / splits;
   splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
-  p.stages = pick_stages(bn, p.kb_per_split);
   p.out = workspace;
   p.ldc = N;
   p.split_stride = slice;
@@ -743,7 +832,6 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   p.Ck = d->c;
   p.num_kb = d->r * d->s * p.CB;
   p.kb_per_split = p.num_kb;
-  p.stages = pick_stages(bn, p.num_kb);
   p.P = d->p;
   p.Q = d->q;
   p.lower_h = -d->pad_h_lo;
@@ -824,8 +912,7 @@ extern "C" int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void
       p.num_kb = nR * nS * p.CB;
       p.kb_per_split = p.num_kb;
       const int bn = pick_bn_for(d->c, p.num_kb);
-      p.stages = pick_stages(bn, p.num_kb);
-      p.P = Hp;
+          p.P = Hp;
       p.Q = Wp;
       p.lower_h = lower_h;
       p.lower_w = lower_w;
@@ -856,14 +943,36 @@ extern "C" int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void
   return 0;
 }
 
+// Tile plan of the weight-gradient GEMM. With C % 64 == 0 the N axis is the flattened
+// (tap, channel) axis, so one CTA covers several taps and re-uses its dy tile for all of them;
+// otherwise every n-tile belongs to one tap.
+static void wgrad_plan(const kfb_conv_desc* d, int* bn, int* n_tiles, int* flat, int* ncb) {
+  const int ntot = d->r * d->s * d->c;
+  if (d->c % 64 == 0) {
+    *flat = 1;
+    *bn = pick_bn(ntot);
+    *n_tiles = (ntot + *bn - 1) / *bn;
+    *ncb = 0;
+  } else {
+    *flat = 0;
+    *bn = pick_bn(d->c);
+    *ncb = (d->c + *bn - 1) / *bn;
+    *n_tiles = d->r * d->s * *ncb;
+  }
+}
+
+static int wgrad_splits(const kfb_conv_desc* d, int tiles, int num_kb, int sms) {
+  (void)d;
+  return balanced_splits(tiles, num_kb, sms);
+}
+
 extern "C" long long kfb_conv_wgrad_workspace_bytes(const kfb_conv_desc* d) {
-  // enough for the split count picked below (<= 2*SMs/tiles + 1 slices, at least 1)
   const long long slice = (long long)d->k * d->r * d->s * d->c * 4;
-  const int bn = pick_bn(d->c);
-  const int tiles = ((d->k + 127) / 128) * d->r * d->s * ((d->c + bn - 1) / bn);
-  int splits = (2 * 148 + tiles - 1) / tiles;
-  if (splits < 1) splits = 1;
-  return slice * splits;
+  int bn, n_tiles, flat, ncb;
+  wgrad_plan(d, &bn, &n_tiles, &flat, &ncb);
+  const int tiles = ((d->k + 127) / 128) * n_tiles;
+  const int num_kb = (d->n * d->p * d->q + 63) / 64;
+  return slice * wgrad_splits(d, tiles, num_kb, 148);  // never fewer SMs assumed than present
 }
 
 // dw[K,R,S,C] (fp32) (+)= scale * sum_pixels dy[pix,K]^T * im2col(x)[pix,(r,s,C)]
@@ -874,7 +983,8 @@ extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void*
   if (check_conv(d, "conv_wgrad")) return 2;
   if (load_driver_fns()) return 1;
   const int pixels = d->n * d->p * d->q;
-  const int bn = pick_bn(d->c);
+  int bn, n_tiles, flat, ncb;
+  wgrad_plan(d, &bn, &n_tiles, &flat, &ncb);
   CUtensorMap tmA, tmB;
   uint64_t da[2] = {(uint64_t)d->k, (uint64_t)pixels}, sa[1] = {(uint64_t)lddy * 2};
   uint32_t bx[2] = {64, 64};
@@ -891,7 +1001,8 @@ extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void*
   p.R = d->r;
   p.S = d->s;
   p.Cn = d->c;
-  p.NCB = (d->c + bn - 1) / bn;
+  p.NCB = ncb;
+  p.wg_flat = flat;
   p.num_kb = (pixels + 63) / 64;
   p.P = d->p;
   p.Q = d->q;
@@ -899,9 +1010,9 @@ extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void*
   p.lower_w = -d->pad_w_lo;
   p.stride_h = d->stride_h;
   p.stride_w = d->stride_w;
-  const int tiles = ((d->k + 127) / 128) * d->r * d->s * p.NCB;
-  int splits = (2 * sm_count() + tiles - 1) / tiles;
-  if (splits > p.num_kb) splits = p.num_kb;
+  const int m_tiles = (d->k + 127) / 128;
+  const int tiles = m_tiles * n_tiles;
+  int splits = wgrad_splits(d, tiles, p.num_kb, sm_count() < 148 ? sm_count() : 148);
   const long long slice = (long long)d->k * d->r * d->s * d->c;
   const long long max_splits = workspace_bytes / (slice * 4);
   if (splits > max_splits) splits = (int)max_splits;
@@ -909,12 +1020,11 @@ extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void*
               workspace_bytes, slice);
   p.kb_per_split = (p.num_kb + splits - 1) / splits;
   splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
-  p.stages = pick_stages(bn, p.kb_per_split);
   p.out = workspace;
   p.ldc = (long long)d->r * d->s * d->c;
   p.split_stride = slice;
   p.out_fp32 = 1;
-  dim3 grid((d->k + 127) / 128, d->r * d->s * p.NCB, splits);
+  dim3 grid(m_tiles, n_tiles, splits);
   if (launch_mode<WGRAD>(bn, tmA, tmB, p, grid, (cudaStream_t)stream)) return 1;
   const long long n4 = (slice + 3) / 4;
   splitk_reduce_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(

@@ -107,7 +107,7 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None
 def gemm_nt_workspace_bytes(m: int, n: int) -> int:
     bn = 64 if n <= 64 else (128 if n <= 128 else 256)
     tiles = ((m + 127) // 128) * ((n + bn - 1) // bn)
-    splits = max(1, (2 * 148 + tiles - 1) // tiles)
+    splits = max(1, (2 * 148) // tiles)
     return m * n * 4 * splits
 
 
