@@ -64,6 +64,9 @@ struct GemmParams {
   int stages;              // smem pipeline depth of this launch (1..kMaxStages)
   int m_tiles, n_tiles, splits;  // tile space walked by the persistent CTAs
   int wg_flat;             // WGRAD: N is the flattened (tap, channel) axis (C % 64 == 0)
+  // optional fused batch-norm statistics of the (fp16-rounded) output: per-column sum and sum
+  // of squares, accumulated per epilogue warp into stats[(cta * epi_warps + warp)][2][N]
+  float* stats;
   // optional row scatter (strided dgrad): row (n,i,j) -> (n, h0 + i*sh, w0 + j*sw) of H x W
   int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw, sc_h0, sc_w0;
   // DGRAD: filter tap visited at (r, s) of this launch's (sub-)filter
@@ -76,6 +79,7 @@ constexpr int kTileABytes = kBlockM * kBlockK * 2;  // 16 KiB
 constexpr int kMaxStages = 8;
 constexpr int kStageRowBytes = 144;                 // 128 B payload + 16 B pad (conflict free)
 constexpr int kSmemBudget = 227 * 1024;
+constexpr int kStatsRows = 148 * 8;  // (max CTAs) x (max epilogue warps) partial rows
 
 template <int BN>
 struct TileCfg {
@@ -333,11 +337,41 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     uint8_t* stage_buf = staging + epi * (32 * kStageRowBytes);
     const int esize = p.out_fp32 ? 4 : 2;
     const int cols_per_chunk = 128 / esize;  // 32 (fp32) or 64 (fp16)
+    // fused BN statistics: lane owns columns (2*lane, 2*lane+1) of each 64-wide chunk it handles
+    constexpr int kStatChunks = (BN / 64) / kColSplit > 0 ? (BN / 64) / kColSplit : 1;
+    float st_sum[kStatChunks][2], st_sq[kStatChunks][2];
+#pragma unroll
+    for (int c = 0; c < kStatChunks; ++c) st_sum[c][0] = st_sum[c][1] = st_sq[c][0] = st_sq[c][1] = 0.f;
+    int st_nblk = -1;
+    const bool do_stats = p.stats != nullptr && !p.out_fp32;
+    float* st_row = do_stats ? p.stats + static_cast<long long>(blockIdx.x * Cfg::kEpiWarps + epi) *
+                                             2 * p.N
+                             : nullptr;
+    auto flush_stats = [&](int nblk) {
+      // adds this warp's running sums of column block `nblk` into its private partial row
+#pragma unroll
+      for (int c = 0; c < kStatChunks; ++c) {
+        const int col = nblk * BN + (col_part + c * kColSplit) * 64 + 2 * lane;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          if (col + e < p.N) {
+            st_row[col + e] += st_sum[c][e];
+            st_row[p.N + col + e] += st_sq[c][e];
+          }
+          st_sum[c][e] = 0.f;
+          st_sq[c][e] = 0.f;
+        }
+      }
+    };
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int z = tile / tiles_mn;
       const int rem_t = tile - z * tiles_mn;
       const int n_blk = rem_t / p.m_tiles;
+      if (do_stats && n_blk != st_nblk) {
+        if (st_nblk >= 0) flush_stats(st_nblk);
+        st_nblk = n_blk;
+      }
       const int m0 = (rem_t - n_blk * p.m_tiles) * kBlockM;
       int n0 = n_blk * BN;
       int col_mem0 = n0;       // first memory column of this tile
@@ -424,6 +458,29 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
         }
         __syncwarp();
+        if (do_stats) {
+          // column sums of the staged (already fp16-rounded) 32 x 64 chunk; rows beyond M and
+          // columns beyond N hold exact zeros (zero-filled operands), so no masking is needed
+          const int sc = (c0 / 64 - col_part) / kColSplit;
+          float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+          for (int r = 0; r < 32; ++r) {
+            const float2 v = __half22float2(
+                *reinterpret_cast<const __half2*>(stage_buf + r * kStageRowBytes + lane * 4));
+            a0 += v.x;
+            a1 += v.y;
+            q0 = fmaf(v.x, v.x, q0);
+            q1 = fmaf(v.y, v.y, q1);
+          }
+#pragma unroll
+          for (int c = 0; c < kStatChunks; ++c)
+            if (c == sc) {
+              st_sum[c][0] += a0;
+              st_sum[c][1] += a1;
+              st_sq[c][0] += q0;
+              st_sq[c][1] += q1;
+            }
+        }
         // ---- staging -> global: lane handles 16-byte piece (lane % 8) of row i8*4 + lane/8.
         //      All old-value loads of an accumulate are issued before the first store so eight
         //      requests per lane are in flight. ----
@@ -488,6 +545,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         __syncwarp();
       }
     }
+    if (do_stats && st_nblk >= 0) flush_stats(st_nblk);
   }
 
   tc_fence_before();
@@ -642,6 +700,11 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   const long long total = (long long)tiles.x * tiles.y * tiles.z;
   KFB_REQUIRE(total > 0 && total < (1ll << 31), "bad tile count %lld", total);
   const int ctas = total < sm_count() ? (int)total : sm_count();
+  if (p.stats != nullptr) {
+    // partial rows [kStatsRows][2][N]; rows of CTAs / warps that do not exist stay zero
+    KFB_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, (size_t)kStatsRows * 2 * p.N * sizeof(float),
+                                   stream));
+  }
   gemm_tcgen05_kernel<BN, MODE><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
       tmA, tmB, p);
   KFB_CHECK_CUDA(cudaGetLastError());
@@ -688,9 +751,11 @@ using namespace kfb;
 // ===========================================================================
 extern "C" const char* kfb_last_error(void) { return kfb::g_err; }
 
+extern "C" int kfb_gemm_stats_rows(void) { return kStatsRows; }
+
 extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, int K,
                            long long lda, long long ldb, long long ldc, const float* bias,
-                           int relu, int out_fp32, void* stream) {
+                           int relu, int out_fp32, float* stats, void* stream) {
   KFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tn: bad shape %d %d %d", M, N, K);
   KFB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tn: lda/ldb must be multiples of 8 elements");
   if (load_driver_fns()) return 1;
@@ -714,6 +779,9 @@ extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, 
   p.bias = bias;
   p.relu = relu;
   p.out_fp32 = out_fp32;
+  p.stats = stats;
+  KFB_REQUIRE(stats == nullptr || (!out_fp32 && sm_count() <= 148),
+              "gemm_tn: fused statistics need fp16 output");
   dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);
   return launch_mode<GEMM_TN>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
 }
@@ -807,7 +875,8 @@ static int check_conv(const kfb_conv_desc* d, const char* who) {
 
 // y[N,P,Q,ldy>=K] = conv(x[N,H,W,C], w[K,R,S,C]) (+bias) (ReLU)
 extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void* w, void* y,
-                              long long ldy, const float* bias, int relu, void* stream) {
+                              long long ldy, const float* bias, int relu, float* stats,
+                              void* stream) {
   if (check_conv(d, "conv_fprop")) return 2;
   if (load_driver_fns()) return 1;
   const int M = d->n * d->p * d->q;
@@ -842,6 +911,8 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   p.ldc = ldy;
   p.bias = bias;
   p.relu = relu;
+  p.stats = stats;
+  KFB_REQUIRE(stats == nullptr || sm_count() <= 148, "conv_fprop: too many SMs for the stats rows");
   dim3 grid((M + 127) / 128, (d->k + bn - 1) / bn, 1);
   return launch_mode<FPROP>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
 }

@@ -59,7 +59,11 @@ __global__ void __launch_bounds__(kRedThreads)
   const int tv = threadIdx.x % cv_per_pass;
   const int tr = threadIdx.x / cv_per_pass;
   const long long rows_per_block = (rows + gridDim.x - 1) / gridDim.x;
-  const long long r_begin = blockIdx.x * rows_per_block;
+  // MODE 1 (BN backward): slabs are handed out last-to-first so the blocks scheduled first read
+  // the end of dy, which the producing dgrad wrote last (L2 reuse); the apply pass that follows
+  // runs first-to-last and finds the beginning fresh.
+  const long long slab = (MODE == 1) ? (gridDim.x - 1 - blockIdx.x) : blockIdx.x;
+  const long long r_begin = slab * rows_per_block;
   long long r_end = r_begin + rows_per_block;
   if (r_end > rows) r_end = rows;
 
@@ -187,7 +191,7 @@ __global__ void __launch_bounds__(kRedThreads)
           sb[i] += o[8 + i];
         }
       }
-      float* pa = partial + static_cast<long long>(blockIdx.x) * 2 * C + cv * 8;
+      float* pa = partial + static_cast<long long>(slab) * 2 * C + cv * 8;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         pa[i] = sa[i];
@@ -199,7 +203,7 @@ __global__ void __launch_bounds__(kRedThreads)
 
 // Folds the stage-1 partials of channel c in a fixed order. Block = (32 channels, 8 lanes):
 // lane ty sums blocks ty, ty+8, ... (coalesced 128-byte rows), then lane 0 adds the 8 lane sums.
-constexpr int kFoldLanes = 8;
+constexpr int kFoldLanes = 16;
 __device__ __forceinline__ bool fold_partials(const float* __restrict__ partial, int nblocks,
                                               int C, int c, float& s0, float& s1) {
   __shared__ float sh[2][kFoldLanes][32];
@@ -287,8 +291,11 @@ __global__ void __launch_bounds__(256)
     sh[0] = b0.x; sh[1] = b0.y; sh[2] = b0.z; sh[3] = b0.w;
     sh[4] = b1.x; sh[5] = b1.y; sh[6] = b1.z; sh[7] = b1.w;
   }
-  for (long long r = static_cast<long long>(blockIdx.y) * blockDim.y + threadIdx.y; r < rows;
-       r += static_cast<long long>(gridDim.y) * blockDim.y) {
+  for (long long rr = static_cast<long long>(blockIdx.y) * blockDim.y + threadIdx.y; rr < rows;
+       rr += static_cast<long long>(gridDim.y) * blockDim.y) {
+    // rows are visited last-to-first: the end of x was written most recently by the producing
+    // conv and is still in L2; the next conv then finds the beginning of y fresh
+    const long long r = rows - 1 - rr;
     float v[8];
     load8(x + r * ldx + cv * 8, v);
 #pragma unroll
@@ -994,14 +1001,17 @@ extern "C" int kfb_bn_forward_train(const void* x, long long ldx, long long rows
                                     const float* gamma, const float* beta, float* moving_mean,
                                     float* moving_var, float eps, float decay, int update_moving,
                                     float* mean_rstd, float* scale_shift, float* scratch,
-                                    const void* residual, long long ldr, int relu, void* y,
-                                    long long ldy, void* stream) {
+                                    int stats_nblocks, const void* residual, long long ldr,
+                                    int relu, void* y, long long ldy, void* stream) {
   KFB_REQ_C8(C, "bn_forward_train");
   cudaStream_t st = (cudaStream_t)stream;
-  const int nb = reduce_blocks(rows, C);
-  channel_reduce_kernel<0><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
-      (const __half*)x, ldx, nullptr, 0, nullptr, 0, nullptr, nullptr, nullptr, 0, rows, C,
-      scratch);
+  int nb = stats_nblocks;
+  if (nb <= 0) {
+    nb = reduce_blocks(rows, C);
+    channel_reduce_kernel<0><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
+        (const __half*)x, ldx, nullptr, 0, nullptr, 0, nullptr, nullptr, nullptr, 0, rows, C,
+        scratch);
+  }
   const float unbias = rows > 1 ? (float)((double)rows / (double)(rows - 1)) : 1.f;
   bn_finalize_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(
       scratch, nb, C, (float)(1.0 / (double)rows), unbias, eps, decay, gamma, beta, moving_mean,

@@ -35,7 +35,12 @@ typedef struct {
  * T/convnet_builder_legacy.py:318 (xw_plus_b) and 1x1 convolutions. */
 int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
                 long long ldb, long long ldc, const float* bias, int relu, int out_fp32,
-                void* stream);
+                float* stats, void* stream);
+/* `stats` (optional, fp16 output only): fused batch-norm statistics of the output. The kernel
+ * writes per-column partial sums / sums of squares as kfb_gemm_stats_rows() rows of [2][N]
+ * floats (zero-filled first), in the format kfb_bn_forward_train consumes when
+ * `stats_nblocks` > 0 - the separate statistics pass over the conv output disappears. */
+int kfb_gemm_stats_rows(void);
 
 /* C[M,N] (+)= A[M,K] * B[K,N]; B is consumed in place as an MN-major operand (FC dgrad). */
 int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
@@ -49,7 +54,7 @@ int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N, int K, lon
 
 /* y = conv(x, w) (+bias) (ReLU). T/convnet_builder_legacy.py:123-141. */
 int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void* w, void* y, long long ldy,
-                   const float* bias, int relu, void* stream);
+                   const float* bias, int relu, float* stats, void* stream);
 
 /* dx (+)= conv^T(dy, w) (autodiff of the above, T/benchmark_cnn.py:3104). Strided convolutions
  * run one launch per output phase. When kfb_conv_dgrad_needs_zero_fill(d) is non-zero some
@@ -76,12 +81,14 @@ int kfb_reduce_blocks(long long rows, int C);
 
 /* Training-mode batch norm fused with ReLU and residual add:
  * y = act(gamma * (x - mean) * rstd + beta (+ residual)); updates the moving statistics.
+ * stats_nblocks > 0: `scratch` already holds that many rows of [2][C] partial sums (written by
+ * the producing GEMM, see kfb_gemm_tn) and the statistics pass is skipped.
  * T/convnet_builder_legacy.py:393-459 (fused_batch_norm + assign_moving_average). */
 int kfb_bn_forward_train(const void* x, long long ldx, long long rows, int C, const float* gamma,
                          const float* beta, float* moving_mean, float* moving_var, float eps,
                          float decay, int update_moving, float* mean_rstd, float* scale_shift,
-                         float* scratch, const void* residual, long long ldr, int relu, void* y,
-                         long long ldy, void* stream);
+                         float* scratch, int stats_nblocks, const void* residual, long long ldr,
+                         int relu, void* y, long long ldy, void* stream);
 int kfb_bn_forward_inference(const void* x, long long ldx, long long rows, int C,
                              const float* gamma, const float* beta, const float* moving_mean,
                              const float* moving_var, float eps, float* scale_shift,

@@ -21,6 +21,7 @@ Design (B200-first, not a translation of the TF graph executor the reference lea
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Callable, Dict, List, Optional
 
 import torch
@@ -88,6 +89,9 @@ class CudaExecutor:
         # reductions / split-K scratch (sized below), loss outputs
         self._scratch_need = 0
         self._ws_need = 0
+        self._stats_rows = int(native.load().kfb_gemm_stats_rows())
+        self.fuse_stats_min_k = int(os.environ.get("KFB_FUSE_STATS_MIN_K", "1000000000"))
+        self._stats_for = None
         self.loss_rows = torch.zeros((2, n), dtype=torch.float32, device=dev)
         self.top = torch.zeros((4, n), dtype=torch.int32, device=dev)
         self.loss_out = torch.zeros((8,), dtype=torch.float32, device=dev)
@@ -215,6 +219,21 @@ class CudaExecutor:
             if a["activation"] == "tanh":
                 raise NotImplementedError("tanh epilogue is not built for the CUDA executor")
             self._need_scratch(node.output.rows, k)
+            # conv -> bn adjacency: the conv epilogue can produce the BN statistics
+            idx = self.graph.nodes.index(node)
+            nxt = self.graph.nodes[idx + 1] if idx + 1 < len(self.graph.nodes) else None
+            # Measured on B200 (profiles/README.md): fusing the statistics doubles the epilogue's
+            # instruction count and the epilogue warps are the bottleneck of the store-bound
+            # layers, while the separate statistics pass streams at ~70% of HBM bandwidth - the
+            # fused variant was 0.4-0.7% slower end to end at every K threshold tried, so it is
+            # off by default (KFB_FUSE_STATS_MIN_K=<K> enables it for reductions >= K).
+            k_reduction = a["kh"] * a["kw"] * c
+            info["fuse_stats"] = bool(
+                nxt is not None and nxt.op == "bn" and nxt.inputs[0] is node.output and
+                len(node.output.consumers) == 1 and not a["has_bias"] and
+                a["activation"] == "linear" and k_reduction >= self.fuse_stats_min_k)
+            if info["fuse_stats"]:
+                self._scratch_need = max(self._scratch_need, self._stats_rows * 2 * k)
         elif node.op == "bn":
             c = node.output.shape[-1]
             info["mean_rstd"] = torch.zeros((2 * c,), dtype=torch.float32, device=dev)
@@ -316,6 +335,8 @@ class CudaExecutor:
         relu = i32(1 if a["activation"] == "relu" else 0)
         d = info["desc"]
         kname = node.params["kernel"].name
+        # the batch-norm that immediately follows gets its statistics from the conv epilogue
+        stats = ptr(self.scratch) if (train and info.get("fuse_stats")) else None
         if info["flat"]:
             col = info["col"]
             native.call("im2col_small_c", x.p, ptr(col), i32(d.n), i32(d.h), i32(d.w), i32(d.c),
@@ -323,10 +344,11 @@ class CudaExecutor:
                         i32(d.pad_h_lo), i32(d.pad_w_lo), i32(info["kpad"]), s)
             native.call("gemm_tn", ptr(col), self._w16(kname), y.p, i32(y.rows), i32(d.k),
                         i32(info["kpad"]), i64(info["kpad"]), i64(info["kpad"]), i64(y.ld), bias,
-                        relu, i32(0), s)
+                        relu, i32(0), stats, s)
         else:
             native.call("conv_fprop", ctypes.byref(d), x.p, self._w16(kname), y.p, i64(y.ld),
-                        bias, relu, s)
+                        bias, relu, stats, s)
+        self._stats_for = node.output.id if stats is not None else None
 
     def _fwd_bn(self, node, train, s):
         info = self._per_node[id(node)]
@@ -339,9 +361,12 @@ class CudaExecutor:
         mv = ptr(self.store.view(node.params["moving_variance"].name))
         c = y.cols
         if train:
+            fused = self._stats_for == node.inputs[0].id
+            self._stats_for = None
             native.call("bn_forward_train", x.p, i64(x.ld), i64(x.rows), i32(c), gamma, beta, mm,
                         mv, f32(a["epsilon"]), f32(a["decay"]), i32(1), ptr(info["mean_rstd"]),
-                        ptr(info["scale_shift"]), ptr(self.scratch), res.p if res else None,
+                        ptr(info["scale_shift"]), ptr(self.scratch),
+                        i32(self._stats_rows if fused else 0), res.p if res else None,
                         i64(res.ld if res else 0), i32(int(a["relu"])), y.p, i64(y.ld), s)
         else:
             native.call("bn_forward_inference", x.p, i64(x.ld), i64(x.rows), i32(c), gamma, beta,
@@ -399,7 +424,7 @@ class CudaExecutor:
                     i32(spec.logical_cols), i64(x.ld), i64(in_pad), i64(y.ld),
                     self._w32(node.params["biases"].name),
                     i32(1 if a["activation"] == "relu" else 0),
-                    i32(int(y.t.dtype == torch.float32)), s)
+                    i32(int(y.t.dtype == torch.float32)), None, s)
 
     def _dropout_offset(self, node) -> int:
         idx = self.graph.nodes.index(node)

@@ -68,7 +68,8 @@ def _chk(t: torch.Tensor, dtype, name: str):
 
 def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None,
             relu: bool = False, out_dtype=torch.float16,
-            out: Optional[torch.Tensor] = None) -> torch.Tensor:
+            out: Optional[torch.Tensor] = None,
+            stats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``a[M,K] @ b[N,K].T`` (+bias) (ReLU)."""
     _chk(a, torch.float16, "a")
     _chk(b, torch.float16, "b")
@@ -79,7 +80,7 @@ def gemm_tn(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
         out = torch.empty((m, n), device=a.device, dtype=out_dtype)
     native.call("gemm_tn", ptr(a), ptr(b), ptr(out), i32(m), i32(n), i32(k), i64(a.stride(0)),
                 i64(b.stride(0)), i64(out.stride(0)), ptr(bias), i32(int(relu)),
-                i32(int(out.dtype == torch.float32)), stream_ptr())
+                i32(int(out.dtype == torch.float32)), ptr(stats), stream_ptr())
     return out
 
 
@@ -124,7 +125,11 @@ def get_workspace(device, nbytes: int) -> torch.Tensor:
     return ws
 
 
-def conv_fprop(x, w, d: ConvDesc, bias=None, relu=False, out=None, ldy=None):
+def stats_rows() -> int:
+    return int(native.load().kfb_gemm_stats_rows())
+
+
+def conv_fprop(x, w, d: ConvDesc, bias=None, relu=False, out=None, ldy=None, stats=None):
     _chk(x, torch.float16, "x")
     _chk(w, torch.float16, "w")
     if out is None:
@@ -133,7 +138,7 @@ def conv_fprop(x, w, d: ConvDesc, bias=None, relu=False, out=None, ldy=None):
     elif ldy is None:
         ldy = out.stride(-2)
     native.call("conv_fprop", ctypes.byref(d), ptr(x), ptr(w), ptr(out), i64(ldy), ptr(bias),
-                i32(int(relu)), stream_ptr())
+                i32(int(relu)), ptr(stats), stream_ptr())
     return out
 
 

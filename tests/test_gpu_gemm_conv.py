@@ -45,3 +45,21 @@ def test_accumulate_and_gemm_nn():
     g1 = gc.conv_wgrad(x, dy, d)
     g2 = gc.conv_wgrad(x, dy, d)
     assert torch.equal(g1, g2)
+
+
+def test_fused_bn_statistics_from_conv_epilogue():
+    import torch
+    from kf_benchmarks_b200.ops import gemm_conv as gc
+    g = torch.Generator(device="cuda").manual_seed(3)
+    for (n, h, c, k, r) in [(4, 28, 64, 256, 1), (3, 14, 128, 64, 3), (2, 9, 64, 320, 3)]:
+        x = torch.randn(n, h, h, c, device="cuda", generator=g).half()
+        w = (torch.randn(k, r, r, c, device="cuda", generator=g) * (r * r * c) ** -0.5).half()
+        pad = (r // 2, r // 2)
+        d = gc.make_desc(x.shape, w.shape, (1, 1), pad, pad)
+        stats = torch.full((gc.stats_rows(), 2, k), 7.0, device="cuda")
+        y = gc.conv_fprop(x, w, d, stats=stats)
+        torch.cuda.synchronize()
+        yf = y.float().reshape(-1, k)
+        tot = stats.sum(0)
+        assert torch.allclose(tot[0], yf.sum(0), atol=0.05, rtol=1e-3)
+        assert torch.allclose(tot[1], (yf * yf).sum(0), atol=0.05, rtol=1e-3)

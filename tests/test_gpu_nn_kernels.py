@@ -40,7 +40,7 @@ def test_bn_forward_backward(rows, c, relu, res, scale):
     scratch = _scratch(rows, c)
     native.call("bn_forward_train", ptr(x), i64(c), i64(rows), i32(c), ptr(gamma), ptr(beta),
                 ptr(mm), ptr(mv), f32(eps), f32(decay), i32(1), ptr(mean_rstd), ptr(ss),
-                ptr(scratch), ptr(r), i64(c), i32(int(relu)), ptr(y), i64(c), _s())
+                ptr(scratch), i32(0), ptr(r), i64(c), i32(int(relu)), ptr(y), i64(c), _s())
     # oracle
     xf = x.float().requires_grad_(True)
     gf = gamma.clone().requires_grad_(True) if scale else None
