@@ -97,6 +97,62 @@ __device__ __forceinline__ float apply_update(const HyperParams& h, float w, flo
   }
 }
 
+// Four consecutive elements at i (i % 4 == 0, all arenas 16-byte aligned).
+__device__ __forceinline__ void apply_update4(const HyperParams& h, float* __restrict__ w,
+                                              const float4 g4, float* m, float* v,
+                                              __half* __restrict__ w16, long long i,
+                                              const float4* blend_with, float blend_alpha) {
+  float4 w4 = *reinterpret_cast<const float4*>(w + i);
+  if (blend_with != nullptr) {
+    const float a = blend_alpha;
+    w4.x = (1.f - a) * w4.x + a * blend_with->x;
+    w4.y = (1.f - a) * w4.y + a * blend_with->y;
+    w4.z = (1.f - a) * w4.z + a * blend_with->z;
+    w4.w = (1.f - a) * w4.w + a * blend_with->w;
+  }
+  float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+  const float gv[4] = {g4.x, g4.y, g4.z, g4.w};
+  float mv[4] = {0.f, 0.f, 0.f, 0.f}, vv[4] = {0.f, 0.f, 0.f, 0.f};
+  if (h.opt != 0) {
+    const float4 t = *reinterpret_cast<const float4*>(m + i);
+    mv[0] = t.x; mv[1] = t.y; mv[2] = t.z; mv[3] = t.w;
+  }
+  if (h.opt >= 2) {
+    const float4 t = *reinterpret_cast<const float4*>(v + i);
+    vv[0] = t.x; vv[1] = t.y; vv[2] = t.z; vv[3] = t.w;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float g = gv[k] * h.grad_scale + h.weight_decay * wv[k];
+    if (h.clip > 0.f) g = fminf(fmaxf(g, -h.clip), h.clip);
+    if (h.opt == 0) {
+      wv[k] -= h.lr * g;
+    } else if (h.opt == 1) {
+      mv[k] = mv[k] * h.momentum + g;
+      wv[k] -= h.lr * (g + h.momentum * mv[k]);
+    } else if (h.opt == 2) {
+      vv[k] = h.decay * vv[k] + (1.f - h.decay) * g * g;
+      mv[k] = h.momentum * mv[k] + h.lr * g * rsqrtf(vv[k] + h.epsilon);
+      wv[k] -= mv[k];
+    } else {
+      const float b1 = h.momentum, b2 = h.decay;
+      mv[k] = b1 * mv[k] + (1.f - b1) * g;
+      vv[k] = b2 * vv[k] + (1.f - b2) * g * g;
+      const float lr_t = h.lr * sqrtf(1.f - __powf(b2, h.adam_t)) / (1.f - __powf(b1, h.adam_t));
+      wv[k] -= lr_t * mv[k] / (sqrtf(vv[k]) + h.epsilon);
+    }
+  }
+  *reinterpret_cast<float4*>(w + i) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+  if (h.opt != 0) *reinterpret_cast<float4*>(m + i) = make_float4(mv[0], mv[1], mv[2], mv[3]);
+  if (h.opt >= 2) *reinterpret_cast<float4*>(v + i) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+  if (w16 != nullptr) {
+    uint2 u;
+    u.x = pack_half2(wv[0], wv[1]);
+    u.y = pack_half2(wv[2], wv[3]);
+    *reinterpret_cast<uint2*>(w16 + i) = u;
+  }
+}
+
 // ---------------------------------------------------------------------------
 // Local fused optimizer over [0, n)
 // ---------------------------------------------------------------------------
@@ -107,8 +163,12 @@ __global__ void __launch_bounds__(256)
                           const int* __restrict__ skip_flag) {
   if (skip_flag != nullptr && *skip_flag != 0) return;
   resolve_dyn(h, dyn);
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  const long long n4 = n & ~3ll;
+  for (long long i = tid * 4; i < n4; i += nthreads * 4)
+    apply_update4(h, w, *reinterpret_cast<const float4*>(g + i), m, v, w16, i, nullptr, 0.f);
+  for (long long i = n4 + tid; i < n; i += nthreads) {
     const float nw = apply_update(h, w[i], g[i], m, v, i);
     w[i] = nw;
     if (w16 != nullptr) w16[i] = __float2half_rn(nw);
@@ -218,31 +278,51 @@ __global__ void __launch_bounds__(512)
   const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
   const float inv_n = 1.f / static_cast<float>(n);
-  for (long long i = s_begin + tid * 4; i < s_end; i += nthreads * 4) {
-    if (i + 4 <= s_end) {
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  // Two float4 per peer per thread are in flight before the first add (2 * n loads).
+  constexpr int kU = 2;
+  for (long long i0 = s_begin + tid * 4; i0 < s_end; i0 += nthreads * 4 * kU) {
+    float4 acc[kU];
+    bool ok[kU];
 #pragma unroll
-      for (int r = 0; r < kMaxRanks; ++r) {
-        if (r < n) {
-          const float4 x = *reinterpret_cast<const float4*>(c.src[r] + i);
-          acc.x += x.x;
-          acc.y += x.y;
-          acc.z += x.z;
-          acc.w += x.w;
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * nthreads * 4;
+      ok[u] = i + 4 <= s_end;
+      acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r) {
+      if (r < n) {
+        float4 x[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u)
+          if (ok[u]) x[u] = *reinterpret_cast<const float4*>(c.src[r] + i0 + u * nthreads * 4);
+#pragma unroll
+        for (int u = 0; u < kU; ++u)
+          if (ok[u]) {
+            acc[u].x += x[u].x;
+            acc[u].y += x[u].y;
+            acc[u].z += x[u].z;
+            acc[u].w += x[u].w;
+          }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * nthreads * 4;
+      if (ok[u]) {
+        if (MODE == 1) {
+          acc[u].x *= inv_n; acc[u].y *= inv_n; acc[u].z *= inv_n; acc[u].w *= inv_n;
         }
-      }
-      if (MODE == 1) {
-        acc.x *= inv_n; acc.y *= inv_n; acc.z *= inv_n; acc.w *= inv_n;
-      }
 #pragma unroll
-      for (int r = 0; r < kMaxRanks; ++r)
-        if (r < n) *reinterpret_cast<float4*>(c.reduced[r] + i) = acc;
-    } else {
-      for (long long j = i; j < s_end; ++j) {
-        float acc = 0.f;
-        for (int r = 0; r < n; ++r) acc += c.src[r][j];
-        if (MODE == 1) acc *= inv_n;
-        for (int r = 0; r < n; ++r) c.reduced[r][j] = acc;
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < n) *reinterpret_cast<float4*>(c.reduced[r] + i) = acc[u];
+      } else if (i < s_end) {
+        for (long long j = i; j < s_end; ++j) {
+          float a1 = 0.f;
+          for (int r = 0; r < n; ++r) a1 += c.src[r][j];
+          if (MODE == 1) a1 *= inv_n;
+          for (int r = 0; r < n; ++r) c.reduced[r][j] = a1;
+        }
       }
     }
   }
@@ -253,12 +333,23 @@ __global__ void __launch_bounds__(512)
   const bool skip = (skip_flag != nullptr && *skip_flag != 0);
   if (!skip) {
     const float* red = c.reduced[c.rank];
-    for (long long i = offset + tid; i < offset + count; i += nthreads) {
+    const long long end = offset + count;
+    const long long end4 = offset + (count & ~3ll);  // offset is a multiple of 4
+    for (long long i = offset + tid * 4; i < end4; i += nthreads * 4) {
+      const float4 r4 = *reinterpret_cast<const float4*>(red + i);
+      if (MODE == 0) {
+        apply_update4(h, w, r4, m, v, w16, i, nullptr, 0.f);
+      } else {
+        // SMA: w <- (1-a) w + a * avg(w); then the local gradient step
+        apply_update4(h, w, *reinterpret_cast<const float4*>(g_local + i), m, v, w16, i, &r4,
+                      sma_alpha);
+      }
+    }
+    for (long long i = end4 + tid; i < end; i += nthreads) {
       float nw;
       if (MODE == 0) {
         nw = apply_update(h, w[i], red[i], m, v, i);
       } else {
-        // SMA: w <- (1-a) w + a * avg(w); then the local gradient step
         const float blended = (1.f - sma_alpha) * w[i] + sma_alpha * red[i];
         nw = apply_update(h, blended, g_local[i], m, v, i);
       }
@@ -451,8 +542,11 @@ extern "C" int kfb_allreduce_update(int mode, int rank, int nranks, void* const*
   KFB_REQUIRE(offset % 4 == 0, "allreduce_update: offset must be a multiple of 4 floats");
   PeerCtx c;
   if (fill_peer_ctx(&c, rank, nranks, src, reduced, flags)) return 2;
-  if (blocks <= 0) blocks = 32;
-  if (blocks > 128) blocks = 128;
+  if (blocks <= 0) {
+    // enough CTAs to keep the links busy, few enough to leave SMs to the backward kernels
+    blocks = count >= (4ll << 20) ? 96 : (count >= (1ll << 20) ? 64 : 32);
+  }
+  if (blocks > 148) blocks = 148;
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 0)
     allreduce_update_kernel<0><<<blocks, 512, 0, st>>>(c, offset, count, seq, w, g_local, m, v,

@@ -39,7 +39,7 @@ def main():
     torch.cuda.set_device(dev)
     comm = P2PComm(dev)
     ok = True
-    n = 3_000_064
+    n = int(os.environ.get("KFB_P2P_N", "3000064"))
     grad = comm.symm_alloc(n, torch.float32)
     w = comm.symm_alloc(n, torch.float32)
     red = comm.symm_alloc(n, torch.float32)
@@ -65,7 +65,7 @@ def main():
         grad.copy_(rank_data(rank, n, 10 + step))
         comm.barrier()
         h = make_hyper(1, scale=1.0 / 128)
-        for lo, hi in [(0, 1_000_064), (1_000_064, 2_500_096), (2_500_096, n)]:
+        for lo, hi in [(0, 1_000_064), (1_000_064, 2_500_096), (2_500_096, n)] if n == 3000064 else [(0, n)]:
             native.call("allreduce_update", i32(0), i32(rank), i32(world), gp, rp, fp, i64(lo),
                         i64(hi - lo), ctypes.c_uint(comm.next_seq()), ptr(w), ptr(grad), ptr(m),
                         None, ptr(w16), ctypes.byref(h), None, None, f32(0.0), i32(0), s)
@@ -131,7 +131,7 @@ def main():
     ok &= good
     comm.barrier()
     # ---- 6. all-reduce micro timing ----
-    if True:
+    for blocks in [int(b) for b in os.environ.get("KFB_AR_BLOCKS_SWEEP", "0").split(",")]:
         reps = 20
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         h = make_hyper(1, scale=1.0)
@@ -140,15 +140,15 @@ def main():
         for _ in range(reps):
             native.call("allreduce_update", i32(0), i32(rank), i32(world), gp, rp, fp, i64(0),
                         i64(n), ctypes.c_uint(comm.next_seq()), ptr(w), ptr(grad), ptr(m), None,
-                        ptr(w16), ctypes.byref(h), None, None, f32(0.0), i32(0), s)
+                        ptr(w16), ctypes.byref(h), None, None, f32(0.0), i32(blocks), s)
         e1.record()
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / reps
         us = comm.max_over_ranks(us)
         if rank == 0:
             link = 2.0 * (world - 1) / world * n * 4 / (us * 1e-6) / 1e9
-            print("allreduce_update %.1f MB fp32 on %d ranks: %.1f us  (%.1f GB/s per-GPU link "
-                  "traffic)" % (n * 4 / 1e6, world, us, link), flush=True)
+            print("allreduce_update %.1f MB fp32 on %d ranks, %d blocks: %.1f us  (%.1f GB/s "
+                  "per-GPU link traffic)" % (n * 4 / 1e6, world, blocks, us, link), flush=True)
     allok = all(comm.allgather_object(bool(ok)))
     if rank == 0:
         print("P2P_CHECK %s" % ("ALL PASS" if allok else "FAILED"), flush=True)
