@@ -191,6 +191,8 @@ def _standin_arm(args, torch) -> int:
             "dtype": "fp16 autocast", "data": "synthetic",
             "config": {"model": args.model, "global_batch": gb,
                        "variable_update": args.variable_update, "optimizer": args.optimizer,
+                       "kungfu_option": args.kungfu_option if args.variable_update == "kungfu"
+                       else "",
                        "note": "PyTorch cuDNN/cuBLAS + NCCL stand-in (not the reference)"},
             "final_loss": float(tr.last_loss)}))
     if world > 1:
@@ -280,6 +282,8 @@ def main() -> int:
                        "image_size": bench.model.image_size,
                        "parallelism": "dp%d" % n_ranks,
                        "variable_update": args.variable_update, "optimizer": args.optimizer,
+                       "kungfu_option": args.kungfu_option if args.variable_update == "kungfu"
+                       else "",
                        "comm_impl": args.comm_impl if n_ranks > 1 else "none",
                        "l2_hygiene": "per-step working set (>5 GB activations) exceeds the "
                                      "126 MB L2; no explicit flush",
