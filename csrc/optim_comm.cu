@@ -357,10 +357,9 @@ __global__ void __launch_bounds__(512)
       if (w16 != nullptr) w16[i] = __float2half_rn(nw);
     }
   }
-  // --- done: peers may overwrite their sources / my landing buffer only after everyone is
-  //     through phase 2 (SMA reads w as a source in the next call) ---
-  grid_arrive_and_signal(c, FLAG_DONE, seq, 1);
-  wait_flags(c, FLAG_DONE, seq);
+  // No trailing barrier: a peer can only touch this range again (write my landing buffer, read
+  // my gradients or weights) after it has seen my READY flag of the NEXT call on this range,
+  // and that flag is sent by a later launch on this stream, i.e. after this kernel has ended.
 }
 
 // Pull `count` floats at `offset` from rank `root`'s arena into mine (+ fp16 shadow).

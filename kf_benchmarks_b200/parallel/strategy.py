@@ -114,7 +114,9 @@ class UpdateEngine:
         self.auto_loss_scale = bool(params.use_fp16 and params.fp16_enable_auto_loss_scale)
         self.loss_scale_normal_steps = 0
         self.skipped_steps = 0
-        bucket_elems = max(int(params.bucket_bytes) // 4, 128)
+        # bucket size: --bucket_bytes, but never more than ~12 buckets for very large models (each
+        # bucket costs two flag rounds across the ranks)
+        bucket_elems = max(int(params.bucket_bytes) // 4, n // 12, 128)
         self.buckets = plan_buckets(n, bucket_elems, params.gradient_repacking)
         self._ready_hi = 0
         self._launched = 0
@@ -223,6 +225,10 @@ class UpdateEngine:
         elif algo == "pair":
             self._pair_update()
         else:
+            if self._launched == 0 and not self._can_overlap():
+                # nothing was overlapped (SMA, auto loss scale, micro-benchmark): one launch
+                self._launch_bucket((0, self.total), overlapped=False)
+                self._launched = len(self.buckets)
             while self._launched < len(self.buckets):
                 self._launch_bucket(self.buckets[self._launched], overlapped=self._can_overlap())
                 self._launched += 1
