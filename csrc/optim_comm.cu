@@ -262,7 +262,7 @@ __global__ void __launch_bounds__(512)
                             float* __restrict__ m, float* __restrict__ v,
                             __half* __restrict__ w16, HyperParams h,
                             const float* __restrict__ dyn, const int* __restrict__ skip_flag,
-                            float sma_alpha) {
+                            float sma_alpha, int reduce_only) {
   resolve_dyn(h, dyn);
   const int n = c.nranks;
   // --- announce: my source data for [offset, offset+count) is final ---
@@ -330,7 +330,7 @@ __global__ void __launch_bounds__(512)
   wait_flags(c, FLAG_REDUCED, seq);
 
   // --- phase 2: every rank applies the identical update to its full replica ---
-  const bool skip = (skip_flag != nullptr && *skip_flag != 0);
+  const bool skip = (skip_flag != nullptr && *skip_flag != 0) || reduce_only;
   if (!skip) {
     const float* red = c.reduced[c.rank];
     const long long end = offset + count;
@@ -547,14 +547,16 @@ extern "C" int kfb_allreduce_update(int mode, int rank, int nranks, void* const*
   }
   if (blocks > 148) blocks = 148;
   cudaStream_t st = (cudaStream_t)stream;
-  if (mode == 0)
-    allreduce_update_kernel<0><<<blocks, 512, 0, st>>>(c, offset, count, seq, w, g_local, m, v,
-                                                       (__half*)w16, make_hyper(hp), dyn,
-                                                       skip_flag, sma_alpha);
-  else
+  // mode 2: reduce only - the sum lands in every rank's `reduced` buffer and is applied later
+  // (variable_consistency=relaxed: one-step-stale gradients, T/batch_allreduce.py:353-388)
+  if (mode == 1)
     allreduce_update_kernel<1><<<blocks, 512, 0, st>>>(c, offset, count, seq, w, g_local, m, v,
                                                        (__half*)w16, make_hyper(hp), dyn,
-                                                       skip_flag, sma_alpha);
+                                                       skip_flag, sma_alpha, 0);
+  else
+    allreduce_update_kernel<0><<<blocks, 512, 0, st>>>(c, offset, count, seq, w, g_local, m, v,
+                                                       (__half*)w16, make_hyper(hp), dyn,
+                                                       skip_flag, sma_alpha, mode == 2 ? 1 : 0);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

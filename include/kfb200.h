@@ -192,8 +192,9 @@ int kfb_check_finite(const float* g, long long n, int* flag, void* stream);
 int kfb_loss_scale_update(float* state, int* flag, int inc_every, float* dyn,
                           float base_grad_scale, void* stream);
 
-/* Two-shot P2P all-reduce over mapped peer arenas fused with the optimizer (mode 0), or
- * SynchronousAveraging of the model (mode 1). src / reduced / flags are host arrays of
+/* Two-shot P2P all-reduce over mapped peer arenas fused with the optimizer (mode 0),
+ * SynchronousAveraging of the model (mode 1), or reduce-only into `reduced` (mode 2, used by
+ * variable_consistency=relaxed where the sum is applied one step later). src / reduced / flags are host arrays of
  * nranks device pointers (peer mappings); seq must increase by one per collective call and
  * be identical on every rank. */
 int kfb_flag_page_bytes(void);

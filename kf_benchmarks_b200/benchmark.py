@@ -351,6 +351,7 @@ class BenchmarkCNN:
             return
         lr = eng.learning_rate(self.global_step, self._examples_per_step(),
                                self.dataset.num_examples_per_epoch("train"))
+        self._last_lr = lr
         eng.begin_step(lr)
         ex.loss_backward(loss_scale=eng.loss_scale, on_grads_ready=eng.on_grads_ready)
         eng.finish_step()
@@ -371,6 +372,8 @@ class BenchmarkCNN:
         if p.tfprof_file or p.trace_file:
             from .utils import profile as profile_lib
             profiler = profile_lib.StepProfiler(p, self.device)
+        from .utils.summaries import SummaryWriter
+        summaries = SummaryWriter(p, p.train_dir) if rank0 else None
         if rank0:
             _log("Running warm up")
         step_train_times: List[float] = []
@@ -427,6 +430,11 @@ class BenchmarkCNN:
                     _log(log_util.step_line(
                         step1, self.batch_size, step_train_times, loss,
                         t1 / n if accuracy_cols else None, t5 / n if accuracy_cols else None))
+            if summaries is not None and summaries.path is not None and \
+                    self.global_step % max(summaries.every, 1) == 0:
+                loss_s = self._reported_loss(self.executor.read_loss()[0])
+                summaries.maybe_write(self.global_step, getattr(self, "_last_lr", 0.0), loss_s,
+                                      self.engine, self.store)
             if p.save_model_steps and step1 % p.save_model_steps == 0:
                 self._save()
             elif p.save_model_secs and time.time() - last_save_time >= p.save_model_secs:

@@ -186,6 +186,11 @@ class UpdateEngine:
     def begin_step(self, lr: float) -> None:
         """Called before backward: arms the overlap scheduler."""
         self._h = self._hyper(lr)
+        if self.relaxed and self.cuda and getattr(self, "_relaxed_pending", False) and \
+                isinstance(self.comm, P2PComm):
+            # the deferred all-reduce reads the gradient arena: it must be done before this
+            # step's backward starts overwriting it (it had the whole forward pass to finish)
+            torch.cuda.current_stream(self.device).wait_event(self.done_event)
         self._ready_hi = 0
         self._launched = 0
         if self.cuda and self.auto_loss_scale:
@@ -218,6 +223,10 @@ class UpdateEngine:
         algo = self._effective_algo()
         if self.auto_loss_scale:
             self._check_finite()
+        if self.relaxed and algo == "allreduce":
+            self._finish_relaxed()
+            self.step_count += 1
+            return
         if not self.cuda or isinstance(self.comm, TorchDistComm):
             self._finish_torch(algo)
         elif algo == "none":
@@ -238,6 +247,38 @@ class UpdateEngine:
         if self.auto_loss_scale:
             self._update_loss_scale()
         self.step_count += 1
+
+    def _finish_relaxed(self) -> None:
+        """variable_consistency=relaxed (T/batch_allreduce.py:353-388): apply the all-reduced
+        gradients of the PREVIOUS step now, then start reducing this step's gradients so the
+        exchange overlaps the next forward pass."""
+        st, c = self.store, self.comm
+        if isinstance(c, P2PComm):
+            if getattr(self, "_relaxed_pending", False):
+                native.call("optimizer_step", ptr(st.w32), ptr(self.reduced), ptr(self.m),
+                            ptr(self.v), ptr(st.w16), i64(self.total), ctypes.byref(self._h), None,
+                            None, self._s())
+            self.ready_event.record(torch.cuda.current_stream(self.device))
+            c.comm_stream.wait_event(self.ready_event)
+            native.call("allreduce_update", i32(2), i32(c.rank), i32(c.size), self._grad_ptrs,
+                        self._red_ptrs, self._flag_ptrs, i64(0), i64(self.total),
+                        ctypes.c_uint(c.next_seq()), ptr(st.w32), ptr(st.grad), ptr(self.m),
+                        ptr(self.v), ptr(st.w16), ctypes.byref(self._h), None, None, f32(0.0),
+                        i32(0), self._s(c.comm_stream))
+            self.done_event.record(c.comm_stream)
+            self._relaxed_pending = True
+        else:
+            prev = getattr(self, "_relaxed_prev", None)
+            if prev is not None:
+                if self.cuda:
+                    native.call("optimizer_step", ptr(st.w32), ptr(prev), ptr(self.m),
+                                ptr(self.v), ptr(st.w16), i64(self.total), ctypes.byref(self._h),
+                                None, None, self._s())
+                else:
+                    optim_ref.apply_update(self._h, st.w32, prev, self.m, self.v, st.w16)
+            cur = st.grad.clone()
+            c.all_reduce_(cur)
+            self._relaxed_prev = cur
 
     # ------------------------------------------------------------------ CUDA paths
     def _s(self, stream=None):

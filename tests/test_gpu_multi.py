@@ -37,6 +37,8 @@ def test_p2p_kernels_match_host_simulation():
     ["--variable_update=kungfu", "--kungfu_option=sync_sgd"],
     ["--variable_update=kungfu", "--kungfu_option=sma"],
     ["--variable_update=kungfu", "--kungfu_option=async_sgd"],
+    ["--variable_update=replicated", "--num_gpus=2", "--variable_consistency=relaxed"],
+    ["--variable_update=parameter_server", "--num_gpus=2", "--fp16_enable_auto_loss_scale"],
 ])
 def test_two_gpu_training_modes_run(mode):
     args = ["-m", "kf_benchmarks_b200.cli", "--model=resnet20", "--data_name=cifar10",

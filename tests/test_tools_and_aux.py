@@ -65,3 +65,19 @@ def test_cli_entry_point_and_help():
     res = subprocess.run([sys.executable, "-m", "kf_benchmarks_b200.cli", "--model", "trivial",
                           "stray"], cwd=ROOT, env=env, capture_output=True, text=True, timeout=60)
     assert res.returncode == 2 and "positional" in res.stderr
+
+
+def test_summaries_jsonl(tmp_path):
+    kw = dict(model="trivial", data_name="cifar10", device="cpu", data_format="NHWC", batch_size=4,
+              num_batches=4, num_warmup_batches=0, train_dir=str(tmp_path), summary_verbosity=3,
+              save_summaries_steps=2)
+    old = log_util.log_fn
+    log_util.log_fn = lambda s: None
+    try:
+        benchmark.BenchmarkCNN(benchmark.setup(P.make_params(**kw))).run()
+    finally:
+        log_util.log_fn = old
+    recs = [json.loads(l) for l in open(os.path.join(str(tmp_path), "summaries.jsonl"))]
+    assert [r["step"] for r in recs] == [2, 4]
+    assert "learning_rate" in recs[0] and "log_gradients" in recs[0]
+    assert "cg/affine0/weights" in recs[0]["variables"]

@@ -198,3 +198,24 @@ def test_forward_only_and_loss_reporting():
     b2, s2, _ = _run_single(dict(BASE, loss_type_to_report="total_loss", num_batches=1))
     l2 = 0.5 * float((b2.store.w32.double() ** 2).sum()) * BASE["weight_decay"]
     assert s2["last_average_loss"] == pytest.approx(s1["last_average_loss"] + l2, rel=1e-4)
+
+
+def test_relaxed_consistency_applies_gradients_one_step_late(tmp_path):
+    """variable_consistency=relaxed (T/benchmark_cnn_test.py:1368-1476: the result lags one
+    step): after K steps the variables equal a strong run's after K-1 updates computed from
+    gradients taken at the stale weights - checked with an explicit re-simulation."""
+    kw = dict(BASE, variable_update="replicated", num_gpus=2, optimizer="sgd",
+              variable_consistency="relaxed", num_batches=3)
+    results = _spawn(kw, 2, tmp_path)
+    sim = _Sim(dict(kw, variable_consistency="strong"), 2)
+    pending = None
+    for k in range(3):
+        h = sim.engine._hyper(kw["init_learning_rate"])
+        h.grad_scale = 1.0
+        gs = [sim.grads(r) for r in range(2)]
+        if pending is not None:
+            for r in range(2):
+                optim_ref.apply_update(h, sim.stores[r].w32, pending, None, None)
+        pending = sum(gs)
+    for r in range(2):
+        assert np.allclose(results[r]["w"], sim.stores[r].w32.numpy(), rtol=2e-5, atol=2e-6)
