@@ -334,8 +334,49 @@ class BenchmarkCNN:
                 out[suffix] = self.store.opt_slots[key]
         return out
 
+    def _graph_eligible(self) -> bool:
+        """--cuda_graph: the whole step (forward, loss, backward, fused update) is captured once
+        and replayed. Limited to a single rank with device-resident inputs: the P2P kernels take
+        a per-call sequence number that a replay could not advance."""
+        return (self.params.cuda_graph and self.device.type == "cuda" and self.world <= 1 and
+                not getattr(self.input_source, "host_resident", False) and
+                not self.engine.auto_loss_scale)
+
+    def _step_graphed(self) -> None:
+        ex, eng = self.executor, self.engine
+        lr = eng.learning_rate(self.global_step, self._examples_per_step(),
+                               self.dataset.num_examples_per_epoch("train"))
+        if getattr(self, "_graph", None) is None:
+            eng.enable_dynamic_hyper()
+            ex.set_inputs(*self.input_source.next_batch())
+            self._graph_warm = getattr(self, "_graph_warm", 0) + 1
+            eng.push_dynamic_hyper(lr)
+            if self._graph_warm <= 2:            # eager steps: lazy inits happen outside capture
+                self._last_lr = lr
+                eng.begin_step(lr)
+                ex.forward(True)
+                ex.loss_backward(loss_scale=eng.loss_scale, on_grads_ready=eng.on_grads_ready)
+                eng.finish_step()
+                self.global_step += 1
+                return
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                eng.begin_step(lr)
+                ex.forward(True)
+                ex.loss_backward(loss_scale=eng.loss_scale, on_grads_ready=eng.on_grads_ready)
+                eng.finish_step()
+            self._graph = g
+            _log("Captured the training step in a CUDA graph")
+        eng.push_dynamic_hyper(lr)
+        self._last_lr = lr
+        self._graph.replay()
+        self.global_step += 1
+
     def _step(self, train: bool = True, backward: bool = True) -> None:
         """One step on this rank: inputs -> forward -> loss/backward -> exchange + update."""
+        if train and backward and self._graph_eligible():
+            return self._step_graphed()
         ex, eng = self.executor, self.engine
         src = self.input_source
         prefetch = getattr(src, "host_resident", False) and hasattr(ex, "stage_inputs")

@@ -124,6 +124,10 @@ class UpdateEngine:
         self.relaxed = params.variable_consistency == "relaxed"
         if self.cuda:
             self.skip_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        # device-resident {lr, grad_scale, adam_t, -}: lets a captured CUDA graph see per-step
+        # values (the kernels read it instead of the by-value fields when given)
+        self.dyn = None
+        self._dyn_host = None
         self._setup_comm_buffers()
 
     # ------------------------------------------------------------------ setup
@@ -182,6 +186,16 @@ class UpdateEngine:
         h.clip = p.gradient_clip if p.gradient_clip else 0.0
         h.adam_t = float(self.step_count + 1)
         return h
+
+    def enable_dynamic_hyper(self) -> None:
+        self.dyn = torch.zeros(4, dtype=torch.float32, device=self.device)
+        self._dyn_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+
+    def push_dynamic_hyper(self, lr: float) -> None:
+        """Uploads this step's learning rate / gradient scale / Adam step for graph replay."""
+        h = self._hyper(lr)
+        self._dyn_host[0], self._dyn_host[1], self._dyn_host[2] = h.lr, h.grad_scale, h.adam_t
+        self.dyn.copy_(self._dyn_host, non_blocking=True)
 
     def begin_step(self, lr: float) -> None:
         """Called before backward: arms the overlap scheduler."""
@@ -293,7 +307,7 @@ class UpdateEngine:
         st = self.store
         native.call("optimizer_step", self._ptr_at(st.w32, lo), self._ptr_at(st.grad, lo),
                     self._ptr_at(self.m, lo), self._ptr_at(self.v, lo), self._ptr_at(st.w16, lo),
-                    i64(hi - lo), ctypes.byref(self._h), None,
+                    i64(hi - lo), ctypes.byref(self._h), ptr(self.dyn),
                     ptr(self.skip_flag) if self.auto_loss_scale else None, self._s())
 
     def _launch_bucket(self, bucket, overlapped: bool) -> None:

@@ -94,3 +94,23 @@ def test_optimizer_kernel_matches_reference_rules():
     native.call("loss_scale_update", ptr(state), ptr(flag), native.i32(1000), ptr(dyn),
                 native.f32(1.0), native.stream_ptr())
     assert state.tolist() == [64.0, 0.0] and float(dyn[1]) == pytest.approx(1 / 64)
+
+
+def test_cuda_graph_step_matches_eager():
+    """--cuda_graph replays the captured step; variables must match the eager run exactly."""
+    from kf_benchmarks_b200 import benchmark, params as P
+    from kf_benchmarks_b200.utils import log_util
+    finals = []
+    for graph in (False, True):
+        old = log_util.log_fn
+        log_util.log_fn = lambda s: None
+        try:
+            p = P.make_params(model="resnet20", data_name="cifar10", batch_size=32, use_fp16=True,
+                              optimizer="momentum", num_batches=8, num_warmup_batches=0,
+                              cuda_graph=graph, variable_update="replicated")
+            b = benchmark.BenchmarkCNN(benchmark.setup(p))
+            b.run()
+        finally:
+            log_util.log_fn = old
+        finals.append(b.store.w32.clone())
+    assert torch.equal(finals[0], finals[1])
