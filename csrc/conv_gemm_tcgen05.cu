@@ -102,7 +102,9 @@ struct TileCfg {
 // Three pipelines run concurrently: TMA -> smem ring (full/empty mbarriers), MMA -> TMEM
 // accumulator pair (tmem_full/tmem_empty), and the epilogue draining accumulator `a` while the
 // MMA warp already fills accumulator `a^1` for the next tile.
-template <int BN, int MODE>
+// FAST = every output piece is a full, 16-byte aligned vector (all conv layers): the scalar
+// fallbacks are compiled out, which shrinks the kernel below the instruction-cache size.
+template <int BN, int MODE, bool FAST>
 __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                         const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
@@ -426,7 +428,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           if (p.bias != nullptr) {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
-              if (cc + j < n_limit) f[j] += __ldg(p.bias + n0 + cc + j);
+              if (FAST || cc + j < n_limit) f[j] += __ldg(p.bias + n0 + cc + j);
           }
           if (p.relu) {
 #pragma unroll
@@ -498,8 +500,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           const long long ro = __shfl_sync(0xffffffffu, row_off, r);
           gps[i8] = reinterpret_cast<uint8_t*>(p.out) + (base + ro * p.ldc + pcol) * esize;
           any_ok[i8] = ro >= 0 && col_ok;
-          vec_ok[i8] =
-              any_ok[i8] && col_full && ((reinterpret_cast<uintptr_t>(gps[i8]) & 15) == 0);
+          vec_ok[i8] = FAST ? any_ok[i8]
+                            : (any_ok[i8] && col_full &&
+                               ((reinterpret_cast<uintptr_t>(gps[i8]) & 15) == 0));
         }
         if (p.accumulate) {
 #pragma unroll
@@ -528,6 +531,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
               }
             }
             *reinterpret_cast<uint4*>(gps[i8]) = val;
+          } else if (FAST) {
+            // unreachable: FAST launches only see full aligned pieces
           } else if (p.out_fp32) {
             const float* e = reinterpret_cast<const float*>(&val);
             float* go = reinterpret_cast<float*>(gps[i8]);
@@ -688,11 +693,21 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   int dev = 0;
   KFB_CHECK_CUDA(cudaGetDevice(&dev));
   if (dev < 16 && !attr_set[dev]) {
-    KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE>,
+    KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE, false>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::smem_bytes(Cfg::max_stages())));
+    KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE, true>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         Cfg::smem_bytes(Cfg::max_stages())));
     attr_set[dev] = true;
   }
+  // every 16-byte piece of the output is full and aligned?
+  const int esz = p.out_fp32 ? 4 : 2;
+  const int epp = 16 / esz;
+  const int n_valid = (MODE == WGRAD && !p.wg_flat) ? p.Cn : p.N;
+  const bool fast = (n_valid % epp == 0) && (p.ldc % epp == 0) && (p.split_stride % epp == 0) &&
+                    ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0) &&
+                    (MODE != WGRAD || p.wg_flat || (p.Cn % epp == 0));
   p.stages = Cfg::max_stages();
   p.m_tiles = (int)tiles.x;
   p.n_tiles = (int)tiles.y;
@@ -705,8 +720,12 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
     KFB_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, (size_t)kStatsRows * 2 * p.N * sizeof(float),
                                    stream));
   }
-  gemm_tcgen05_kernel<BN, MODE><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
-      tmA, tmB, p);
+  if (fast)
+    gemm_tcgen05_kernel<BN, MODE, true><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
+        tmA, tmB, p);
+  else
+    gemm_tcgen05_kernel<BN, MODE, false><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
+        tmA, tmB, p);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
