@@ -334,6 +334,18 @@ class BenchmarkCNN:
                 out[suffix] = self.store.opt_slots[key]
         return out
 
+    def _maybe_inject_fault(self) -> None:
+        """Test hook: KFB_FAULT_INJECT="<rank>:<global_step>:<exit|hang>" makes
+        one rank die or stall at a step so the launcher's kill-the-group path can be exercised."""
+        spec = os.environ.get("KFB_FAULT_INJECT")
+        if not spec:
+            return
+        rank, step, kind = spec.split(":")
+        if int(rank) == self.rank and int(step) == self.global_step:
+            if kind == "exit":
+                os._exit(17)
+            time.sleep(10 ** 6)
+
     def _graph_eligible(self) -> bool:
         """--cuda_graph: the whole step (forward, loss, backward, fused update) is captured once
         and replayed. Limited to a single rank with device-resident inputs: the P2P kernels take
@@ -375,6 +387,7 @@ class BenchmarkCNN:
 
     def _step(self, train: bool = True, backward: bool = True) -> None:
         """One step on this rank: inputs -> forward -> loss/backward -> exchange + update."""
+        self._maybe_inject_fault()
         if train and backward and self._graph_eligible():
             return self._step_graphed()
         ex, eng = self.executor, self.engine

@@ -39,6 +39,7 @@ def test_p2p_kernels_match_host_simulation():
     ["--variable_update=kungfu", "--kungfu_option=async_sgd"],
     ["--variable_update=replicated", "--num_gpus=2", "--variable_consistency=relaxed"],
     ["--variable_update=parameter_server", "--num_gpus=2", "--fp16_enable_auto_loss_scale"],
+    ["--variable_update=replicated", "--num_gpus=2", "--comm_impl=nccl"],   # comparison baseline
 ])
 def test_two_gpu_training_modes_run(mode):
     args = ["-m", "kf_benchmarks_b200.cli", "--model=resnet20", "--data_name=cifar10",
@@ -50,3 +51,26 @@ def test_two_gpu_training_modes_run(mode):
     losses = [float(l.split("\t")[-1]) for l in res.stdout.splitlines()
               if "images/sec:" in l and l[0].isdigit()]
     assert losses and all(x == x and x < 20 for x in losses), res.stdout[-2000:]
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+def test_replicas_stay_bit_identical_and_match_nccl_baseline(tmp_path):
+    """Synchronous modes keep every replica's variables bit-identical, and the fused P2P path
+    lands on (numerically) the same variables as the NCCL + separate-update baseline."""
+    import json
+    import numpy as np
+    outs = {}
+    for impl in ("p2p", "nccl"):
+        d = tmp_path / impl
+        d.mkdir()
+        kw = dict(model="resnet20", data_name="cifar10", batch_size=32, use_fp16=True,
+                  optimizer="momentum", init_learning_rate=0.05, num_batches=6,
+                  num_warmup_batches=0, variable_update="replicated", num_gpus=2, comm_impl=impl)
+        res = _launch(2, [os.path.join(ROOT, "tests", "helpers", "rank_worker.py"), json.dumps(kw),
+                          str(d)])
+        assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+        outs[impl] = [np.load(str(d / ("rank%d.npz" % r)))["w"] for r in range(2)]
+        assert np.array_equal(outs[impl][0], outs[impl][1])
+    a, b = outs["p2p"][0], outs["nccl"][0]
+    cos = float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b)))
+    assert cos > 0.9999 and np.abs(a - b).max() < 5e-2

@@ -81,3 +81,37 @@ def test_summaries_jsonl(tmp_path):
     assert [r["step"] for r in recs] == [2, 4]
     assert "learning_rate" in recs[0] and "log_gradients" in recs[0]
     assert "cg/affine0/weights" in recs[0]["variables"]
+
+
+def test_launcher_kills_group_when_a_rank_dies(tmp_path):
+    """One rank exits at step 1: the launcher reports it, stops the survivor (which would
+    otherwise wait forever in the all-reduce) and returns the failing exit code."""
+    import time
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2", KFB_FAULT_INJECT="1:1:exit")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    cmd = [sys.executable, "-m", "kf_benchmarks_b200.cli", "--model=trivial", "--data_name=cifar10",
+           "--device=cpu", "--data_format=NHWC", "--batch_size=4", "--num_batches=50",
+           "--num_warmup_batches=0", "--num_gpus=2", "--variable_update=replicated"]
+    t0 = time.time()
+    res = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=240)
+    assert res.returncode == 17, (res.returncode, res.stderr[-500:])
+    assert "rank 1 exited with 17" in res.stderr
+    assert time.time() - t0 < 200
+
+
+def test_export_tool_lists_reference_names(tmp_path):
+    kw = dict(model="trivial", data_name="cifar10", device="cpu", data_format="NHWC", batch_size=4,
+              num_batches=1, num_warmup_batches=0, train_dir=str(tmp_path), optimizer="momentum")
+    old = log_util.log_fn
+    log_util.log_fn = lambda s: None
+    try:
+        benchmark.BenchmarkCNN(benchmark.setup(P.make_params(**kw))).run()
+    finally:
+        log_util.log_fn = old
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "export_tf_checkpoint.py"),
+                          "--list", os.path.join(str(tmp_path), "model.ckpt-1.npz")],
+                         capture_output=True, text=True, timeout=60)
+    assert res.returncode == 0
+    assert "v0/cg/affine0/weights" in res.stdout and "v0/cg/affine0/weights/Momentum" in res.stdout
+    assert "global_step" in res.stdout
