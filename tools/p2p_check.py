@@ -149,6 +149,33 @@ def main():
             link = 2.0 * (world - 1) / world * n * 4 / (us * 1e-6) / 1e9
             print("allreduce_update %.1f MB fp32 on %d ranks, %d blocks: %.1f us  (%.1f GB/s "
                   "per-GPU link traffic)" % (n * 4 / 1e6, world, blocks, us, link), flush=True)
+    # ---- 7. protocol stress: many back-to-back calls on random bucket partitions; replicas must
+    #         stay bit-identical and match the host model ----
+    iters = int(os.environ.get("KFB_P2P_STRESS", "200"))
+    import random
+    rng = random.Random(4242)  # same partition sequence on every rank
+    m.zero_()
+    w.copy_(rank_data(99, n, 50))
+    grad.copy_(rank_data(rank, n, 51))
+    comm.barrier()
+    h = make_hyper(0, lr=1e-3, scale=1.0, wd=0.0)
+    for it in range(iters):
+        cuts = sorted({0, n} | {rng.randrange(0, n // 128) * 128 for _ in range(rng.randint(0, 4))})
+        for lo, hi in zip(cuts[:-1], cuts[1:]):
+            native.call("allreduce_update", i32(0), i32(rank), i32(world), gp, rp, fp, i64(lo),
+                        i64(hi - lo), ctypes.c_uint(comm.next_seq()), ptr(w), ptr(grad), None,
+                        None, ptr(w16), ctypes.byref(h), None, None, f32(0.0),
+                        i32(rng.choice([0, 8, 33, 148])), s)
+    torch.cuda.synchronize()
+    gsum = sum(rank_data(r, n, 51) for r in range(world))
+    want = rank_data(99, n, 50) - iters * 1e-3 * gsum
+    check("stress: %d iterations" % iters, w, want, 2e-4)
+    mine = w.cpu()
+    all_w = comm.allgather_object(mine[:: max(n // 65536, 1)].clone())
+    same = all(torch.equal(all_w[0], x) for x in all_w)
+    ok &= same
+    print("[rank %d] %s stress: replicas bit-identical" % (rank, "PASS" if same else "FAIL"),
+          flush=True)
     allok = all(comm.allgather_object(bool(ok)))
     if rank == 0:
         print("P2P_CHECK %s" % ("ALL PASS" if allok else "FAILED"), flush=True)
