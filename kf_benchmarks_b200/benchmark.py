@@ -254,6 +254,11 @@ class BenchmarkCNN:
         self.nclass = nclass
         self.graph = self.model.build_graph(nclass, phase_train=phase_train,
                                             batch_size=self.batch_size_per_device)
+        if self.device.type == "cuda":
+            # odd channel counts (DenseNet k=12, NASNet, SSD heads) get zero phantom channels so
+            # every tensor meets the 16-byte granularity of the TMA / vectorised kernels
+            from .nn.legalize import legalize
+            self.graph = legalize(self.graph)
         self.comm = comm_lib.create_comm(p, self.device)
         self.store = ParameterStore(self.graph, self.device,
                                     fp16_shadow=self.device.type == "cuda",

@@ -32,6 +32,10 @@ class ParamSpec:
                                         # ("glorot_uniform", fan_in, fan_out)
     logical_cols: Optional[int] = None  # conv_kernel_flat: R*S*C before padding to a multiple of 8
     conv_rsc: Optional[Tuple[int, int, int]] = None
+    # channel legalisation (nn/legalize.py): physical position of each logical input channel
+    # (or of each element, for per-channel vectors) and the padded output-channel count
+    in_map: Optional[Tuple[int, ...]] = None
+    out_pad: Optional[int] = None
 
     @property
     def numel(self) -> int:
@@ -101,8 +105,12 @@ class Graph:
 
     # -- statistics ---------------------------------------------------------
     def num_trainable(self) -> int:
-        return sum(p.numel if p.logical_cols is None else p.shape[0] * p.logical_cols
-                   for p in self.params.values() if p.trainable)
+        def logical(p):
+            n = 1
+            for d in p.tf_shape:
+                n *= d
+            return n
+        return sum(logical(p) for p in self.params.values() if p.trainable)
 
     def trainable_params(self) -> List[ParamSpec]:
         return [p for p in self.params.values() if p.trainable]

@@ -123,11 +123,14 @@ class ParameterStore:
             self.w16.copy_(self.w32)
 
     # -- TF-layout import / export ------------------------------------------------
-    def to_tf_arrays(self, prefix: str = "v0/") -> Dict[str, np.ndarray]:
-        """{tf variable name: ndarray in the reference's layout}."""
+    def to_tf_arrays(self, prefix: str = "v0/", which: str = "w32") -> Dict[str, np.ndarray]:
+        """{tf variable name: ndarray in the reference's layout}. ``which``
+        selects the arena ("w32" weights, "grad" gradients of the trainable variables)."""
         out = {}
         for p in self.graph.params.values():
-            t = self.view(p.name).detach().float().cpu()
+            if which != "w32" and not p.trainable:
+                continue
+            t = self.view(p.name, which).detach().float().cpu()
             out[prefix + p.name] = _native_to_tf(p, t).numpy()
         return out
 
@@ -179,26 +182,60 @@ def _init_value(p: ParamSpec, gen) -> torch.Tensor:
 
 def _tf_to_native(p: ParamSpec, t: torch.Tensor) -> torch.Tensor:
     if p.kind == "conv_kernel":            # HWIO -> OHWI
-        return t.permute(3, 0, 1, 2).contiguous()
+        v = t.permute(3, 0, 1, 2).contiguous()
+        if p.in_map is None and p.out_pad is None:
+            return v
+        out = torch.zeros(p.shape, dtype=t.dtype)
+        if p.in_map is None:
+            out[:v.shape[0]] = v
+        else:
+            out[:v.shape[0], :, :, list(p.in_map)] = v
+        return out
     if p.kind == "conv_kernel_flat":       # HWIO -> [O, pad(H*W*I)]
         o = t.shape[3]
         flat = t.permute(3, 0, 1, 2).reshape(o, -1)
         out = torch.zeros(p.shape, dtype=t.dtype)
-        out[:, :flat.shape[1]] = flat
+        out[:o, :flat.shape[1]] = flat
+        return out
+    if p.kind == "dw_kernel":              # [H, W, C, 1] -> [H, W, Cphys]
+        v = t[..., 0]
+        if p.in_map is None:
+            return v.contiguous()
+        out = torch.zeros(p.shape, dtype=t.dtype)
+        out[:, :, list(p.in_map)] = v
         return out
     if p.kind == "fc_weight":              # [in, out] -> [out, pad(in)]
         out = torch.zeros(p.shape, dtype=t.dtype)
-        out[:, :t.shape[0]] = t.t()
+        if p.in_map is None:
+            out[:, :t.shape[0]] = t.t()
+        else:
+            out[:, list(p.in_map)] = t.t()
+        return out
+    if p.in_map is not None:               # per-channel vector on a padded layout
+        out = torch.zeros(p.shape, dtype=t.dtype)
+        out[list(p.in_map)] = t
         return out
     return t.contiguous()
 
 
 def _native_to_tf(p: ParamSpec, t: torch.Tensor) -> torch.Tensor:
     if p.kind == "conv_kernel":
-        return t.permute(1, 2, 3, 0).contiguous()
+        k = p.tf_shape[3]
+        if p.in_map is not None:
+            t = t[:, :, :, list(p.in_map)]
+        return t[:k].permute(1, 2, 3, 0).contiguous()
     if p.kind == "conv_kernel_flat":
         r, s, c = p.conv_rsc
-        return t[:, :r * s * c].reshape(t.shape[0], r, s, c).permute(1, 2, 3, 0).contiguous()
+        k = p.tf_shape[3]
+        return t[:k, :r * s * c].reshape(k, r, s, c).permute(1, 2, 3, 0).contiguous()
+    if p.kind == "dw_kernel":
+        if p.in_map is not None:
+            t = t[:, :, list(p.in_map)]
+        return t.unsqueeze(-1).contiguous()
     if p.kind == "fc_weight":
+        if p.in_map is not None:
+            return t[:, list(p.in_map)].t().contiguous()
         return t[:, :p.tf_shape[0]].t().contiguous()
+    if p.in_map is not None:
+        return t[list(p.in_map)].contiguous()
     return t.contiguous()

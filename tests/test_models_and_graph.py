@@ -106,3 +106,39 @@ def test_arena_layout_is_backward_completion_order():
     assert offs == sorted(offs) and all(o % 128 == 0 for o in offs)
     lo, hi = st.span(["cg/affine0/biases", "cg/affine0/weights"])
     assert lo == 0 and hi == st.slots[order[2]].offset
+
+
+def test_channel_legalization_is_transparent():
+    """DenseNet's growth rate 12 gets zero phantom channels for the CUDA executor; the padded
+    graph computes the same loss and the same logical gradients, and the phantom lanes of every
+    gradient are exactly zero."""
+    import numpy as np
+    import torch
+    from kf_benchmarks_b200.nn.executor_ref import RefExecutor
+    from kf_benchmarks_b200.nn.legalize import legalize, needs_legalization
+
+    _, g = _graph("densenet40_k12", "cifar10", batch=2)
+    assert needs_legalization(g)
+    pg = legalize(g)
+    assert not needs_legalization(pg) and pg.num_trainable() == g.num_trainable()
+    _, r50 = _graph("resnet50")
+    assert legalize(r50) is r50                       # mainstream models are untouched
+    st = ParameterStore(g, "cpu", fp16_shadow=False)
+    st.initialize(7)
+    pst = ParameterStore(pg, "cpu", fp16_shadow=False)
+    pst.from_tf_arrays(st.to_tf_arrays())
+    gen = torch.Generator().manual_seed(0)
+    img = torch.randn(2, 32, 32, 3, generator=gen)
+    lab = torch.randint(0, 10, (2,), generator=gen)
+    res = []
+    for gg, ss in ((g, st), (pg, pst)):
+        ex = RefExecutor(gg, ss, 11)
+        ex.set_inputs(img, lab)
+        ex.forward(True)
+        ex.loss_backward(1.0)
+        res.append((ex.read_loss()[0], ss.to_tf_arrays(which="grad")))
+    assert abs(res[0][0] - res[1][0]) < 1e-5
+    for k, a in res[0][1].items():
+        assert np.abs(a - res[1][1][k]).max() <= 1e-4 * np.abs(a).max() + 1e-6, k
+    logical = sum(float(np.abs(v).sum()) for v in res[1][1].values())
+    assert abs(float(pst.grad.abs().sum()) - logical) <= 1e-4 * logical

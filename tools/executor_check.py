@@ -29,7 +29,8 @@ def compare(model_name, data_name, batch, image_size=None, seed=0, verbose=False
     if image_size:
         model.image_size = image_size
     nclass = ds.num_classes
-    g = model.build_graph(nclass, batch_size=batch)
+    from kf_benchmarks_b200.nn.legalize import legalize
+    g = legalize(model.build_graph(nclass, batch_size=batch))
     dev = torch.device("cuda")
     st_gpu = ParameterStore(g, dev)
     st_gpu.initialize(1234)
