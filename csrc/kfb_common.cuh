@@ -228,4 +228,25 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// 8 halves <-> 8 floats through one 16-byte access (the unit of the NHWC elementwise kernels)
+struct alignas(16) Half8 {
+  __half2 h[4];
+};
+
+__device__ __forceinline__ void load8(const __half* p, float (&f)[8]) {
+  const Half8 v = *reinterpret_cast<const Half8*>(p);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __half22float2(v.h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ void store8(__half* p, const float (&f)[8]) {
+  Half8 v;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v.h[i] = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+  *reinterpret_cast<Half8*>(p) = v;
+}
+
 }  // namespace kfb

@@ -224,6 +224,31 @@ int kfb_ipc_open(const void* handle, void** out);
 int kfb_ipc_close(void* p);
 int kfb_enable_peer_access(int peer_device);
 
+/* ---- wider model zoo (csrc/extra_ops.cu) ------------------------------------------------ */
+/* Activations on NHWC fp16 rows. kind: 1 relu, 2 relu6 (MobileNet-v2,
+ * T/models/mobilenet_v2.py:42-82), 3 tanh, 4 sigmoid. Backward reads the stored output y. */
+int kfb_act_forward(const void* x, long long ldx, void* y, long long ldy, long long rows, int C,
+                    int kind, void* stream);
+int kfb_act_backward(const void* dy, long long lddy, const void* y, long long ldy, void* dx,
+                     long long lddx, int accumulate, long long rows, int C, int kind,
+                     void* stream);
+/* Depthwise convolution, channel multiplier 1 (slim.separable_conv2d with num_outputs=None,
+ * T/models/mobilenet_conv_blocks.py:246-256; the depthwise half of NASNet's separable convs,
+ * T/models/nasnet_utils.py:212-260). d->k must equal d->c; w is [R][S][C] fp16, dw fp32. */
+int kfb_dwconv_fprop(const kfb_conv_desc* d, const void* x, long long ldx, const void* w, void* y,
+                     long long ldy, void* stream);
+int kfb_dwconv_dgrad(const kfb_conv_desc* d, const void* dy, long long lddy, const void* w,
+                     void* dx, long long lddx, int accumulate, void* stream);
+long long kfb_dwconv_wgrad_workspace_bytes(const kfb_conv_desc* d);
+int kfb_dwconv_wgrad(const kfb_conv_desc* d, const void* x, long long ldx, const void* dy,
+                     long long lddy, float* dw, void* workspace, long long workspace_bytes,
+                     int accumulate, float scale, void* stream);
+/* Per-sample drop-path (T/models/nasnet_utils.py:113-138): y (+)= x * (u_n < keep ? 1/keep : 0)
+ * with u_n a pure function of (seed, offset, sample); the same call replays it for dy. */
+int kfb_drop_path(const void* x, long long ldx, void* y, long long ldy, int accumulate,
+                  long long rows, long long rows_per_sample, int C, float keep_prob,
+                  unsigned long long seed, unsigned long long offset, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,7 +5,7 @@ from __future__ import annotations
 from functools import partial
 
 from . import (alexnet_model, densenet_model, googlenet_model, inception_model, lenet_model,
-               overfeat_model, resnet_model, trivial_model, vgg_model)
+               mobilenet_v2, official_resnet_model, overfeat_model, resnet_model, trivial_model, vgg_model)
 
 _model_name_to_imagenet_model = {
     "vgg11": vgg_model.Vgg11Model,
@@ -18,8 +18,10 @@ _model_name_to_imagenet_model = {
     "trivial": trivial_model.TrivialModel,
     "inception3": inception_model.Inceptionv3Model,
     "inception4": inception_model.Inceptionv4Model,
+    "mobilenet": mobilenet_v2.MobilenetModel,
 }
 _model_name_to_imagenet_model.update(resnet_model.imagenet_factories())
+_model_name_to_imagenet_model.update(official_resnet_model.factories())
 
 _model_name_to_cifar_model = {
     "alexnet": alexnet_model.AlexnetCifar10Model,
@@ -33,15 +35,11 @@ _model_name_to_cifar_model.update(resnet_model.cifar_factories())
 # Models of the reference that need external repositories / datasets the fork itself
 # disabled. They resolve to a clear error instead of an import failure.
 _UNSUPPORTED = {
-    "mobilenet": "slim-based MobileNet-v2 (depthwise kernels not built)",
     "nasnet": "slim-based NASNet", "nasnetlarge": "slim-based NASNet",
     "ssd300": "needs COCO + the object_detection package",
     "deepspeech2": "needs LibriSpeech; LSTM/CTC kernels not built",
     "ncf": "needs the official NCF package",
 }
-for _d in (18, 34, 50, 101, 152, 200):
-    _UNSUPPORTED["official_resnet%d" % _d] = "needs the tensorflow/models official.resnet package"
-    _UNSUPPORTED["official_resnet%d_v2" % _d] = _UNSUPPORTED["official_resnet%d" % _d]
 
 
 def _get_model_map(dataset_name):

@@ -89,8 +89,11 @@ class NetBuilder:
     # -- layers ---------------------------------------------------------------
     def conv(self, num_out_channels, k_height, k_width, d_height=1, d_width=1, mode="SAME",
              input_layer=None, num_channels_in=None, use_batch_norm=None, stddev=None,
-             activation="relu", bias=0.0, kernel_initializer=None) -> TensorRef:
-        """T/convnet_builder_legacy.py:143-226."""
+             activation="relu", bias=0.0, kernel_initializer=None, scope_name=None,
+             kernel_leaf="conv2d/kernel", bias_leaf="biases", bn_scope_name=None) -> TensorRef:
+        """T/convnet_builder_legacy.py:143-226. ``scope_name`` / ``*_leaf`` override the
+        variable names for the slim-style models (MobilenetV2/Conv/weights ...); activation
+        "relu6" is accepted for those."""
         if input_layer is None:
             input_layer = self.top_layer
         if num_channels_in is None:
@@ -100,8 +103,11 @@ class NetBuilder:
         n, h, w, c = input_layer.shape
         if c != num_channels_in:
             raise ValueError(f"conv: input has {c} channels, num_channels_in={num_channels_in}")
-        name = "conv" + str(self.counts["conv"])
-        self.counts["conv"] += 1
+        if scope_name is None:
+            name = "conv" + str(self.counts["conv"])
+            self.counts["conv"] += 1
+        else:
+            name = scope_name
         if use_batch_norm is None:
             use_batch_norm = self.use_batch_norm
         pad_h = resolve_padding(mode, h, k_height, d_height)
@@ -120,46 +126,91 @@ class NetBuilder:
             params = {}
             tf_shape = (k_height, k_width, c, num_out_channels)
             if c % 8 == 0:
-                params["kernel"] = ParamSpec(self._full("conv2d/kernel"),
+                params["kernel"] = ParamSpec(self._full(kernel_leaf),
                                              (num_out_channels, k_height, k_width, c), tf_shape,
                                              "conv_kernel", True, init)
             else:
                 # tiny-C stem: filters stored as rows of an explicit-im2col GEMM, K padded to 8
                 kpad = (fan_in + 7) // 8 * 8
-                params["kernel"] = ParamSpec(self._full("conv2d/kernel"),
+                params["kernel"] = ParamSpec(self._full(kernel_leaf),
                                              (num_out_channels, kpad), tf_shape,
                                              "conv_kernel_flat", True, init, logical_cols=fan_in,
                                              conv_rsc=(k_height, k_width, c))
             has_bias = (not use_batch_norm) and bias is not None
             if has_bias:
-                params["biases"] = ParamSpec(self._full("biases"), (num_out_channels,),
+                params["biases"] = ParamSpec(self._full(bias_leaf), (num_out_channels,),
                                              (num_out_channels,), "bias", True,
                                              ("const", float(bias)))
-            if activation not in ("relu", "linear", "tanh", None):
+            if activation not in ("relu", "relu6", "linear", "tanh", None):
                 raise KeyError("Invalid activation type '%s'" % activation)
             act = "linear" if activation is None else activation
+            fused_act = act if act in ("relu", "linear") else "linear"
             node = self.graph.add_node(
                 "conv", self._full(""), [input_layer], (n, p, q, num_out_channels),
                 dict(kh=k_height, kw=k_width, sh=d_height, sw=d_width, pad_h=pad_h, pad_w=pad_w,
-                     activation="linear" if use_batch_norm else act, has_bias=has_bias),
+                     activation="linear" if use_batch_norm else fused_act,
+                     has_bias=has_bias),
                 params)
             self.top_layer, self.top_size = node.output, num_out_channels
             if use_batch_norm:
-                self.batch_norm(**self.batch_norm_config)
+                self.batch_norm(scope_name=bn_scope_name, **self.batch_norm_config)
                 if act == "relu":
                     self.relu()
-                elif act == "tanh":
-                    self.tanh()
+            if act == "tanh":
+                self.tanh()
+            elif act == "relu6":
+                self.relu6()
         return self.top_layer
 
-    def batch_norm(self, input_layer=None, decay=0.999, scale=False, epsilon=0.001) -> TensorRef:
+    def depthwise_conv(self, k_height, k_width, d_height=1, d_width=1, mode="SAME",
+                       input_layer=None, stddev=None, scope_name=None,
+                       kernel_leaf="depthwise_weights", use_batch_norm=None, activation=None,
+                       bn_scope_name=None) -> TensorRef:
+        """Depthwise convolution with channel multiplier 1: the depthwise half of
+        slim.separable_conv2d (T/models/mobilenet_conv_blocks.py:246-256,
+        T/models/nasnet_utils.py:212-260). No bias; optional BN + activation after it."""
+        x = self.top_layer if input_layer is None else input_layer
+        n, h, w, c = x.shape
+        if scope_name is None:
+            scope_name = "depthwise" + str(self.counts["depthwise"])
+            self.counts["depthwise"] += 1
+        pad_h = resolve_padding(mode, h, k_height, d_height)
+        pad_w = resolve_padding(mode, w, k_width, d_width)
+        p = out_size(h, k_height, d_height, pad_h)
+        q = out_size(w, k_width, d_width, pad_w)
+        fan = k_height * k_width
+        init = (("trunc_normal", float(stddev)) if stddev is not None
+                else ("glorot_uniform", fan * c, fan * c))
+        if use_batch_norm is None:
+            use_batch_norm = self.use_batch_norm
+        with self.scope(scope_name):
+            spec = ParamSpec(self._full(kernel_leaf), (k_height, k_width, c),
+                             (k_height, k_width, c, 1), "dw_kernel", True, init)
+            node = self.graph.add_node(
+                "dwconv", self._full(""), [x], (n, p, q, c),
+                dict(kh=k_height, kw=k_width, sh=d_height, sw=d_width, pad_h=pad_h, pad_w=pad_w),
+                {"kernel": spec})
+            self.top_layer, self.top_size = node.output, c
+            if use_batch_norm:
+                self.batch_norm(scope_name=bn_scope_name, **self.batch_norm_config)
+            if activation == "relu":
+                self.relu()
+            elif activation == "relu6":
+                self.relu6()
+        return self.top_layer
+
+    def batch_norm(self, input_layer=None, decay=0.999, scale=False, epsilon=0.001,
+                   scope_name=None) -> TensorRef:
         """T/convnet_builder_legacy.py:433-459 (defaults decay .999, eps 1e-3, no scale)."""
         if input_layer is None:
             input_layer = self.top_layer
         else:
             self.top_size = None
-        name = "batchnorm" + str(self.counts["batchnorm"])
-        self.counts["batchnorm"] += 1
+        if scope_name is None:
+            name = "batchnorm" + str(self.counts["batchnorm"])
+            self.counts["batchnorm"] += 1
+        else:
+            name = scope_name
         c = input_layer.shape[-1]
         with self.scope(name):
             params = {"beta": ParamSpec(self._full("beta"), (c,), (c,), "beta", True, ("zeros",))}
@@ -191,6 +242,28 @@ class NetBuilder:
         node = self.graph.add_node("act", "relu%d" % self.counts["relu"], [x], x.shape,
                                    dict(kind="relu"))
         self.counts["relu"] += 1
+        self.top_layer = node.output
+        return self.top_layer
+
+    def relu6(self, input_layer=None) -> TensorRef:
+        """min(max(x, 0), 6) - the activation of the MobileNet family."""
+        x = self.top_layer if input_layer is None else input_layer
+        node = self.graph.add_node("act", "relu6_%d" % self.counts["relu6"], [x], x.shape,
+                                   dict(kind="relu6"))
+        self.counts["relu6"] += 1
+        self.top_layer = node.output
+        return self.top_layer
+
+    def drop_path(self, keep_prob_fn, input_layer=None) -> TensorRef:
+        """Per-sample stochastic depth (T/models/nasnet_utils.py:113-138, 430-458).
+        ``keep_prob_fn(step) -> float`` gives the scheduled keep probability; identity when
+        not training."""
+        x = self.top_layer if input_layer is None else input_layer
+        if not self.phase_train:
+            return x
+        node = self.graph.add_node("drop_path", "drop_path%d" % self.counts["drop_path"], [x],
+                                   x.shape, dict(keep_prob_fn=keep_prob_fn))
+        self.counts["drop_path"] += 1
         self.top_layer = node.output
         return self.top_layer
 
@@ -273,7 +346,7 @@ class NetBuilder:
         return self.top_layer
 
     def affine(self, num_out_channels, input_layer=None, num_channels_in=None, bias=0.0,
-               stddev=None, activation="relu") -> TensorRef:
+               stddev=None, activation="relu", scope_name=None) -> TensorRef:
         """T/convnet_builder_legacy.py:288-325."""
         if input_layer is None:
             input_layer = self.top_layer
@@ -281,8 +354,11 @@ class NetBuilder:
             num_channels_in = self.top_size
         if len(input_layer.shape) != 2 or input_layer.shape[1] != num_channels_in:
             raise ValueError(f"affine: bad input {input_layer.shape} for in={num_channels_in}")
-        name = "affine" + str(self.counts["affine"])
-        self.counts["affine"] += 1
+        if scope_name is None:
+            name = "affine" + str(self.counts["affine"])
+            self.counts["affine"] += 1
+        else:
+            name = scope_name
         if activation not in ("relu", "linear", None):
             raise KeyError("Invalid activation type '%s'" % activation)
         act = "linear" if activation is None else activation

@@ -234,6 +234,20 @@ class CudaExecutor:
                 a["activation"] == "linear" and k_reduction >= self.fuse_stats_min_k)
             if info["fuse_stats"]:
                 self._scratch_need = max(self._scratch_need, self._stats_rows * 2 * k)
+        elif node.op == "dwconv":
+            x = node.inputs[0]
+            n, h, w, c = x.shape
+            d = ConvDesc()
+            d.n, d.h, d.w, d.c = n, h, w, c
+            d.k, d.r, d.s = c, a["kh"], a["kw"]
+            d.pad_h_lo, d.pad_h_hi = a["pad_h"]
+            d.pad_w_lo, d.pad_w_hi = a["pad_w"]
+            d.stride_h, d.stride_w = a["sh"], a["sw"]
+            d.p, d.q = node.output.shape[1], node.output.shape[2]
+            info["desc"] = d
+            fn = native.load().kfb_dwconv_wgrad_workspace_bytes
+            fn.restype = ctypes.c_longlong
+            self._ws_need = max(self._ws_need, int(fn(ctypes.byref(d))))
         elif node.op == "bn":
             c = node.output.shape[-1]
             info["mean_rstd"] = torch.zeros((2 * c,), dtype=torch.float32, device=dev)
@@ -374,12 +388,39 @@ class CudaExecutor:
                         res.p if res else None, i64(res.ld if res else 0), i32(int(a["relu"])),
                         y.p, i64(y.ld), s)
 
+    _ACT_KIND = {"relu": 1, "relu6": 2, "tanh": 3, "sigmoid": 4}
+
     def _fwd_act(self, node, train, s):
-        if node.attrs["kind"] != "relu":
-            raise NotImplementedError("only ReLU is built as a stand-alone activation")
+        kind = self._ACT_KIND[node.attrs["kind"]]
         x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
-        native.call("add_act", x.p, i64(x.ld), None, i64(0), y.p, i64(y.ld), i64(x.rows),
-                    i32(_pad8(x.cols)), i32(1), s)
+        if kind == 1:
+            native.call("add_act", x.p, i64(x.ld), None, i64(0), y.p, i64(y.ld), i64(x.rows),
+                        i32(_pad8(x.cols)), i32(1), s)
+        else:
+            native.call("act_forward", x.p, i64(x.ld), y.p, i64(y.ld), i64(x.rows),
+                        i32(_pad8(x.cols)), i32(kind), s)
+
+    def _fwd_dwconv(self, node, train, s):
+        d = self._per_node[id(node)]["desc"]
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        native.call("dwconv_fprop", ctypes.byref(d), x.p, i64(x.ld),
+                    self._w16(node.params["kernel"].name), y.p, i64(y.ld), s)
+
+    def _drop_path_args(self, node):
+        kp = float(node.attrs["keep_prob_fn"](self.step_index))
+        idx = self.graph.nodes.index(node)
+        b = self.buf[node.output.id]
+        return (i64(b.rows), i64(b.rows // self.graph.batch_size), i32(_pad8(b.cols)), f32(kp),
+                u64(self.dropout_seed), u64((self.step_index * 4096 + idx) * 65536))
+
+    def _fwd_drop_path(self, node, train, s):
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        if not train:
+            native.call("copy2d", x.p, i64(x.ld), y.p, i64(y.ld), i64(x.rows), i32(x.cols),
+                        i32(0), s)
+            return
+        native.call("drop_path", x.p, i64(x.ld), y.p, i64(y.ld), i32(0),
+                    *self._drop_path_args(node), s)
 
     def _fwd_add(self, node, train, s):
         a, b = self.buf[node.inputs[0].id], self.buf[node.inputs[1].id]
@@ -579,8 +620,34 @@ class CudaExecutor:
         if not self.needs_grad[xin.id]:
             return
         y, gy, gx = self.buf[node.output.id], self._grad(node.output), self._grad(xin)
-        native.call("relu_backward", gy.p, i64(gy.ld), y.p, i64(y.ld), gx.p, i64(gx.ld),
-                    i32(self._acc(node, 0)), i64(gy.rows), i32(_pad8(gy.cols)), s)
+        kind = self._ACT_KIND[node.attrs["kind"]]
+        if kind == 1:
+            native.call("relu_backward", gy.p, i64(gy.ld), y.p, i64(y.ld), gx.p, i64(gx.ld),
+                        i32(self._acc(node, 0)), i64(gy.rows), i32(_pad8(gy.cols)), s)
+        else:
+            native.call("act_backward", gy.p, i64(gy.ld), y.p, i64(y.ld), gx.p, i64(gx.ld),
+                        i32(self._acc(node, 0)), i64(gy.rows), i32(_pad8(gy.cols)), i32(kind), s)
+
+    def _bwd_dwconv(self, node, s):
+        d = self._per_node[id(node)]["desc"]
+        xin = node.inputs[0]
+        x, gy = self.buf[xin.id], self._grad(node.output)
+        kname = node.params["kernel"].name
+        if self.needs_grad[xin.id]:
+            gx = self._grad(xin)
+            native.call("dwconv_dgrad", ctypes.byref(d), gy.p, i64(gy.ld), self._w16(kname), gx.p,
+                        i64(gx.ld), i32(self._acc(node, 0)), s)
+        native.call("dwconv_wgrad", ctypes.byref(d), x.p, i64(x.ld), gy.p, i64(gy.ld),
+                    self._g32(kname), ptr(self.workspace), i64(self.workspace.numel() * 4),
+                    i32(0), f32(1.0), s)
+
+    def _bwd_drop_path(self, node, s):
+        xin = node.inputs[0]
+        if not self.needs_grad[xin.id]:
+            return
+        gy, gx = self._grad(node.output), self._grad(xin)
+        native.call("drop_path", gy.p, i64(gy.ld), gx.p, i64(gx.ld), i32(self._acc(node, 0)),
+                    *self._drop_path_args(node), s)
 
     def _bwd_add(self, node, s):
         y, gy = self.buf[node.output.id], self._grad(node.output)

@@ -47,6 +47,7 @@ class RefExecutor:
         self._loss = None
         self._gen = torch.Generator(device="cpu").manual_seed(dropout_seed)
         self.last = (float("nan"), 0, 0)
+        self.step_index = 0
 
     # -- inputs ---------------------------------------------------------------
     def set_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
@@ -63,6 +64,8 @@ class RefExecutor:
             t = v[:, :r * s * c].reshape(v.shape[0], r, s, c).permute(0, 3, 1, 2)
         elif spec.kind == "fc_weight":
             t = v[:, :spec.logical_cols]
+        elif spec.kind == "dw_kernel":
+            t = v.permute(2, 0, 1).unsqueeze(1)             # [R,S,C] -> [C,1,R,S] view
         else:
             t = v
         t = t.clone()
@@ -97,6 +100,20 @@ class RefExecutor:
             y = F.conv2d(x, w, b, stride=(a["sh"], a["sw"]))
             y = _act(y, a["activation"])
             return y.permute(0, 2, 3, 1)
+        if op == "dwconv":
+            x = xs[0].permute(0, 3, 1, 2)
+            w = self._param(node.params["kernel"], train)
+            ph, pw = a["pad_h"], a["pad_w"]
+            x = F.pad(x, (pw[0], pw[1], ph[0], ph[1]))
+            y = F.conv2d(x, w, None, stride=(a["sh"], a["sw"]), groups=x.shape[1])
+            return y.permute(0, 2, 3, 1)
+        if op == "drop_path":
+            if not train:
+                return xs[0]
+            kp = float(a["keep_prob_fn"](self.step_index))
+            n = xs[0].shape[0]
+            keep = (torch.rand((n,), generator=self._gen) < kp).to(xs[0])
+            return xs[0] * (keep / kp).view(n, *([1] * (xs[0].dim() - 1)))
         if op == "bn":
             x = xs[0]
             beta = self._param(node.params["beta"], train)
@@ -199,10 +216,13 @@ class RefExecutor:
                 gv[:, :r * s * c] = gr.permute(0, 2, 3, 1).reshape(gr.shape[0], -1)
             elif spec.kind == "fc_weight":
                 gv[:, :spec.logical_cols] = gr
+            elif spec.kind == "dw_kernel":
+                gv.copy_(gr.squeeze(1).permute(1, 2, 0))
             else:
                 gv.copy_(gr)
         if on_grads_ready is not None:
             on_grads_ready(0, self.store.num_trainable_padded)
+        self.step_index += 1
 
     def read_loss(self):
         return self.last
@@ -217,6 +237,10 @@ class RefExecutor:
 def _act(y, kind):
     if kind == "relu":
         return F.relu(y)
+    if kind == "relu6":
+        return F.relu6(y)
     if kind == "tanh":
         return torch.tanh(y)
+    if kind == "sigmoid":
+        return torch.sigmoid(y)
     return y

@@ -1,0 +1,91 @@
+"""Kernels of the wider zoo (csrc/extra_ops.cu) vs plain PyTorch fp32 restatements."""
+import ctypes
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from kf_benchmarks_b200.ops import native  # noqa: E402
+from kf_benchmarks_b200.ops.native import ConvDesc, f32, i32, i64, ptr  # noqa: E402
+
+u64 = ctypes.c_ulonglong
+
+
+def _s():
+    return native.stream_ptr()
+
+
+@pytest.mark.parametrize("kind,name", [(2, "relu6"), (3, "tanh"), (4, "sigmoid")])
+def test_activation_forward_backward(kind, name):
+    g = torch.Generator(device="cuda").manual_seed(kind)
+    rows, c = 333, 40
+    x = (torch.randn(rows, c, device="cuda", generator=g) * 4).half()
+    dy = torch.randn(rows, c, device="cuda", generator=g).half()
+    y, dx = torch.empty_like(x), torch.empty_like(x)
+    native.call("act_forward", ptr(x), i64(c), ptr(y), i64(c), i64(rows), i32(c), i32(kind), _s())
+    native.call("act_backward", ptr(dy), i64(c), ptr(y), i64(c), ptr(dx), i64(c), i32(0),
+                i64(rows), i32(c), i32(kind), _s())
+    xf = x.float().requires_grad_(True)
+    yr = {"relu6": F.relu6, "tanh": torch.tanh, "sigmoid": torch.sigmoid}[name](xf)
+    yr.backward(dy.float())
+    assert torch.allclose(y.float(), yr, atol=2e-3, rtol=2e-3)
+    assert torch.allclose(dx.float(), xf.grad, atol=1e-2, rtol=1e-2)
+    # accumulate
+    native.call("act_backward", ptr(dy), i64(c), ptr(y), i64(c), ptr(dx), i64(c), i32(1),
+                i64(rows), i32(c), i32(kind), _s())
+    assert torch.allclose(dx.float(), 2 * xf.grad, atol=2e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("n,h,w,c,r,stride,pad", [
+    (2, 14, 14, 32, 3, 1, (1, 1)), (3, 15, 15, 96, 3, 2, (1, 1)), (2, 12, 12, 48, 5, 2, (1, 2)),
+    (1, 9, 9, 264, 7, 1, (3, 3)), (2, 8, 8, 8, 3, 2, (0, 1))])
+def test_depthwise_conv(n, h, w, c, r, stride, pad):
+    g = torch.Generator(device="cuda").manual_seed(c)
+    x = torch.randn(n, h, w, c, device="cuda", generator=g).half()
+    wt = (torch.randn(r, r, c, device="cuda", generator=g) * 0.3).half()
+    p = (h + pad[0] + pad[1] - r) // stride + 1
+    d = ConvDesc()
+    d.n, d.h, d.w, d.c, d.k, d.r, d.s = n, h, w, c, c, r, r
+    d.pad_h_lo, d.pad_h_hi, d.pad_w_lo, d.pad_w_hi = pad[0], pad[1], pad[0], pad[1]
+    d.stride_h = d.stride_w = stride
+    d.p = d.q = p
+    y = torch.empty(n, p, p, c, device="cuda", dtype=torch.float16)
+    native.call("dwconv_fprop", ctypes.byref(d), ptr(x), i64(c), ptr(wt), ptr(y), i64(c), _s())
+    xf = x.float().requires_grad_(True)
+    wf = wt.float().requires_grad_(True)
+    xp = F.pad(xf.permute(0, 3, 1, 2), (pad[0], pad[1], pad[0], pad[1]))
+    yr = F.conv2d(xp, wf.permute(2, 0, 1).unsqueeze(1), stride=stride, groups=c)
+    yr = yr.permute(0, 2, 3, 1)
+    assert yr.shape == y.shape
+    assert torch.allclose(y.float(), yr, atol=2e-2, rtol=2e-2)
+    dy = torch.randn(y.shape, device="cuda", generator=g).half()
+    yr.backward(dy.float())
+    dx = torch.empty_like(x)
+    native.call("dwconv_dgrad", ctypes.byref(d), ptr(dy), i64(c), ptr(wt), ptr(dx), i64(c), i32(0),
+                _s())
+    assert torch.allclose(dx.float(), xf.grad, atol=2e-2, rtol=2e-2)
+    fn = native.load().kfb_dwconv_wgrad_workspace_bytes
+    fn.restype = ctypes.c_longlong
+    ws = torch.zeros(int(fn(ctypes.byref(d))) // 4 + 16, device="cuda")
+    dw = torch.zeros(r, r, c, device="cuda")
+    native.call("dwconv_wgrad", ctypes.byref(d), ptr(x), i64(c), ptr(dy), i64(c), ptr(dw), ptr(ws),
+                i64(ws.numel() * 4), i32(0), f32(1.0), _s())
+    ref = wf.grad
+    assert (dw - ref).abs().max() <= 2e-2 * ref.abs().max() + 1e-2
+
+
+def test_drop_path_is_per_sample_and_replayable():
+    n, hw, c = 64, 9, 16
+    x = torch.ones(n * hw, c, device="cuda", dtype=torch.float16)
+    y, y2 = torch.empty_like(x), torch.empty_like(x)
+    args = (i64(n * hw), i64(hw), i32(c), f32(0.75), u64(99), u64(12345))
+    native.call("drop_path", ptr(x), i64(c), ptr(y), i64(c), i32(0), *args, _s())
+    native.call("drop_path", ptr(x), i64(c), ptr(y2), i64(c), i32(0), *args, _s())
+    assert torch.equal(y, y2)
+    per = y.float().view(n, hw * c)
+    assert bool(((per == 0).all(1) | torch.isclose(per, torch.tensor(1 / 0.75, device="cuda"),
+                                                    atol=1e-3).all(1)).all())
+    kept = int((per[:, 0] > 0).sum())
+    assert 32 <= kept <= 60
