@@ -31,6 +31,11 @@ def compare(model_name, data_name, batch, image_size=None, seed=0, verbose=False
     nclass = ds.num_classes
     from kf_benchmarks_b200.nn.legalize import legalize
     g = legalize(model.build_graph(nclass, batch_size=batch))
+    for node in g.nodes:  # the two executors draw different random streams: compare without them
+        if node.op == "dropout":
+            node.attrs["keep_prob"] = 1.0
+        elif node.op == "drop_path":
+            node.attrs["keep_prob_fn"] = lambda step: 1.0
     dev = torch.device("cuda")
     st_gpu = ParameterStore(g, dev)
     st_gpu.initialize(1234)
