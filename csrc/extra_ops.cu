@@ -279,6 +279,37 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// ---------------------------------------------------------------------------
+// Channel gather: y[r][c] (+)= idx[c] >= 0 ? x[r][idx[c]] : 0. Converts between two phantom-
+// channel layouts of the same logical tensor (nn/legalize.py); its backward is the same
+// kernel with the inverse index.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    channel_gather_kernel(const __half* __restrict__ x, long long ldx, __half* __restrict__ y,
+                          long long ldy, int accumulate, long long rows, int C,
+                          const int* __restrict__ idx) {
+  const int vpr = C >> 3;
+  const long long total = rows * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int src = idx[cv * 8 + k];
+      v[k] = src >= 0 ? __half2float(x[r * ldx + src]) : 0.f;
+    }
+    if (accumulate) {
+      float o[8];
+      load8(y + r * ldy + cv * 8, o);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] += o[k];
+    }
+    store8(y + r * ldy + cv * 8, v);
+  }
+}
+
 }  // namespace kfb
 
 using namespace kfb;
@@ -378,6 +409,17 @@ extern "C" int kfb_drop_path(const void* x, long long ldx, void* y, long long ld
   drop_path_kernel<<<xgrid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
       (const __half*)x, ldx, (__half*)y, ldy, accumulate, rows, rows_per_sample, C, keep_prob,
       seed, offset);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_channel_gather(const void* x, long long ldx, void* y, long long ldy,
+                                  int accumulate, long long rows, int C, const int* idx,
+                                  void* stream) {
+  KFB_REQ_C8(C, "channel_gather");
+  KFB_REQUIRE(idx != nullptr, "channel_gather: null index");
+  channel_gather_kernel<<<xgrid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)x, ldx, (__half*)y, ldy, accumulate, rows, C, idx);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -243,6 +243,10 @@ long long kfb_dwconv_wgrad_workspace_bytes(const kfb_conv_desc* d);
 int kfb_dwconv_wgrad(const kfb_conv_desc* d, const void* x, long long ldx, const void* dy,
                      long long lddy, float* dw, void* workspace, long long workspace_bytes,
                      int accumulate, float scale, void* stream);
+/* y[r][c] (+)= idx[c] >= 0 ? x[r][idx[c]] : 0 over C output channels (idx on the device):
+ * converts between two zero-padded channel layouts of one logical tensor (nn/legalize.py). */
+int kfb_channel_gather(const void* x, long long ldx, void* y, long long ldy, int accumulate,
+                       long long rows, int C, const int* idx, void* stream);
 /* Per-sample drop-path (T/models/nasnet_utils.py:113-138): y (+)= x * (u_n < keep ? 1/keep : 0)
  * with u_n a pure function of (seed, offset, sample); the same call replays it for dy. */
 int kfb_drop_path(const void* x, long long ldx, void* y, long long ldy, int accumulate,

@@ -5,7 +5,8 @@ from __future__ import annotations
 from functools import partial
 
 from . import (alexnet_model, densenet_model, googlenet_model, inception_model, lenet_model,
-               mobilenet_v2, official_resnet_model, overfeat_model, resnet_model, trivial_model, vgg_model)
+               mobilenet_v2, nasnet_model,
+               official_resnet_model, overfeat_model, resnet_model, trivial_model, vgg_model)
 
 _model_name_to_imagenet_model = {
     "vgg11": vgg_model.Vgg11Model,
@@ -19,6 +20,8 @@ _model_name_to_imagenet_model = {
     "inception3": inception_model.Inceptionv3Model,
     "inception4": inception_model.Inceptionv4Model,
     "mobilenet": mobilenet_v2.MobilenetModel,
+    "nasnet": nasnet_model.NasnetModel,
+    "nasnetlarge": nasnet_model.NasnetLargeModel,
 }
 _model_name_to_imagenet_model.update(resnet_model.imagenet_factories())
 _model_name_to_imagenet_model.update(official_resnet_model.factories())
@@ -26,6 +29,7 @@ _model_name_to_imagenet_model.update(official_resnet_model.factories())
 _model_name_to_cifar_model = {
     "alexnet": alexnet_model.AlexnetCifar10Model,
     "trivial": trivial_model.TrivialCifar10Model,
+    "nasnet": nasnet_model.NasnetCifarModel,
     "densenet40_k12": densenet_model.create_densenet40_k12_model,
     "densenet100_k12": densenet_model.create_densenet100_k12_model,
     "densenet100_k24": densenet_model.create_densenet100_k24_model,
@@ -35,7 +39,6 @@ _model_name_to_cifar_model.update(resnet_model.cifar_factories())
 # Models of the reference that need external repositories / datasets the fork itself
 # disabled. They resolve to a clear error instead of an import failure.
 _UNSUPPORTED = {
-    "nasnet": "slim-based NASNet", "nasnetlarge": "slim-based NASNet",
     "ssd300": "needs COCO + the object_detection package",
     "deepspeech2": "needs LibriSpeech; LSTM/CTC kernels not built",
     "ncf": "needs the official NCF package",

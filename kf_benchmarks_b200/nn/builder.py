@@ -230,11 +230,13 @@ class NetBuilder:
             self.top_size = c
         return self.top_layer
 
-    def relu(self, input_layer=None) -> TensorRef:
-        """ReLU on the top layer; folded into a preceding batch-norm when possible."""
+    def relu(self, input_layer=None, fold=True) -> TensorRef:
+        """ReLU on the top layer; folded into a preceding batch-norm when possible. Pass
+        ``fold=False`` when the pre-activation value has other (later) readers - NASNet's hidden
+        states feed pooling branches raw and separable branches through a ReLU."""
         x = self.top_layer if input_layer is None else input_layer
         prod = x.producer
-        if (prod is not None and prod.op == "bn" and not prod.attrs["relu"] and
+        if (fold and prod is not None and prod.op == "bn" and not prod.attrs["relu"] and
                 not x.consumers and x is not self.graph.logits):
             prod.attrs["relu"] = True
             self.top_layer = x
@@ -275,14 +277,15 @@ class NetBuilder:
         self.top_layer = node.output
         return self.top_layer
 
-    def add(self, shortcut: TensorRef, res: TensorRef, relu: bool = False) -> TensorRef:
+    def add(self, shortcut: TensorRef, res: TensorRef, relu: bool = False,
+            fold: bool = True) -> TensorRef:
         """``act(shortcut + res)``: the residual join of the ResNet blocks
         (T/models/resnet_model_legacy.py:77). Folded into the batch-norm that produced ``res``
         when that is legal."""
         if shortcut.shape != res.shape:
             raise ValueError(f"add: shapes differ {shortcut.shape} vs {res.shape}")
         prod = res.producer
-        if (prod is not None and prod.op == "bn" and not prod.attrs["relu"] and
+        if (fold and prod is not None and prod.op == "bn" and not prod.attrs["relu"] and
                 len(prod.inputs) == 1 and not res.consumers):
             prod.inputs.append(shortcut)
             shortcut.consumers.append(prod)
@@ -328,6 +331,22 @@ class NetBuilder:
               num_channels_in=None) -> TensorRef:
         return self._pool("apool", k_height, k_width, d_height, d_width, mode, input_layer,
                           num_channels_in)
+
+    def subsample(self, stride: int, shift: int = 0, input_layer=None) -> TensorRef:
+        """Keeps every ``stride``-th pixel starting at ``shift`` (zeros past the edge): the
+        1x1 VALID average pool of NASNet's factorised reduction, whose second path reads the
+        input shifted by one pixel (T/models/nasnet_utils.py:87-108)."""
+        x = self.top_layer if input_layer is None else input_layer
+        n, h, w, c = x.shape
+        pad = (-shift, shift)
+        p = out_size(h, 1, stride, pad)
+        q = out_size(w, 1, stride, pad)
+        node = self.graph.add_node(
+            "pool", "subsample%d" % self.counts["subsample"], [x], (n, p, q, c),
+            dict(kind="avg", kh=1, kw=1, sh=stride, sw=stride, pad_h=pad, pad_w=pad))
+        self.counts["subsample"] += 1
+        self.top_layer, self.top_size = node.output, c
+        return self.top_layer
 
     def reshape(self, shape: Sequence[int], input_layer=None) -> TensorRef:
         """Only the flattening reshapes the zoo uses (``[-1, F]``) are supported."""

@@ -266,6 +266,9 @@ class CudaExecutor:
         elif node.op == "pad_channels":
             if a["before"] % 8 or a["after"] % 8:
                 raise NotImplementedError("pad_channels: pads must be multiples of 8")
+        elif node.op == "relayout":
+            info["index"] = torch.tensor(a["index"], dtype=torch.int32, device=dev)
+            info["inverse"] = torch.tensor(a["inverse"], dtype=torch.int32, device=dev)
         elif node.op == "lrn" or node.op == "dropout":
             pass
         self._per_node[id(node)] = info
@@ -491,6 +494,20 @@ class CudaExecutor:
             native.call("copy2d", x.p, i64(x.ld), ctypes.c_void_p(y.t.data_ptr() + off * 2),
                         i64(y.ld), i64(x.rows), i32(x.cols), i32(0), s)
             off += x.cols
+
+    def _fwd_relayout(self, node, train, s):
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        native.call("channel_gather", x.p, i64(x.ld), y.p, i64(y.ld), i32(0), i64(x.rows),
+                    i32(y.cols), ptr(self._per_node[id(node)]["index"]), s)
+
+    def _bwd_relayout(self, node, s):
+        xin = node.inputs[0]
+        if not self.needs_grad[xin.id]:
+            return
+        gy, gx = self._grad(node.output), self._grad(xin)
+        native.call("channel_gather", gy.p, i64(gy.ld), gx.p, i64(gx.ld),
+                    i32(self._acc(node, 0)), i64(gy.rows), i32(gx.cols),
+                    ptr(self._per_node[id(node)]["inverse"]), s)
 
     def _fwd_pad_channels(self, node, train, s):
         x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]

@@ -158,7 +158,7 @@ class RefExecutor:
                                    divisor_override=1)
                 cnt = F.avg_pool2d(F.pad(ones, (pw[0], pw[1], ph[0], ph[1])), k, s,
                                    divisor_override=1)
-                y = xs_ / cnt
+                y = xs_ / cnt.clamp(min=1.0)   # windows entirely in the padding give 0
             return y.permute(0, 2, 3, 1)
         if op == "spatial_mean":
             return xs[0].mean((1, 2))
@@ -181,6 +181,10 @@ class RefExecutor:
             return x / (a["bias"] + a["alpha"] * win) ** a["beta"]
         if op == "concat":
             return torch.cat(xs, dim=-1)
+        if op == "relayout":
+            idx = torch.tensor(a["index"], dtype=torch.long, device=xs[0].device)
+            y = xs[0][..., idx.clamp(min=0)]
+            return y * (idx >= 0).to(y)
         if op == "pad_channels":
             return F.pad(xs[0], (a["before"], a["after"]))
         raise NotImplementedError(op)

@@ -76,6 +76,23 @@ def legalize(graph: Graph) -> Graph:
     # old tensor id -> (new tensor, channel map, physical channels)
     tmap: Dict[int, Tuple[TensorRef, ChanMap, int]] = {graph.input.id: (out.input, None, c)}
 
+    def relayout(src, logical, want_map, want_phys):
+        """Brings operand ``src`` = (tensor, map, phys) to the layout (want_map, want_phys)."""
+        t, m, p = src
+        if (m, p) == (want_map, want_phys):
+            return src
+        index = [-1] * want_phys
+        for frm, to in zip(_full_map(m, logical), _full_map(want_map, logical)):
+            index[to] = frm
+        inverse = [-1] * p
+        for dst, frm in enumerate(index):
+            if frm >= 0:
+                inverse[frm] = dst
+        node = out.add_node("relayout", "relayout%d" % len(out.nodes), [t],
+                            t.shape[:-1] + (want_phys,),
+                            dict(index=tuple(index), inverse=tuple(inverse)))
+        return (node.output, want_map, want_phys)
+
     for node in graph.nodes:
         ins = [tmap[t.id] for t in node.inputs]
         new_inputs = [i[0] for i in ins]
@@ -115,9 +132,9 @@ def legalize(graph: Graph) -> Graph:
         elif op == "bn":
             for key, spec in node.params.items():
                 params[key] = _vec(spec, xm, xp)
-            for other, t in zip(ins[1:], node.inputs[1:]):
-                if (other[1], other[2]) != (xm, xp):
-                    raise NotImplementedError(f"{node.name}: residual layouts differ")
+            for i in range(1, len(ins)):
+                ins[i] = relayout(ins[i], logical_c, xm, xp)
+            new_inputs = [i[0] for i in ins]
             shape, omap, ophys = t_out.shape[:-1] + (xp,), xm, xp
         elif op in ("act", "pool", "dropout", "spatial_mean", "drop_path"):
             shape, omap, ophys = t_out.shape[:-1] + (xp,), xm, xp
@@ -126,9 +143,9 @@ def legalize(graph: Graph) -> Graph:
                 raise NotImplementedError("lrn over a padded channel layout")
             shape, omap, ophys = t_out.shape, xm, xp
         elif op == "add":
-            for other in ins[1:]:
-                if (other[1], other[2]) != (xm, xp):
-                    raise NotImplementedError(f"{node.name}: operand layouts differ")
+            for i in range(1, len(ins)):
+                ins[i] = relayout(ins[i], logical_c, xm, xp)
+            new_inputs = [i[0] for i in ins]
             shape, omap, ophys = t_out.shape[:-1] + (xp,), xm, xp
         elif op == "concat":
             full, off = [], 0

@@ -30,6 +30,8 @@ import executor_check  # noqa: E402
     ("densenet40_k12", "cifar10", 8, 0.99, 5e-3),      # growth 12: phantom-channel layout
     ("mobilenet", "imagenet", 2, 0.6, 5e-2),           # depthwise + ReLU6
     ("official_resnet18", "imagenet", 2, 0.9, 5e-3),
+    ("nasnet", "cifar10", 8, 0.8, 2e-2),               # separable 3/5/7, shifted subsampling
+    ("nasnet", "imagenet", 2, 0.5, 5e-2),              # 11/22/44-wide cells: relayout nodes
 ])
 def test_executor_matches_reference(model, data, batch, min_cos, max_logit_rel):
     r = executor_check.compare(model, data, batch)

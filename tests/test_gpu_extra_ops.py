@@ -89,3 +89,22 @@ def test_drop_path_is_per_sample_and_replayable():
                                                     atol=1e-3).all(1)).all())
     kept = int((per[:, 0] > 0).sum())
     assert 32 <= kept <= 60
+
+
+def test_channel_gather_and_inverse():
+    rows, cin, cout = 77, 32, 24
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(rows, cin, device="cuda", generator=g).half()
+    index = [-1] * cout
+    for dst, src in zip((0, 1, 2, 5, 9, 10, 11, 17, 23), (3, 2, 1, 30, 16, 17, 18, 0, 31)):
+        index[dst] = src
+    idx = torch.tensor(index, dtype=torch.int32, device="cuda")
+    y = torch.empty(rows, cout, device="cuda", dtype=torch.float16)
+    native.call("channel_gather", ptr(x), i64(cin), ptr(y), i64(cout), i32(0), i64(rows),
+                i32(cout), ptr(idx), _s())
+    li = idx.long()
+    ref = x[:, li.clamp(min=0)] * (li >= 0)
+    assert torch.equal(y, ref.half())
+    native.call("channel_gather", ptr(x), i64(cin), ptr(y), i64(cout), i32(1), i64(rows),
+                i32(cout), ptr(idx), _s())
+    assert torch.allclose(y.float(), 2 * ref.float(), atol=1e-2)
