@@ -57,7 +57,43 @@ def setup(params):
             raise ValueError("--%s: %s" % (name, why))
     if params.num_intra_threads:
         torch.set_num_threads(int(params.num_intra_threads))
+    _apply_cluster_role(params)
     return params
+
+
+def _apply_cluster_role(params) -> None:
+    """TF cluster roles (T/benchmark_cnn.py:1354-1406, T/cnn_util.py:201-251) on a runtime that
+    has one process per GPU and no parameter-server processes:
+
+    * ``--job_name=worker --task_index=i --worker_hosts=h0:p0,h1:p1,...`` - this process is rank
+      ``i`` of ``len(worker_hosts)``; the first worker's host:port is the rendezvous address.
+      Nothing is changed when a launcher (torchrun / parallel.launcher) already set RANK.
+    * ``--job_name=ps`` / ``controller`` - there is nothing for these roles to do (variables are
+      replicated and updated by the fused all-reduce kernels; there is no separate graph-owning
+      controller): the process logs that and exits 0, so reference launch scripts keep working.
+    """
+    role = params.job_name
+    if not role:
+        return
+    if role in ("ps", "controller"):
+        _log("--job_name=%s: this runtime has no %s processes (variables live with the workers); "
+             "nothing to do, exiting." % (role, "parameter-server" if role == "ps"
+                                          else "controller"))
+        raise SystemExit(0)
+    hosts = [h for h in (params.worker_hosts or "").split(",") if h]
+    if not hosts:
+        raise ValueError("--job_name=worker needs --worker_hosts")
+    if not 0 <= params.task_index < len(hosts):
+        raise ValueError("--task_index=%d out of range for %d worker_hosts" %
+                         (params.task_index, len(hosts)))
+    if "RANK" in os.environ and "WORLD_SIZE" in os.environ:
+        return
+    host, _, port = hosts[0].partition(":")
+    os.environ["RANK"] = str(params.task_index)
+    os.environ["LOCAL_RANK"] = str(params.task_index)
+    os.environ["WORLD_SIZE"] = str(len(hosts))
+    os.environ.setdefault("MASTER_ADDR", host or "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", port or "29500")
 
 
 class BenchmarkCNN:
@@ -79,7 +115,11 @@ class BenchmarkCNN:
         self.rank = int(os.environ.get("RANK", "0"))
         self.world = int(os.environ.get("WORLD_SIZE", "1"))
         self.local_rank = int(os.environ.get("LOCAL_RANK", str(self.rank)))
-        if p.variable_update in ("kungfu", "horovod"):
+        if p.variable_update in ("kungfu", "horovod") or p.job_name == "worker":
+            # one GPU per worker process (KungFu / Horovod / TF-cluster style launches)
+            if p.job_name == "worker" and p.num_gpus != 1:
+                raise ValueError("--job_name=worker: start one worker process per GPU "
+                                 "(--num_gpus=1) on this runtime")
             self.num_workers = self.world      # num_gpus == 1 per worker
             self.replicas_per_worker = 1
         else:

@@ -121,7 +121,11 @@ class UpdateEngine:
         self._ready_hi = 0
         self._launched = 0
         self._rng = np.random.RandomState(seed + 7919 * comm.rank)
-        self.relaxed = params.variable_consistency == "relaxed"
+        # --staged_vars (T/variable_mgr_util.py:236-393) software-pipelines the parameter-server
+        # traffic by one step through StagingAreas: the step computes on variables that miss
+        # the newest update. The deferred-exchange path below has the same one-step staleness
+        # and the same overlap (exchange of step k under the forward pass of step k+1).
+        self.relaxed = params.variable_consistency == "relaxed" or bool(params.staged_vars)
         if self.cuda:
             self.skip_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         # device-resident {lr, grad_scale, adam_t, -}: lets a captured CUDA graph see per-step

@@ -169,10 +169,12 @@ _D.DEFINE_integer("agg_small_grads_max_group", 10, "Most small tensors per folde
 _D.DEFINE_integer("allreduce_merge_scope", 1, "Accepted for compatibility.")
 _D.DEFINE_enum("job_name", "", ("ps", "worker", "controller", ""),
                "TF-cluster role; not supported on this build (single NVSwitch box).")
-_D.DEFINE_string("ps_hosts", "", "Accepted for compatibility.")
-_D.DEFINE_string("worker_hosts", "", "Accepted for compatibility.")
+_D.DEFINE_string("ps_hosts", "", "Comma-separated list of parameter-server hosts (accepted; "
+                 "the ps role has no work on this runtime).")
+_D.DEFINE_string("worker_hosts", "", "Comma-separated host:port list of the workers; with "
+                 "--job_name=worker it defines world size and the rendezvous address.")
 _D.DEFINE_string("controller_host", None, "Accepted for compatibility.")
-_D.DEFINE_integer("task_index", 0, "Accepted for compatibility.")
+_D.DEFINE_integer("task_index", 0, "Index of this task within --job_name (the worker's rank).")
 _D.DEFINE_string("server_protocol", "grpc", "Accepted for compatibility.")
 _D.DEFINE_boolean("cross_replica_sync", True, "Accepted for compatibility.")
 _D.DEFINE_string("horovod_device", "", "Accepted for compatibility.")
@@ -218,7 +220,6 @@ UNSUPPORTED_WHEN_SET = {
     "xla": "XLA is not available (no tracing compiler on the hot path)",
     "xla_compile": "XLA is not available (no tracing compiler on the hot path)",
     "trt_mode": "TensorRT conversion is not available",
-    "job_name": "TF cluster roles (ps/worker/controller) are not supported: one NVSwitch box",
 }
 
 Params = namedtuple("Params", list(flags.param_specs.keys()))  # type: ignore

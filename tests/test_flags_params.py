@@ -83,9 +83,16 @@ def test_invalid_combinations_raise(kw):
 
 
 def test_unsupported_features_fail_loudly_in_setup():
-    for kw in (dict(xla=True), dict(job_name="worker")):
+    for kw in (dict(xla=True), dict(job_name="worker"), dict(trt_mode="FP16")):
         with pytest.raises(ValueError):
             benchmark.setup(P.make_params(**kw))
+
+
+def test_ps_and_controller_roles_exit_cleanly():
+    for role in ("ps", "controller"):
+        with pytest.raises(SystemExit) as e:
+            benchmark.setup(P.make_params(job_name=role, ps_hosts="a:1", worker_hosts="b:2"))
+        assert e.value.code == 0
 
 
 def test_warmup_default_and_batch_sizes():

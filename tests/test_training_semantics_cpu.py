@@ -168,6 +168,38 @@ def test_two_ranks_match_simulation(extra, tmp_path):
     assert same == synced      # synchronous modes keep replicas bit-identical, others do not
 
 
+def test_tf_cluster_flags_start_workers_without_a_launcher(tmp_path):
+    """Reference-style launch (T/benchmark_cnn.py:1354-1406): one process per worker with
+    --job_name=worker --task_index=i --worker_hosts=...; no torchrun / launcher environment."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    hosts = "127.0.0.1:%d,127.0.0.1:%d" % (port, port + 1)
+    out = str(tmp_path)
+    env = dict(os.environ, PYTHONPATH=ROOT, OMP_NUM_THREADS="2")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    procs = []
+    for i in range(2):
+        kw = dict(BASE, variable_update="distributed_replicated", optimizer="sgd",
+                  job_name="worker", task_index=i, worker_hosts=hosts, ps_hosts="127.0.0.1:1")
+        procs.append(subprocess.Popen(
+            [sys.executable, os.path.join(ROOT, "tests", "helpers", "rank_worker.py"),
+             json.dumps(kw), out], cwd=ROOT, env=env, stdout=subprocess.PIPE,
+            stderr=subprocess.STDOUT, text=True))
+    for pr in procs:
+        o, _ = pr.communicate(timeout=600)
+        assert pr.returncode == 0, o[-3000:]
+    w0 = np.load(os.path.join(out, "rank0.npz"))["w"]
+    w1 = np.load(os.path.join(out, "rank1.npz"))["w"]
+    assert np.array_equal(w0, w1)          # averaged-gradient sync keeps the replicas identical
+    sim = _Sim(dict(BASE, variable_update="parameter_server", num_gpus=2, optimizer="sgd"), 2)
+    for k in range(BASE["num_batches"]):
+        sim.step(k)
+    assert np.allclose(w0, sim.stores[0].w32.numpy(), rtol=2e-5, atol=2e-6)
+
+
 def test_resume_from_checkpoint(tmp_path):
     kw = dict(BASE, optimizer="momentum", train_dir=str(tmp_path / "ckpt"), num_batches=2)
     bench, _, lines = _run_single(kw)
