@@ -310,6 +310,135 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// ---------------------------------------------------------------------------
+// Embedding lookup (NCF, T/models/experimental/official_ncf_model.py:62-83): one row of the
+// table per example, optionally only a column range of it (the MF / MLP halves of NeuMF share
+// one table). The gradient is dense (the reference's --sparse_to_dense_grads): the executor
+// zeroes the table's gradient and this kernel scatter-adds into it.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    embedding_gather_kernel(const __half* __restrict__ table, long long ldt, int col_lo,
+                            const int* __restrict__ ids, long long num_rows_table,
+                            __half* __restrict__ y, long long ldy, long long n, int cols) {
+  const int vpr = cols >> 3;
+  const long long total = n * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    long long id = ids[r];
+    id = id < 0 ? 0 : (id >= num_rows_table ? num_rows_table - 1 : id);
+    *reinterpret_cast<Half8*>(y + r * ldy + cv * 8) =
+        *reinterpret_cast<const Half8*>(table + id * ldt + col_lo + cv * 8);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    embedding_scatter_kernel(const __half* __restrict__ dy, long long lddy,
+                             const int* __restrict__ ids, long long num_rows_table,
+                             float* __restrict__ dtable, long long ldt, int col_lo, long long n,
+                             int cols) {
+  const int vpr = cols >> 3;
+  const long long total = n * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    long long id = ids[r];
+    id = id < 0 ? 0 : (id >= num_rows_table ? num_rows_table - 1 : id);
+    float g[8];
+    load8(dy + r * lddy + cv * 8, g);
+    float* dst = dtable + id * ldt + col_lo + cv * 8;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) atomicAdd(dst + k, g[k]);
+  }
+}
+
+// y = a * b ; backward: da (+)= dy * b, db (+)= dy * a
+__global__ void __launch_bounds__(256)
+    mul_fwd_kernel(const __half* __restrict__ a, long long lda, const __half* __restrict__ b,
+                   long long ldb, __half* __restrict__ y, long long ldy, long long rows, int C) {
+  const int vpr = C >> 3;
+  const long long total = rows * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    float u[8], v[8];
+    load8(a + r * lda + cv * 8, u);
+    load8(b + r * ldb + cv * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) u[k] *= v[k];
+    store8(y + r * ldy + cv * 8, u);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    mul_bwd_kernel(const __half* __restrict__ dy, long long lddy, const __half* __restrict__ other,
+                   long long ldo, __half* __restrict__ dx, long long lddx, int accumulate,
+                   long long rows, int C) {
+  const int vpr = C >> 3;
+  const long long total = rows * vpr;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / vpr;
+    const int cv = static_cast<int>(i - r * vpr);
+    float g[8], v[8];
+    load8(dy + r * lddy + cv * 8, g);
+    load8(other + r * ldo + cv * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] *= v[k];
+    if (accumulate) {
+      load8(dx + r * lddx + cv * 8, v);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += v[k];
+    }
+    store8(dx + r * lddx + cv * 8, g);
+  }
+}
+
+// NCF loss: 2-class softmax cross-entropy over [1, z] (the reference prepends a column of ones,
+// T/models/experimental/official_ncf_model.py:85-97). One block; deterministic tree reduction.
+// out[0] = mean loss, out[1] = number of correct predictions (as float), dz = scale*(p1 - y).
+__global__ void __launch_bounds__(1024)
+    ncf_loss_kernel(const float* __restrict__ z, long long ldz, const int* __restrict__ labels,
+                    int n, float scale, const float* __restrict__ dyn_scale,
+                    __half* __restrict__ dz, long long lddz, float* __restrict__ out) {
+  __shared__ float red[2][32];
+  const float sc = scale * (dyn_scale != nullptr ? *dyn_scale : 1.f);
+  float loss = 0.f, hits = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float v = z[i * ldz];
+    const int y = labels[i] != 0;
+    const float m = fmaxf(v, 1.f);
+    const float lse = m + __logf(__expf(1.f - m) + __expf(v - m));
+    loss += lse - (y ? v : 1.f);
+    const float p1 = __expf(v - lse);
+    hits += ((v > 1.f) == (y != 0)) ? 1.f : 0.f;
+    if (dz != nullptr) dz[i * lddz] = __float2half_rn(sc * (p1 - static_cast<float>(y)));
+  }
+  loss = warp_sum(loss);
+  hits = warp_sum(hits);
+  if ((threadIdx.x & 31) == 0) {
+    red[0][threadIdx.x >> 5] = loss;
+    red[1][threadIdx.x >> 5] = hits;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int nw = (blockDim.x + 31) >> 5;
+    float a = threadIdx.x < nw ? red[0][threadIdx.x] : 0.f;
+    float b = threadIdx.x < nw ? red[1][threadIdx.x] : 0.f;
+    a = warp_sum(a);
+    b = warp_sum(b);
+    if (threadIdx.x == 0) {
+      out[0] = a / static_cast<float>(n);
+      out[1] = b;
+      out[2] = b;
+      out[3] = 0.f;
+    }
+  }
+}
+
 }  // namespace kfb
 
 using namespace kfb;
@@ -420,6 +549,56 @@ extern "C" int kfb_channel_gather(const void* x, long long ldx, void* y, long lo
   KFB_REQUIRE(idx != nullptr, "channel_gather: null index");
   channel_gather_kernel<<<xgrid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
       (const __half*)x, ldx, (__half*)y, ldy, accumulate, rows, C, idx);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_embedding_gather(const void* table, long long ldt, int col_lo, const int* ids,
+                                    long long num_rows_table, void* y, long long ldy, long long n,
+                                    int cols, void* stream) {
+  KFB_REQ_C8(cols, "embedding_gather");
+  KFB_REQUIRE(col_lo % 8 == 0 && ldt % 8 == 0, "embedding_gather: col_lo/ld must be multiples of 8");
+  embedding_gather_kernel<<<xgrid_for(n * (cols / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)table, ldt, col_lo, ids, num_rows_table, (__half*)y, ldy, n, cols);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_embedding_scatter_add(const void* dy, long long lddy, const int* ids,
+                                         long long num_rows_table, float* dtable, long long ldt,
+                                         int col_lo, long long n, int cols, void* stream) {
+  KFB_REQ_C8(cols, "embedding_scatter_add");
+  embedding_scatter_kernel<<<xgrid_for(n * (cols / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)dy, lddy, ids, num_rows_table, dtable, ldt, col_lo, n, cols);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_mul_forward(const void* a, long long lda, const void* b, long long ldb, void* y,
+                               long long ldy, long long rows, int C, void* stream) {
+  KFB_REQ_C8(C, "mul_forward");
+  mul_fwd_kernel<<<xgrid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)a, lda, (const __half*)b, ldb, (__half*)y, ldy, rows, C);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_mul_backward(const void* dy, long long lddy, const void* other, long long ldo,
+                                void* dx, long long lddx, int accumulate, long long rows, int C,
+                                void* stream) {
+  KFB_REQ_C8(C, "mul_backward");
+  mul_bwd_kernel<<<xgrid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)dy, lddy, (const __half*)other, ldo, (__half*)dx, lddx, accumulate, rows, C);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_ncf_loss(const float* z, long long ldz, const int* labels, int n, float scale,
+                            const float* dyn_scale, void* dz, long long lddz, float* out,
+                            void* stream) {
+  KFB_REQUIRE(n > 0, "ncf_loss: empty batch");
+  ncf_loss_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(z, ldz, labels, n, scale, dyn_scale,
+                                                        (__half*)dz, lddz, out);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

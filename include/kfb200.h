@@ -243,6 +243,26 @@ long long kfb_dwconv_wgrad_workspace_bytes(const kfb_conv_desc* d);
 int kfb_dwconv_wgrad(const kfb_conv_desc* d, const void* x, long long ldx, const void* dy,
                      long long lddy, float* dw, void* workspace, long long workspace_bytes,
                      int accumulate, float scale, void* stream);
+/* Embedding lookup of a column range [col_lo, col_lo+cols) of a [rows][ldt] fp16 table, and the
+ * dense scatter-add of its gradient into the fp32 gradient of the table (zeroed by the caller;
+ * fp32 atomics, so the summation order is not fixed). NeuMF embeddings,
+ * T/models/experimental/official_ncf_model.py:62-83. */
+int kfb_embedding_gather(const void* table, long long ldt, int col_lo, const int* ids,
+                         long long num_rows_table, void* y, long long ldy, long long n, int cols,
+                         void* stream);
+int kfb_embedding_scatter_add(const void* dy, long long lddy, const int* ids,
+                              long long num_rows_table, float* dtable, long long ldt, int col_lo,
+                              long long n, int cols, void* stream);
+/* Elementwise product (the GMF branch of NeuMF) and its backward for one operand. */
+int kfb_mul_forward(const void* a, long long lda, const void* b, long long ldb, void* y,
+                    long long ldy, long long rows, int C, void* stream);
+int kfb_mul_backward(const void* dy, long long lddy, const void* other, long long ldo, void* dx,
+                     long long lddx, int accumulate, long long rows, int C, void* stream);
+/* NCF loss: 2-class softmax cross-entropy over [1, z] with labels in {0,1}
+ * (T/models/experimental/official_ncf_model.py:85-97). out[0] mean loss, out[1] correct count;
+ * dz (fp16, may be null) = scale * dyn * (p1 - y). */
+int kfb_ncf_loss(const float* z, long long ldz, const int* labels, int n, float scale,
+                 const float* dyn_scale, void* dz, long long lddz, float* out, void* stream);
 /* y[r][c] (+)= idx[c] >= 0 ? x[r][idx[c]] : 0 over C output channels (idx on the device):
  * converts between two zero-padded channel layouts of one logical tensor (nn/legalize.py). */
 int kfb_channel_gather(const void* x, long long ldx, void* y, long long ldy, int accumulate,

@@ -69,6 +69,9 @@ class SyntheticHostSource(InputSource):
 def create_input_source(params, dataset, model, batch, device, nclass, seed, rank, world,
                         train=True) -> InputSource:
     device = torch.device(device)
+    if hasattr(model, "make_input_source"):
+        # models whose inputs are not images (NCF ids, spectrograms, detection targets)
+        return model.make_input_source(batch, device, seed, rank)
     image_size, depth = model.image_size, model.depth
     if dataset.use_synthetic_gpu_inputs():
         if device.type == "cuda":

@@ -4,6 +4,7 @@ from __future__ import annotations
 
 from functools import partial
 
+from .experimental import official_ncf_model
 from . import (alexnet_model, densenet_model, googlenet_model, inception_model, lenet_model,
                mobilenet_v2, nasnet_model,
                official_resnet_model, overfeat_model, resnet_model, trivial_model, vgg_model)
@@ -22,6 +23,7 @@ _model_name_to_imagenet_model = {
     "mobilenet": mobilenet_v2.MobilenetModel,
     "nasnet": nasnet_model.NasnetModel,
     "nasnetlarge": nasnet_model.NasnetLargeModel,
+    "ncf": official_ncf_model.NcfModel,
 }
 _model_name_to_imagenet_model.update(resnet_model.imagenet_factories())
 _model_name_to_imagenet_model.update(official_resnet_model.factories())
@@ -41,7 +43,6 @@ _model_name_to_cifar_model.update(resnet_model.cifar_factories())
 _UNSUPPORTED = {
     "ssd300": "needs COCO + the object_detection package",
     "deepspeech2": "needs LibriSpeech; LSTM/CTC kernels not built",
-    "ncf": "needs the official NCF package",
 }
 
 

@@ -449,6 +449,40 @@ class NetBuilder:
         self.top_layer, self.top_size = node.output, total
         return self.top_layer
 
+    def embedding(self, ids: TensorRef, num_rows: int, dim: int, col_lo: int = 0,
+                  cols: Optional[int] = None, scope_name: str = "embedding",
+                  share_with: Optional[str] = None) -> TensorRef:
+        """Embedding lookup ``table[ids][col_lo:col_lo+cols]`` (Keras ``Embedding`` of the
+        official NeuMF model, T/models/experimental/official_ncf_model.py:62-83). The first
+        lookup of a table creates it (Glorot-uniform); later ones pass ``share_with`` (the
+        table's variable name) to read another column range of the same table."""
+        cols = dim if cols is None else cols
+        n = ids.shape[0]
+        params = {}
+        if share_with is None:
+            with self.scope(scope_name):
+                spec = ParamSpec(self._full("embeddings"), (num_rows, dim), (num_rows, dim),
+                                 "embedding", True, ("glorot_uniform", num_rows, dim))
+            params["table"] = spec
+            table = spec.name
+        else:
+            table = share_with
+        node = self.graph.add_node("embedding", "%s_%d" % (scope_name, self.counts["embedding"]),
+                                   [ids], (n, cols),
+                                   dict(table=table, num_rows=num_rows, dim=dim, col_lo=col_lo),
+                                   params)
+        self.counts["embedding"] += 1
+        self.top_layer, self.top_size = node.output, cols
+        return self.top_layer
+
+    def mul(self, a: TensorRef, b: TensorRef) -> TensorRef:
+        if a.shape != b.shape:
+            raise ValueError("mul: shapes differ")
+        node = self.graph.add_node("mul", "mul%d" % self.counts["mul"], [a, b], a.shape)
+        self.counts["mul"] += 1
+        self.top_layer, self.top_size = node.output, a.shape[-1]
+        return self.top_layer
+
     def pad_channels(self, before: int, after: int, input_layer=None) -> TensorRef:
         """Zero-pad the channel axis ("plan A" shortcut, T/models/resnet_model_legacy.py:239-247)."""
         x = self.top_layer if input_layer is None else input_layer

@@ -38,6 +38,9 @@ def _pad8(n: int) -> int:
     return (n + 7) // 8 * 8
 
 
+_TORCH_DTYPE = {"f16": torch.float16, "i32": torch.int32, "f32": torch.float32}
+
+
 class _Buf:
     """A 2-D fp16 view [rows][cols] with row stride ld (elements)."""
     __slots__ = ("t", "rows", "cols", "ld")
@@ -71,14 +74,15 @@ class CudaExecutor:
         self.buf: Dict[int, _Buf] = {}
         self.gbuf: Dict[int, _Buf] = {}
         self._alias: Dict[int, int] = {}
-        h, w, c = graph.input.shape[1:]
-        self.images = torch.zeros((n, h, w, c), dtype=torch.float16, device=dev)
-        self.buf[graph.input.id] = _Buf(self.images, n * h * w, c, c)
-        self.labels = torch.zeros((n,), dtype=torch.int32, device=dev)
-        # host batches are prefetched into a second buffer on a copy stream (double buffering)
-        self._img_bufs = [self.images, None]
-        self._lab_bufs = [self.labels, None]
+        # per-step inputs: primary input, extra inputs, labels (in the input source's order);
+        # host batches are prefetched into a second set on a copy stream (double buffering)
+        self._in_refs = [graph.input] + list(graph.extra_inputs)
+        specs = [(t.shape, t.dtype) for t in self._in_refs] + list(graph.label_specs)
+        first = [torch.zeros(tuple(shape), dtype=_TORCH_DTYPE[dt], device=dev)
+                 for shape, dt in specs]
+        self._in_sets = [first, None]
         self._cur = 0
+        self._bind_inputs(first)
         self._staged = False
         self._copy_stream = None
         self._ready = [torch.cuda.Event(), torch.cuda.Event()]
@@ -111,8 +115,11 @@ class CudaExecutor:
 
     def _mark_needs_grad(self, need_input_grad: bool) -> Dict[int, bool]:
         need = {self.graph.input.id: need_input_grad}
+        for t in self.graph.extra_inputs:
+            need[t.id] = False
         for node in self.graph.nodes:
-            has_param = any(p.trainable for p in node.params.values())
+            has_param = (any(p.trainable for p in node.params.values()) or
+                         node.op == "embedding")  # shared tables: the owner node holds the spec
             need[node.output.id] = has_param or any(need[t.id] for t in node.inputs)
         return need
 
@@ -266,6 +273,11 @@ class CudaExecutor:
         elif node.op == "pad_channels":
             if a["before"] % 8 or a["after"] % 8:
                 raise NotImplementedError("pad_channels: pads must be multiples of 8")
+        elif node.op == "embedding":
+            if node.params:
+                # dense gradient of the table is scatter-accumulated: zero it every backward
+                self._scatter_tables = getattr(self, "_scatter_tables", []) + \
+                    [node.params["table"].name]
         elif node.op == "relayout":
             info["index"] = torch.tensor(a["index"], dtype=torch.int32, device=dev)
             info["inverse"] = torch.tensor(a["inverse"], dtype=torch.int32, device=dev)
@@ -281,39 +293,47 @@ class CudaExecutor:
         return m * n * 4 * splits
 
     # ------------------------------------------------------------------ inputs
-    def _bind_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
-        self.images, self.labels = images, labels
-        b = self.buf[self.graph.input.id]
-        self.buf[self.graph.input.id] = _Buf(images, b.rows, b.cols, b.ld)
+    def _bind_inputs(self, tensors) -> None:
+        ni = len(self._in_refs)
+        for ref, t in zip(self._in_refs, tensors[:ni]):
+            if len(ref.shape) >= 2:
+                cols = ref.shape[-1]
+                rows = t.numel() // cols
+            else:
+                rows, cols = ref.shape[0], 1
+            self.buf[ref.id] = _Buf(t, rows, cols, cols)
+        self.images = tensors[0]
+        self.label_tensors = list(tensors[ni:])
+        self.labels = self.label_tensors[0]
 
-    def set_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
-        """Makes a batch the input of the next step. Device tensors of the right type are used
-        in place (the synthetic device source hands over the same cached buffers every step);
-        host tensors are copied on the compute stream (see stage_inputs for the overlapped
-        path)."""
-        ref = self._img_bufs[self._cur]
-        if (images.is_cuda and images.dtype == torch.float16 and images.is_contiguous() and
-                images.shape == ref.shape and labels.is_cuda and labels.dtype == torch.int32):
-            self._bind_inputs(images, labels)
+    def set_inputs(self, *tensors: torch.Tensor) -> None:
+        """Makes a batch (primary input, *extra inputs, *labels) the input of the next step.
+        Device tensors of the right type are used in place (the synthetic device source hands
+        over the same cached buffers every step); host tensors are copied on the compute stream
+        (see stage_inputs for the overlapped path)."""
+        mine = self._in_sets[self._cur]
+        if len(tensors) != len(mine):
+            raise ValueError("expected %d input tensors, got %d" % (len(mine), len(tensors)))
+        if all(t.is_cuda and t.dtype == m.dtype and t.is_contiguous() and t.shape == m.shape
+               for t, m in zip(tensors, mine)):
+            self._bind_inputs(list(tensors))
             return
-        img, lab = self._img_bufs[self._cur], self._lab_bufs[self._cur]
-        img.copy_(images, non_blocking=True)
-        lab.copy_(labels, non_blocking=True)
-        self._bind_inputs(img, lab)
+        for t, m in zip(tensors, mine):
+            m.copy_(t, non_blocking=True)
+        self._bind_inputs(mine)
 
-    def stage_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+    def stage_inputs(self, *tensors: torch.Tensor) -> None:
         """Starts the host->device copy of the NEXT step's batch on a copy stream into the back
-        buffer; it overlaps the kernels of the step that is currently enqueued."""
+        buffer set; it overlaps the kernels of the step that is currently enqueued."""
         b = 1 - self._cur
-        if self._img_bufs[b] is None:
-            self._img_bufs[b] = torch.zeros_like(self._img_bufs[self._cur])
-            self._lab_bufs[b] = torch.zeros_like(self._lab_bufs[self._cur])
+        if self._in_sets[b] is None:
+            self._in_sets[b] = [torch.zeros_like(t) for t in self._in_sets[self._cur]]
             self._copy_stream = torch.cuda.Stream(device=self.device)
         cs = self._copy_stream
         cs.wait_event(self._free[b])  # the forward pass that last read this buffer is done
         with torch.cuda.stream(cs):
-            self._img_bufs[b].copy_(images, non_blocking=True)
-            self._lab_bufs[b].copy_(labels, non_blocking=True)
+            for t, m in zip(tensors, self._in_sets[b]):
+                m.copy_(t, non_blocking=True)
             self._ready[b].record(cs)
         self._staged = True
 
@@ -325,7 +345,7 @@ class CudaExecutor:
         torch.cuda.current_stream(self.device).wait_event(self._ready[b])
         self._cur = b
         self._staged = False
-        self._bind_inputs(self._img_bufs[b], self._lab_bufs[b])
+        self._bind_inputs(self._in_sets[b])
 
     # ------------------------------------------------------------------ forward
     def forward(self, train: bool = True) -> None:
@@ -495,6 +515,36 @@ class CudaExecutor:
                         i64(y.ld), i64(x.rows), i32(x.cols), i32(0), s)
             off += x.cols
 
+    def _fwd_embedding(self, node, train, s):
+        a = node.attrs
+        ids, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        native.call("embedding_gather", self._w16(a["table"]), i64(a["dim"]), i32(a["col_lo"]),
+                    ids.p, i64(a["num_rows"]), y.p, i64(y.ld), i64(y.rows), i32(y.cols), s)
+
+    def _bwd_embedding(self, node, s):
+        a = node.attrs
+        ids, gy = self.buf[node.inputs[0].id], self._grad(node.output)
+        native.call("embedding_scatter_add", gy.p, i64(gy.ld), ids.p, i64(a["num_rows"]),
+                    self._g32(a["table"]), i64(a["dim"]), i32(a["col_lo"]), i64(gy.rows),
+                    i32(gy.cols), s)
+
+    def _fwd_mul(self, node, train, s):
+        a, b = self.buf[node.inputs[0].id], self.buf[node.inputs[1].id]
+        y = self.buf[node.output.id]
+        native.call("mul_forward", a.p, i64(a.ld), b.p, i64(b.ld), y.p, i64(y.ld), i64(a.rows),
+                    i32(_pad8(a.cols)), s)
+
+    def _bwd_mul(self, node, s):
+        gy = self._grad(node.output)
+        for idx, t in enumerate(node.inputs):
+            if not self.needs_grad[t.id]:
+                continue
+            other = self.buf[node.inputs[1 - idx].id]
+            gx = self._grad(t)
+            native.call("mul_backward", gy.p, i64(gy.ld), other.p, i64(other.ld), gx.p,
+                        i64(gx.ld), i32(self._acc(node, idx)), i64(gy.rows),
+                        i32(_pad8(gy.cols)), s)
+
     def _fwd_relayout(self, node, train, s):
         x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
         native.call("channel_gather", x.p, i64(x.ld), y.p, i64(y.ld), i32(0), i64(x.rows),
@@ -525,7 +575,17 @@ class CudaExecutor:
         s = self._s()
         g = self.graph
         n = g.batch_size
-        heads = [(g.logits, 1.0, 0)]
+        kind = g.loss["kind"]
+        heads = [(g.logits, 1.0, 0)] if kind == "softmax_xent" else []
+        if kind == "ncf":
+            lb = self.buf[g.logits.id]
+            gb = self._grad(g.logits) if backward else None
+            native.call("ncf_loss", lb.p, i64(lb.ld), ptr(self.labels), i32(n),
+                        f32(loss_scale / n), ptr(dyn_scale), gb.p if gb else None,
+                        i64(gb.ld if gb else 0), ptr(self.loss_out), s)
+        elif kind != "softmax_xent":
+            from . import losses_cuda
+            losses_cuda.run(self, kind, loss_scale, dyn_scale, backward, s)
         if g.aux_logits is not None:
             heads.append((g.aux_logits, self.aux_weight, 1))
         for t, weight, slot in heads:
@@ -538,6 +598,8 @@ class CudaExecutor:
                         ctypes.c_void_p(self.loss_out.data_ptr() + 16 * slot), s)
         if not backward:
             return
+        for name in getattr(self, "_scatter_tables", []):
+            self.store.view(name, "grad").zero_()
         for node in reversed(g.nodes):
             if not self.needs_grad[node.output.id]:
                 continue

@@ -50,9 +50,20 @@ class RefExecutor:
         self.step_index = 0
 
     # -- inputs ---------------------------------------------------------------
-    def set_inputs(self, images: torch.Tensor, labels: torch.Tensor) -> None:
-        self.images = images.to(self.device, self.dtype)
-        self.labels = labels.to(self.device, torch.long)
+    def set_inputs(self, *tensors: torch.Tensor) -> None:
+        """(primary input, *extra inputs, *labels) in the order the input source yields them."""
+        g = self.graph
+        ne = len(g.extra_inputs)
+
+        def conv(t, dtype):
+            if dtype == "i32":
+                return t.to(self.device, torch.long)
+            return t.to(self.device, self.dtype)
+        self.images = conv(tensors[0], g.input.dtype)
+        self.extras = [conv(t, ref.dtype) for t, ref in zip(tensors[1:1 + ne], g.extra_inputs)]
+        labs = tensors[1 + ne:]
+        self.label_tensors = [conv(t, spec[1]) for t, spec in zip(labs, g.label_specs)]
+        self.labels = self.label_tensors[0]
 
     def _param(self, spec, train: bool) -> torch.Tensor:
         """Leaf tensor in the *TF* layout so gradients map back trivially."""
@@ -79,6 +90,8 @@ class RefExecutor:
         g = self.graph
         self._leaves.clear()
         vals = {g.input.id: self.images}
+        for ref, t in zip(g.extra_inputs, getattr(self, "extras", [])):
+            vals[ref.id] = t
         for node in g.nodes:
             y = self._run(node, [vals[t.id] for t in node.inputs], train)
             if self.emulate_fp16 and node.output is not g.logits and \
@@ -100,6 +113,15 @@ class RefExecutor:
             y = F.conv2d(x, w, b, stride=(a["sh"], a["sw"]))
             y = _act(y, a["activation"])
             return y.permute(0, 2, 3, 1)
+        if op == "embedding":
+            name = a["table"]
+            if name not in self._leaves:
+                self._param(self.graph.params[name], train)
+            table = self._leaves[name]
+            lo = a["col_lo"]
+            return table[xs[0].clamp(0, a["num_rows"] - 1)][:, lo:lo + node.output.shape[-1]]
+        if op == "mul":
+            return xs[0] * xs[1]
         if op == "dwconv":
             x = xs[0].permute(0, 3, 1, 2)
             w = self._param(node.params["kernel"], train)
@@ -194,14 +216,26 @@ class RefExecutor:
                       on_grads_ready: Optional[Callable[[int, int], None]] = None) -> None:
         g = self.graph
         logits = self._vals[g.logits.id].float()
-        loss = F.cross_entropy(logits, self.labels)
-        if g.aux_logits is not None:
-            loss = loss + self.aux_weight * F.cross_entropy(self._vals[g.aux_logits.id].float(),
-                                                            self.labels)
-        with torch.no_grad():
-            top5 = logits.topk(min(5, logits.shape[1]), dim=1).indices
-            t1 = int((top5[:, 0] == self.labels).sum())
-            t5 = int((top5 == self.labels[:, None]).any(1).sum())
+        kind = g.loss["kind"]
+        if kind == "softmax_xent":
+            loss = F.cross_entropy(logits, self.labels)
+            if g.aux_logits is not None:
+                loss = loss + self.aux_weight * F.cross_entropy(
+                    self._vals[g.aux_logits.id].float(), self.labels)
+            with torch.no_grad():
+                top5 = logits.topk(min(5, logits.shape[1]), dim=1).indices
+                t1 = int((top5[:, 0] == self.labels).sum())
+                t5 = int((top5 == self.labels[:, None]).any(1).sum())
+        elif kind == "ncf":
+            # softmax over [1, z]: T/models/experimental/official_ncf_model.py:85-97
+            two = torch.cat([torch.ones_like(logits), logits], dim=1)
+            loss = F.cross_entropy(two, (self.labels != 0).long())
+            with torch.no_grad():
+                t1 = int(((logits[:, 0] > 1.0) == (self.labels != 0)).sum())
+                t5 = t1
+        else:
+            from . import losses_ref
+            loss, t1, t5 = losses_ref.compute(kind, g, self._vals, self.label_tensors)
         self.last = (float(loss.detach()), t1, t5)
         if not backward:
             return

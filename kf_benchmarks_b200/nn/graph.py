@@ -51,6 +51,7 @@ class TensorRef:
     shape: Tuple[int, ...]
     producer: Optional["Node"] = None
     consumers: List["Node"] = field(default_factory=list)
+    dtype: str = "f16"              # f16 activations; i32 ids / labels; f32 targets
 
     @property
     def channels(self) -> int:
@@ -75,15 +76,34 @@ class Node:
 
 
 class Graph:
-    def __init__(self, batch_size: int, image_shape: Tuple[int, int, int]):
+    def __init__(self, batch_size: int, image_shape: Optional[Tuple[int, int, int]] = None,
+                 input_shape: Optional[Tuple[int, ...]] = None, input_dtype: str = "f16"):
+        """``image_shape`` (h, w, c) gives the usual NHWC image input; models with other
+        inputs (NCF ids, spectrograms ...) pass the full ``input_shape`` / ``input_dtype``."""
         self.batch_size = batch_size
         self.nodes: List[Node] = []
         self.tensors: List[TensorRef] = []
         self.params: Dict[str, ParamSpec] = {}
-        h, w, c = image_shape
-        self.input = self.new_tensor((batch_size, h, w, c))
+        if input_shape is None:
+            h, w, c = image_shape
+            input_shape = (batch_size, h, w, c)
+        self.input = self.new_tensor(input_shape)
+        self.input.dtype = input_dtype
+        # further per-step inputs (NCF item ids ...), in the order the input source yields them
+        # after the primary input and before the labels
+        self.extra_inputs: List[TensorRef] = []
+        # label tensors: (shape, dtype); classification has one int32 label per example
+        self.label_specs: List[Tuple[Tuple[int, ...], str]] = [((batch_size,), "i32")]
+        # loss head run on ``logits`` (see the executors): softmax_xent | ncf | ssd | ctc
+        self.loss: Dict[str, Any] = {"kind": "softmax_xent"}
         self.logits: Optional[TensorRef] = None
         self.aux_logits: Optional[TensorRef] = None
+
+    def add_input(self, shape, dtype: str = "f16") -> TensorRef:
+        t = self.new_tensor(shape)
+        t.dtype = dtype
+        self.extra_inputs.append(t)
+        return t
 
     def new_tensor(self, shape) -> TensorRef:
         t = TensorRef(len(self.tensors), tuple(int(s) for s in shape))

@@ -70,11 +70,15 @@ def legalize(graph: Graph) -> Graph:
     """Returns a padded copy of ``graph`` (or ``graph`` itself if it is already legal)."""
     if not needs_legalization(graph):
         return graph
-    h, w, c = graph.input.shape[1:]
-    out = Graph(graph.batch_size, (h, w, c))
+    c = graph.input.shape[-1]
+    out = Graph(graph.batch_size, input_shape=graph.input.shape, input_dtype=graph.input.dtype)
     out.logical = graph
+    out.label_specs = list(graph.label_specs)
+    out.loss = dict(graph.loss)
     # old tensor id -> (new tensor, channel map, physical channels)
     tmap: Dict[int, Tuple[TensorRef, ChanMap, int]] = {graph.input.id: (out.input, None, c)}
+    for t in graph.extra_inputs:
+        tmap[t.id] = (out.add_input(t.shape, t.dtype), None, t.shape[-1])
 
     def relayout(src, logical, want_map, want_phys):
         """Brings operand ``src`` = (tensor, map, phys) to the layout (want_map, want_phys)."""
@@ -143,6 +147,13 @@ def legalize(graph: Graph) -> Graph:
                 raise NotImplementedError("lrn over a padded channel layout")
             shape, omap, ophys = t_out.shape, xm, xp
         elif op == "add":
+            for i in range(1, len(ins)):
+                ins[i] = relayout(ins[i], logical_c, xm, xp)
+            new_inputs = [i[0] for i in ins]
+            shape, omap, ophys = t_out.shape[:-1] + (xp,), xm, xp
+        elif op == "embedding":
+            shape, omap, ophys = t_out.shape, None, t_out.shape[-1]
+        elif op == "mul":
             for i in range(1, len(ins)):
                 ins[i] = relayout(ins[i], logical_c, xm, xp)
             new_inputs = [i[0] for i in ins]

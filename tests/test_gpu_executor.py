@@ -30,6 +30,7 @@ import executor_check  # noqa: E402
     ("densenet40_k12", "cifar10", 8, 0.99, 5e-3),      # growth 12: phantom-channel layout
     ("mobilenet", "imagenet", 2, 0.6, 5e-2),           # depthwise + ReLU6
     ("official_resnet18", "imagenet", 2, 0.9, 5e-3),
+    ("ncf", "imagenet", 512, 0.999, 5e-3),             # embeddings + GMF/MLP + [1, z] softmax
 ])
 def test_executor_matches_reference(model, data, batch, min_cos, max_logit_rel):
     r = executor_check.compare(model, data, batch)

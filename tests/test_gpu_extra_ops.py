@@ -108,3 +108,48 @@ def test_channel_gather_and_inverse():
     native.call("channel_gather", ptr(x), i64(cin), ptr(y), i64(cout), i32(1), i64(rows),
                 i32(cout), ptr(idx), _s())
     assert torch.allclose(y.float(), 2 * ref.float(), atol=1e-2)
+
+
+def test_embedding_gather_scatter_and_mul():
+    g = torch.Generator(device="cuda").manual_seed(11)
+    rows_t, dim, n, lo, cols = 500, 48, 1000, 16, 32
+    table = torch.randn(rows_t, dim, device="cuda", generator=g).half()
+    ids = torch.randint(0, rows_t, (n,), device="cuda", generator=g, dtype=torch.int32)
+    y = torch.empty(n, cols, device="cuda", dtype=torch.float16)
+    native.call("embedding_gather", ptr(table), i64(dim), i32(lo), ptr(ids), i64(rows_t), ptr(y),
+                i64(cols), i64(n), i32(cols), _s())
+    assert torch.equal(y, table[ids.long(), lo:lo + cols])
+    dy = torch.randn(n, cols, device="cuda", generator=g).half()
+    dt = torch.zeros(rows_t, dim, device="cuda")
+    native.call("embedding_scatter_add", ptr(dy), i64(cols), ptr(ids), i64(rows_t), ptr(dt),
+                i64(dim), i32(lo), i64(n), i32(cols), _s())
+    ref = torch.zeros(rows_t, dim, device="cuda")
+    ref[:, lo:lo + cols].index_add_(0, ids.long(), dy.float())
+    assert torch.allclose(dt, ref, atol=1e-3, rtol=1e-3)
+    a = torch.randn(n, cols, device="cuda", generator=g).half()
+    b = torch.randn(n, cols, device="cuda", generator=g).half()
+    out, da = torch.empty_like(a), torch.empty_like(a)
+    native.call("mul_forward", ptr(a), i64(cols), ptr(b), i64(cols), ptr(out), i64(cols), i64(n),
+                i32(cols), _s())
+    assert torch.allclose(out.float(), a.float() * b.float(), atol=1e-2, rtol=1e-2)
+    native.call("mul_backward", ptr(dy), i64(cols), ptr(b), i64(cols), ptr(da), i64(cols), i32(0),
+                i64(n), i32(cols), _s())
+    assert torch.allclose(da.float(), dy.float() * b.float(), atol=1e-2, rtol=1e-2)
+
+
+def test_ncf_loss_matches_two_class_softmax():
+    g = torch.Generator(device="cuda").manual_seed(3)
+    n = 3000
+    z = torch.randn(n, 8, device="cuda", generator=g) * 3
+    labels = torch.randint(0, 2, (n,), device="cuda", generator=g, dtype=torch.int32)
+    dz = torch.zeros(n, 8, device="cuda", dtype=torch.float16)
+    out = torch.zeros(8, device="cuda")
+    native.call("ncf_loss", ptr(z), i64(8), ptr(labels), i32(n), f32(64.0 / n), None, ptr(dz),
+                i64(8), ptr(out), _s())
+    zf = z[:, 0].clone().requires_grad_(True)
+    two = torch.stack([torch.ones_like(zf), zf], dim=1)
+    loss = F.cross_entropy(two, labels.long())
+    (loss * 64.0).backward()
+    assert abs(float(out[0]) - float(loss)) < 1e-4
+    assert torch.allclose(dz[:, 0].float(), zf.grad, atol=2e-4, rtol=1e-2)
+    assert int(out[1]) == int(((z[:, 0] > 1.0) == (labels != 0)).sum())

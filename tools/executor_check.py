@@ -46,18 +46,23 @@ def compare(model_name, data_name, batch, image_size=None, seed=0, verbose=False
     st_cpu.state.copy_(st_gpu.state)
     st_gpu.w32.copy_(st_cpu.w32)
     gen = torch.Generator().manual_seed(seed)
-    h = model.image_size
-    images = (torch.randn(batch, h, h, 3, generator=gen) * 0.5).half()
-    labels = torch.randint(0, nclass - 1, (batch,), generator=gen)
+    if hasattr(model, "make_input_source"):
+        model.set_batch_size(batch)
+        inputs = list(model.make_input_source(batch, "cpu", seed).next_batch())
+    else:
+        h = model.image_size
+        images = (torch.randn(batch, h, h, 3, generator=gen) * 0.5).half()
+        labels = torch.randint(0, nclass - 1, (batch,), generator=gen)
+        inputs = [images, labels.int()]
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
     ex = CudaExecutor(g, st_gpu, nclass)
-    ex.set_inputs(images.cuda(), labels.int().cuda())
+    ex.set_inputs(*[t.cuda() for t in inputs])
     ex.forward(True)
     ex.loss_backward(loss_scale=LOSS_SCALE)
     torch.cuda.synchronize()
     ref = RefExecutor(g, st_cpu, nclass, emulate_fp16=True)
-    ref.set_inputs(images.float(), labels)
+    ref.set_inputs(*[t.float() if t.dtype == torch.float16 else t for t in inputs])
     # dropout: both must draw the same mask -> disable by comparing only deterministic models
     ref.forward(True)
     if verbose:
