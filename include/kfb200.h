@@ -273,6 +273,21 @@ int kfb_drop_path(const void* x, long long ldx, void* y, long long ldy, int accu
                   long long rows, long long rows_per_sample, int C, float keep_prob,
                   unsigned long long seed, unsigned long long offset, void* stream);
 
+/* ---- loss heads (csrc/loss_kernels.cu) ---------------------------------------------------- */
+/* SSD-300 multibox loss (T/models/ssd_model.py:299-384): smooth-L1 on matched anchors + softmax
+ * cross-entropy on positives and the 3:1 hardest negatives, each normalised by the sample's
+ * number of matched boxes, mean over the batch. Reads the 6 loc / 6 conf head convolutions
+ * (NHWC fp16, row strides ld_*) in place and writes their gradients in place; gt_loc
+ * [N,A,4], gt_label [N,A], num_matched [N] are fp32 as in the reference's input pipeline.
+ * out[0] total, out[4] class part, out[5] box part. dloc/dconf may be null (forward only). */
+long long kfb_ssd_loss_workspace_floats(int batch, int num_anchors);
+int kfb_ssd_loss(int batch, int num_classes, const int* map_size, const int* map_ndef,
+                 void* const* loc, const long long* ld_loc, void* const* conf,
+                 const long long* ld_conf, void* const* dloc, void* const* dconf,
+                 const float* gt_loc, const float* gt_label, const float* num_matched,
+                 int negs_per_positive, float scale, const float* dyn_scale, float* workspace,
+                 long long workspace_floats, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

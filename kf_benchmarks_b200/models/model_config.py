@@ -5,6 +5,7 @@ from __future__ import annotations
 from functools import partial
 
 from .experimental import official_ncf_model
+from . import ssd_model
 from . import (alexnet_model, densenet_model, googlenet_model, inception_model, lenet_model,
                mobilenet_v2, nasnet_model,
                official_resnet_model, overfeat_model, resnet_model, trivial_model, vgg_model)
@@ -41,14 +42,18 @@ _model_name_to_cifar_model.update(resnet_model.cifar_factories())
 # Models of the reference that need external repositories / datasets the fork itself
 # disabled. They resolve to a clear error instead of an import failure.
 _UNSUPPORTED = {
-    "ssd300": "needs COCO + the object_detection package",
     "deepspeech2": "needs LibriSpeech; LSTM/CTC kernels not built",
 }
+
+
+_model_name_to_object_detection_model = {"ssd300": ssd_model.SSD300Model}
 
 
 def _get_model_map(dataset_name):
     if dataset_name == "cifar10":
         return _model_name_to_cifar_model
+    if dataset_name == "coco":
+        return _model_name_to_object_detection_model
     if dataset_name in ("imagenet", "synthetic"):
         return _model_name_to_imagenet_model
     raise ValueError("Invalid dataset name: %s" % dataset_name)

@@ -108,6 +108,9 @@ class CudaExecutor:
         self.workspace = torch.zeros((max(self._ws_need // 4, 1024),), dtype=torch.float32,
                                      device=dev)
         self._plan_grad_writes()
+        if graph.loss["kind"] not in ("softmax_xent", "ncf"):
+            from . import losses_cuda
+            losses_cuda.prepare(self)
 
     # ------------------------------------------------------------------ helpers
     def _s(self):

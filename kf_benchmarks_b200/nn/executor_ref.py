@@ -99,7 +99,7 @@ class RefExecutor:
                 y = _RoundFp16.apply(y)
             vals[node.output.id] = y
         self._vals = vals
-        return vals[g.logits.id]
+        return vals[g.logits.id] if g.logits is not None else None
 
     def _run(self, node: Node, xs, train: bool) -> torch.Tensor:
         a = node.attrs
@@ -215,7 +215,7 @@ class RefExecutor:
     def loss_backward(self, loss_scale: float = 1.0, backward: bool = True,
                       on_grads_ready: Optional[Callable[[int, int], None]] = None) -> None:
         g = self.graph
-        logits = self._vals[g.logits.id].float()
+        logits = self._vals[g.logits.id].float() if g.logits is not None else None
         kind = g.loss["kind"]
         if kind == "softmax_xent":
             loss = F.cross_entropy(logits, self.labels)

@@ -216,5 +216,8 @@ def legalize(graph: Graph) -> Graph:
     for attr in ("extra",):
         if hasattr(graph, attr):
             setattr(out, attr, getattr(graph, attr))
+    for key in ("loc", "conf"):     # loss heads that name tensors (SSD)
+        if key in out.loss:
+            out.loss[key] = [tmap[tid][0].id for tid in graph.loss[key]]
     out.tensor_layout = {tid: (v[0].id, v[1], v[2]) for tid, v in tmap.items()}
     return out

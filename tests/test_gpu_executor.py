@@ -31,10 +31,12 @@ import executor_check  # noqa: E402
     ("mobilenet", "imagenet", 2, 0.6, 5e-2),           # depthwise + ReLU6
     ("official_resnet18", "imagenet", 2, 0.9, 5e-3),
     ("ncf", "imagenet", 512, 0.999, 5e-3),             # embeddings + GMF/MLP + [1, z] softmax
+    ("ssd300", "coco", 2, 0.9, None),                  # multibox loss on the head convs
 ])
 def test_executor_matches_reference(model, data, batch, min_cos, max_logit_rel):
     r = executor_check.compare(model, data, batch)
-    assert r["logits_rel"] < max_logit_rel, r
+    if max_logit_rel is not None:
+        assert r["logits_rel"] < max_logit_rel, r
     assert r["grad_cosine"] > min_cos, r
     assert abs(r["loss_gpu"] - r["loss_ref"]) < 0.02 * abs(r["loss_ref"]), r
     assert r["moving_stats_rel"] < 2e-2, r

@@ -153,3 +153,50 @@ def test_ncf_loss_matches_two_class_softmax():
     assert abs(float(out[0]) - float(loss)) < 1e-4
     assert torch.allclose(dz[:, 0].float(), zf.grad, atol=2e-4, rtol=1e-2)
     assert int(out[1]) == int(((z[:, 0] > 1.0) == (labels != 0)).sum())
+
+
+def test_ssd_multibox_loss_and_gradients():
+    """csrc/loss_kernels.cu vs nn/losses_ref.ssd_loss on small heads with real positives."""
+    from kf_benchmarks_b200.nn import losses_ref
+    g = torch.Generator(device="cuda").manual_seed(21)
+    n, L = 3, 11
+    sizes, ndef = (6, 4, 3, 2, 1, 1), (4, 6, 6, 6, 4, 4)
+    locs = [torch.randn(n, s, s, d * 4, device="cuda", generator=g).half()
+            for s, d in zip(sizes, ndef)]
+    lds = [((d * L + 7) // 8) * 8 for d in ndef]                      # padded rows (phantom lanes)
+    confs = [(torch.randn(n, s, s, ld, device="cuda", generator=g) * 2).half()
+             for s, ld in zip(sizes, lds)]
+    A = sum(s * s * d for s, d in zip(sizes, ndef))
+    gt_loc = torch.randn(n, A, 4, device="cuda", generator=g) * 1.5
+    gt_label = (torch.rand(n, A, device="cuda", generator=g) < 0.1).float() * \
+        torch.randint(1, L, (n, A), device="cuda", generator=g).float()
+    nm = torch.tensor([3.0, 1.7, 9.2], device="cuda")
+    dlocs = [torch.full_like(t, 7.0) for t in locs]
+    dconfs = [torch.zeros_like(t) for t in confs]
+    fn = native.load().kfb_ssd_loss_workspace_floats
+    fn.restype = ctypes.c_longlong
+    ws = torch.zeros(int(fn(i32(n), i32(A))), device="cuda")
+    out = torch.zeros(8, device="cuda")
+
+    def parr(ts):
+        return (ctypes.c_void_p * 6)(*[t.data_ptr() for t in ts])
+    scale = 128.0
+    native.call("ssd_loss", i32(n), i32(L), (ctypes.c_int * 6)(*sizes), (ctypes.c_int * 6)(*ndef),
+                parr(locs), (ctypes.c_longlong * 6)(*[d * 4 for d in ndef]), parr(confs),
+                (ctypes.c_longlong * 6)(*lds), parr(dlocs), parr(dconfs), ptr(gt_loc),
+                ptr(gt_label), ptr(nm), i32(3), f32(scale / n), None, ptr(ws), i64(ws.numel()),
+                ptr(out), _s())
+    # oracle
+    lf = [t.float().requires_grad_(True) for t in locs]
+    cf = [t.float().requires_grad_(True) for t in confs]
+    pl = torch.cat([t.reshape(n, s, s, d, 4).permute(0, 3, 1, 2, 4).reshape(n, -1, 4)
+                    for t, s, d in zip(lf, sizes, ndef)], 1)
+    pc = torch.cat([t[..., :d * L].reshape(n, s, s, d, L).permute(0, 3, 1, 2, 4).reshape(n, -1, L)
+                    for t, s, d in zip(cf, sizes, ndef)], 1)
+    total, cls, box = losses_ref.ssd_loss(pl, pc, gt_loc, gt_label, nm, 3)
+    (total * scale).backward()
+    assert abs(float(out[0]) - float(total)) < 2e-3 * float(total)
+    assert abs(float(out[4]) - float(cls)) < 2e-3 * float(cls)
+    assert abs(float(out[5]) - float(box)) < 2e-3 * float(box) + 1e-4
+    for got, ref in zip(dlocs + dconfs, lf + cf):
+        assert torch.allclose(got.float(), ref.grad, atol=2e-2, rtol=2e-2)

@@ -83,8 +83,11 @@ def compare(model_name, data_name, batch, image_size=None, seed=0, verbose=False
             print(line)
     torch.cuda.synchronize()
     out = {"model": model_name, "batch": batch}
-    lg, lr = ex.logits().float(), ref.logits().float()
-    out["logits_rel"] = float((lg - lr).abs().max() / (lr.abs().max() + 1e-6))
+    if g.logits is not None:
+        lg, lr = ex.logits().float(), ref.logits().float()
+        out["logits_rel"] = float((lg - lr).abs().max() / (lr.abs().max() + 1e-6))
+    else:
+        out["logits_rel"] = None
     out["loss_gpu"], out["loss_ref"] = ex.read_loss()[0], ref.read_loss()[0]
     gg, gr = st_gpu.grad, st_cpu.grad
     worst = (None, 0.0)

@@ -6,6 +6,7 @@ run() { echo "### $*" >> gpurun_out/exec_check2.log; timeout 300 python tools/ex
 for m in "$@"; do
   case $m in
     densenet*|resnet20*|nasnet_cifar) run --model ${m%_cifar} --data_name cifar10 --batch 8 ;;
+    ssd300) run --model ssd300 --data_name coco --batch 2 ;;
     *) run --model $m --batch 2 ;;
   esac
 done
