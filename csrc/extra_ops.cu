@@ -602,3 +602,105 @@ extern "C" int kfb_ncf_loss(const float* z, long long ldz, const int* labels, in
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------------------
+// LSTM cell (tf.nn.rnn_cell.BasicLSTMCell, forget_bias 1, gate order i, j, f, o -
+// T/models/experimental/deepspeech.py:121-126,232-268). The matrix products of a layer are
+// tcgen05 GEMMs (input projection for all steps at once, recurrent projection per step); these
+// kernels are the pointwise part of one time step for the whole batch.
+// ---------------------------------------------------------------------------
+namespace kfb {
+
+__device__ __forceinline__ float sigmoidf_(float v) { return 1.f / (1.f + __expf(-v)); }
+
+// gates_io: in = x-projection pre-activations of this step, out = activated gates (saved for
+// backward). gh = recurrent projection. Writes c, h (into the layer output) and h again into
+// the "previous hidden state" slot of the next step (operand of the recurrent wgrad GEMM).
+__global__ void __launch_bounds__(256)
+    lstm_cell_fwd_kernel(__half* __restrict__ gates_io, long long ldg,
+                         const __half* __restrict__ gh, long long ldgh,
+                         const float* __restrict__ bias, const float* __restrict__ c_prev,
+                         long long ldcp, float* __restrict__ c_out, long long ldc,
+                         __half* __restrict__ h_out, long long ldh,
+                         __half* __restrict__ h_next, long long ldhn, int n, int H,
+                         float forget_bias) {
+  const int total = n * H;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int b = i / H, u = i - b * H;
+    __half* g = gates_io + static_cast<long long>(b) * ldg;
+    const __half* r = gh + static_cast<long long>(b) * ldgh;
+    const float gi = __half2float(g[u]) + __half2float(r[u]) + bias[u];
+    const float gj = __half2float(g[H + u]) + __half2float(r[H + u]) + bias[H + u];
+    const float gf = __half2float(g[2 * H + u]) + __half2float(r[2 * H + u]) + bias[2 * H + u];
+    const float go = __half2float(g[3 * H + u]) + __half2float(r[3 * H + u]) + bias[3 * H + u];
+    const float ai = sigmoidf_(gi), aj = tanhf(gj), af = sigmoidf_(gf + forget_bias),
+                ao = sigmoidf_(go);
+    const float cp = c_prev != nullptr ? c_prev[static_cast<long long>(b) * ldcp + u] : 0.f;
+    const float c = cp * af + ai * aj;
+    const float h = tanhf(c) * ao;
+    g[u] = __float2half_rn(ai);
+    g[H + u] = __float2half_rn(aj);
+    g[2 * H + u] = __float2half_rn(af);
+    g[3 * H + u] = __float2half_rn(ao);
+    c_out[static_cast<long long>(b) * ldc + u] = c;
+    const __half hh = __float2half_rn(h);
+    h_out[static_cast<long long>(b) * ldh + u] = hh;
+    if (h_next != nullptr) h_next[static_cast<long long>(b) * ldhn + u] = hh;
+  }
+}
+
+// gates_io: in = activated gates of this step, out = gradients w.r.t. the pre-activations.
+// dh = dy (this step's slice of the output gradient) + dh_rec (from the following step).
+// dc_io: in = dL/dc from the following step, out = dL/dc for the preceding step.
+__global__ void __launch_bounds__(256)
+    lstm_cell_bwd_kernel(__half* __restrict__ gates_io, long long ldg,
+                         const __half* __restrict__ dy, long long lddy,
+                         const __half* __restrict__ dh_rec, long long lddh,
+                         const float* __restrict__ c, long long ldc,
+                         const float* __restrict__ c_prev, long long ldcp,
+                         float* __restrict__ dc_io, int n, int H) {
+  const int total = n * H;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int b = i / H, u = i - b * H;
+    __half* g = gates_io + static_cast<long long>(b) * ldg;
+    const float ai = __half2float(g[u]), aj = __half2float(g[H + u]),
+                af = __half2float(g[2 * H + u]), ao = __half2float(g[3 * H + u]);
+    float dh = __half2float(dy[static_cast<long long>(b) * lddy + u]);
+    if (dh_rec != nullptr) dh += __half2float(dh_rec[static_cast<long long>(b) * lddh + u]);
+    const float tc = tanhf(c[static_cast<long long>(b) * ldc + u]);
+    const float cp = c_prev != nullptr ? c_prev[static_cast<long long>(b) * ldcp + u] : 0.f;
+    const float dc = dc_io[i] + dh * ao * (1.f - tc * tc);
+    g[u] = __float2half_rn(dc * aj * ai * (1.f - ai));
+    g[H + u] = __float2half_rn(dc * ai * (1.f - aj * aj));
+    g[2 * H + u] = __float2half_rn(dc * cp * af * (1.f - af));
+    g[3 * H + u] = __float2half_rn(dh * tc * ao * (1.f - ao));
+    dc_io[i] = dc * af;
+  }
+}
+
+}  // namespace kfb
+
+extern "C" int kfb_lstm_cell_forward(void* gates_io, long long ldg, const void* gh, long long ldgh,
+                                     const float* bias, const float* c_prev, long long ldcp,
+                                     float* c_out, long long ldc, void* h_out, long long ldh,
+                                     void* h_next, long long ldhn, int n, int H,
+                                     float forget_bias, void* stream) {
+  KFB_REQUIRE(n > 0 && H > 0, "lstm_cell_forward: bad sizes");
+  lstm_cell_fwd_kernel<<<xgrid_for((long long)n * H), 256, 0, (cudaStream_t)stream>>>(
+      (__half*)gates_io, ldg, (const __half*)gh, ldgh, bias, c_prev, ldcp, c_out, ldc,
+      (__half*)h_out, ldh, (__half*)h_next, ldhn, n, H, forget_bias);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int kfb_lstm_cell_backward(void* gates_io, long long ldg, const void* dy, long long lddy,
+                                      const void* dh_rec, long long lddh, const float* c,
+                                      long long ldc, const float* c_prev, long long ldcp,
+                                      float* dc_io, int n, int H, void* stream) {
+  KFB_REQUIRE(n > 0 && H > 0, "lstm_cell_backward: bad sizes");
+  lstm_cell_bwd_kernel<<<xgrid_for((long long)n * H), 256, 0, (cudaStream_t)stream>>>(
+      (__half*)gates_io, ldg, (const __half*)dy, lddy, (const __half*)dh_rec, lddh, c, ldc, c_prev,
+      ldcp, dc_io, n, H);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -223,6 +223,199 @@ __global__ void ssd_finalize_kernel(const float* __restrict__ sample_loss, int n
   }
 }
 
+
+// ---------------------------------------------------------------------------
+// CTC loss (DeepSpeech2, T/models/experimental/deepspeech.py:359-396): the reference feeds
+// log(softmax(z) + eps) to tf.nn.ctc_loss, which normalises again, so the emission
+// probabilities are p = (softmax(z) + eps) / (1 + C*eps); blank is the last class; samples whose
+// label does not fit their input length contribute zero loss and gradient
+// (ignore_longer_outputs_than_inputs). One block per sample, log-space alpha/beta recursions
+// over the 2L+1 extended-label states, alpha kept in global memory for the gradient pass.
+// ---------------------------------------------------------------------------
+constexpr float kCtcNegInf = -1.0e30f;
+
+__device__ __forceinline__ float log_add(float a, float b) {
+  const float m = fmaxf(a, b);
+  if (m <= kCtcNegInf) return kCtcNegInf;
+  return m + __logf(__expf(a - m) + __expf(b - m));
+}
+
+// lp[k] = log p_t(k) for the C classes of one time step; executed by warp 0.
+__device__ __forceinline__ void ctc_log_probs(const float* __restrict__ z, int C, float eps,
+                                              float* __restrict__ lp, float* __restrict__ q) {
+  const int lane = threadIdx.x;
+  float mx = -3.0e38f;
+  for (int k = lane; k < C; k += 32) mx = fmaxf(mx, z[k]);
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int k = lane; k < C; k += 32) sum += __expf(z[k] - mx);
+  sum = warp_sum(sum);
+  const float norm = 1.f + C * eps;
+  for (int k = lane; k < C; k += 32) {
+    const float qk = __expf(z[k] - mx) / sum;
+    if (q != nullptr) q[k] = qk;
+    lp[k] = __logf((qk + eps) / norm);
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+    ctc_alpha_kernel(const float* __restrict__ z, long long ldz, int T, int C,
+                     const int* __restrict__ labels, int lmax, const int* __restrict__ in_len,
+                     const int* __restrict__ lab_len, float eps, float* __restrict__ alpha,
+                     float* __restrict__ sample_loss) {
+  extern __shared__ float sm[];
+  const int S_max = 2 * lmax + 1;
+  float* a0 = sm;
+  float* a1 = a0 + S_max;
+  float* lp = a1 + S_max;
+  int* ext = reinterpret_cast<int*>(lp + C);
+  const int n = blockIdx.x;
+  const int blank = C - 1;
+  int L = lab_len[n];
+  L = L < 0 ? 0 : (L > lmax ? lmax : L);
+  int Tn = in_len[n];
+  Tn = Tn < 0 ? 0 : (Tn > T ? T : Tn);
+  const int S = 2 * L + 1;
+  for (int s = threadIdx.x; s < S; s += blockDim.x) {
+    int l = (s & 1) ? labels[n * lmax + (s >> 1)] : blank;
+    ext[s] = l < 0 ? 0 : (l >= C ? C - 1 : l);
+  }
+  __syncthreads();
+  float* prev = a0;
+  float* cur = a1;
+  float* an = alpha + static_cast<long long>(n) * T * S_max;
+  for (int t = 0; t < Tn; ++t) {
+    if (threadIdx.x < 32)
+      ctc_log_probs(z + (static_cast<long long>(n) * T + t) * ldz, C, eps, lp, nullptr);
+    __syncthreads();
+    for (int s = threadIdx.x; s < S; s += blockDim.x) {
+      float v;
+      if (t == 0) {
+        v = s < 2 ? 0.f : kCtcNegInf;
+      } else {
+        v = prev[s];
+        if (s >= 1) v = log_add(v, prev[s - 1]);
+        if (s >= 2 && ext[s] != blank && ext[s] != ext[s - 2]) v = log_add(v, prev[s - 2]);
+      }
+      v = v <= kCtcNegInf ? kCtcNegInf : v + lp[ext[s]];
+      cur[s] = v;
+      an[static_cast<long long>(t) * S_max + s] = v;
+    }
+    __syncthreads();
+    float* tmp = prev;
+    prev = cur;
+    cur = tmp;
+  }
+  if (threadIdx.x == 0) {
+    float logp = kCtcNegInf;
+    if (Tn > 0) {
+      logp = prev[S - 1];
+      if (S >= 2) logp = log_add(logp, prev[S - 2]);
+    }
+    // infeasible alignment -> ignored (loss 0, no gradient); flagged with a +inf marker
+    sample_loss[n] = logp <= kCtcNegInf * 0.5f ? 3.0e38f : -logp;
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+    ctc_beta_grad_kernel(const float* __restrict__ z, long long ldz, int T, int C,
+                         const int* __restrict__ labels, int lmax, const int* __restrict__ in_len,
+                         const int* __restrict__ lab_len, float eps,
+                         const float* __restrict__ alpha, const float* __restrict__ sample_loss,
+                         float scale, const float* __restrict__ dyn_scale,
+                         __half* __restrict__ dz, long long lddz) {
+  extern __shared__ float sm[];
+  const int S_max = 2 * lmax + 1;
+  float* b0 = sm;
+  float* b1 = b0 + S_max;
+  float* lp = b1 + S_max;
+  float* q = lp + C;
+  float* occ = q + C;
+  int* ext = reinterpret_cast<int*>(occ + C);
+  const int n = blockIdx.x;
+  const int blank = C - 1;
+  int L = lab_len[n];
+  L = L < 0 ? 0 : (L > lmax ? lmax : L);
+  int Tn = in_len[n];
+  Tn = Tn < 0 ? 0 : (Tn > T ? T : Tn);
+  const int S = 2 * L + 1;
+  const float loss = sample_loss[n];
+  const bool feasible = loss < 1.0e38f;
+  const float logp = -loss;
+  const float sc = scale * (dyn_scale != nullptr ? *dyn_scale : 1.f);
+  for (int s = threadIdx.x; s < S; s += blockDim.x) {
+    int l = (s & 1) ? labels[n * lmax + (s >> 1)] : blank;
+    ext[s] = l < 0 ? 0 : (l >= C ? C - 1 : l);
+  }
+  // time steps past the input length (or an ignored sample) get zero gradient
+  for (int t = feasible ? Tn : 0; t < T; ++t)
+    for (int k = threadIdx.x; k < C; k += blockDim.x)
+      dz[(static_cast<long long>(n) * T + t) * lddz + k] = __float2half_rn(0.f);
+  if (!feasible) return;
+  __syncthreads();
+  float* next = b0;
+  float* cur = b1;
+  const float* an = alpha + static_cast<long long>(n) * T * S_max;
+  for (int t = Tn - 1; t >= 0; --t) {
+    const long long row = static_cast<long long>(n) * T + t;
+    if (threadIdx.x < 32) ctc_log_probs(z + row * ldz, C, eps, lp, q);
+    for (int k = threadIdx.x; k < C; k += blockDim.x) occ[k] = 0.f;
+    __syncthreads();
+    for (int s = threadIdx.x; s < S; s += blockDim.x) {
+      float v;
+      if (t == Tn - 1) {
+        v = s >= S - 2 ? 0.f : kCtcNegInf;
+      } else {
+        v = next[s];
+        if (s + 1 < S) v = log_add(v, next[s + 1]);
+        if (s + 2 < S && ext[s] != blank && ext[s] != ext[s + 2]) v = log_add(v, next[s + 2]);
+      }
+      const float e = lp[ext[s]];
+      v = v <= kCtcNegInf ? kCtcNegInf : v + e;
+      cur[s] = v;
+      const float a = an[static_cast<long long>(t) * S_max + s];
+      if (a > kCtcNegInf && v > kCtcNegInf)
+        atomicAdd(&occ[ext[s]], __expf(a + v - e - logp));  // alpha*beta / p, normalised
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      // g_k = p_k - occ_k w.r.t. the ctc "logits" u = log(q + eps); chain to z through
+      // du_k/dz_j = q_k (delta_kj - q_j) / (q_k + eps)
+      float rsum = 0.f;
+      for (int k = threadIdx.x; k < C; k += 32) {
+        const float g = __expf(lp[k]) - occ[k];
+        const float r = g * q[k] / (q[k] + eps);
+        lp[k] = r;  // reuse as r_k
+        rsum += r;
+      }
+      rsum = warp_sum(rsum);
+      for (int k = threadIdx.x; k < C; k += 32)
+        dz[row * lddz + k] = __float2half_rn(sc * (lp[k] - q[k] * rsum));
+    }
+    __syncthreads();
+    float* tmp = next;
+    next = cur;
+    cur = tmp;
+  }
+}
+
+// out[0] = mean over the batch of the per-sample losses (ignored samples count as 0)
+__global__ void ctc_finalize_kernel(const float* __restrict__ sample_loss, int n,
+                                    float* __restrict__ out) {
+  float s = 0.f;
+  for (int i = threadIdx.x; i < n; i += 32) {
+    const float v = sample_loss[i];
+    s += v < 1.0e38f ? v : 0.f;
+  }
+  s = warp_sum(s);
+  if (threadIdx.x == 0) {
+    out[0] = s / n;
+    out[1] = 0.f;
+    out[2] = 0.f;
+    out[3] = 0.f;
+  }
+}
+
 }  // namespace kfb
 
 using namespace kfb;
@@ -286,6 +479,46 @@ extern "C" int kfb_ssd_loss(int batch, int num_classes, const int* map_size, con
     KFB_CHECK_CUDA(cudaGetLastError());
   }
   ssd_finalize_kernel<<<1, 32, 0, st>>>(sample, batch, out);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" long long kfb_ctc_loss_workspace_floats(int batch, int T, int max_label_len) {
+  return static_cast<long long>(batch) * T * (2 * max_label_len + 1) + batch;
+}
+
+extern "C" int kfb_ctc_loss(const float* z, long long ldz, int batch, int T, int C,
+                            const int* labels, int max_label_len, const int* input_len,
+                            const int* label_len, float eps, float scale, const float* dyn_scale,
+                            void* dz, long long lddz, float* workspace, long long workspace_floats,
+                            float* out, void* stream) {
+  KFB_REQUIRE(batch > 0 && T > 0 && C > 1 && max_label_len > 0, "ctc_loss: bad sizes");
+  const long long need = kfb_ctc_loss_workspace_floats(batch, T, max_label_len);
+  KFB_REQUIRE(workspace != nullptr && workspace_floats >= need,
+              "ctc_loss: workspace %lld floats < %lld", workspace_floats, need);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int S = 2 * max_label_len + 1;
+  float* alpha = workspace;
+  float* sample = workspace + static_cast<long long>(batch) * T * S;
+  const int threads = S >= 1024 ? 1024 : ((S + 31) / 32 * 32 < 64 ? 64 : (S + 31) / 32 * 32);
+  const size_t smem_a = (2 * S + C) * sizeof(float) + S * sizeof(int);
+  const size_t smem_b = (2 * S + 3 * C) * sizeof(float) + S * sizeof(int);
+  KFB_REQUIRE(smem_b <= 200 * 1024, "ctc_loss: label length %d needs too much shared memory",
+              max_label_len);
+  KFB_CHECK_CUDA(cudaFuncSetAttribute(ctc_alpha_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_a));
+  KFB_CHECK_CUDA(cudaFuncSetAttribute(ctc_beta_grad_kernel,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+  ctc_alpha_kernel<<<batch, threads, smem_a, st>>>(z, ldz, T, C, labels, max_label_len, input_len,
+                                                   label_len, eps, alpha, sample);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  if (dz != nullptr) {
+    ctc_beta_grad_kernel<<<batch, threads, smem_b, st>>>(z, ldz, T, C, labels, max_label_len,
+                                                         input_len, label_len, eps, alpha, sample,
+                                                         scale, dyn_scale, (__half*)dz, lddz);
+    KFB_CHECK_CUDA(cudaGetLastError());
+  }
+  ctc_finalize_kernel<<<1, 32, 0, st>>>(sample, batch, out);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

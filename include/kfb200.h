@@ -263,6 +263,19 @@ int kfb_mul_backward(const void* dy, long long lddy, const void* other, long lon
  * dz (fp16, may be null) = scale * dyn * (p1 - y). */
 int kfb_ncf_loss(const float* z, long long ldz, const int* labels, int n, float scale,
                  const float* dyn_scale, void* dz, long long lddz, float* out, void* stream);
+/* Pointwise part of one BasicLSTMCell time step for the whole batch (gate order i, j, f, o,
+ * forget_bias added to f; T/models/experimental/deepspeech.py:232-268). gates_io holds the
+ * input-projection pre-activations on entry and the activated gates on exit (backward: the
+ * activated gates on entry, the pre-activation gradients on exit); gh is the recurrent
+ * projection h_{t-1}.Wh; c is kept in fp32. The GEMMs of the layer are the kfb_gemm_* calls. */
+int kfb_lstm_cell_forward(void* gates_io, long long ldg, const void* gh, long long ldgh,
+                          const float* bias, const float* c_prev, long long ldcp, float* c_out,
+                          long long ldc, void* h_out, long long ldh, void* h_next, long long ldhn,
+                          int n, int H, float forget_bias, void* stream);
+int kfb_lstm_cell_backward(void* gates_io, long long ldg, const void* dy, long long lddy,
+                           const void* dh_rec, long long lddh, const float* c, long long ldc,
+                           const float* c_prev, long long ldcp, float* dc_io, int n, int H,
+                           void* stream);
 /* y[r][c] (+)= idx[c] >= 0 ? x[r][idx[c]] : 0 over C output channels (idx on the device):
  * converts between two zero-padded channel layouts of one logical tensor (nn/legalize.py). */
 int kfb_channel_gather(const void* x, long long ldx, void* y, long long ldy, int accumulate,
@@ -286,6 +299,16 @@ int kfb_ssd_loss(int batch, int num_classes, const int* map_size, const int* map
                  const long long* ld_conf, void* const* dloc, void* const* dconf,
                  const float* gt_loc, const float* gt_label, const float* num_matched,
                  int negs_per_positive, float scale, const float* dyn_scale, float* workspace,
+                 long long workspace_floats, float* out, void* stream);
+
+/* CTC loss as the reference computes it (T/models/experimental/deepspeech.py:359-396):
+ * emissions (softmax(z)+eps)/(1+C*eps), blank = C-1, mean over the batch, samples whose labels
+ * do not fit are ignored. z [batch*T][ldz] fp32 (row n*T+t), labels [batch][max_label_len];
+ * dz fp16 (may be null) receives scale*dyn*dL/dz. out[0] = mean loss. */
+long long kfb_ctc_loss_workspace_floats(int batch, int T, int max_label_len);
+int kfb_ctc_loss(const float* z, long long ldz, int batch, int T, int C, const int* labels,
+                 int max_label_len, const int* input_len, const int* label_len, float eps,
+                 float scale, const float* dyn_scale, void* dz, long long lddz, float* workspace,
                  long long workspace_floats, float* out, void* stream);
 
 #ifdef __cplusplus

@@ -4,7 +4,7 @@ from __future__ import annotations
 
 from functools import partial
 
-from .experimental import official_ncf_model
+from .experimental import deepspeech, official_ncf_model
 from . import ssd_model
 from . import (alexnet_model, densenet_model, googlenet_model, inception_model, lenet_model,
                mobilenet_v2, nasnet_model,
@@ -39,14 +39,13 @@ _model_name_to_cifar_model = {
 }
 _model_name_to_cifar_model.update(resnet_model.cifar_factories())
 
-# Models of the reference that need external repositories / datasets the fork itself
-# disabled. They resolve to a clear error instead of an import failure.
-_UNSUPPORTED = {
-    "deepspeech2": "needs LibriSpeech; LSTM/CTC kernels not built",
-}
+# Every model of the reference's zoo is registered; this map is kept for
+# names that may have to be rejected with an explanation in a future build.
+_UNSUPPORTED = {}
 
 
 _model_name_to_object_detection_model = {"ssd300": ssd_model.SSD300Model}
+_model_name_to_speech_model = {"deepspeech2": deepspeech.DeepSpeech2Model}
 
 
 def _get_model_map(dataset_name):
@@ -54,6 +53,8 @@ def _get_model_map(dataset_name):
         return _model_name_to_cifar_model
     if dataset_name == "coco":
         return _model_name_to_object_detection_model
+    if dataset_name == "librispeech":
+        return _model_name_to_speech_model
     if dataset_name in ("imagenet", "synthetic"):
         return _model_name_to_imagenet_model
     raise ValueError("Invalid dataset name: %s" % dataset_name)

@@ -90,7 +90,8 @@ class NetBuilder:
     def conv(self, num_out_channels, k_height, k_width, d_height=1, d_width=1, mode="SAME",
              input_layer=None, num_channels_in=None, use_batch_norm=None, stddev=None,
              activation="relu", bias=0.0, kernel_initializer=None, scope_name=None,
-             kernel_leaf="conv2d/kernel", bias_leaf="biases", bn_scope_name=None) -> TensorRef:
+             kernel_leaf="conv2d/kernel", bias_leaf="biases", bn_scope_name=None,
+             explicit_pad=None) -> TensorRef:
         """T/convnet_builder_legacy.py:143-226. ``scope_name`` / ``*_leaf`` override the
         variable names for the slim-style models (MobilenetV2/Conv/weights ...); activation
         "relu6" is accepted for those."""
@@ -110,8 +111,12 @@ class NetBuilder:
             name = scope_name
         if use_batch_norm is None:
             use_batch_norm = self.use_batch_norm
-        pad_h = resolve_padding(mode, h, k_height, d_height)
-        pad_w = resolve_padding(mode, w, k_width, d_width)
+        if explicit_pad is not None:     # tf.pad + VALID (DeepSpeech2's conv layers)
+            pad_h = (int(explicit_pad[0]), int(explicit_pad[0]))
+            pad_w = (int(explicit_pad[1]), int(explicit_pad[1]))
+        else:
+            pad_h = resolve_padding(mode, h, k_height, d_height)
+            pad_w = resolve_padding(mode, w, k_width, d_width)
         p = out_size(h, k_height, d_height, pad_h)
         q = out_size(w, k_width, d_width, pad_w)
         fan_in = k_height * k_width * c
@@ -371,7 +376,7 @@ class NetBuilder:
             input_layer = self.top_layer
         if num_channels_in is None:
             num_channels_in = self.top_size
-        if len(input_layer.shape) != 2 or input_layer.shape[1] != num_channels_in:
+        if len(input_layer.shape) not in (2, 3) or input_layer.shape[-1] != num_channels_in:
             raise ValueError(f"affine: bad input {input_layer.shape} for in={num_channels_in}")
         if scope_name is None:
             name = "affine" + str(self.counts["affine"])
@@ -396,7 +401,7 @@ class NetBuilder:
                                     (num_out_channels,), "bias", True, ("const", float(bias))),
             }
             node = self.graph.add_node("affine", self._full(""), [input_layer],
-                                       (input_layer.shape[0], num_out_channels),
+                                       tuple(input_layer.shape[:-1]) + (num_out_channels,),
                                        dict(activation=act), params)
         self.top_layer, self.top_size = node.output, num_out_channels
         return self.top_layer
@@ -447,6 +452,47 @@ class NetBuilder:
                                    tuple(base) + (total,))
         self.counts["concat"] += 1
         self.top_layer, self.top_size = node.output, total
+        return self.top_layer
+
+    def merge_last_dims(self, input_layer=None) -> TensorRef:
+        """[N, T, F, C] -> [N, T, F*C]: the reshape between DeepSpeech2's convolutions and its
+        recurrent stack (T/models/experimental/deepspeech.py:336-340)."""
+        x = self.top_layer if input_layer is None else input_layer
+        n, t, f, c = x.shape
+        node = self.graph.add_node("reshape", "reshape%d" % self.counts["reshape"], [x],
+                                   (n, t, f * c))
+        self.counts["reshape"] += 1
+        self.top_layer, self.top_size = node.output, f * c
+        return self.top_layer
+
+    def lstm(self, hidden: int, bidirectional: bool = True, forget_bias: float = 1.0,
+             scope_name: str = "rnn", input_layer=None) -> TensorRef:
+        """(Bi)LSTM layer over [N, T, I] with BasicLSTMCell semantics (gate order i, j, f, o,
+        forget_bias added to f; zero initial state; outputs of the two directions concatenated)
+        - T/models/experimental/deepspeech.py:232-268. TF keeps one ``kernel`` of shape
+        [I + H, 4H] per cell; here it is split into the input part (``kernel_x``, applied to all
+        time steps by one GEMM) and the recurrent part (``kernel_h``)."""
+        x = self.top_layer if input_layer is None else input_layer
+        n, t, i = x.shape
+        dirs = ("fw", "bw") if bidirectional else ("fw",)
+        params = {}
+        with self.scope(scope_name):
+            for d in dirs:
+                init = ("glorot_uniform", i + hidden, 4 * hidden)
+                params[d + "_wx"] = ParamSpec(self._full(d + "/kernel_x"),
+                                              (4 * hidden, (i + 7) // 8 * 8), (i, 4 * hidden),
+                                              "fc_weight", True, init, logical_cols=i)
+                params[d + "_wh"] = ParamSpec(self._full(d + "/kernel_h"),
+                                              (4 * hidden, (hidden + 7) // 8 * 8),
+                                              (hidden, 4 * hidden), "fc_weight", True, init,
+                                              logical_cols=hidden)
+                params[d + "_b"] = ParamSpec(self._full(d + "/bias"), (4 * hidden,),
+                                             (4 * hidden,), "bias", True, ("zeros",))
+            node = self.graph.add_node("lstm", self._full(""), [x],
+                                       (n, t, hidden * len(dirs)),
+                                       dict(hidden=hidden, dirs=dirs,
+                                            forget_bias=float(forget_bias)), params)
+        self.top_layer, self.top_size = node.output, hidden * len(dirs)
         return self.top_layer
 
     def embedding(self, ids: TensorRef, num_rows: int, dim: int, col_lo: int = 0,

@@ -137,7 +137,7 @@ class CudaExecutor:
                     "that are multiples of 8 (use --device=cpu for this model)")
             ld = cols
         else:
-            rows, cols = t.shape[0], t.shape[1]
+            rows, cols = t.rows, t.shape[-1]
             ld = _pad8(cols)
         if node.op == "reshape":
             src = self.buf[node.inputs[0].id]
@@ -276,6 +276,23 @@ class CudaExecutor:
         elif node.op == "pad_channels":
             if a["before"] % 8 or a["after"] % 8:
                 raise NotImplementedError("pad_channels: pads must be multiples of 8")
+        elif node.op == "lstm":
+            n, t_steps, _ = node.inputs[0].shape
+            hid = a["hidden"]
+            for d in a["dirs"]:
+                info[d] = dict(
+                    gates=torch.zeros((n * t_steps, 4 * hid), dtype=torch.float16, device=dev),
+                    c=torch.zeros((n * t_steps, hid), dtype=torch.float32, device=dev),
+                    hprev=torch.zeros((n * t_steps, hid), dtype=torch.float16, device=dev))
+            info["gh"] = torch.zeros((n, 4 * hid), dtype=torch.float16, device=dev)
+            info["dh"] = torch.zeros((n, hid), dtype=torch.float16, device=dev)
+            info["dc"] = torch.zeros((n, hid), dtype=torch.float32, device=dev)
+            info["h0"] = torch.zeros((n, hid), dtype=torch.float16, device=dev)
+            for key, spec in node.params.items():
+                if key.endswith("_b"):
+                    continue
+                self._ws_need = max(self._ws_need, self._nt_ws(spec.shape[0], spec.shape[1]))
+            self._need_scratch(n * t_steps, 4 * hid)
         elif node.op == "embedding":
             if node.params:
                 # dense gradient of the table is scatter-accumulated: zero it every backward
@@ -517,6 +534,105 @@ class CudaExecutor:
             native.call("copy2d", x.p, i64(x.ld), ctypes.c_void_p(y.t.data_ptr() + off * 2),
                         i64(y.ld), i64(x.rows), i32(x.cols), i32(0), s)
             off += x.cols
+
+    # LSTM layer = one big input-projection GEMM per direction, then per time step a small
+    # recurrent GEMM (batch x 4H x H) and the pointwise cell kernel. Batch-major [N, T, *]
+    # buffers are sliced per step through the row stride (ld = T * width), so the two
+    # directions write straight into their halves of the concatenated output.
+    def _fwd_lstm(self, node, train, s):
+        info = self._per_node[id(node)]
+        a = node.attrs
+        hid = a["hidden"]
+        x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
+        n, t_steps, _ = node.inputs[0].shape
+        e2 = 2  # bytes per half
+        for di, d in enumerate(a["dirs"]):
+            st = info[d]
+            wx, wh, b = (node.params[d + k] for k in ("_wx", "_wh", "_b"))
+            gates, cbuf, hprev = st["gates"], st["c"], st["hprev"]
+            native.call("gemm_tn", x.p, self._w16(wx.name), ptr(gates), i32(x.rows), i32(4 * hid),
+                        i32(wx.logical_cols), i64(x.ld), i64(wx.shape[1]), i64(4 * hid), None,
+                        i32(0), i32(0), None, s)
+            order = range(t_steps) if d == "fw" else range(t_steps - 1, -1, -1)
+            step = 1 if d == "fw" else -1
+            ybase = y.t.data_ptr() + di * hid * e2
+            for t in order:
+                tp = t - step                       # previous step in processing order
+                first = tp < 0 or tp >= t_steps
+                if first:
+                    hp_ptr, hp_ld = info["h0"].data_ptr(), hid
+                else:
+                    hp_ptr, hp_ld = ybase + tp * y.ld * e2, t_steps * y.ld
+                native.call("gemm_tn", ctypes.c_void_p(hp_ptr), self._w16(wh.name),
+                            ptr(info["gh"]), i32(n), i32(4 * hid), i32(hid), i64(hp_ld),
+                            i64(wh.shape[1]), i64(4 * hid), None, i32(0), i32(0), None, s)
+                tn = t + step
+                has_next = 0 <= tn < t_steps
+                native.call(
+                    "lstm_cell_forward",
+                    ctypes.c_void_p(gates.data_ptr() + t * 4 * hid * e2), i64(t_steps * 4 * hid),
+                    ptr(info["gh"]), i64(4 * hid), self._w32(b.name),
+                    None if first else ctypes.c_void_p(cbuf.data_ptr() + tp * hid * 4),
+                    i64(t_steps * hid),
+                    ctypes.c_void_p(cbuf.data_ptr() + t * hid * 4), i64(t_steps * hid),
+                    ctypes.c_void_p(ybase + t * y.ld * e2), i64(t_steps * y.ld),
+                    ctypes.c_void_p(hprev.data_ptr() + tn * hid * e2) if has_next else None,
+                    i64(t_steps * hid), i32(n), i32(hid), f32(a["forget_bias"]), s)
+
+    def _bwd_lstm(self, node, s):
+        info = self._per_node[id(node)]
+        a = node.attrs
+        hid = a["hidden"]
+        xin = node.inputs[0]
+        x = self.buf[xin.id]
+        gy = self._grad(node.output)
+        n, t_steps, _ = xin.shape
+        e2 = 2
+        need_dx = self.needs_grad[xin.id]
+        acc = self._acc(node, 0) if need_dx else 0
+        for di, d in enumerate(a["dirs"]):
+            st = info[d]
+            wx, wh, b = (node.params[d + k] for k in ("_wx", "_wh", "_b"))
+            gates, cbuf, hprev = st["gates"], st["c"], st["hprev"]
+            info["dc"].zero_()
+            step = 1 if d == "fw" else -1
+            order = range(t_steps - 1, -1, -1) if d == "fw" else range(t_steps)
+            gybase = gy.t.data_ptr() + di * hid * e2
+            for k, t in enumerate(order):
+                tp = t - step
+                first = tp < 0 or tp >= t_steps
+                native.call(
+                    "lstm_cell_backward",
+                    ctypes.c_void_p(gates.data_ptr() + t * 4 * hid * e2), i64(t_steps * 4 * hid),
+                    ctypes.c_void_p(gybase + t * gy.ld * e2), i64(t_steps * gy.ld),
+                    ptr(info["dh"]) if k > 0 else None, i64(hid),
+                    ctypes.c_void_p(cbuf.data_ptr() + t * hid * 4), i64(t_steps * hid),
+                    None if first else ctypes.c_void_p(cbuf.data_ptr() + tp * hid * 4),
+                    i64(t_steps * hid), ptr(info["dc"]), i32(n), i32(hid), s)
+                if not first:
+                    # dh_{t-1} = dgates_t . Wh
+                    native.call("gemm_nn",
+                                ctypes.c_void_p(gates.data_ptr() + t * 4 * hid * e2),
+                                self._w16(wh.name), ptr(info["dh"]), i32(n), i32(wh.shape[1]),
+                                i32(4 * hid), i64(t_steps * 4 * hid), i64(wh.shape[1]), i64(hid),
+                                i32(0), i32(0), s)
+            rows = n * t_steps
+            # bias gradient = column sums of the gate gradients
+            native.call("bias_act_backward", ptr(gates), i64(4 * hid), None, i64(0), i64(rows),
+                        i32(4 * hid), None, i64(0), self._g32(b.name), i32(0), f32(1.0),
+                        ptr(self.scratch), s)
+            ws, wsb = ptr(self.workspace), i64(self.workspace.numel() * 4)
+            native.call("gemm_nt", ptr(gates), ptr(hprev), self._g32(wh.name), i32(4 * hid),
+                        i32(wh.shape[1]), i32(rows), i64(4 * hid), i64(hid), i64(wh.shape[1]),
+                        ws, wsb, i32(0), f32(1.0), s)
+            native.call("gemm_nt", ptr(gates), x.p, self._g32(wx.name), i32(4 * hid),
+                        i32(wx.shape[1]), i32(rows), i64(4 * hid), i64(x.ld), i64(wx.shape[1]),
+                        ws, wsb, i32(0), f32(1.0), s)
+            if need_dx:
+                gx = self._grad(xin)
+                native.call("gemm_nn", ptr(gates), self._w16(wx.name), gx.p, i32(rows),
+                            i32(wx.shape[1]), i32(4 * hid), i64(4 * hid), i64(wx.shape[1]),
+                            i64(gx.ld), i32(0), i32(1 if (acc or di > 0) else 0), s)
 
     def _fwd_embedding(self, node, train, s):
         a = node.attrs

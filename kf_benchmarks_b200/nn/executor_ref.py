@@ -185,7 +185,9 @@ class RefExecutor:
         if op == "spatial_mean":
             return xs[0].mean((1, 2))
         if op == "reshape":
-            return xs[0].reshape(xs[0].shape[0], -1)
+            return xs[0].reshape(node.output.shape)
+        if op == "lstm":
+            return self._lstm(node, xs[0], train)
         if op == "affine":
             w = self._param(node.params["weights"], train)
             b = self._param(node.params["biases"], train)
@@ -210,6 +212,31 @@ class RefExecutor:
         if op == "pad_channels":
             return F.pad(xs[0], (a["before"], a["after"]))
         raise NotImplementedError(op)
+
+    def _lstm(self, node: Node, x: torch.Tensor, train: bool) -> torch.Tensor:
+        """BasicLSTMCell recurrences, mirroring the CUDA executor's storage precision when
+        fp16 emulation is on (projections and hidden states are kept in half)."""
+        a = node.attrs
+        H = a["hidden"]
+        rnd = _RoundFp16.apply if self.emulate_fp16 else (lambda v: v)
+        n, T, _ = x.shape
+        outs = []
+        for d in a["dirs"]:
+            wx = self._param(node.params[d + "_wx"], train)
+            wh = self._param(node.params[d + "_wh"], train)
+            b = self._param(node.params[d + "_b"], train)
+            gx = rnd(x @ wx.t())
+            h = torch.zeros(n, H, dtype=x.dtype, device=x.device)
+            c = torch.zeros(n, H, dtype=x.dtype, device=x.device)
+            hs = [None] * T
+            for t in (range(T) if d == "fw" else range(T - 1, -1, -1)):
+                g = gx[:, t] + rnd(h @ wh.t()) + b
+                gi, gj, gf, go = g.split(H, dim=1)
+                c = c * torch.sigmoid(gf + a["forget_bias"]) + torch.sigmoid(gi) * torch.tanh(gj)
+                h = rnd(torch.tanh(c) * torch.sigmoid(go))
+                hs[t] = h
+            outs.append(torch.stack(hs, dim=1))
+        return torch.cat(outs, dim=-1)
 
     # -- loss / backward ------------------------------------------------------------
     def loss_backward(self, loss_scale: float = 1.0, backward: bool = True,

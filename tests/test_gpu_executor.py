@@ -57,6 +57,19 @@ def test_nasnet_shallow_matches_reference(data, batch, size, min_cos):
     assert abs(r["loss_gpu"] - r["loss_ref"]) < 0.02 * abs(r["loss_ref"]), r
 
 
+def test_deepspeech2_small_matches_reference():
+    """Conv(41x11 / 21x11, explicit pads, ReLU6, BN) -> 2 x BiLSTM -> BN -> dense -> CTC on a
+    reduced geometry: exercises the LSTM cell kernels, the per-step GEMM slicing and the CTC
+    alpha/beta kernels end to end against the PyTorch executor."""
+    def small(m):
+        m.max_time_steps, m.num_feature_bins, m.max_label_length = 96, 33, 8
+        m.rnn_hidden_size, m.num_rnn_layers = 64, 2
+    r = executor_check.compare("deepspeech2", "librispeech", 4, tweak=small)
+    assert r["logits_rel"] < 2e-2, r
+    assert r["grad_cosine"] > 0.98, r
+    assert abs(r["loss_gpu"] - r["loss_ref"]) < 0.02 * abs(r["loss_ref"]), r
+
+
 def test_training_reduces_loss_and_checkpoints(tmp_path):
     from kf_benchmarks_b200 import benchmark, params as P
     from kf_benchmarks_b200.utils import log_util

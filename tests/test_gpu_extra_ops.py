@@ -200,3 +200,30 @@ def test_ssd_multibox_loss_and_gradients():
     assert abs(float(out[5]) - float(box)) < 2e-3 * float(box) + 1e-4
     for got, ref in zip(dlocs + dconfs, lf + cf):
         assert torch.allclose(got.float(), ref.grad, atol=2e-2, rtol=2e-2)
+
+
+def test_ctc_loss_matches_reference_formulation():
+    from kf_benchmarks_b200.nn import ctc_ref
+    g = torch.Generator(device="cuda").manual_seed(8)
+    n, T, C, lmax = 5, 40, 29, 12
+    z = torch.randn(n * T, 32, device="cuda", generator=g) * 2
+    labels = torch.randint(0, C - 1, (n, lmax), device="cuda", generator=g, dtype=torch.int32)
+    labels[1, 3] = labels[1, 2]                      # a repeated symbol needs a blank in between
+    in_len = torch.tensor([40, 33, 40, 9, 25], dtype=torch.int32, device="cuda")
+    lab_len = torch.tensor([12, 7, 1, 12, 12], dtype=torch.int32, device="cuda")   # sample 3 infeasible
+    fn = native.load().kfb_ctc_loss_workspace_floats
+    fn.restype = ctypes.c_longlong
+    ws = torch.zeros(int(fn(i32(n), i32(T), i32(lmax))), device="cuda")
+    dz = torch.full((n * T, 32), 5.0, device="cuda", dtype=torch.float16)
+    out = torch.zeros(8, device="cuda")
+    scale = 64.0
+    native.call("ctc_loss", ptr(z), i64(32), i32(n), i32(T), i32(C), ptr(labels), i32(lmax),
+                ptr(in_len), ptr(lab_len), f32(1e-7), f32(scale / n), None, ptr(dz), i64(32),
+                ptr(ws), i64(ws.numel()), ptr(out), _s())
+    zf = z[:, :C].reshape(n, T, C).clone().requires_grad_(True)
+    loss = ctc_ref.ctc_loss(zf, labels, in_len, lab_len)
+    (loss * scale).backward()
+    assert abs(float(out[0]) - float(loss)) < 1e-3 * float(loss)
+    got = dz[:, :C].float().reshape(n, T, C)
+    assert torch.allclose(got, zf.grad, atol=3e-3, rtol=2e-2)
+    assert float(got[3].abs().max()) == 0.0           # ignored sample
