@@ -948,7 +948,7 @@ class CudaExecutor:
     # ------------------------------------------------------------------ inspection
     def logits(self) -> torch.Tensor:
         b = self.buf[self.graph.logits.id]
-        return b.t[:, :b.cols]
+        return b.t[:, :b.cols].reshape(self.graph.logits.shape)
 
     def value(self, tensor_id: int) -> torch.Tensor:
         b = self.buf[tensor_id]
