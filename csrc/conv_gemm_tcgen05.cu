@@ -71,6 +71,14 @@ struct GemmParams {
   int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw, sc_h0, sc_w0;
   // DGRAD: filter tap visited at (r, s) of this launch's (sub-)filter
   int wt_r0, wt_rstep, wt_s0, wt_sstep, wt_S;
+  // Fused reduce-scatter (weight gradients, data-parallel training): when push_n > 1 the
+  // epilogue stores each 16-byte piece of the fp32 result straight into the staging slot of
+  // the rank that owns it - a peer-mapped address over NVLink for every owner but this rank -
+  // so the gradient transfer overlaps the MMA main loop tile by tile. Element e of the output
+  // belongs to owner #{r >= 1 : e >= push_bound[r]}; push_base[o] is where e = 0 lands on o.
+  int push_n;
+  long long push_bound[8];
+  float* push_base[8];
 };
 
 constexpr int kBlockM = 128;
@@ -498,7 +506,15 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         for (int i8 = 0; i8 < 8; ++i8) {
           const int r = i8 * 4 + (lane >> 3);
           const long long ro = __shfl_sync(0xffffffffu, row_off, r);
-          gps[i8] = reinterpret_cast<uint8_t*>(p.out) + (base + ro * p.ldc + pcol) * esize;
+          const long long e_idx = base + ro * p.ldc + pcol;
+          uint8_t* obase = reinterpret_cast<uint8_t*>(p.out);
+          if (p.push_n > 1) {
+            int owner = 0;
+#pragma unroll
+            for (int r = 1; r < 8; ++r) owner += (r < p.push_n && e_idx >= p.push_bound[r]) ? 1 : 0;
+            obase = reinterpret_cast<uint8_t*>(p.push_base[owner]);
+          }
+          gps[i8] = obase + e_idx * esize;
           any_ok[i8] = ro >= 0 && col_ok;
           vec_ok[i8] = FAST ? any_ok[i8]
                             : (any_ok[i8] && col_full &&
@@ -551,6 +567,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       }
     }
     if (do_stats && st_nblk >= 0) flush_stats(st_nblk);
+    // remote (NVLink) stores of a fused reduce-scatter must be performed system-wide before
+    // this kernel counts as complete for the ranks that wait on the stream-ordered READY flag
+    if (p.push_n > 1) __threadfence_system();
   }
 
   tc_fence_before();
@@ -592,6 +611,43 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __rest
       out[i] = accumulate ? out[i] + acc : acc;
     }
   }
+}
+
+// Split-K reduction whose result is scattered to the owning ranks' staging slots (the second
+// stage of a fused wgrad + reduce-scatter when the GEMM needed more than one K split).
+struct PushTarget {
+  int n;
+  long long bound[8];
+  float* base[8];
+};
+
+__global__ void splitk_reduce_push_kernel(const float* __restrict__ ws, PushTarget t, long long n,
+                                          int splits, float scale) {
+  const long long i4 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+  if (i4 >= n) return;
+  int owner = 0;
+#pragma unroll
+  for (int r = 1; r < 8; ++r) owner += (r < t.n && i4 >= t.bound[r]) ? 1 : 0;
+  float* out = t.base[owner];
+  if (i4 + 4 <= n) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int z = 0; z < splits; ++z) {
+      const float4 v = *reinterpret_cast<const float4*>(ws + static_cast<long long>(z) * n + i4);
+      acc.x += v.x;
+      acc.y += v.y;
+      acc.z += v.z;
+      acc.w += v.w;
+    }
+    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+    *reinterpret_cast<float4*>(out + i4) = acc;
+  } else {
+    for (long long i = i4; i < n; ++i) {
+      float acc = 0.f;
+      for (int z = 0; z < splits; ++z) acc += ws[static_cast<long long>(z) * n + i];
+      out[i] = acc * scale;
+    }
+  }
+  __threadfence_system();
 }
 
 // ---------------------------------------------------------------------------
@@ -835,10 +891,51 @@ extern "C" int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, 
   return launch_mode<GEMM_NN>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
 }
 
-// C[M,N] (fp32) = A[K,M]^T * B[K,N]; split over K into `workspace` then reduced.
-extern "C" int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N, int K,
-                           long long lda, long long ldb, long long ldc, float* workspace,
-                           long long workspace_bytes, int accumulate, float scale, void* stream) {
+
+// Fills the kernel-side description of a fused reduce-scatter from the C ABI struct.
+static int fill_push(const kfb_push_target* t, long long out_elems, int* n_out,
+                     long long* bound, float** base) {
+  *n_out = 0;
+  if (t == nullptr || t->nranks <= 1) return 0;
+  KFB_REQUIRE(t->nranks <= 8, "push: at most 8 ranks (%d)", t->nranks);
+  KFB_REQUIRE(t->per > 0 && t->per % 4 == 0 && t->rel >= 0 && t->rel % 4 == 0,
+              "push: shard length %lld / offset %lld must be positive multiples of 4", t->per,
+              t->rel);
+  for (int r = 0; r < 8; ++r) {
+    bound[r] = r < t->nranks ? (long long)r * t->per - t->rel : (1ll << 62);
+    base[r] = r < t->nranks ? (float*)t->dst[r] : nullptr;
+    if (r < t->nranks) KFB_REQUIRE(base[r] != nullptr, "push: null destination for rank %d", r);
+  }
+  (void)out_elems;
+  *n_out = t->nranks;
+  return 0;
+}
+
+// Final stage shared by the weight-gradient entry points: either the deterministic split-K
+// reduction into `out`, or (push) the same reduction scattered to the owners' staging slots.
+static int finish_wgrad(float* workspace, float* out, long long slice, int splits, int accumulate,
+                        float scale, const kfb_push_target* push, cudaStream_t st) {
+  const long long n4 = (slice + 3) / 4;
+  if (push != nullptr && push->nranks > 1) {
+    PushTarget t;
+    if (fill_push(push, slice, &t.n, t.bound, t.base)) return 2;
+    splitk_reduce_push_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(workspace, t, slice,
+                                                                           splits, scale);
+  } else {
+    splitk_reduce_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(workspace, out, slice,
+                                                                      splits, accumulate, scale);
+  }
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// C[M,N] (fp32) = A[K,M]^T * B[K,N]; split over K into `workspace` then reduced. With a push
+// target and a single K split the tcgen05 kernel's epilogue itself scatters the tiles to their
+// owners (GEMM + reduce-scatter in one kernel); with several splits the reduction kernel does.
+static int gemm_nt_impl(const void* A, const void* B, float* C, int M, int N, int K,
+                        long long lda, long long ldb, long long ldc, float* workspace,
+                        long long workspace_bytes, int accumulate, float scale,
+                        const kfb_push_target* push, void* stream) {
   KFB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_nt: bad shape %d %d %d", M, N, K);
   KFB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_nt: lda/ldb must be multiples of 8 elements");
   KFB_REQUIRE(ldc == N, "gemm_nt: output must be dense (ldc == N)");
@@ -870,12 +967,29 @@ extern "C" int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N,
   p.split_stride = slice;
   p.out_fp32 = 1;
   dim3 grid((M + 127) / 128, (N + bn - 1) / bn, splits);
+  const bool pushing = push != nullptr && push->nranks > 1;
+  KFB_REQUIRE(!(pushing && accumulate), "gemm_nt: a pushed gradient cannot accumulate");
+  if (pushing && splits == 1 && scale == 1.0f) {
+    if (fill_push(push, slice, &p.push_n, p.push_bound, p.push_base)) return 2;
+    return launch_mode<GEMM_NT>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
+  }
   if (launch_mode<GEMM_NT>(bn, tmA, tmB, p, grid, (cudaStream_t)stream)) return 1;
-  const long long n4 = (slice + 3) / 4;
-  splitk_reduce_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      workspace, C, slice, splits, accumulate, scale);
-  KFB_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return finish_wgrad(workspace, C, slice, splits, accumulate, scale, push, (cudaStream_t)stream);
+}
+
+extern "C" int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N, int K,
+                           long long lda, long long ldb, long long ldc, float* workspace,
+                           long long workspace_bytes, int accumulate, float scale, void* stream) {
+  return gemm_nt_impl(A, B, C, M, N, K, lda, ldb, ldc, workspace, workspace_bytes, accumulate,
+                      scale, nullptr, stream);
+}
+
+extern "C" int kfb_gemm_nt_rs(const void* A, const void* B, int M, int N, int K, long long lda,
+                              long long ldb, float* workspace, long long workspace_bytes,
+                              float scale, const kfb_push_target* push, void* stream) {
+  KFB_REQUIRE(push != nullptr && push->nranks > 1, "gemm_nt_rs: needs a push target");
+  return gemm_nt_impl(A, B, nullptr, M, N, K, lda, ldb, N, workspace, workspace_bytes, 0, scale,
+                      push, stream);
 }
 
 static int check_conv(const kfb_conv_desc* d, const char* who) {
@@ -1066,10 +1180,9 @@ extern "C" long long kfb_conv_wgrad_workspace_bytes(const kfb_conv_desc* d) {
 }
 
 // dw[K,R,S,C] (fp32) (+)= scale * sum_pixels dy[pix,K]^T * im2col(x)[pix,(r,s,C)]
-extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void* dy,
-                              long long lddy, float* dw, float* workspace,
-                              long long workspace_bytes, int accumulate, float scale,
-                              void* stream) {
+static int conv_wgrad_impl(const kfb_conv_desc* d, const void* x, const void* dy, long long lddy,
+                           float* dw, float* workspace, long long workspace_bytes, int accumulate,
+                           float scale, const kfb_push_target* push, void* stream) {
   if (check_conv(d, "conv_wgrad")) return 2;
   if (load_driver_fns()) return 1;
   const int pixels = d->n * d->p * d->q;
@@ -1115,10 +1228,28 @@ extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void*
   p.split_stride = slice;
   p.out_fp32 = 1;
   dim3 grid(m_tiles, n_tiles, splits);
+  const bool pushing = push != nullptr && push->nranks > 1;
+  KFB_REQUIRE(!(pushing && accumulate), "conv_wgrad: a pushed gradient cannot accumulate");
+  if (pushing && splits == 1 && scale == 1.0f) {
+    if (fill_push(push, slice, &p.push_n, p.push_bound, p.push_base)) return 2;
+    return launch_mode<WGRAD>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
+  }
   if (launch_mode<WGRAD>(bn, tmA, tmB, p, grid, (cudaStream_t)stream)) return 1;
-  const long long n4 = (slice + 3) / 4;
-  splitk_reduce_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      workspace, dw, slice, splits, accumulate, scale);
-  KFB_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return finish_wgrad(workspace, dw, slice, splits, accumulate, scale, push, (cudaStream_t)stream);
+}
+
+extern "C" int kfb_conv_wgrad(const kfb_conv_desc* d, const void* x, const void* dy,
+                              long long lddy, float* dw, float* workspace,
+                              long long workspace_bytes, int accumulate, float scale,
+                              void* stream) {
+  return conv_wgrad_impl(d, x, dy, lddy, dw, workspace, workspace_bytes, accumulate, scale,
+                         nullptr, stream);
+}
+
+extern "C" int kfb_conv_wgrad_rs(const kfb_conv_desc* d, const void* x, const void* dy,
+                                 long long lddy, float* workspace, long long workspace_bytes,
+                                 float scale, const kfb_push_target* push, void* stream) {
+  KFB_REQUIRE(push != nullptr && push->nranks > 1, "conv_wgrad_rs: needs a push target");
+  return conv_wgrad_impl(d, x, dy, lddy, nullptr, workspace, workspace_bytes, 0, scale, push,
+                         stream);
 }

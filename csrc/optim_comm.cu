@@ -254,6 +254,10 @@ __device__ __forceinline__ void grid_arrive_and_signal(const PeerCtx& c, int kin
   }
 }
 
+struct PushDst {
+  float* base[kMaxRanks];
+};
+
 // MODE 0: gradient all-reduce + optimizer. MODE 1: SMA (source = weights).
 template <int MODE>
 __global__ void __launch_bounds__(512)
@@ -262,9 +266,17 @@ __global__ void __launch_bounds__(512)
                             float* __restrict__ m, float* __restrict__ v,
                             __half* __restrict__ w16, HyperParams h,
                             const float* __restrict__ dyn, const int* __restrict__ skip_flag,
-                            float sma_alpha, int reduce_only) {
+                            float sma_alpha, int reduce_only, const float* __restrict__ stage,
+                            long long stage_stride) {
   resolve_dyn(h, dyn);
   const int n = c.nranks;
+  // Reduce-scatter sources: the peers' arenas (pull over NVLink), or - when the weight-gradient
+  // kernels already pushed their tiles here (kfb_*_rs) - this rank's n local staging slots.
+  const float* srcp[kMaxRanks];
+#pragma unroll
+  for (int r = 0; r < kMaxRanks; ++r)
+    srcp[r] = stage != nullptr ? stage + static_cast<long long>(r) * stage_stride
+                               : (r < n ? c.src[r] : nullptr);
   // --- announce: my source data for [offset, offset+count) is final ---
   if (blockIdx.x == 0 && threadIdx.x < n)
     st_release_sys(c.flags[threadIdx.x] + FLAG_READY * kMaxRanks + c.rank, seq);
@@ -295,7 +307,7 @@ __global__ void __launch_bounds__(512)
         float4 x[kU];
 #pragma unroll
         for (int u = 0; u < kU; ++u)
-          if (ok[u]) x[u] = *reinterpret_cast<const float4*>(c.src[r] + i0 + u * nthreads * 4);
+          if (ok[u]) x[u] = *reinterpret_cast<const float4*>(srcp[r] + i0 + u * nthreads * 4);
 #pragma unroll
         for (int u = 0; u < kU; ++u)
           if (ok[u]) {
@@ -319,7 +331,7 @@ __global__ void __launch_bounds__(512)
       } else if (i < s_end) {
         for (long long j = i; j < s_end; ++j) {
           float a1 = 0.f;
-          for (int r = 0; r < n; ++r) a1 += c.src[r][j];
+          for (int r = 0; r < n; ++r) a1 += srcp[r][j];
           if (MODE == 1) a1 *= inv_n;
           for (int r = 0; r < n; ++r) c.reduced[r][j] = a1;
         }
@@ -552,11 +564,79 @@ extern "C" int kfb_allreduce_update(int mode, int rank, int nranks, void* const*
   if (mode == 1)
     allreduce_update_kernel<1><<<blocks, 512, 0, st>>>(c, offset, count, seq, w, g_local, m, v,
                                                        (__half*)w16, make_hyper(hp), dyn,
-                                                       skip_flag, sma_alpha, 0);
+                                                       skip_flag, sma_alpha, 0, nullptr, 0);
   else
     allreduce_update_kernel<0><<<blocks, 512, 0, st>>>(c, offset, count, seq, w, g_local, m, v,
                                                        (__half*)w16, make_hyper(hp), dyn,
-                                                       skip_flag, sma_alpha, mode == 2 ? 1 : 0);
+                                                       skip_flag, sma_alpha, mode == 2 ? 1 : 0,
+                                                       nullptr, 0);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Second half of the fused weight-gradient reduce-scatter: the gradients of [offset,
+// offset+count) were pushed into this rank's `stage` slots (slot r = contribution of rank r,
+// `stage_stride` floats apart, indexed like the arena) by kfb_conv_wgrad_rs / kfb_gemm_nt_rs /
+// kfb_push_ranges on every rank. READY now means "my pushes are complete"; the shard is summed
+// from local memory in rank order (bit-identical to the pull path), pushed to every rank's
+// `reduced` buffer and applied as usual.
+extern "C" int kfb_allreduce_update_staged(int rank, int nranks, void* const* reduced,
+                                           void* const* flags, long long offset, long long count,
+                                           unsigned seq, float* w, float* m, float* v, void* w16,
+                                           const kfb_hyper* hp, const float* dyn,
+                                           const int* skip_flag, const float* stage,
+                                           long long stage_stride, int blocks, void* stream) {
+  KFB_REQUIRE(hp != nullptr && stage != nullptr, "allreduce_update_staged: null argument");
+  KFB_REQUIRE(offset % 4 == 0, "allreduce_update_staged: offset must be a multiple of 4");
+  PeerCtx c;
+  if (fill_peer_ctx(&c, rank, nranks, reduced, reduced, flags)) return 2;
+  if (blocks <= 0) {
+    blocks = static_cast<int>((count / 4 + 511) / 512);
+    if (blocks < 8) blocks = 8;
+  }
+  if (blocks > 148) blocks = 148;
+  allreduce_update_kernel<0><<<blocks, 512, 0, (cudaStream_t)stream>>>(
+      c, offset, count, seq, w, nullptr, m, v, (__half*)w16, make_hyper(hp), dyn, skip_flag, 0.f,
+      0, stage, stage_stride);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Pushes gradients that are not produced by a GEMM epilogue (batch-norm scales, biases,
+// depthwise filters ...) into the owners' staging slots, same ownership rule as kfb_push_target.
+__global__ void __launch_bounds__(256)
+    push_ranges_kernel(const float* __restrict__ grad, const long long* __restrict__ ranges,
+                       int nranges, long long bucket_lo, long long per, int n, PushDst d) {
+  for (int k = blockIdx.y; k < nranges; k += gridDim.y) {
+    const long long lo = ranges[2 * k], hi = ranges[2 * k + 1];
+    for (long long i = lo + (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+         i < hi; i += static_cast<long long>(gridDim.x) * blockDim.x * 4) {
+      long long o = (i - bucket_lo) / per;
+      o = o < 0 ? 0 : (o >= n ? n - 1 : o);
+      if (i + 4 <= hi) {
+        *reinterpret_cast<float4*>(d.base[o] + i) = *reinterpret_cast<const float4*>(grad + i);
+      } else {
+        for (long long j = i; j < hi; ++j) d.base[o][j] = grad[j];
+      }
+    }
+  }
+  __threadfence_system();
+}
+
+extern "C" int kfb_push_ranges(const float* grad, const long long* ranges_dev, int nranges,
+                               long long max_range_elems, long long bucket_lo, long long per,
+                               int nranks, void* const* slot_base, void* stream) {
+  KFB_REQUIRE(nranks > 1 && nranks <= kMaxRanks && per > 0 && per % 4 == 0,
+              "push_ranges: bad ranks / shard length");
+  if (nranges <= 0) return 0;
+  PushDst d;
+  for (int r = 0; r < kMaxRanks; ++r) d.base[r] = r < nranks ? (float*)slot_base[r] : nullptr;
+  long long bx = (max_range_elems / 4 + 255) / 256;
+  if (bx < 1) bx = 1;
+  if (bx > 64) bx = 64;
+  dim3 grid((unsigned)bx, (unsigned)(nranges < 1024 ? nranges : 1024));
+  push_ranges_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(grad, ranges_dev, nranges, bucket_lo,
+                                                            per, nranks, d);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

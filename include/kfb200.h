@@ -46,6 +46,20 @@ int kfb_gemm_stats_rows(void);
 int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
                 long long ldb, long long ldc, int out_fp32, int accumulate, void* stream);
 
+/* Destination of a fused weight-gradient reduce-scatter. The gradient bucket that contains this
+ * output is cut into `nranks` shards of `per` elements; element e of the output has bucket
+ * index rel + e and belongs to rank (rel + e) / per; dst[o] is the address on rank o (a
+ * peer-mapped pointer for o != this rank) where element 0 of the output lands inside this
+ * rank's staging slot. The owners sum their nranks slots in rank order (kfb_allreduce_update_
+ * staged), so the result is bit-identical to the pull-based all-reduce. No counterpart in the
+ * reference (TF schedules NcclAllReduce after the gradient op, T/allreduce.py:298-299). */
+typedef struct kfb_push_target {
+  int nranks;
+  long long per;
+  long long rel;
+  void* dst[8];
+} kfb_push_target;
+
 /* C[M,N] (fp32) (+)= scale * A[K,M]^T * B[K,N]; K is split across CTAs into `workspace`
  * (fp32 slices of M*N) and reduced in a fixed order. FC weight gradient. */
 int kfb_gemm_nt(const void* A, const void* B, float* C, int M, int N, int K, long long lda,
@@ -203,6 +217,19 @@ int kfb_allreduce_update(int mode, int rank, int nranks, void* const* src, void*
                          float* w, const float* g_local, float* m, float* v, void* w16,
                          const kfb_hyper* hp, const float* dyn, const int* skip_flag,
                          float sma_alpha, int blocks, void* stream);
+/* Owner side of the fused weight-gradient reduce-scatter (see kfb_push_target): sums the nranks
+ * local staging slots of this rank's shard of [offset, offset+count), pushes the sum to every
+ * rank and applies the optimizer - kfb_allreduce_update with local instead of peer sources. */
+int kfb_allreduce_update_staged(int rank, int nranks, void* const* reduced, void* const* flags,
+                                long long offset, long long count, unsigned seq, float* w,
+                                float* m, float* v, void* w16, const kfb_hyper* hp,
+                                const float* dyn, const int* skip_flag, const float* stage,
+                                long long stage_stride, int blocks, void* stream);
+/* Pushes arena ranges [lo, hi) (pairs in device memory, multiples of 4) of `grad` into the
+ * owners' staging slots; slot_base[o] = this rank's slot on rank o at arena index 0. */
+int kfb_push_ranges(const float* grad, const long long* ranges_dev, int nranges,
+                    long long max_range_elems, long long bucket_lo, long long per, int nranks,
+                    void* const* slot_base, void* stream);
 int kfb_broadcast_pull(int rank, int nranks, void* const* src, void* const* flags, int root,
                        long long offset, long long count, unsigned seq, float* dst, void* dst16,
                        int blocks, void* stream);
@@ -223,6 +250,17 @@ int kfb_ipc_get_handle(void* p, void* handle_out);
 int kfb_ipc_open(const void* handle, void** out);
 int kfb_ipc_close(void* p);
 int kfb_enable_peer_access(int peer_device);
+
+/* Weight-gradient GEMM / convolution fused with the reduce-scatter of data-parallel training:
+ * the fp32 result is not written locally but scattered over NVLink into the owners' staging
+ * slots - by the epilogue of the tcgen05 kernel itself when one K split suffices (scale 1), by
+ * the split-K reduction kernel otherwise. */
+int kfb_gemm_nt_rs(const void* A, const void* B, int M, int N, int K, long long lda,
+                   long long ldb, float* workspace, long long workspace_bytes, float scale,
+                   const kfb_push_target* push, void* stream);
+int kfb_conv_wgrad_rs(const kfb_conv_desc* d, const void* x, const void* dy, long long lddy,
+                      float* workspace, long long workspace_bytes, float scale,
+                      const kfb_push_target* push, void* stream);
 
 /* ---- wider model zoo (csrc/extra_ops.cu) ------------------------------------------------ */
 /* Activations on NHWC fp16 rows. kind: 1 relu, 2 relu6 (MobileNet-v2,

@@ -316,6 +316,10 @@ class BenchmarkCNN:
                                         aux_weight=self.model.aux_loss_weight,
                                         dropout_seed=4321 + self.rank)
         self.engine = UpdateEngine(p, self.store, self.comm, self.model, seed=self.seed)
+        if getattr(self.engine, "fused_push", False) and hasattr(self.executor,
+                                                                 "rs_capable_params"):
+            self.engine.register_rs_params(self.executor.rs_capable_params())
+            self.executor.push_lookup = self.engine.push_target
         self.input_source = self._make_input_source(phase_train)
 
     def _make_input_source(self, train: bool):

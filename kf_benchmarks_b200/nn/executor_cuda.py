@@ -67,6 +67,8 @@ class CudaExecutor:
         self.dropout_seed = int(dropout_seed)
         self.step_index = 0
         self._stream = None
+        # set by the benchmark driver when --comm_impl=p2p_fused: name -> kfb_push_target
+        self.push_lookup: Optional[Callable[[str], object]] = None
         dev = self.device
         n = graph.batch_size
 
@@ -759,6 +761,12 @@ class CudaExecutor:
             if self.needs_grad[xin.id]:
                 raise NotImplementedError("input gradient of a tiny-C stem conv is not built")
             col = info["col"]
+            push = self.push_lookup(kname) if self.push_lookup else None
+            if push is not None:
+                native.call("gemm_nt_rs", gy.p, ptr(col), i32(d.k), i32(info["kpad"]),
+                            i32(gy.rows), i64(gy.ld), i64(info["kpad"]), ptr(self.workspace),
+                            i64(self.workspace.numel() * 4), f32(1.0), ctypes.byref(push), s)
+                return
             native.call("gemm_nt", gy.p, ptr(col), self._g32(kname), i32(d.k), i32(info["kpad"]),
                         i32(gy.rows), i64(gy.ld), i64(info["kpad"]), i64(info["kpad"]),
                         ptr(self.workspace), i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
@@ -769,6 +777,13 @@ class CudaExecutor:
             if info["dgrad_zero_fill"] and not acc:
                 gx.t.zero_()
             native.call("conv_dgrad", ctypes.byref(d), gy.p, self._w16(kname), gx.p, i32(acc), s)
+        push = self.push_lookup(kname) if self.push_lookup else None
+        if push is not None:
+            # fused GEMM + reduce-scatter: tiles go straight to the owning rank over NVLink
+            native.call("conv_wgrad_rs", ctypes.byref(d), x.p, gy.p, i64(gy.ld),
+                        ptr(self.workspace), i64(self.workspace.numel() * 4), f32(1.0),
+                        ctypes.byref(push), s)
+            return
         native.call("conv_wgrad", ctypes.byref(d), x.p, gy.p, i64(gy.ld), self._g32(kname),
                     ptr(self.workspace), i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
 
@@ -898,9 +913,15 @@ class CudaExecutor:
             native.call("gemm_nn", gy.p, self._w16(spec.name), gx.p, i32(gy.rows), i32(in_pad),
                         i32(out), i64(gy.ld), i64(in_pad), i64(gx.ld), i32(0),
                         i32(self._acc(node, 0)), s)
-        native.call("gemm_nt", gy.p, x.p, self._g32(spec.name), i32(out), i32(in_pad),
-                    i32(gy.rows), i64(gy.ld), i64(x.ld), i64(in_pad), ptr(self.workspace),
-                    i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
+        push = self.push_lookup(spec.name) if self.push_lookup else None
+        if push is not None:
+            native.call("gemm_nt_rs", gy.p, x.p, i32(out), i32(in_pad), i32(gy.rows), i64(gy.ld),
+                        i64(x.ld), ptr(self.workspace), i64(self.workspace.numel() * 4), f32(1.0),
+                        ctypes.byref(push), s)
+        else:
+            native.call("gemm_nt", gy.p, x.p, self._g32(spec.name), i32(out), i32(in_pad),
+                        i32(gy.rows), i64(gy.ld), i64(x.ld), i64(in_pad), ptr(self.workspace),
+                        i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
 
     def _bwd_dropout(self, node, s):
         xin = node.inputs[0]
@@ -944,6 +965,17 @@ class CudaExecutor:
         off = node.attrs["before"]
         native.call("copy2d", ctypes.c_void_p(gy.t.data_ptr() + off * 2), i64(gy.ld), gx.p,
                     i64(gx.ld), i64(gx.rows), i32(gx.cols), i32(self._acc(node, 0)), s)
+
+    def rs_capable_params(self) -> List[str]:
+        """Variables whose weight-gradient kernel can scatter its result to the owning ranks
+        (kfb_conv_wgrad_rs / kfb_gemm_nt_rs): conv kernels and FC weights."""
+        names = []
+        for node in self.graph.nodes:
+            if node.op == "conv":
+                names.append(node.params["kernel"].name)
+            elif node.op == "affine":
+                names.append(node.params["weights"].name)
+        return names
 
     # ------------------------------------------------------------------ inspection
     def logits(self) -> torch.Tensor:

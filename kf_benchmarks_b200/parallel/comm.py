@@ -236,4 +236,4 @@ def create_comm(params, device) -> Comm:
         return TorchDistComm("nccl", dev)
     if impl == "gloo":
         raise ValueError("--comm_impl=gloo needs --device=cpu")
-    return P2PComm(dev)
+    return P2PComm(dev)      # p2p and p2p_fused

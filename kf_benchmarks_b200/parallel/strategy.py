@@ -41,6 +41,12 @@ from .comm import Comm, P2PComm, TorchDistComm
 OPT_IDS = {"sgd": 0, "momentum": 1, "rmsprop": 2, "adam": 3}
 
 
+class PushTarget(ctypes.Structure):
+    """Mirror of ``kfb_push_target`` (include/kfb200.h)."""
+    _fields_ = [("nranks", ctypes.c_int), ("per", ctypes.c_longlong), ("rel", ctypes.c_longlong),
+                ("dst", ctypes.c_void_p * 8)]
+
+
 class Hyper(ctypes.Structure):
     """Mirror of ``kfb_hyper`` (include/kfb200.h)."""
     _fields_ = [("opt", ctypes.c_int), ("lr", ctypes.c_float), ("momentum", ctypes.c_float),
@@ -132,6 +138,15 @@ class UpdateEngine:
         # values (the kernels read it instead of the by-value fields when given)
         self.dyn = None
         self._dyn_host = None
+        # p2p_fused: weight-gradient kernels push their tiles to the owning rank (fused GEMM +
+        # reduce-scatter); only on the overlapped synchronous all-reduce path
+        self.fused_push = bool(
+            getattr(params, "comm_impl", "p2p") == "p2p_fused" and self.cuda and
+            isinstance(comm, P2PComm) and self.algo == "allreduce" and
+            not self.auto_loss_scale and not self.relaxed)
+        self._push_targets = {}
+        if self.fused_push:
+            self.buckets = self._plan_buckets_on_slots(bucket_elems)
         self._setup_comm_buffers()
 
     # ------------------------------------------------------------------ setup
@@ -142,6 +157,58 @@ class UpdateEngine:
         if p.fp16_loss_scale is not None:
             return float(p.fp16_loss_scale)
         return float(self.model.get_fp16_loss_scale()) if (p.use_fp16 or self.cuda) else 1.0
+
+    def _plan_buckets_on_slots(self, bucket_elems: int) -> List[Tuple[int, int]]:
+        """Buckets that only cut between variables, so every weight gradient lies in exactly
+        one bucket and its owner map is a single (lo, per) pair."""
+        out, lo, hi = [], 0, 0
+        for slot in self.store.order:
+            hi = slot.offset + (slot.numel + 127) // 128 * 128
+            if hi - lo >= bucket_elems:
+                out.append((lo, hi))
+                lo = hi
+        if hi > lo:
+            out.append((lo, hi))
+        return out
+
+    def register_rs_params(self, names) -> None:
+        """Called by the executor with the variables whose gradient kernels can push (conv
+        kernels, FC weights). Everything else in a bucket is pushed by ``kfb_push_ranges``."""
+        if not self.fused_push:
+            return
+        c, st = self.comm, self.store
+        n = c.size
+        names = set(names)
+        self.stage = c.symm_alloc(n * self.total, torch.float32)
+        stage_peers = c.peers(self.stage)
+        slot_bytes = self.total * 4
+        self._slot_base = (ctypes.c_void_p * 8)()
+        for o in range(n):
+            self._slot_base[o] = stage_peers[o] + c.rank * slot_bytes
+        self._bucket_push = []
+        slots = list(st.order)
+        for (lo, hi) in self.buckets:
+            per = ((hi - lo + n - 1) // n + 3) & ~3
+            ranges = []
+            for s in slots:
+                if not (lo <= s.offset < hi):
+                    continue
+                if s.spec.name in names:
+                    t = PushTarget()
+                    t.nranks, t.per, t.rel = n, per, s.offset - lo
+                    for o in range(n):
+                        t.dst[o] = stage_peers[o] + c.rank * slot_bytes + s.offset * 4
+                    self._push_targets[s.spec.name] = t
+                else:
+                    ranges.append((s.offset, s.offset + (s.numel + 3) // 4 * 4))
+            flat = [v for r in ranges for v in r]
+            dev = (torch.tensor(flat, dtype=torch.int64, device=self.device) if flat else None)
+            longest = max((b - a for a, b in ranges), default=0)
+            self._bucket_push.append((per, dev, len(ranges), longest))
+
+    def push_target(self, name):
+        """ctypes descriptor for the fused reduce-scatter of variable ``name`` (or None)."""
+        return self._push_targets.get(name)
 
     def _setup_comm_buffers(self) -> None:
         c = self.comm
@@ -326,6 +393,17 @@ class UpdateEngine:
         mode = 1 if algo == "sma" else 0
         src = self._w_ptrs if mode == 1 else self._grad_ptrs
         h = self._h
+        if self.fused_push and self._push_targets:
+            per, ranges_dev, nranges, longest = self._bucket_push[self.buckets.index(bucket)]
+            if nranges:
+                native.call("push_ranges", ptr(st.grad), ptr(ranges_dev), i32(nranges),
+                            i64(longest), i64(lo), i64(per), i32(c.size), self._slot_base,
+                            self._s(stream))
+            native.call("allreduce_update_staged", i32(c.rank), i32(c.size), self._red_ptrs,
+                        self._flag_ptrs, i64(lo), i64(hi - lo), ctypes.c_uint(c.next_seq()),
+                        ptr(st.w32), ptr(self.m), ptr(self.v), ptr(st.w16), ctypes.byref(h),
+                        None, None, ptr(self.stage), i64(self.total), i32(0), self._s(stream))
+            return
         native.call("allreduce_update", i32(mode), i32(c.rank), i32(c.size), src, self._red_ptrs,
                     self._flag_ptrs, i64(lo), i64(hi - lo), ctypes.c_uint(c.next_seq()),
                     ptr(st.w32), ptr(st.grad), ptr(self.m), ptr(self.v), ptr(st.w16),

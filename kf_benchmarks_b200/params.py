@@ -196,8 +196,10 @@ NUM_REFERENCE_FLAGS = len(flags.param_specs)
 
 # ---- B200-native additions ------------------------------------------------------------
 _D.DEFINE_alias("kungfu_strategy", "kungfu_option")
-_D.DEFINE_enum("comm_impl", "p2p", ("p2p", "nccl", "gloo"),
-               "p2p: fused NVLink all-reduce+update kernels (the product). nccl: "
+_D.DEFINE_enum("comm_impl", "p2p", ("p2p", "p2p_fused", "nccl", "gloo"),
+               "p2p: fused NVLink all-reduce+update kernels (the product). p2p_fused: in "
+               "addition the weight-gradient GEMMs scatter their tiles to the owning ranks from "
+               "their own epilogue (GEMM + reduce-scatter in one kernel). nccl: "
                "torch.distributed NCCL + separate update (comparison baseline). gloo: CPU ranks.")
 _D.DEFINE_float("sma_alpha", 0.1, "Blend factor of SynchronousAveraging.")
 _D.DEFINE_integer("bucket_bytes", 8 << 20, "Target gradient bucket size for overlap.")

@@ -74,3 +74,27 @@ def test_replicas_stay_bit_identical_and_match_nccl_baseline(tmp_path):
     a, b = outs["p2p"][0], outs["nccl"][0]
     cos = float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b)))
     assert cos > 0.9999 and np.abs(a - b).max() < 5e-2
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+@pytest.mark.parametrize("model,data,batch", [("resnet20", "cifar10", 32), ("vgg11", "imagenet", 8)])
+def test_fused_wgrad_reduce_scatter_is_bit_identical_to_the_pull_path(tmp_path, model, data, batch):
+    """--comm_impl=p2p_fused: the weight-gradient kernels push their tiles to the owning rank
+    (tcgen05 epilogue for single-split GEMMs such as the VGG FC layers, the split-K reduction
+    otherwise); owners sum their staging slots in rank order, so the trained variables must be
+    bit-identical to the pull-based all-reduce."""
+    import json
+    import numpy as np
+    outs = {}
+    for impl in ("p2p", "p2p_fused"):
+        d = tmp_path / impl
+        d.mkdir()
+        kw = dict(model=model, data_name=data, batch_size=batch, use_fp16=True,
+                  optimizer="momentum", init_learning_rate=0.01, num_batches=5,
+                  num_warmup_batches=0, variable_update="replicated", num_gpus=2, comm_impl=impl)
+        res = _launch(2, [os.path.join(ROOT, "tests", "helpers", "rank_worker.py"), json.dumps(kw),
+                          str(d)])
+        assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+        outs[impl] = [np.load(str(d / ("rank%d.npz" % r)))["w"] for r in range(2)]
+        assert np.array_equal(outs[impl][0], outs[impl][1])
+    assert np.array_equal(outs["p2p"][0], outs["p2p_fused"][0])
