@@ -90,11 +90,12 @@ def test_fused_wgrad_reduce_scatter_is_bit_identical_to_the_pull_path(tmp_path, 
         d = tmp_path / impl
         d.mkdir()
         kw = dict(model=model, data_name=data, batch_size=batch, use_fp16=True,
-                  optimizer="momentum", init_learning_rate=0.01, num_batches=5,
+                  optimizer="momentum", init_learning_rate=1e-4, num_batches=5,
                   num_warmup_batches=0, variable_update="replicated", num_gpus=2, comm_impl=impl)
         res = _launch(2, [os.path.join(ROOT, "tests", "helpers", "rank_worker.py"), json.dumps(kw),
                           str(d)])
         assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
         outs[impl] = [np.load(str(d / ("rank%d.npz" % r)))["w"] for r in range(2)]
+        assert np.isfinite(outs[impl][0]).all()
         assert np.array_equal(outs[impl][0], outs[impl][1])
     assert np.array_equal(outs["p2p"][0], outs["p2p_fused"][0])
