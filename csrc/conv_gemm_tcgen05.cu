@@ -119,6 +119,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
   using Cfg = TileCfg<BN>;
   const int kStages = p.stages;
   constexpr uint32_t kAMajor = (MODE == GEMM_NT || MODE == WGRAD) ? kMajorMN : kMajorK;
+  // only the weight-gradient modes carry the fused reduce-scatter epilogue
+  constexpr bool kCanPush = (MODE == GEMM_NT || MODE == WGRAD);
   constexpr uint32_t kBMajor =
       (MODE == GEMM_NT || MODE == WGRAD || MODE == DGRAD || MODE == GEMM_NN) ? kMajorMN : kMajorK;
 
@@ -508,7 +510,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           const long long ro = __shfl_sync(0xffffffffu, row_off, r);
           const long long e_idx = base + ro * p.ldc + pcol;
           uint8_t* obase = reinterpret_cast<uint8_t*>(p.out);
-          if (p.push_n > 1) {
+          if (kCanPush && p.push_n > 1) {
             int owner = 0;
 #pragma unroll
             for (int r = 1; r < 8; ++r) owner += (r < p.push_n && e_idx >= p.push_bound[r]) ? 1 : 0;
@@ -569,7 +571,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     if (do_stats && st_nblk >= 0) flush_stats(st_nblk);
     // remote (NVLink) stores of a fused reduce-scatter must be performed system-wide before
     // this kernel counts as complete for the ranks that wait on the stream-ordered READY flag
-    if (p.push_n > 1) __threadfence_system();
+    if (kCanPush && p.push_n > 1) __threadfence_system();
   }
 
   tc_fence_before();
