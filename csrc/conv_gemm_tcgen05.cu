@@ -585,20 +585,53 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
 // ---------------------------------------------------------------------------
 // Deterministic split-K reduction: out[i] = (accumulate ? out[i] : 0) + sum_z ws[z][i]
 // ---------------------------------------------------------------------------
-__global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out,
-                                     long long n, int splits, int accumulate, float scale) {
+// Block = (32 float4 columns, kSplitLanes split lanes): lane y sums slices y, y+L, ... so the
+// loads of a thin output (a 1x1 conv's few thousand weights) still fill the memory pipeline;
+// the lane sums are combined in lane order, so the result does not depend on the launch.
+constexpr int kSplitLanes = 8;
+// launch shape: as many split lanes as there are splits (up to 8), 256 threads per block
+static inline void splitk_launch_shape(long long n4, int splits, dim3* grid, dim3* block) {
+  int lanes = 1;
+  while (lanes < kSplitLanes && lanes < splits) lanes <<= 1;
+  const int bx = 256 / lanes;
+  *block = dim3(bx, lanes);
+  *grid = dim3((unsigned)((n4 + bx - 1) / bx));
+}
+__global__ void __launch_bounds__(256)
+    splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out, long long n,
+                         int splits, int accumulate, float scale) {
+  __shared__ float4 sh[256];  // [blockDim.y lanes][blockDim.x columns], 256 threads in all
   const long long i4 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
-  if (i4 >= n) return;
-  if (i4 + 4 <= n) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int z = 0; z < splits; ++z) {
-      const float4 v = *reinterpret_cast<const float4*>(ws + static_cast<long long>(z) * n + i4);
-      acc.x += v.x;
-      acc.y += v.y;
-      acc.z += v.z;
-      acc.w += v.w;
+  const bool full = i4 + 4 <= n;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i4 < n) {
+    for (int z = threadIdx.y; z < splits; z += blockDim.y) {
+      const float* p = ws + static_cast<long long>(z) * n + i4;
+      if (full) {
+        const float4 v = *reinterpret_cast<const float4*>(p);
+        acc.x += v.x;
+        acc.y += v.y;
+        acc.z += v.z;
+        acc.w += v.w;
+      } else {
+        acc.x += p[0];
+        if (i4 + 1 < n) acc.y += p[1];
+        if (i4 + 2 < n) acc.z += p[2];
+      }
     }
-    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+  }
+  sh[threadIdx.y * blockDim.x + threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y != 0 || i4 >= n) return;
+  for (int l = 1; l < static_cast<int>(blockDim.y); ++l) {
+    const float4 v = sh[l * blockDim.x + threadIdx.x];
+    acc.x += v.x;
+    acc.y += v.y;
+    acc.z += v.z;
+    acc.w += v.w;
+  }
+  acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+  if (full) {
     float4* o = reinterpret_cast<float4*>(out + i4);
     if (accumulate) {
       const float4 old = *o;
@@ -606,12 +639,8 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __rest
     }
     *o = acc;
   } else {
-    for (long long i = i4; i < n; ++i) {
-      float acc = 0.f;
-      for (int z = 0; z < splits; ++z) acc += ws[static_cast<long long>(z) * n + i];
-      acc *= scale;
-      out[i] = accumulate ? out[i] + acc : acc;
-    }
+    const float e[3] = {acc.x, acc.y, acc.z};
+    for (int j = 0; i4 + j < n; ++j) out[i4 + j] = accumulate ? out[i4 + j] + e[j] : e[j];
   }
 }
 
@@ -623,31 +652,49 @@ struct PushTarget {
   float* base[8];
 };
 
-__global__ void splitk_reduce_push_kernel(const float* __restrict__ ws, PushTarget t, long long n,
-                                          int splits, float scale) {
+__global__ void __launch_bounds__(256)
+    splitk_reduce_push_kernel(const float* __restrict__ ws, PushTarget t, long long n, int splits,
+                              float scale) {
+  __shared__ float4 sh[256];  // [blockDim.y lanes][blockDim.x columns], 256 threads in all
   const long long i4 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
-  if (i4 >= n) return;
+  const bool full = i4 + 4 <= n;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i4 < n) {
+    for (int z = threadIdx.y; z < splits; z += blockDim.y) {
+      const float* p = ws + static_cast<long long>(z) * n + i4;
+      if (full) {
+        const float4 v = *reinterpret_cast<const float4*>(p);
+        acc.x += v.x;
+        acc.y += v.y;
+        acc.z += v.z;
+        acc.w += v.w;
+      } else {
+        acc.x += p[0];
+        if (i4 + 1 < n) acc.y += p[1];
+        if (i4 + 2 < n) acc.z += p[2];
+      }
+    }
+  }
+  sh[threadIdx.y * blockDim.x + threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y != 0 || i4 >= n) return;
+  for (int l = 1; l < static_cast<int>(blockDim.y); ++l) {
+    const float4 v = sh[l * blockDim.x + threadIdx.x];
+    acc.x += v.x;
+    acc.y += v.y;
+    acc.z += v.z;
+    acc.w += v.w;
+  }
+  acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
   int owner = 0;
 #pragma unroll
   for (int r = 1; r < 8; ++r) owner += (r < t.n && i4 >= t.bound[r]) ? 1 : 0;
   float* out = t.base[owner];
-  if (i4 + 4 <= n) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int z = 0; z < splits; ++z) {
-      const float4 v = *reinterpret_cast<const float4*>(ws + static_cast<long long>(z) * n + i4);
-      acc.x += v.x;
-      acc.y += v.y;
-      acc.z += v.z;
-      acc.w += v.w;
-    }
-    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+  if (full) {
     *reinterpret_cast<float4*>(out + i4) = acc;
   } else {
-    for (long long i = i4; i < n; ++i) {
-      float acc = 0.f;
-      for (int z = 0; z < splits; ++z) acc += ws[static_cast<long long>(z) * n + i];
-      out[i] = acc * scale;
-    }
+    const float e[3] = {acc.x, acc.y, acc.z};
+    for (int j = 0; i4 + j < n; ++j) out[i4 + j] = e[j];
   }
   __threadfence_system();
 }
@@ -918,14 +965,15 @@ static int fill_push(const kfb_push_target* t, long long out_elems, int* n_out,
 static int finish_wgrad(float* workspace, float* out, long long slice, int splits, int accumulate,
                         float scale, const kfb_push_target* push, cudaStream_t st) {
   const long long n4 = (slice + 3) / 4;
+  dim3 grid, block;
+  splitk_launch_shape(n4, splits, &grid, &block);
   if (push != nullptr && push->nranks > 1) {
     PushTarget t;
     if (fill_push(push, slice, &t.n, t.bound, t.base)) return 2;
-    splitk_reduce_push_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(workspace, t, slice,
-                                                                           splits, scale);
+    splitk_reduce_push_kernel<<<grid, block, 0, st>>>(workspace, t, slice, splits, scale);
   } else {
-    splitk_reduce_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(workspace, out, slice,
-                                                                      splits, accumulate, scale);
+    splitk_reduce_kernel<<<grid, block, 0, st>>>(workspace, out, slice, splits, accumulate,
+                                                 scale);
   }
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -96,14 +96,11 @@ __global__ void __launch_bounds__(256)
                     __half* __restrict__ y, long long ldy, DwGeom g) {
   const int vpr = g.c >> 3;
   const long long total = static_cast<long long>(g.n) * g.p * g.q * vpr;
+  const bool fits32 = total < 0xFFFFFFFFll;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % vpr);
-    long long t = i / vpr;
-    const int q = static_cast<int>(t % g.q);
-    t /= g.q;
-    const int p = static_cast<int>(t % g.p);
-    const int n = static_cast<int>(t / g.p);
+    int cv, q, p, n;
+    split_index(i, fits32, vpr, g.q, g.p, cv, q, p, n);
     const int h0 = p * g.sh - g.pad_h, w0 = q * g.sw - g.pad_w;
     float acc[8];
 #pragma unroll
@@ -132,14 +129,11 @@ __global__ void __launch_bounds__(256)
                     __half* __restrict__ dx, long long lddx, int accumulate, DwGeom g) {
   const int vpr = g.c >> 3;
   const long long total = static_cast<long long>(g.n) * g.h * g.w * vpr;
+  const bool fits32 = total < 0xFFFFFFFFll;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % vpr);
-    long long t = i / vpr;
-    const int ww = static_cast<int>(t % g.w);
-    t /= g.w;
-    const int hh = static_cast<int>(t % g.h);
-    const int n = static_cast<int>(t / g.h);
+    int cv, ww, hh, n;
+    split_index(i, fits32, vpr, g.w, g.h, cv, ww, hh, n);
     float acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0.f;

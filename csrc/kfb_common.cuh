@@ -228,6 +228,30 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// i -> (i % d0, (i / d0) % d1, (i / d0 / d1) % d2, i / d0 / d1 / d2) with 32-bit divisions when
+// the index space allows it (64-bit integer division costs ~10x more and made the pooling /
+// im2col kernels ALU-bound).
+__device__ __forceinline__ void split_index(long long i, bool fits32, int d0, int d1, int d2,
+                                            int& r0, int& r1, int& r2, int& r3) {
+  if (fits32) {
+    unsigned t = static_cast<unsigned>(i);
+    const unsigned q0 = t / static_cast<unsigned>(d0);
+    r0 = static_cast<int>(t - q0 * d0);
+    const unsigned q1 = q0 / static_cast<unsigned>(d1);
+    r1 = static_cast<int>(q0 - q1 * d1);
+    const unsigned q2 = q1 / static_cast<unsigned>(d2);
+    r2 = static_cast<int>(q1 - q2 * d2);
+    r3 = static_cast<int>(q2);
+  } else {
+    r0 = static_cast<int>(i % d0);
+    long long t = i / d0;
+    r1 = static_cast<int>(t % d1);
+    t /= d1;
+    r2 = static_cast<int>(t % d2);
+    r3 = static_cast<int>(t / d2);
+  }
+}
+
 // 8 halves <-> 8 floats through one 16-byte access (the unit of the NHWC elementwise kernels)
 struct alignas(16) Half8 {
   __half2 h[4];

@@ -181,19 +181,34 @@ __global__ void __launch_bounds__(kRedThreads)
   }
 }
 
-// Folds the stage-1 partials of channel c in a fixed order. Block = (32 channels, 8 lanes):
-// lane ty sums blocks ty, ty+8, ... (coalesced 128-byte rows), then lane 0 adds the 8 lane sums.
-constexpr int kFoldLanes = 16;
+// Folds the stage-1 partials of channel c in a fixed order. Block = (32 channels, 32 lanes):
+// lane ty sums blocks ty, ty+32, ... (coalesced 128-byte rows) through four independent
+// accumulators so the L2 round trips overlap, then lane 0 adds the lane sums.
+constexpr int kFoldLanes = 32;
 __device__ __forceinline__ bool fold_partials(const float* __restrict__ partial, int nblocks,
                                               int C, int c, float& s0, float& s1) {
   __shared__ float sh[2][kFoldLanes][32];
   const int tx = threadIdx.x, ty = threadIdx.y;
   float a = 0.f, b = 0.f;
   if (c < C) {
-    for (int blk = ty; blk < nblocks; blk += kFoldLanes) {
-      a += partial[static_cast<long long>(blk) * 2 * C + c];
-      b += partial[static_cast<long long>(blk) * 2 * C + C + c];
+    float a4[4] = {0.f, 0.f, 0.f, 0.f}, b4[4] = {0.f, 0.f, 0.f, 0.f};
+    const long long row = 2ll * C;
+    int blk = ty;
+    for (; blk + 3 * kFoldLanes < nblocks; blk += 4 * kFoldLanes) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float* q = partial + static_cast<long long>(blk + u * kFoldLanes) * row + c;
+        a4[u] += q[0];
+        b4[u] += q[C];
+      }
     }
+    for (int u = 0; blk < nblocks; blk += kFoldLanes, ++u) {
+      const float* q = partial + static_cast<long long>(blk) * row + c;
+      a4[u] += q[0];
+      b4[u] += q[C];
+    }
+    a = (a4[0] + a4[1]) + (a4[2] + a4[3]);
+    b = (b4[0] + b4[1]) + (b4[2] + b4[3]);
   }
   sh[0][ty][tx] = a;
   sh[1][ty][tx] = b;
@@ -459,14 +474,11 @@ __global__ void __launch_bounds__(256)
                     long long ldy, unsigned char* __restrict__ argmax, PoolGeom g, int is_max) {
   const int vpr = g.c >> 3;
   const long long total = static_cast<long long>(g.n) * g.p * g.q * vpr;
+  const bool fits32 = total < 0xFFFFFFFFll;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % vpr);
-    long long t = i / vpr;
-    const int q = static_cast<int>(t % g.q);
-    t /= g.q;
-    const int p = static_cast<int>(t % g.p);
-    const int n = static_cast<int>(t / g.p);
+    int cv, q, p, n;
+    split_index(i, fits32, vpr, g.q, g.p, cv, q, p, n);
     const int h0 = p * g.sh - g.pad_h, w0 = q * g.sw - g.pad_w;
     float acc[8];
     int arg[8];
@@ -521,14 +533,11 @@ __global__ void __launch_bounds__(256)
                     long long lddx, int accumulate, PoolGeom g, int is_max) {
   const int vpr = g.c >> 3;
   const long long total = static_cast<long long>(g.n) * g.h * g.w * vpr;
+  const bool fits32 = total < 0xFFFFFFFFll;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % vpr);
-    long long t = i / vpr;
-    const int ww = static_cast<int>(t % g.w);
-    t /= g.w;
-    const int hh = static_cast<int>(t % g.h);
-    const int n = static_cast<int>(t / g.h);
+    int cv, ww, hh, n;
+    split_index(i, fits32, vpr, g.w, g.h, cv, ww, hh, n);
     float acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0.f;
@@ -670,14 +679,12 @@ __global__ void __launch_bounds__(256)
   const int kpad = TC > 0 ? ((TC * TKH * TKW + 7) / 8 * 8) : kpad_rt;
   const int vpr = kpad >> 3;
   const long long total = static_cast<long long>(n) * p * q * vpr;
+  const bool fits32 = total < 0xFFFFFFFFll;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long row = i / vpr;
-    const int kv = static_cast<int>(i - row * vpr);
-    const int qq = static_cast<int>(row % q);
-    const long long t = row / q;
-    const int pp = static_cast<int>(t % p);
-    const int nn = static_cast<int>(t / p);
+    int kv, qq, pp, nn;
+    split_index(i, fits32, vpr, q, p, kv, qq, pp, nn);
+    const long long row = (static_cast<long long>(nn) * p + pp) * q + qq;
     const int h0 = pp * sh - pad_h, w0 = qq * sw - pad_w;
     const __half* xin = x + static_cast<long long>(nn) * h * w * c;
     float v[8];
