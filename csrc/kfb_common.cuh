@@ -266,6 +266,14 @@ __device__ __forceinline__ void load8(const __half* p, float (&f)[8]) {
     f[2 * i + 1] = t.y;
   }
 }
+__device__ __forceinline__ void unpack8(const Half8& v, float (&f)[8]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __half22float2(v.h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
 __device__ __forceinline__ void store8(__half* p, const float (&f)[8]) {
   Half8 v;
 #pragma unroll

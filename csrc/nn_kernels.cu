@@ -77,16 +77,25 @@ __global__ void __launch_bounds__(kRedThreads)
       }
     }
     if (active) {
+      // kRowUnroll rows per iteration, all their 16-byte loads issued before the first use:
+      // the kernel is bound by bytes in flight per SM (512-1024 resident threads), not by math.
+      constexpr int kRowUnroll = 4;
       if (MODE == 0) {
         long long r = r_begin + tr;
-        for (; r + row_lanes < r_end; r += 2 * row_lanes) {
-          float v0[8], v1[8];
-          load8(x + r * ldx + cv * 8, v0);
-          load8(x + (r + row_lanes) * ldx + cv * 8, v1);
+        for (; r + (kRowUnroll - 1) * row_lanes < r_end; r += kRowUnroll * row_lanes) {
+          Half8 q[kRowUnroll];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            a[i] += v0[i] + v1[i];
-            b[i] += v0[i] * v0[i] + v1[i] * v1[i];
+          for (int u = 0; u < kRowUnroll; ++u)
+            q[u] = *reinterpret_cast<const Half8*>(x + (r + u * row_lanes) * ldx + cv * 8);
+#pragma unroll
+          for (int u = 0; u < kRowUnroll; ++u) {
+            float v[8];
+            unpack8(q[u], v);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              a[i] += v[i];
+              b[i] += v[i] * v[i];
+            }
           }
         }
         for (; r < r_end; r += row_lanes) {
@@ -99,48 +108,58 @@ __global__ void __launch_bounds__(kRedThreads)
           }
         }
       } else {
-        for (long long r = r_begin + tr; r < r_end; r += 2 * row_lanes) {
-          const bool two = r + row_lanes < r_end;
-          const long long r1 = two ? r + row_lanes : r;
-          float g0[8], g1[8], v0[8], v1[8], m0[8], m1[8];
-          load8(dy + r * lddy + cv * 8, g0);
-          load8(dy + r1 * lddy + cv * 8, g1);
+        for (long long r = r_begin + tr; r < r_end; r += kRowUnroll * row_lanes) {
+          long long ru[kRowUnroll];
+          bool ok[kRowUnroll];
+          Half8 gq[kRowUnroll], xq[kRowUnroll], mq[kRowUnroll];
+#pragma unroll
+          for (int u = 0; u < kRowUnroll; ++u) {
+            ru[u] = r + static_cast<long long>(u) * row_lanes;
+            ok[u] = ru[u] < r_end;
+            if (!ok[u]) ru[u] = r;  // any valid row; its contribution is zeroed below
+            gq[u] = *reinterpret_cast<const Half8*>(dy + ru[u] * lddy + cv * 8);
+          }
           if (MODE == 1) {
-            load8(x + r * ldx + cv * 8, v0);
-            load8(x + r1 * ldx + cv * 8, v1);
+#pragma unroll
+            for (int u = 0; u < kRowUnroll; ++u)
+              xq[u] = *reinterpret_cast<const Half8*>(x + ru[u] * ldx + cv * 8);
           }
           if (mask != nullptr) {
-            load8(mask + r * ldm + cv * 8, m0);
-            load8(mask + r1 * ldm + cv * 8, m1);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              g0[i] = m0[i] > 0.f ? g0[i] : 0.f;
-              g1[i] = m1[i] > 0.f ? g1[i] : 0.f;
-            }
-          } else if (recompute_mask) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const bool ng = (neg_bits >> i) & 1u;
-              g0[i] = ((v0[i] > thr[i]) != ng) ? g0[i] : 0.f;
-              g1[i] = ((v1[i] > thr[i]) != ng) ? g1[i] : 0.f;
-            }
+            for (int u = 0; u < kRowUnroll; ++u)
+              mq[u] = *reinterpret_cast<const Half8*>(mask + ru[u] * ldm + cv * 8);
           }
-          if (!two) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) g1[i] = 0.f;
-          }
-          if (MODE == 1) {
+          for (int u = 0; u < kRowUnroll; ++u) {
+            float g[8], v[8];
+            unpack8(gq[u], g);
+            if (MODE == 1) unpack8(xq[u], v);
+            if (mask != nullptr) {
+              float m[8];
+              unpack8(mq[u], m);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              a[i] += g0[i] + g1[i];
-              b[i] += g0[i] * (v0[i] - mu[i]) + g1[i] * (v1[i] - mu[i]);
+              for (int i = 0; i < 8; ++i) g[i] = m[i] > 0.f ? g[i] : 0.f;
+            } else if (recompute_mask) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const bool ng = (neg_bits >> i) & 1u;
+                g[i] = ((v[i] > thr[i]) != ng) ? g[i] : 0.f;
+              }
             }
-          } else {
+            if (!ok[u]) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] += g0[i] + g1[i];
-            if (dz != nullptr) {
-              store8(dz + r * lddz + cv * 8, g0);
-              if (two) store8(dz + r1 * lddz + cv * 8, g1);
+              for (int i = 0; i < 8; ++i) g[i] = 0.f;
+            }
+            if (MODE == 1) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                a[i] += g[i];
+                b[i] += g[i] * (v[i] - mu[i]);
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) a[i] += g[i];
+              if (dz != nullptr && ok[u]) store8(dz + ru[u] * lddz + cv * 8, g);
             }
           }
         }
@@ -469,9 +488,17 @@ struct PoolGeom {
   int n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w;
 };
 
+// TK / TS > 0 fix the (square) window and stride at compile time: the 3x3/2 and 2x2/2 pools of
+// the zoo then run without integer divisions and with fully unrolled window loops.
+template <int TK, int TS>
 __global__ void __launch_bounds__(256)
     pool_fwd_kernel(const __half* __restrict__ x, long long ldx, __half* __restrict__ y,
-                    long long ldy, unsigned char* __restrict__ argmax, PoolGeom g, int is_max) {
+                    long long ldy, unsigned char* __restrict__ argmax, PoolGeom gg, int is_max) {
+  PoolGeom g = gg;
+  if (TK > 0) {
+    g.kh = g.kw = TK;
+    g.sh = g.sw = TS;
+  }
   const int vpr = g.c >> 3;
   const long long total = static_cast<long long>(g.n) * g.p * g.q * vpr;
   const bool fits32 = total < 0xFFFFFFFFll;
@@ -488,10 +515,12 @@ __global__ void __launch_bounds__(256)
       arg[k] = 0;
     }
     int count = 0;
-    for (int r = 0; r < g.kh; ++r) {
+#pragma unroll
+    for (int r = 0; r < (TK > 0 ? TK : g.kh); ++r) {
       const int hh = h0 + r;
       if (hh < 0 || hh >= g.h) continue;
-      for (int s = 0; s < g.kw; ++s) {
+#pragma unroll
+      for (int s = 0; s < (TK > 0 ? TK : g.kw); ++s) {
         const int ww = w0 + s;
         if (ww < 0 || ww >= g.w) continue;
         float v[8];
@@ -527,10 +556,16 @@ __global__ void __launch_bounds__(256)
 }
 
 // Gather formulation: one thread per input vector visits the output windows that cover it.
+template <int TK, int TS>
 __global__ void __launch_bounds__(256)
     pool_bwd_kernel(const __half* __restrict__ dy, long long lddy,
                     const unsigned char* __restrict__ argmax, __half* __restrict__ dx,
-                    long long lddx, int accumulate, PoolGeom g, int is_max) {
+                    long long lddx, int accumulate, PoolGeom gg, int is_max) {
+  PoolGeom g = gg;
+  if (TK > 0) {
+    g.kh = g.kw = TK;
+    g.sh = g.sw = TS;
+  }
   const int vpr = g.c >> 3;
   const long long total = static_cast<long long>(g.n) * g.h * g.w * vpr;
   const bool fits32 = total < 0xFFFFFFFFll;
@@ -699,7 +734,7 @@ __global__ void __launch_bounds__(256)
         const int s = tap - r * kw;
         const int hh = h0 + r, ww = w0 + s;
         if (hh >= 0 && hh < h && ww >= 0 && ww < w)
-          val = __half2float(xin[(static_cast<long long>(hh) * w + ww) * c + cc]);
+          val = __half2float(xin[(hh * w + ww) * c + cc]);  // one image < 2^31 elements
       }
       v[j] = val;
     }
@@ -1112,8 +1147,20 @@ extern "C" int kfb_pool_forward(const void* x, long long ldx, void* y, long long
                                 void* stream) {
   PoolGeom g;
   if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
-  pool_fwd_kernel<<<grid_for((long long)n * p * q * (c / 8)), 256, 0, (cudaStream_t)stream>>>(
-      (const __half*)x, ldx, (__half*)y, ldy, argmax, g, is_max);
+  const int blocks = grid_for((long long)n * p * q * (c / 8));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
+    pool_fwd_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y, ldy, argmax,
+                                                  g, is_max);
+  else if (kh == 2 && kw == 2 && sh == 2 && sw == 2)
+    pool_fwd_kernel<2, 2><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y, ldy, argmax,
+                                                  g, is_max);
+  else if (kh == 3 && kw == 3 && sh == 1 && sw == 1)
+    pool_fwd_kernel<3, 1><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y, ldy, argmax,
+                                                  g, is_max);
+  else
+    pool_fwd_kernel<0, 0><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y, ldy, argmax,
+                                                  g, is_max);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1124,8 +1171,20 @@ extern "C" int kfb_pool_backward(const void* dy, long long lddy, const unsigned 
                                  int pad_w, int is_max, void* stream) {
   PoolGeom g;
   if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
-  pool_bwd_kernel<<<grid_for((long long)n * h * w * (c / 8)), 256, 0, (cudaStream_t)stream>>>(
-      (const __half*)dy, lddy, argmax, (__half*)dx, lddx, accumulate, g, is_max);
+  const int blocks = grid_for((long long)n * h * w * (c / 8));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
+    pool_bwd_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)dy, lddy, argmax, (__half*)dx,
+                                                  lddx, accumulate, g, is_max);
+  else if (kh == 2 && kw == 2 && sh == 2 && sw == 2)
+    pool_bwd_kernel<2, 2><<<blocks, 256, 0, st>>>((const __half*)dy, lddy, argmax, (__half*)dx,
+                                                  lddx, accumulate, g, is_max);
+  else if (kh == 3 && kw == 3 && sh == 1 && sw == 1)
+    pool_bwd_kernel<3, 1><<<blocks, 256, 0, st>>>((const __half*)dy, lddy, argmax, (__half*)dx,
+                                                  lddx, accumulate, g, is_max);
+  else
+    pool_bwd_kernel<0, 0><<<blocks, 256, 0, st>>>((const __half*)dy, lddy, argmax, (__half*)dx,
+                                                  lddx, accumulate, g, is_max);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
