@@ -305,47 +305,26 @@ __global__ void __launch_bounds__(256)
     sh[0] = b0.x; sh[1] = b0.y; sh[2] = b0.z; sh[3] = b0.w;
     sh[4] = b1.x; sh[5] = b1.y; sh[6] = b1.z; sh[7] = b1.w;
   }
-  // kApplyRows rows per iteration with all their 16-byte loads issued up front (the kernel is
-  // bound by bytes in flight per SM). Rows are visited last-to-first: the end of x was written
-  // most recently by the producing conv and is still in L2; the next conv then finds the
-  // beginning of y fresh.
-  constexpr int kApplyRows = 4;
-  const long long stride = static_cast<long long>(gridDim.y) * blockDim.y;
   for (long long rr = static_cast<long long>(blockIdx.y) * blockDim.y + threadIdx.y; rr < rows;
-       rr += kApplyRows * stride) {
-    long long ru[kApplyRows];
-    bool ok[kApplyRows];
-    Half8 xq[kApplyRows], rq[kApplyRows];
+       rr += static_cast<long long>(gridDim.y) * blockDim.y) {
+    // rows are visited last-to-first: the end of x was written most recently by the producing
+    // conv and is still in L2; the next conv then finds the beginning of y fresh
+    const long long r = rows - 1 - rr;
+    float v[8];
+    load8(x + r * ldx + cv * 8, v);
 #pragma unroll
-    for (int u = 0; u < kApplyRows; ++u) {
-      const long long q = rr + u * stride;
-      ok[u] = q < rows;
-      ru[u] = rows - 1 - (ok[u] ? q : rr);
-      xq[u] = *reinterpret_cast<const Half8*>(x + ru[u] * ldx + cv * 8);
-    }
+    for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], sc[k], sh[k]);
     if (res != nullptr) {
+      float rr[8];
+      load8(res + r * ldr + cv * 8, rr);
 #pragma unroll
-      for (int u = 0; u < kApplyRows; ++u)
-        rq[u] = *reinterpret_cast<const Half8*>(res + ru[u] * ldr + cv * 8);
+      for (int k = 0; k < 8; ++k) v[k] += rr[k];
     }
+    if (relu) {
 #pragma unroll
-    for (int u = 0; u < kApplyRows; ++u) {
-      float v[8];
-      unpack8(xq[u], v);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], sc[k], sh[k]);
-      if (res != nullptr) {
-        float w[8];
-        unpack8(rq[u], w);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] += w[k];
-      }
-      if (relu) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
-      }
-      if (ok[u]) store8(y + ru[u] * ldy + cv * 8, v);
+      for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
     }
+    store8(y + r * ldy + cv * 8, v);
   }
 }
 
@@ -403,56 +382,33 @@ __global__ void __launch_bounds__(256)
       if (sc < 0.f) neg_bits |= 1u << k;
     }
   }
-  constexpr int kApplyRows = 4;
-  const long long stride = static_cast<long long>(gridDim.y) * blockDim.y;
-  for (long long r0 = static_cast<long long>(blockIdx.y) * blockDim.y + threadIdx.y; r0 < rows;
-       r0 += kApplyRows * stride) {
-    long long ru[kApplyRows];
-    bool ok[kApplyRows];
-    Half8 gq[kApplyRows], xq[kApplyRows], mq[kApplyRows];
-#pragma unroll
-    for (int u = 0; u < kApplyRows; ++u) {
-      const long long q = r0 + u * stride;
-      ok[u] = q < rows;
-      ru[u] = ok[u] ? q : r0;
-      gq[u] = *reinterpret_cast<const Half8*>(dy + ru[u] * lddy + cv * 8);
-      xq[u] = *reinterpret_cast<const Half8*>(x + ru[u] * ldx + cv * 8);
-    }
+  for (long long r = static_cast<long long>(blockIdx.y) * blockDim.y + threadIdx.y; r < rows;
+       r += static_cast<long long>(gridDim.y) * blockDim.y) {
+    float g[8], v[8];
+    load8(dy + r * lddy + cv * 8, g);
+    load8(x + r * ldx + cv * 8, v);
     if (mask != nullptr) {
+      float m[8];
+      load8(mask + r * ldm + cv * 8, m);
 #pragma unroll
-      for (int u = 0; u < kApplyRows; ++u)
-        mq[u] = *reinterpret_cast<const Half8*>(mask + ru[u] * ldm + cv * 8);
+      for (int k = 0; k < 8; ++k) g[k] = m[k] > 0.f ? g[k] : 0.f;
+    } else if (relu_affine != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        g[k] = ((v[k] > thr[k]) != (((neg_bits >> k) & 1u) != 0)) ? g[k] : 0.f;
     }
+    float out[8];
 #pragma unroll
-    for (int u = 0; u < kApplyRows; ++u) {
-      if (!ok[u]) continue;
-      const long long r = ru[u];
-      float g[8], v[8];
-      unpack8(gq[u], g);
-      unpack8(xq[u], v);
-      if (mask != nullptr) {
-        float m[8];
-        unpack8(mq[u], m);
+    for (int k = 0; k < 8; ++k) out[k] = fmaf(A[k], g[k], fmaf(B[k], v[k], D[k]));
+    store8(dz + r * lddz + cv * 8, out);
+    if (dres != nullptr) {
+      if (dres_accumulate) {
+        float o[8];
+        load8(dres + r * lddr + cv * 8, o);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) g[k] = m[k] > 0.f ? g[k] : 0.f;
-      } else if (relu_affine != nullptr) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-          g[k] = ((v[k] > thr[k]) != (((neg_bits >> k) & 1u) != 0)) ? g[k] : 0.f;
+        for (int k = 0; k < 8; ++k) g[k] += o[k];
       }
-      float out[8];
-#pragma unroll
-      for (int k = 0; k < 8; ++k) out[k] = fmaf(A[k], g[k], fmaf(B[k], v[k], D[k]));
-      store8(dz + r * lddz + cv * 8, out);
-      if (dres != nullptr) {
-        if (dres_accumulate) {
-          float o[8];
-          load8(dres + r * lddr + cv * 8, o);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) g[k] += o[k];
-        }
-        store8(dres + r * lddr + cv * 8, g);
-      }
+      store8(dres + r * lddr + cv * 8, g);
     }
   }
 }
