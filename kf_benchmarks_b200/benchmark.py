@@ -621,12 +621,21 @@ class BenchmarkCNN:
         loss_sum = 0.0
         self._sync()
         start = time.time()
+        custom = getattr(self.model, "eval_step", None)
         for step in range(num_batches):
-            images, labels = src.next_batch()
-            self.executor.set_inputs(images, labels)
-            self.executor.forward(False)
-            self.executor.loss_backward(backward=False)
-            loss, t1, t5 = self.executor.read_loss()
+            try:
+                batch = src.next_batch()
+            except StopIteration:
+                break
+            if custom is not None:
+                # models whose metric is not top-k accuracy (SSD: mAP, DeepSpeech2: CER / WER)
+                # run their own forward + bookkeeping and report at the end (eval_finish)
+                loss, t1, t5 = custom(self.executor, batch, src), 0, 0
+            else:
+                self.executor.set_inputs(*batch)
+                self.executor.forward(False)
+                self.executor.loss_backward(backward=False)
+                loss, t1, t5 = self.executor.read_loss()
             top1 += t1
             top5 += t5
             loss_sum += loss
@@ -638,9 +647,17 @@ class BenchmarkCNN:
         acc1, acc5 = top1 / max(total, 1), top5 / max(total, 1)
         if self.rank == 0:
             _log("Accuracy @ 1 = %.4f Accuracy @ 5 = %.4f [%d examples]" % (acc1, acc5, total))
-        return {"top_1_accuracy": acc1, "top_5_accuracy": acc5, "num_examples": total,
-                "eval_average_loss": loss_sum / max(num_batches, 1),
-                "images_per_sec": total / max(dt, 1e-9)}
+        result = {"top_1_accuracy": acc1, "top_5_accuracy": acc5, "num_examples": total,
+                  "eval_average_loss": loss_sum / max(num_batches, 1),
+                  "images_per_sec": total / max(dt, 1e-9)}
+        finish = getattr(self.model, "eval_finish", None)
+        if finish is not None:
+            extra = finish(self.params) or {}
+            for k, v in extra.items():
+                if self.rank == 0:
+                    _log("%s = %s" % (k, v))
+            result.update(extra)
+        return result
 
     def _eval_during_training(self) -> Dict:
         from .data import inputs

@@ -71,7 +71,14 @@ def create_input_source(params, dataset, model, batch, device, nclass, seed, ran
     device = torch.device(device)
     if hasattr(model, "make_input_source"):
         # models whose inputs are not images (NCF ids, spectrograms, detection targets)
-        return model.make_input_source(batch, device, seed, rank)
+        import inspect
+        kw = {}
+        accepted = inspect.signature(model.make_input_source).parameters
+        if "world" in accepted:
+            kw["world"] = world
+        if "train" in accepted:
+            kw["train"] = train
+        return model.make_input_source(batch, device, seed, rank, **kw)
     image_size, depth = model.image_size, model.depth
     if dataset.use_synthetic_gpu_inputs():
         if device.type == "cuda":

@@ -15,9 +15,13 @@ Reference: T/models/ssd_model.py:47-552, constants T/ssd_constants.py.
   5 warm-up epochs, x0.1 at 160k and 200k steps of batch 32 (:223-256).
 
 Synthetic inputs follow :541-552 (uniform images, boxes and classes in [0,1), 1..9 matched
-boxes). COCO input pipeline, mAP evaluation (pycocotools + the object_detection package) and
---backbone_model_path loading need external packages / data that are not available offline:
-they raise a clear error.
+boxes). With ``--data_dir`` the COCO TFRecords are read, augmented and labelled by
+``data/ssd_dataloader.py`` (NumPy restatement of T/ssd_dataloader.py and of the pieces of the
+external object_detection package it uses); ``--eval`` decodes the heads, runs per-class NMS and
+computes COCO AP/AR with ``coco_metric.py`` (NumPy restatement of the COCOeval protocol -
+pycocotools is not available offline). ``--backbone_model_path`` expects a TF checkpoint of the
+official ResNet-34 and is not supported (no TF checkpoint reader); checkpoints of this framework
+restore through ``--train_dir`` as for every model.
 """
 import torch
 
@@ -145,14 +149,52 @@ class SSD300Model(model.CNNModel):
         sched = model.LRSchedule([lr0, lr0 * 0.1, lr0 * 0.01], boundaries)
         return sched(global_step)
 
-    def make_input_source(self, batch, device, seed, rank=0, host=False):
+    def make_input_source(self, batch, device, seed, rank=0, host=False, world=1, train=True):
         if self.params is not None and self.params.data_dir:
-            raise NotImplementedError(
-                "the COCO input pipeline needs the object_detection package and the COCO "
-                "TFRecords (T/ssd_dataloader.py); only synthetic inputs are available offline")
+            from ..data.ssd_dataloader import CocoInputSource
+            return CocoInputSource(self.params.data_dir, batch, device, seed, rank, world, train)
         return _SsdSyntheticSource(batch, self.image_size, device, seed * 1000003 + rank,
                                    host=host)
 
+    # -- evaluation: decode the heads, collect detections, COCO mAP at the end -------------
+    def predict(self, executor):
+        """(boxes [N, 8732, 4] decoded + normalised, scores [N, 8732, 81]) of the last forward
+        pass (T/models/ssd_model.py:455-479)."""
+        from ..data import ssd_dataloader as sd
+        from ..nn.losses_ref import ssd_gather
+        g = executor.graph
+        vals = {tid: executor.value(tid) for tid in list(g.loss["loc"]) + list(g.loss["conf"])}
+        loc, conf = ssd_gather(g, vals)
+        scores = torch.softmax(conf.float(), dim=2).cpu().numpy()
+        boxes = sd.decode_boxes(loc.float().cpu().numpy(), sd.default_boxes()("ltrb"))
+        return boxes, scores
+
+    def eval_step(self, executor, batch, src):
+        executor.set_primary_input(batch[0])
+        executor.forward(False)
+        boxes, scores = self.predict(executor)
+        meta = getattr(src, "last_eval_meta", None) or [(i, (300, 300, 3))
+                                                        for i in range(len(boxes))]
+        if not hasattr(self, "predictions"):
+            self.predictions = {}
+        for i, (sid, raw) in enumerate(meta):
+            self.predictions[int(sid)] = {"pred_boxes": boxes[i], "pred_scores": scores[i],
+                                          "source_id": int(sid), "raw_shape": raw}
+        return 0.0
+
+    def eval_finish(self, params):
+        """COCO mAP over everything collected (T/models/ssd_model.py:481-539)."""
+        import os
+        from .. import coco_metric
+        preds = list(getattr(self, "predictions", {}).values())
+        self.predictions = {}
+        ann = os.path.join(params.data_dir or "", "annotations", "instances_val2017.json")
+        if not preds or not os.path.exists(ann):
+            return {"top_1_accuracy": 0.0, "top_5_accuracy": 0.0,
+                    "detections_collected": len(preds)}
+        out = coco_metric.compute_map(preds, ann)
+        out.update({"top_1_accuracy": 0.0, "top_5_accuracy": 0.0})
+        return out
+
     def postprocess(self, results):
-        raise NotImplementedError("COCO mAP evaluation needs pycocotools and the COCO "
-                                  "annotations (T/models/ssd_model.py:481-539)")
+        return results

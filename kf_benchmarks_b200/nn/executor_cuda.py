@@ -75,6 +75,7 @@ class CudaExecutor:
         # ---- buffers ------------------------------------------------------------
         self.buf: Dict[int, _Buf] = {}
         self.gbuf: Dict[int, _Buf] = {}
+        self._tmp: Dict[tuple, _Buf] = {}
         self._alias: Dict[int, int] = {}
         # per-step inputs: primary input, extra inputs, labels (in the input source's order);
         # host batches are prefetched into a second set on a copy stream (double buffering)
@@ -342,6 +343,12 @@ class CudaExecutor:
             return
         for t, m in zip(tensors, mine):
             m.copy_(t, non_blocking=True)
+        self._bind_inputs(mine)
+
+    def set_primary_input(self, images: torch.Tensor) -> None:
+        """Only the primary input changes (evaluation of models whose labels are not fed)."""
+        mine = self._in_sets[self._cur]
+        mine[0].copy_(images, non_blocking=True)
         self._bind_inputs(mine)
 
     def stage_inputs(self, *tensors: torch.Tensor) -> None:
@@ -818,10 +825,9 @@ class CudaExecutor:
             native.call("copy2d", gz.p, i64(gz.ld), gdst.p, i64(gdst.ld), i64(gz.rows),
                         i32(gz.cols), i32(1), s)
 
-    _tmp: Dict[tuple, _Buf] = {}
-
     def _tmp_like(self, b: _Buf) -> _Buf:
-        key = (self.device.index, b.rows, b.ld)
+        """Scratch activation-gradient buffer (one per distinct shape, owned by this executor)."""
+        key = (b.rows, b.ld)
         if key not in self._tmp:
             self._tmp[key] = _Buf(torch.zeros((b.rows, b.ld), dtype=torch.float16,
                                               device=self.device), b.rows, b.cols, b.ld)

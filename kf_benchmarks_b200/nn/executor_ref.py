@@ -65,6 +65,10 @@ class RefExecutor:
         self.label_tensors = [conv(t, spec[1]) for t, spec in zip(labs, g.label_specs)]
         self.labels = self.label_tensors[0]
 
+    def set_primary_input(self, images: torch.Tensor) -> None:
+        self.images = images.to(self.device, self.dtype if self.graph.input.dtype != "i32"
+                                else torch.long)
+
     def _param(self, spec, train: bool) -> torch.Tensor:
         """Leaf tensor in the *TF* layout so gradients map back trivially."""
         v = self.store.view(spec.name).detach().to(self.dtype)
