@@ -95,42 +95,76 @@ def _fields(buf: bytes):
         yield field, wire, val
 
 
+def _parse_feature(feature: bytes) -> list:
+    """tf.train.Feature -> python list (bytes / floats / ints)."""
+    values: list = []
+    for kind, _, payload in _fields(feature):
+        if kind == 1:      # BytesList
+            values = [v for f, _, v in _fields(payload) if f == 1]
+        elif kind == 2:    # FloatList (packed or not)
+            for f, w, v in _fields(payload):
+                if f == 1 and w == 2:
+                    values.extend(struct.unpack("<%df" % (len(v) // 4), v))
+                elif f == 1:
+                    values.append(struct.unpack("<f", v)[0])
+        elif kind == 3:    # Int64List
+            for f, w, v in _fields(payload):
+                if f == 1 and w == 2:
+                    p = 0
+                    while p < len(v):
+                        x, p = _varint(v, p)
+                        values.append(x - (1 << 64) if x >> 63 else x)
+                elif f == 1:
+                    values.append(v - (1 << 64) if v >> 63 else v)
+    return values
+
+
+def _parse_features(features: bytes) -> Dict[str, list]:
+    """tf.train.Features (map<string, Feature>) -> dict."""
+    out: Dict[str, list] = {}
+    for f2, _, entry in _fields(features):
+        if f2 != 1:
+            continue
+        key, feature = None, b""
+        for f3, _, v in _fields(entry):
+            if f3 == 1:
+                key = v.decode("utf-8")
+            elif f3 == 2:
+                feature = v
+        if key is not None:
+            out[key] = _parse_feature(feature)
+    return out
+
+
 def parse_example(data: bytes) -> Dict[str, list]:
     out: Dict[str, list] = {}
     for f1, _, features in _fields(data):
-        if f1 != 1:
-            continue
-        for f2, _, entry in _fields(features):
-            if f2 != 1:
-                continue
-            key, feature = None, b""
-            for f3, _, v in _fields(entry):
-                if f3 == 1:
-                    key = v.decode("utf-8")
-                elif f3 == 2:
-                    feature = v
-            values: list = []
-            for kind, _, payload in _fields(feature):
-                if kind == 1:      # BytesList
-                    values = [v for f, _, v in _fields(payload) if f == 1]
-                elif kind == 2:    # FloatList (packed or not)
-                    for f, w, v in _fields(payload):
-                        if f == 1 and w == 2:
-                            values.extend(struct.unpack("<%df" % (len(v) // 4), v))
-                        elif f == 1:
-                            values.append(struct.unpack("<f", v)[0])
-                elif kind == 3:    # Int64List
-                    for f, w, v in _fields(payload):
-                        if f == 1 and w == 2:
-                            p = 0
-                            while p < len(v):
-                                x, p = _varint(v, p)
-                                values.append(x - (1 << 64) if x >> 63 else x)
-                        elif f == 1:
-                            values.append(v - (1 << 64) if v >> 63 else v)
-            if key is not None:
-                out[key] = values
+        if f1 == 1:
+            out.update(_parse_features(features))
     return out
+
+
+def parse_sequence_example(data: bytes):
+    """tf.train.SequenceExample -> (context dict, {name: [list per step]}): the record format
+    of the preprocessed LibriSpeech set (T/preprocessing.py:1079-1112)."""
+    context: Dict[str, list] = {}
+    lists: Dict[str, list] = {}
+    for f1, _, payload in _fields(data):
+        if f1 == 1:
+            context.update(_parse_features(payload))
+        elif f1 == 2:
+            for f2, _, entry in _fields(payload):       # map<string, FeatureList>
+                if f2 != 1:
+                    continue
+                key, flist = None, b""
+                for f3, _, v in _fields(entry):
+                    if f3 == 1:
+                        key = v.decode("utf-8")
+                    elif f3 == 2:
+                        flist = v
+                if key is not None:
+                    lists[key] = [_parse_feature(v) for f, _, v in _fields(flist) if f == 1]
+    return context, lists
 
 
 # ---- encoder (tests / tools) --------------------------------------------------------------
@@ -149,14 +183,28 @@ def _ld(field: int, payload: bytes) -> bytes:
     return _enc_varint((field << 3) | 2) + _enc_varint(len(payload)) + payload
 
 
-def encode_example(features: Dict[str, list]) -> bytes:
+def _enc_feature(values: list) -> bytes:
+    if values and isinstance(values[0], (bytes, bytearray)):
+        return _ld(1, b"".join(_ld(1, bytes(v)) for v in values))
+    if values and isinstance(values[0], float):
+        return _ld(2, _ld(1, struct.pack("<%df" % len(values), *values)))
+    return _ld(3, _ld(1, b"".join(_enc_varint(int(v)) for v in values)))
+
+
+def _enc_features(features: Dict[str, list]) -> bytes:
     entries = b""
     for key, values in features.items():
-        if values and isinstance(values[0], (bytes, bytearray)):
-            feat = _ld(1, b"".join(_ld(1, bytes(v)) for v in values))
-        elif values and isinstance(values[0], float):
-            feat = _ld(2, _ld(1, struct.pack("<%df" % len(values), *values)))
-        else:
-            feat = _ld(3, _ld(1, b"".join(_enc_varint(int(v)) for v in values)))
-        entries += _ld(1, _ld(1, key.encode("utf-8")) + _ld(2, feat))
-    return _ld(1, entries)
+        entries += _ld(1, _ld(1, key.encode("utf-8")) + _ld(2, _enc_feature(values)))
+    return entries
+
+
+def encode_example(features: Dict[str, list]) -> bytes:
+    return _ld(1, _enc_features(features))
+
+
+def encode_sequence_example(context: Dict[str, list], feature_lists: Dict[str, list]) -> bytes:
+    lists = b""
+    for key, steps in feature_lists.items():
+        flist = b"".join(_ld(1, _enc_feature(list(step))) for step in steps)
+        lists += _ld(1, _ld(1, key.encode("utf-8")) + _ld(2, flist))
+    return _ld(1, _enc_features(context)) + _ld(2, lists)

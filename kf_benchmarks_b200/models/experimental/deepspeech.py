@@ -83,6 +83,70 @@ class _SpeechSyntheticSource:
         return tuple(self.tensors)
 
 
+class LibrispeechInputSource:
+    """Preprocessed LibriSpeech TFRecords (T/preprocessing.py:977-1112): SequenceExamples with
+    per-frame 161-bin spectrogram ``features`` and ``labels`` / ``input_length`` /
+    ``label_length`` in the context; batches are zero-padded to the model's static shapes
+    (``train-clean-*.tfrecords`` / ``test-clean.tfrecords``, T/datasets.py:93-99)."""
+    host_resident = True
+
+    def __init__(self, data_dir, batch, t, f, lmax, device, seed, rank=0, world=1, train=True):
+        import glob
+        import os
+        from ...data import tfrecord
+        pat = "train-clean-*.tfrecords" if train else "test-clean.tfrecords"
+        files = sorted(glob.glob(os.path.join(data_dir, pat)))
+        if not files:
+            raise FileNotFoundError("Found no files in --data_dir matching: %s" %
+                                    os.path.join(data_dir, pat))
+        self.files = files[rank::world] or files
+        self.batch, self.t, self.f, self.lmax, self.train = batch, t, f, lmax, train
+        self.rng = np.random.RandomState(seed * 7919 + rank)
+        self._tf = tfrecord
+        self._it = self._records()
+        self.pin = torch.device(device).type == "cuda"
+        self.bytes_per_step = batch * (t * f * 2 + lmax * 4 + 8)
+
+    def _records(self):
+        while True:
+            order = list(self.files)
+            if self.train:
+                self.rng.shuffle(order)
+            for path in order:
+                for rec in self._tf.read_records(path):
+                    yield rec
+            if not self.train:
+                return
+
+    def next_batch(self):
+        x = np.zeros((self.batch, self.t, self.f, 1), np.float32)
+        lab = np.zeros((self.batch, self.lmax), np.int32)
+        ilen = np.zeros((self.batch, 1), np.int32)
+        llen = np.zeros((self.batch, 1), np.int32)
+        n = 0
+        while n < self.batch:
+            try:
+                rec = next(self._it)
+            except StopIteration:
+                if n == 0:
+                    raise
+                break
+            ctx, lists = self._tf.parse_sequence_example(rec)
+            feats = np.asarray(lists.get("features", []), np.float32).reshape(-1, self.f)
+            steps = min(len(feats), self.t)
+            x[n, :steps, :, 0] = feats[:steps]
+            labels = np.asarray(ctx.get("labels", []), np.int32)[:self.lmax]
+            lab[n, :len(labels)] = labels
+            ilen[n, 0] = min(int(ctx.get("input_length", [steps])[0]), self.t)
+            llen[n, 0] = min(int(ctx.get("label_length", [len(labels)])[0]), self.lmax)
+            n += 1
+        out = [torch.from_numpy(x).half(), torch.from_numpy(lab), torch.from_numpy(ilen),
+               torch.from_numpy(llen)]
+        if self.pin:
+            out = [v.pin_memory() for v in out]
+        return tuple(out)
+
+
 class DeepSpeech2Model(model.Model):
     BATCH_NORM_EPSILON = 1e-5
     BATCH_NORM_DECAY = 0.997
@@ -144,14 +208,36 @@ class DeepSpeech2Model(model.Model):
         g.loss = {"kind": "ctc", "max_time_steps": self.max_time_steps, "eps": 1e-7}
         return g
 
-    def make_input_source(self, batch, device, seed, rank=0, host=False):
+    def make_input_source(self, batch, device, seed, rank=0, host=False, world=1, train=True):
         if self.params is not None and self.params.data_dir:
-            raise NotImplementedError(
-                "the LibriSpeech input pipeline (T/preprocessing.py LibrispeechPreprocessor) "
-                "needs the preprocessed TFRecords; only synthetic inputs are available offline")
+            return LibrispeechInputSource(self.params.data_dir, batch, self.max_time_steps,
+                                          self.num_feature_bins, self.max_label_length, device,
+                                          seed, rank, world, train)
         return _SpeechSyntheticSource(batch, self.max_time_steps, self.num_feature_bins,
                                       self.max_label_length, device, seed * 1000003 + rank,
                                       host=host)
+
+    # -- evaluation: CTC loss + greedy decoding, CER / WER at the end ------------------------
+    def eval_step(self, executor, batch, src):
+        executor.set_inputs(*batch)
+        executor.forward(False)
+        executor.loss_backward(backward=False)
+        loss = executor.read_loss()[0]
+        probs = torch.softmax(executor.logits().float(), dim=-1).cpu().numpy()
+        labels, _, lab_len = (t.cpu().numpy() for t in batch[1:])
+        if not hasattr(self, "_eval_items"):
+            self._eval_items = {"probs": [], "labels": []}
+        for i in range(probs.shape[0]):
+            self._eval_items["probs"].append(probs[i])
+            self._eval_items["labels"].append(labels[i][:int(lab_len[i, 0])])
+        return loss
+
+    def eval_finish(self, params):
+        items = getattr(self, "_eval_items", None)
+        self._eval_items = {"probs": [], "labels": []}
+        if not items or not items["probs"]:
+            return {}
+        return self.postprocess(items)
 
     def postprocess(self, results):
         """results: {'probs': [N, T, 29], 'labels': [N, L]} -> logs CER / WER

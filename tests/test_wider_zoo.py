@@ -187,3 +187,39 @@ def test_ctc_reference_ignores_infeasible_samples():
     only0 = ctc_loss(z[:1], labels[:1], torch.tensor([6]), torch.tensor([4]))
     assert float(loss) == pytest.approx(float(only0) / 2, rel=1e-5)
     assert ctc_input_lengths(torch.tensor([[3494], [1747]]), 874, 3494).tolist() == [874, 437]
+
+
+def test_librispeech_tfrecords_and_eval_hooks(tmp_path):
+    from kf_benchmarks_b200 import params as P
+    from kf_benchmarks_b200.data import tfrecord
+    rng = np.random.RandomState(0)
+    recs = []
+    for n_frames, labels in ((30, [8, 9]), (48, [1, 2, 3, 4]), (20, [5])):
+        feats = rng.rand(n_frames, 21).astype(np.float32)
+        recs.append(tfrecord.encode_sequence_example(
+            {"labels": labels, "input_length": [n_frames], "label_length": [len(labels)]},
+            {"features": [[float(v) for v in row] for row in feats]}))
+        ctx, lists = tfrecord.parse_sequence_example(recs[-1])
+        assert ctx["labels"] == labels and ctx["input_length"] == [n_frames]
+        assert np.allclose(np.asarray(lists["features"], np.float32), feats)
+    tfrecord.write_records(str(tmp_path / "train-clean-100.tfrecords"), recs)
+    tfrecord.write_records(str(tmp_path / "test-clean.tfrecords"), recs[:2])
+    ds = datasets.create_dataset(str(tmp_path), "librispeech")
+    p = P.make_params(model="deepspeech2", data_name="librispeech", data_dir=str(tmp_path),
+                      device="cpu", data_format="NHWC")
+    m = model_config.get_model_config("deepspeech2", ds, p)
+    m.max_time_steps, m.num_feature_bins, m.max_label_length = 48, 21, 4
+    m.rnn_hidden_size, m.num_rnn_layers = 16, 1
+    src = m.make_input_source(2, "cpu", seed=1, train=False)
+    x, lab, ilen, llen = src.next_batch()
+    assert x.shape == (2, 48, 21, 1) and lab.shape == (2, 4)
+    assert ilen.view(-1).tolist() == [30, 48] and llen.view(-1).tolist() == [2, 4]
+    assert float(x[0, 30:].abs().sum()) == 0.0          # zero padding past the utterance
+    g = m.build_graph(29, phase_train=False, batch_size=2)
+    st = ParameterStore(g, "cpu", fp16_shadow=False)
+    st.initialize(1)
+    ex = RefExecutor(g, st, 29)
+    loss = m.eval_step(ex, (x, lab, ilen, llen), src)
+    assert loss > 0
+    out = m.eval_finish(p)
+    assert "cer" in out and "wer" in out and out["cer"] >= 0
