@@ -321,6 +321,7 @@ class BenchmarkCNN:
             self.engine.register_rs_params(self.executor.rs_capable_params())
             self.executor.push_lookup = self.engine.push_target
         self.input_source = self._make_input_source(phase_train)
+        self._dump_graph_files()
 
     def _make_input_source(self, train: bool):
         from .data import inputs
@@ -359,6 +360,48 @@ class BenchmarkCNN:
         self.global_step = int(arrays.get("global_step", step))
         if self.rank == 0:
             _log("Restored checkpoint %s (global_step %d)" % (path, self.global_step))
+
+    def _maybe_load_backbone(self) -> None:
+        """--backbone_model_path (T/benchmark_cnn.py:2204-2205, T/models/ssd_model.py:256-297):
+        initialise the backbone variables from a checkpoint before training starts."""
+        p = self.params
+        if not p.backbone_model_path or self.global_step > 0:
+            return
+        loader = getattr(self.model, "load_backbone_model", None)
+        if loader is None:
+            raise ValueError("--backbone_model_path: model %s has no backbone to load" % p.model)
+        n = loader(self.store, p.backbone_model_path)
+        if self.rank == 0:
+            _log("Loaded %d backbone variables from %s" % (n, p.backbone_model_path))
+
+    def _dump_graph_files(self) -> None:
+        """--graph_file / --partitioned_graph_file_prefix (T/benchmark_cnn.py:2142-2148,
+        869-883): the layer graph as text (or JSON for a .json name), and per rank the graph
+        the executor actually runs (after channel legalisation) with the bucket plan."""
+        p = self.params
+        import json as _json
+
+        def dump(graph, path, extra=None):
+            if path.endswith(".json"):
+                doc = {"nodes": [{"op": n.op, "name": n.name, "inputs": [t.id for t in n.inputs],
+                                  "output": n.output.id, "shape": list(n.output.shape),
+                                  "params": {k: v.name for k, v in n.params.items()}}
+                                 for n in graph.nodes],
+                       "variables": {v.name: list(v.tf_shape) for v in graph.params.values()}}
+                doc.update(extra or {})
+                with open(path, "w") as f:
+                    _json.dump(doc, f, indent=1)
+            else:
+                with open(path, "w") as f:
+                    f.write(graph.describe() + "\n")
+                    for k, v in (extra or {}).items():
+                        f.write("%s: %s\n" % (k, v))
+        if p.graph_file and self.rank == 0:
+            dump(getattr(self.graph, "logical", self.graph), p.graph_file)
+        if p.partitioned_graph_file_prefix:
+            ext = ".json" if (p.graph_file or "").endswith(".json") else ".txt"
+            dump(self.graph, "%s%d%s" % (p.partitioned_graph_file_prefix, self.rank, ext),
+                 {"rank": self.rank, "buckets": [list(b) for b in self.engine.buckets]})
 
     def _save(self) -> None:
         p = self.params
@@ -468,6 +511,7 @@ class BenchmarkCNN:
         forward_only = bool(p.forward_only)
         self._build(phase_train=not forward_only)
         self._maybe_restore()
+        self._maybe_load_backbone()
         self.engine.broadcast_initial_variables()
         rank0 = self.rank == 0
         cuda = self.device.type == "cuda"

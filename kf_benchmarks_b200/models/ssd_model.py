@@ -19,9 +19,9 @@ boxes). With ``--data_dir`` the COCO TFRecords are read, augmented and labelled 
 ``data/ssd_dataloader.py`` (NumPy restatement of T/ssd_dataloader.py and of the pieces of the
 external object_detection package it uses); ``--eval`` decodes the heads, runs per-class NMS and
 computes COCO AP/AR with ``coco_metric.py`` (NumPy restatement of the COCOeval protocol -
-pycocotools is not available offline). ``--backbone_model_path`` expects a TF checkpoint of the
-official ResNet-34 and is not supported (no TF checkpoint reader); checkpoints of this framework
-restore through ``--train_dir`` as for every model.
+pycocotools is not available offline). ``--backbone_model_path`` loads the ResNet-34 backbone
+from a checkpoint of this framework or from an npz keyed like the TF official ResNet (there is
+no reader for TF's binary checkpoint format: convert with ``np.savez`` first).
 """
 import torch
 
@@ -155,6 +155,43 @@ class SSD300Model(model.CNNModel):
             return CocoInputSource(self.params.data_dir, batch, device, seed, rank, world, train)
         return _SsdSyntheticSource(batch, self.image_size, device, seed * 1000003 + rank,
                                    host=host)
+
+    def load_backbone_model(self, store, path) -> int:
+        """Initialises the ResNet-34 backbone from a checkpoint (T/models/ssd_model.py:256-297,
+        386-394). Accepted layouts: a checkpoint of this framework (variables named
+        ``v0/cg/resnet34_backbone/...``) or an npz keyed like the TF official ResNet the
+        reference expects (``conv2d[_N]/kernel``, ``batch_normalization[_N]/gamma`` ...), matched
+        by layer index exactly as ``_var_name_in_official_model_ckpt`` does. Returns the number
+        of variables loaded."""
+        import re
+        from .. import ckpt as ckpt_lib
+        arrays = ckpt_lib.load_arrays(path)
+        wanted = {}
+        for name in store.graph.params:
+            if "resnet34_backbone" not in name:
+                continue
+            key = "v0/" + name
+            if key in arrays:
+                wanted[key] = arrays[key]
+                continue
+            m = re.search(r"conv(\d+)/conv2d/(.+)$", name)
+            official = None
+            if m:
+                official = "conv2d" + ("_%s" % m.group(1) if int(m.group(1)) else "") + "/" + \
+                    m.group(2)
+            else:
+                m = re.search(r"batchnorm(\d+)/(.+)$", name)
+                if m:
+                    official = "batch_normalization" + \
+                        ("_%s" % m.group(1) if int(m.group(1)) else "") + "/" + m.group(2)
+            for cand in (official, "resnet_model/%s" % official if official else None):
+                if cand and cand in arrays:
+                    wanted[key] = arrays[cand]
+                    break
+        if not wanted:
+            raise ValueError("no backbone variables found in %s" % path)
+        store.from_tf_arrays(wanted, strict=False)
+        return len(wanted)
 
     # -- evaluation: decode the heads, collect detections, COCO mAP at the end -------------
     def predict(self, executor):

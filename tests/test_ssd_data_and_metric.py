@@ -216,3 +216,54 @@ def test_ssd_eval_hooks_on_the_cpu_executor(tmp_path):
     assert np.allclose(scores.sum(-1), 1.0, atol=1e-4)
     out = m.eval_finish(p)
     assert "COCO/AP" in out and 0.0 <= out["COCO/AP"] <= 1.0 and m.predictions == {}
+
+
+def test_backbone_loading_and_graph_dumps(tmp_path):
+    import torch
+    from kf_benchmarks_b200 import benchmark, ckpt as ckpt_lib, datasets, params as P
+    from kf_benchmarks_b200.models import model_config
+    from kf_benchmarks_b200.nn.params import ParameterStore
+    ds = datasets.create_dataset(None, "coco")
+    m = model_config.get_model_config("ssd300", ds, None)
+    g = m.build_graph(81, batch_size=1)
+    src_store = ParameterStore(g, "cpu", fp16_shadow=False)
+    src_store.initialize(11)
+    arrays = src_store.to_tf_arrays()
+    # (a) a checkpoint of this framework
+    np.savez(str(tmp_path / "model.ckpt-5.npz"), **arrays)
+    dst = ParameterStore(g, "cpu", fp16_shadow=False)
+    dst.initialize(99)
+    n = m.load_backbone_model(dst, str(tmp_path / "model.ckpt-5"))
+    bb = [k for k in g.params if "resnet34_backbone" in k]
+    assert n == len(bb) and n > 100
+    for k in bb:
+        assert torch.equal(dst.view(k), src_store.view(k))
+    head = [k for k in g.params if "resnet34_backbone" not in k][0]
+    assert not torch.equal(dst.view(head), src_store.view(head))       # heads keep their init
+    # (b) an npz with the TF official-ResNet names (conv2d, conv2d_1, batch_normalization_3/gamma)
+    official = {}
+    import re
+    for k in bb:
+        mm = re.search(r"conv(\d+)/conv2d/(.+)$", k)
+        if mm:
+            official["conv2d" + ("_" + mm.group(1) if int(mm.group(1)) else "") + "/" +
+                     mm.group(2)] = arrays["v0/" + k]
+            continue
+        mm = re.search(r"batchnorm(\d+)/(.+)$", k)
+        official["batch_normalization" + ("_" + mm.group(1) if int(mm.group(1)) else "") + "/" +
+                 mm.group(2)] = arrays["v0/" + k]
+    np.savez(str(tmp_path / "official.npz"), **official)
+    dst2 = ParameterStore(g, "cpu", fp16_shadow=False)
+    dst2.initialize(5)
+    assert m.load_backbone_model(dst2, str(tmp_path / "official")) == len(bb)
+    assert torch.equal(dst2.view(bb[0]), src_store.view(bb[0]))
+    # graph dumps
+    p = P.make_params(model="trivial", device="cpu", data_format="NHWC", batch_size=2,
+                      num_batches=1, num_warmup_batches=0, graph_file=str(tmp_path / "g.json"),
+                      partitioned_graph_file_prefix=str(tmp_path / "part_"))
+    benchmark.BenchmarkCNN(benchmark.setup(p)).run()
+    doc = json.loads((tmp_path / "g.json").read_text())
+    assert [n["op"] for n in doc["nodes"]][:2] == ["reshape", "affine"]
+    assert "cg/affine0/weights" in doc["variables"]
+    part = json.loads((tmp_path / "part_0.json").read_text())
+    assert part["rank"] == 0 and part["buckets"]
