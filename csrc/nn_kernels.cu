@@ -722,6 +722,31 @@ __global__ void __launch_bounds__(256)
     const long long row = (static_cast<long long>(nn) * p + pp) * q + qq;
     const int h0 = pp * sh - pad_h, w0 = qq * sw - pad_w;
     const __half* xin = x + static_cast<long long>(nn) * h * w * c;
+    if (kw * c >= 8 && h0 >= 0 && h0 + kh <= h && w0 >= 0 && w0 + kw <= w) {
+      // Interior window (~95 % of a 7x7/2 stem): a patch row (kw * c halves) is contiguous in
+      // the NHWC input, so the 8 outputs of this thread are 8 consecutive halves of at most two
+      // patch rows - raw 16-bit copies, no bounds checks, no conversions.
+      const unsigned short* src = reinterpret_cast<const unsigned short*>(xin);
+      const int rowlen = kw * c;
+      const int k0 = kv * 8;
+      const int r0 = k0 / rowlen;
+      const int o0 = k0 - r0 * rowlen;
+      const int base0 = ((h0 + r0) * w + w0) * c + o0;
+      const int base1 = base0 + w * c - rowlen;       // same offset in the next patch row
+      unsigned short e[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int addr = (o0 + j < rowlen) ? base0 + j : base1 + j;
+        e[j] = (k0 + j < ktot) ? __ldg(src + addr) : static_cast<unsigned short>(0);
+      }
+      uint4 packed;
+      packed.x = e[0] | (static_cast<unsigned>(e[1]) << 16);
+      packed.y = e[2] | (static_cast<unsigned>(e[3]) << 16);
+      packed.z = e[4] | (static_cast<unsigned>(e[5]) << 16);
+      packed.w = e[6] | (static_cast<unsigned>(e[7]) << 16);
+      *reinterpret_cast<uint4*>(col + row * kpad + kv * 8) = packed;
+      continue;
+    }
     float v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
