@@ -29,8 +29,11 @@ def get_command_to_run_python_module(module):
 
 
 def get_cluster_manager(params, config_proto=None):
-    raise ValueError("TF-cluster roles (ps / worker / controller) are not supported: the "
-                     "B200 build is one process per GPU on one NVSwitch box")
+    """T/platforms/default/util.py:52-66. Returns a description of the cluster; workers are
+    ranks of the process group (benchmark._apply_cluster_role)."""
+    del config_proto
+    from ..utils.cnn_util import GrpcClusterManager
+    return GrpcClusterManager(params)
 
 
 def initialize(params, config_proto=None):

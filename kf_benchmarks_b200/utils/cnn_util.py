@@ -102,3 +102,37 @@ class ImageProducer:
             self._cond.notify_all()
         if self._thread is not None:
             self._thread.join(timeout=5)
+
+
+class BaseClusterManager:
+    """Cluster description derived from ``--worker_hosts`` / ``--ps_hosts`` / ``--job_name`` /
+    ``--task_index`` (T/cnn_util.py:201-251). On this runtime a worker is a rank of the
+    process group and parameter servers have no process of their own, so the manager is a
+    plain description: who the workers are, where the rendezvous is, what this process is."""
+
+    def __init__(self, params):
+        self.worker_hosts = [h for h in (params.worker_hosts or "").split(",") if h]
+        self.ps_hosts = [h for h in (params.ps_hosts or "").split(",") if h]
+        self.job_name = params.job_name or ""
+        self.task_index = int(params.task_index or 0)
+
+    def get_target(self):
+        """Rendezvous address (first worker), the counterpart of the TF session target."""
+        return self.worker_hosts[0] if self.worker_hosts else ""
+
+    def join_server(self):
+        """A TF parameter server blocks here forever; there is nothing to serve."""
+        return None
+
+    def get_cluster_spec(self):
+        return {"worker": list(self.worker_hosts), "ps": list(self.ps_hosts)}
+
+    def num_workers(self):
+        return len(self.worker_hosts)
+
+    def num_ps(self):
+        return len(self.ps_hosts)
+
+
+class GrpcClusterManager(BaseClusterManager):
+    """Name kept for code written against the reference; no gRPC server is started."""

@@ -115,3 +115,28 @@ def test_export_tool_lists_reference_names(tmp_path):
     assert res.returncode == 0
     assert "v0/cg/affine0/weights" in res.stdout and "v0/cg/affine0/weights/Momentum" in res.stdout
     assert "global_step" in res.stdout
+
+
+def test_platform_hooks_and_cluster_manager():
+    from kf_benchmarks_b200 import params as P
+    from kf_benchmarks_b200.platforms import util as platforms_util
+    assert os.path.isdir(platforms_util.get_test_output_dir())
+    cmd = platforms_util.get_command_to_run_python_module("cli")
+    assert cmd[-1] == "kf_benchmarks_b200.cli"
+    p = P.make_params(job_name="worker", task_index=1, worker_hosts="a:1,b:2", ps_hosts="c:3")
+    cm = platforms_util.get_cluster_manager(p)
+    assert cm.num_workers() == 2 and cm.num_ps() == 1 and cm.get_target() == "a:1"
+    assert cm.get_cluster_spec() == {"worker": ["a:1", "b:2"], "ps": ["c:3"]}
+    assert cm.join_server() is None
+    platforms_util.initialize(p)
+
+
+def test_keras_style_epoch_benchmark_runs():
+    import json
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "keras_benchmarks",
+                                                       "run_benchmark.py"), "--model", "mnist_mlp",
+                          "--device", "cpu", "--epochs", "2", "--num_samples", "256"],
+                         capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    d = json.loads(res.stdout.strip().splitlines()[-1])
+    assert d["test_name"] == "mnist_mlp" and d["epochs"] == 2 and d["total_time"] > 0
