@@ -585,6 +585,51 @@ __global__ void __launch_bounds__(256)
     if (ww + g.pad_w - g.kw + 1 <= 0) q_lo = 0;
     int q_hi = (ww + g.pad_w) / g.sw;
     if (q_hi >= g.q) q_hi = g.q - 1;
+    __half* o = dx + ((static_cast<long long>(n) * g.h + hh) * g.w + ww) * lddx + cv * 8;
+    if (is_max) {
+      // Max pooling: the kernel is issue-bound, so stay in packed form. The 8 arg-max bytes
+      // of a window are compared with the tap this pixel is in it by a SWAR "byte == 0" test,
+      // widened to 16-bit lane masks with PRMT, ANDed onto the raw half2 gradient words and
+      // summed with HADD2 (at most kh*kw/(sh*sw) terms, almost always 0 or 1 non-zero).
+      __half2 hacc[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) hacc[k] = __floats2half2_rn(0.f, 0.f);
+      for (int p = p_lo; p <= p_hi; ++p) {
+        const int r = hh - (p * g.sh - g.pad_h);
+        if (r < 0 || r >= g.kh) continue;
+        for (int q = q_lo; q <= q_hi; ++q) {
+          const int s = ww - (q * g.sw - g.pad_w);
+          if (s < 0 || s >= g.kw) continue;
+          const long long orow = (static_cast<long long>(n) * g.p + p) * g.q + q;
+          const uint4 dv = *reinterpret_cast<const uint4*>(dy + orow * lddy + cv * 8);
+          const uint2 am = *reinterpret_cast<const uint2*>(argmax + orow * g.c + cv * 8);
+          const unsigned tapv = static_cast<unsigned>(r * g.kw + s) * 0x01010101u;
+          const unsigned e0 = am.x ^ tapv, e1 = am.y ^ tapv;
+          // 0x80 in every byte of e that is zero, then 0xFF
+          const unsigned z0 = ~(((e0 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | e0 | 0x7F7F7F7Fu);
+          const unsigned z1 = ~(((e1 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | e1 | 0x7F7F7F7Fu);
+          const unsigned b0 = (z0 >> 7) * 0xFFu, b1 = (z1 >> 7) * 0xFFu;
+          unsigned w[4];
+          w[0] = dv.x & __byte_perm(b0, 0, 0x1100);
+          w[1] = dv.y & __byte_perm(b0, 0, 0x3322);
+          w[2] = dv.z & __byte_perm(b1, 0, 0x1100);
+          w[3] = dv.w & __byte_perm(b1, 0, 0x3322);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            hacc[k] = __hadd2(hacc[k], *reinterpret_cast<const __half2*>(&w[k]));
+        }
+      }
+      if (accumulate) {
+        const Half8 old = *reinterpret_cast<const Half8*>(o);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) hacc[k] = __hadd2(hacc[k], old.h[k]);
+      }
+      Half8 outv;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) outv.h[k] = hacc[k];
+      *reinterpret_cast<Half8*>(o) = outv;
+      continue;
+    }
     for (int p = p_lo; p <= p_hi; ++p) {
       const int r = hh - (p * g.sh - g.pad_h);
       if (r < 0 || r >= g.kh) continue;
@@ -613,7 +658,6 @@ __global__ void __launch_bounds__(256)
         }
       }
     }
-    __half* o = dx + ((static_cast<long long>(n) * g.h + hh) * g.w + ww) * lddx + cv * 8;
     if (accumulate) {
       float old[8];
       load8(o, old);
