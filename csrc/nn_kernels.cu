@@ -500,12 +500,13 @@ __global__ void __launch_bounds__(256)
     g.sh = g.sw = TS;
   }
   const int vpr = g.c >> 3;
-  const long long total = static_cast<long long>(g.n) * g.p * g.q * vpr;
-  const bool fits32 = total < 0xFFFFFFFFll;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    int cv, q, p, n;
-    split_index(i, fits32, vpr, g.q, g.p, cv, q, p, n);
+  // grid = (column x channel-vector chunks, output rows, images): no division of a flat index
+  for (int n = blockIdx.z; n < g.n; n += gridDim.z)
+  for (int p = blockIdx.y; p < g.p; p += gridDim.y)
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < g.q * vpr;
+       t += gridDim.x * blockDim.x) {
+    const int q = t / vpr;
+    const int cv = t - q * vpr;
     const int h0 = p * g.sh - g.pad_h, w0 = q * g.sw - g.pad_w;
     float acc[8];
     int arg[8];
@@ -567,12 +568,12 @@ __global__ void __launch_bounds__(256)
     g.sh = g.sw = TS;
   }
   const int vpr = g.c >> 3;
-  const long long total = static_cast<long long>(g.n) * g.h * g.w * vpr;
-  const bool fits32 = total < 0xFFFFFFFFll;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    int cv, ww, hh, n;
-    split_index(i, fits32, vpr, g.w, g.h, cv, ww, hh, n);
+  for (int n = blockIdx.z; n < g.n; n += gridDim.z)
+  for (int hh = blockIdx.y; hh < g.h; hh += gridDim.y)
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < g.w * vpr;
+       t += gridDim.x * blockDim.x) {
+    const int ww = t / vpr;
+    const int cv = t - ww * vpr;
     float acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0.f;
@@ -594,6 +595,57 @@ __global__ void __launch_bounds__(256)
       __half2 hacc[4];
 #pragma unroll
       for (int k = 0; k < 4; ++k) hacc[k] = __floats2half2_rn(0.f, 0.f);
+      if (TK > 0 && g.pad_h >= 0 && g.pad_w >= 0) {
+        // Compile-time window: the covering windows are p0 - j (tap row r0 + j*TS), j = 0..J-1,
+        // straight-line and predicated, so all their loads are in flight together.
+        constexpr int TSS = TS > 0 ? TS : 1;
+        constexpr int J = TK > 0 ? (TK + TSS - 1) / TSS : 1;
+        const int ph = hh + g.pad_h, pw = ww + g.pad_w;
+        const int p0 = ph / TSS, r0 = ph - p0 * TSS;
+        const int q0 = pw / TSS, s0 = pw - q0 * TSS;
+        uint4 dv[J * J];
+        uint2 am[J * J];
+        bool ok[J * J];
+#pragma unroll
+        for (int jp = 0; jp < J; ++jp) {
+#pragma unroll
+          for (int jq = 0; jq < J; ++jq) {
+            const int p = p0 - jp, q = q0 - jq;
+            const int idx = jp * J + jq;
+            ok[idx] = (r0 + jp * TSS < TK) && (s0 + jq * TSS < TK) && p >= 0 && p < g.p &&
+                      q >= 0 && q < g.q;
+            dv[idx] = make_uint4(0u, 0u, 0u, 0u);
+            am[idx] = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+            if (ok[idx]) {
+              const long long orow = (static_cast<long long>(n) * g.p + p) * g.q + q;
+              dv[idx] = *reinterpret_cast<const uint4*>(dy + orow * lddy + cv * 8);
+              am[idx] = *reinterpret_cast<const uint2*>(argmax + orow * g.c + cv * 8);
+            }
+          }
+        }
+#pragma unroll
+        for (int jp = 0; jp < J; ++jp) {
+#pragma unroll
+          for (int jq = 0; jq < J; ++jq) {
+            const int idx = jp * J + jq;
+            const unsigned tapv =
+                static_cast<unsigned>((r0 + jp * TSS) * TK + s0 + jq * TSS) * 0x01010101u;
+            const unsigned e0 = am[idx].x ^ tapv, e1 = am[idx].y ^ tapv;
+            const unsigned z0 = ~(((e0 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | e0 | 0x7F7F7F7Fu);
+            const unsigned z1 = ~(((e1 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | e1 | 0x7F7F7F7Fu);
+            const unsigned b0 = ok[idx] ? (z0 >> 7) * 0xFFu : 0u;
+            const unsigned b1 = ok[idx] ? (z1 >> 7) * 0xFFu : 0u;
+            unsigned w[4];
+            w[0] = dv[idx].x & __byte_perm(b0, 0, 0x1100);
+            w[1] = dv[idx].y & __byte_perm(b0, 0, 0x3322);
+            w[2] = dv[idx].z & __byte_perm(b1, 0, 0x1100);
+            w[3] = dv[idx].w & __byte_perm(b1, 0, 0x3322);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              hacc[k] = __hadd2(hacc[k], *reinterpret_cast<const __half2*>(&w[k]));
+          }
+        }
+      } else
       for (int p = p_lo; p <= p_hi; ++p) {
         const int r = hh - (p * g.sh - g.pad_h);
         if (r < 0 || r >= g.kh) continue;
@@ -757,12 +809,12 @@ __global__ void __launch_bounds__(256)
   const int ktot = kh * kw * c;
   const int kpad = TC > 0 ? ((TC * TKH * TKW + 7) / 8 * 8) : kpad_rt;
   const int vpr = kpad >> 3;
-  const long long total = static_cast<long long>(n) * p * q * vpr;
-  const bool fits32 = total < 0xFFFFFFFFll;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    int kv, qq, pp, nn;
-    split_index(i, fits32, vpr, q, p, kv, qq, pp, nn);
+  // grid = (column x K-vector chunks, output rows, images): no division of a flat index
+  for (int nn = blockIdx.z; nn < n; nn += gridDim.z)
+  for (int pp = blockIdx.y; pp < p; pp += gridDim.y)
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < q * vpr; t += gridDim.x * blockDim.x) {
+    const int qq = t / vpr;
+    const int kv = t - qq * vpr;
     const long long row = (static_cast<long long>(nn) * p + pp) * q + qq;
     const int h0 = pp * sh - pad_h, w0 = qq * sw - pad_w;
     const __half* xin = x + static_cast<long long>(nn) * h * w * c;
@@ -1216,7 +1268,8 @@ extern "C" int kfb_pool_forward(const void* x, long long ldx, void* y, long long
                                 void* stream) {
   PoolGeom g;
   if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
-  const int blocks = grid_for((long long)n * p * q * (c / 8));
+  const dim3 blocks((unsigned)((q * (c / 8) + 255) / 256), (unsigned)(p < 65535 ? p : 65535),
+                    (unsigned)(n < 65535 ? n : 65535));
   cudaStream_t st = (cudaStream_t)stream;
   if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
     pool_fwd_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y, ldy, argmax,
@@ -1240,7 +1293,8 @@ extern "C" int kfb_pool_backward(const void* dy, long long lddy, const unsigned 
                                  int pad_w, int is_max, void* stream) {
   PoolGeom g;
   if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
-  const int blocks = grid_for((long long)n * h * w * (c / 8));
+  const dim3 blocks((unsigned)((w * (c / 8) + 255) / 256), (unsigned)(h < 65535 ? h : 65535),
+                    (unsigned)(n < 65535 ? n : 65535));
   cudaStream_t st = (cudaStream_t)stream;
   if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
     pool_bwd_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)dy, lddy, argmax, (__half*)dx,
@@ -1299,7 +1353,8 @@ extern "C" int kfb_im2col_small_c(const void* x, void* col, int n, int h, int w,
                                   int q, int kh, int kw, int sh, int sw, int pad_h, int pad_w,
                                   int kpad, void* stream) {
   KFB_REQUIRE(kpad % 8 == 0 && kpad >= kh * kw * c, "im2col_small_c: bad kpad %d", kpad);
-  const int blocks = grid_for((long long)n * p * q * (kpad / 8), 256, 148 * 32);
+  const dim3 blocks((unsigned)((q * (kpad / 8) + 255) / 256), (unsigned)(p < 65535 ? p : 65535),
+                    (unsigned)(n < 65535 ? n : 65535));
   cudaStream_t st = (cudaStream_t)stream;
 #define KFB_IM2COL(TC, TKH, TKW)                                                              \
   im2col_small_c_kernel<TC, TKH, TKW><<<blocks, 256, 0, st>>>(                                \
