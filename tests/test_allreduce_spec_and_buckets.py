@@ -61,3 +61,34 @@ def test_plan_buckets():
 ])
 def test_reduction_semantics(vu, opt, expect):
     assert reduction_semantics(P.make_params(variable_update=vu, kungfu_option=opt)) == expect
+
+
+def test_fused_push_buckets_cut_only_between_variables():
+    """--comm_impl=p2p_fused: every weight gradient must lie in exactly one bucket so that its
+    owner map is one (bucket start, shard length) pair (parallel/strategy.py)."""
+    import types
+    from kf_benchmarks_b200 import datasets
+    from kf_benchmarks_b200.models import model_config
+    from kf_benchmarks_b200.nn.params import ParameterStore
+    from kf_benchmarks_b200.parallel.strategy import PushTarget, UpdateEngine
+    ds = datasets.create_dataset(None, "cifar10")
+    g = model_config.get_model_config("resnet20", ds, None).build_graph(11, batch_size=2)
+    st = ParameterStore(g, "cpu", fp16_shadow=False)
+    buckets = UpdateEngine._plan_buckets_on_slots(types.SimpleNamespace(store=st), 40000)
+    assert buckets[0][0] == 0 and buckets[-1][1] == st.num_trainable_padded
+    assert all(a[1] == b[0] for a, b in zip(buckets, buckets[1:]))
+    starts = {s.offset for s in st.order} | {st.num_trainable_padded}
+    assert all(lo in starts and hi in starts for lo, hi in buckets)
+    assert all(hi - lo >= 40000 for lo, hi in buckets[:-1]) and len(buckets) > 2
+    for s in st.order:       # no variable straddles a bucket boundary
+        assert sum(1 for lo, hi in buckets if lo <= s.offset < hi) == 1
+        lo, hi = next(b for b in buckets if b[0] <= s.offset < b[1])
+        assert s.offset + s.numel <= hi
+    t = PushTarget()
+    t.nranks, t.per, t.rel = 8, 1024, 256
+    assert ctypes_sizeof(t) >= 4 + 8 + 8 + 8 * 8
+
+
+def ctypes_sizeof(obj):
+    import ctypes
+    return ctypes.sizeof(obj)
