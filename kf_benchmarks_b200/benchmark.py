@@ -507,6 +507,26 @@ class BenchmarkCNN:
             ex.stage_inputs(*src.next_batch())
 
     def _benchmark_train(self) -> Dict:
+        """Timed training loop; a device-side failure (a trapped flag / mbarrier wait - the
+        kernels bound every wait - or any other CUDA error) is reported with the rank, the step
+        and the state of the gradient exchange before it propagates, so a stuck peer is
+        identifiable from the logs of the surviving ranks."""
+        try:
+            return self._benchmark_train_impl()
+        except RuntimeError as e:
+            text = str(e)
+            if "CUDA" in text or "device-side" in text or "launch failure" in text or \
+                    "kfb_" in text:
+                eng = self.engine
+                _log("FATAL rank %d/%d: device error at global step %d (%s). Gradient exchange: "
+                     "algo=%s, buckets=%d, launched this step=%s, flag sequence=%s. A trap in a "
+                     "peer wait means another rank stopped signalling: check its log." %
+                     (self.rank, max(self.world, 1), self.global_step, text.splitlines()[0][:200],
+                      getattr(eng, "algo", "?"), len(getattr(eng, "buckets", []) or []),
+                      getattr(eng, "_launched", "?"), getattr(self.comm, "seq", "?")))
+            raise
+
+    def _benchmark_train_impl(self) -> Dict:
         p = self.params
         forward_only = bool(p.forward_only)
         self._build(phase_train=not forward_only)
