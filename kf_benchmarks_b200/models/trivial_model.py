@@ -1,23 +1,25 @@
-"""Trivial models: one flatten and two tiny FC layers (T/models/trivial_model.py:20-43).
-Used by config #1 (CPU plumbing) and as the fastest smoke model."""
+"""Trivial models: a flatten and two tiny FC layers in front of the classifier
+(T/models/trivial_model.py:20-43). Config #1 of BASELINE.json (CPU plumbing) and the fastest
+smoke model."""
 from . import model
+from .plain_stack import build_stack
+
+_PLAN = [("flatten",), ("fc", 1), ("fc", 4096)]
 
 
-class TrivialModel(model.CNNModel):
+class _Trivial(model.CNNModel):
+    image = 0
+
     def __init__(self, params=None):
-        super().__init__("trivial", 224 + 3, 32, 0.005, params=params)
+        super().__init__("trivial", self.image, 32, 0.005, params=params)
 
     def add_inference(self, cnn):
-        cnn.reshape([-1, 227 * 227 * 3])
-        cnn.affine(1)
-        cnn.affine(4096)
+        build_stack(cnn, _PLAN)
 
 
-class TrivialCifar10Model(model.CNNModel):
-    def __init__(self, params=None):
-        super().__init__("trivial", 32, 32, 0.005, params=params)
+class TrivialModel(_Trivial):
+    image = 227
 
-    def add_inference(self, cnn):
-        cnn.reshape([-1, 32 * 32 * 3])
-        cnn.affine(1)
-        cnn.affine(4096)
+
+class TrivialCifar10Model(_Trivial):
+    image = 32
