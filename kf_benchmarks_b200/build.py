@@ -51,7 +51,30 @@ def _compile_one(src: str, verbose: bool) -> str:
     return obj
 
 
+HOST_LIB = os.path.join(OUT_DIR, "libkfb200_host.so")
+
+
+def build_host(force: bool = False) -> str:
+    """Host-side input runtime (csrc/host/*.cpp, plain g++): TFRecord streaming threads,
+    CRC32C, tf.Example scanner. No CUDA involved, so it also serves the --device=cpu path."""
+    os.makedirs(OUT_DIR, exist_ok=True)
+    srcs = sorted(glob.glob(os.path.join(CSRC, "host", "*.cpp")))
+    if not srcs:
+        raise RuntimeError("no host sources found under csrc/host/")
+    newest = max(os.path.getmtime(s) for s in srcs)
+    if not force and os.path.exists(HOST_LIB) and os.path.getmtime(HOST_LIB) >= newest:
+        return HOST_LIB
+    cxx = os.environ.get("CXX", "g++")
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", "-msse4.2", "-o", HOST_LIB] \
+        + srcs
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"host library build failed:\n{res.stdout}\n{res.stderr}")
+    return HOST_LIB
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
+    build_host(force)
     os.makedirs(OUT_DIR, exist_ok=True)
     os.makedirs(OBJ_DIR, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))

@@ -131,7 +131,21 @@ def decode_jpeg(buf: bytes) -> np.ndarray:
 
 
 def parse_example_proto(record: bytes):
-    """(image bytes, label, bbox or None, text) - T/preprocessing.py:27-72."""
+    """(image bytes, label, bbox or None, text) - T/preprocessing.py:27-72. Uses the native
+    tf.Example scanner (csrc/host/example_scan.cpp) when the host library is built."""
+    from . import native_reader
+    if native_reader.available():
+        buf = native_reader.example_bytes(record, "image/encoded")
+        lab = native_reader.example_numbers(record, "image/class/label", cap=4)
+        if buf is not None and lab:
+            bbox = None
+            xmin = native_reader.example_numbers(record, "image/object/bbox/xmin", cap=64)
+            if xmin:
+                cols = [native_reader.example_numbers(record, "image/object/bbox/" + k, cap=64)
+                        for k in ("ymin", "xmin", "ymax", "xmax")]
+                bbox = tuple(float(c[0]) for c in cols)
+            text = native_reader.example_bytes(record, "image/class/text")
+            return buf, int(lab[0]), bbox, text or b""
     ex = tfrecord.parse_example(record)
     label = int(ex["image/class/label"][0])
     bbox = None
@@ -188,11 +202,23 @@ class ImagenetSource(_BatchSource):
                              dataset.tf_record_pattern(subset))
         shift = int(len(files) * (rank / float(max(world, 1))))
         self.files = files[shift:] + files[:shift]       # shift_ratio = rank / world
+        self.p = params
         self.records = self._record_iter()
         self.cached = None
         super().__init__(params, batch, height, width, device, train, seed * 7919 + rank)
 
     def _record_iter(self):
+        """Endless record stream. With the host library built, files are read and CRC-checked
+        by background C++ threads (--datasets_num_private_threads of them, default 2), file
+        i on thread i % n like a parallel interleave; otherwise by the Python codec."""
+        from . import native_reader
+        if native_reader.available():
+            threads = int(getattr(self.p, "datasets_num_private_threads", None) or 2)
+            return iter(native_reader.RecordReader(self.files, num_threads=threads, capacity=512,
+                                                   check_crc=True, repeat=True))
+        return self._python_record_iter()
+
+    def _python_record_iter(self):
         while True:
             order = list(self.files)
             for path in order:

@@ -1,0 +1,98 @@
+"""Host-side input runtime (csrc/host, libkfb200_host.so): CRC32C, threaded TFRecord streaming,
+tf.Example scanner - checked against the pure-Python codec of data/tfrecord.py."""
+import os
+
+import numpy as np
+import pytest
+
+from kf_benchmarks_b200 import build as build_lib
+from kf_benchmarks_b200.data import native_reader, tfrecord
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built():
+    build_lib.build_host()
+    assert native_reader.available()
+
+
+def test_crc32c_matches_python_and_known_vector():
+    assert native_reader.crc32c(b"123456789") == 0xE3069283          # standard check value
+    rng = np.random.RandomState(0)
+    for n in (0, 1, 7, 8, 9, 63, 1000, 65537):
+        data = rng.bytes(n)
+        assert native_reader.crc32c(data) == tfrecord.crc32c(data)
+        assert native_reader.masked_crc32c(data) == tfrecord.masked_crc(data)
+
+
+def _write(tmp_path, nfiles, per_file):
+    rng = np.random.RandomState(1)
+    paths, all_recs = [], []
+    for f in range(nfiles):
+        recs = [bytes([f]) + rng.bytes(int(rng.randint(0, 3000))) for _ in range(per_file)]
+        path = str(tmp_path / ("part-%05d" % f))
+        tfrecord.write_records(path, recs)
+        paths.append(path)
+        all_recs.append(recs)
+    return paths, all_recs
+
+
+def test_single_thread_preserves_file_order(tmp_path):
+    paths, recs = _write(tmp_path, 3, 20)
+    got = list(native_reader.RecordReader(paths, num_threads=1))
+    assert got == [r for f in recs for r in f]
+    assert got == [r for p in paths for r in tfrecord.read_records(p)]
+
+
+def test_threads_interleave_but_keep_per_file_order(tmp_path):
+    paths, recs = _write(tmp_path, 5, 40)
+    got = list(native_reader.RecordReader(paths, num_threads=3, capacity=8))
+    assert sorted(got) == sorted(r for f in recs for r in f)
+    for f in range(5):                                   # order within one file is preserved
+        assert [r for r in got if r[0] == f] == recs[f]
+
+
+def test_repeat_and_close_do_not_hang(tmp_path):
+    paths, recs = _write(tmp_path, 2, 5)
+    rd = native_reader.RecordReader(paths, num_threads=2, capacity=4, repeat=True,
+                                    shuffle_files=True, seed=3)
+    got = [next(rd) for _ in range(37)]                  # more than one pass
+    assert len(got) == 37 and set(got) <= set(r for f in recs for r in f)
+    rd.close()                                           # readers blocked on a full queue exit
+    with pytest.raises(StopIteration):
+        next(rd)
+
+
+def test_corruption_is_reported(tmp_path):
+    paths, recs = _write(tmp_path, 1, 6)
+    raw = bytearray(open(paths[0], "rb").read())
+    raw[len(raw) // 2] ^= 0x40                           # flip one bit in the middle
+    open(paths[0], "wb").write(bytes(raw))
+    rd = native_reader.RecordReader(paths, num_threads=1)
+    with pytest.raises(IOError) as e:
+        list(rd)
+    assert "corrupt" in str(e.value)
+    ok = list(native_reader.RecordReader(paths, num_threads=1, check_crc=False))
+    assert len(ok) == 6                                  # without validation the bytes pass
+    with pytest.raises(IOError):
+        list(native_reader.RecordReader([str(tmp_path / "missing")]))
+
+
+def test_example_scanner_matches_python_parser():
+    feats = {"image/encoded": [b"\xff\xd8jpegbytes\x00\x01"], "image/class/label": [417],
+             "image/object/bbox/xmin": [0.1, 0.25, 0.5], "image/class/text": [b"dog"],
+             "negatives": [-3, 7, -(1 << 40)], "image/source_id": [b"12345"]}
+    rec = tfrecord.encode_example(feats)
+    assert native_reader.example_bytes(rec, "image/encoded") == feats["image/encoded"][0]
+    assert native_reader.example_bytes(rec, "image/source_id") == b"12345"
+    assert native_reader.example_numbers(rec, "image/class/label") == [417.0]
+    assert native_reader.example_numbers(rec, "negatives") == [-3.0, 7.0, float(-(1 << 40))]
+    assert np.allclose(native_reader.example_numbers(rec, "image/object/bbox/xmin"),
+                       [0.1, 0.25, 0.5])
+    assert native_reader.example_numbers(rec, "absent") is None
+    assert native_reader.example_bytes(rec, "absent") is None
+    assert native_reader.example_bytes(rec, "image/class/label") is None      # not a bytes list
+    assert native_reader.example_numbers(rec, "negatives", cap=1) == [-3.0, 7.0,
+                                                                      float(-(1 << 40))]
+    py = tfrecord.parse_example(rec)
+    for k, v in feats.items():
+        assert py[k] == pytest.approx(v) if isinstance(v[0], float) else py[k] == v
