@@ -116,6 +116,10 @@ class UpdateEngine:
         self.total = n
         self.m = store.opt_slot("m") if self.opt != 0 else None
         self.v = store.opt_slot("v") if self.opt in (2, 3) else None
+        if self.opt == 2 and float(self.v.abs().sum()) == 0.0:
+            # tf.train.RMSPropOptimizer creates its "rms" slot filled with ones
+            # (T/benchmark_cnn.py:1179-1185 uses it with momentum / decay / epsilon flags)
+            self.v.fill_(1.0)
         self.loss_scale = self._initial_loss_scale()
         self.auto_loss_scale = bool(params.use_fp16 and params.fp16_enable_auto_loss_scale)
         self.loss_scale_normal_steps = 0
@@ -249,7 +253,13 @@ class UpdateEngine:
             h.momentum, h.decay, h.epsilon = p.rmsprop_momentum, p.rmsprop_decay, p.rmsprop_epsilon
         elif self.opt == 3:
             h.momentum, h.decay, h.epsilon = p.adam_beta1, p.adam_beta2, p.adam_epsilon
+        # The reference adds num_towers * wd * l2_loss to the loss of ONE tower
+        # (T/benchmark_cnn.py:3078-3099), so the L2 term follows the reduction: summed
+        # gradients (replicated / horovod / *_all_reduce) carry N * wd * w, averaged ones
+        # (parameter_server, KungFu S-SGD) and local steps carry wd * w.
         h.weight_decay = p.weight_decay or 0.0
+        if self._effective_algo() == "allreduce" and not self.average:
+            h.weight_decay *= self.comm.size
         scale = 1.0 / self.loss_scale
         if self._effective_algo() == "allreduce" and self.average:
             scale /= self.comm.size

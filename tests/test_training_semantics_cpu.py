@@ -54,7 +54,8 @@ class _Sim:
             self.srcs.append(inputs.SyntheticHostSource(
                 self.p.batch_size, 32, 3, ds.num_classes, "cpu", seed * 1000003 + r,
                 dtype=torch.float32))
-            self.slots.append((torch.zeros_like(st.w32), torch.zeros_like(st.w32)))
+            rms_init = 1.0 if self.p.optimizer == "rmsprop" else 0.0      # TF: rms slot = ones
+            self.slots.append((torch.zeros_like(st.w32), torch.full_like(st.w32, rms_init)))
         # every mode starts from rank 0's variables (broadcast at start)
         for st in self.stores[1:]:
             st.w32.copy_(self.stores[0].w32)
@@ -74,6 +75,9 @@ class _Sim:
         h = self.engine._hyper(p.init_learning_rate)
         h.adam_t = float(k + 1)
         h.grad_scale = 1.0
+        # the reference puts num_towers * wd * l2 on one tower: summed gradients carry N * wd * w
+        h.weight_decay = p.weight_decay * (n if p.variable_update in ("replicated", "horovod")
+                                           else 1)
         gs = [self.grads(r) for r in range(n)]
         vu, opt = p.variable_update, p.kungfu_option
         if vu == "independent" or n == 1:
@@ -244,6 +248,7 @@ def test_relaxed_consistency_applies_gradients_one_step_late(tmp_path):
     for k in range(3):
         h = sim.engine._hyper(kw["init_learning_rate"])
         h.grad_scale = 1.0
+        h.weight_decay = kw["weight_decay"] * 2        # summed gradients carry N * wd * w
         gs = [sim.grads(r) for r in range(2)]
         if pending is not None:
             for r in range(2):
