@@ -256,3 +256,85 @@ def test_relaxed_consistency_applies_gradients_one_step_late(tmp_path):
         pending = sum(gs)
     for r in range(2):
         assert np.allclose(results[r]["w"], sim.stores[r].w32.numpy(), rtol=2e-5, atol=2e-6)
+
+
+def _numpy_trivial_losses(kw, steps):
+    """Independent float64 NumPy re-simulation of the driver on the trivial CIFAR model
+    (flatten -> FC1+ReLU -> FC4096+ReLU -> FC11, softmax cross-entropy + wd * l2): the printed
+    loss of every step. Counterpart of the reference's `manually_compute_losses`
+    (T/test_util.py:365-443, T/benchmark_cnn_test.py:1236-1365); nothing of the framework's
+    executors or update kernels is used - only the initial variables and the input batches."""
+    p = P.make_params(**kw)
+    ds = datasets.create_dataset(None, "cifar10")
+    model = model_config.get_model_config(p.model, ds, p)
+    g = model.build_graph(ds.num_classes, batch_size=p.batch_size)
+    st = ParameterStore(g, "cpu", fp16_shadow=False)
+    st.initialize(p.tf_random_seed)
+    tf = st.to_tf_arrays()
+    names = ["v0/cg/affine%d/%s" % (i, k) for i in range(3) for k in ("weights", "biases")]
+    w = [tf[n].astype(np.float64) for n in names]          # [in,out] weights, [out] biases
+    slots = [(np.zeros_like(x), np.full_like(x, 1.0 if p.optimizer == "rmsprop" else 0.0))
+             for x in w]
+    src = inputs.SyntheticHostSource(p.batch_size, 32, 3, ds.num_classes, "cpu",
+                                     p.tf_random_seed * 1000003, dtype=torch.float32)
+    lr, wd = p.init_learning_rate, p.weight_decay or 0.0
+    losses = []
+    for k in range(steps):
+        images, labels = src.next_batch()
+        x0 = images.numpy().astype(np.float64).reshape(p.batch_size, -1)
+        y = labels.numpy().astype(np.int64)
+        z1 = x0 @ w[0] + w[1]
+        a1 = np.maximum(z1, 0)
+        z2 = a1 @ w[2] + w[3]
+        a2 = np.maximum(z2, 0)
+        z3 = a2 @ w[4] + w[5]
+        z3s = z3 - z3.max(1, keepdims=True)
+        logp = z3s - np.log(np.exp(z3s).sum(1, keepdims=True))
+        base = -logp[np.arange(len(y)), y].mean()
+        losses.append(base + wd * sum(0.5 * (v ** 2).sum() for v in w))
+        d3 = np.exp(logp)
+        d3[np.arange(len(y)), y] -= 1
+        d3 /= len(y)
+        grads = [None] * 6
+        grads[4], grads[5] = a2.T @ d3, d3.sum(0)
+        d2 = (d3 @ w[4].T) * (z2 > 0)
+        grads[2], grads[3] = a1.T @ d2, d2.sum(0)
+        d1 = (d2 @ w[2].T) * (z1 > 0)
+        grads[0], grads[1] = x0.T @ d1, d1.sum(0)
+        for i in range(6):
+            gi = grads[i] + wd * w[i]
+            if p.gradient_clip:
+                gi = np.clip(gi, -p.gradient_clip, p.gradient_clip)
+            m, v = slots[i]
+            if p.optimizer == "sgd":
+                w[i] = w[i] - lr * gi
+            elif p.optimizer == "momentum":                     # ApplyMomentum, use_nesterov
+                m[:] = p.momentum * m + gi
+                w[i] = w[i] - lr * (gi + p.momentum * m)
+            elif p.optimizer == "rmsprop":
+                v[:] = p.rmsprop_decay * v + (1 - p.rmsprop_decay) * gi * gi
+                m[:] = p.rmsprop_momentum * m + lr * gi / np.sqrt(v + p.rmsprop_epsilon)
+                w[i] = w[i] - m
+            else:                                               # adam
+                b1, b2, t = p.adam_beta1, p.adam_beta2, k + 1
+                m[:] = b1 * m + (1 - b1) * gi
+                v[:] = b2 * v + (1 - b2) * gi * gi
+                w[i] = w[i] - lr * np.sqrt(1 - b2 ** t) / (1 - b1 ** t) * m / \
+                    (np.sqrt(v) + p.adam_epsilon)
+    return losses
+
+
+@pytest.mark.parametrize("extra", [
+    dict(optimizer="sgd"), dict(optimizer="momentum"), dict(optimizer="rmsprop"),
+    dict(optimizer="adam"), dict(optimizer="momentum", gradient_clip=0.01),
+    dict(optimizer="sgd", weight_decay=0.0),
+])
+def test_printed_losses_match_an_independent_numpy_simulation(extra):
+    kw = dict(BASE, num_batches=5, init_learning_rate=1e-7, **extra)
+    kw.update(extra)
+    _, _, lines = _run_single(kw)
+    printed = [float(l.split("\t")[-1]) for l in lines if re.match(r"^\d+\timages/sec: ", l)]
+    want = _numpy_trivial_losses(kw, 5)
+    assert len(printed) == 5
+    assert np.allclose(printed, want, rtol=2e-4, atol=2e-3), (printed, want)
+    assert printed[0] != printed[-1]                    # the variables really move
