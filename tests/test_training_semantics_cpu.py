@@ -338,3 +338,33 @@ def test_printed_losses_match_an_independent_numpy_simulation(extra):
     assert len(printed) == 5
     assert np.allclose(printed, want, rtol=2e-4, atol=2e-3), (printed, want)
     assert printed[0] != printed[-1]                    # the variables really move
+
+
+def test_early_stop_and_eval_schedule_with_mocked_accuracies(monkeypatch):
+    """T/benchmark_cnn_test.py:1005-1169: evaluations happen exactly at the requested steps
+    and training stops at the first evaluation whose top-1 reaches --stop_at_top_1_accuracy."""
+    accs = iter([0.1, 0.4, 0.95, 0.99])
+    calls = []
+
+    def fake_eval(self):
+        calls.append(self.global_step)
+        a = next(accs)
+        return {"top_1_accuracy": a, "top_5_accuracy": a, "num_examples": 4,
+                "eval_average_loss": 0.0, "images_per_sec": 1.0}
+    monkeypatch.setattr(benchmark.BenchmarkCNN, "_eval_during_training", fake_eval)
+    kw = dict(BASE, num_batches=10, eval_during_training_at_specified_steps=["2", "3", "5", "8"],
+              stop_at_top_1_accuracy=0.9)
+    bench, stats, lines = _run_single(kw)
+    assert calls == [2, 3, 5]                       # stopped after the third evaluation
+    assert stats["num_steps"] == 5
+    assert any("top_1_accuracy" in l and "0.95" in l or "Stopping" in l or "stop" in l.lower()
+               for l in lines)
+    # every-n-steps schedule without early stop evaluates floor(10 / 4) times
+    accs2 = iter([0.0] * 10)
+    calls.clear()
+    monkeypatch.setattr(benchmark.BenchmarkCNN, "_eval_during_training",
+                        lambda self: (calls.append(self.global_step), {
+                            "top_1_accuracy": next(accs2), "top_5_accuracy": 0.0, "num_examples": 4,
+                            "eval_average_loss": 0.0, "images_per_sec": 1.0})[1])
+    _, stats, _ = _run_single(dict(BASE, num_batches=10, eval_during_training_every_n_steps=4))
+    assert calls == [4, 8] and stats["num_steps"] == 10
