@@ -414,7 +414,8 @@ class BenchmarkCNN:
                                                           dtype=np.int64)
         path = ckpt_lib.save_checkpoint(p.train_dir, self.global_step, self.store, extra,
                                         max_to_keep=p.max_ckpts_to_keep,
-                                        opt_slots=self._opt_slot_arrays())
+                                        opt_slots=self._opt_slot_arrays(),
+                                        fmt=p.checkpoint_format)
         _log("Saved checkpoint %s" % path)
 
     def _opt_slot_arrays(self):
@@ -552,7 +553,10 @@ class BenchmarkCNN:
         pending = []  # (event_start, event_end) of steps whose time has not been read yet
         n_done = 0
         stop_early = False
-        for local_step in range(-self.num_warmup_batches, self.num_batches):
+        # --num_batches counts from global step 0: a run resumed from a checkpoint only does the
+        # remaining steps (T/benchmark_cnn.py:2242-2250); warm-up steps run (and train) anyway
+        end_local_step = max(self.num_batches - self.global_step, 0)
+        for local_step in range(-self.num_warmup_batches, end_local_step):
             if local_step == 0:
                 self._sync()
                 self.comm.barrier()

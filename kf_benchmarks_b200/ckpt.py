@@ -2,13 +2,15 @@
 
 The reference saves ``train_dir/model.ckpt-<global_step>`` through ``tf.train.Saver`` plus a
 ``checkpoint`` state file (T/benchmark_cnn.py:2076-2082,2373-2378) and loads the newest or a
-named one (``load_checkpoint`` :905-950). TensorFlow is not available on this image, so the
-tensors are stored as one ``.npz`` per checkpoint whose *keys are the reference's TF variable
-names* (``v0/cg/conv0/conv2d/kernel`` ..., HWIO / [in,out] layouts, fp32, plus ``global_step``,
-``loss_scale``, ``loss_scale_normal_steps`` and ``<var>/Momentum`` style optimizer slots) -
-``tools/export_tf_checkpoint.py`` turns such a file into a real TF bundle wherever TensorFlow
-is installed. The ``checkpoint`` state file uses TF's text format with relative paths so a
-moved ``train_dir`` still resolves.
+named one (``load_checkpoint`` :905-950). By default the tensors are stored as one ``.npz`` per
+checkpoint whose *keys are the reference's TF variable names* (``v0/cg/conv0/conv2d/kernel``
+..., HWIO / [in,out] layouts, fp32, plus ``global_step``, ``loss_scale``,
+``loss_scale_normal_steps`` and ``<var>/Momentum`` style optimizer slots);
+``--checkpoint_format=tf`` writes the same tensors as a TensorFlow V2 bundle (``tf_bundle.py``,
+no TensorFlow needed) and either format - including bundles written by the reference - is
+restored transparently. ``tools/export_tf_checkpoint.py`` converts between the two. The
+``checkpoint`` state file uses TF's text format with relative paths so a moved ``train_dir``
+still resolves.
 """
 from __future__ import annotations
 
@@ -49,8 +51,24 @@ def _read_state(train_dir: str):
     return names
 
 
+def _exists(base: str) -> bool:
+    return os.path.exists(base + _SUFFIX) or os.path.exists(base + ".index")
+
+
+def _remove(base: str) -> None:
+    import glob
+    for path in [base + _SUFFIX, base + ".index"] + glob.glob(base + ".data-*"):
+        try:
+            os.remove(path)
+        except OSError:
+            pass
+
+
 def save_checkpoint(train_dir: str, global_step: int, store, extra: Optional[Dict] = None,
-                    max_to_keep: int = 5, opt_slots: Optional[Dict] = None) -> str:
+                    max_to_keep: int = 5, opt_slots: Optional[Dict] = None,
+                    fmt: str = "npz") -> str:
+    """``fmt="npz"`` (default) or ``"tf"``: a TensorFlow V2 bundle (``model.ckpt-N.index`` +
+    ``.data-00000-of-00001``, see tf_bundle.py) the reference's Saver can restore."""
     os.makedirs(train_dir, exist_ok=True)
     arrays = store.to_tf_arrays("v0/")
     if opt_slots:
@@ -65,16 +83,16 @@ def save_checkpoint(train_dir: str, global_step: int, store, extra: Optional[Dic
     for k, v in (extra or {}).items():
         arrays[k] = np.asarray(v)
     name = "model.ckpt-%d" % global_step
-    tmp = os.path.join(train_dir, name + ".tmp" + _SUFFIX)
-    np.savez(tmp, **arrays)
-    os.replace(tmp, os.path.join(train_dir, name + _SUFFIX))
+    if fmt == "tf":
+        from . import tf_bundle
+        tf_bundle.write_bundle(os.path.join(train_dir, name), arrays)
+    else:
+        tmp = os.path.join(train_dir, name + ".tmp" + _SUFFIX)
+        np.savez(tmp, **arrays)
+        os.replace(tmp, os.path.join(train_dir, name + _SUFFIX))
     names = [n for n in _read_state(train_dir) if n != name] + [name]
     while max_to_keep and len(names) > max_to_keep:
-        old = names.pop(0)
-        try:
-            os.remove(os.path.join(train_dir, old + _SUFFIX))
-        except OSError:
-            pass
+        _remove(os.path.join(train_dir, names.pop(0)))
     _write_state(train_dir, names)
     return os.path.join(train_dir, name)
 
@@ -87,7 +105,7 @@ def latest_checkpoint(path: str) -> Tuple[str, int]:
     m = re.match(r".*ckpt-(\d+)$", path[:-len(_SUFFIX)] if path.endswith(_SUFFIX) else path)
     if m:
         base = path[:-len(_SUFFIX)] if path.endswith(_SUFFIX) else path
-        if not os.path.exists(base + _SUFFIX):
+        if not _exists(base):
             raise CheckpointNotFoundException("No checkpoint file found at %s" % base)
         return base, int(m.group(1))
     names = _read_state(path)
@@ -95,11 +113,18 @@ def latest_checkpoint(path: str) -> Tuple[str, int]:
         raise CheckpointNotFoundException("No checkpoint file found in dir:`%s`" % path)
     name = os.path.basename(names[-1])
     base = os.path.join(path, name)
-    if not os.path.exists(base + _SUFFIX):
+    if not _exists(base):
         raise CheckpointNotFoundException("No checkpoint file found at %s" % base)
     return base, int(name.split("-")[-1])
 
 
 def load_arrays(base_path: str) -> Dict[str, np.ndarray]:
+    """Tensors of a checkpoint: the framework's ``.npz`` or a TensorFlow V2 bundle (for
+    example one written by the reference's Saver)."""
+    if base_path.endswith(_SUFFIX):
+        base_path = base_path[:-len(_SUFFIX)]
+    if not os.path.exists(base_path + _SUFFIX) and os.path.exists(base_path + ".index"):
+        from . import tf_bundle
+        return tf_bundle.read_bundle(base_path)
     with np.load(base_path + _SUFFIX) as z:
         return {k: z[k] for k in z.files}

@@ -67,3 +67,36 @@ def test_optimizer_slots_are_saved(tmp_path):
     arrays = ckpt.load_arrays(path)
     mom = arrays["v0/cg/conv1/conv2d/kernel/Momentum"]
     assert mom.shape == (3, 3, 16, 16) and np.all(mom == 0.5)
+
+
+def test_tf_bundle_checkpoints_save_resume_and_interchange(tmp_path):
+    """--checkpoint_format=tf writes TensorFlow V2 bundles; both formats restore through the
+    same entry points, and the two are interchangeable tensor for tensor."""
+    from kf_benchmarks_b200 import tf_bundle
+    st = _store()
+    g = st.graph
+    d = str(tmp_path / "tfck")
+    ckpt.save_checkpoint(d, 7, st, {"global_step": np.asarray(7, np.int64)}, fmt="tf")
+    assert os.path.exists(os.path.join(d, "model.ckpt-7.index"))
+    assert os.path.exists(os.path.join(d, "model.ckpt-7.data-00000-of-00001"))
+    assert not os.path.exists(os.path.join(d, "model.ckpt-7.npz"))
+    path, step = ckpt.latest_checkpoint(d)
+    assert step == 7
+    arrays = ckpt.load_arrays(path)
+    assert int(arrays["global_step"]) == 7
+    want = st.to_tf_arrays("v0/")
+    for k, v in want.items():
+        assert np.array_equal(arrays[k], v), k
+    assert arrays["v0/cg/conv0/conv2d/kernel"].shape[:2] == (3, 3)       # HWIO, as TF stores it
+    st2 = ParameterStore(g, "cpu", fp16_shadow=False)
+    st2.from_tf_arrays(arrays)
+    assert np.array_equal(st2.w32.numpy(), st.w32.numpy())
+    # max_to_keep removes both files of old bundles
+    for s in (8, 9, 10):
+        ckpt.save_checkpoint(d, s, st, fmt="tf", max_to_keep=2)
+    left = sorted(f for f in os.listdir(d) if f.startswith("model.ckpt-"))
+    assert left == ["model.ckpt-10.data-00000-of-00001", "model.ckpt-10.index",
+                    "model.ckpt-9.data-00000-of-00001", "model.ckpt-9.index"]
+    # explicit path to a bundle
+    assert ckpt.latest_checkpoint(os.path.join(d, "model.ckpt-9"))[1] == 9
+    assert "v0/cg/affine0/biases" in tf_bundle.list_bundle(os.path.join(d, "model.ckpt-9"))

@@ -115,6 +115,24 @@ def test_export_tool_lists_reference_names(tmp_path):
     assert res.returncode == 0
     assert "v0/cg/affine0/weights" in res.stdout and "v0/cg/affine0/weights/Momentum" in res.stdout
     assert "global_step" in res.stdout
+    # npz -> TensorFlow bundle -> resume training from the bundle
+    out = tmp_path / "tf" / "model.ckpt-1"
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "export_tf_checkpoint.py"),
+                          os.path.join(str(tmp_path), "model.ckpt-1.npz"), str(out)],
+                         capture_output=True, text=True, timeout=60)
+    assert res.returncode == 0 and os.path.exists(str(out) + ".index"), res.stderr
+    with open(str(tmp_path / "tf" / "checkpoint"), "w") as f:
+        f.write('model_checkpoint_path: "model.ckpt-1"\nall_model_checkpoint_paths: '
+                '"model.ckpt-1"\n')
+    lines = []
+    log_util.log_fn = lines.append
+    try:
+        kw2 = dict(kw, train_dir=str(tmp_path / "tf"), num_batches=2, checkpoint_format="tf")
+        benchmark.BenchmarkCNN(benchmark.setup(P.make_params(**kw2))).run()
+    finally:
+        log_util.log_fn = old
+    assert any("Restored checkpoint" in l and "global_step 1" in l for l in lines)
+    assert os.path.exists(str(tmp_path / "tf" / "model.ckpt-2.index"))
 
 
 def test_platform_hooks_and_cluster_manager():
