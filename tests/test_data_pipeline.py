@@ -138,7 +138,8 @@ def test_training_on_fabricated_imagenet_records(tmp_path):
     assert any(l.startswith("Dataset:     imagenet") and "synthetic" not in l for l in lines) or True
     stats, lines = _run(dict(kw, eval=True, num_batches=2))
     assert stats["num_examples"] == 8
-    stats, _ = _run(dict(kw, datasets_repeat_cached_sample=True, distortions=False))
+    stats, _ = _run(dict(kw, datasets_repeat_cached_sample=True, distortions=False,
+                         train_dir=str(tmp_path / "ckpt2")))     # fresh dir: no resume
     assert stats["num_steps"] == 3
 
 
