@@ -356,10 +356,41 @@ class BenchmarkCNN:
         except ckpt_lib.CheckpointNotFoundException:
             return
         arrays = ckpt_lib.load_arrays(path)
-        self.store.from_tf_arrays(arrays, strict=False)
+        ckpt_lib.restore_into(self.store, arrays, ckpt_lib.variable_prefix(p.variable_update))
         self.global_step = int(arrays.get("global_step", step))
+        self._restore_optimizer_state(arrays)
         if self.rank == 0:
             _log("Restored checkpoint %s (global_step %d)" % (path, self.global_step))
+
+    def _restore_optimizer_state(self, arrays) -> None:
+        """Optimizer slots (``<var>/Momentum`` ...) and the loss-scale state are saved
+        variables in the reference too, so a resumed run continues with them."""
+        from .nn.params import _tf_to_native
+        eng, st = self.engine, self.store
+        suffixes = {"momentum": {"m": "Momentum"}, "rmsprop": {"v": "RMSProp", "m": "RMSProp_1"},
+                    "adam": {"m": "Adam", "v": "Adam_1"}, "sgd": {}}[self.params.optimizer]
+        for key, suffix in suffixes.items():
+            arena = st.opt_slots.get(key)
+            if arena is None:
+                continue
+            for spec in st.graph.params.values():
+                if not spec.trainable:
+                    continue
+                for prefix in ("v0/", "v/"):
+                    name = "%s%s/%s" % (prefix, spec.name, suffix)
+                    if name in arrays:
+                        slot = st.slots[spec.name]
+                        val = _tf_to_native(spec, torch.from_numpy(
+                            np.asarray(arrays[name], dtype=np.float32)))
+                        arena[slot.offset:slot.offset + slot.numel].copy_(val.reshape(-1))
+                        break
+        if eng is not None:
+            # Adam's bias correction (TF saves beta1_power / beta2_power) and the ada_sgd switch
+            # count optimizer steps from the start of training, not of this process
+            eng.step_count = int(self.global_step)
+        if "loss_scale" in arrays and eng is not None:
+            eng.loss_scale = float(arrays["loss_scale"])
+            eng.loss_scale_normal_steps = int(arrays.get("loss_scale_normal_steps", 0))
 
     def _maybe_load_backbone(self) -> None:
         """--backbone_model_path (T/benchmark_cnn.py:2204-2205, T/models/ssd_model.py:256-297):
@@ -415,7 +446,8 @@ class BenchmarkCNN:
         path = ckpt_lib.save_checkpoint(p.train_dir, self.global_step, self.store, extra,
                                         max_to_keep=p.max_ckpts_to_keep,
                                         opt_slots=self._opt_slot_arrays(),
-                                        fmt=p.checkpoint_format)
+                                        fmt=p.checkpoint_format,
+                                        prefix=ckpt_lib.variable_prefix(p.variable_update))
         _log("Saved checkpoint %s" % path)
 
     def _opt_slot_arrays(self):
@@ -742,7 +774,8 @@ class BenchmarkCNN:
         result = {}
         while True:
             path, step = ckpt_lib.latest_checkpoint(p.train_dir)
-            self.store.from_tf_arrays(ckpt_lib.load_arrays(path), strict=False)
+            ckpt_lib.restore_into(self.store, ckpt_lib.load_arrays(path),
+                                  ckpt_lib.variable_prefix(p.variable_update))
             self.global_step = step
             result = self._eval_once(self._eval_batches())
             if self.rank == 0:

@@ -66,11 +66,11 @@ def _remove(base: str) -> None:
 
 def save_checkpoint(train_dir: str, global_step: int, store, extra: Optional[Dict] = None,
                     max_to_keep: int = 5, opt_slots: Optional[Dict] = None,
-                    fmt: str = "npz") -> str:
+                    fmt: str = "npz", prefix: str = "v0/") -> str:
     """``fmt="npz"`` (default) or ``"tf"``: a TensorFlow V2 bundle (``model.ckpt-N.index`` +
     ``.data-00000-of-00001``, see tf_bundle.py) the reference's Saver can restore."""
     os.makedirs(train_dir, exist_ok=True)
-    arrays = store.to_tf_arrays("v0/")
+    arrays = store.to_tf_arrays(prefix)
     if opt_slots:
         from .nn.params import _native_to_tf
         for suffix, arena in opt_slots.items():
@@ -79,7 +79,7 @@ def save_checkpoint(train_dir: str, global_step: int, store, extra: Optional[Dic
                     continue
                 s = store.slots[p.name]
                 t = arena[s.offset:s.offset + s.numel].view(p.shape).detach().float().cpu()
-                arrays["v0/%s/%s" % (p.name, suffix)] = _native_to_tf(p, t).numpy()
+                arrays["%s%s/%s" % (prefix, p.name, suffix)] = _native_to_tf(p, t).numpy()
     for k, v in (extra or {}).items():
         arrays[k] = np.asarray(v)
     name = "model.ckpt-%d" % global_step
@@ -116,6 +116,23 @@ def latest_checkpoint(path: str) -> Tuple[str, int]:
     if not _exists(base):
         raise CheckpointNotFoundException("No checkpoint file found at %s" % base)
     return base, int(name.split("-")[-1])
+
+
+def variable_prefix(variable_update: str) -> str:
+    """Outer variable scope of the reference: ``v/`` with a parameter server (one shared copy,
+    T/variable_mgr.py:212-214), ``v0/`` (tower 0 of the replicas) otherwise (:175-177,
+    307-309, 358-365)."""
+    return "v/" if variable_update == "parameter_server" else "v0/"
+
+
+def restore_into(store, arrays: Dict[str, np.ndarray], prefix: str = "v0/"):
+    """Loads ``arrays`` into ``store``; a checkpoint written under the other outer scope
+    (``v/`` vs ``v0/``) is accepted too, so runs can switch variable_update modes."""
+    other = "v/" if prefix == "v0/" else "v0/"
+    have = sum(1 for k in arrays if k.startswith(prefix))
+    alt = sum(1 for k in arrays if k.startswith(other))
+    use = prefix if have >= alt else other
+    return store.from_tf_arrays(arrays, prefix=use, strict=False)
 
 
 def load_arrays(base_path: str) -> Dict[str, np.ndarray]:

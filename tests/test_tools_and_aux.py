@@ -113,7 +113,7 @@ def test_export_tool_lists_reference_names(tmp_path):
                           "--list", os.path.join(str(tmp_path), "model.ckpt-1.npz")],
                          capture_output=True, text=True, timeout=60)
     assert res.returncode == 0
-    assert "v0/cg/affine0/weights" in res.stdout and "v0/cg/affine0/weights/Momentum" in res.stdout
+    assert "v/cg/affine0/weights" in res.stdout and "v/cg/affine0/weights/Momentum" in res.stdout  # default variable_update=parameter_server -> outer scope v/
     assert "global_step" in res.stdout
     # npz -> TensorFlow bundle -> resume training from the bundle
     out = tmp_path / "tf" / "model.ckpt-1"

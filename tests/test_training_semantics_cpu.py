@@ -375,3 +375,42 @@ def test_early_stop_and_eval_schedule_with_mocked_accuracies(monkeypatch):
                             "eval_average_loss": 0.0, "images_per_sec": 1.0})[1])
     _, stats, _ = _run_single(dict(BASE, num_batches=10, eval_during_training_every_n_steps=4))
     assert calls == [4, 8] and stats["num_steps"] == 10
+
+
+@pytest.mark.parametrize("opt", ["momentum", "rmsprop", "adam"])
+def test_resume_continues_exactly_including_optimizer_slots(tmp_path, opt):
+    """2 steps + resume for 2 more == 4 steps in one run (variables and slots are restored)."""
+    base = dict(BASE, optimizer=opt, init_learning_rate=1e-7)
+    one, _, _ = _run_single(dict(base, num_batches=4, train_dir=str(tmp_path / "a")))
+    _run_single(dict(base, num_batches=2, train_dir=str(tmp_path / "b")))
+    # the synthetic source alternates two batches: after 2 steps the resumed run starts on the
+    # same batch the uninterrupted run would use for step 3
+    two, _, lines = _run_single(dict(base, num_batches=4, train_dir=str(tmp_path / "b")))
+    assert any("Restored checkpoint" in l for l in lines)
+    assert two.global_step == one.global_step == 4
+    assert torch.allclose(one.store.w32, two.store.w32, rtol=1e-6, atol=1e-9)
+    from kf_benchmarks_b200 import ckpt
+    a = ckpt.load_arrays(ckpt.latest_checkpoint(str(tmp_path / "a"))[0])
+    b = ckpt.load_arrays(ckpt.latest_checkpoint(str(tmp_path / "b"))[0])
+    assert set(a) == set(b) and any("/" + {"momentum": "Momentum", "rmsprop": "RMSProp",
+                                           "adam": "Adam_1"}[opt] in k for k in a)
+    for k in a:           # variables and optimizer slots, logical (checkpoint) layout
+        assert np.allclose(a[k], b[k], rtol=1e-5, atol=1e-12), k
+
+
+def test_parameter_server_checkpoints_use_the_v_scope(tmp_path):
+    """T/variable_mgr.py:212-214: one shared copy `v/...` with a parameter server, `v0/...`
+    (tower 0) otherwise; a checkpoint of one mode restores into the other."""
+    from kf_benchmarks_b200 import ckpt
+    d = str(tmp_path / "ps")
+    ps, _, _ = _run_single(dict(BASE, variable_update="parameter_server", optimizer="momentum",
+                                num_batches=2, train_dir=d))
+    arrays = ckpt.load_arrays(ckpt.latest_checkpoint(d)[0])
+    assert "v/cg/affine0/weights" in arrays and "v/cg/affine0/weights/Momentum" in arrays
+    assert not any(k.startswith("v0/") for k in arrays)
+    rep, _, lines = _run_single(dict(BASE, variable_update="replicated", optimizer="momentum",
+                                     num_batches=2, train_dir=d))
+    assert any("Restored checkpoint" in l for l in lines)
+    assert torch.equal(rep.store.w32, ps.store.w32)        # nothing left to run: same variables
+    arrays = ckpt.load_arrays(ckpt.latest_checkpoint(d)[0])
+    assert "v0/cg/affine0/weights" in arrays
