@@ -1436,9 +1436,8 @@ extern "C" int kfb_softmax_xent(const float* logits, long long ldl, const int* l
 // kfb_softmax_xent needs three per-row scratch arrays (row losses and the top-1 / top-5 hit
 // flags that the finalize kernel folds). Some callers have no way to provide them: code that
 // runs where cudaMalloc is off limits (inside a latency-critical serving or training loop
-// where the implicit device synchronisation of an allocation is not acceptable, inside a
-// region that is being stream-captured, or embedded in a host application that owns all device
-// memory and hands this library none). For those, the scratch lives in the fixed-size device
+// where the implicit device synchronisation of an allocation is not acceptable, or embedded
+// in a host application that owns all device memory and hands this library none). For those, the scratch lives in the fixed-size device
 // array below, which every GPU that loads this library keeps until the process exits
 // (kXentStaticMaxRows * 12 bytes = 48 KiB).
 //

@@ -167,7 +167,7 @@ int kfb_softmax_xent(const float* logits, long long ldl, const int* labels, int 
                      float* loss_rows, int* top1, int* top5, float* out3, void* stream);
 /* Allocation-free variant of kfb_softmax_xent (no counterpart in the reference; it exists for
  * callers of this library that cannot allocate device memory: hot loops that must not hit the
- * implicit synchronisation of cudaMalloc, code inside a stream capture, hosts that own the
+ * implicit synchronisation of cudaMalloc, and hosts that own the
  * whole device heap). The per-row scratch lives in a 48 KiB static device array inside the
  * library, so rows <= kfb_softmax_xent_static_max_rows() (4096); larger batches are rejected
  * with an error. No cudaMalloc / cudaFree / allocating call is made. The first call on each

@@ -1,8 +1,7 @@
 """The allocation-free softmax-cross-entropy entry point (``kfb_softmax_xent_static``).
 
 Some users of the library cannot give it scratch memory: a training or serving loop that must
-never reach ``cudaMalloc`` (it synchronises the device), code running inside a stream capture,
-or a host program that owns the whole device heap. For them the entry point keeps its per-row
+never reach ``cudaMalloc`` (it synchronises the device), or a host program that owns the whole device heap. For them the entry point keeps its per-row
 scratch in a fixed 48 KiB device array inside the shared library (at most 4096 rows per call).
 
 The test drives the function through the C ABI only (``ctypes`` on the built ``.so``) and checks
