@@ -96,3 +96,50 @@ def test_example_scanner_matches_python_parser():
     py = tfrecord.parse_example(rec)
     for k, v in feats.items():
         assert py[k] == pytest.approx(v) if isinstance(v[0], float) else py[k] == v
+
+
+# ---- sanitizer builds of the host runtime (TSAN build of the C++ runtime) -------
+def _sanitizer_run(tmp_path, name, flags, env_extra):
+    import glob
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    srcs = sorted(glob.glob(os.path.join(root, "csrc", "host", "*.cpp")))
+    srcs.append(os.path.join(root, "csrc", "host", "stress", "reader_stress.cpp"))
+    exe = str(tmp_path / name)
+    # $CXX may point at a toolchain that ships without the sanitizer runtimes: try the system
+    # compilers as well before giving up
+    res = None
+    for cxx in dict.fromkeys([os.environ.get("CXX", "g++"), "/usr/bin/g++", "g++", "clang++"]):
+        if shutil.which(cxx) is None:
+            continue
+        res = subprocess.run([cxx, "-g", "-O1", "-std=c++17", "-pthread", "-msse4.2"] + flags
+                             + srcs + ["-o", exe], capture_output=True, text=True)
+        if res.returncode == 0 or "cannot find" not in res.stderr:
+            break
+    if res is None:
+        pytest.skip("no C++ compiler")
+    if res.returncode != 0 and ("cannot find" in res.stderr or "unrecognized" in res.stderr):
+        pytest.skip("sanitizer runtime not installed: " + res.stderr.strip()[-300:])
+    assert res.returncode == 0, res.stderr
+    scratch = tmp_path / "data"
+    scratch.mkdir()
+    env = dict(os.environ, **env_extra)
+    run = subprocess.run([exe, str(scratch), "12"], capture_output=True, text=True, env=env,
+                         timeout=600)
+    report = run.stdout + run.stderr
+    assert run.returncode == 0, report
+    assert "reader_stress ok" in run.stdout
+    assert "ThreadSanitizer" not in report and "AddressSanitizer" not in report \
+        and "runtime error" not in report, report
+
+
+def test_host_runtime_is_clean_under_thread_sanitizer(tmp_path):
+    _sanitizer_run(tmp_path, "rs_tsan", ["-fsanitize=thread"],
+                   {"TSAN_OPTIONS": "halt_on_error=1 exitcode=66"})
+
+
+def test_host_runtime_is_clean_under_address_and_ub_sanitizers(tmp_path):
+    _sanitizer_run(tmp_path, "rs_asan",
+                   ["-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"],
+                   {"ASAN_OPTIONS": "detect_leaks=1"})
