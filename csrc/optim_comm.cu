@@ -374,6 +374,129 @@ __global__ void __launch_bounds__(512)
   // and that flag is sent by a later launch on this stream, i.e. after this kernel has ended.
 }
 
+// ---------------------------------------------------------------------------
+// NVLS variant (--comm_impl=nvls): the same two-shot all-reduce + update, with the reduction
+// and the broadcast done by the NVSwitch. The source arena and the landing buffer are bound to
+// a multicast object (parallel/comm.py, torch symmetric memory); one
+// multimem.ld_reduce on the multicast address returns the sum over all ranks' copies of that
+// address (added inside the switch), one multimem.st writes every rank's copy. Per bucket of
+// S bytes each GPU's NVLink port carries about S in and S out (S/N reduced shard in, the
+// other ranks' broadcasts in, its own copies read out by the switch, S/N broadcast out) -
+// half of the pull kernel's 2 (N-1)/N S per direction - and the N loads + N stores per element
+// become one instruction each. The flag protocol is the one of allreduce_update_kernel.
+// The switch's summation order is fixed per address but is not the rank order of the pull
+// kernel, so results match it to rounding, not bit for bit; replicas stay bit-identical to
+// each other because every element is reduced once and broadcast.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float4 multimem_ld_reduce_add4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ float multimem_ld_reduce_add1(const float* mc) {
+  float v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st4(float* mc, const float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc),
+               "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void multimem_st1(float* mc, const float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
+
+// c.src is unused (the switch reads every rank's copy through src_mc); c.reduced[c.rank] is
+// this rank's landing buffer, reduced_mc its multicast alias.
+template <int MODE>
+__global__ void __launch_bounds__(512)
+    allreduce_update_nvls_kernel(PeerCtx c, const float* __restrict__ src_mc,
+                                 float* __restrict__ reduced_mc, long long offset,
+                                 long long count, uint32_t seq, float* __restrict__ w,
+                                 const float* __restrict__ g_local, float* __restrict__ m,
+                                 float* __restrict__ v, __half* __restrict__ w16, HyperParams h,
+                                 const float* __restrict__ dyn,
+                                 const int* __restrict__ skip_flag, float sma_alpha,
+                                 int reduce_only) {
+  resolve_dyn(h, dyn);
+  const int n = c.nranks;
+  // --- announce: my source data for [offset, offset+count) is final ---
+  if (blockIdx.x == 0 && threadIdx.x < n)
+    st_release_sys(c.flags[threadIdx.x] + FLAG_READY * kMaxRanks + c.rank, seq);
+  wait_flags(c, FLAG_READY, seq);
+
+  // --- phase 1: in-switch reduction of my shard, in-switch broadcast of the result ---
+  const long long per = ((count + n - 1) / n + 3) & ~3ll;
+  const long long s_begin = offset + per * c.rank;
+  long long s_end = s_begin + per;
+  if (s_end > offset + count) s_end = offset + count;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  const float inv_n = 1.f / static_cast<float>(n);
+  constexpr int kU = 4;  // reductions in flight per thread before the first store
+  for (long long i0 = s_begin + tid * 4; i0 < s_end; i0 += nthreads * 4 * kU) {
+    float4 acc[kU];
+    bool ok[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * nthreads * 4;
+      ok[u] = i + 4 <= s_end;
+      if (ok[u]) acc[u] = multimem_ld_reduce_add4(src_mc + i);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * nthreads * 4;
+      if (ok[u]) {
+        if (MODE == 1) {
+          acc[u].x *= inv_n; acc[u].y *= inv_n; acc[u].z *= inv_n; acc[u].w *= inv_n;
+        }
+        multimem_st4(reduced_mc + i, acc[u]);
+      } else if (i < s_end) {
+        for (long long j = i; j < s_end; ++j) {  // at most 3 elements, end of the last shard
+          float a1 = multimem_ld_reduce_add1(src_mc + j);
+          if (MODE == 1) a1 *= inv_n;
+          multimem_st1(reduced_mc + j, a1);
+        }
+      }
+    }
+  }
+  grid_arrive_and_signal(c, FLAG_REDUCED, seq, 0);
+  wait_flags(c, FLAG_REDUCED, seq);
+
+  // --- phase 2: every rank applies the identical update to its full replica ---
+  const bool skip = (skip_flag != nullptr && *skip_flag != 0) || reduce_only;
+  if (!skip) {
+    const float* red = c.reduced[c.rank];
+    const long long end = offset + count;
+    const long long end4 = offset + (count & ~3ll);
+    for (long long i = offset + tid * 4; i < end4; i += nthreads * 4) {
+      const float4 r4 = *reinterpret_cast<const float4*>(red + i);
+      if (MODE == 0) {
+        apply_update4(h, w, r4, m, v, w16, i, nullptr, 0.f);
+      } else {
+        apply_update4(h, w, *reinterpret_cast<const float4*>(g_local + i), m, v, w16, i, &r4,
+                      sma_alpha);
+      }
+    }
+    for (long long i = end4 + tid; i < end; i += nthreads) {
+      float nw;
+      if (MODE == 0) {
+        nw = apply_update(h, w[i], red[i], m, v, i);
+      } else {
+        const float blended = (1.f - sma_alpha) * w[i] + sma_alpha * red[i];
+        nw = apply_update(h, blended, g_local[i], m, v, i);
+      }
+      w[i] = nw;
+      if (w16 != nullptr) w16[i] = __float2half_rn(nw);
+    }
+  }
+}
+
 // Pull `count` floats at `offset` from rank `root`'s arena into mine (+ fp16 shadow).
 __global__ void __launch_bounds__(512)
     broadcast_pull_kernel(PeerCtx c, int root, long long offset, long long count, uint32_t seq,
@@ -570,6 +693,45 @@ extern "C" int kfb_allreduce_update(int mode, int rank, int nranks, void* const*
                                                        (__half*)w16, make_hyper(hp), dyn,
                                                        skip_flag, sma_alpha, mode == 2 ? 1 : 0,
                                                        nullptr, 0);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// NVLS form of kfb_allreduce_update: `src_mc` / `reduced_mc` are the multicast addresses of
+// the source arena and of the landing buffer (element 0 of the arena, like the entries of
+// src / reduced), `reduced_local` this rank's own landing buffer.
+extern "C" int kfb_allreduce_update_nvls(int mode, int rank, int nranks, const void* src_mc,
+                                         void* reduced_mc, void* reduced_local,
+                                         void* const* flags, long long offset, long long count,
+                                         unsigned seq, float* w, const float* g_local, float* m,
+                                         float* v, void* w16, const kfb_hyper* hp,
+                                         const float* dyn, const int* skip_flag,
+                                         float sma_alpha, int blocks, void* stream) {
+  KFB_REQUIRE(hp != nullptr, "allreduce_update_nvls: null hyper");
+  KFB_REQUIRE(src_mc != nullptr && reduced_mc != nullptr && reduced_local != nullptr,
+              "allreduce_update_nvls: multicast addresses are required (is the allocation bound "
+              "to a multicast object?)");
+  KFB_REQUIRE(offset % 4 == 0, "allreduce_update_nvls: offset must be a multiple of 4 floats");
+  KFB_REQUIRE(((uintptr_t)src_mc | (uintptr_t)reduced_mc | (uintptr_t)reduced_local) % 16 == 0,
+              "allreduce_update_nvls: arenas must be 16-byte aligned");
+  PeerCtx c;
+  if (fill_peer_ctx(&c, rank, nranks, flags, nullptr, flags)) return 2;
+  for (int r = 0; r < kMaxRanks; ++r) c.src[r] = nullptr;
+  c.reduced[rank] = (float*)reduced_local;
+  if (blocks <= 0) {
+    // the switch does the adds: fewer CTAs than the pull kernel saturate the links
+    blocks = count >= (4ll << 20) ? 64 : (count >= (1ll << 20) ? 48 : 24);
+  }
+  if (blocks > 148) blocks = 148;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == 1)
+    allreduce_update_nvls_kernel<1><<<blocks, 512, 0, st>>>(
+        c, (const float*)src_mc, (float*)reduced_mc, offset, count, seq, w, g_local, m, v,
+        (__half*)w16, make_hyper(hp), dyn, skip_flag, sma_alpha, 0);
+  else
+    allreduce_update_nvls_kernel<0><<<blocks, 512, 0, st>>>(
+        c, (const float*)src_mc, (float*)reduced_mc, offset, count, seq, w, g_local, m, v,
+        (__half*)w16, make_hyper(hp), dyn, skip_flag, sma_alpha, mode == 2 ? 1 : 0);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

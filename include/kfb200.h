@@ -217,6 +217,18 @@ int kfb_allreduce_update(int mode, int rank, int nranks, void* const* src, void*
                          float* w, const float* g_local, float* m, float* v, void* w16,
                          const kfb_hyper* hp, const float* dyn, const int* skip_flag,
                          float sma_alpha, int blocks, void* stream);
+/* NVLS form of kfb_allreduce_update (--comm_impl=nvls; W10 "nvls" of SURVEY.md 8, the
+ * in-switch counterpart of the NcclAllReduce path T/allreduce.py:280-324): the reduction is one
+ * multimem.ld_reduce and the broadcast one multimem.st on the multicast aliases `src_mc` /
+ * `reduced_mc` of the source arena and of the landing buffer (both must be bound to a multicast
+ * object on every rank; parallel/comm.py does it through torch symmetric memory);
+ * `reduced_local` is this rank's own landing buffer. Same modes, flags and seq rules. */
+int kfb_allreduce_update_nvls(int mode, int rank, int nranks, const void* src_mc,
+                              void* reduced_mc, void* reduced_local, void* const* flags,
+                              long long offset, long long count, unsigned seq, float* w,
+                              const float* g_local, float* m, float* v, void* w16,
+                              const kfb_hyper* hp, const float* dyn, const int* skip_flag,
+                              float sma_alpha, int blocks, void* stream);
 /* Owner side of the fused weight-gradient reduce-scatter (see kfb_push_target): sums the nranks
  * local staging slots of this rank's shard of [offset, offset+count), pushes the sum to every
  * rank and applies the optimizer - kfb_allreduce_update with local instead of peer sources. */

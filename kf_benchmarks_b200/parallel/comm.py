@@ -9,6 +9,10 @@ the plumbing only - and three interchangeable communicators:
   page are cudaMalloc'ed by the native runtime, exported over CUDA IPC and mapped by every
   peer, so the fused kernels of ``csrc/optim_comm.cu`` read and write peer HBM directly
   over NVLink 5 / NVSwitch.
+  With ``nvls=True`` (``--comm_impl=nvls``) the same allocations come from torch's symmetric
+  memory instead (VMM allocations bound to an NVSwitch multicast object): peers are still
+  addressable one by one, and ``mc_ptr`` gives the multicast alias the ``multimem`` kernels
+  reduce / broadcast through.
 * ``TorchDistComm`` - ``torch.distributed`` all-reduce (NCCL on GPUs, gloo on CPU ranks)
   followed by a separate update: the "only calls NCCL" baseline and the CPU-replica path.
 * ``SingleComm`` - world size 1.
@@ -122,7 +126,7 @@ class P2PComm(Comm):
     """
     kind = "p2p"
 
-    def __init__(self, device, bootstrap_backend: str = "gloo"):
+    def __init__(self, device, bootstrap_backend: str = "gloo", nvls: bool = False):
         import torch.distributed as dist
         init_process_group(bootstrap_backend)
         self.dist = dist
@@ -135,6 +139,11 @@ class P2PComm(Comm):
         self.lib = native.load()
         self._allocs = []  # (local_ptr, nbytes, [peer ptrs])
         self._by_ptr = {}
+        self.nvls = bool(nvls)
+        self._mc_by_ptr = {}   # local pointer -> multicast alias (nvls only)
+        self._symm_keep = []   # torch symmetric-memory tensors and handles (nvls only)
+        if self.nvls:
+            self.kind = "nvls"
         self.seq = 0
         flag_bytes = int(self.lib.kfb_flag_page_bytes())
         self.flags = self.symm_alloc(flag_bytes // 4, torch.int32)
@@ -143,7 +152,41 @@ class P2PComm(Comm):
         self.barrier()
 
     # -- symmetric allocation -------------------------------------------------------
+    def _symm_alloc_multicast(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        """Symmetric allocation bound to a multicast object (torch symmetric memory does the
+        cuMemCreate / cuMulticastBindMem / handle exchange; the kernels are ours)."""
+        import torch.distributed._symmetric_memory as symm_mem
+        esize = torch.empty((), dtype=dtype).element_size()
+        padded = (max(int(numel) * esize, 256) + 15) // 16 * 16 // esize
+        t = symm_mem.empty(padded, dtype=dtype, device=self.device)
+        t.zero_()
+        torch.cuda.synchronize(self.device)
+        hdl = symm_mem.rendezvous(t, self.dist.group.WORLD)
+        base = [int(a) for a in hdl.buffer_ptrs]
+        if len(base) != self.size:
+            raise native.KfbError("symmetric memory rendezvous returned %d peers, expected %d"
+                                  % (len(base), self.size))
+        # the handle describes the allocation block; the tensor may start inside it
+        off = t.data_ptr() - base[self.rank]
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        if mc == 0:
+            raise native.KfbError(
+                "--comm_impl=nvls needs NVSwitch multicast (NVLS) support, which this "
+                "driver / fabric does not report; use --comm_impl=p2p")
+        peer_ptrs = [a + off for a in base]
+        self._by_ptr[t.data_ptr()] = peer_ptrs
+        self._mc_by_ptr[t.data_ptr()] = mc + off
+        self._symm_keep.append((t, hdl))
+        self.dist.barrier()   # every rank has zeroed and mapped before anyone writes
+        return t[:int(numel)] if padded != int(numel) else t
+
+    def mc_ptr(self, t: torch.Tensor) -> int:
+        """Multicast alias of the symmetric allocation `t` starts at (nvls only)."""
+        return self._mc_by_ptr[t.data_ptr()]
+
     def symm_alloc(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        if self.nvls:
+            return self._symm_alloc_multicast(numel, dtype)
         nbytes = max(int(numel) * torch.empty((), dtype=dtype).element_size(), 256)
         p = ctypes.c_void_p()
         native.check(self.lib.kfb_symm_alloc(ctypes.c_longlong(nbytes), ctypes.byref(p)),
@@ -221,6 +264,7 @@ class P2PComm(Comm):
                 if r != self.rank:
                     self.lib.kfb_ipc_close(ctypes.c_void_p(a))
         self._allocs = []
+        self._symm_keep = []
 
 
 def create_comm(params, device) -> Comm:
@@ -236,4 +280,4 @@ def create_comm(params, device) -> Comm:
         return TorchDistComm("nccl", dev)
     if impl == "gloo":
         raise ValueError("--comm_impl=gloo needs --device=cpu")
-    return P2PComm(dev)      # p2p and p2p_fused
+    return P2PComm(dev, nvls=impl == "nvls")      # p2p, p2p_fused, nvls

@@ -217,6 +217,7 @@ class UpdateEngine:
     def _setup_comm_buffers(self) -> None:
         c = self.comm
         self.reduced = None
+        self.nvls = False
         if isinstance(c, P2PComm) and self.algo != "none":
             st = self.store
             self.reduced = c.symm_alloc(self.total, torch.float32)
@@ -224,6 +225,12 @@ class UpdateEngine:
             self._w_ptrs = c.ptr_array(st.w32)
             self._red_ptrs = c.ptr_array(self.reduced)
             self._flag_ptrs = c.ptr_array(c.flags)
+            # --comm_impl=nvls: multicast aliases of the same arenas (in-switch reduce / bcast)
+            self.nvls = bool(getattr(c, "nvls", False))
+            if self.nvls:
+                self._grad_mc = ctypes.c_void_p(c.mc_ptr(st.grad))
+                self._w_mc = ctypes.c_void_p(c.mc_ptr(st.w32))
+                self._red_mc = ctypes.c_void_p(c.mc_ptr(self.reduced))
             self.ready_event = torch.cuda.Event()
             self.done_event = torch.cuda.Event()
             if self.algo in ("pair", "ada"):
@@ -355,11 +362,7 @@ class UpdateEngine:
                             None, self._s())
             self.ready_event.record(torch.cuda.current_stream(self.device))
             c.comm_stream.wait_event(self.ready_event)
-            native.call("allreduce_update", i32(2), i32(c.rank), i32(c.size), self._grad_ptrs,
-                        self._red_ptrs, self._flag_ptrs, i64(0), i64(self.total),
-                        ctypes.c_uint(c.next_seq()), ptr(st.w32), ptr(st.grad), ptr(self.m),
-                        ptr(self.v), ptr(st.w16), ctypes.byref(self._h), None, None, f32(0.0),
-                        i32(0), self._s(c.comm_stream))
+            self._allreduce_call(2, 0, self.total, self._h, None, c.comm_stream)
             self.done_event.record(c.comm_stream)
             self._relaxed_pending = True
         else:
@@ -401,7 +404,6 @@ class UpdateEngine:
             c.comm_stream.wait_event(self.ready_event)
             stream = c.comm_stream
         mode = 1 if algo == "sma" else 0
-        src = self._w_ptrs if mode == 1 else self._grad_ptrs
         h = self._h
         if self.fused_push and self._push_targets:
             per, ranges_dev, nranges, longest = self._bucket_push[self.buckets.index(bucket)]
@@ -414,11 +416,24 @@ class UpdateEngine:
                         ptr(st.w32), ptr(self.m), ptr(self.v), ptr(st.w16), ctypes.byref(h),
                         None, None, ptr(self.stage), i64(self.total), i32(0), self._s(stream))
             return
-        native.call("allreduce_update", i32(mode), i32(c.rank), i32(c.size), src, self._red_ptrs,
-                    self._flag_ptrs, i64(lo), i64(hi - lo), ctypes.c_uint(c.next_seq()),
-                    ptr(st.w32), ptr(st.grad), ptr(self.m), ptr(self.v), ptr(st.w16),
-                    ctypes.byref(h), None, ptr(self.skip_flag) if self.auto_loss_scale else None,
-                    f32(self.params.sma_alpha), i32(0), self._s(stream))
+        self._allreduce_call(mode, lo, hi - lo, h,
+                             ptr(self.skip_flag) if self.auto_loss_scale else None, stream)
+
+    def _allreduce_call(self, mode: int, lo: int, count: int, h, skip_flag, stream) -> None:
+        """One fused all-reduce(+update) over [lo, lo+count): mode 0 gradients + optimizer,
+        1 SMA (source = weights), 2 reduce only. Pull kernel, or its NVLS form."""
+        st, c = self.store, self.comm
+        tail = (i64(lo), i64(count), ctypes.c_uint(c.next_seq()), ptr(st.w32), ptr(st.grad),
+                ptr(self.m), ptr(self.v), ptr(st.w16), ctypes.byref(h), None, skip_flag,
+                f32(self.params.sma_alpha if mode == 1 else 0.0), i32(0), self._s(stream))
+        if self.nvls:
+            native.call("allreduce_update_nvls", i32(mode), i32(c.rank), i32(c.size),
+                        self._w_mc if mode == 1 else self._grad_mc, self._red_mc,
+                        ptr(self.reduced), self._flag_ptrs, *tail)
+        else:
+            native.call("allreduce_update", i32(mode), i32(c.rank), i32(c.size),
+                        self._w_ptrs if mode == 1 else self._grad_ptrs, self._red_ptrs,
+                        self._flag_ptrs, *tail)
 
     def _pair_update(self) -> None:
         c, st = self.comm, self.store

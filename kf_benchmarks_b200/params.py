@@ -200,10 +200,12 @@ _D.DEFINE_enum("checkpoint_format", "npz", ("npz", "tf"),
                "npz: one .npz per checkpoint keyed by the reference's TF variable names. tf: a "
                "TensorFlow V2 checkpoint bundle (.index + .data) the reference can restore. "
                "Both are read back transparently.")
-_D.DEFINE_enum("comm_impl", "p2p", ("p2p", "p2p_fused", "nccl", "gloo"),
+_D.DEFINE_enum("comm_impl", "p2p", ("p2p", "p2p_fused", "nvls", "nccl", "gloo"),
                "p2p: fused NVLink all-reduce+update kernels (the product). p2p_fused: in "
                "addition the weight-gradient GEMMs scatter their tiles to the owning ranks from "
-               "their own epilogue (GEMM + reduce-scatter in one kernel). nccl: "
+               "their own epilogue (GEMM + reduce-scatter in one kernel). nvls: the p2p kernels with "
+               "the reduction and the broadcast done inside the NVSwitch (multimem.ld_reduce / "
+               "multimem.st on multicast-bound arenas). nccl: "
                "torch.distributed NCCL + separate update (comparison baseline). gloo: CPU ranks.")
 _D.DEFINE_float("sma_alpha", 0.1, "Blend factor of SynchronousAveraging.")
 _D.DEFINE_integer("bucket_bytes", 8 << 20, "Target gradient bucket size for overlap.")

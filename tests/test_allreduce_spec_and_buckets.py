@@ -92,3 +92,48 @@ def test_fused_push_buckets_cut_only_between_variables():
 def ctypes_sizeof(obj):
     import ctypes
     return ctypes.sizeof(obj)
+
+
+def test_nvls_symmetric_allocation_bookkeeping(monkeypatch):
+    """--comm_impl=nvls: peer pointers / multicast alias follow the tensor's offset inside the
+    symmetric block, and a fabric without multicast support is a loud error (torch's symmetric
+    memory and the device are faked; the kernels are covered by tools/nvls_check.py)."""
+    import types
+
+    import torch
+    import torch.distributed._symmetric_memory as symm_mem
+    from kf_benchmarks_b200.ops import native
+    from kf_benchmarks_b200.parallel.comm import P2PComm
+
+    class FakeTensor:
+        def __init__(self, n):
+            self.n = n
+
+        def zero_(self):
+            return self
+
+        def data_ptr(self):
+            return 0x7000_0000_1000 + 0x40          # 64 bytes into the block
+
+        def __getitem__(self, sl):
+            return self
+
+    class FakeHandle:
+        buffer_ptrs = [0x7000_0000_1000, 0x7100_0000_0000]
+        multicast_ptr = 0x7F00_0000_0000
+
+    monkeypatch.setattr(symm_mem, "empty", lambda n, dtype, device: FakeTensor(n))
+    monkeypatch.setattr(symm_mem, "rendezvous", lambda t, group: FakeHandle())
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda dev=None: None)
+    fake_dist = types.SimpleNamespace(group=types.SimpleNamespace(WORLD=object()),
+                                      barrier=lambda: None)
+    comm = types.SimpleNamespace(rank=0, size=2, device=torch.device("cpu"), dist=fake_dist,
+                                 _by_ptr={}, _mc_by_ptr={}, _symm_keep=[])
+    t = P2PComm._symm_alloc_multicast(comm, 1000, torch.float32)
+    assert comm._by_ptr[t.data_ptr()] == [0x7000_0000_1040, 0x7100_0000_0040]
+    assert comm._mc_by_ptr[t.data_ptr()] == 0x7F00_0000_0040
+    assert P2PComm.mc_ptr(comm, t) == 0x7F00_0000_0040
+
+    FakeHandle.multicast_ptr = 0
+    with pytest.raises(native.KfbError, match="NVLS"):
+        P2PComm._symm_alloc_multicast(comm, 1000, torch.float32)

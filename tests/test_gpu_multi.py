@@ -99,3 +99,38 @@ def test_fused_wgrad_reduce_scatter_is_bit_identical_to_the_pull_path(tmp_path, 
         assert np.isfinite(outs[impl][0]).all()
         assert np.array_equal(outs[impl][0], outs[impl][1])
     assert np.array_equal(outs["p2p"][0], outs["p2p_fused"][0])
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+@pytest.mark.skipif(os.environ.get("KFB_TEST_NVLS") != "1",
+                    reason="--comm_impl=nvls was written without GPU time left in the round; set "
+                           "KFB_TEST_NVLS=1 to run it (tools/nvls_check.py does the same by hand)")
+@pytest.mark.parametrize("mode", [["--variable_update=replicated", "--num_gpus=2"],
+                                  ["--variable_update=kungfu", "--kungfu_option=sma"]])
+def test_nvls_all_reduce_matches_the_pull_kernels(tmp_path, mode):
+    """--comm_impl=nvls (multimem.ld_reduce / multimem.st on multicast-bound arenas): replicas
+    bit-identical to each other, variables equal to the pull path up to summation order."""
+    import json
+    import numpy as np
+    outs = {}
+    kung = "kungfu" in mode[0]
+    for impl in ("p2p", "nvls"):
+        d = tmp_path / impl
+        d.mkdir()
+        kw = dict(model="resnet20", data_name="cifar10", batch_size=32, use_fp16=True,
+                  optimizer="momentum", init_learning_rate=0.05, num_batches=6,
+                  num_warmup_batches=0, comm_impl=impl,
+                  variable_update="kungfu" if kung else "replicated",
+                  num_gpus=1 if kung else 2)
+        if kung:
+            kw["kungfu_option"] = "sma"
+        res = _launch(2, [os.path.join(ROOT, "tests", "helpers", "rank_worker.py"), json.dumps(kw),
+                          str(d)])
+        assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+        outs[impl] = [np.load(str(d / ("rank%d.npz" % r)))["w"] for r in range(2)]
+        assert np.isfinite(outs[impl][0]).all()
+        if not kung:
+            assert np.array_equal(outs[impl][0], outs[impl][1])
+    a, b = outs["p2p"][0], outs["nvls"][0]
+    cos = float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b)))
+    assert cos > 0.9999 and np.abs(a - b).max() < 5e-2

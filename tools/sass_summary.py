@@ -10,7 +10,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "kf_benchmarks_b200", "_lib", "libkfb200.so")
 KEYS = ("UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "UTCBAR",
-        "UTCATOMSWS", "SYNCS", "HMMA", "MEMBAR", "LDG", "STG", "LDS", "STS", "ATOM", "RED",
+        "UTCATOMSWS", "SYNCS", "HMMA", "MEMBAR", "LDGMC", "LDG", "STG", "LDS", "STS", "ATOM", "RED",
         "LD.E", "ST.E")
 
 
@@ -24,14 +24,14 @@ def main():
             fn = m.group(1)
             counts[fn] = collections.Counter()
             continue
-        m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
+        m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Za-z0-9_.]+)", line)
         if m and fn:
             op = m.group(1)
             counts[fn]["_total"] += 1
             for k in KEYS:
                 if op.startswith(k):
                     # keep the informative suffixes (IM2COL, SYS scope, vector width)
-                    keep = op if k in ("UTMALDG", "MEMBAR", "LDTM") else k
+                    keep = op if k in ("UTMALDG", "MEMBAR", "LDTM", "LDGMC") else k
                     counts[fn][keep] += 1
                     break
     out = ["# SASS evidence for libkfb200.so (cuobjdump -sass, sm_100a)", "",
@@ -53,6 +53,13 @@ def main():
               if not any(k.startswith(("UTC", "UTMA", "LDTM")) for k in c)]
     out.append("## other kernels (CUDA-core, bandwidth-bound): %d" % len(others))
     out.append("  " + ", ".join(re.sub(r"^_ZN3kfb\d+", "", f)[:40] for f in others))
+    out.append("")
+    out.append("## NVLS all-reduce (--comm_impl=nvls): multimem.ld_reduce = LDGMC.*.ADD, "
+               "multimem.st = STG.E.*.STRONG.SYS on the multicast alias")
+    for fn, c in counts.items():
+        mc = {k: v for k, v in c.items() if k.startswith("LDGMC")}
+        if mc:
+            out.append("  %s: %s" % (fn, ", ".join("%s x%d" % kv for kv in sorted(mc.items()))))
     hm = sum(c["HMMA"] for c in counts.values())
     out.append("")
     out.append("HMMA (legacy tensor path) instructions in the whole library: %d" % hm)
