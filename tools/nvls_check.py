@@ -44,6 +44,14 @@ def main() -> int:
     print("NVLS_CHECK max abs diff vs p2p %.3e, cosine %.8f" %
           (float(np.abs(a - b).max()),
            float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b)))))
+    env_nvls = dict(os.environ, KFB_P2P_NVLS="1")
+    os.environ.update(env_nvls)       # _launch copies os.environ
+    r = _launch(n, [os.path.join(ROOT, "tools", "p2p_check.py")])
+    os.environ.pop("KFB_P2P_NVLS", None)
+    print("p2p_check under NVLS: rc", r.returncode,
+          "ALL PASS" if "P2P_CHECK ALL PASS" in r.stdout else "FAILED")
+    if r.returncode != 0:
+        print(r.stdout[-3000:], r.stderr[-2000:])
     for impl in ("p2p", "nvls", "nccl"):
         r = _launch(n, ["-m", "kf_benchmarks_b200.all_reduce_benchmark", "--model=" + model,
                         "--variable_update=replicated", "--num_gpus=%d" % n, "--use_fp16",

@@ -37,7 +37,9 @@ def main():
     world = int(os.environ["WORLD_SIZE"])
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
     torch.cuda.set_device(dev)
-    comm = P2PComm(dev)
+    # KFB_P2P_NVLS=1: same checks through the NVLS (multimem) form of the all-reduce kernel
+    nvls = os.environ.get("KFB_P2P_NVLS") == "1"
+    comm = P2PComm(dev, nvls=nvls)
     ok = True
     n = int(os.environ.get("KFB_P2P_N", "3000064"))
     grad = comm.symm_alloc(n, torch.float32)
@@ -48,6 +50,15 @@ def main():
     s = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     gp, wp, rp, fp = (comm.ptr_array(grad), comm.ptr_array(w), comm.ptr_array(red),
                       comm.ptr_array(comm.flags))
+
+    def ar(mode, src, *tail):
+        if nvls:
+            native.call("allreduce_update_nvls", i32(mode), i32(rank), i32(world),
+                        ctypes.c_void_p(comm.mc_ptr(src)), ctypes.c_void_p(comm.mc_ptr(red)),
+                        ptr(red), fp, *tail)
+        else:
+            native.call("allreduce_update", i32(mode), i32(rank), i32(world),
+                        gp if src is grad else wp, rp, fp, *tail)
 
     def check(name, got, want, tol=1e-5):
         nonlocal ok
@@ -66,7 +77,7 @@ def main():
         comm.barrier()
         h = make_hyper(1, scale=1.0 / 128)
         for lo, hi in [(0, 1_000_064), (1_000_064, 2_500_096), (2_500_096, n)] if n == 3000064 else [(0, n)]:
-            native.call("allreduce_update", i32(0), i32(rank), i32(world), gp, rp, fp, i64(lo),
+            ar(0, grad, i64(lo),
                         i64(hi - lo), ctypes.c_uint(comm.next_seq()), ptr(w), ptr(grad), ptr(m),
                         None, ptr(w16), ctypes.byref(h), None, None, f32(0.0), i32(0), s)
         torch.cuda.synchronize()
@@ -80,7 +91,7 @@ def main():
     grad.copy_(rank_data(rank, n, 21))
     comm.barrier()
     h = make_hyper(0, scale=1.0, wd=0.0)
-    native.call("allreduce_update", i32(1), i32(rank), i32(world), wp, rp, fp, i64(0), i64(n),
+    ar(1, w, i64(0), i64(n),
                 ctypes.c_uint(comm.next_seq()), ptr(w), ptr(grad), None, None, ptr(w16),
                 ctypes.byref(h), None, None, f32(0.1), i32(0), s)
     torch.cuda.synchronize()
@@ -138,7 +149,7 @@ def main():
         comm.barrier()
         e0.record()
         for _ in range(reps):
-            native.call("allreduce_update", i32(0), i32(rank), i32(world), gp, rp, fp, i64(0),
+            ar(0, grad, i64(0),
                         i64(n), ctypes.c_uint(comm.next_seq()), ptr(w), ptr(grad), ptr(m), None,
                         ptr(w16), ctypes.byref(h), None, None, f32(0.0), i32(blocks), s)
         e1.record()
@@ -162,7 +173,7 @@ def main():
     for it in range(iters):
         cuts = sorted({0, n} | {rng.randrange(0, n // 128) * 128 for _ in range(rng.randint(0, 4))})
         for lo, hi in zip(cuts[:-1], cuts[1:]):
-            native.call("allreduce_update", i32(0), i32(rank), i32(world), gp, rp, fp, i64(lo),
+            ar(0, grad, i64(lo),
                         i64(hi - lo), ctypes.c_uint(comm.next_seq()), ptr(w), ptr(grad), None,
                         None, ptr(w16), ctypes.byref(h), None, None, f32(0.0),
                         i32(rng.choice([0, 8, 33, 148])), s)
