@@ -1,0 +1,177 @@
+#!/usr/bin/env python
+"""Analytic roofline of one training step, per kernel class, against the measured launch list.
+
+For every node of the model graph (built on the CPU, no GPU needed) it counts the FLOPs of the
+forward / dgrad / wgrad GEMMs and the HBM bytes each kernel class *has* to move with the pass
+structure this framework uses (fp16 NHWC activations, fp32 weight gradients, two-pass batch norm
+forward and backward), turns both into a time at the measured peaks of MEASURED_PEAKS.json
+(roofline = max(FLOPs / tensor peak, bytes / copy bandwidth)) and sets that against the device
+time ncu measured for the same class (profiles/resnet50_bs256_launches_*.txt, written by
+tools/summarize_launches.py). SURVEY.md 8 asks for the achieved fraction of the roof per row.
+
+usage: python tools/roofline_model.py [--model resnet50] [--batch_size 256]
+                                      [--launches profiles/resnet50_bs256_launches_r1e.txt]
+"""
+import argparse
+import json
+import os
+import re
+import sys
+from collections import defaultdict
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def peaks():
+    with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+        d = json.load(f)
+    return float(d["hbm_gbs"]) * 1e9, float(d["bf16_tflops_sustained"]) * 1e12
+
+
+def numel(shape):
+    n = 1
+    for s in shape:
+        n *= s
+    return n
+
+
+class _Costs(defaultdict):
+    """class -> [flops, bytes, roof seconds]; the roof is summed kernel by kernel (a class that
+    mixes tensor-bound and HBM-bound layers is bounded by the sum of the per-layer maxima)."""
+
+    def __init__(self, bw, fl):
+        super().__init__(lambda: [0.0, 0.0, 0.0])
+        self.bw, self.fl = bw, fl
+
+    def add(self, cls, flops, nbytes):
+        e = self[cls]
+        e[0] += flops
+        e[1] += nbytes
+        e[2] += max(flops / self.fl, nbytes / self.bw)
+
+
+def model_costs(graph, bw, fl):
+    """Costs of one training step (forward + backward) per kernel class."""
+    c = _Costs(bw, fl)
+    first = graph.nodes[0]
+    for n in graph.nodes:
+        x = numel(n.inputs[0].shape)
+        y = numel(n.output.shape)
+        if n.op == "conv":
+            k = n.attrs["kh"] * n.attrs["kw"] * n.inputs[0].shape[-1]
+            w = k * n.output.shape[-1]
+            macs = (y // n.output.shape[-1]) * n.output.shape[-1] * k
+            c.add("conv fprop (W1)", 2.0 * macs, 2 * x + 2 * w + 2 * y)
+            if n is not first:                       # no input gradient for the image
+                c.add("conv dgrad (W2)", 2.0 * macs, 2 * y + 2 * w + 2 * x)
+            c.add("conv wgrad (W3)", 2.0 * macs, 2 * x + 2 * y + 4 * w)
+        elif n.op == "bn":
+            res = len(n.inputs) > 1
+            # forward: statistics pass reads x; apply pass reads x (+ residual), writes y
+            c.add("BN fwd statistics (W4/W5)", 0, 2 * x)
+            c.add("BN fwd apply+ReLU+add (W5)", 0, 2 * x * (3 if res else 2))
+            # backward: reduce pass reads dy, x; apply pass reads dy, x, writes dx (+ d residual)
+            c.add("BN bwd reduce (W5)", 0, 2 * x * 2)
+            c.add("BN bwd apply (W5)", 0, 2 * x * (4 if res else 3))
+        elif n.op == "pool":
+            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y) + 2 * (y + x))
+        elif n.op == "spatial_mean":
+            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y) * 2)
+        elif n.op == "affine":
+            k, m = n.inputs[0].shape[-1], n.output.shape[-1]
+            rows = x // k
+            for cls in ("conv fprop (W1)", "conv dgrad (W2)", "conv wgrad (W3)"):
+                c.add(cls, 2.0 * rows * k * m, 2 * x + 2 * k * m + 4 * y)
+    ntrain = sum(p.numel for p in graph.params.values() if p.trainable)
+    # fused optimizer: read g, w, m (fp32), write w, m (fp32) and the fp16 shadow
+    c.add("optimizer / all-reduce epilogue (W10/W11)", 0, ntrain * (4 * 5 + 2))
+    return c
+
+
+CLASS_OF = [
+    (r"gemm_tcgen05_kernel<\d+, 0,", "conv fprop (W1)"),
+    (r"gemm_tcgen05_kernel<\d+, 2,", "conv fprop (W1)"),
+    (r"im2col_small_c", "conv fprop (W1)"),
+    (r"gemm_tcgen05_kernel<\d+, 3,", "conv dgrad (W2)"),
+    (r"gemm_tcgen05_kernel<\d+, 5,", "conv dgrad (W2)"),
+    (r"gemm_tcgen05_kernel<\d+, [14],", "conv wgrad (W3)"),
+    (r"splitk_reduce", "conv wgrad (W3)"),
+    (r"channel_reduce_kernel<0>|bn_finalize", "BN fwd statistics (W4/W5)"),
+    (r"bn_apply_kernel", "BN fwd apply+ReLU+add (W5)"),
+    (r"channel_reduce_kernel<1>|bn_bwd_finalize", "BN bwd reduce (W5)"),
+    (r"bn_bwd_apply", "BN bwd apply (W5)"),
+    (r"pool_|spatial_mean", "pool fwd+bwd (W6)"),
+    (r"optimizer_step|allreduce_update", "optimizer / all-reduce epilogue (W10/W11)"),
+]
+
+
+def measured(path):
+    out = defaultdict(float)
+    other = 0.0
+    with open(path) as f:
+        for ln in f:
+            m = re.match(r"\s+([\d.]+)\s+[\d.]+%\s+\d+\s+[\d.]+\s+[\d.]+\s+[\d.]+%\s+(.*)$", ln)
+            if not m:
+                continue
+            ms, name = float(m.group(1)), m.group(2)
+            for pat, cls in CLASS_OF:
+                if re.search(pat, name):
+                    out[cls] += ms
+                    break
+            else:
+                other += ms
+    return out, other
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="resnet50")
+    ap.add_argument("--batch_size", type=int, default=256)
+    ap.add_argument("--launches",
+                    default=os.path.join(ROOT, "profiles", "resnet50_bs256_launches_r1e.txt"))
+    ap.add_argument("--step_ms", type=float, default=None,
+                    help="free-running step time to set the total against")
+    args = ap.parse_args()
+    from kf_benchmarks_b200 import datasets, params as params_lib
+    from kf_benchmarks_b200.models import model_config
+    p = params_lib.make_params(model=args.model, batch_size=args.batch_size, use_fp16=True,
+                               data_format="NHWC")
+    ds = datasets.create_dataset(None, None)
+    model = model_config.get_model_config(args.model, ds, p)
+    model.set_batch_size(args.batch_size)
+    graph = model.build_graph(ds.num_classes, batch_size=args.batch_size)
+    bw, fl = peaks()
+    costs = model_costs(graph, bw, fl)
+    meas, other = measured(args.launches) if os.path.exists(args.launches) else ({}, 0.0)
+    print("# Roofline of one %s training step, batch %d (tools/roofline_model.py)" %
+          (args.model, args.batch_size))
+    print()
+    print("Peaks: HBM copy %.1f GB/s, dense 16-bit GEMM %.1f TFLOP/s sustained "
+          "(MEASURED_PEAKS.json). Roof = sum over kernels of max(FLOPs / peak, bytes / bandwidth) "
+          "with the bytes this pass structure must move; measured = ncu device time of the class (%s)." %
+          (bw / 1e9, fl / 1e12, os.path.relpath(args.launches, ROOT)))
+    print()
+    print("| class | GFLOP | GB accessed (HBM traffic if nothing stays in L2) | roof ms | bound | measured ms | achieved |")
+    print("|---|---|---|---|---|---|---|")
+    tot_roof = tot_meas = 0.0
+    for cls, (flops, nbytes, roof_s) in costs.items():
+        t_f, t_b = flops / fl * 1e3, nbytes / bw * 1e3
+        roof = roof_s * 1e3
+        m = meas.get(cls)
+        tot_roof += roof
+        tot_meas += m or 0.0
+        print("| %s | %.0f | %.2f | %.3f | %s | %s | %s |" %
+              (cls, flops / 1e9, nbytes / 1e9, roof, "tensor" if t_f > t_b else ("HBM" if flops == 0 or roof <= t_b * 1.001
+                                                           else "mixed"),
+               "%.3f" % m if m else "-", "%.0f %%" % (100 * roof / m) if m else "-"))
+    print("| **sum** | | | **%.2f** | | **%.2f** (+ %.2f other) | **%.0f %%** |" %
+          (tot_roof, tot_meas, other, 100 * tot_roof / max(tot_meas + other, 1e-9)))
+    if args.step_ms:
+        print()
+        print("Free-running step: %.2f ms -> %.0f %% of the summed roof." %
+              (args.step_ms, 100 * tot_roof / args.step_ms))
+
+
+if __name__ == "__main__":
+    main()
