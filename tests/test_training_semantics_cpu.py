@@ -414,3 +414,28 @@ def test_parameter_server_checkpoints_use_the_v_scope(tmp_path):
     assert torch.equal(rep.store.w32, ps.store.w32)        # nothing left to run: same variables
     arrays = ckpt.load_arrays(ckpt.latest_checkpoint(d)[0])
     assert "v0/cg/affine0/weights" in arrays
+
+
+@pytest.mark.parametrize("extra", [
+    dict(gradient_repacking=2),
+    dict(all_reduce_spec="xring"),
+    dict(all_reduce_spec="pscpu:2k:xring", agg_small_grads_max_bytes=1024,
+         agg_small_grads_max_group=10),
+    dict(all_reduce_spec="nccl", compact_gradient_transfer=False),
+    dict(hierarchical_copy=True, gradient_repacking=3),
+])
+def test_gradient_aggregation_matrix(extra, tmp_path):
+    """Counterpart of VariableMgrLocalReplicatedTest (T/benchmark_cnn_test.py:1368-1476): whatever
+    the packing / algorithm flags say about HOW gradients travel (repacking, small-tensor
+    aggregation, compact transfer, hierarchical copy, all_reduce_spec), the applied gradient of
+    every variable is the plain sum over replicas."""
+    kw = dict(BASE)
+    kw.update(variable_update="replicated", num_gpus=2, optimizer="sgd")
+    kw.update(extra)
+    results = _spawn(kw, 2, tmp_path)
+    sim = _Sim(dict(BASE, variable_update="replicated", num_gpus=2, optimizer="sgd"), 2)
+    for k in range(kw["num_batches"]):
+        sim.step(k)
+    for r in range(2):
+        assert np.allclose(results[r]["w"], sim.stores[r].w32.numpy(), rtol=2e-5, atol=2e-6)
+    assert np.array_equal(results[0]["w"], results[1]["w"])
