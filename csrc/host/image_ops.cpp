@@ -1,0 +1,302 @@
+// Host-side image transforms of the real-data input pipeline (plain C++17, no CUDA): crop +
+// resize + horizontal flip + colour jitter + normalisation + cast, one call per decoded image,
+// written straight into the caller's (pinned) batch buffer. Counterpart of the TensorFlow image
+// kernels the reference's preprocessing graph runs per example on the tf.data thread pool
+// (crop + resize_{bilinear,nearest_neighbor,bicubic,area}, flip, distort_color, normalise:
+// T/preprocessing.py:130-307, 653-737).
+//
+// The resize kernels follow the semantics the reference gets from TF1-style
+// tf.image.resize_* with align_corners=False: source coordinate = destination index *
+// (in_size / out_size), no half-pixel shift, no antialiasing.
+//
+// The call releases the GIL (ctypes), so a Python thread pool scales across cores: JPEG decode
+// (Pillow, also GIL-free) and this function are the two per-image costs.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#if defined(__F16C__)
+#include <immintrin.h>
+#endif
+
+extern "C" {
+typedef struct {
+  int ih, iw, src_stride;  // source: uint8 RGB, ih x iw, row stride in bytes
+  int top, left, ch, cw;   // crop rectangle in source pixels
+  int vh, vw;              // size the crop is resized to
+  int oy, ox, oh, ow;      // window of that resized image which is produced (eval centre crop)
+  int method;              // 0 bilinear, 1 nearest, 2 bicubic, 3 area
+  int flip;                // mirror the produced window horizontally
+  int distort_order;       // 0 none, 1 brightness-saturation-contrast, 2 brightness-contrast-sat.
+  float brightness;        // added (0..255 scale)
+  float saturation;        // factor around the per-pixel grey value
+  float contrast;          // factor around the per-channel image mean
+  float scale, bias;       // out = value * scale + bias
+  int out_f16;             // 0: float32 output, 1: IEEE binary16 output
+} kfb_image_op;
+}
+
+namespace {
+
+thread_local std::vector<float> g_plane;   // oh * ow * 3 floats
+thread_local char g_err[256];
+
+inline uint16_t to_half(float f) {
+#if defined(__F16C__)
+  return static_cast<uint16_t>(_cvtss_sh(f, _MM_FROUND_TO_NEAREST_INT));
+#else
+  uint32_t x;
+  std::memcpy(&x, &f, 4);
+  const uint32_t sign = (x >> 16) & 0x8000u;
+  const int32_t exp = static_cast<int32_t>((x >> 23) & 0xFF) - 127 + 15;
+  uint32_t man = x & 0x7FFFFFu;
+  if (((x >> 23) & 0xFF) == 0xFF) return static_cast<uint16_t>(sign | 0x7C00u | (man ? 0x200u : 0));
+  if (exp >= 31) return static_cast<uint16_t>(sign | 0x7C00u);
+  if (exp <= 0) {
+    if (exp < -10) return static_cast<uint16_t>(sign);
+    man |= 0x800000u;
+    const int shift = 14 - exp;
+    uint32_t h = man >> shift;
+    const uint32_t rem = man & ((1u << shift) - 1), half = 1u << (shift - 1);
+    if (rem > half || (rem == half && (h & 1))) ++h;
+    return static_cast<uint16_t>(sign | h);
+  }
+  uint32_t h = (static_cast<uint32_t>(exp) << 10) | (man >> 13);
+  const uint32_t rem = man & 0x1FFFu;
+  if (rem > 0x1000u || (rem == 0x1000u && (h & 1))) ++h;
+  return static_cast<uint16_t>(sign | h);
+#endif
+}
+
+struct Tap2 {
+  int i0, i1;
+  float w1;  // weight of i1; i0 gets 1 - w1
+};
+
+// Keys cubic convolution, A = -0.75, fraction quantised to 1/1024 like TF's coefficient table
+inline void cubic_weights(float frac, float w[4]) {
+  const float a = -0.75f;
+  const float x = std::lrint(frac * 1024.f) / 1024.f;
+  auto near = [a](float t) { return ((a + 2.f) * t - (a + 3.f)) * t * t + 1.f; };
+  auto far = [a](float t) { return ((a * t - 5.f * a) * t + 8.f * a) * t - 4.f * a; };
+  w[0] = far(x + 1.f);
+  w[1] = near(x);
+  w[2] = near(1.f - x);
+  w[3] = far(2.f - x);
+}
+
+inline const uint8_t* px(const uint8_t* src, const kfb_image_op& op, int y, int x) {
+  return src + static_cast<size_t>(op.top + y) * op.src_stride + static_cast<size_t>(op.left + x) * 3;
+}
+
+void resize_window(const uint8_t* src, const kfb_image_op& op, float* out) {
+  const float sy = static_cast<float>(op.ch) / op.vh, sx = static_cast<float>(op.cw) / op.vw;
+  const int oh = op.oh, ow = op.ow;
+  if (op.method == 1) {  // nearest
+    std::vector<int> xs(ow);
+    for (int x = 0; x < ow; ++x)
+      xs[x] = std::min(static_cast<int>(std::floor((op.ox + x) * sx)), op.cw - 1);
+    for (int y = 0; y < oh; ++y) {
+      const int iy = std::min(static_cast<int>(std::floor((op.oy + y) * sy)), op.ch - 1);
+      float* o = out + static_cast<size_t>(y) * ow * 3;
+      for (int x = 0; x < ow; ++x) {
+        const uint8_t* p = px(src, op, iy, xs[x]);
+        o[3 * x] = p[0];
+        o[3 * x + 1] = p[1];
+        o[3 * x + 2] = p[2];
+      }
+    }
+    return;
+  }
+  if (op.method == 0) {  // bilinear
+    std::vector<Tap2> xt(ow);
+    for (int x = 0; x < ow; ++x) {
+      const float in = (op.ox + x) * sx;
+      const int lo = std::min(static_cast<int>(std::floor(in)), op.cw - 1);
+      xt[x] = {lo, std::min(lo + 1, op.cw - 1), in - std::floor(in)};
+    }
+    for (int y = 0; y < oh; ++y) {
+      const float in = (op.oy + y) * sy;
+      const int y0 = std::min(static_cast<int>(std::floor(in)), op.ch - 1);
+      const int y1 = std::min(y0 + 1, op.ch - 1);
+      const float wy = in - std::floor(in);
+      float* o = out + static_cast<size_t>(y) * ow * 3;
+      for (int x = 0; x < ow; ++x) {
+        const Tap2& t = xt[x];
+        const uint8_t *a = px(src, op, y0, t.i0), *b = px(src, op, y0, t.i1);
+        const uint8_t *c = px(src, op, y1, t.i0), *d = px(src, op, y1, t.i1);
+        for (int k = 0; k < 3; ++k) {
+          const float top = a[k] + (b[k] - a[k]) * t.w1;
+          const float bot = c[k] + (d[k] - c[k]) * t.w1;
+          o[3 * x + k] = top + (bot - top) * wy;
+        }
+      }
+    }
+    return;
+  }
+  if (op.method == 2) {  // bicubic
+    struct Tap4 {
+      int i[4];
+      float w[4];
+    };
+    std::vector<Tap4> xt(ow);
+    for (int x = 0; x < ow; ++x) {
+      const float in = (op.ox + x) * sx;
+      const int base = static_cast<int>(std::floor(in));
+      cubic_weights(in - base, xt[x].w);
+      for (int k = 0; k < 4; ++k) xt[x].i[k] = std::min(std::max(base - 1 + k, 0), op.cw - 1);
+    }
+    for (int y = 0; y < oh; ++y) {
+      const float in = (op.oy + y) * sy;
+      const int base = static_cast<int>(std::floor(in));
+      float wy[4];
+      int iy[4];
+      cubic_weights(in - base, wy);
+      for (int k = 0; k < 4; ++k) iy[k] = std::min(std::max(base - 1 + k, 0), op.ch - 1);
+      float* o = out + static_cast<size_t>(y) * ow * 3;
+      for (int x = 0; x < ow; ++x) {
+        float acc[3] = {0.f, 0.f, 0.f};
+        for (int r = 0; r < 4; ++r) {
+          float row[3] = {0.f, 0.f, 0.f};
+          for (int c = 0; c < 4; ++c) {
+            const uint8_t* p = px(src, op, iy[r], xt[x].i[c]);
+            row[0] += p[0] * xt[x].w[c];
+            row[1] += p[1] * xt[x].w[c];
+            row[2] += p[2] * xt[x].w[c];
+          }
+          acc[0] += row[0] * wy[r];
+          acc[1] += row[1] * wy[r];
+          acc[2] += row[2] * wy[r];
+        }
+        o[3 * x] = acc[0];
+        o[3 * x + 1] = acc[1];
+        o[3 * x + 2] = acc[2];
+      }
+    }
+    return;
+  }
+  // area: average of the source box [o*s, (o+1)*s) with fractional edge weights
+  struct Span {
+    int begin, end;            // source indices [begin, end)
+    std::vector<float> w;
+  };
+  auto spans = [](int off, int n, float s) {
+    std::vector<Span> v(n);
+    for (int o = 0; o < n; ++o) {
+      const float a = (off + o) * s, b = (off + o + 1) * s;
+      Span& sp = v[o];
+      sp.begin = static_cast<int>(std::floor(a));
+      sp.end = static_cast<int>(std::ceil(b));
+      for (int i = sp.begin; i < sp.end; ++i)
+        sp.w.push_back(i < a ? (i + 1 > b ? b - a : i + 1 - a) : (i + 1 > b ? b - i : 1.f));
+    }
+    return v;
+  };
+  const std::vector<Span> ys = spans(op.oy, oh, sy), xs = spans(op.ox, ow, sx);
+  const float norm = 1.f / (sy * sx);
+  for (int y = 0; y < oh; ++y) {
+    float* o = out + static_cast<size_t>(y) * ow * 3;
+    for (int x = 0; x < ow; ++x) {
+      float acc[3] = {0.f, 0.f, 0.f};
+      for (int i = ys[y].begin; i < ys[y].end; ++i) {
+        const int iy = std::min(i, op.ch - 1);
+        const float wy = ys[y].w[i - ys[y].begin];
+        for (int j = xs[x].begin; j < xs[x].end; ++j) {
+          const uint8_t* p = px(src, op, iy, std::min(j, op.cw - 1));
+          const float w = wy * xs[x].w[j - xs[x].begin];
+          acc[0] += p[0] * w;
+          acc[1] += p[1] * w;
+          acc[2] += p[2] * w;
+        }
+      }
+      o[3 * x] = acc[0] * norm;
+      o[3 * x + 1] = acc[1] * norm;
+      o[3 * x + 2] = acc[2] * norm;
+    }
+  }
+}
+
+void distort(const kfb_image_op& op, float* img, size_t npix) {
+  auto brightness = [&] {
+    for (size_t i = 0; i < npix * 3; ++i) img[i] += op.brightness;
+  };
+  auto saturation = [&] {
+    for (size_t i = 0; i < npix; ++i) {
+      float* p = img + 3 * i;
+      const float g = (p[0] + p[1] + p[2]) * (1.f / 3.f);
+      for (int k = 0; k < 3; ++k) p[k] = g + (p[k] - g) * op.saturation;
+    }
+  };
+  auto contrast = [&] {
+    double m[3] = {0, 0, 0};
+    for (size_t i = 0; i < npix; ++i)
+      for (int k = 0; k < 3; ++k) m[k] += img[3 * i + k];
+    for (int k = 0; k < 3; ++k) m[k] /= static_cast<double>(npix);
+    for (size_t i = 0; i < npix; ++i)
+      for (int k = 0; k < 3; ++k) {
+        const float mk = static_cast<float>(m[k]);
+        img[3 * i + k] = mk + (img[3 * i + k] - mk) * op.contrast;
+      }
+  };
+  brightness();
+  if (op.distort_order == 1) {
+    saturation();
+    contrast();
+  } else {
+    contrast();
+    saturation();
+  }
+  for (size_t i = 0; i < npix * 3; ++i) img[i] = std::min(std::max(img[i], 0.f), 255.f);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* kfb_image_last_error() { return g_err; }
+
+// 0 on success; -1 on invalid arguments (kfb_image_last_error()).
+int kfb_image_transform(const uint8_t* src, const kfb_image_op* opp, void* out) {
+  if (src == nullptr || opp == nullptr || out == nullptr) {
+    std::snprintf(g_err, sizeof(g_err), "image_transform: null argument");
+    return -1;
+  }
+  const kfb_image_op& op = *opp;
+  if (op.ih <= 0 || op.iw <= 0 || op.src_stride < op.iw * 3 || op.ch <= 0 || op.cw <= 0 ||
+      op.top < 0 || op.left < 0 || op.top + op.ch > op.ih || op.left + op.cw > op.iw ||
+      op.vh <= 0 || op.vw <= 0 || op.oh <= 0 || op.ow <= 0 || op.oy < 0 || op.ox < 0 ||
+      op.oy + op.oh > op.vh || op.ox + op.ow > op.vw || op.method < 0 || op.method > 3) {
+    std::snprintf(g_err, sizeof(g_err),
+                  "image_transform: bad geometry (image %dx%d, crop %d,%d %dx%d, resize %dx%d, "
+                  "window %d,%d %dx%d, method %d)",
+                  op.ih, op.iw, op.top, op.left, op.ch, op.cw, op.vh, op.vw, op.oy, op.ox, op.oh,
+                  op.ow, op.method);
+    return -1;
+  }
+  const size_t npix = static_cast<size_t>(op.oh) * op.ow;
+  if (g_plane.size() < npix * 3) g_plane.resize(npix * 3);
+  float* plane = g_plane.data();
+  resize_window(src, op, plane);
+  if (op.distort_order != 0) distort(op, plane, npix);
+  const int ow = op.ow;
+  for (int y = 0; y < op.oh; ++y) {
+    const float* row = plane + static_cast<size_t>(y) * ow * 3;
+    for (int x = 0; x < ow; ++x) {
+      const float* p = row + 3 * (op.flip ? ow - 1 - x : x);
+      const size_t o = (static_cast<size_t>(y) * ow + x) * 3;
+      if (op.out_f16) {
+        uint16_t* d = static_cast<uint16_t*>(out) + o;
+        for (int k = 0; k < 3; ++k) d[k] = to_half(p[k] * op.scale + op.bias);
+      } else {
+        float* d = static_cast<float*>(out) + o;
+        for (int k = 0; k < 3; ++k) d[k] = p[k] * op.scale + op.bias;
+      }
+    }
+  }
+  return 0;
+}
+
+}  // extern "C"

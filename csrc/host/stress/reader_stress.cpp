@@ -25,6 +25,12 @@ int kfb_example_get_bytes(const uint8_t* data, uint64_t len, const char* key, co
                           uint64_t* out_len);
 int kfb_example_get_numbers(const uint8_t* data, uint64_t len, const char* key, double* out,
                             int cap);
+typedef struct {
+  int ih, iw, src_stride, top, left, ch, cw, vh, vw, oy, ox, oh, ow, method, flip, distort_order;
+  float brightness, saturation, contrast, scale, bias;
+  int out_f16;
+} kfb_image_op;
+int kfb_image_transform(const uint8_t* src, const kfb_image_op* op, void* out);
 }
 
 namespace {
@@ -168,6 +174,57 @@ int main(int argc, char** argv) {
       kfb_example_get_bytes(buf.data(), buf.size(), "k", &out, &out_len);
       kfb_example_get_numbers(buf.data(), buf.size(), "n", nums, 2);
     }
+  }
+  // (f) image transform: random crops / resizes / windows of every method from several threads
+  // at once (it keeps thread-local scratch); source and destination are heap blocks of exactly
+  // the size the geometry implies, so an out-of-range tap is an ASAN report
+  {
+    auto worker = [](uint64_t seed) {
+      uint64_t st = seed * 0x9E3779B97F4A7C15ull + 1;
+      auto r = [&st](uint32_t n) {
+        st ^= st << 13;
+        st ^= st >> 7;
+        st ^= st << 17;
+        return static_cast<int>((st >> 20) % n);
+      };
+      for (int it = 0; it < 300; ++it) {
+        kfb_image_op op{};
+        op.ih = 1 + r(60);
+        op.iw = 1 + r(60);
+        op.src_stride = op.iw * 3 + r(8);
+        op.ch = 1 + r(op.ih);
+        op.cw = 1 + r(op.iw);
+        op.top = r(op.ih - op.ch + 1);
+        op.left = r(op.iw - op.cw + 1);
+        op.vh = 1 + r(70);
+        op.vw = 1 + r(70);
+        op.oh = 1 + r(op.vh);
+        op.ow = 1 + r(op.vw);
+        op.oy = r(op.vh - op.oh + 1);
+        op.ox = r(op.vw - op.ow + 1);
+        op.method = it % 4;
+        op.flip = r(2);
+        op.distort_order = r(3);
+        op.brightness = 5.f;
+        op.saturation = 1.2f;
+        op.contrast = 0.8f;
+        op.scale = 1.f / 127.5f;
+        op.bias = -1.f;
+        op.out_f16 = r(2);
+        // the last row needs only iw*3 bytes: allocate exactly that
+        std::vector<uint8_t> src(static_cast<size_t>(op.ih - 1) * op.src_stride + op.iw * 3);
+        for (auto& b : src) b = static_cast<uint8_t>(r(256));
+        std::vector<uint8_t> out(static_cast<size_t>(op.oh) * op.ow * 3 * (op.out_f16 ? 2 : 4));
+        REQUIRE(kfb_image_transform(src.data(), &op, out.data()) == 0, "image transform failed");
+      }
+      kfb_image_op bad{};
+      uint8_t px[3] = {0, 0, 0};
+      float o[3];
+      REQUIRE(kfb_image_transform(px, &bad, o) == -1, "bad geometry accepted");
+    };
+    std::vector<std::thread> ts;
+    for (int t = 0; t < 4; ++t) ts.emplace_back(worker, static_cast<uint64_t>(t + 1));
+    for (auto& t : ts) t.join();
   }
   std::printf("reader_stress ok (%d iterations)\n", iters);
   return 0;

@@ -65,7 +65,7 @@ def build_host(force: bool = False) -> str:
     if not force and os.path.exists(HOST_LIB) and os.path.getmtime(HOST_LIB) >= newest:
         return HOST_LIB
     cxx = os.environ.get("CXX", "g++")
-    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", "-msse4.2", "-o", HOST_LIB] \
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", "-msse4.2", "-mf16c", "-o", HOST_LIB] \
         + srcs
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:

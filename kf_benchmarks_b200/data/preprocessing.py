@@ -54,13 +54,18 @@ def _resize(img: np.ndarray, h: int, w: int, method: str) -> np.ndarray:
     return np.asarray(pil.resize((w, h), resample=_RESIZE[method]))
 
 
+def eval_geometry(ih: int, iw: int, height: int, width: int):
+    """((resized h, w), (top, left, h, w) of the centre crop): the short side is resized to cover
+    1.15x the target (T/preprocessing.py:216-259)."""
+    ratio = max(height / float(ih), width / float(iw))
+    rh, rw = max(int(ih * ratio * 1.15), height), max(int(iw * ratio * 1.15), width)
+    return (rh, rw), ((rh - height) // 2, (rw - width) // 2, height, width)
+
+
 def eval_image(img: np.ndarray, height: int, width: int, batch_position: int = 0,
                resize_method: str = "bilinear") -> np.ndarray:
-    ih, iw = img.shape[:2]
-    ratio = max(height / float(ih), width / float(iw))
-    rh, rw = int(ih * ratio * 1.15), int(iw * ratio * 1.15)
+    (rh, rw), (top, left, _, _) = eval_geometry(img.shape[0], img.shape[1], height, width)
     out = _resize(img, rh, rw, get_image_resize_method(resize_method, batch_position))
-    top, left = (rh - height) // 2, (rw - width) // 2
     return out[top:top + height, left:left + width]
 
 
@@ -156,41 +161,79 @@ def parse_example_proto(record: bytes):
     return ex["image/encoded"][0], label, bbox, text[0] if text else b""
 
 
+def _decode_workers(params) -> int:
+    """Threads that decode / transform examples of one batch in parallel
+    (--datasets_num_private_threads; default: this rank's share of the cores, at most 16)."""
+    n = getattr(params, "datasets_num_private_threads", None)
+    if n:
+        return max(int(n), 1)
+    local = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")) or 1)
+    return max(1, min(16, (os.cpu_count() or 2) // max(local, 1)))
+
+
 class _BatchSource(InputSource):
-    """Common machinery: a producer thread filling pinned batches."""
+    """Common machinery: a producer thread filling a ring of (pinned) batch buffers, the
+    examples of one batch spread over a pool of worker threads. JPEG decode (Pillow) and the
+    native transform (csrc/host/image_ops.cpp) both run without the GIL, so the pool scales
+    with the cores like the reference's tf.data map(num_parallel_calls) does
+    (T/preprocessing.py:566-651). Augmentation randomness is drawn per example from a seed
+    taken in order on the producer thread: the batches do not depend on the thread count."""
     host_resident = True
 
     def __init__(self, params, batch, height, width, device, train, seed):
+        from concurrent.futures import ThreadPoolExecutor
         self.p = params
         self.batch, self.h, self.w = batch, height, width
         self.device = torch.device(device)
         self.train = train
         self.rng = random.Random(seed)
         self.out_dtype = torch.float16 if self.device.type == "cuda" else torch.float32
-        self.producer = ImageProducer(self._make_batch, params.batch_group_size)
+        group = max(int(params.batch_group_size or 1), 1)
+        pin = self.device.type == "cuda" and torch.cuda.is_available()
+        # 2*group batches may be staged, one is being filled, one or two are still being read
+        # by the consumer (host->device copy in flight): a slot comes round again after that
+        self._ring = [(torch.empty((batch, height, width, 3), dtype=self.out_dtype,
+                                   pin_memory=pin),
+                       torch.empty((batch,), dtype=torch.int32, pin_memory=pin))
+                      for _ in range(2 * group + 3)]
+        self._ring_pos = 0
+        nthreads = _decode_workers(params)
+        self._pool = ThreadPoolExecutor(nthreads, thread_name_prefix="kfb-decode") \
+            if nthreads > 1 else None
+        self.producer = ImageProducer(self._make_batch, group)
         self.producer.start()
         self.bytes_per_step = batch * height * width * 3 * (2 if self.out_dtype ==
                                                             torch.float16 else 4) + batch * 4
 
-    def _next_example(self, position: int):
+    def _draw(self, position: int):
+        """Producer thread, in batch order: everything sequential about example `position`
+        (next record, its augmentation seed). Returns the job handed to `_fill`."""
+        raise NotImplementedError
+
+    def _fill(self, images: torch.Tensor, labels: np.ndarray, position: int, job) -> None:
+        """Worker thread: decode / transform the example and write slot `position`."""
         raise NotImplementedError
 
     def _make_batch(self):
-        imgs = np.empty((self.batch, self.h, self.w, 3), dtype=np.float32)
-        labels = np.empty((self.batch,), dtype=np.int32)
-        for i in range(self.batch):
-            imgs[i], labels[i] = self._next_example(i)
-        t = torch.from_numpy(imgs).to(self.out_dtype)
-        lab = torch.from_numpy(labels)
-        if self.device.type == "cuda":
-            t, lab = t.pin_memory(), lab.pin_memory()
-        return t, lab
+        images, labels_t = self._ring[self._ring_pos % len(self._ring)]
+        self._ring_pos += 1
+        labels = labels_t.numpy()
+        jobs = [self._draw(i) for i in range(self.batch)]
+        if self._pool is not None:
+            list(self._pool.map(lambda ij: self._fill(images, labels, ij[0], ij[1]),
+                                enumerate(jobs)))
+        else:
+            for i, job in enumerate(jobs):
+                self._fill(images, labels, i, job)
+        return images, labels_t
 
     def next_batch(self):
         return self.producer.get()
 
     def close(self):
         self.producer.done()
+        if self._pool is not None:
+            self._pool.shutdown(wait=False)
 
 
 class ImagenetSource(_BatchSource):
@@ -205,16 +248,17 @@ class ImagenetSource(_BatchSource):
         self.p = params
         self.records = self._record_iter()
         self.cached = None
+        from . import native_image
+        self._native = native_image if native_image.available() else None
         super().__init__(params, batch, height, width, device, train, seed * 7919 + rank)
 
     def _record_iter(self):
         """Endless record stream. With the host library built, files are read and CRC-checked
-        by background C++ threads (--datasets_num_private_threads of them, default 2), file
-        i on thread i % n like a parallel interleave; otherwise by the Python codec."""
+        by two background C++ threads, file i on thread i % 2 like a parallel interleave;
+        otherwise by the Python codec."""
         from . import native_reader
         if native_reader.available():
-            threads = int(getattr(self.p, "datasets_num_private_threads", None) or 2)
-            return iter(native_reader.RecordReader(self.files, num_threads=threads, capacity=512,
+            return iter(native_reader.RecordReader(self.files, num_threads=2, capacity=512,
                                                    check_crc=True, repeat=True))
         return self._python_record_iter()
 
@@ -225,20 +269,45 @@ class ImagenetSource(_BatchSource):
                 for rec in tfrecord.read_records(path):
                     yield rec
 
-    def _next_example(self, position: int):
+    def _draw(self, position: int):
+        if self.p.datasets_repeat_cached_sample and self.cached is not None:
+            record = self.cached
+        else:
+            record = next(self.records)
+            self.cached = record
+        return record, self.rng.getrandbits(62)
+
+    def _fill(self, images, labels, position, job) -> None:
+        record, seed = job
         p = self.p
-        if p.datasets_repeat_cached_sample and self.cached is not None:
-            buf, label, bbox = self.cached
-        else:
-            buf, label, bbox, _ = parse_example_proto(next(self.records))
-            self.cached = (buf, label, bbox)
+        buf, label, bbox, _ = parse_example_proto(record)
         img = decode_jpeg(buf)
+        rng = random.Random(seed)
+        labels[position] = label
+        if self._native is None:
+            if self.train:
+                out = train_image(img, self.h, self.w, bbox, position, p.resize_method,
+                                  p.distortions, rng)
+            else:
+                out = eval_image(img, self.h, self.w, position, p.resize_method)
+            images[position] = torch.from_numpy(normalized_image(out)).to(images.dtype)
+            return
+        ni = self._native
+        method = get_image_resize_method(p.resize_method, position)
+        crop, window, flip, distort = None, None, False, None
+        resized = (self.h, self.w)
         if self.train:
-            out = train_image(img, self.h, self.w, bbox, position, p.resize_method, p.distortions,
-                              self.rng)
+            if p.distortions:
+                crop = sample_distorted_bounding_box(img.shape[0], img.shape[1], bbox, rng)
+                flip = rng.random() < 0.5
+                distort = (1 if position % 2 == 0 else 2, rng.uniform(-32.0, 32.0),
+                           rng.uniform(0.5, 1.5), rng.uniform(0.5, 1.5))
         else:
-            out = eval_image(img, self.h, self.w, position, p.resize_method)
-        return normalized_image(out), label
+            resized, window = eval_geometry(img.shape[0], img.shape[1], self.h, self.w)
+        op = ni.make_op(img, crop, resized, window, method, flip, distort,
+                        out_f16=images.dtype == torch.float16)
+        ni.transform_into(np.ascontiguousarray(img), op,
+                          images.data_ptr() + position * images.stride(0) * images.element_size())
 
 
 class Cifar10Source(_BatchSource):
@@ -251,22 +320,29 @@ class Cifar10Source(_BatchSource):
             self.np_rng.shuffle(self.order)
         super().__init__(params, batch, 32, 32, device, train, seed * 7919 + rank)
 
-    def _next_example(self, position: int):
+    def _draw(self, position: int):
         if self.pos >= len(self.order):
             self.pos = 0
             if self.train:
                 self.np_rng.shuffle(self.order)
         idx = self.order[self.pos]
         self.pos += 1
+        return idx, self.rng.getrandbits(62)
+
+    def _fill(self, images, labels, position, job) -> None:
+        idx, seed = job
+        rng = random.Random(seed)
         img = self.images[idx]
         if self.train and self.p.distortions:
             padded = np.zeros((40, 40, 3), dtype=img.dtype)
             padded[4:36, 4:36] = img
-            top, left = self.rng.randint(0, 8), self.rng.randint(0, 8)
+            top, left = rng.randint(0, 8), rng.randint(0, 8)
             img = padded[top:top + 32, left:left + 32]
-            if self.rng.random() < 0.5:
+            if rng.random() < 0.5:
                 img = img[:, ::-1]
-        return normalized_image(img), int(self.labels[idx])
+        images[position] = torch.from_numpy(normalized_image(np.ascontiguousarray(img))) \
+            .to(images.dtype)
+        labels[position] = int(self.labels[idx])
 
 
 _PREPROCESSORS = {"imagenet": {"default": ImagenetSource}, "cifar10": {"default": Cifar10Source}}

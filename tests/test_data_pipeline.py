@@ -157,3 +157,83 @@ def test_training_on_cifar10_pickles(tmp_path):
     stats, _ = _run(dict(model="trivial", data_dir=d, data_name="cifar10", device="cpu",
                          data_format="NHWC", batch_size=8, num_batches=3, num_warmup_batches=0))
     assert stats["num_steps"] == 3 and np.isfinite(stats["last_average_loss"])
+
+
+# ---- native image transform (csrc/host/image_ops.cpp) and the parallel batch producer ----------
+def _native_image():
+    from kf_benchmarks_b200 import build as build_lib
+    from kf_benchmarks_b200.data import native_image
+    build_lib.build_host()
+    assert native_image.available()
+    return native_image
+
+
+@pytest.mark.parametrize("method", ["bilinear", "nearest", "bicubic", "area"])
+def test_native_image_transform_matches_numpy_restatement(method):
+    ni = _native_image()
+    img = np.random.RandomState(3).randint(0, 256, (75, 101, 3)).astype(np.uint8)
+    cases = [((5, 7, 60, 80), (32, 48), None, True, (1, 12.0, 1.3, 0.7)),     # train crop
+             (None, (90, 121), (13, 28, 64, 64), False, None),                 # eval centre crop
+             ((0, 0, 20, 18), (64, 64), None, False, (2, -20.0, 0.6, 1.4)),    # upsampling
+             ((5, 5, 1, 1), (7, 9), None, True, None)]                         # 1-pixel crop
+    for crop, resized, window, flip, distort in cases:
+        op = ni.make_op(img, crop, resized, window, method, flip, distort)
+        got, want = ni.transform(img, op), ni.transform_reference(img, op)
+        assert got.shape == want.shape and np.abs(got - want).max() < 1e-4
+    op = ni.make_op(img, None, (40, 40), None, method, out_f16=True)
+    got, want = ni.transform(img, op), ni.transform_reference(img, op)
+    assert got.dtype == np.float16 and np.abs(got.astype(np.float32) - want).max() < 2e-3
+    # rows padded beyond the pixels (a view into a wider image) are read through the stride
+    wide = np.zeros((75, 140, 3), np.uint8)
+    wide[:, :101] = img
+    view = wide[:, :101]
+    op_v, op_c = ni.make_op(view, (5, 7, 60, 80), (32, 48), None, method), \
+        ni.make_op(img, (5, 7, 60, 80), (32, 48), None, method)
+    assert np.array_equal(ni.transform(view, op_v), ni.transform(img, op_c))
+
+
+def test_native_image_transform_constant_images_and_bad_geometry():
+    """The reference's preprocessing test: a constant-colour image stays constant through every
+    resize method, with and without distortions (T/benchmark_cnn_test.py:817-886)."""
+    ni = _native_image()
+    for color in (0, 255):
+        img = np.full((90, 120, 3), color, dtype=np.uint8)
+        want = color / 127.5 - 1.0
+        for method in ni.METHODS:
+            (rh, rw), win = pp.eval_geometry(90, 120, 64, 64)
+            ev = ni.transform(img, ni.make_op(img, None, (rh, rw), win, method))
+            assert ev.shape == (64, 64, 3) and np.abs(ev - want).max() < 1e-3
+            tr = ni.transform(img, ni.make_op(img, (9, 12, 50, 70), (48, 56), None, method, True,
+                                              (1, 10.0, 1.2, 0.8)))
+            assert tr.shape == (48, 56, 3) and np.abs(tr - want).max() <= 50 / 127.5
+    img = np.zeros((10, 10, 3), np.uint8)
+    with pytest.raises(ValueError, match="bad geometry"):
+        ni.transform(img, ni.make_op(img, (5, 5, 8, 8), (4, 4)))
+    with pytest.raises(ValueError, match="packed pixels"):
+        ni.transform(img[:, ::2], ni.make_op(img, None, (4, 4)))
+    assert pp.eval_geometry(375, 500, 224, 224) == ((257, 343), (16, 59, 224, 224))
+
+
+def test_batches_do_not_depend_on_the_number_of_decode_threads(tmp_path):
+    """Examples of a batch are decoded / transformed on a thread pool; augmentation seeds are
+    drawn in order on the producer thread, so 1 thread and 4 threads give identical batches."""
+    from kf_benchmarks_b200 import datasets
+    _native_image()
+    d = str(tmp_path / "imagenet")
+    os.makedirs(d)
+    _write_imagenet(d, "train", n=6, shards=1)
+    ds = datasets.create_dataset(d, "imagenet")
+    got = {}
+    for threads in (1, 4):
+        p = P.make_params(model="trivial", data_dir=d, data_name="imagenet", device="cpu",
+                          data_format="NHWC", batch_size=5,
+                          datasets_num_private_threads=threads)
+        src = pp.ImagenetSource(p, ds, 5, 32, 32, "cpu", True, 11, 0, 1)
+        got[threads] = [tuple(t.clone() for t in src.next_batch()) for _ in range(4)]
+        src.close()
+    for (a_img, a_lab), (b_img, b_lab) in zip(got[1], got[4]):
+        assert torch.equal(a_img, b_img) and torch.equal(a_lab, b_lab)
+    labels = torch.cat([lab for _, lab in got[1]]).tolist()
+    assert labels[:6] == [1, 2, 3, 4, 5, 1]           # record order is kept
+    assert all(abs(float(img.min()) + 1) < 0.4 or abs(float(img.max()) - 1) < 0.4
+               for img, _ in got[1])
