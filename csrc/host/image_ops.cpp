@@ -219,38 +219,56 @@ void resize_window(const uint8_t* src, const kfb_image_op& op, float* out) {
   }
 }
 
-void distort(const kfb_image_op& op, float* img, size_t npix) {
-  auto brightness = [&] {
-    for (size_t i = 0; i < npix * 3; ++i) img[i] += op.brightness;
-  };
-  auto saturation = [&] {
-    for (size_t i = 0; i < npix; ++i) {
-      float* p = img + 3 * i;
-      const float g = (p[0] + p[1] + p[2]) * (1.f / 3.f);
-      for (int k = 0; k < 3; ++k) p[k] = g + (p[k] - g) * op.saturation;
-    }
-  };
-  auto contrast = [&] {
+// Colour jitter folded into one per-pixel function. Brightness, saturation (around the pixel's
+// grey value) and contrast (around the per-channel image mean) are all affine, so the channel
+// means the contrast step needs follow in closed form from the means of the resized image and
+// the whole chain is applied in the same pass that normalises and stores.
+struct Jitter {
+  bool on = false;
+  int order = 0;
+  float b = 0.f, fs = 1.f, fc = 1.f;
+  float mean[3] = {0.f, 0.f, 0.f};  // channel means at the point where contrast is applied
+
+  void prepare(const kfb_image_op& op, const float* img, size_t npix) {
+    on = op.distort_order != 0;
+    if (!on) return;
+    order = op.distort_order;
+    b = op.brightness;
+    fs = op.saturation;
+    fc = op.contrast;
     double m[3] = {0, 0, 0};
-    for (size_t i = 0; i < npix; ++i)
-      for (int k = 0; k < 3; ++k) m[k] += img[3 * i + k];
-    for (int k = 0; k < 3; ++k) m[k] /= static_cast<double>(npix);
-    for (size_t i = 0; i < npix; ++i)
-      for (int k = 0; k < 3; ++k) {
-        const float mk = static_cast<float>(m[k]);
-        img[3 * i + k] = mk + (img[3 * i + k] - mk) * op.contrast;
-      }
-  };
-  brightness();
-  if (op.distort_order == 1) {
-    saturation();
-    contrast();
-  } else {
-    contrast();
-    saturation();
+    for (size_t i = 0; i < npix; ++i) {
+      m[0] += img[3 * i];
+      m[1] += img[3 * i + 1];
+      m[2] += img[3 * i + 2];
+    }
+    for (int k = 0; k < 3; ++k) m[k] = m[k] / static_cast<double>(npix) + b;
+    if (order == 1) {  // saturation already applied when contrast runs
+      const double g = (m[0] + m[1] + m[2]) / 3.0;
+      for (int k = 0; k < 3; ++k) mean[k] = static_cast<float>(g + (m[k] - g) * fs);
+    } else {
+      for (int k = 0; k < 3; ++k) mean[k] = static_cast<float>(m[k]);
+    }
   }
-  for (size_t i = 0; i < npix * 3; ++i) img[i] = std::min(std::max(img[i], 0.f), 255.f);
-}
+
+  inline void apply(const float* p, float v[3]) const {
+    v[0] = p[0];
+    v[1] = p[1];
+    v[2] = p[2];
+    if (!on) return;
+    for (int k = 0; k < 3; ++k) v[k] += b;
+    if (order == 1) {
+      const float g = (v[0] + v[1] + v[2]) * (1.f / 3.f);
+      for (int k = 0; k < 3; ++k) v[k] = g + (v[k] - g) * fs;
+      for (int k = 0; k < 3; ++k) v[k] = mean[k] + (v[k] - mean[k]) * fc;
+    } else {
+      for (int k = 0; k < 3; ++k) v[k] = mean[k] + (v[k] - mean[k]) * fc;
+      const float g = (v[0] + v[1] + v[2]) * (1.f / 3.f);
+      for (int k = 0; k < 3; ++k) v[k] = g + (v[k] - g) * fs;
+    }
+    for (int k = 0; k < 3; ++k) v[k] = std::min(std::max(v[k], 0.f), 255.f);
+  }
+};
 
 }  // namespace
 
@@ -280,12 +298,14 @@ int kfb_image_transform(const uint8_t* src, const kfb_image_op* opp, void* out) 
   if (g_plane.size() < npix * 3) g_plane.resize(npix * 3);
   float* plane = g_plane.data();
   resize_window(src, op, plane);
-  if (op.distort_order != 0) distort(op, plane, npix);
+  Jitter jitter;
+  jitter.prepare(op, plane, npix);
   const int ow = op.ow;
   for (int y = 0; y < op.oh; ++y) {
     const float* row = plane + static_cast<size_t>(y) * ow * 3;
     for (int x = 0; x < ow; ++x) {
-      const float* p = row + 3 * (op.flip ? ow - 1 - x : x);
+      float p[3];
+      jitter.apply(row + 3 * (op.flip ? ow - 1 - x : x), p);
       const size_t o = (static_cast<size_t>(y) * ow + x) * 3;
       if (op.out_f16) {
         uint16_t* d = static_cast<uint16_t*>(out) + o;
