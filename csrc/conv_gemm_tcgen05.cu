@@ -22,6 +22,7 @@
 #include "../include/kfb200.h"
 
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace kfb {
@@ -79,6 +80,10 @@ struct GemmParams {
   int push_n;
   long long push_bound[8];
   float* push_base[8];
+  // TMA-store epilogue (opt-in, KFB_TMA_STORE=1): the staged 32 x 64 fp16 chunks leave through
+  // cp.async.bulk.tensor stores on `tmC` instead of per-lane 16-byte stores. Host-side
+  // eligibility: fp16 output, no accumulate / row scatter / split-K / fused statistics / push.
+  int tma_store;
 };
 
 constexpr int kBlockM = 128;
@@ -115,7 +120,8 @@ struct TileCfg {
 template <int BN, int MODE, bool FAST>
 __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
-                        const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+                        const __grid_constant__ CUtensorMap tmB,
+                        const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   using Cfg = TileCfg<BN>;
   const int kStages = p.stages;
   constexpr uint32_t kAMajor = (MODE == GEMM_NT || MODE == WGRAD) ? kMajorMN : kMajorK;
@@ -346,7 +352,12 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     const int epi = warp - 2;                      // 0 .. kEpiWarps-1
     constexpr int kColSplit = Cfg::kEpiWarps / 4;  // warps sharing a lane quarter
     const int col_part = epi / 4;                  // which interleaved set of chunks is mine
-    uint8_t* stage_buf = staging + epi * (32 * kStageRowBytes);
+    // TMA-store variant: dense 128-byte rows with the 128B swizzle of `tmC` (16-byte piece index
+    // XOR row % 8), 4 KiB per warp, 1 KiB aligned (the staging area starts 1 KiB aligned)
+    constexpr bool kTmaStoreMode = FAST && (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD);
+    const bool tma_store = kTmaStoreMode && p.tma_store != 0;
+    bool store_pending = false;  // warp-uniform: a bulk store may still be reading stage_buf
+    uint8_t* stage_buf = tma_store ? staging + epi * 4096 : staging + epi * (32 * kStageRowBytes);
     const int esize = p.out_fp32 ? 4 : 2;
     const int cols_per_chunk = 128 / esize;  // 32 (fp32) or 64 (fp16)
     // fused BN statistics: lane owns columns (2*lane, 2*lane+1) of each 64-wide chunk it handles
@@ -444,6 +455,26 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
           }
+          if (kTmaStoreMode && tma_store) {
+            if (h == 0 && store_pending) {
+              // the previous chunk's bulk store must have read the staging tile before it is
+              // overwritten (the wait overlapped the TMEM load above)
+              if (lane == 0) bulk_wait_group_read_all();
+              __syncwarp();
+            }
+            uint8_t* srow = stage_buf + lane * 128;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 u;
+              u.x = pack_half2(f[j], f[j + 1]);
+              u.y = pack_half2(f[j + 2], f[j + 3]);
+              u.z = pack_half2(f[j + 4], f[j + 5]);
+              u.w = pack_half2(f[j + 6], f[j + 7]);
+              const int piece = h * 4 + (j >> 3);
+              *reinterpret_cast<uint4*>(srow + ((piece ^ (lane & 7)) << 4)) = u;
+            }
+            continue;
+          }
           uint8_t* srow = stage_buf + lane * kStageRowBytes;
           if (p.out_fp32) {
 #pragma unroll
@@ -470,6 +501,18 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
         }
         __syncwarp();
+        if (kTmaStoreMode && tma_store) {
+          // generic-proxy writes of every lane -> visible to the async proxy, then one lane
+          // stores the 32-row x 64-column box; rows >= M and columns >= N are clipped by TMA
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && m0 + quarter * 32 < p.M) {
+            tma_store_2d(&tmC, smem_u32(stage_buf), col_mem0 + c0, m0 + quarter * 32);
+            bulk_commit_group();
+          }
+          store_pending = true;
+          continue;
+        }
         if (do_stats) {
           // column sums of the staged (already fp16-rounded) 32 x 64 chunk; rows beyond M and
           // columns beyond N hold exact zeros (zero-filled operands), so no masking is needed
@@ -569,6 +612,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       }
     }
     if (do_stats && st_nblk >= 0) flush_stats(st_nblk);
+    if (kTmaStoreMode && tma_store && store_pending && lane == 0) bulk_wait_group_all();
     // remote (NVLink) stores of a fused reduce-scatter must be performed system-wide before
     // this kernel counts as complete for the ranks that wait on the stream-ordered READY flag
     if (kCanPush && p.push_n > 1) __threadfence_system();
@@ -813,6 +857,23 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   const bool fast = (n_valid % epp == 0) && (p.ldc % epp == 0) && (p.split_stride % epp == 0) &&
                     ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0) &&
                     (MODE != WGRAD || p.wg_flat || (p.Cn % epp == 0));
+  // TMA-store epilogue: opt-in until it has been measured (KFB_TMA_STORE=1)
+  static int tma_store_env = -1;
+  if (tma_store_env < 0) {
+    const char* e = getenv("KFB_TMA_STORE");
+    tma_store_env = (e != nullptr && atoi(e) != 0) ? 1 : 0;
+  }
+  CUtensorMap tmC = tmA;  // placeholder, only dereferenced when p.tma_store is set
+  p.tma_store = 0;
+  if (tma_store_env == 1 && fast && (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) &&
+      !p.out_fp32 && !p.accumulate && p.sc_P == 0 && tiles.z == 1 && p.stats == nullptr &&
+      p.push_n <= 1 && p.N >= 64 && p.M >= 32 && (p.ldc % 8) == 0) {
+    const uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
+    const uint64_t strides[1] = {(uint64_t)p.ldc * 2};
+    const uint32_t box[2] = {64, 32};
+    if (encode_tiled(&tmC, p.out, 2, dims, strides, box)) return 1;
+    p.tma_store = 1;
+  }
   p.stages = Cfg::max_stages();
   p.m_tiles = (int)tiles.x;
   p.n_tiles = (int)tiles.y;
@@ -827,10 +888,10 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   }
   if (fast)
     gemm_tcgen05_kernel<BN, MODE, true><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
-        tmA, tmB, p);
+        tmA, tmB, tmC, p);
   else
     gemm_tcgen05_kernel<BN, MODE, false><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
-        tmA, tmB, p);
+        tmA, tmB, tmC, p);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

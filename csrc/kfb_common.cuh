@@ -129,6 +129,28 @@ __device__ __forceinline__ void tma_load_im2col_4d(void* smem_dst, const CUtenso
 }
 
 // ---- tcgen05 ----
+// TMA store: one 2-D box from shared memory (dense, swizzled like the tensor map says) to the
+// tensor; elements outside the tensor's extent are not written. Completion is tracked by bulk
+// async-groups of the issuing thread.
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, uint32_t smem_src, int x,
+                                             int y) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               :
+               : "l"(m), "r"(smem_src), "r"(x), "r"(y)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// all of this thread's bulk groups have finished READING shared memory (it may be overwritten)
+__device__ __forceinline__ void bulk_wait_group_read_all() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+// all of this thread's bulk groups are complete (their global writes are performed)
+__device__ __forceinline__ void bulk_wait_group_all() {
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }

@@ -1,0 +1,32 @@
+#!/bin/bash
+# Code paths that were written when no GPU time was left (NEXT.md) - run these first:
+#   1 GPU : bash tools/run_pending_gpu_checks.sh
+#   2 GPUs: bash tools/run_pending_gpu_checks.sh 2        (adds the NVLS all-reduce checks)
+# Everything lands in gpurun_out/pending_*.log; nothing here is a bench value.
+set -u
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+N=${1:-1}
+echo "== TMA-store epilogue: numerics of every GEMM / conv case =="
+KFB_TMA_STORE=1 timeout 1500 python tools/kernel_check.py > gpurun_out/pending_tma_store_check.log 2>&1
+tail -1 gpurun_out/pending_tma_store_check.log
+echo "== TMA-store epilogue: A/B on the headline step (1 GPU) =="
+for v in 0 1; do
+  KFB_TMA_STORE=$v timeout 900 python bench.py --steps 20 --warmup 5 --no_e2e \
+    > gpurun_out/pending_bench_tma_store_$v.json 2> gpurun_out/pending_bench_tma_store_$v.err
+  python - "$v" <<'PY'
+import json, sys
+v = sys.argv[1]
+try:
+    d = json.loads(open("gpurun_out/pending_bench_tma_store_%s.json" % v).read().strip().splitlines()[-1])
+    print("KFB_TMA_STORE=%s: %.0f img/s, %.2f ms/step, loss %.4f" %
+          (v, d["value"], d["ms_per_step"], d["final_loss"]))
+except Exception as e:
+    print("KFB_TMA_STORE=%s: no result (%r)" % (v, e))
+PY
+done
+if [ "$N" -ge 2 ]; then
+  echo "== NVLS all-reduce (--comm_impl=nvls) on $N GPUs =="
+  timeout 1800 python tools/nvls_check.py "$N" > gpurun_out/pending_nvls_check.log 2>&1
+  grep -E "NVLS_CHECK|replicas|p2p_check|Average|per all-reduce|FAILED|==" gpurun_out/pending_nvls_check.log
+fi
