@@ -82,7 +82,7 @@ struct GemmParams {
   float* push_base[8];
   // TMA-store epilogue (opt-in, KFB_TMA_STORE=1): the staged 32 x 64 fp16 chunks leave through
   // cp.async.bulk.tensor stores on `tmC` instead of per-lane 16-byte stores. Host-side
-  // eligibility: fp16 output, no accumulate / row scatter / split-K / fused statistics / push.
+  // eligibility: fp16 output, no accumulate / row scatter / split-K / push.
   int tma_store;
 };
 
@@ -501,18 +501,6 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
         }
         __syncwarp();
-        if (kTmaStoreMode && tma_store) {
-          // generic-proxy writes of every lane -> visible to the async proxy, then one lane
-          // stores the 32-row x 64-column box; rows >= M and columns >= N are clipped by TMA
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0 && m0 + quarter * 32 < p.M) {
-            tma_store_2d(&tmC, smem_u32(stage_buf), col_mem0 + c0, m0 + quarter * 32);
-            bulk_commit_group();
-          }
-          store_pending = true;
-          continue;
-        }
         if (do_stats) {
           // column sums of the staged (already fp16-rounded) 32 x 64 chunk; rows beyond M and
           // columns beyond N hold exact zeros (zero-filled operands), so no masking is needed
@@ -520,8 +508,12 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll 8
           for (int r = 0; r < 32; ++r) {
-            const float2 v = __half22float2(
-                *reinterpret_cast<const __half2*>(stage_buf + r * kStageRowBytes + lane * 4));
+            // the lane's two columns of row r (swizzled 16-byte pieces in the TMA-store layout)
+            const uint8_t* sp =
+                (kTmaStoreMode && tma_store)
+                    ? stage_buf + r * 128 + ((((lane >> 2) ^ (r & 7)) << 4) | ((lane & 3) << 2))
+                    : stage_buf + r * kStageRowBytes + lane * 4;
+            const float2 v = __half22float2(*reinterpret_cast<const __half2*>(sp));
             a0 += v.x;
             a1 += v.y;
             q0 = fmaf(v.x, v.x, q0);
@@ -535,6 +527,18 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
               st_sq[c][0] += q0;
               st_sq[c][1] += q1;
             }
+        }
+        if (kTmaStoreMode && tma_store) {
+          // generic-proxy writes of every lane -> visible to the async proxy, then one lane
+          // stores the 32-row x 64-column box; rows >= M and columns >= N are clipped by TMA
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && m0 + quarter * 32 < p.M) {
+            tma_store_2d(&tmC, smem_u32(stage_buf), col_mem0 + c0, m0 + quarter * 32);
+            bulk_commit_group();
+          }
+          store_pending = true;
+          continue;
         }
         // ---- staging -> global: lane handles 16-byte piece (lane % 8) of row i8*4 + lane/8.
         //      All old-value loads of an accumulate are issued before the first store so eight
@@ -866,8 +870,8 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   CUtensorMap tmC = tmA;  // placeholder, only dereferenced when p.tma_store is set
   p.tma_store = 0;
   if (tma_store_env == 1 && fast && (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) &&
-      !p.out_fp32 && !p.accumulate && p.sc_P == 0 && tiles.z == 1 && p.stats == nullptr &&
-      p.push_n <= 1 && p.N >= 64 && p.M >= 32 && (p.ldc % 8) == 0) {
+      !p.out_fp32 && !p.accumulate && p.sc_P == 0 && tiles.z == 1 && p.push_n <= 1 &&
+      p.N >= 64 && p.M >= 32 && (p.ldc % 8) == 0) {
     const uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
     const uint64_t strides[1] = {(uint64_t)p.ldc * 2};
     const uint32_t box[2] = {64, 32};

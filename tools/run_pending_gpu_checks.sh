@@ -11,20 +11,27 @@ echo "== TMA-store epilogue: numerics of every GEMM / conv case =="
 KFB_TMA_STORE=1 timeout 1500 python tools/kernel_check.py > gpurun_out/pending_tma_store_check.log 2>&1
 tail -1 gpurun_out/pending_tma_store_check.log
 echo "== TMA-store epilogue: A/B on the headline step (1 GPU) =="
-for v in 0 1; do
-  KFB_TMA_STORE=$v timeout 900 python bench.py --steps 20 --warmup 5 --no_e2e \
+# v=2: TMA stores + BN statistics fused into the conv epilogue (all layers)
+for v in 0 1 2; do
+  if [ "$v" = 2 ]; then export KFB_FUSE_STATS_MIN_K=0; fi
+  KFB_TMA_STORE=$((v > 0 ? 1 : 0)) timeout 900 python bench.py --steps 20 --warmup 5 --no_e2e \
     > gpurun_out/pending_bench_tma_store_$v.json 2> gpurun_out/pending_bench_tma_store_$v.err
   python - "$v" <<'PY'
 import json, sys
 v = sys.argv[1]
 try:
     d = json.loads(open("gpurun_out/pending_bench_tma_store_%s.json" % v).read().strip().splitlines()[-1])
-    print("KFB_TMA_STORE=%s: %.0f img/s, %.2f ms/step, loss %.4f" %
+    print("config %s (0 = default, 1 = TMA store, 2 = TMA store + fused BN stats): %.0f img/s, %.2f ms/step, loss %.4f" %
           (v, d["value"], d["ms_per_step"], d["final_loss"]))
 except Exception as e:
     print("KFB_TMA_STORE=%s: no result (%r)" % (v, e))
 PY
 done
+unset KFB_FUSE_STATS_MIN_K
+echo "== fused BN statistics through the TMA-store layout: numerics =="
+KFB_TMA_STORE=1 timeout 600 python -m pytest tests/test_gpu_gemm_conv.py -q -m gpu \
+  -k fused_bn_statistics > gpurun_out/pending_fused_stats_tma.log 2>&1
+tail -1 gpurun_out/pending_fused_stats_tma.log
 if [ "$N" -ge 2 ]; then
   echo "== NVLS all-reduce (--comm_impl=nvls) on $N GPUs =="
   timeout 1800 python tools/nvls_check.py "$N" > gpurun_out/pending_nvls_check.log 2>&1
