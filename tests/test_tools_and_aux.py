@@ -158,3 +158,24 @@ def test_keras_style_epoch_benchmark_runs():
     assert res.returncode == 0, res.stderr[-2000:]
     d = json.loads(res.stdout.strip().splitlines()[-1])
     assert d["test_name"] == "mnist_mlp" and d["epochs"] == 2 and d["total_time"] > 0
+
+
+def test_keras_style_benchmark_mode_writes_the_reference_record_schema(tmp_path):
+    """--mode runs all three models and emits the columns of the original's results table
+    (K/upload_benchmarks_bq.py:58-75) to a JSONL sink."""
+    import json
+    out = str(tmp_path / "records.jsonl")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "keras_benchmarks",
+                                                       "run_benchmark.py"), "--mode", "cpu_config",
+                          "--num_samples", "128", "--output", out],
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    recs = [json.loads(l) for l in open(out)]
+    assert [r["test_name"] for r in recs] == ["mnist_mlp", "cifar10_cnn", "lstm"]
+    cols = {"test_id", "test_name", "metrics_totaltime", "metrics_epochs", "metrics_batch_size",
+            "metrics_sampletype", "keras_backend_type", "keras_backend_version", "keras_version",
+            "cpu_info_numcores", "cpu_info_memory", "cpu_info_memory_units", "platform_info_type",
+            "platform_info_machine_type", "gpu_info_count", "gpu_info_platform"}
+    for r in recs:
+        assert set(r) == cols and r["metrics_totaltime"] > 0 and r["gpu_info_count"] == 0
+        assert r["cpu_info_numcores"] >= 1 and r["metrics_sampletype"] == "synthetic"
