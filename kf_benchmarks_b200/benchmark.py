@@ -272,7 +272,7 @@ class BenchmarkCNN:
         _log("Num epochs:  %.2f" % self.num_epochs)
         kind = "gpu" if self.device_kind == "gpu" else "cpu"
         _log("Devices:     %s" % ["/%s:%d" % (kind, i) for i in range(self.num_gpus)])
-        _log("Data format: %s" % ("NHWC" if True else p.data_format))
+        _log("Data format: %s" % p.data_format)
         _log("Optimizer:   %s" % p.optimizer)
         _log("Variables:   %s" % p.variable_update)
         if p.variable_update in ("replicated", "distributed_all_reduce", "collective_all_reduce"):
@@ -284,6 +284,10 @@ class BenchmarkCNN:
             from . import flags
             if getattr(p, name) != flags.param_specs[name].default_value:
                 _log("note: --%s has no effect on the B200-native runtime" % name)
+        if self.device.type == "cuda" and not p.use_fp16:
+            _log("note: --use_fp16=false: the CUDA executor keeps activations and the tensor-core "
+                 "operands in fp16 (fp32 accumulation, fp32 master weights, optimizer and batch-"
+                 "norm statistics); full fp32 arithmetic is available with --device=cpu")
 
     # ------------------------------------------------------------------ build
     def _build(self, phase_train: bool) -> None:
