@@ -31,7 +31,7 @@ namespace {
 uint32_t g_table[256];
 std::once_flag g_table_once;
 
-void init_table() {
+[[maybe_unused]] void init_table() {
   for (uint32_t i = 0; i < 256; ++i) {
     uint32_t c = i;
     for (int k = 0; k < 8; ++k) c = (c & 1) ? (c >> 1) ^ 0x82F63B78u : c >> 1;

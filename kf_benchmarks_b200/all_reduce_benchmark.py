@@ -19,7 +19,7 @@ import sys
 
 import torch
 
-from . import benchmark, datasets, flags, params as params_lib
+from . import datasets, flags, params as params_lib
 from .models import model_config
 from .nn.params import ParameterStore
 from .parallel import comm as comm_lib

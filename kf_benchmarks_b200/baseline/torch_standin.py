@@ -16,7 +16,7 @@ architecture is identical by construction.
 from __future__ import annotations
 
 import math
-from typing import Dict, List
+from typing import Dict
 
 import torch
 import torch.nn as nn

@@ -9,10 +9,9 @@ fused NVLink update kernels instead of TF's gradient-aggregation graph.
 """
 from __future__ import annotations
 
-import json
 import os
 import time
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import numpy as np
 import torch
@@ -23,7 +22,7 @@ from .constants import BenchmarkMode
 from .models import model_config
 from .nn.params import ParameterStore
 from .parallel import comm as comm_lib
-from .parallel.strategy import UpdateEngine, reduction_semantics
+from .parallel.strategy import UpdateEngine
 from .params import IGNORED_ON_B200, UNSUPPORTED_WHEN_SET, make_params
 from .utils import log_util
 from .utils.log_util import log_fn  # noqa: F401  (re-exported, monkey-patchable via log_util)

@@ -23,7 +23,7 @@ import glob
 import io
 import os
 import random
-from typing import List, Optional, Tuple
+from typing import Optional, Tuple
 
 import numpy as np
 import torch

@@ -14,7 +14,7 @@ import glob
 import itertools
 import math
 import os
-from typing import Optional, Tuple
+from typing import Optional
 
 import numpy as np
 import torch

@@ -11,7 +11,7 @@ ymin,xmax,ymax}``. A writer is included so tests can fabricate records
 from __future__ import annotations
 
 import struct
-from typing import Dict, Iterator, List
+from typing import Dict, Iterator
 
 
 def _crc32c_table():

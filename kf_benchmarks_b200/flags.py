@@ -11,7 +11,7 @@ arguments so that ``--distortions False`` cannot silently mean True
 from __future__ import annotations
 
 from collections import OrderedDict, namedtuple
-from typing import Any, Dict, List, Optional, Sequence
+from typing import Any, Dict, Sequence
 
 ParamSpec = namedtuple("_ParamSpec", ["flag_type", "default_value", "description", "kwargs"])
 

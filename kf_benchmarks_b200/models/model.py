@@ -9,7 +9,7 @@ one of the bugs we do not reproduce - SURVEY.md appendix A).
 """
 from __future__ import annotations
 
-from typing import Callable, List, Optional, Tuple
+from typing import Callable, List, Optional
 
 from ..nn.builder import NetBuilder
 from ..nn.graph import Graph

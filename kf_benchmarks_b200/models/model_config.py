@@ -2,7 +2,6 @@
 registers the ResNets, every CNN of the zoo is registered here."""
 from __future__ import annotations
 
-from functools import partial
 
 from .experimental import deepspeech, official_ncf_model
 from . import ssd_model

@@ -21,7 +21,7 @@ import math
 from collections import defaultdict
 from typing import List, Optional, Sequence, Tuple
 
-from .graph import Graph, Node, ParamSpec, TensorRef
+from .graph import Graph, ParamSpec, TensorRef
 
 
 def _same_pad(in_size: int, k: int, stride: int) -> Tuple[int, int]:

@@ -15,7 +15,7 @@ from __future__ import annotations
 
 import re
 from collections import namedtuple
-from typing import List, Sequence, Tuple
+from typing import List, Sequence
 
 AllReduceSpecTuple = namedtuple("AllReduceSpecTuple", "alg shards limit")
 

@@ -21,12 +21,12 @@ from __future__ import annotations
 
 import ctypes
 import os
-from typing import List, Optional
+from typing import List
 
 import torch
 
 from ..ops import native
-from ..ops.native import f32, i32, i64, ptr
+from ..ops.native import i32, ptr
 
 
 class _CudaArray:

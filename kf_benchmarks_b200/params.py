@@ -14,7 +14,7 @@ from __future__ import annotations
 
 import sys
 from collections import namedtuple
-from typing import Any, Dict, Optional, Sequence
+from typing import Optional, Sequence
 
 from . import flags
 from .constants import NetworkTopology
