@@ -29,10 +29,12 @@ typedef struct {
   int vh, vw;              // size the crop is resized to
   int oy, ox, oh, ow;      // window of that resized image which is produced (eval centre crop)
   int method;              // 0 bilinear, 1 nearest, 2 bicubic, 3 area
-  int flip;                // mirror the produced window horizontally
-  int distort_order;       // 0 none, 1 brightness-saturation-contrast, 2 brightness-contrast-sat.
+  int flip;                // mirror the crop horizontally before it is resized
+  int distort_order;       // 0 none, 1 brightness - saturation/hue - contrast,
+                           // 2 brightness - contrast - saturation/hue (T/preprocessing.py:281-303)
   float brightness;        // added (0..255 scale)
-  float saturation;        // factor around the per-pixel grey value
+  float saturation;        // HSV saturation factor (result clamped to [0, 1])
+  float hue;               // HSV hue shift in turns ([-0.2, 0.2] in the reference)
   float contrast;          // factor around the per-channel image mean
   float scale, bias;       // out = value * scale + bias
   int out_f16;             // 0: float32 output, 1: IEEE binary16 output
@@ -88,8 +90,11 @@ inline void cubic_weights(float frac, float w[4]) {
   w[3] = far(2.f - x);
 }
 
+// pixel (y, x) of the (optionally mirrored) crop
 inline const uint8_t* px(const uint8_t* src, const kfb_image_op& op, int y, int x) {
-  return src + static_cast<size_t>(op.top + y) * op.src_stride + static_cast<size_t>(op.left + x) * 3;
+  const int sx = op.flip ? op.cw - 1 - x : x;
+  return src + static_cast<size_t>(op.top + y) * op.src_stride +
+         static_cast<size_t>(op.left + sx) * 3;
 }
 
 void resize_window(const uint8_t* src, const kfb_image_op& op, float* out) {
@@ -219,36 +224,90 @@ void resize_window(const uint8_t* src, const kfb_image_op& op, float* out) {
   }
 }
 
-// Colour jitter folded into one per-pixel function. Brightness, saturation (around the pixel's
-// grey value) and contrast (around the per-channel image mean) are all affine, so the channel
-// means the contrast step needs follow in closed form from the means of the resized image and
-// the whole chain is applied in the same pass that normalises and stores.
+// Colour jitter with the arithmetic of tf.image.adjust_{brightness,saturation,hue,contrast}
+// (values on the 0..255 scale here, 0..1 there): brightness adds, saturation and hue go through
+// HSV (one round trip for both: they touch different components), contrast scales around the
+// per-channel image mean taken at the point where it is applied; one clamp at the very end.
+inline void rgb_to_hsv(const float* p, float* h, float* s, float* v) {
+  const float r = p[0], g = p[1], b = p[2];
+  const float vv = std::max(r, std::max(g, b));
+  const float range = vv - std::min(r, std::min(g, b));
+  *v = vv;
+  *s = vv > 0.f ? range / vv : 0.f;
+  float hh = 0.f;
+  if (range > 0.f) {
+    const float norm = 1.f / (6.f * range);
+    if (r == vv) {
+      hh = norm * (g - b);
+    } else if (g == vv) {
+      hh = norm * (b - r) + 2.f / 6.f;
+    } else {
+      hh = norm * (r - g) + 4.f / 6.f;
+    }
+    if (hh < 0.f) hh += 1.f;
+  }
+  *h = hh;
+}
+
+inline void hsv_to_rgb(float h, float s, float v, float* p) {
+  const float c = s * v, m = v - c;
+  const float dh = h * 6.f;
+  const float fmodu = dh - 2.f * std::floor(dh * 0.5f);  // dh mod 2
+  const float x = c * (1.f - std::fabs(fmodu - 1.f));
+  float r = 0.f, g = 0.f, b = 0.f;
+  switch (static_cast<int>(dh)) {
+    case 0: r = c; g = x; break;
+    case 1: r = x; g = c; break;
+    case 2: g = c; b = x; break;
+    case 3: g = x; b = c; break;
+    case 4: r = x; b = c; break;
+    default: r = c; b = x; break;  // 5 (and h == 1 after rounding)
+  }
+  p[0] = r + m;
+  p[1] = g + m;
+  p[2] = b + m;
+}
+
 struct Jitter {
   bool on = false;
   int order = 0;
-  float b = 0.f, fs = 1.f, fc = 1.f;
+  float b = 0.f, fs = 1.f, dh = 0.f, fc = 1.f;
   float mean[3] = {0.f, 0.f, 0.f};  // channel means at the point where contrast is applied
 
-  void prepare(const kfb_image_op& op, const float* img, size_t npix) {
+  inline void sat_hue(float* v) const {
+    float h, s, val;
+    rgb_to_hsv(v, &h, &s, &val);
+    s = std::min(1.f, std::max(0.f, s * fs));
+    h += dh;
+    h -= std::floor(h);  // wrap into [0, 1)
+    hsv_to_rgb(h, s, val, v);
+  }
+
+  // Order 1 applies brightness + saturation/hue in place here (contrast needs the channel means
+  // of that result); order 2 only needs the means of the resized image.
+  void prepare(const kfb_image_op& op, float* img, size_t npix) {
     on = op.distort_order != 0;
     if (!on) return;
     order = op.distort_order;
     b = op.brightness;
     fs = op.saturation;
+    dh = op.hue;
     fc = op.contrast;
     double m[3] = {0, 0, 0};
     for (size_t i = 0; i < npix; ++i) {
-      m[0] += img[3 * i];
-      m[1] += img[3 * i + 1];
-      m[2] += img[3 * i + 2];
+      float* p = img + 3 * i;
+      if (order == 1) {
+        p[0] += b;
+        p[1] += b;
+        p[2] += b;
+        sat_hue(p);
+      }
+      m[0] += p[0];
+      m[1] += p[1];
+      m[2] += p[2];
     }
-    for (int k = 0; k < 3; ++k) m[k] = m[k] / static_cast<double>(npix) + b;
-    if (order == 1) {  // saturation already applied when contrast runs
-      const double g = (m[0] + m[1] + m[2]) / 3.0;
-      for (int k = 0; k < 3; ++k) mean[k] = static_cast<float>(g + (m[k] - g) * fs);
-    } else {
-      for (int k = 0; k < 3; ++k) mean[k] = static_cast<float>(m[k]);
-    }
+    for (int k = 0; k < 3; ++k)
+      mean[k] = static_cast<float>(m[k] / static_cast<double>(npix)) + (order == 1 ? 0.f : b);
   }
 
   inline void apply(const float* p, float v[3]) const {
@@ -256,15 +315,11 @@ struct Jitter {
     v[1] = p[1];
     v[2] = p[2];
     if (!on) return;
-    for (int k = 0; k < 3; ++k) v[k] += b;
     if (order == 1) {
-      const float g = (v[0] + v[1] + v[2]) * (1.f / 3.f);
-      for (int k = 0; k < 3; ++k) v[k] = g + (v[k] - g) * fs;
       for (int k = 0; k < 3; ++k) v[k] = mean[k] + (v[k] - mean[k]) * fc;
     } else {
-      for (int k = 0; k < 3; ++k) v[k] = mean[k] + (v[k] - mean[k]) * fc;
-      const float g = (v[0] + v[1] + v[2]) * (1.f / 3.f);
-      for (int k = 0; k < 3; ++k) v[k] = g + (v[k] - g) * fs;
+      for (int k = 0; k < 3; ++k) v[k] = mean[k] + (v[k] + b - mean[k]) * fc;
+      sat_hue(v);
     }
     for (int k = 0; k < 3; ++k) v[k] = std::min(std::max(v[k], 0.f), 255.f);
   }
@@ -305,7 +360,7 @@ int kfb_image_transform(const uint8_t* src, const kfb_image_op* opp, void* out) 
     const float* row = plane + static_cast<size_t>(y) * ow * 3;
     for (int x = 0; x < ow; ++x) {
       float p[3];
-      jitter.apply(row + 3 * (op.flip ? ow - 1 - x : x), p);
+      jitter.apply(row + 3 * x, p);
       const size_t o = (static_cast<size_t>(y) * ow + x) * 3;
       if (op.out_f16) {
         uint16_t* d = static_cast<uint16_t*>(out) + o;

@@ -27,7 +27,7 @@ int kfb_example_get_numbers(const uint8_t* data, uint64_t len, const char* key, 
                             int cap);
 typedef struct {
   int ih, iw, src_stride, top, left, ch, cw, vh, vw, oy, ox, oh, ow, method, flip, distort_order;
-  float brightness, saturation, contrast, scale, bias;
+  float brightness, saturation, hue, contrast, scale, bias;
   int out_f16;
 } kfb_image_op;
 int kfb_image_transform(const uint8_t* src, const kfb_image_op* op, void* out);
@@ -207,6 +207,7 @@ int main(int argc, char** argv) {
         op.distort_order = r(3);
         op.brightness = 5.f;
         op.saturation = 1.2f;
+        op.hue = 0.15f;
         op.contrast = 0.8f;
         op.scale = 1.f / 127.5f;
         op.bias = -1.f;

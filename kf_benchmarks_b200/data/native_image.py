@@ -25,8 +25,8 @@ class ImageOp(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in ("ih", "iw", "src_stride", "top", "left", "ch", "cw",
                                             "vh", "vw", "oy", "ox", "oh", "ow", "method", "flip",
                                             "distort_order")] + \
-               [(n, ctypes.c_float) for n in ("brightness", "saturation", "contrast", "scale",
-                                              "bias")] + [("out_f16", ctypes.c_int)]
+               [(n, ctypes.c_float) for n in ("brightness", "saturation", "hue", "contrast",
+                                              "scale", "bias")] + [("out_f16", ctypes.c_int)]
 
 
 _fn = None
@@ -53,11 +53,12 @@ def _function():
 
 def make_op(img: np.ndarray, crop: Optional[Tuple[int, int, int, int]], resized: Tuple[int, int],
             window: Optional[Tuple[int, int, int, int]] = None, method: str = "bilinear",
-            flip: bool = False, distort: Optional[Tuple[int, float, float, float]] = None,
+            flip: bool = False, distort: Optional[Tuple[int, float, float, float, float]] = None,
             scale: float = 1.0 / 127.5, bias: float = -1.0, out_f16: bool = False) -> ImageOp:
     """crop = (top, left, h, w) or None for the whole image; resized = (h, w) the crop is scaled
     to; window = (top, left, h, w) of the resized image to produce (None: all of it);
-    distort = (order 1|2, brightness delta, saturation factor, contrast factor)."""
+    distort = (order 1|2, brightness delta, saturation factor, hue shift in turns, contrast
+    factor) - see ``distort_color`` in data/preprocessing.py."""
     ih, iw = img.shape[:2]
     top, left, ch, cw = crop if crop is not None else (0, 0, ih, iw)
     vh, vw = resized
@@ -68,7 +69,7 @@ def make_op(img: np.ndarray, crop: Optional[Tuple[int, int, int, int]], resized:
     op.vh, op.vw, op.oy, op.ox, op.oh, op.ow = int(vh), int(vw), int(oy), int(ox), int(oh), int(ow)
     op.method, op.flip = METHODS[method], int(bool(flip))
     if distort is not None:
-        op.distort_order, op.brightness, op.saturation, op.contrast = distort
+        op.distort_order, op.brightness, op.saturation, op.hue, op.contrast = distort
     op.scale, op.bias, op.out_f16 = scale, bias, int(bool(out_f16))
     return op
 
@@ -137,24 +138,62 @@ def _axis_matrix(n_in: int, n_virtual: int, off: int, n_out: int, method: int) -
     return m
 
 
+def rgb_to_hsv(x: np.ndarray):
+    """tf.image.rgb_to_hsv arithmetic on arbitrary floats (last axis RGB)."""
+    r, g, b = x[..., 0], x[..., 1], x[..., 2]
+    v = x.max(axis=-1)
+    rng = v - x.min(axis=-1)
+    s = np.where(v > 0, rng / np.where(v > 0, v, 1.0), 0.0)
+    norm = 1.0 / (6.0 * np.where(rng > 0, rng, 1.0))
+    h = np.where(r == v, norm * (g - b),
+                 np.where(g == v, norm * (b - r) + 2.0 / 6.0, norm * (r - g) + 4.0 / 6.0))
+    h = np.where(rng > 0, h, 0.0)
+    return np.where(h < 0, h + 1.0, h), s, v
+
+
+def hsv_to_rgb(h, s, v) -> np.ndarray:
+    c = s * v
+    m = v - c
+    dh = h * 6.0
+    x = c * (1.0 - np.abs(dh - 2.0 * np.floor(dh * 0.5) - 1.0))
+    cat = dh.astype(np.int64)
+    z = np.zeros_like(c)
+    r = np.select([cat == 0, cat == 1, cat == 2, cat == 3, cat == 4], [c, x, z, z, x], c)
+    g = np.select([cat == 0, cat == 1, cat == 2, cat == 3, cat == 4], [x, c, c, x, z], z)
+    b = np.select([cat == 0, cat == 1, cat == 2, cat == 3, cat == 4], [z, z, x, c, c], x)
+    return np.stack([r + m, g + m, b + m], axis=-1)
+
+
+def distort_reference(x: np.ndarray, order: int, brightness: float, saturation: float,
+                      hue: float, contrast: float) -> np.ndarray:
+    """Colour jitter on 0..255 floats with the arithmetic of tf.image.adjust_brightness /
+    adjust_saturation / adjust_hue / adjust_contrast; order 1 = brightness, saturation + hue,
+    contrast; order 2 = brightness, contrast, saturation + hue; clipped at the end
+    (T/preprocessing.py:268-307)."""
+    x = x.astype(np.float64) + brightness
+
+    def sat_hue(v):
+        h, s, val = rgb_to_hsv(v)
+        s = np.clip(s * saturation, 0.0, 1.0)
+        h = h + hue
+        return hsv_to_rgb(h - np.floor(h), s, val)
+
+    def con(v):
+        m = v.mean(axis=(0, 1), keepdims=True)
+        return m + (v - m) * contrast
+    x = con(sat_hue(x)) if order == 1 else sat_hue(con(x))
+    return np.clip(x, 0.0, 255.0)
+
+
 def transform_reference(img: np.ndarray, op: ImageOp) -> np.ndarray:
     crop = img[op.top:op.top + op.ch, op.left:op.left + op.cw].astype(np.float64)
+    if op.flip:                       # the reference flips the crop, then resizes it
+        crop = crop[:, ::-1]
     my = _axis_matrix(op.ch, op.vh, op.oy, op.oh, op.method)
     mx = _axis_matrix(op.cw, op.vw, op.ox, op.ow, op.method)
     x = np.einsum("yi,ijc,xj->yxc", my, crop, mx)
     if op.distort_order:
-        x = x + op.brightness
-
-        def sat(v):
-            g = v.mean(axis=2, keepdims=True)
-            return g + (v - g) * op.saturation
-
-        def con(v):
-            m = v.mean(axis=(0, 1), keepdims=True)
-            return m + (v - m) * op.contrast
-        x = con(sat(x)) if op.distort_order == 1 else sat(con(x))
-        x = np.clip(x, 0.0, 255.0)
-    if op.flip:
-        x = x[:, ::-1]
+        x = distort_reference(x, op.distort_order, op.brightness, op.saturation, op.hue,
+                              op.contrast)
     x = x * op.scale + op.bias
     return x.astype(np.float16 if op.out_f16 else np.float32)

@@ -6,10 +6,12 @@ Image transforms follow the reference (T/preprocessing.py:130-307,653-737):
 * normalisation ``x / 127.5 - 1``;
 * ImageNet eval: resize so the short side covers 1.15x the target, centre crop;
 * ImageNet train: sample a distorted bounding box (object coverage >= 0.1, aspect ratio in
-  [3/4, 4/3], area in [0.05, 1], up to 100 attempts), crop, resize (bilinear / nearest / bicubic
-  / area, ``round_robin`` cycles through them by batch position), random horizontal flip,
-  optional colour distortion (brightness 32/255, saturation [0.5, 1.5], contrast [0.5, 1.5],
-  order alternating with batch position);
+  [3/4, 4/3], area in [0.05, 1], up to 100 attempts), crop, random horizontal flip, resize
+  (bilinear / nearest / bicubic / area, ``round_robin`` cycles through them by batch position);
+  with ``--distortions`` also the colour jitter (brightness 32/255, saturation [0.5, 1.5] and
+  hue +-0.2 in HSV, contrast [0.5, 1.5], order alternating with batch position);
+* training records pass through a 10 000-record shuffle buffer like the reference's
+  ``ds.shuffle(buffer_size=10000)``;
 * CIFAR-10 train: pad 4, random 32x32 crop, random flip; eval: centre crop / pad.
 
 A background ``ImageProducer`` keeps ``2 * batch_group_size`` batches staged
@@ -31,6 +33,10 @@ import torch
 from ..utils.cnn_util import ImageProducer
 from . import tfrecord
 from .inputs import InputSource
+
+# records held by the training shuffle buffer (ds.shuffle(buffer_size=10000),
+# T/preprocessing.py:536-537)
+SHUFFLE_BUFFER_SIZE = 10000
 
 _RESIZE = {"nearest": 0, "bilinear": 2, "bicubic": 3, "area": 4}  # PIL resample codes
 _ROUND_ROBIN = ["bilinear", "nearest", "bicubic", "area"]
@@ -92,41 +98,37 @@ def sample_distorted_bounding_box(ih: int, iw: int, bbox: Optional[Tuple[float, 
     return 0, 0, ih, iw
 
 
+def draw_color_distortion(batch_position: int, rng):
+    """(order, brightness delta, saturation factor, hue shift, contrast factor) of one example:
+    the random parameters of the reference's distort_color (T/preprocessing.py:268-307) -
+    brightness +-32/255, saturation and contrast in [0.5, 1.5], hue +-0.2 turns; even batch
+    positions apply saturation / hue before contrast, odd ones after."""
+    return (1 if batch_position % 2 == 0 else 2, rng.uniform(-32.0, 32.0), rng.uniform(0.5, 1.5),
+            rng.uniform(-0.2, 0.2), rng.uniform(0.5, 1.5))
+
+
 def distort_color(img: np.ndarray, batch_position: int, rng) -> np.ndarray:
-    """Brightness / saturation / contrast jitter on [0, 255] floats; the op order alternates with
-    the batch position (T/preprocessing.py:262-307)."""
-    x = img.astype(np.float32)
-
-    def brightness(v):
-        return v + rng.uniform(-32.0, 32.0)
-
-    def saturation(v):
-        g = v.mean(axis=2, keepdims=True)
-        return g + (v - g) * rng.uniform(0.5, 1.5)
-
-    def contrast(v):
-        m = v.mean(axis=(0, 1), keepdims=True)
-        return m + (v - m) * rng.uniform(0.5, 1.5)
-
-    ops = [brightness, saturation, contrast] if batch_position % 2 == 0 else \
-        [brightness, contrast, saturation]
-    for op in ops:
-        x = op(x)
-    return np.clip(x, 0.0, 255.0)
+    """Brightness / saturation / hue / contrast jitter on [0, 255] floats (NumPy path; the
+    native transform applies the same arithmetic)."""
+    from .native_image import distort_reference
+    return distort_reference(img.astype(np.float32), *draw_color_distortion(batch_position, rng)) \
+        .astype(np.float32)
 
 
 def train_image(img: np.ndarray, height: int, width: int, bbox, batch_position: int,
                 resize_method: str, distortions: bool, rng, distort_colors: bool = True):
-    if distortions:
-        top, left, h, w = sample_distorted_bounding_box(img.shape[0], img.shape[1], bbox, rng)
-        img = img[top:top + h, left:left + w]
-        img = _resize(img, height, width, get_image_resize_method(resize_method, batch_position))
-        if rng.random() < 0.5:
-            img = img[:, ::-1]
-        if distort_colors:
-            img = distort_color(img, batch_position, rng)
-    else:
-        img = _resize(img, height, width, get_image_resize_method(resize_method, batch_position))
+    """Training transform of the reference (T/preprocessing.py:192-265): sample a distorted
+    bounding box, crop, random horizontal flip, resize - always - and, with --distortions, the
+    colour jitter. (NumPy / PIL path; the native transform is used when the host library is
+    built.)"""
+    top, left, h, w = sample_distorted_bounding_box(img.shape[0], img.shape[1], bbox, rng)
+    img = img[top:top + h, left:left + w]
+    if rng.random() < 0.5:
+        img = img[:, ::-1]
+    img = _resize(np.ascontiguousarray(img), height, width,
+                  get_image_resize_method(resize_method, batch_position))
+    if distortions and distort_colors:
+        img = distort_color(img, batch_position, rng)
     return np.ascontiguousarray(img)
 
 
@@ -159,6 +161,16 @@ def parse_example_proto(record: bytes):
                 float(ex["image/object/bbox/ymax"][0]), float(ex["image/object/bbox/xmax"][0]))
     text = ex.get("image/class/text", [b""])
     return ex["image/encoded"][0], label, bbox, text[0] if text else b""
+
+
+_logged = set()
+
+
+def _log_once(msg: str) -> None:
+    if msg not in _logged:
+        _logged.add(msg)
+        from ..utils import log_util
+        log_util.log_fn(msg)
 
 
 def _decode_workers(params) -> int:
@@ -248,6 +260,8 @@ class ImagenetSource(_BatchSource):
         self.p = params
         self.records = self._record_iter()
         self.cached = None
+        self._shuffle_n = SHUFFLE_BUFFER_SIZE if train else 0
+        self._shuffle_buf = []
         from . import native_image
         self._native = native_image if native_image.available() else None
         super().__init__(params, batch, height, width, device, train, seed * 7919 + rank)
@@ -273,9 +287,24 @@ class ImagenetSource(_BatchSource):
         if self.p.datasets_repeat_cached_sample and self.cached is not None:
             record = self.cached
         else:
-            record = next(self.records)
+            record = self._next_record()
             self.cached = record
         return record, self.rng.getrandbits(62)
+
+    def _next_record(self):
+        """Next record of the stream; in training through a shuffle buffer: a uniformly drawn
+        buffered record leaves, the next record of the stream takes its place."""
+        if self._shuffle_n <= 0:
+            return next(self.records)
+        buf = self._shuffle_buf
+        if len(buf) < self._shuffle_n:
+            _log_once("Filling up shuffle buffer (this may take a while): %d records"
+                      % self._shuffle_n)
+            while len(buf) < self._shuffle_n:
+                buf.append(next(self.records))
+        i = self.rng.randrange(len(buf))
+        record, buf[i] = buf[i], next(self.records)
+        return record
 
     def _fill(self, images, labels, position, job) -> None:
         record, seed = job
@@ -297,11 +326,10 @@ class ImagenetSource(_BatchSource):
         crop, window, flip, distort = None, None, False, None
         resized = (self.h, self.w)
         if self.train:
+            crop = sample_distorted_bounding_box(img.shape[0], img.shape[1], bbox, rng)
+            flip = rng.random() < 0.5
             if p.distortions:
-                crop = sample_distorted_bounding_box(img.shape[0], img.shape[1], bbox, rng)
-                flip = rng.random() < 0.5
-                distort = (1 if position % 2 == 0 else 2, rng.uniform(-32.0, 32.0),
-                           rng.uniform(0.5, 1.5), rng.uniform(0.5, 1.5))
+                distort = draw_color_distortion(position, rng)
         else:
             resized, window = eval_geometry(img.shape[0], img.shape[1], self.h, self.w)
         op = ni.make_op(img, crop, resized, window, method, flip, distort,

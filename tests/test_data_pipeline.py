@@ -172,9 +172,9 @@ def _native_image():
 def test_native_image_transform_matches_numpy_restatement(method):
     ni = _native_image()
     img = np.random.RandomState(3).randint(0, 256, (75, 101, 3)).astype(np.uint8)
-    cases = [((5, 7, 60, 80), (32, 48), None, True, (1, 12.0, 1.3, 0.7)),     # train crop
+    cases = [((5, 7, 60, 80), (32, 48), None, True, (1, 12.0, 1.3, 0.07, 0.7)),     # train crop
              (None, (90, 121), (13, 28, 64, 64), False, None),                 # eval centre crop
-             ((0, 0, 20, 18), (64, 64), None, False, (2, -20.0, 0.6, 1.4)),    # upsampling
+             ((0, 0, 20, 18), (64, 64), None, False, (2, -20.0, 0.6, -0.15, 1.4)),    # upsampling
              ((5, 5, 1, 1), (7, 9), None, True, None)]                         # 1-pixel crop
     for crop, resized, window, flip, distort in cases:
         op = ni.make_op(img, crop, resized, window, method, flip, distort)
@@ -204,7 +204,7 @@ def test_native_image_transform_constant_images_and_bad_geometry():
             ev = ni.transform(img, ni.make_op(img, None, (rh, rw), win, method))
             assert ev.shape == (64, 64, 3) and np.abs(ev - want).max() < 1e-3
             tr = ni.transform(img, ni.make_op(img, (9, 12, 50, 70), (48, 56), None, method, True,
-                                              (1, 10.0, 1.2, 0.8)))
+                                              (1, 10.0, 1.2, 0.1, 0.8)))
             assert tr.shape == (48, 56, 3) and np.abs(tr - want).max() <= 50 / 127.5
     img = np.zeros((10, 10, 3), np.uint8)
     with pytest.raises(ValueError, match="bad geometry"):
@@ -214,11 +214,12 @@ def test_native_image_transform_constant_images_and_bad_geometry():
     assert pp.eval_geometry(375, 500, 224, 224) == ((257, 343), (16, 59, 224, 224))
 
 
-def test_batches_do_not_depend_on_the_number_of_decode_threads(tmp_path):
+def test_batches_do_not_depend_on_the_number_of_decode_threads(tmp_path, monkeypatch):
     """Examples of a batch are decoded / transformed on a thread pool; augmentation seeds are
     drawn in order on the producer thread, so 1 thread and 4 threads give identical batches."""
     from kf_benchmarks_b200 import datasets
     _native_image()
+    monkeypatch.setattr(pp, "SHUFFLE_BUFFER_SIZE", 0)
     d = str(tmp_path / "imagenet")
     os.makedirs(d)
     _write_imagenet(d, "train", n=6, shards=1)
@@ -237,3 +238,51 @@ def test_batches_do_not_depend_on_the_number_of_decode_threads(tmp_path):
     assert labels[:6] == [1, 2, 3, 4, 5, 1]           # record order is kept
     assert all(abs(float(img.min()) + 1) < 0.4 or abs(float(img.max()) - 1) < 0.4
                for img, _ in got[1])
+
+
+def test_training_records_go_through_a_shuffle_buffer(tmp_path, monkeypatch):
+    """ds.shuffle(buffer_size=10000) of the reference (T/preprocessing.py:536-537), here with a
+    4-record buffer over a 6-record stream: every record keeps turning up, the order is not the
+    file order, and it is reproducible from the seed; evaluation is not shuffled."""
+    from kf_benchmarks_b200 import datasets
+    monkeypatch.setattr(pp, "SHUFFLE_BUFFER_SIZE", 4)
+    d = str(tmp_path / "imagenet")
+    os.makedirs(d)
+    for subset in ("train", "validation"):
+        recs = [tfrecord.encode_example({"image/encoded": [_jpeg(40 * i)],
+                                         "image/class/label": [i + 1]}) for i in range(6)]
+        tfrecord.write_records(os.path.join(d, "%s-00000-of-00001" % subset), recs)
+    ds = datasets.create_dataset(d, "imagenet")
+    p = P.make_params(model="trivial", data_dir=d, data_name="imagenet", device="cpu",
+                      data_format="NHWC", batch_size=6, datasets_num_private_threads=1)
+
+    def labels(train, seed):
+        src = pp.ImagenetSource(p, ds, 6, 16, 16, "cpu", train, seed, 0, 1)
+        out = torch.cat([src.next_batch()[1].clone() for _ in range(5)]).tolist()
+        src.close()
+        return out
+    a, b, c = labels(True, 3), labels(True, 3), labels(True, 4)
+    assert a == b and a != c
+    assert set(a) == {1, 2, 3, 4, 5, 6} and a != [1, 2, 3, 4, 5, 6] * 5
+    assert labels(False, 3) == [1, 2, 3, 4, 5, 6] * 5
+
+
+def test_hsv_colour_jitter_arithmetic():
+    import colorsys
+    from kf_benchmarks_b200.data import native_image as ni
+    rng = np.random.RandomState(0)
+    x = rng.rand(5, 7, 3)
+    h, s, v = ni.rgb_to_hsv(x)
+    for i in range(5):
+        for j in range(7):
+            assert np.allclose((h[i, j], s[i, j], v[i, j]), colorsys.rgb_to_hsv(*x[i, j]), atol=1e-9)
+    assert np.allclose(ni.hsv_to_rgb(h, s, v), x, atol=1e-9)
+    img = x * 255.0
+    same = ni.distort_reference(img, 1, 0.0, 1.0, 0.0, 1.0)
+    assert np.allclose(same, img, atol=1e-6)                       # neutral parameters
+    red = np.zeros((2, 2, 3))
+    red[..., 0] = 200.0
+    green = ni.distort_reference(red, 2, 0.0, 1.0, 1.0 / 3.0, 1.0)   # a third of a turn
+    assert np.allclose(green[..., 1], 200.0) and np.allclose(green[..., [0, 2]], 0.0, atol=1e-6)
+    grey = ni.distort_reference(img, 1, 0.0, 0.0, 0.1, 1.0)          # saturation 0 -> value
+    assert np.allclose(grey, np.repeat(img.max(axis=2, keepdims=True), 3, axis=2), atol=1e-6)
