@@ -28,7 +28,8 @@ typedef struct {
   int top, left, ch, cw;   // crop rectangle in source pixels
   int vh, vw;              // size the crop is resized to
   int oy, ox, oh, ow;      // window of that resized image which is produced (eval centre crop)
-  int method;              // 0 bilinear, 1 nearest, 2 bicubic, 3 area
+  int method;              // 0 bilinear, 1 nearest, 2 bicubic, 3 area,
+                           // 4 tf.image.crop_and_resize (bilinear) of the float `box`
   int flip;                // mirror the crop horizontally before it is resized
   int distort_order;       // 0 none, 1 brightness - saturation/hue - contrast,
                            // 2 brightness - contrast - saturation/hue (T/preprocessing.py:281-303)
@@ -38,6 +39,13 @@ typedef struct {
   float contrast;          // factor around the per-channel image mean
   float scale, bias;       // out = value * scale + bias
   int out_f16;             // 0: float32 output, 1: IEEE binary16 output
+  // method 4: normalised (y0, x0, y1, x1) window of the whole image, sampled like
+  // tf.image.crop_and_resize: in = y0 (H-1) + i (y1-y0)(H-1)/(oh-1), zero outside the image;
+  // `flip` then mirrors the output. crop / resized / window fields are ignored except oh, ow.
+  float box[4];
+  int per_channel;         // 1: out = value * scale3[k] + bias3[k] instead of scale / bias
+  float scale3[3], bias3[3];
+  int no_clamp;            // 1: the colour jitter does not clamp to [0, 255] at the end
 } kfb_image_op;
 }
 
@@ -95,6 +103,53 @@ inline const uint8_t* px(const uint8_t* src, const kfb_image_op& op, int y, int 
   const int sx = op.flip ? op.cw - 1 - x : x;
   return src + static_cast<size_t>(op.top + y) * op.src_stride +
          static_cast<size_t>(op.left + sx) * 3;
+}
+
+// tf.image.crop_and_resize, bilinear, extrapolation value 0 (T/ssd_dataloader.py:218-223)
+void crop_and_resize(const uint8_t* src, const kfb_image_op& op, float* out) {
+  const int oh = op.oh, ow = op.ow, H = op.ih, W = op.iw;
+  const float y0 = op.box[0], x0 = op.box[1], y1 = op.box[2], x1 = op.box[3];
+  const float hs = oh > 1 ? (y1 - y0) * (H - 1) / (oh - 1) : 0.f;
+  const float ws = ow > 1 ? (x1 - x0) * (W - 1) / (ow - 1) : 0.f;
+  struct XT {
+    int lo, hi;
+    float w;
+    bool ok;
+  };
+  std::vector<XT> xt(ow);
+  for (int x = 0; x < ow; ++x) {
+    const int xx = op.flip ? ow - 1 - x : x;
+    const float in = ow > 1 ? x0 * (W - 1) + xx * ws : 0.5f * (x0 + x1) * (W - 1);
+    xt[x].ok = in >= 0.f && in <= static_cast<float>(W - 1);
+    xt[x].lo = static_cast<int>(std::floor(in));
+    xt[x].hi = static_cast<int>(std::ceil(in));
+    xt[x].w = in - std::floor(in);
+  }
+  for (int y = 0; y < oh; ++y) {
+    float* o = out + static_cast<size_t>(y) * ow * 3;
+    const float in = oh > 1 ? y0 * (H - 1) + y * hs : 0.5f * (y0 + y1) * (H - 1);
+    if (in < 0.f || in > static_cast<float>(H - 1)) {
+      std::memset(o, 0, sizeof(float) * ow * 3);
+      continue;
+    }
+    const int top = static_cast<int>(std::floor(in)), bot = static_cast<int>(std::ceil(in));
+    const float wy = in - std::floor(in);
+    const uint8_t* rt = src + static_cast<size_t>(top) * op.src_stride;
+    const uint8_t* rb = src + static_cast<size_t>(bot) * op.src_stride;
+    for (int x = 0; x < ow; ++x) {
+      if (!xt[x].ok) {
+        o[3 * x] = o[3 * x + 1] = o[3 * x + 2] = 0.f;
+        continue;
+      }
+      const uint8_t *a = rt + 3 * xt[x].lo, *b = rt + 3 * xt[x].hi;
+      const uint8_t *c = rb + 3 * xt[x].lo, *d = rb + 3 * xt[x].hi;
+      for (int k = 0; k < 3; ++k) {
+        const float t = a[k] + (b[k] - a[k]) * xt[x].w;
+        const float u = c[k] + (d[k] - c[k]) * xt[x].w;
+        o[3 * x + k] = t + (u - t) * wy;
+      }
+    }
+  }
 }
 
 void resize_window(const uint8_t* src, const kfb_image_op& op, float* out) {
@@ -269,7 +324,7 @@ inline void hsv_to_rgb(float h, float s, float v, float* p) {
 }
 
 struct Jitter {
-  bool on = false;
+  bool on = false, clamp = true;
   int order = 0;
   float b = 0.f, fs = 1.f, dh = 0.f, fc = 1.f;
   float mean[3] = {0.f, 0.f, 0.f};  // channel means at the point where contrast is applied
@@ -288,6 +343,7 @@ struct Jitter {
   void prepare(const kfb_image_op& op, float* img, size_t npix) {
     on = op.distort_order != 0;
     if (!on) return;
+    clamp = op.no_clamp == 0;
     order = op.distort_order;
     b = op.brightness;
     fs = op.saturation;
@@ -321,7 +377,8 @@ struct Jitter {
       for (int k = 0; k < 3; ++k) v[k] = mean[k] + (v[k] + b - mean[k]) * fc;
       sat_hue(v);
     }
-    for (int k = 0; k < 3; ++k) v[k] = std::min(std::max(v[k], 0.f), 255.f);
+    if (clamp)
+      for (int k = 0; k < 3; ++k) v[k] = std::min(std::max(v[k], 0.f), 255.f);
   }
 };
 
@@ -338,7 +395,14 @@ int kfb_image_transform(const uint8_t* src, const kfb_image_op* opp, void* out) 
     return -1;
   }
   const kfb_image_op& op = *opp;
-  if (op.ih <= 0 || op.iw <= 0 || op.src_stride < op.iw * 3 || op.ch <= 0 || op.cw <= 0 ||
+  const bool car = op.method == 4;
+  if (car) {
+    if (op.ih <= 0 || op.iw <= 0 || op.src_stride < op.iw * 3 || op.oh <= 0 || op.ow <= 0) {
+      std::snprintf(g_err, sizeof(g_err), "image_transform: bad geometry (image %dx%d, output %dx%d)",
+                    op.ih, op.iw, op.oh, op.ow);
+      return -1;
+    }
+  } else if (op.ih <= 0 || op.iw <= 0 || op.src_stride < op.iw * 3 || op.ch <= 0 || op.cw <= 0 ||
       op.top < 0 || op.left < 0 || op.top + op.ch > op.ih || op.left + op.cw > op.iw ||
       op.vh <= 0 || op.vw <= 0 || op.oh <= 0 || op.ow <= 0 || op.oy < 0 || op.ox < 0 ||
       op.oy + op.oh > op.vh || op.ox + op.ow > op.vw || op.method < 0 || op.method > 3) {
@@ -352,7 +416,11 @@ int kfb_image_transform(const uint8_t* src, const kfb_image_op* opp, void* out) 
   const size_t npix = static_cast<size_t>(op.oh) * op.ow;
   if (g_plane.size() < npix * 3) g_plane.resize(npix * 3);
   float* plane = g_plane.data();
-  resize_window(src, op, plane);
+  if (car) {
+    crop_and_resize(src, op, plane);
+  } else {
+    resize_window(src, op, plane);
+  }
   Jitter jitter;
   jitter.prepare(op, plane, npix);
   const int ow = op.ow;
@@ -362,12 +430,17 @@ int kfb_image_transform(const uint8_t* src, const kfb_image_op* opp, void* out) 
       float p[3];
       jitter.apply(row + 3 * x, p);
       const size_t o = (static_cast<size_t>(y) * ow + x) * 3;
+      if (op.per_channel) {
+        for (int k = 0; k < 3; ++k) p[k] = p[k] * op.scale3[k] + op.bias3[k];
+      } else {
+        for (int k = 0; k < 3; ++k) p[k] = p[k] * op.scale + op.bias;
+      }
       if (op.out_f16) {
         uint16_t* d = static_cast<uint16_t*>(out) + o;
-        for (int k = 0; k < 3; ++k) d[k] = to_half(p[k] * op.scale + op.bias);
+        for (int k = 0; k < 3; ++k) d[k] = to_half(p[k]);
       } else {
         float* d = static_cast<float*>(out) + o;
-        for (int k = 0; k < 3; ++k) d[k] = p[k] * op.scale + op.bias;
+        for (int k = 0; k < 3; ++k) d[k] = p[k];
       }
     }
   }

@@ -29,6 +29,10 @@ typedef struct {
   int ih, iw, src_stride, top, left, ch, cw, vh, vw, oy, ox, oh, ow, method, flip, distort_order;
   float brightness, saturation, hue, contrast, scale, bias;
   int out_f16;
+  float box[4];
+  int per_channel;
+  float scale3[3], bias3[3];
+  int no_clamp;
 } kfb_image_op;
 int kfb_image_transform(const uint8_t* src, const kfb_image_op* op, void* out);
 }
@@ -202,7 +206,19 @@ int main(int argc, char** argv) {
         op.ow = 1 + r(op.vw);
         op.oy = r(op.vh - op.oh + 1);
         op.ox = r(op.vw - op.ow + 1);
-        op.method = it % 4;
+        op.method = it % 5;
+        if (op.method == 4) {  // crop_and_resize window, partly outside the image now and then
+          op.box[0] = -0.1f + 0.01f * r(60);
+          op.box[1] = -0.1f + 0.01f * r(60);
+          op.box[2] = op.box[0] + 0.01f * (1 + r(70));
+          op.box[3] = op.box[1] + 0.01f * (1 + r(70));
+          op.per_channel = 1;
+          for (int k = 0; k < 3; ++k) {
+            op.scale3[k] = 0.01f;
+            op.bias3[k] = -1.f;
+          }
+          op.no_clamp = r(2);
+        }
         op.flip = r(2);
         op.distort_order = r(3);
         op.brightness = 5.f;

@@ -18,6 +18,7 @@ import numpy as np
 from . import native_reader
 
 METHODS = {"bilinear": 0, "nearest": 1, "bicubic": 2, "area": 3}
+CROP_AND_RESIZE = 4     # tf.image.crop_and_resize of a normalised float window (SSD)
 
 
 class ImageOp(ctypes.Structure):
@@ -26,7 +27,10 @@ class ImageOp(ctypes.Structure):
                                             "vh", "vw", "oy", "ox", "oh", "ow", "method", "flip",
                                             "distort_order")] + \
                [(n, ctypes.c_float) for n in ("brightness", "saturation", "hue", "contrast",
-                                              "scale", "bias")] + [("out_f16", ctypes.c_int)]
+                                              "scale", "bias")] + \
+               [("out_f16", ctypes.c_int), ("box", ctypes.c_float * 4),
+                ("per_channel", ctypes.c_int), ("scale3", ctypes.c_float * 3),
+                ("bias3", ctypes.c_float * 3), ("no_clamp", ctypes.c_int)]
 
 
 _fn = None
@@ -71,6 +75,28 @@ def make_op(img: np.ndarray, crop: Optional[Tuple[int, int, int, int]], resized:
     if distort is not None:
         op.distort_order, op.brightness, op.saturation, op.hue, op.contrast = distort
     op.scale, op.bias, op.out_f16 = scale, bias, int(bool(out_f16))
+    return op
+
+
+def make_crop_and_resize_op(img: np.ndarray, box, size: Tuple[int, int], flip: bool = False,
+                            distort: Optional[Tuple[int, float, float, float, float]] = None,
+                            scale3=(1.0, 1.0, 1.0), bias3=(0.0, 0.0, 0.0), clamp: bool = True,
+                            out_f16: bool = False) -> ImageOp:
+    """tf.image.crop_and_resize of the normalised window ``box`` = (y0, x0, y1, x1) to ``size``,
+    then mirror, colour jitter (on the 0..255 scale) and per-channel ``v * scale3 + bias3``:
+    the SSD training transform (T/ssd_dataloader.py:218-254, T/preprocessing.py:792-800)."""
+    op = ImageOp()
+    op.ih, op.iw, op.src_stride = img.shape[0], img.shape[1], img.strides[0]
+    op.oh, op.ow = int(size[0]), int(size[1])
+    op.method, op.flip = CROP_AND_RESIZE, int(bool(flip))
+    op.box = (ctypes.c_float * 4)(*[float(v) for v in box])
+    if distort is not None:
+        op.distort_order, op.brightness, op.saturation, op.hue, op.contrast = distort
+    op.per_channel = 1
+    op.scale3 = (ctypes.c_float * 3)(*[float(v) for v in scale3])
+    op.bias3 = (ctypes.c_float * 3)(*[float(v) for v in bias3])
+    op.no_clamp = int(not clamp)
+    op.out_f16 = int(bool(out_f16))
     return op
 
 
@@ -165,7 +191,7 @@ def hsv_to_rgb(h, s, v) -> np.ndarray:
 
 
 def distort_reference(x: np.ndarray, order: int, brightness: float, saturation: float,
-                      hue: float, contrast: float) -> np.ndarray:
+                      hue: float, contrast: float, clamp: bool = True) -> np.ndarray:
     """Colour jitter on 0..255 floats with the arithmetic of tf.image.adjust_brightness /
     adjust_saturation / adjust_hue / adjust_contrast; order 1 = brightness, saturation + hue,
     contrast; order 2 = brightness, contrast, saturation + hue; clipped at the end
@@ -182,10 +208,41 @@ def distort_reference(x: np.ndarray, order: int, brightness: float, saturation: 
         m = v.mean(axis=(0, 1), keepdims=True)
         return m + (v - m) * contrast
     x = con(sat_hue(x)) if order == 1 else sat_hue(con(x))
-    return np.clip(x, 0.0, 255.0)
+    return np.clip(x, 0.0, 255.0) if clamp else x
+
+
+def _crop_and_resize_reference(img: np.ndarray, op: ImageOp) -> np.ndarray:
+    H, W = img.shape[:2]
+    y0, x0, y1, x1 = [np.float32(v) for v in op.box]
+    out = np.zeros((op.oh, op.ow, 3), np.float64)
+    f32 = np.float32
+    for i in range(op.oh):
+        iy = y0 * f32(H - 1) + f32(i) * ((y1 - y0) * f32(H - 1) / f32(op.oh - 1)) if op.oh > 1 \
+            else f32(0.5) * (y0 + y1) * f32(H - 1)
+        if iy < 0 or iy > H - 1:
+            continue
+        t, b, wy = int(np.floor(iy)), int(np.ceil(iy)), float(iy - np.floor(iy))
+        for j in range(op.ow):
+            jj = op.ow - 1 - j if op.flip else j
+            ix = x0 * f32(W - 1) + f32(jj) * ((x1 - x0) * f32(W - 1) / f32(op.ow - 1)) \
+                if op.ow > 1 else f32(0.5) * (x0 + x1) * f32(W - 1)
+            if ix < 0 or ix > W - 1:
+                continue
+            lo, hi, wx = int(np.floor(ix)), int(np.ceil(ix)), float(ix - np.floor(ix))
+            top = img[t, lo] + (img[t, hi].astype(np.float64) - img[t, lo]) * wx
+            bot = img[b, lo] + (img[b, hi].astype(np.float64) - img[b, lo]) * wx
+            out[i, j] = top + (bot - top) * wy
+    return out
 
 
 def transform_reference(img: np.ndarray, op: ImageOp) -> np.ndarray:
+    if op.method == CROP_AND_RESIZE:
+        x = _crop_and_resize_reference(img, op)
+        if op.distort_order:
+            x = distort_reference(x, op.distort_order, op.brightness, op.saturation, op.hue,
+                                  op.contrast, clamp=not op.no_clamp)
+        x = x * np.asarray(list(op.scale3)) + np.asarray(list(op.bias3))
+        return x.astype(np.float16 if op.out_f16 else np.float32)
     crop = img[op.top:op.top + op.ch, op.left:op.left + op.cw].astype(np.float64)
     if op.flip:                       # the reference flips the crop, then resizes it
         crop = crop[:, ::-1]

@@ -111,7 +111,15 @@ def _crop_and_resize(image: np.ndarray, bounds, size: int) -> np.ndarray:
 
 
 def ssd_crop(image, boxes, classes, rng: np.random.RandomState):
-    """IoU-biased random crop (T/ssd_dataloader.py:113-227): every pass either keeps the whole
+    """IoU-biased random crop: geometry from ``ssd_crop_geometry``, pixels through the PIL
+    stand-in of crop_and_resize (the native path resamples with the exact TF arithmetic)."""
+    bounds, kept, cls = ssd_crop_geometry(boxes, classes, rng)
+    return _crop_and_resize(image, bounds, IMAGE_SIZE), kept, cls
+
+
+def ssd_crop_geometry(boxes, classes, rng: np.random.RandomState):
+    """-> (window (y0, x0, y1, x1), boxes kept / clipped / renormalised, their classes).
+    IoU-biased random crop (T/ssd_dataloader.py:113-227): every pass either keeps the whole
     image (p = 1/7) or draws 50 windows (sides in [0.3, 1]) and a minimum IoU from
     {0, .1, .3, .5, .7, .9}; a window is valid if height/width < 2, every box overlaps it by
     more than the minimum IoU and at least one box centre lies inside; the last valid window
@@ -143,7 +151,7 @@ def ssd_crop(image, boxes, classes, rng: np.random.RandomState):
     span = np.array([bounds[2] - bounds[0], bounds[3] - bounds[1]] * 2, np.float32)
     off = np.array([bounds[0], bounds[1]] * 2, np.float32)
     kept = (kept - off) / span
-    return _crop_and_resize(image, bounds, IMAGE_SIZE), kept.astype(np.float32), classes[mask]
+    return bounds, kept.astype(np.float32), classes[mask]
 
 
 def random_horizontal_flip(image, boxes, rng: np.random.RandomState):
@@ -269,6 +277,34 @@ def preprocess_train(image_u8: np.ndarray, boxes: np.ndarray, labels: np.ndarray
     return image, enc_boxes, enc_classes, num_matched
 
 
+def preprocess_train_native(image_u8: np.ndarray, boxes: np.ndarray, labels: np.ndarray,
+                            rng: np.random.RandomState, out_ptr: int, out_f16: bool):
+    """``preprocess_train`` with the pixel work (crop_and_resize, flip, colour jitter,
+    normalisation, cast) in one native call that writes the image at ``out_ptr``
+    (csrc/host/image_ops.cpp). Draws from ``rng`` in the same order as ``preprocess_train``.
+    Returns (encoded boxes, encoded classes, matched anchors)."""
+    from . import native_image as ni
+    classes = np.asarray([CLASS_MAP[int(c)] if 0 <= int(c) < len(CLASS_MAP) else -1
+                          for c in labels], np.float32)
+    bounds, boxes, classes = ssd_crop_geometry(boxes.astype(np.float32), classes, rng)
+    flip = rng.uniform() < 0.5
+    if flip:
+        boxes = np.stack([boxes[:, 0], 1 - boxes[:, 3], boxes[:, 2], 1 - boxes[:, 1]], 1)
+    # colour jitter of color_jitter(): brightness, contrast, saturation, hue - no clamp
+    brightness = 255.0 * rng.uniform(-0.125, 0.125)
+    contrast = rng.uniform(0.5, 1.5)
+    saturation = rng.uniform(0.5, 1.5)
+    hue = rng.uniform(-0.05, 0.05)
+    distort = (2, brightness, saturation, hue, contrast)
+    mean, std = np.asarray(NORMALIZATION_MEAN, np.float64), np.asarray(NORMALIZATION_STD, np.float64)
+    op = ni.make_crop_and_resize_op(image_u8, bounds, (IMAGE_SIZE, IMAGE_SIZE), flip, distort,
+                                    scale3=1.0 / (255.0 * std), bias3=-mean / std, clamp=False,
+                                    out_f16=out_f16)
+    ni.transform_into(image_u8, op, out_ptr)
+    enc_classes, enc_boxes, num_matched = encode_labels(boxes, classes)
+    return enc_boxes, enc_classes, num_matched
+
+
 def preprocess_eval(image_u8: np.ndarray, boxes: np.ndarray, labels: np.ndarray):
     """Resize to 300x300, normalise, pad / trim the ground truth to 200 boxes
     (T/preprocessing.py:811-834)."""
@@ -316,20 +352,48 @@ def coco_files(data_dir: str, subset: str):
 
 class CocoInputSource:
     """Real-data input source for SSD-300: decodes, augments and labels on the host, yields
-    pinned batches (image fp16 NHWC, encoded boxes, encoded classes, matched counts)."""
+    pinned batches (image fp16 NHWC, encoded boxes, encoded classes, matched counts).
+
+    Training batches are produced ahead of the consumer by a background thread; the examples of
+    a batch are spread over a thread pool (JPEG decode, the native image transform and the
+    NumPy anchor matching all release the GIL for most of their time). Every example gets its
+    own seed, drawn in record order, and rejected examples (no box left after the crop) are
+    dropped in that order, so batches do not depend on the number of threads. Evaluation walks
+    the files once, in order, on the caller's thread."""
     host_resident = True
 
     def __init__(self, data_dir: str, batch: int, device, seed: int, rank: int = 0, world: int = 1,
-                 train: bool = True):
-        from . import tfrecord
+                 train: bool = True, num_threads: Optional[int] = None):
+        from concurrent.futures import ThreadPoolExecutor
+        from . import native_image, tfrecord
+        from ..utils.cnn_util import ImageProducer
         self.batch, self.train = batch, train
         self.rng = np.random.RandomState(seed * 9973 + rank)
         files = coco_files(data_dir, "train" if train else "val")
         self.files = files[rank::world] or files
         self._tf = tfrecord
         self._it = self._records()
-        self.pin = torch.device(device).type == "cuda"
+        self.pin = torch.device(device).type == "cuda" and torch.cuda.is_available()
         self.bytes_per_step = batch * (IMAGE_SIZE * IMAGE_SIZE * 3 * 2 + NUM_SSD_BOXES * 5 * 4 + 4)
+        self._native = native_image if native_image.available() else None
+        if num_threads is None:
+            local = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")) or 1)
+            num_threads = max(1, min(16, (os.cpu_count() or 2) // max(local, 1)))
+        self._pool = ThreadPoolExecutor(num_threads, thread_name_prefix="kfb-coco") \
+            if (train and num_threads > 1) else None
+        self._producer = None
+        if train:
+            self._ring = [self._alloc_slot() for _ in range(5)]
+            self._ring_pos = 0
+            self._producer = ImageProducer(self._make_train_batch, 1)
+            self._producer.start()
+
+    def _alloc_slot(self):
+        b, pin = self.batch, self.pin
+        return (torch.empty((b, IMAGE_SIZE, IMAGE_SIZE, 3), dtype=torch.float16, pin_memory=pin),
+                torch.empty((b, NUM_SSD_BOXES, 4), dtype=torch.float32, pin_memory=pin),
+                torch.empty((b, NUM_SSD_BOXES, 1), dtype=torch.float32, pin_memory=pin),
+                torch.empty((b,), dtype=torch.float32, pin_memory=pin))
 
     def _records(self):
         while True:
@@ -342,8 +406,56 @@ class CocoInputSource:
             if not self.train:
                 return
 
+    # ---- training: pooled, produced ahead ---------------------------------------------------
+    def _train_example(self, job):
+        """Worker: (record, seed) -> (image fp16 [300,300,3], boxes, classes, matched) or None."""
+        rec, seed = job
+        rng = np.random.RandomState(seed)
+        img, boxes, labels, _, _ = parse_coco_example(rec)
+        if len(boxes) == 0:
+            return None
+        if self._native is not None:
+            image = torch.empty((IMAGE_SIZE, IMAGE_SIZE, 3), dtype=torch.float16)
+            eb, ec, nm = preprocess_train_native(np.ascontiguousarray(img), boxes, labels, rng,
+                                                 image.data_ptr(), True)
+        else:
+            im, eb, ec, nm = preprocess_train(img, boxes, labels, rng)
+            image = torch.from_numpy(im).half()
+        if nm <= 0:
+            return None
+        return image, eb, ec, nm
+
+    def _make_train_batch(self):
+        slot = self._ring[self._ring_pos % len(self._ring)]
+        self._ring_pos += 1
+        filled = 0
+        while filled < self.batch:
+            jobs = [(next(self._it), int(self.rng.randint(0, 2 ** 31 - 1)))
+                    for _ in range(self.batch - filled)]
+            results = list(self._pool.map(self._train_example, jobs)) if self._pool is not None \
+                else [self._train_example(j) for j in jobs]
+            for r in results:
+                if r is None:
+                    continue
+                image, eb, ec, nm = r
+                slot[0][filled] = image
+                slot[1][filled] = torch.from_numpy(eb)
+                slot[2][filled] = torch.from_numpy(ec)
+                slot[3][filled] = float(nm)
+                filled += 1
+        return slot
+
+    def close(self):
+        if self._producer is not None:
+            self._producer.done()
+        if self._pool is not None:
+            self._pool.shutdown(wait=False)
+
+    # ---- evaluation: one ordered pass ---------------------------------------------------------
     def next_batch(self):
-        imgs, bxs, cls, nms, extra = [], [], [], [], []
+        if self.train:
+            return self._producer.get()
+        imgs, bxs, cls, extra = [], [], [], []
         while len(imgs) < self.batch:
             try:
                 rec = next(self._it)
@@ -352,25 +464,14 @@ class CocoInputSource:
                     raise
                 break
             img, boxes, labels, sid, raw = parse_coco_example(rec)
-            if self.train:
-                if len(boxes) == 0:
-                    continue
-                image, eb, ec, nm = preprocess_train(img, boxes, labels, self.rng)
-                if nm <= 0:
-                    continue
-                nms.append(nm)
-            else:
-                image, eb, ec = preprocess_eval(img, boxes, labels)
-                extra.append((sid, raw))
+            image, eb, ec = preprocess_eval(img, boxes, labels)
+            extra.append((sid, raw))
             imgs.append(image)
             bxs.append(eb)
             cls.append(ec)
         out = [torch.from_numpy(np.stack(imgs)).half(), torch.from_numpy(np.stack(bxs)),
                torch.from_numpy(np.stack(cls))]
-        if self.train:
-            out.append(torch.from_numpy(np.asarray(nms, np.float32)))
-        else:
-            self.last_eval_meta = extra
+        self.last_eval_meta = extra
         if self.pin:
             out = [t.pin_memory() for t in out]
         return tuple(out)

@@ -6,6 +6,7 @@ import os
 
 import numpy as np
 import pytest
+import torch
 
 from kf_benchmarks_b200 import coco_metric
 from kf_benchmarks_b200.data import ssd_dataloader as sd
@@ -267,3 +268,45 @@ def test_backbone_loading_and_graph_dumps(tmp_path):
     assert "cg/affine0/weights" in doc["variables"]
     part = json.loads((tmp_path / "part_0.json").read_text())
     assert part["rank"] == 0 and part["buckets"]
+
+
+def test_native_crop_and_resize_and_ssd_train_transform(tmp_path):
+    """The SSD training image goes through one native call (tf.image.crop_and_resize arithmetic,
+    mirror, un-clamped colour jitter, per-channel normalisation): checked against the NumPy
+    restatement, and the pooled COCO source yields the same batches with 1 and 4 threads."""
+    from kf_benchmarks_b200 import build as build_lib
+    from kf_benchmarks_b200.data import native_image as ni
+    build_lib.build_host()
+    assert ni.available()
+    img = np.random.RandomState(1).randint(0, 256, (48, 64, 3)).astype(np.uint8)
+    cases = [((0.1, 0.2, 0.8, 0.9), False, None, True),
+             ((0.0, 0.0, 1.0, 1.0), True, (2, 10.0, 1.2, 0.03, 0.8), False),
+             ((-0.2, 0.3, 0.7, 1.3), True, (2, -8.0, 0.7, -0.04, 1.3), True)]   # partly outside
+    for box, flip, distort, clamp in cases:
+        op = ni.make_crop_and_resize_op(img, box, (30, 31), flip, distort, (1 / 255 / 0.2,) * 3,
+                                        (-2.0, -1.9, -1.8), clamp)
+        got, want = ni.transform(img, op), ni.transform_reference(img, op)
+        assert got.shape == (30, 31, 3) and np.abs(got - want).max() < 1e-4
+    # the identity window reproduces the image (then normalised)
+    op = ni.make_crop_and_resize_op(img, (0, 0, 1, 1), (48, 64), scale3=(1, 1, 1))
+    assert np.array_equal(ni.transform(img, op), img.astype(np.float32))
+
+    rng = np.random.RandomState(0)
+    recs = []
+    for i in range(6):
+        im = rng.randint(0, 255, (90, 120, 3)).astype(np.uint8)
+        boxes = np.array([[0.1, 0.1, 0.6, 0.5], [0.3, 0.4, 0.9, 0.95]], np.float32)
+        recs.append(_coco_record(im, boxes, [1, 18], 100 + i))
+    tfrecord.write_records(str(tmp_path / "train-00000-of-00001"), recs)
+    got = {}
+    for threads in (1, 4):
+        src = sd.CocoInputSource(str(tmp_path), 4, "cpu", seed=5, num_threads=threads)
+        got[threads] = [tuple(t.clone() for t in src.next_batch()) for _ in range(3)]
+        src.close()
+    for a, b in zip(got[1], got[4]):
+        assert all(torch.equal(x, y) for x, y in zip(a, b))
+    images, boxes, classes, nm = got[1][0]
+    assert images.dtype == torch.float16 and images.shape == (4, 300, 300, 3)
+    assert float(nm.min()) >= 1 and torch.isfinite(images.float()).all()
+    # normalised pixels: (v - mean) / std of values in [0, 1] plus jitter stay within a few units
+    assert float(images.float().abs().max()) < 6
