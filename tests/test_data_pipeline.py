@@ -286,3 +286,50 @@ def test_hsv_colour_jitter_arithmetic():
     assert np.allclose(green[..., 1], 200.0) and np.allclose(green[..., [0, 2]], 0.0, atol=1e-6)
     grey = ni.distort_reference(img, 1, 0.0, 0.0, 0.1, 1.0)          # saturation 0 -> value
     assert np.allclose(grey, np.repeat(img.max(axis=2, keepdims=True), 3, axis=2), atol=1e-6)
+
+
+_REF_DATA = "/root/reference/scripts/tf_cnn_benchmarks/test_data"
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(_REF_DATA, "fake_tf_record_data")),
+                    reason="the reference tree (with its TensorFlow-written test records) is "
+                           "not present on this machine")
+def test_tensorflow_written_records_of_the_reference_tree(tmp_path):
+    """The reference ships ten small ImageNet-style TFRecord shards written by TensorFlow itself
+    (T/test_data/fake_tf_record_data, used by its testImagenetPreprocessor): both record readers
+    accept their CRCs, both Example parsers agree on every field, the JPEGs decode, and a
+    training + evaluation run on that directory works (data files only - no reference code)."""
+    import glob
+    from kf_benchmarks_b200.data import native_reader
+    d = os.path.join(_REF_DATA, "fake_tf_record_data")
+    files = sorted(glob.glob(os.path.join(d, "*")))
+    assert len(files) == 10
+    total = 0
+    for f in files:
+        recs = list(tfrecord.read_records(f, check_crc=True))
+        assert recs == list(native_reader.RecordReader([f], num_threads=1))
+        for r in recs:
+            buf, label, bbox, text = pp.parse_example_proto(r)          # native scanner
+            ex = tfrecord.parse_example(r)                              # Python codec
+            assert buf == ex["image/encoded"][0] and label == ex["image/class/label"][0]
+            assert 0 <= label <= 1000 and text == ex["image/class/text"][0]
+            img = pp.decode_jpeg(buf)
+            assert img.ndim == 3 and img.shape[2] == 3
+            assert img.shape[0] == ex["image/height"][0] and img.shape[1] == ex["image/width"][0]
+            if "train" in os.path.basename(f):
+                assert bbox is not None and 0 <= bbox[0] < bbox[2] <= 1 and 0 <= bbox[1] < bbox[3] <= 1
+            total += 1
+    assert total == 640
+    kw = dict(model="trivial", data_dir=d, data_name="imagenet", device="cpu", data_format="NHWC",
+              batch_size=8, num_batches=3, num_warmup_batches=0, display_every=1,
+              train_dir=str(tmp_path / "ckpt"))
+    stats, _ = _run(kw)
+    assert stats["num_steps"] == 3 and np.isfinite(stats["last_average_loss"])
+    stats, _ = _run(dict(kw, eval=True, num_batches=4))
+    assert stats["num_examples"] == 32
+    # the constant-colour JPEGs of the reference's preprocessing test stay constant
+    for name, color in (("black_image.jpg", 0), ("white_image.jpg", 255)):
+        with open(os.path.join(_REF_DATA, "images", name), "rb") as fh:
+            img = pp.decode_jpeg(fh.read())
+        ev = pp.eval_image(img, 64, 64, 0, "bilinear")
+        assert np.abs(ev.astype(int) - color).max() <= 2
