@@ -217,7 +217,14 @@ struct PeerCtx {
   float* src[kMaxRanks];      // per-rank source arena (gradients, or weights for SMA)
   float* reduced[kMaxRanks];  // per-rank landing buffer for reduced shards
   uint32_t* flags[kMaxRanks]; // per-rank flag page
+  // Optional device-resident offset added to every call's sequence number (kfb_set_seq_base):
+  // a captured CUDA graph replays the same by-value `seq`, the counter moves it forward.
+  const uint32_t* seq_base;
 };
+
+__device__ __forceinline__ uint32_t seq_offset(const PeerCtx& c) {
+  return c.seq_base != nullptr ? *reinterpret_cast<const volatile uint32_t*>(c.seq_base) : 0u;
+}
 
 __device__ __forceinline__ void wait_flags(const PeerCtx& c, int kind, uint32_t seq) {
   // thread t < nranks polls the flag written by rank t into MY page
@@ -269,6 +276,7 @@ __global__ void __launch_bounds__(512)
                             float sma_alpha, int reduce_only, const float* __restrict__ stage,
                             long long stage_stride) {
   resolve_dyn(h, dyn);
+  seq += seq_offset(c);
   const int n = c.nranks;
   // Reduce-scatter sources: the peers' arenas (pull over NVLink), or - when the weight-gradient
   // kernels already pushed their tiles here (kfb_*_rs) - this rank's n local staging slots.
@@ -424,6 +432,7 @@ __global__ void __launch_bounds__(512)
                                  const int* __restrict__ skip_flag, float sma_alpha,
                                  int reduce_only) {
   resolve_dyn(h, dyn);
+  seq += seq_offset(c);
   const int n = c.nranks;
   // --- announce: my source data for [offset, offset+count) is final ---
   if (blockIdx.x == 0 && threadIdx.x < n)
@@ -501,6 +510,7 @@ __global__ void __launch_bounds__(512)
 __global__ void __launch_bounds__(512)
     broadcast_pull_kernel(PeerCtx c, int root, long long offset, long long count, uint32_t seq,
                           float* __restrict__ dst, __half* __restrict__ dst16) {
+  seq += seq_offset(c);
   if (blockIdx.x == 0 && threadIdx.x < c.nranks)
     st_release_sys(c.flags[threadIdx.x] + FLAG_READY * kMaxRanks + c.rank, seq);
   wait_flags(c, FLAG_READY, seq);
@@ -517,6 +527,7 @@ __global__ void __launch_bounds__(512)
 }
 
 __global__ void device_barrier_kernel(PeerCtx c, uint32_t seq) {
+  seq += seq_offset(c);
   if (threadIdx.x < c.nranks) {
     __threadfence_system();
     st_release_sys(c.flags[threadIdx.x] + FLAG_BARRIER * kMaxRanks + c.rank, seq);
@@ -527,6 +538,7 @@ __global__ void device_barrier_kernel(PeerCtx c, uint32_t seq) {
 // flag <- OR over ranks of flag (auto loss scale: every rank must take the same skip decision,
 // T/variable_mgr.py:321-332). Each rank posts its value into every page, then reads all.
 __global__ void flag_or_kernel(PeerCtx c, uint32_t seq, int* __restrict__ flag) {
+  seq += seq_offset(c);
   constexpr int kPostWord = kCounterWord + 8;  // [src_rank] words after the arrival counters
   if (threadIdx.x < c.nranks) {
     *reinterpret_cast<volatile uint32_t*>(c.flags[threadIdx.x] + kPostWord + c.rank) =
@@ -601,12 +613,19 @@ __global__ void __launch_bounds__(512)
   }
 }
 
+// device counter added to the sequence numbers of every collective launched by this process
+// (one process drives one GPU); null = sequence numbers are taken as passed
+static const uint32_t* g_seq_base = nullptr;
+
+__global__ void seq_advance_kernel(uint32_t* counter, uint32_t k) { *counter += k; }
+
 static int fill_peer_ctx(PeerCtx* c, int rank, int nranks, void* const* src, void* const* reduced,
                          void* const* flags) {
   KFB_REQUIRE(nranks >= 1 && nranks <= kMaxRanks && rank >= 0 && rank < nranks,
               "peer ctx: bad rank %d / %d", rank, nranks);
   c->rank = rank;
   c->nranks = nranks;
+  c->seq_base = g_seq_base;
   for (int r = 0; r < kMaxRanks; ++r) {
     c->src[r] = r < nranks ? (float*)src[r] : nullptr;
     c->reduced[r] = (r < nranks && reduced) ? (float*)reduced[r] : nullptr;
@@ -634,6 +653,23 @@ static HyperParams make_hyper(const kfb_hyper* hp) {
 using namespace kfb;
 
 extern "C" int kfb_flag_page_bytes(void) { return 4096; }
+
+// Sequence numbers from device memory (multi-rank CUDA graphs): after kfb_set_seq_base(p) every
+// collective of this process adds *p (a uint32 in device memory, 0 at first) to the `seq` it is
+// given. A captured step ends with kfb_seq_advance(p, k), k = collectives per step, so each
+// replay of the same captured constants runs with fresh sequence numbers; the host mirrors the
+// counter and passes `absolute - mirror` for calls outside the graph. Null switches it off.
+extern "C" int kfb_set_seq_base(const void* counter) {
+  g_seq_base = static_cast<const uint32_t*>(counter);
+  return 0;
+}
+
+extern "C" int kfb_seq_advance(void* counter, unsigned k, void* stream) {
+  KFB_REQUIRE(counter != nullptr, "seq_advance: null counter");
+  seq_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(static_cast<uint32_t*>(counter), k);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
 
 extern "C" int kfb_optimizer_step(float* w, const float* g, float* m, float* v, void* w16,
                                   long long n, const kfb_hyper* hp, const float* dyn,

@@ -212,6 +212,11 @@ int kfb_loss_scale_update(float* state, int* flag, int inc_every, float* dyn,
  * nranks device pointers (peer mappings); seq must increase by one per collective call and
  * be identical on every rank. */
 int kfb_flag_page_bytes(void);
+/* Device-resident sequence offset for multi-rank CUDA graphs (B200 addition; the reference has no
+ * graph replay): once set, every collective below adds the uint32 at `counter` (device memory)
+ * to its `seq`; kfb_seq_advance bumps it on a stream (the last node of a captured step). */
+int kfb_set_seq_base(const void* counter);
+int kfb_seq_advance(void* counter, unsigned k, void* stream);
 int kfb_allreduce_update(int mode, int rank, int nranks, void* const* src, void* const* reduced,
                          void* const* flags, long long offset, long long count, unsigned seq,
                          float* w, const float* g_local, float* m, float* v, void* w16,

@@ -476,11 +476,21 @@ class BenchmarkCNN:
 
     def _graph_eligible(self) -> bool:
         """--cuda_graph: the whole step (forward, loss, backward, fused update) is captured once
-        and replayed. Limited to a single rank with device-resident inputs: the P2P kernels take
-        a per-call sequence number that a replay could not advance."""
-        return (self.params.cuda_graph and self.device.type == "cuda" and self.world <= 1 and
+        and replayed, with device-resident inputs. Several ranks can do so when the gradient
+        exchange is the overlapped P2P all-reduce: the kernels then take part of their per-call
+        sequence number from a device counter that the captured step advances
+        (P2PComm.enable_device_seq). That path has not run on hardware yet and is switched on
+        with KFB_MULTI_RANK_GRAPH=1."""
+        if not (self.params.cuda_graph and self.device.type == "cuda" and
                 not getattr(self.input_source, "host_resident", False) and
-                not self.engine.auto_loss_scale)
+                not self.engine.auto_loss_scale):
+            return False
+        if self.world <= 1:
+            return True
+        from .parallel.comm import P2PComm
+        eng = self.engine
+        return (os.environ.get("KFB_MULTI_RANK_GRAPH") == "1" and isinstance(self.comm, P2PComm)
+                and eng._can_overlap() and not eng.fused_push)
 
     def _step_graphed(self) -> None:
         ex, eng = self.executor, self.engine
@@ -499,18 +509,34 @@ class BenchmarkCNN:
                 eng.finish_step()
                 self.global_step += 1
                 return
+            multi = self.world > 1
+            counter = self.comm.enable_device_seq() if multi else None
             torch.cuda.synchronize(self.device)
+            if multi:
+                self.comm.barrier()               # every rank starts capturing at the same step
+            seq0 = self.comm.seq if multi else 0
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 eng.begin_step(lr)
                 ex.forward(True)
                 ex.loss_backward(loss_scale=eng.loss_scale, on_grads_ready=eng.on_grads_ready)
                 eng.finish_step()
+                if multi:
+                    # last node: move the device part of the sequence numbers past this step
+                    self._graph_collectives = self.comm.seq - seq0
+                    from .ops import native
+                    import ctypes
+                    native.call("seq_advance", native.ptr(counter),
+                                ctypes.c_uint(self._graph_collectives), native.stream_ptr())
+            if multi:
+                self.comm.seq = seq0              # nothing ran during capture
             self._graph = g
             _log("Captured the training step in a CUDA graph")
         eng.push_dynamic_hyper(lr)
         self._last_lr = lr
         self._graph.replay()
+        if self.world > 1:
+            self.comm.graph_replayed(self._graph_collectives)
         self.global_step += 1
 
     def _step(self, train: bool = True, backward: bool = True) -> None:

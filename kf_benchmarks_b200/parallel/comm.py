@@ -145,6 +145,10 @@ class P2PComm(Comm):
         if self.nvls:
             self.kind = "nvls"
         self.seq = 0
+        # device-resident part of the sequence numbers (multi-rank CUDA graphs, see
+        # enable_device_seq): the kernels add the device counter, the host mirrors it
+        self._seq_counter = None
+        self._dev_base = 0
         flag_bytes = int(self.lib.kfb_flag_page_bytes())
         self.flags = self.symm_alloc(flag_bytes // 4, torch.int32)
         self._flag_ptrs = self._ptr_array(self.flags)
@@ -241,8 +245,26 @@ class P2PComm(Comm):
         return float(t.item())
 
     def next_seq(self) -> int:
+        """Sequence number of the next collective as the kernels must be given it: the absolute
+        count minus what the device counter already holds (0 unless enable_device_seq)."""
         self.seq += 1
-        return self.seq
+        return (self.seq - self._dev_base) & 0xFFFFFFFF
+
+    def enable_device_seq(self) -> torch.Tensor:
+        """Keep part of the sequence numbers in device memory so that a captured CUDA graph,
+        which replays the same by-value numbers, still presents fresh ones: every collective
+        adds the counter, the captured step ends with ``kfb_seq_advance`` and ``graph_replayed``
+        moves the host mirror. Must be called on every rank at the same point."""
+        if self._seq_counter is None:
+            self._seq_counter = torch.zeros(1, dtype=torch.int32, device=self.device)
+            torch.cuda.synchronize(self.device)
+            native.check(self.lib.kfb_set_seq_base(ptr(self._seq_counter)), "set_seq_base")
+        return self._seq_counter
+
+    def graph_replayed(self, collectives_per_step: int) -> None:
+        """Host mirror of the device counter after one replay of a captured step."""
+        self.seq += collectives_per_step
+        self._dev_base += collectives_per_step
 
     def device_barrier(self, stream=None) -> None:
         s = ctypes.c_void_p((stream or torch.cuda.current_stream(self.device)).cuda_stream)
@@ -265,6 +287,9 @@ class P2PComm(Comm):
                     self.lib.kfb_ipc_close(ctypes.c_void_p(a))
         self._allocs = []
         self._symm_keep = []
+        if self._seq_counter is not None:
+            self.lib.kfb_set_seq_base(None)
+            self._seq_counter = None
 
 
 def create_comm(params, device) -> Comm:

@@ -137,3 +137,37 @@ def test_nvls_symmetric_allocation_bookkeeping(monkeypatch):
     FakeHandle.multicast_ptr = 0
     with pytest.raises(native.KfbError, match="NVLS"):
         P2PComm._symm_alloc_multicast(comm, 1000, torch.float32)
+
+
+def test_sequence_numbers_stay_consecutive_across_graph_replays():
+    """Multi-rank CUDA graphs: a captured step replays the same by-value sequence numbers, the
+    kernels add a device counter that the step's last node advances. Model the device side and
+    check that the effective numbers (what the flag protocol compares) increase by one per
+    collective through eager calls, capture, replays and eager calls again."""
+    import types
+    from kf_benchmarks_b200.parallel.comm import P2PComm
+    comm = types.SimpleNamespace(seq=0, _dev_base=0)
+    device_counter = 0
+    effective = []
+
+    def launch(rel):                      # what a kernel does with the number it is given
+        effective.append((rel + device_counter) & 0xFFFFFFFF)
+
+    for _ in range(5):                    # warm-up steps, eager
+        launch(P2PComm.next_seq(comm))
+    seq0 = comm.seq
+    captured = [P2PComm.next_seq(comm) for _ in range(3)]     # capture: nothing executes
+    k = comm.seq - seq0
+    comm.seq = seq0
+    for _ in range(4):                    # replays
+        for rel in captured:
+            launch(rel)
+        device_counter += k               # kfb_seq_advance, last node of the graph
+        P2PComm.graph_replayed(comm, k)
+    for _ in range(2):                    # e.g. the barrier at exit
+        launch(P2PComm.next_seq(comm))
+    assert effective == list(range(1, 5 + 4 * 3 + 2 + 1))
+    # wrap-around of the 32-bit counter keeps the differences intact
+    comm = types.SimpleNamespace(seq=2 ** 32 - 2, _dev_base=7)
+    a, b, c = (P2PComm.next_seq(comm) for _ in range(3))
+    assert ((b - a) & 0xFFFFFFFF) == 1 and ((c - b) & 0xFFFFFFFF) == 1

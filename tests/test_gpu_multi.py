@@ -134,3 +134,31 @@ def test_nvls_all_reduce_matches_the_pull_kernels(tmp_path, mode):
     a, b = outs["p2p"][0], outs["nvls"][0]
     cos = float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b)))
     assert cos > 0.9999 and np.abs(a - b).max() < 5e-2
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
+@pytest.mark.skipif(os.environ.get("KFB_MULTI_RANK_GRAPH") != "1",
+                    reason="multi-rank CUDA graphs were written without GPU time left in the "
+                           "round; set KFB_MULTI_RANK_GRAPH=1 to run (and to enable) them")
+def test_multi_rank_cuda_graph_matches_the_eager_step(tmp_path):
+    """--cuda_graph on 2 ranks (device-resident sequence offset for the P2P flag protocol):
+    same trained variables as the eager step, replicas bit-identical."""
+    import json
+    import numpy as np
+    outs = {}
+    for graph in (False, True):
+        d = tmp_path / ("graph" if graph else "eager")
+        d.mkdir()
+        kw = dict(model="resnet20", data_name="cifar10", batch_size=32, use_fp16=True,
+                  optimizer="momentum", init_learning_rate=0.05, num_batches=8,
+                  num_warmup_batches=0, variable_update="replicated", num_gpus=2,
+                  cuda_graph=graph)
+        res = _launch(2, [os.path.join(ROOT, "tests", "helpers", "rank_worker.py"), json.dumps(kw),
+                          str(d)])
+        assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+        outs[graph] = [np.load(str(d / ("rank%d.npz" % r)))["w"] for r in range(2)]
+        assert np.isfinite(outs[graph][0]).all()
+        assert np.array_equal(outs[graph][0], outs[graph][1])
+    a, b = outs[False][0], outs[True][0]
+    cos = float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b)))
+    assert cos > 0.9999 and np.abs(a - b).max() < 5e-2

@@ -36,4 +36,14 @@ if [ "$N" -ge 2 ]; then
   echo "== NVLS all-reduce (--comm_impl=nvls) on $N GPUs =="
   timeout 1800 python tools/nvls_check.py "$N" > gpurun_out/pending_nvls_check.log 2>&1
   grep -E "NVLS_CHECK|replicas|p2p_check|Average|per all-reduce|FAILED|==" gpurun_out/pending_nvls_check.log
+  echo "== multi-rank CUDA graph (device-resident sequence offset) on 2 GPUs =="
+  KFB_MULTI_RANK_GRAPH=1 timeout 900 python -m pytest tests/test_gpu_multi.py -q -m gpu \
+    -k multi_rank_cuda_graph > gpurun_out/pending_multi_rank_graph.log 2>&1
+  tail -3 gpurun_out/pending_multi_rank_graph.log
+  for g in "" "--cuda_graph"; do
+    KFB_MULTI_RANK_GRAPH=1 timeout 900 python -m kf_benchmarks_b200.parallel.launcher -np "$N" -- \
+      -m kf_benchmarks_b200.cli --model=mobilenet --batch_size=64 --use_fp16 --optimizer=momentum \
+      --variable_update=replicated --num_gpus="$N" --num_batches=40 --num_warmup_batches=10 $g \
+      2>&1 | grep -E "total images/sec|Captured" | sed "s/^/mobilenet $g: /"
+  done
 fi
