@@ -421,10 +421,11 @@ class UpdateEngine:
 
     def _allreduce_call(self, mode: int, lo: int, count: int, h, skip_flag, stream) -> None:
         """One fused all-reduce(+update) over [lo, lo+count): mode 0 gradients + optimizer,
-        1 SMA (source = weights), 2 reduce only. Pull kernel, or its NVLS form."""
+        1 SMA (source = weights), 2 reduce only. Pull kernel, or its NVLS form. ``self.dyn``
+        (null unless a CUDA graph is in use) carries the per-step learning rate / scale."""
         st, c = self.store, self.comm
         tail = (i64(lo), i64(count), ctypes.c_uint(c.next_seq()), ptr(st.w32), ptr(st.grad),
-                ptr(self.m), ptr(self.v), ptr(st.w16), ctypes.byref(h), None, skip_flag,
+                ptr(self.m), ptr(self.v), ptr(st.w16), ctypes.byref(h), ptr(self.dyn), skip_flag,
                 f32(self.params.sma_alpha if mode == 1 else 0.0), i32(0), self._s(stream))
         if self.nvls:
             native.call("allreduce_update_nvls", i32(mode), i32(c.rank), i32(c.size),
