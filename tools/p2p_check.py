@@ -187,6 +187,31 @@ def main():
     ok &= same
     print("[rank %d] %s stress: replicas bit-identical" % (rank, "PASS" if same else "FAIL"),
           flush=True)
+    # ---- 8. device-resident sequence offset (multi-rank CUDA graphs): the same by-value
+    #         numbers are presented three times, the device counter moves them forward ----
+    if os.environ.get("KFB_P2P_DEVSEQ", "1") == "1":
+        counter = comm.enable_device_seq()
+        w.copy_(rank_data(99, n, 60))
+        grad.copy_(rank_data(rank, n, 61))
+        comm.barrier()
+        h = make_hyper(0, lr=1e-3, scale=1.0, wd=0.0)
+        seq0 = comm.seq
+        fixed = [ctypes.c_uint(comm.next_seq()) for _ in range(2)]   # what a capture would bake in
+        k = comm.seq - seq0
+        comm.seq = seq0
+        half = (n // 2) // 128 * 128
+        for _ in range(3):                                           # three "replays"
+            ar(0, grad, i64(0), i64(half), fixed[0], ptr(w), ptr(grad), None, None, ptr(w16),
+               ctypes.byref(h), None, None, f32(0.0), i32(0), s)
+            ar(0, grad, i64(half), i64(n - half), fixed[1], ptr(w), ptr(grad), None, None,
+               ptr(w16), ctypes.byref(h), None, None, f32(0.0), i32(0), s)
+            native.call("seq_advance", ptr(counter), ctypes.c_uint(k), s)
+            comm.graph_replayed(k)
+        comm.device_barrier()                                        # an eager call afterwards
+        torch.cuda.synchronize()
+        gsum = sum(rank_data(r, n, 61) for r in range(world))
+        check("device sequence offset: 3 replays", w, rank_data(99, n, 60) - 3 * 1e-3 * gsum, 2e-5)
+        check("device counter value", counter.float(), torch.tensor([3.0 * k]), 0.0)
     allok = all(comm.allgather_object(bool(ok)))
     if rank == 0:
         print("P2P_CHECK %s" % ("ALL PASS" if allok else "FAILED"), flush=True)
