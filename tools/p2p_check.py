@@ -189,7 +189,7 @@ def main():
           flush=True)
     # ---- 8. device-resident sequence offset (multi-rank CUDA graphs): the same by-value
     #         numbers are presented three times, the device counter moves them forward ----
-    if os.environ.get("KFB_P2P_DEVSEQ", "1") == "1":
+    if os.environ.get("KFB_P2P_DEVSEQ") == "1":
         counter = comm.enable_device_seq()
         w.copy_(rank_data(99, n, 60))
         grad.copy_(rank_data(rank, n, 61))

@@ -36,6 +36,10 @@ if [ "$N" -ge 2 ]; then
   echo "== NVLS all-reduce (--comm_impl=nvls) on $N GPUs =="
   timeout 1800 python tools/nvls_check.py "$N" > gpurun_out/pending_nvls_check.log 2>&1
   grep -E "NVLS_CHECK|replicas|p2p_check|Average|per all-reduce|FAILED|==" gpurun_out/pending_nvls_check.log
+  echo "== device-resident sequence offset: p2p_check section 8 =="
+  KFB_P2P_DEVSEQ=1 timeout 900 python -m kf_benchmarks_b200.parallel.launcher -np "$N" -- \
+    tools/p2p_check.py > gpurun_out/pending_p2p_devseq.log 2>&1
+  grep -E "device sequence|device counter|P2P_CHECK" gpurun_out/pending_p2p_devseq.log
   echo "== multi-rank CUDA graph (device-resident sequence offset) on 2 GPUs =="
   KFB_MULTI_RANK_GRAPH=1 timeout 900 python -m pytest tests/test_gpu_multi.py -q -m gpu \
     -k multi_rank_cuda_graph > gpurun_out/pending_multi_rank_graph.log 2>&1
