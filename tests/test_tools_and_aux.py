@@ -179,3 +179,21 @@ def test_keras_style_benchmark_mode_writes_the_reference_record_schema(tmp_path)
     for r in recs:
         assert set(r) == cols and r["metrics_totaltime"] > 0 and r["gpu_info_count"] == 0
         assert r["cpu_info_numcores"] >= 1 and r["metrics_sampletype"] == "synthetic"
+
+
+def test_fake_imagenet_generator_and_pipeline_bench(tmp_path):
+    """tools/make_fake_imagenet.py (counterpart of T/test_data/tfrecord_image_generator.py) and
+    the host-side input benchmark built on it."""
+    d = str(tmp_path / "imnet")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_fake_imagenet.py"), d,
+                          "--images", "8", "--shards", "2", "--size", "60x80"],
+                         capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert sorted(os.listdir(d)) == ["train-00000-of-00002", "train-00001-of-00002",
+                                     "validation-00000-of-00002", "validation-00001-of-00002"]
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "input_pipeline_bench.py"), d,
+                          "--seconds", "1", "--batch_size", "4", "--image_size", "32",
+                          "--threads", "2", "--shuffle_buffer", "4"],
+                         capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert "images/sec" in res.stdout and "2 decode threads" in res.stdout
