@@ -1,0 +1,79 @@
+#!/bin/bash
+# One-call refresh of the measured evidence under profiles/ for the current build (1 GPU):
+#   1. plain bench run (must exit 0 before anything is profiled)       -> profiles/bench_1gpu_<tag>.json
+#   2. launch list of one training step with device time + DRAM bytes  -> profiles/resnet50_bs256_launches_<tag>.txt
+#   3. ncu --set full on the heaviest kernels (3 launches each)         -> gpurun_out/prof_<name>.ncu-rep,
+#      selected raw metrics                                             -> profiles/ncu_<tag>_<name>.csv
+#   4. per-class roofline against the new launch list                   -> profiles/roofline_resnet50_bs256_<tag>.md
+# Usage (on the GPU box, e.g. through gpurun):  bash tools/capture_profiles.sh r2a
+# Numbers printed by runs under ncu are never bench values.
+set -u
+cd "$(dirname "$0")/.."
+TAG=${1:-new}
+mkdir -p gpurun_out profiles
+CMD="python tools/profile_step.py --model resnet50 --batch_size 256 --steps 3"
+
+echo "== 1. bench (plain) =="
+timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err || {
+  echo "bench failed"; tail -5 gpurun_out/bench_$TAG.err; exit 1; }
+tail -1 gpurun_out/bench_$TAG.json > profiles/bench_1gpu_$TAG.json
+python - "$TAG" <<'PY'
+import json, sys
+d = json.loads(open("profiles/bench_1gpu_%s.json" % sys.argv[1]).read())
+print("%.0f img/s, %.2f ms/step, e2e %s, clocks %s" %
+      (d["value"], d["ms_per_step"], (d.get("e2e") or {}).get("value"), d.get("clocks")))
+PY
+
+echo "== 2. launch list of one step =="
+$CMD > gpurun_out/plain.log 2>&1 || { echo "profile_step failed"; tail -5 gpurun_out/plain.log; exit 1; }
+PER=$(grep -o "launches per step (approx): [0-9]*" gpurun_out/plain.log | grep -o "[0-9]*$")
+PER=${PER:-543}
+# skip build-time launches + the first two steps; capture exactly one step
+TOTAL=$(ncu --metrics gpu__time_duration.sum --clock-control none --csv \
+          --log-file gpurun_out/launches_all_$TAG.csv $CMD > gpurun_out/ncu_count.log 2>&1;
+        grep -c '"gpu__time_duration.sum"' gpurun_out/launches_all_$TAG.csv)
+SKIP=$((TOTAL - PER))
+echo "launches in the run: $TOTAL, per step: $PER, skipping $SKIP"
+ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum \
+    --clock-control none -s "$SKIP" -c "$PER" --csv --log-file gpurun_out/launches_$TAG.csv \
+    $CMD > gpurun_out/ncu_launches.log 2>&1
+python tools/summarize_launches.py gpurun_out/launches_$TAG.csv \
+    > profiles/resnet50_bs256_launches_$TAG.txt && head -12 profiles/resnet50_bs256_launches_$TAG.txt
+
+echo "== 3. ncu --set full on the heaviest kernels =="
+for spec in "gemm:gemm_tcgen05_kernel" "bnbwd:bn_bwd_apply_kernel" "bnred:channel_reduce_kernel" \
+            "bnapply:bn_apply_kernel"; do
+  name=${spec%%:*}; pat=${spec##*:}
+  ncu --set full --clock-control none --import-source on -k regex:$pat -s 60 -c 3 -f \
+      -o gpurun_out/prof_${TAG}_$name $CMD > gpurun_out/ncu_$name.log 2>&1
+  if [ -f gpurun_out/prof_${TAG}_$name.ncu-rep ]; then
+    ncu -i gpurun_out/prof_${TAG}_$name.ncu-rep --page raw --csv 2>/dev/null | python - "$TAG" "$name" <<'PY'
+import csv, sys
+tag, name = sys.argv[1], sys.argv[2]
+keep = ("gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_tensor_subpipe_hmma_cycles_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
+        "lts__t_sector_hit_rate.pct", "sm__inst_executed_pipe_uniform", "smsp__issue_active.avg.pct_of_peak_sustained_active")
+rows = list(csv.reader(sys.stdin))
+if len(rows) > 2:
+    hdr = rows[0]
+    cols = [i for i, h in enumerate(hdr) if h in ("ID", "Kernel Name") or any(h.startswith(k) for k in keep)]
+    with open("profiles/ncu_%s_%s.csv" % (tag, name), "w", newline="") as f:
+        w = csv.writer(f)
+        for r in rows:
+            w.writerow([r[i][:120] for i in cols if i < len(r)])
+    print("profiles/ncu_%s_%s.csv: %d launches, %d metrics" % (tag, name, len(rows) - 2, len(cols)))
+else:
+    print("no rows for", name)
+PY
+  else
+    echo "no report for $name"; tail -3 gpurun_out/ncu_$name.log
+  fi
+done
+
+echo "== 4. roofline =="
+MS=$(python -c "import json;print(json.loads(open('profiles/bench_1gpu_$TAG.json').read())['ms_per_step'])")
+python tools/roofline_model.py --launches profiles/resnet50_bs256_launches_$TAG.txt --step_ms "$MS" \
+    > profiles/roofline_resnet50_bs256_$TAG.md && tail -14 profiles/roofline_resnet50_bs256_$TAG.md
