@@ -197,3 +197,30 @@ def test_fake_imagenet_generator_and_pipeline_bench(tmp_path):
                          capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stderr[-2000:]
     assert "images/sec" in res.stdout and "2 decode threads" in res.stdout
+
+
+def test_bench_reference_arm_and_clock_sampler(tmp_path, monkeypatch):
+    """bench.py contract pieces that need no GPU: `--impl reference` prints one JSON line with
+    `unavailable` and exits 0; the nvidia-smi sampler parses clocks / throttle reasons."""
+    import json
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference",
+                          "--gpus", "1", "--steps", "2", "--warmup", "1"],
+                         capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    d = json.loads(res.stdout.strip().splitlines()[-1])
+    assert d["impl"] == "reference" and isinstance(d["unavailable"], str) and d["unavailable"]
+
+    sys.path.insert(0, ROOT)
+    import bench
+    s = bench.ClockSampler(0)
+    s.proc = type("P", (), {"terminate": lambda self: None, "wait": lambda self, timeout=None: 0,
+                            "kill": lambda self: None})()
+    s.lines = ["0, 1965, 1965, 650.12, 0x0000000000000000, Not Active, Not Active, Not Active, Not Active",
+               "0, 1905, 1965, 980.50, 0x0000000000000004, Not Active, Not Active, Not Active, Active",
+               "0, 1935, 1965, 900.00, 0x0000000000000000, Not Active, Not Active, Not Active, Not Active",
+               "garbage line"]
+    out = s.stop()
+    assert out["sm_mhz"] == 1935.0 and out["sm_max_mhz"] == 1965.0 and out["samples"] == 3
+    assert out["reasons"] == ["sw_power_cap"] and out["power_w_max"] == 980.5
+    s.lines = ["0, 1200, 1965, 300.0, 0x8, Active, Active, Not Active, Not Active"]
+    assert bench.ClockSampler.stop(s)["reasons"] == ["hw_slowdown", "hw_thermal_slowdown"]
