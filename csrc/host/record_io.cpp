@@ -4,10 +4,16 @@
 // drives through RecordInput / tf.data (T/preprocessing.py:358-399, 601-609).
 //
 // Threading model: `num_threads` readers each own a disjoint subset of the files (file i goes
-// to reader i % num_threads, like a parallel interleave with cycle length = num_threads) and
-// push complete records into one bounded queue; the consumer pops. With one reader the order is
-// the file order; with several it is an interleaving. A reader that hits a corrupt record
-// stores the error and stops; the consumer sees it after draining what was queued before it.
+// to reader i % num_threads, like a parallel interleave with cycle length = num_threads). Two
+// ways to merge their output:
+//   * sloppy (kfb_rr_open): all readers push into one bounded queue, the consumer pops whatever
+//     came first - the order depends on thread timing
+//     (datasets_sloppy_parallel_interleave=true in the reference, T/preprocessing.py:516-519);
+//   * deterministic (kfb_rr_open2, deterministic=1): every reader has its own bounded queue and
+//     the consumer takes one record from each live reader in turn - tf.data's interleave with
+//     block length 1 - so the record order is a function of the file list alone.
+// With one reader both give the file order. A reader that hits a corrupt record stores the
+// error and stops; the consumer sees it after draining what was queued before it.
 #include <algorithm>
 #include <atomic>
 #include <condition_variable>
@@ -67,7 +73,12 @@ struct Reader {
 
   std::mutex mu;
   std::condition_variable not_empty, not_full;
-  std::deque<std::vector<uint8_t>> queue;
+  std::deque<std::vector<uint8_t>> queue;               // sloppy mode
+  bool deterministic = false;
+  std::vector<std::deque<std::vector<uint8_t>>> queues;  // deterministic mode: one per reader
+  std::vector<char> finished;                            // reader t has returned
+  int cursor = 0;                                        // reader the consumer takes from next
+  int per_reader_capacity = 1;
   int live_readers = 0;
   bool stop = false;
   std::string error;
@@ -79,8 +90,16 @@ struct Reader {
     if (error.empty()) error = msg;
   }
 
-  bool push(std::vector<uint8_t>&& rec) {
+  bool push(int tid, std::vector<uint8_t>&& rec) {
     std::unique_lock<std::mutex> lk(mu);
+    if (deterministic) {
+      auto& q = queues[tid];
+      not_full.wait(lk, [&] { return stop || static_cast<int>(q.size()) < per_reader_capacity; });
+      if (stop) return false;
+      q.emplace_back(std::move(rec));
+      not_empty.notify_all();  // the consumer may be waiting for exactly this reader
+      return true;
+    }
     not_full.wait(lk, [&] { return stop || static_cast<int>(queue.size()) < capacity; });
     if (stop) return false;
     queue.emplace_back(std::move(rec));
@@ -89,7 +108,7 @@ struct Reader {
   }
 
   // returns false on error / stop
-  bool read_file(const std::string& path) {
+  bool read_file(int tid, const std::string& path) {
     FILE* f = std::fopen(path.c_str(), "rb");
     if (!f) {
       fail("cannot open " + path);
@@ -131,7 +150,7 @@ struct Reader {
         ok = false;
         break;
       }
-      if (!push(std::move(rec))) {
+      if (!push(tid, std::move(rec))) {
         ok = false;
         break;
       }
@@ -148,12 +167,13 @@ struct Reader {
     do {
       if (shuffle) std::shuffle(mine.begin(), mine.end(), rng);
       for (const auto& p : mine) {
-        ok = read_file(p);
+        ok = read_file(tid, p);
         if (!ok) break;
       }
     } while (ok && repeat && !mine.empty());
     std::lock_guard<std::mutex> lk(mu);
     --live_readers;
+    if (deterministic) finished[tid] = 1;
     not_empty.notify_all();
   }
 };
@@ -174,8 +194,9 @@ uint32_t kfb_masked_crc32c(const void* data, uint64_t len) {
   return masked(crc32c(static_cast<const uint8_t*>(data), len));
 }
 
-void* kfb_rr_open(const char* const* paths, int npaths, int num_threads, int capacity,
-                  int check_crc, int repeat, int shuffle_files, uint64_t seed) {
+void* kfb_rr_open2(const char* const* paths, int npaths, int num_threads, int capacity,
+                   int check_crc, int repeat, int shuffle_files, uint64_t seed,
+                   int deterministic) {
   if (npaths <= 0 || paths == nullptr) {
     g_last_error = "record reader: no files";
     return nullptr;
@@ -189,8 +210,20 @@ void* kfb_rr_open(const char* const* paths, int npaths, int num_threads, int cap
   r->shuffle = shuffle_files != 0;
   r->seed = seed;
   r->live_readers = r->num_threads;
+  r->deterministic = deterministic != 0;
+  if (r->deterministic) {
+    r->queues.resize(r->num_threads);
+    r->finished.assign(r->num_threads, 0);
+    r->per_reader_capacity = std::max(1, r->capacity / r->num_threads);
+  }
   for (int t = 0; t < r->num_threads; ++t) r->threads.emplace_back([r, t] { r->run(t); });
   return r;
+}
+
+void* kfb_rr_open(const char* const* paths, int npaths, int num_threads, int capacity,
+                  int check_crc, int repeat, int shuffle_files, uint64_t seed) {
+  return kfb_rr_open2(paths, npaths, num_threads, capacity, check_crc, repeat, shuffle_files,
+                      seed, 0);
 }
 
 // 1: *data / *len describe the next record (valid until the next call on this handle);
@@ -198,6 +231,31 @@ void* kfb_rr_open(const char* const* paths, int npaths, int num_threads, int cap
 int kfb_rr_next(void* handle, const uint8_t** data, uint64_t* len) {
   auto* r = static_cast<Reader*>(handle);
   std::unique_lock<std::mutex> lk(r->mu);
+  if (r->deterministic) {
+    const int n = r->num_threads;
+    for (int tried = 0; tried < n;) {
+      const int t = r->cursor;
+      r->not_empty.wait(lk, [&] { return !r->queues[t].empty() || r->finished[t]; });
+      if (!r->queues[t].empty()) {
+        r->current = std::move(r->queues[t].front());
+        r->queues[t].pop_front();
+        r->cursor = (t + 1) % n;
+        r->not_full.notify_all();
+        *data = r->current.data();
+        *len = r->current.size();
+        return 1;
+      }
+      // reader t is exhausted (or failed): leave it out of the rotation from now on
+      r->cursor = (t + 1) % n;
+      ++tried;
+      if (!r->error.empty()) break;
+    }
+    if (!r->error.empty()) {
+      g_last_error = r->error;
+      return -1;
+    }
+    return 0;
+  }
   r->not_empty.wait(lk, [&] { return !r->queue.empty() || r->live_readers == 0; });
   if (r->queue.empty()) {
     if (!r->error.empty()) {

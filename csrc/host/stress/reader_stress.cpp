@@ -19,6 +19,8 @@ const char* kfb_host_last_error();
 uint32_t kfb_masked_crc32c(const void* data, uint64_t len);
 void* kfb_rr_open(const char* const* paths, int npaths, int num_threads, int capacity,
                   int check_crc, int repeat, int shuffle_files, uint64_t seed);
+void* kfb_rr_open2(const char* const* paths, int npaths, int num_threads, int capacity,
+                   int check_crc, int repeat, int shuffle_files, uint64_t seed, int deterministic);
 int kfb_rr_next(void* handle, const uint8_t** data, uint64_t* len);
 void kfb_rr_close(void* handle);
 int kfb_example_get_bytes(const uint8_t* data, uint64_t len, const char* key, const uint8_t** out,
@@ -109,6 +111,24 @@ int main(int argc, char** argv) {
             "pass %d: %llu records / %llu bytes", it, (unsigned long long)count,
             (unsigned long long)bytes);
     kfb_rr_close(h);
+    // (a2) deterministic interleave: same count, and the same order on a second pass
+    {
+      std::vector<uint64_t> order[2];
+      for (int pass = 0; pass < 2; ++pass) {
+        void* hd = kfb_rr_open2(cpaths.data(), nfiles, threads, capacity, 1, 0, 0, it, 1);
+        REQUIRE(hd != nullptr, "open2: %s", kfb_host_last_error());
+        while ((rc = kfb_rr_next(hd, &data, &len)) == 1) order[pass].push_back(len);
+        REQUIRE(rc == 0, "next (deterministic): %s", kfb_host_last_error());
+        kfb_rr_close(hd);
+      }
+      REQUIRE(order[0].size() == static_cast<size_t>(nfiles * per_file) && order[0] == order[1],
+              "deterministic interleave differs between passes");
+      // endless, closed early
+      void* hd = kfb_rr_open2(cpaths.data(), nfiles, threads, capacity, 1, 1, 0, it, 1);
+      const int take2 = static_cast<int>(rnd() % 300);
+      for (int k = 0; k < take2; ++k) REQUIRE(kfb_rr_next(hd, &data, &len) == 1, "repeat next (det)");
+      kfb_rr_close(hd);
+    }
     // (b) endless repeat, closed while the readers are blocked on a full queue or mid-file
     h = kfb_rr_open(cpaths.data(), nfiles, threads, capacity, 1, 1, 1, it + 100);
     REQUIRE(h != nullptr, "open: %s", kfb_host_last_error());

@@ -34,6 +34,8 @@ def _load():
         lib.kfb_rr_open.argtypes = [ctypes.POINTER(ctypes.c_char_p), ctypes.c_int, ctypes.c_int,
                                     ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_uint64]
+        lib.kfb_rr_open2.restype = ctypes.c_void_p
+        lib.kfb_rr_open2.argtypes = lib.kfb_rr_open.argtypes + [ctypes.c_int]
         lib.kfb_rr_next.restype = ctypes.c_int
         lib.kfb_rr_next.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p),
                                     ctypes.POINTER(ctypes.c_uint64)]
@@ -60,15 +62,18 @@ def masked_crc32c(data: bytes) -> int:
 class RecordReader:
     """Iterates the records of TFRecord files read by ``num_threads`` background threads
     (file i belongs to thread i % num_threads). ``repeat`` cycles forever, ``shuffle_files``
-    reshuffles each thread's file list every pass."""
+    reshuffles each thread's file list every pass. ``deterministic`` takes one record from each
+    reader in turn (tf.data interleave, block length 1): the order then depends on the file
+    list only; otherwise records come in whatever order the threads deliver them (sloppy)."""
 
     def __init__(self, paths: Sequence[str], num_threads: int = 1, capacity: int = 256,
                  check_crc: bool = True, repeat: bool = False, shuffle_files: bool = False,
-                 seed: int = 0):
+                 seed: int = 0, deterministic: bool = False):
         lib = _load()
         arr = (ctypes.c_char_p * len(paths))(*[os.fsencode(p) for p in paths])
-        self._h = lib.kfb_rr_open(arr, len(paths), int(num_threads), int(capacity),
-                                  int(check_crc), int(repeat), int(shuffle_files), int(seed))
+        self._h = lib.kfb_rr_open2(arr, len(paths), int(num_threads), int(capacity),
+                                   int(check_crc), int(repeat), int(shuffle_files), int(seed),
+                                   int(deterministic))
         if not self._h:
             raise IOError(lib.kfb_host_last_error().decode())
 

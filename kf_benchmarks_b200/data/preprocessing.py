@@ -268,13 +268,34 @@ class ImagenetSource(_BatchSource):
 
     def _record_iter(self):
         """Endless record stream. With the host library built, files are read and CRC-checked
-        by two background C++ threads, file i on thread i % 2 like a parallel interleave;
-        otherwise by the Python codec."""
+        by background C++ threads: --datasets_parallel_interleave_cycle_length of them (default
+        10 like the reference's interleave, T/preprocessing.py:516-519), file i on thread
+        i % n, merged one record per file in turn - or first come first served with
+        --datasets_sloppy_parallel_interleave. Otherwise the Python codec, file by file."""
         from . import native_reader
         if native_reader.available():
-            return iter(native_reader.RecordReader(self.files, num_threads=2, capacity=512,
-                                                   check_crc=True, repeat=True))
+            cycle = int(getattr(self.p, "datasets_parallel_interleave_cycle_length", None) or 10)
+            sloppy = bool(getattr(self.p, "datasets_sloppy_parallel_interleave", False))
+            caching = bool(getattr(self.p, "datasets_use_caching", False))
+            reader = native_reader.RecordReader(
+                self.files, num_threads=max(1, min(cycle, 16, len(self.files))), capacity=512,
+                check_crc=True, repeat=not caching, deterministic=not sloppy)
+            return self._cached(reader) if caching else iter(reader)
+        if getattr(self.p, "datasets_use_caching", False):
+            return self._cached(rec for path in self.files for rec in tfrecord.read_records(path))
         return self._python_record_iter()
+
+    @staticmethod
+    def _cached(one_pass):
+        """--datasets_use_caching (ds.cache(), T/preprocessing.py:533-534): the first pass over
+        the files keeps every record in host memory, later passes never touch the disk."""
+        cache = []
+        for rec in one_pass:
+            cache.append(rec)
+            yield rec
+        while cache:
+            for rec in cache:
+                yield rec
 
     def _python_record_iter(self):
         while True:

@@ -333,3 +333,23 @@ def test_tensorflow_written_records_of_the_reference_tree(tmp_path):
             img = pp.decode_jpeg(fh.read())
         ev = pp.eval_image(img, 64, 64, 0, "bilinear")
         assert np.abs(ev.astype(int) - color).max() <= 2
+
+
+def test_datasets_use_caching_reads_the_files_once(tmp_path, monkeypatch):
+    from kf_benchmarks_b200 import datasets
+    monkeypatch.setattr(pp, "SHUFFLE_BUFFER_SIZE", 0)
+    d = str(tmp_path / "imagenet")
+    os.makedirs(d)
+    _write_imagenet(d, "train", n=3, shards=2)
+    ds = datasets.create_dataset(d, "imagenet")
+    p = P.make_params(model="trivial", data_dir=d, data_name="imagenet", device="cpu",
+                      data_format="NHWC", batch_size=4, datasets_use_caching=True,
+                      datasets_num_private_threads=1)
+    src = pp.ImagenetSource(p, ds, 4, 16, 16, "cpu", True, 1, 0, 1)
+    first = torch.cat([src.next_batch()[1].clone() for _ in range(3)]).tolist()     # two passes
+    for f in os.listdir(d):
+        os.remove(os.path.join(d, f))                   # later passes come from memory
+    more = torch.cat([src.next_batch()[1].clone() for _ in range(6)]).tolist()
+    src.close()
+    seq = first + more
+    assert seq[:6] == seq[6:12] == seq[12:18] and sorted(seq[:6]) == [1, 1, 2, 2, 3, 3]

@@ -143,3 +143,42 @@ def test_host_runtime_is_clean_under_address_and_ub_sanitizers(tmp_path):
     _sanitizer_run(tmp_path, "rs_asan",
                    ["-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"],
                    {"ASAN_OPTIONS": "detect_leaks=1"})
+
+
+def test_deterministic_interleave_is_round_robin_over_files(tmp_path):
+    """deterministic=True: one record from each reader in turn (tf.data interleave, block
+    length 1); exhausted files drop out of the rotation; identical on every run."""
+    rng = np.random.RandomState(5)
+    paths, recs = [], []
+    for f, n in enumerate([7, 3, 5]):
+        r = [bytes([f, i]) + rng.bytes(int(rng.randint(0, 500))) for i in range(n)]
+        path = str(tmp_path / ("part-%d" % f))
+        tfrecord.write_records(path, r)
+        paths.append(path)
+        recs.append(r)
+    want = []
+    for i in range(7):
+        for f in range(3):
+            if i < len(recs[f]):
+                want.append(recs[f][i])
+    for _ in range(5):
+        got = list(native_reader.RecordReader(paths, num_threads=3, capacity=6, deterministic=True))
+        assert got == want
+    # two readers over three files: reader 0 owns files 0 and 2 (one after the other), reader 1
+    # owns file 1
+    got = list(native_reader.RecordReader(paths, num_threads=2, capacity=4, deterministic=True))
+    seq0, seq1 = recs[0] + recs[2], recs[1]
+    want2 = []
+    for i in range(max(len(seq0), len(seq1))):
+        if i < len(seq0):
+            want2.append(seq0[i])
+        if i < len(seq1):
+            want2.append(seq1[i])
+    assert got == want2
+    # repeat + early close does not hang
+    rd = native_reader.RecordReader(paths, num_threads=3, capacity=3, repeat=True,
+                                    deterministic=True)
+    first = [next(rd) for _ in range(40)]
+    rd.close()
+    # every file restarts when it ends, so rotation r takes record r % len(file) of each file
+    assert first == [recs[k % 3][(k // 3) % len(recs[k % 3])] for k in range(40)]
