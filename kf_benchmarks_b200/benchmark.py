@@ -796,6 +796,21 @@ class BenchmarkCNN:
                                          world=max(self.world, 1), train=False)
         return self._eval_once(self._eval_batches(), src)
 
+    def _write_eval_summary(self, step: int, result: Dict) -> None:
+        """--eval_dir: one JSON line per evaluated checkpoint in eval_dir/summaries.jsonl (the
+        reference writes the same scalars as a TensorBoard event, T/benchmark_cnn.py:1771,
+        1895-1904)."""
+        d = self.params.eval_dir
+        if not d:
+            return
+        import json
+        try:
+            os.makedirs(d, exist_ok=True)
+            with open(os.path.join(d, "summaries.jsonl"), "a") as f:
+                f.write(json.dumps(_eval_summary_record(step, result)) + "\n")
+        except OSError as e:
+            _log("note: could not write the eval summary to %s: %s" % (d, e))
+
     def _run_eval(self) -> Dict:
         """T/benchmark_cnn.py:1757-1794."""
         p = self.params
@@ -811,10 +826,24 @@ class BenchmarkCNN:
                 _log("-" * 64)
                 _log("total images/sec: %.2f" % result["images_per_sec"])
                 _log("-" * 64)
+                self._write_eval_summary(step, result)
             if p.eval_interval_secs <= 0:
                 break
             time.sleep(p.eval_interval_secs)
         return result
+
+
+def _eval_summary_record(step: int, result: Dict) -> Dict:
+    """The scalars the reference adds to its eval summary (T/benchmark_cnn.py:1895-1904):
+    eval/Accuracy@1, eval/Accuracy@5 and every model result marked as a simple value."""
+    from . import constants
+    rec = {"step": int(step), "eval/Accuracy@1": result["top_1_accuracy"],
+           "eval/Accuracy@5": result["top_5_accuracy"]}
+    prefix = constants.SIMPLE_VALUE_RESULT_PREFIX
+    for k, v in result.items():
+        if isinstance(k, str) and k.startswith(prefix):
+            rec["eval/" + k[len(prefix):]] = float(v)
+    return rec
 
 
 def run_from_kwargs(**kwargs) -> Dict:

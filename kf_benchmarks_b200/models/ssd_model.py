@@ -229,7 +229,11 @@ class SSD300Model(model.CNNModel):
         if not preds or not os.path.exists(ann):
             return {"top_1_accuracy": 0.0, "top_5_accuracy": 0.0,
                     "detections_collected": len(preds)}
-        out = coco_metric.compute_map(preds, ann)
+        from .. import constants
+        # like the reference (T/models/ssd_model.py:531-535) the metrics are marked as simple
+        # values, which sends them to the eval summary as eval/COCO/AP ...
+        out = {constants.SIMPLE_VALUE_RESULT_PREFIX + k: v
+               for k, v in coco_metric.compute_map(preds, ann).items()}
         out.update({"top_1_accuracy": 0.0, "top_5_accuracy": 0.0})
         return out
 

@@ -222,6 +222,15 @@ IGNORED_ON_B200 = (
     "single_l2_loss_op", "use_resource_vars", "compute_lr_on_cpu", "sparse_to_dense_grads", "mkl",
     "kmp_blocktime", "kmp_affinity", "kmp_settings", "allreduce_merge_scope", "server_protocol",
     "cross_replica_sync", "horovod_device", "trt_max_workspace_size_bytes",
+    # one input pipeline serves both settings of --use_datasets; prefetching is the pinned ring
+    # plus the copy stream; Pillow decodes whole images; saturation and hue commute in HSV, so
+    # the two --distort_color_in_yiq orders coincide
+    "use_datasets", "datasets_use_prefetch", "datasets_prefetch_buffer_size",
+    "datasets_parallel_interleave_prefetch", "fuse_decode_and_crop", "distort_color_in_yiq",
+    # gradients lie back to back in one fp32 arena: nothing to aggregate or compact, no
+    # parameter device to choose; there is no controller process
+    "compact_gradient_transfer", "agg_small_grads_max_bytes", "agg_small_grads_max_group",
+    "local_parameter_device", "controller_host",
 )
 # Reference features this build rejects with an explicit error when requested.
 UNSUPPORTED_WHEN_SET = {

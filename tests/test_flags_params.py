@@ -101,3 +101,23 @@ def test_warmup_default_and_batch_sizes():
     b = benchmark.BenchmarkCNN(P.make_params(device="cpu", data_format="NHWC", autotune_threshold=3,
                                              batch_size=8, num_gpus=1))
     assert b.num_warmup_batches == 45 and b.batch_size == 8
+
+
+def test_every_flag_is_either_used_or_declared_without_effect():
+    """No flag is swallowed silently: each one is read somewhere in the package, rejected with
+    an error, or listed in IGNORED_ON_B200 (a note is logged when it is set)."""
+    import os
+    import re
+    from kf_benchmarks_b200 import params as P
+    root = os.path.dirname(os.path.abspath(P.__file__))
+    src = ""
+    for d, _, fs in os.walk(root):
+        for f in fs:
+            if f.endswith(".py") and f != "params.py":
+                with open(os.path.join(d, f)) as fh:
+                    src += fh.read()
+    declared = set(P.IGNORED_ON_B200) | set(P.UNSUPPORTED_WHEN_SET)
+    silent = [f for f in P.make_params()._fields
+              if f not in declared and not re.search(r"\b%s\b" % re.escape(f), src)]
+    assert silent == []
+    assert not (set(P.IGNORED_ON_B200) - set(P.make_params()._fields))

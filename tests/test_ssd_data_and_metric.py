@@ -216,7 +216,10 @@ def test_ssd_eval_hooks_on_the_cpu_executor(tmp_path):
     assert boxes.shape == (1, 8732, 4) and scores.shape == (1, 8732, 81)
     assert np.allclose(scores.sum(-1), 1.0, atol=1e-4)
     out = m.eval_finish(p)
-    assert "COCO/AP" in out and 0.0 <= out["COCO/AP"] <= 1.0 and m.predictions == {}
+    assert 0.0 <= out["simple_value:COCO/AP"] <= 1.0 and m.predictions == {}
+    from kf_benchmarks_b200.benchmark import _eval_summary_record
+    rec = _eval_summary_record(7, out)
+    assert rec["step"] == 7 and "eval/COCO/AP" in rec and rec["eval/Accuracy@1"] == 0.0
 
 
 def test_backbone_loading_and_graph_dumps(tmp_path):

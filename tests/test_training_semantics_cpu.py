@@ -228,10 +228,16 @@ def test_eval_and_eval_during_training(tmp_path):
     acc = [l for l in lines if l.startswith("Accuracy @ 1 = ")]
     assert len(acc) == 2 and re.match(
         r"^Accuracy @ 1 = \d\.\d{4} Accuracy @ 5 = \d\.\d{4} \[8 examples\]$", acc[0])
-    kw = dict(BASE, train_dir=str(tmp_path / "ckpt"), eval=True, num_batches=3)
+    kw = dict(BASE, train_dir=str(tmp_path / "ckpt"), eval=True, num_batches=3,
+              eval_dir=str(tmp_path / "eval"))
     kw.pop("init_learning_rate")
     _, res, lines = _run_single(kw)
     assert res["num_examples"] == 12 and 0.0 <= res["top_1_accuracy"] <= res["top_5_accuracy"]
+    # --eval_dir receives the scalars of the reference's eval summary
+    recs = [json.loads(l) for l in open(str(tmp_path / "eval" / "summaries.jsonl"))]
+    assert len(recs) == 1 and recs[0]["step"] == 2
+    assert recs[0]["eval/Accuracy@1"] == res["top_1_accuracy"]
+    assert recs[0]["eval/Accuracy@5"] == res["top_5_accuracy"]
 
 
 def test_forward_only_and_loss_reporting():
