@@ -73,8 +73,27 @@ def build_host(force: bool = False) -> str:
     return HOST_LIB
 
 
+LAUNCHER = os.path.join(OUT_DIR, "kfb-run")
+
+
+def build_launcher(force: bool = False) -> str:
+    """Native rank launcher (csrc/host/launcher/kfb_run.cpp): the `kungfu-run -np N` /
+    `mpirun -np N` of this runtime as one small executable."""
+    os.makedirs(OUT_DIR, exist_ok=True)
+    src = os.path.join(CSRC, "host", "launcher", "kfb_run.cpp")
+    if not force and os.path.exists(LAUNCHER) and os.path.getmtime(LAUNCHER) >= os.path.getmtime(src):
+        return LAUNCHER
+    cxx = os.environ.get("CXX", "g++")
+    res = subprocess.run([cxx, "-O2", "-std=c++17", "-o", LAUNCHER, src], capture_output=True,
+                         text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"launcher build failed:\n{res.stdout}\n{res.stderr}")
+    return LAUNCHER
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     build_host(force)
+    build_launcher(force)
     os.makedirs(OUT_DIR, exist_ok=True)
     os.makedirs(OBJ_DIR, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))

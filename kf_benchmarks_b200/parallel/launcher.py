@@ -5,6 +5,10 @@ Each rank gets RANK / LOCAL_RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT. Rank 
 passed through; other ranks are prefixed. The first non-zero exit kills the whole group
 (failure mode of the reference: one rank dies, the launcher reports it and reaps the rest,
 SURVEY.md 5.3).
+
+``--native`` hands the job to the C++ launcher ``_lib/kfb-run`` (csrc/host/launcher/kfb_run.cpp,
+same environment, prefixes and failure handling, plus ``-logdir`` / ``-timeout``), which can
+also be used directly for any command: ``kfb-run -np 8 -- python -m kf_benchmarks_b200.cli ...``.
 """
 from __future__ import annotations
 
@@ -84,8 +88,15 @@ def main(argv=None) -> int:
         return 2
     n = int(argv[1])
     rest = argv[2:]
+    native = bool(rest) and rest[0] == "--native"
+    if native:
+        rest = rest[1:]
     if rest and rest[0] == "--":
         rest = rest[1:]
+    if native:
+        from .. import build as build_lib
+        exe = build_lib.build_launcher()
+        os.execv(exe, [exe, "-np", str(n), "--", sys.executable] + rest)
     return launch_local(rest, n)
 
 

@@ -224,3 +224,43 @@ def test_bench_reference_arm_and_clock_sampler(tmp_path, monkeypatch):
     assert out["reasons"] == ["sw_power_cap"] and out["power_w_max"] == 980.5
     s.lines = ["0, 1200, 1965, 300.0, 0x8, Active, Active, Not Active, Not Active"]
     assert bench.ClockSampler.stop(s)["reasons"] == ["hw_slowdown", "hw_thermal_slowdown"]
+
+
+def test_native_launcher(tmp_path):
+    """kfb-run (csrc/host/launcher/kfb_run.cpp): rank environment, output prefixes, per-rank log
+    files named like kungfu-run's, first failure stops the job, timeout, and a real 2-rank
+    gloo job started through it."""
+    import time
+    from kf_benchmarks_b200 import build as build_lib
+    exe = build_lib.build_launcher()
+    code = "import os;print('hi', os.environ['RANK'], os.environ['WORLD_SIZE'], " \
+           "os.environ['LOCAL_WORLD_SIZE'], os.environ['MASTER_ADDR'])"
+    res = subprocess.run([exe, "-np", "3", "-logdir", str(tmp_path / "logs"), "--", sys.executable,
+                          "-c", code], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stderr
+    assert sorted(res.stdout.splitlines()) == ["[rank 1] hi 1 3 3 127.0.0.1",
+                                               "[rank 2] hi 2 3 3 127.0.0.1", "hi 0 3 3 127.0.0.1"]
+    logs = sorted(os.listdir(str(tmp_path / "logs")))
+    assert logs == ["127.0.0.1.1000%d.%s.log" % (r, k) for r in range(3) for k in ("stderr", "stdout")]
+    assert open(str(tmp_path / "logs" / "127.0.0.1.10002.stdout.log")).read() == "hi 2 3 3 127.0.0.1\n"
+    # the first failing rank ends the job quickly and sets the exit status
+    code = "import os,sys,time\nif os.environ['RANK']=='1': sys.exit(7)\ntime.sleep(60)"
+    t0 = time.time()
+    res = subprocess.run([exe, "-np", "3", "-grace", "1", "--", sys.executable, "-c", code],
+                         capture_output=True, text=True, timeout=120)
+    assert res.returncode == 7 and time.time() - t0 < 30
+    assert "rank 1 exited with 7" in res.stderr
+    res = subprocess.run([exe, "-np", "2", "-timeout", "1", "-grace", "1", "--", "sleep", "30"],
+                         capture_output=True, text=True, timeout=120)
+    assert res.returncode == 124 and "timeout" in res.stderr
+    assert subprocess.run([exe, "-np", "0", "--", "true"], capture_output=True).returncode == 2
+    # a real job: two CPU replicas over gloo, started by the native launcher
+    res = subprocess.run([sys.executable, "-m", "kf_benchmarks_b200.parallel.launcher", "-np", "2",
+                          "--native", "--", "-m", "kf_benchmarks_b200.cli", "--model=trivial",
+                          "--device=cpu", "--data_format=NHWC", "--num_gpus=2", "--batch_size=4",
+                          "--variable_update=replicated", "--num_batches=3",
+                          "--num_warmup_batches=0", "--display_every=1"],
+                         cwd=ROOT, env=dict(os.environ, PYTHONPATH=ROOT), capture_output=True,
+                         text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert "total images/sec:" in res.stdout
