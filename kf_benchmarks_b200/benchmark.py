@@ -341,8 +341,19 @@ class BenchmarkCNN:
                 return self._run_eval()
             return self._benchmark_train()
         finally:
+            self._close_source(getattr(self, "input_source", None))
             if self.comm is not None:
                 self.comm.close()
+
+    @staticmethod
+    def _close_source(src) -> None:
+        """Real-data sources own a producer thread and a decode pool: stop them."""
+        close = getattr(src, "close", None)
+        if close is not None:
+            try:
+                close()
+            except Exception:  # pragma: no cover - shutting down must not mask the result
+                pass
 
     def _examples_per_step(self) -> int:
         """Batch size the LR schedule sees (T/benchmark_cnn.py:2757-2765)."""
@@ -794,7 +805,10 @@ class BenchmarkCNN:
                                          self.batch_size_per_device, self.device, self.nclass,
                                          seed=self.seed + 1, rank=self.rank,
                                          world=max(self.world, 1), train=False)
-        return self._eval_once(self._eval_batches(), src)
+        try:
+            return self._eval_once(self._eval_batches(), src)
+        finally:
+            self._close_source(src)
 
     def _write_eval_summary(self, step: int, result: Dict) -> None:
         """--eval_dir: one JSON line per evaluated checkpoint in eval_dir/summaries.jsonl (the
