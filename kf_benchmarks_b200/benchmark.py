@@ -820,8 +820,13 @@ class BenchmarkCNN:
         import json
         try:
             os.makedirs(d, exist_ok=True)
+            rec = _eval_summary_record(step, result)
             with open(os.path.join(d, "summaries.jsonl"), "a") as f:
-                f.write(json.dumps(_eval_summary_record(step, result)) + "\n")
+                f.write(json.dumps(rec) + "\n")
+            from .utils import tfevents
+            if getattr(self, "_eval_events", None) is None:
+                self._eval_events = tfevents.EventFileWriter(d)
+            self._eval_events.add(step, {k: v for k, v in rec.items() if k != "step"})
         except OSError as e:
             _log("note: could not write the eval summary to %s: %s" % (d, e))
 

@@ -1,8 +1,11 @@
 """Training summaries (T/benchmark_cnn.py:2811-2846): scalars at ``--summary_verbosity`` >= 1
 (learning rate, loss, loss scale), a gradient-magnitude histogram at >= 2 and per-variable /
 per-gradient histograms at >= 3, written every ``--save_summaries_steps`` steps by rank 0 as
-JSON lines in ``train_dir/summaries.jsonl`` (the reference writes TensorBoard event files through
-TF; there is no TensorFlow here, and JSONL is trivially convertible)."""
+JSON lines in ``train_dir/summaries.jsonl`` and - like the reference, which goes through
+``tf.summary.FileWriter`` - as a TensorBoard event file ``train_dir/events.out.tfevents.*``
+(written by ``utils/tfevents.py`` without TensorFlow) with the reference's tags:
+``learning_rate``, the reported loss type, ``loss_scale``, ``log_gradients``, ``<variable>`` and
+``<variable>/gradients``."""
 from __future__ import annotations
 
 import json
@@ -28,6 +31,9 @@ class SummaryWriter:
         if self.verbosity > 0 and self.every > 0 and directory:
             os.makedirs(directory, exist_ok=True)
             self.path = os.path.join(directory, "summaries.jsonl")
+        self.loss_tag = getattr(params, "loss_type_to_report", None) or "total_loss"
+        self.use_loss_scale = bool(getattr(params, "use_fp16", False))
+        self._events = None
 
     def maybe_write(self, step, lr, loss, engine, store) -> None:
         if self.path is None or step % self.every != 0:
@@ -46,3 +52,28 @@ class SummaryWriter:
                 rec["gradients"][name] = _hist(store.view(name, "grad"))
         with open(self.path, "a") as f:
             f.write(json.dumps(rec) + "\n")
+        self._write_event(step, lr, loss, engine, store)
+
+    def _write_event(self, step, lr, loss, engine, store) -> None:
+        from . import tfevents
+        if self._events is None:
+            self._events = tfevents.EventFileWriter(os.path.dirname(self.path))
+        scalars = {"learning_rate": lr, self.loss_tag: loss}
+        if self.use_loss_scale:
+            scalars["loss_scale"] = engine.loss_scale
+        hists = {}
+        if self.verbosity >= 2:
+            g = store.grad.detach().float().abs() / max(engine.loss_scale, 1e-30)
+            hists["log_gradients"] = tfevents.histogram_of(torch.log10(g[g > 0]).cpu().numpy())
+        if self.verbosity >= 3:
+            for name, slot in store.slots.items():
+                if slot.arena != "w":
+                    continue
+                hists[name] = tfevents.histogram_of(store.view(name).detach().float().cpu().numpy())
+                hists[name + "/gradients"] = tfevents.histogram_of(
+                    store.view(name, "grad").detach().float().cpu().numpy())
+        self._events.add(step, scalars, hists)
+
+    def close(self) -> None:
+        if self._events is not None:
+            self._events.close()

@@ -81,6 +81,37 @@ def test_summaries_jsonl(tmp_path):
     assert [r["step"] for r in recs] == [2, 4]
     assert "learning_rate" in recs[0] and "log_gradients" in recs[0]
     assert "cg/affine0/weights" in recs[0]["variables"]
+    # the same summaries as a TensorBoard event file (what tf.summary.FileWriter leaves behind)
+    from kf_benchmarks_b200.utils import tfevents
+    path = tfevents.latest_event_file(str(tmp_path))
+    assert os.path.basename(path).startswith("events.out.tfevents.")
+    events = list(tfevents.read_events(path))                  # CRC-checked TFRecord framing
+    assert events[0]["file_version"] == "brain.Event:2"
+    assert [e["step"] for e in events[1:]] == [2, 4]
+    e = events[1]
+    assert abs(e["scalars"]["learning_rate"] - recs[0]["learning_rate"]) < 1e-6
+    assert abs(e["scalars"]["total_loss"] - recs[0]["loss"]) < 1e-3 * max(1.0, abs(recs[0]["loss"]))
+    h = e["histograms"]["cg/affine0/weights"]
+    assert h["num"] > 0 and len(h["bucket"]) == len(h["bucket_limit"]) == 30
+    assert abs(sum(h["bucket"]) - h["num"]) < 1e-6 and h["min"] <= h["max"]
+    assert "cg/affine0/weights/gradients" in e["histograms"] and "log_gradients" in e["histograms"]
+
+
+def test_tfevents_encoding_against_hand_assembled_bytes():
+    """The Event encoder against bytes assembled by hand from the protobuf wire format."""
+    import struct
+    from kf_benchmarks_b200.utils import tfevents
+    got = tfevents.encode_event(3, 1.5, scalars={"a": 0.25})
+    value = b"\x0a\x01a" + b"\x15" + struct.pack("<f", 0.25)          # tag = 1, simple_value = 2
+    summary = b"\x0a" + bytes([len(value)]) + value                     # Summary.value = 1
+    want = b"\x09" + struct.pack("<d", 1.5) + b"\x10\x03" + b"\x2a" + bytes([len(summary)]) + summary
+    assert got == want
+    assert tfevents.parse_event(got) == {"wall_time": 1.5, "step": 3, "scalars": {"a": 0.25},
+                                         "histograms": {}}
+    h = tfevents.histogram_of([1.0, 2.0, 2.0, 4.0], bins=3)
+    assert h["num"] == 4 and h["sum"] == 9 and h["sum_squares"] == 25 and h["bucket"] == [1, 2, 1]
+    back = tfevents.parse_event(tfevents.encode_event(-1, 0.0, histograms={"h": h}))
+    assert back["step"] == -1 and back["histograms"]["h"] == h
 
 
 def test_launcher_kills_group_when_a_rank_dies(tmp_path):
