@@ -673,6 +673,14 @@ class BenchmarkCNN:
                     _log(log_util.step_line(
                         step1, self.batch_size, step_train_times, loss,
                         t1 / n if accuracy_cols else None, t5 / n if accuracy_cols else None))
+                    if p.benchmark_log_dir:
+                        from .utils import benchmark_logger
+                        speed = log_util.get_perf_timing(self.batch_size, step_train_times)[0]
+                        benchmark_logger.log_metric(p, "current_examples_per_sec", speed, step1,
+                                                    "examples/sec")
+                        if accuracy_cols:
+                            benchmark_logger.log_metric(p, "top_1_accuracy", t1 / n, step1)
+                            benchmark_logger.log_metric(p, "top_5_accuracy", t5 / n, step1)
             if summaries is not None and summaries.path is not None and \
                     self.global_step % max(summaries.every, 1) == 0:
                 loss_s = self._reported_loss(self.executor.read_loss()[0])
@@ -790,6 +798,9 @@ class BenchmarkCNN:
         result = {"top_1_accuracy": acc1, "top_5_accuracy": acc5, "num_examples": total,
                   "eval_average_loss": loss_sum / max(num_batches, 1),
                   "images_per_sec": total / max(dt, 1e-9)}
+        if self.rank == 0 and self.params.benchmark_log_dir:
+            from .utils import benchmark_logger
+            benchmark_logger.log_evaluation_result(self.params, result, self.global_step)
         finish = getattr(self.model, "eval_finish", None)
         if finish is not None:
             extra = finish(self.params) or {}

@@ -48,7 +48,10 @@ def test_trace_profile_and_benchmark_log(tmp_path):
     assert info["model_name"] == "trivial" and info["test_id"] == "t1"
     with open(os.path.join(kw["benchmark_log_dir"], "metric.log")) as f:
         metrics = [json.loads(l) for l in f]
-    assert {m["name"] for m in metrics} >= {"average_examples_per_sec", "last_average_loss"}
+    assert {m["name"] for m in metrics} >= {"average_examples_per_sec", "last_average_loss",
+                                            "current_examples_per_sec"}
+    cur = [m for m in metrics if m["name"] == "current_examples_per_sec"]
+    assert [m["global_step"] for m in cur] == [1, 10] and cur[0]["unit"] == "examples/sec"
 
 
 def test_cli_entry_point_and_help():
