@@ -165,8 +165,14 @@ def main():
               (cls, flops / 1e9, nbytes / 1e9, roof, "tensor" if t_f > t_b else ("HBM" if flops == 0 or roof <= t_b * 1.001
                                                            else "mixed"),
                "%.3f" % m if m else "-", "%.0f %%" % (100 * roof / m) if m else "-"))
-    print("| **sum** | | | **%.2f** | | **%.2f** (+ %.2f other) | **%.0f %%** |" %
-          (tot_roof, tot_meas, other, 100 * tot_roof / max(tot_meas + other, 1e-9)))
+    if tot_meas + other > 0:
+        print("| **sum** | | | **%.2f** | | **%.2f** (+ %.2f other) | **%.0f %%** |" %
+              (tot_roof, tot_meas, other, 100 * tot_roof / (tot_meas + other)))
+    else:
+        print("| **sum** | | | **%.2f** | | - | - |" % tot_roof)
+        print()
+        print("No launch list given: at the roof this step would take %.2f ms = %.0f examples/sec." %
+              (tot_roof, args.batch_size / (tot_roof * 1e-3)))
     if args.step_ms:
         print()
         print("Free-running step: %.2f ms -> %.0f %% of the summed roof." %
