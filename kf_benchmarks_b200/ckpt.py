@@ -2,12 +2,13 @@
 
 The reference saves ``train_dir/model.ckpt-<global_step>`` through ``tf.train.Saver`` plus a
 ``checkpoint`` state file (T/benchmark_cnn.py:2076-2082,2373-2378) and loads the newest or a
-named one (``load_checkpoint`` :905-950). By default the tensors are stored as one ``.npz`` per
-checkpoint whose *keys are the reference's TF variable names* (``v0/cg/conv0/conv2d/kernel``
-..., HWIO / [in,out] layouts, fp32, plus ``global_step``, ``loss_scale``,
-``loss_scale_normal_steps`` and ``<var>/Momentum`` style optimizer slots);
-``--checkpoint_format=tf`` writes the same tensors as a TensorFlow V2 bundle (``tf_bundle.py``,
-no TensorFlow needed) and either format - including bundles written by the reference - is
+named one (``load_checkpoint`` :905-950). The tensors are keyed by *the reference's TF variable
+names* (``v0/cg/conv0/conv2d/kernel`` ..., HWIO / [in,out] layouts, fp32, plus ``global_step``,
+``loss_scale``, ``loss_scale_normal_steps`` and ``<var>/Momentum`` style optimizer slots) and
+stored, by default (``--checkpoint_format=tf``), as a TensorFlow V2 bundle (``tf_bundle.py``,
+no TensorFlow needed: ``model.ckpt-N.index`` + ``.data-00000-of-00001``, CRC32C through the
+host library) like the reference's own train_dir, or as one ``.npz`` per checkpoint
+(``--checkpoint_format=npz``); either format - including bundles written by the reference - is
 restored transparently. ``tools/export_tf_checkpoint.py`` converts between the two. The
 ``checkpoint`` state file uses TF's text format with relative paths so a moved ``train_dir``
 still resolves.

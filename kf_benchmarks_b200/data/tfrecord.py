@@ -28,11 +28,30 @@ def _crc32c_table():
 _TABLE = _crc32c_table()
 
 
-def crc32c(data: bytes) -> int:
+def _crc32c_python(data: bytes) -> int:
     c = 0xFFFFFFFF
     for b in data:
         c = _TABLE[(c ^ b) & 0xFF] ^ (c >> 8)
     return c ^ 0xFFFFFFFF
+
+
+_native_crc = None          # None: not looked up yet; False: host library not built
+
+
+def crc32c(data: bytes) -> int:
+    """CRC32C (Castagnoli). Uses the host library's hardware implementation
+    (csrc/host/record_io.cpp, several GB/s) when it is built - checkpoint bundles put hundreds
+    of megabytes through this - and the table-driven Python loop otherwise."""
+    global _native_crc
+    if _native_crc is None:
+        try:
+            from . import native_reader
+            _native_crc = native_reader.crc32c if native_reader.available() else False
+        except Exception:  # pragma: no cover - a broken build must not break the codec
+            _native_crc = False
+    if _native_crc and len(data) >= 64:
+        return _native_crc(bytes(data) if not isinstance(data, bytes) else data)
+    return _crc32c_python(data)
 
 
 def masked_crc(data: bytes) -> int:

@@ -196,10 +196,10 @@ NUM_REFERENCE_FLAGS = len(flags.param_specs)
 
 # ---- B200-native additions ------------------------------------------------------------
 _D.DEFINE_alias("kungfu_strategy", "kungfu_option")
-_D.DEFINE_enum("checkpoint_format", "npz", ("npz", "tf"),
-               "npz: one .npz per checkpoint keyed by the reference's TF variable names. tf: a "
-               "TensorFlow V2 checkpoint bundle (.index + .data) the reference can restore. "
-               "Both are read back transparently.")
+_D.DEFINE_enum("checkpoint_format", "tf", ("tf", "npz"),
+               "tf (default): a TensorFlow V2 checkpoint bundle (model.ckpt-N.index + .data-*), "
+               "what the reference's Saver writes and can restore. npz: one .npz per checkpoint "
+               "keyed by the same TF variable names. Both are read back transparently.")
 _D.DEFINE_enum("comm_impl", "p2p", ("p2p", "p2p_fused", "nvls", "nccl", "gloo"),
                "p2p: fused NVLink all-reduce+update kernels (the product). p2p_fused: in "
                "addition the weight-gradient GEMMs scatter their tiles to the owning ranks from "

@@ -136,7 +136,8 @@ def test_launcher_kills_group_when_a_rank_dies(tmp_path):
 
 def test_export_tool_lists_reference_names(tmp_path):
     kw = dict(model="trivial", data_name="cifar10", device="cpu", data_format="NHWC", batch_size=4,
-              num_batches=1, num_warmup_batches=0, train_dir=str(tmp_path), optimizer="momentum")
+              num_batches=1, num_warmup_batches=0, train_dir=str(tmp_path), optimizer="momentum",
+              checkpoint_format="npz")
     old = log_util.log_fn
     log_util.log_fn = lambda s: None
     try:

@@ -210,7 +210,8 @@ def test_tf_cluster_flags_start_workers_without_a_launcher(tmp_path):
 def test_resume_from_checkpoint(tmp_path):
     kw = dict(BASE, optimizer="momentum", train_dir=str(tmp_path / "ckpt"), num_batches=2)
     bench, _, lines = _run_single(kw)
-    assert os.path.exists(os.path.join(kw["train_dir"], "model.ckpt-2.npz"))
+    # the reference's testSaveLoadModel looks for exactly this file (T/benchmark_cnn_test.py:74-142)
+    assert os.path.exists(os.path.join(kw["train_dir"], "model.ckpt-2.index"))
     # --num_batches is the total from global step 0 (T/benchmark_cnn.py:2242-2250): resuming
     # with the same value has nothing left to do, with a larger one runs the difference
     bench2, stats2, lines2 = _run_single(kw)
@@ -218,7 +219,8 @@ def test_resume_from_checkpoint(tmp_path):
     assert bench2.global_step == 2 and stats2["num_steps"] == 0
     bench3, stats3, _ = _run_single(dict(kw, num_batches=5))
     assert bench3.global_step == 5 and stats3["num_steps"] == 3
-    assert os.path.exists(os.path.join(kw["train_dir"], "model.ckpt-5.npz"))
+    assert os.path.exists(os.path.join(kw["train_dir"], "model.ckpt-5.index"))
+    assert os.path.exists(os.path.join(kw["train_dir"], "model.ckpt-5.data-00000-of-00001"))
 
 
 def test_eval_and_eval_during_training(tmp_path):
