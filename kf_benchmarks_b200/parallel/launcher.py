@@ -1,7 +1,7 @@
 """Local launcher: N ranks of one command on one box (the role of ``kungfu-run -np N`` /
 ``mpirun -np N`` in the reference's launch scripts, T/README.md:97-114, T/run_kf.sh-bak:18-21).
 
-Each rank gets RANK / LOCAL_RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT. Rank 0's stdout is
+Each rank gets RANK / LOCAL_RANK / WORLD_SIZE / LOCAL_WORLD_SIZE / MASTER_ADDR / MASTER_PORT. Rank 0's stdout is
 passed through; other ranks are prefixed. The first non-zero exit kills the whole group
 (failure mode of the reference: one rank dies, the launcher reports it and reaps the rest,
 SURVEY.md 5.3).
@@ -34,7 +34,8 @@ def launch_local(py_args: List[str], nproc: int, env_extra=None, timeout=None) -
     for r in range(nproc):
         env = dict(os.environ)
         env.update({"RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(nproc),
-                    "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port)})
+                    "LOCAL_WORLD_SIZE": str(nproc), "MASTER_ADDR": "127.0.0.1",
+                    "MASTER_PORT": str(port)})
         env.update(env_extra or {})
         out = None if r == 0 else subprocess.PIPE
         p = subprocess.Popen([sys.executable] + py_args, env=env, stdout=out,
