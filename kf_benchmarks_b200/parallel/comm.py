@@ -128,7 +128,10 @@ class P2PComm(Comm):
 
     def __init__(self, device, bootstrap_backend: str = "gloo", nvls: bool = False):
         import torch.distributed as dist
-        init_process_group(bootstrap_backend)
+        # the process group is plumbing only (rendezvous, barriers, object exchange on the host).
+        # KFB_BOOTSTRAP_BACKEND overrides it, e.g. "cpu:gloo,cuda:nccl" should torch's symmetric
+        # memory (nvls) want a CUDA-capable group for its rendezvous.
+        init_process_group(os.environ.get("KFB_BOOTSTRAP_BACKEND") or bootstrap_backend)
         self.dist = dist
         self.rank = dist.get_rank()
         self.size = dist.get_world_size()
@@ -165,7 +168,12 @@ class P2PComm(Comm):
         t = symm_mem.empty(padded, dtype=dtype, device=self.device)
         t.zero_()
         torch.cuda.synchronize(self.device)
-        hdl = symm_mem.rendezvous(t, self.dist.group.WORLD)
+        try:
+            hdl = symm_mem.rendezvous(t, self.dist.group.WORLD)
+        except Exception as e:
+            raise native.KfbError(
+                "--comm_impl=nvls: torch symmetric-memory rendezvous failed (%s). If it objects "
+                "to the gloo bootstrap group, set KFB_BOOTSTRAP_BACKEND=cpu:gloo,cuda:nccl" % e)
         base = [int(a) for a in hdl.buffer_ptrs]
         if len(base) != self.size:
             raise native.KfbError("symmetric memory rendezvous returned %d peers, expected %d"
