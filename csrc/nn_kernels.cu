@@ -1107,6 +1107,24 @@ static inline int grid_for(long long work_items, int threads = 256, int max_bloc
 }
 
 // 2-D launch shape for the per-row apply kernels: x = channel vectors, y = rows.
+// Launch-shape knobs for sweeps on the device without a rebuild (read once; the defaults are the
+// measured configuration): KFB_APPLY_CTAS_PER_SM (default 16) caps the grid of the BN apply
+// kernels, KFB_REDUCE_BLOCKS_PER_SM (default 4) the grid of the channel reductions.
+static int env_int(const char* name, int dflt, int lo, int hi) {
+  const char* e = getenv(name);
+  if (e == nullptr || *e == 0) return dflt;
+  const int v = atoi(e);
+  return v < lo ? lo : (v > hi ? hi : v);
+}
+static int apply_ctas_per_sm() {
+  static const int v = env_int("KFB_APPLY_CTAS_PER_SM", 16, 1, 64);
+  return v;
+}
+static int reduce_blocks_per_sm() {
+  static const int v = env_int("KFB_REDUCE_BLOCKS_PER_SM", 4, 1, 16);
+  return v;
+}
+
 static inline void apply_launch_shape(long long rows, int C, dim3* grid, dim3* block) {
   const int vpr = C >> 3;
   int vx = 1;
@@ -1115,7 +1133,7 @@ static inline void apply_launch_shape(long long rows, int C, dim3* grid, dim3* b
   const int vy = 256 / vx > 0 ? 256 / vx : 1;
   const int gx = (vpr + vx - 1) / vx;
   long long gy = (rows + vy - 1) / vy;
-  const long long cap = (148LL * 16 + gx - 1) / gx;
+  const long long cap = (148LL * apply_ctas_per_sm() + gx - 1) / gx;
   if (gy > cap) gy = cap;
   if (gy < 1) gy = 1;
   *grid = dim3((unsigned)gx, (unsigned)gy, 1);
@@ -1125,7 +1143,7 @@ static inline void apply_launch_shape(long long rows, int C, dim3* grid, dim3* b
 static inline int reduce_blocks(long long rows, int C) {
   // enough blocks to fill the machine, but each block should own >= 64 rows
   long long b = rows / 64;
-  const long long cap = 148 * 4;
+  const long long cap = 148LL * reduce_blocks_per_sm();
   if (b > cap) b = cap;
   if (b < 1) b = 1;
   return static_cast<int>(b);
