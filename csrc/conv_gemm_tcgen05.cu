@@ -914,7 +914,27 @@ static int launch_mode(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, c
 
 // Tile width: the widest tile that covers N (wider tiles amortise the A-operand smem reads);
 // short-K, wide-N problems keep 128-wide tiles so more tiles exist to balance across SMs.
-static int pick_bn(int n) { return n <= 64 ? 64 : (n <= 128 ? 128 : 256); }
+// Policy knobs for on-device sweeps without a rebuild (read once; defaults = measured setup):
+// KFB_GEMM_MAX_BN (64 | 128 | 256, default 256) caps the tile width, KFB_SPLIT_ROUNDS (default 2)
+// is the number of persistent-grid rounds the split-K count aims for.
+static int env_knob(const char* name, int dflt, int lo, int hi) {
+  const char* e = getenv(name);
+  if (e == nullptr || *e == 0) return dflt;
+  const int v = atoi(e);
+  return v < lo ? lo : (v > hi ? hi : v);
+}
+static int max_bn() {
+  static const int v = env_knob("KFB_GEMM_MAX_BN", 256, 64, 256);
+  return v >= 256 ? 256 : (v >= 128 ? 128 : 64);
+}
+static int split_rounds() {
+  static const int v = env_knob("KFB_SPLIT_ROUNDS", 2, 1, 8);
+  return v;
+}
+static int pick_bn(int n) {
+  const int bn = n <= 64 ? 64 : (n <= 128 ? 128 : 256);
+  return bn < max_bn() ? bn : max_bn();
+}
 static int pick_bn_for(int n, int num_kb) {
   int bn = pick_bn(n);
   if (num_kb <= 2 && bn == 256) bn = 128;
@@ -924,7 +944,7 @@ static int pick_bn_for(int n, int num_kb) {
 // Split count such that tiles * splits fills k whole rounds of the persistent grid (k = 2 when
 // possible): a partial last round would leave most SMs idle for a full tile time.
 static int balanced_splits(int tiles, int num_kb, int sms) {
-  int splits = (2 * sms) / tiles;
+  int splits = (split_rounds() * sms) / tiles;
   if (splits < 1) splits = 1;
   if (splits > num_kb) splits = num_kb;
   return splits < 1 ? 1 : splits;

@@ -2,6 +2,8 @@
 # Sweep the environment launch knobs on one GPU in a single call (no rebuild between points):
 #   KFB_APPLY_CTAS_PER_SM   grid cap of the BN apply kernels      (default 16)
 #   KFB_REDUCE_BLOCKS_PER_SM grid cap of the channel reductions    (default 4)
+#   KFB_GEMM_MAX_BN          widest GEMM tile (64 | 128 | 256)     (default 256)
+#   KFB_SPLIT_ROUNDS         persistent-grid rounds split-K aims at (default 2)
 #   KFB_TMA_STORE            TMA-store GEMM epilogue               (default 0)
 # Prints images/sec of the headline step per point; everything lands in gpurun_out/sweep_*.json.
 set -u
@@ -26,5 +28,8 @@ PY
 run default KFB_DUMMY=0
 for v in 4 8 32; do run apply_ctas_$v KFB_APPLY_CTAS_PER_SM=$v; done
 for v in 2 6 8; do run reduce_blocks_$v KFB_REDUCE_BLOCKS_PER_SM=$v; done
+run gemm_max_bn_128 KFB_GEMM_MAX_BN=128
+for v in 1 3 4; do run split_rounds_$v KFB_SPLIT_ROUNDS=$v; done
 run tma_store KFB_TMA_STORE=1
+run tma_store_bn128 KFB_TMA_STORE=1 KFB_GEMM_MAX_BN=128
 run default_again KFB_DUMMY=0
