@@ -103,6 +103,16 @@ _MAX_DETS = (1, 10, 100)
 
 def _evaluate_img(dets, gts, area_rng, max_det):
     """Greedy matching of one (image, category) pair, COCOeval.evaluateImg."""
+    if not gts:
+        # no ground truth of this category in the image (most pairs of a detector's output):
+        # every detection is unmatched, ignored only if its area is out of range
+        dets = sorted(dets, key=lambda d: -d["score"])[:max_det]
+        d_area = np.array([d["bbox"][2] * d["bbox"][3] for d in dets])
+        oor = (d_area < area_rng[0]) | (d_area > area_rng[1]) if dets else np.zeros(0, bool)
+        T = len(_IOU_THRS)
+        return dict(scores=np.array([d["score"] for d in dets]),
+                    dtm=-np.ones((T, len(dets)), np.int64),
+                    dt_ignore=np.repeat(oor[None, :], T, 0), num_gt=0)
     g_ignore = np.array([(g["iscrowd"] or g["area"] < area_rng[0] or g["area"] > area_rng[1])
                          for g in gts], bool)
     g_order = np.argsort(g_ignore, kind="mergesort")
@@ -161,16 +171,20 @@ def coco_eval(gt_annotations: Sequence[dict], detections: Sequence[Sequence[floa
     recall = -np.ones((T, len(cats), len(_AREAS), len(_MAX_DETS)))
     for ci, cat in enumerate(cats):
         for ai, rng in enumerate(_AREAS.values()):
+            # One greedy matching per image with the largest detection budget: detections are
+            # visited in score order and a match never depends on later detections, so the
+            # result for a smaller budget is the leading part of the same arrays.
+            full = [_evaluate_img(dts.get((im, cat), []), gts.get((im, cat), []), rng,
+                                  max(_MAX_DETS))
+                    for im in imgs if (im, cat) in gts or (im, cat) in dts]
+            npig = sum(r["num_gt"] for r in full)
+            if npig == 0:
+                continue
             for mi, md in enumerate(_MAX_DETS):
-                res = [_evaluate_img(dts.get((im, cat), []), gts.get((im, cat), []), rng, md)
-                       for im in imgs if (im, cat) in gts or (im, cat) in dts]
-                npig = sum(r["num_gt"] for r in res)
-                if npig == 0:
-                    continue
-                scores = np.concatenate([r["scores"] for r in res]) if res else np.zeros(0)
+                scores = np.concatenate([r["scores"][:md] for r in full]) if full else np.zeros(0)
                 order = np.argsort(-scores, kind="mergesort")
-                dtm = np.concatenate([r["dtm"] for r in res], 1)[:, order]
-                dig = np.concatenate([r["dt_ignore"] for r in res], 1)[:, order]
+                dtm = np.concatenate([r["dtm"][:, :md] for r in full], 1)[:, order]
+                dig = np.concatenate([r["dt_ignore"][:, :md] for r in full], 1)[:, order]
                 tps = np.cumsum((dtm >= 0) & ~dig, 1).astype(np.float64)
                 fps = np.cumsum((dtm < 0) & ~dig, 1).astype(np.float64)
                 for ti in range(T):
