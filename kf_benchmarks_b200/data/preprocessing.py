@@ -307,6 +307,10 @@ class ImagenetSource(_BatchSource):
     def _draw(self, position: int):
         if self.p.datasets_repeat_cached_sample and self.cached is not None:
             record = self.cached
+        elif self.p.datasets_repeat_cached_sample:
+            # ds.take(1).cache().repeat() sits in front of the shuffle (T/preprocessing.py:
+            # 520-522): one record, no buffer to fill
+            record = self.cached = next(self.records)
         else:
             record = self._next_record()
             self.cached = record

@@ -63,6 +63,7 @@ class ImageProducer:
         self._items = []
         self._cond = threading.Condition()
         self._done = False
+        self._error = None
         self._thread = None
 
     def start(self) -> None:
@@ -70,15 +71,22 @@ class ImageProducer:
         self._thread.start()
 
     def _loop(self) -> None:
-        while True:
+        try:
+            while True:
+                with self._cond:
+                    while len(self._items) + self.batch_group_size > self.capacity and \
+                            not self._done:
+                        self._cond.wait()
+                    if self._done:
+                        return
+                group = [self.produce() for _ in range(self.batch_group_size)]
+                with self._cond:
+                    self._items.extend(group)
+                    self._cond.notify_all()
+        except BaseException as e:  # a failing producer must not leave the consumer waiting
             with self._cond:
-                while len(self._items) + self.batch_group_size > self.capacity and not self._done:
-                    self._cond.wait()
-                if self._done:
-                    return
-            group = [self.produce() for _ in range(self.batch_group_size)]
-            with self._cond:
-                self._items.extend(group)
+                self._error = e
+                self._done = True
                 self._cond.notify_all()
 
     def staged(self) -> int:
@@ -91,6 +99,9 @@ class ImageProducer:
             while not self._items and not self._done:
                 self._cond.wait()
             if not self._items:
+                if self._error is not None:
+                    raise RuntimeError("input pipeline failed: %r" % (self._error,)) \
+                        from self._error
                 raise RuntimeError("producer stopped")
             item = self._items.pop(0)
             self._cond.notify_all()

@@ -353,3 +353,27 @@ def test_datasets_use_caching_reads_the_files_once(tmp_path, monkeypatch):
     src.close()
     seq = first + more
     assert seq[:6] == seq[6:12] == seq[12:18] and sorted(seq[:6]) == [1, 1, 2, 2, 3, 3]
+
+
+def test_a_corrupt_image_fails_the_run_instead_of_hanging_it(tmp_path, monkeypatch):
+    """An exception on a decode worker travels through the producer thread to next_batch()."""
+    from kf_benchmarks_b200 import datasets
+    monkeypatch.setattr(pp, "SHUFFLE_BUFFER_SIZE", 0)
+    d = str(tmp_path / "imagenet")
+    os.makedirs(d)
+    recs = [tfrecord.encode_example({"image/encoded": [_jpeg(10)], "image/class/label": [1]}),
+            tfrecord.encode_example({"image/encoded": [b"this is not a JPEG"],
+                                     "image/class/label": [2]})]
+    tfrecord.write_records(os.path.join(d, "train-00000-of-00001"), recs)
+    ds = datasets.create_dataset(d, "imagenet")
+    p = P.make_params(model="trivial", data_dir=d, data_name="imagenet", device="cpu",
+                      data_format="NHWC", batch_size=2, datasets_num_private_threads=2)
+    src = pp.ImagenetSource(p, ds, 2, 16, 16, "cpu", True, 1, 0, 1)
+    with pytest.raises(RuntimeError, match="input pipeline failed"):
+        src.next_batch()
+    src.close()
+    # a producer that raises is reported by the generic ImageProducer as well
+    prod = cnn_util.ImageProducer(lambda: 1 / 0, 1)
+    prod.start()
+    with pytest.raises(RuntimeError, match="ZeroDivisionError"):
+        prod.get()
