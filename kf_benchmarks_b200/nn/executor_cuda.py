@@ -67,6 +67,7 @@ class CudaExecutor:
         self.dropout_seed = int(dropout_seed)
         self.step_index = 0
         self._stream = None
+        self._nvtx = os.environ.get("KFB_NVTX") == "1"
         # set by the benchmark driver when --comm_impl=p2p_fused: name -> kfb_push_target
         self.push_lookup: Optional[Callable[[str], object]] = None
         dev = self.device
@@ -379,8 +380,16 @@ class CudaExecutor:
     # ------------------------------------------------------------------ forward
     def forward(self, train: bool = True) -> None:
         s = self._s()
-        for node in self.graph.nodes:
-            getattr(self, "_fwd_" + node.op)(node, train, s)
+        if self._nvtx:
+            # KFB_NVTX=1: one NVTX range per node so that profilers attribute kernels to layers
+            # (ncu --nvtx --nvtx-include "fwd/<node name>")
+            for node in self.graph.nodes:
+                torch.cuda.nvtx.range_push("fwd/" + node.name)
+                getattr(self, "_fwd_" + node.op)(node, train, s)
+                torch.cuda.nvtx.range_pop()
+        else:
+            for node in self.graph.nodes:
+                getattr(self, "_fwd_" + node.op)(node, train, s)
         # the image buffer is only read by the forward pass (backward uses saved activations)
         self._free[self._cur].record(torch.cuda.current_stream(self.device))
 
@@ -731,7 +740,12 @@ class CudaExecutor:
         for node in reversed(g.nodes):
             if not self.needs_grad[node.output.id]:
                 continue
-            getattr(self, "_bwd_" + node.op)(node, s)
+            if self._nvtx:
+                torch.cuda.nvtx.range_push("bwd/" + node.name)
+                getattr(self, "_bwd_" + node.op)(node, s)
+                torch.cuda.nvtx.range_pop()
+            else:
+                getattr(self, "_bwd_" + node.op)(node, s)
             if on_grads_ready is not None and node.params:
                 lo, hi = self.store.span([p.name for p in node.params.values() if p.trainable])
                 if hi > lo:
