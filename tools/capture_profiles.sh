@@ -40,6 +40,16 @@ ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum 
 python tools/summarize_launches.py gpurun_out/launches_$TAG.csv \
     > profiles/resnet50_bs256_launches_$TAG.txt && head -12 profiles/resnet50_bs256_launches_$TAG.txt
 
+echo "== 2b. the same launch list with kernels renamed after the enclosing NVTX range (layer) =="
+KFB_NVTX=1 ncu --nvtx --print-nvtx-rename kernel \
+    --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum \
+    --clock-control none -s "$SKIP" -c "$PER" --csv --log-file gpurun_out/launches_nvtx_$TAG.csv \
+    $CMD > gpurun_out/ncu_launches_nvtx.log 2>&1 \
+  && python tools/summarize_launches.py gpurun_out/launches_nvtx_$TAG.csv 400 \
+       > profiles/resnet50_bs256_launches_by_layer_$TAG.txt \
+  && head -8 profiles/resnet50_bs256_launches_by_layer_$TAG.txt \
+  || echo "(per-layer list not produced; see gpurun_out/ncu_launches_nvtx.log)"
+
 echo "== 3. ncu --set full on the heaviest kernels =="
 for spec in "gemm:gemm_tcgen05_kernel" "bnbwd:bn_bwd_apply_kernel" "bnred:channel_reduce_kernel" \
             "bnapply:bn_apply_kernel"; do
