@@ -30,6 +30,8 @@ def peak_gbs():
 
 
 def short(name):
+    if name.startswith(("fwd/", "bwd/")):   # renamed after its NVTX range (KFB_NVTX=1): a layer
+        return name
     name = re.sub(r"^void ", "", name)
     m = re.match(r"([\w:]+(?:<[^(]*>)?)", name)
     return (m.group(1) if m else name).replace("kfb::", "")
