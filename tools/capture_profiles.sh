@@ -86,4 +86,5 @@ done
 echo "== 4. roofline =="
 MS=$(python -c "import json;print(json.loads(open('profiles/bench_1gpu_$TAG.json').read())['ms_per_step'])")
 python tools/roofline_model.py --launches profiles/resnet50_bs256_launches_$TAG.txt --step_ms "$MS" \
+    --by_layer profiles/resnet50_bs256_launches_by_layer_$TAG.txt \
     > profiles/roofline_resnet50_bs256_$TAG.md && tail -14 profiles/roofline_resnet50_bs256_$TAG.md

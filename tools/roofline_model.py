@@ -43,12 +43,14 @@ class _Costs(defaultdict):
     def __init__(self, bw, fl):
         super().__init__(lambda: [0.0, 0.0, 0.0])
         self.bw, self.fl = bw, fl
+        self.layers = defaultdict(lambda: [0.0, 0.0, 0.0])   # "fwd/<node>" | "bwd/<node>"
 
-    def add(self, cls, flops, nbytes):
-        e = self[cls]
-        e[0] += flops
-        e[1] += nbytes
-        e[2] += max(flops / self.fl, nbytes / self.bw)
+    def add(self, cls, flops, nbytes, layer=None):
+        roof = max(flops / self.fl, nbytes / self.bw)
+        for e in ([self[cls]] + ([self.layers[layer]] if layer else [])):
+            e[0] += flops
+            e[1] += nbytes
+            e[2] += roof
 
 
 def model_costs(graph, bw, fl):
@@ -62,27 +64,30 @@ def model_costs(graph, bw, fl):
             k = n.attrs["kh"] * n.attrs["kw"] * n.inputs[0].shape[-1]
             w = k * n.output.shape[-1]
             macs = (y // n.output.shape[-1]) * n.output.shape[-1] * k
-            c.add("conv fprop (W1)", 2.0 * macs, 2 * x + 2 * w + 2 * y)
+            c.add("conv fprop (W1)", 2.0 * macs, 2 * x + 2 * w + 2 * y, "fwd/" + n.name)
             if n is not first:                       # no input gradient for the image
-                c.add("conv dgrad (W2)", 2.0 * macs, 2 * y + 2 * w + 2 * x)
-            c.add("conv wgrad (W3)", 2.0 * macs, 2 * x + 2 * y + 4 * w)
+                c.add("conv dgrad (W2)", 2.0 * macs, 2 * y + 2 * w + 2 * x, "bwd/" + n.name)
+            c.add("conv wgrad (W3)", 2.0 * macs, 2 * x + 2 * y + 4 * w, "bwd/" + n.name)
         elif n.op == "bn":
             res = len(n.inputs) > 1
             # forward: statistics pass reads x; apply pass reads x (+ residual), writes y
-            c.add("BN fwd statistics (W4/W5)", 0, 2 * x)
-            c.add("BN fwd apply+ReLU+add (W5)", 0, 2 * x * (3 if res else 2))
+            c.add("BN fwd statistics (W4/W5)", 0, 2 * x, "fwd/" + n.name)
+            c.add("BN fwd apply+ReLU+add (W5)", 0, 2 * x * (3 if res else 2), "fwd/" + n.name)
             # backward: reduce pass reads dy, x; apply pass reads dy, x, writes dx (+ d residual)
-            c.add("BN bwd reduce (W5)", 0, 2 * x * 2)
-            c.add("BN bwd apply (W5)", 0, 2 * x * (4 if res else 3))
+            c.add("BN bwd reduce (W5)", 0, 2 * x * 2, "bwd/" + n.name)
+            c.add("BN bwd apply (W5)", 0, 2 * x * (4 if res else 3), "bwd/" + n.name)
         elif n.op == "pool":
-            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y) + 2 * (y + x))
+            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y), "fwd/" + n.name)
+            c.add("pool fwd+bwd (W6)", 0, 2 * (y + x), "bwd/" + n.name)
         elif n.op == "spatial_mean":
-            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y) * 2)
+            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y), "fwd/" + n.name)
+            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y), "bwd/" + n.name)
         elif n.op == "affine":
             k, m = n.inputs[0].shape[-1], n.output.shape[-1]
             rows = x // k
-            for cls in ("conv fprop (W1)", "conv dgrad (W2)", "conv wgrad (W3)"):
-                c.add(cls, 2.0 * rows * k * m, 2 * x + 2 * k * m + 4 * y)
+            for cls, ph in (("conv fprop (W1)", "fwd/"), ("conv dgrad (W2)", "bwd/"),
+                            ("conv wgrad (W3)", "bwd/")):
+                c.add(cls, 2.0 * rows * k * m, 2 * x + 2 * k * m + 4 * y, ph + n.name)
     ntrain = sum(p.numel for p in graph.params.values() if p.trainable)
     # fused optimizer: read g, w, m (fp32), write w, m (fp32) and the fp16 shadow
     c.add("optimizer / all-reduce epilogue (W10/W11)", 0, ntrain * (4 * 5 + 2))
@@ -124,12 +129,43 @@ def measured(path):
     return out, other
 
 
+def by_layer_report(costs, path, top=25):
+    """Per-layer table from a launch list whose kernels were renamed after their NVTX range
+    (tools/capture_profiles.sh step 2b): measured time of "fwd/<node>" / "bwd/<node>" against
+    the roof of the same node and phase, largest absolute gap first."""
+    meas = {}
+    with open(path) as f:
+        for ln in f:
+            m = re.match(r"\s+([\d.]+)\s+[\d.]+%\s+\d+\s+[\d.]+\s+[\d.]+\s+[\d.]+%\s+((?:fwd|bwd)/\S+)",
+                         ln)
+            if m:
+                meas[m.group(2).rstrip("/")] = meas.get(m.group(2).rstrip("/"), 0.0) + \
+                    float(m.group(1))
+    rows = []
+    for layer, (flops, nbytes, roof_s) in costs.layers.items():
+        t = meas.get(layer.rstrip("/"))
+        if t is not None:
+            rows.append((t - roof_s * 1e3, layer, flops, nbytes, roof_s * 1e3, t))
+    rows.sort(reverse=True)
+    print()
+    print("## Layers farthest from their roof (%d of %d matched layers)" % (min(top, len(rows)),
+                                                                            len(rows)))
+    print()
+    print("| layer / phase | GFLOP | GB | roof ms | measured ms | achieved | gap ms |")
+    print("|---|---|---|---|---|---|---|")
+    for gap, layer, flops, nbytes, roof, t in rows[:top]:
+        print("| %s | %.1f | %.3f | %.3f | %.3f | %.0f %% | %.3f |" %
+              (layer, flops / 1e9, nbytes / 1e9, roof, t, 100 * roof / t if t else 0.0, gap))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--model", default="resnet50")
     ap.add_argument("--batch_size", type=int, default=256)
     ap.add_argument("--launches",
                     default=os.path.join(ROOT, "profiles", "resnet50_bs256_launches_r1e.txt"))
+    ap.add_argument("--by_layer", default=None,
+                    help="launch list with NVTX-renamed kernels (per-layer table)")
     ap.add_argument("--step_ms", type=float, default=None,
                     help="free-running step time to set the total against")
     args = ap.parse_args()
@@ -173,6 +209,8 @@ def main():
         print()
         print("No launch list given: at the roof this step would take %.2f ms = %.0f examples/sec." %
               (tot_roof, args.batch_size / (tot_roof * 1e-3)))
+    if args.by_layer and os.path.exists(args.by_layer):
+        by_layer_report(costs, args.by_layer)
     if args.step_ms:
         print()
         print("Free-running step: %.2f ms -> %.0f %% of the summed roof." %
