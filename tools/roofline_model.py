@@ -166,6 +166,8 @@ def main():
                     default=os.path.join(ROOT, "profiles", "resnet50_bs256_launches_r1e.txt"))
     ap.add_argument("--by_layer", default=None,
                     help="launch list with NVTX-renamed kernels (per-layer table)")
+    ap.add_argument("--list_layers", type=int, default=0,
+                    help="also list the N layers / phases with the largest roof (analytic only)")
     ap.add_argument("--step_ms", type=float, default=None,
                     help="free-running step time to set the total against")
     args = ap.parse_args()
@@ -211,6 +213,17 @@ def main():
               (tot_roof, args.batch_size / (tot_roof * 1e-3)))
     if args.by_layer and os.path.exists(args.by_layer):
         by_layer_report(costs, args.by_layer)
+    if args.list_layers > 0:
+        print()
+        print("## Largest layers by roof (analytic)")
+        print()
+        print("| layer / phase | GFLOP | GB | roof us | bound |")
+        print("|---|---|---|---|---|")
+        rows = sorted(costs.layers.items(), key=lambda kv: -kv[1][2])[:args.list_layers]
+        for layer, (flops, nbytes, roof_s) in rows:
+            print("| %s | %.1f | %.3f | %.1f | %s |" %
+                  (layer, flops / 1e9, nbytes / 1e9, roof_s * 1e6,
+                   "tensor" if flops / fl > nbytes / bw else "HBM"))
     if args.step_ms:
         print()
         print("Free-running step: %.2f ms -> %.0f %% of the summed roof." %
