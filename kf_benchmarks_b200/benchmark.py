@@ -611,7 +611,8 @@ class BenchmarkCNN:
         profiler = None
         if p.tfprof_file or p.trace_file:
             from .utils import profile as profile_lib
-            profiler = profile_lib.StepProfiler(p, self.device)
+            profiler = profile_lib.StepProfiler(p, self.device,
+                                                graph=getattr(self.executor, "graph", None))
         from .utils.summaries import SummaryWriter
         summaries = SummaryWriter(p, p.train_dir) if rank0 else None
         if rank0:

@@ -299,3 +299,29 @@ def test_native_launcher(tmp_path):
                          text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert "total images/sec:" in res.stdout
+
+
+def test_analytic_roofline_of_the_headline_step():
+    """utils/roofline.py: FLOPs / bytes / roof per kernel class from the graph alone; ResNet-50
+    at batch 256 needs 5.9 TFLOP of GEMM work per step (3 x 2 x 4.1 GMAC x 256 minus the stem's
+    input gradient) and its roof is a memory-bound ~14 ms at the B200 peaks."""
+    from kf_benchmarks_b200 import datasets
+    from kf_benchmarks_b200.models import model_config
+    from kf_benchmarks_b200.utils import roofline
+    p = P.make_params(model="resnet50", batch_size=256, use_fp16=True, data_format="NHWC")
+    ds = datasets.create_dataset(None, None)
+    m = model_config.get_model_config("resnet50", ds, p)
+    m.set_batch_size(256)
+    g = m.build_graph(ds.num_classes, batch_size=256)
+    costs = roofline.model_costs(g, 6550.7e9, 1399.7e12)
+    flops = sum(v[0] for v in costs.values())
+    assert 5.7e12 < flops < 6.1e12
+    fprop = costs["conv fprop (W1)"][0]
+    assert abs(fprop - 2 * 256 * 4.09e9) / fprop < 0.06            # 4.1 GMAC per image
+    roof_ms = sum(v[2] for v in costs.values()) * 1e3
+    assert 13.0 < roof_ms < 15.0
+    assert sum(v[2] for v in costs.layers.values()) <= sum(v[2] for v in costs.values())
+    assert roofline.class_of("void kfb::gemm_tcgen05_kernel<128, 2, true>(...)") == "conv fprop (W1)"
+    assert roofline.class_of("void kfb::gemm_tcgen05_kernel<64, 4, true>(...)") == "conv wgrad (W3)"
+    assert roofline.class_of("void kfb::bn_bwd_apply_kernel(...)") == "BN bwd apply (W5)"
+    assert roofline.class_of("at::native::vectorized_elementwise_kernel") is None

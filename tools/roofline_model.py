@@ -13,7 +13,6 @@ usage: python tools/roofline_model.py [--model resnet50] [--batch_size 256]
                                       [--launches profiles/resnet50_bs256_launches_r1e.txt]
 """
 import argparse
-import json
 import os
 import re
 import sys
@@ -23,92 +22,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def peaks():
-    with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-        d = json.load(f)
-    return float(d["hbm_gbs"]) * 1e9, float(d["bf16_tflops_sustained"]) * 1e12
-
-
-def numel(shape):
-    n = 1
-    for s in shape:
-        n *= s
-    return n
-
-
-class _Costs(defaultdict):
-    """class -> [flops, bytes, roof seconds]; the roof is summed kernel by kernel (a class that
-    mixes tensor-bound and HBM-bound layers is bounded by the sum of the per-layer maxima)."""
-
-    def __init__(self, bw, fl):
-        super().__init__(lambda: [0.0, 0.0, 0.0])
-        self.bw, self.fl = bw, fl
-        self.layers = defaultdict(lambda: [0.0, 0.0, 0.0])   # "fwd/<node>" | "bwd/<node>"
-
-    def add(self, cls, flops, nbytes, layer=None):
-        roof = max(flops / self.fl, nbytes / self.bw)
-        for e in ([self[cls]] + ([self.layers[layer]] if layer else [])):
-            e[0] += flops
-            e[1] += nbytes
-            e[2] += roof
-
-
-def model_costs(graph, bw, fl):
-    """Costs of one training step (forward + backward) per kernel class."""
-    c = _Costs(bw, fl)
-    first = graph.nodes[0]
-    for n in graph.nodes:
-        x = numel(n.inputs[0].shape)
-        y = numel(n.output.shape)
-        if n.op == "conv":
-            k = n.attrs["kh"] * n.attrs["kw"] * n.inputs[0].shape[-1]
-            w = k * n.output.shape[-1]
-            macs = (y // n.output.shape[-1]) * n.output.shape[-1] * k
-            c.add("conv fprop (W1)", 2.0 * macs, 2 * x + 2 * w + 2 * y, "fwd/" + n.name)
-            if n is not first:                       # no input gradient for the image
-                c.add("conv dgrad (W2)", 2.0 * macs, 2 * y + 2 * w + 2 * x, "bwd/" + n.name)
-            c.add("conv wgrad (W3)", 2.0 * macs, 2 * x + 2 * y + 4 * w, "bwd/" + n.name)
-        elif n.op == "bn":
-            res = len(n.inputs) > 1
-            # forward: statistics pass reads x; apply pass reads x (+ residual), writes y
-            c.add("BN fwd statistics (W4/W5)", 0, 2 * x, "fwd/" + n.name)
-            c.add("BN fwd apply+ReLU+add (W5)", 0, 2 * x * (3 if res else 2), "fwd/" + n.name)
-            # backward: reduce pass reads dy, x; apply pass reads dy, x, writes dx (+ d residual)
-            c.add("BN bwd reduce (W5)", 0, 2 * x * 2, "bwd/" + n.name)
-            c.add("BN bwd apply (W5)", 0, 2 * x * (4 if res else 3), "bwd/" + n.name)
-        elif n.op == "pool":
-            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y), "fwd/" + n.name)
-            c.add("pool fwd+bwd (W6)", 0, 2 * (y + x), "bwd/" + n.name)
-        elif n.op == "spatial_mean":
-            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y), "fwd/" + n.name)
-            c.add("pool fwd+bwd (W6)", 0, 2 * (x + y), "bwd/" + n.name)
-        elif n.op == "affine":
-            k, m = n.inputs[0].shape[-1], n.output.shape[-1]
-            rows = x // k
-            for cls, ph in (("conv fprop (W1)", "fwd/"), ("conv dgrad (W2)", "bwd/"),
-                            ("conv wgrad (W3)", "bwd/")):
-                c.add(cls, 2.0 * rows * k * m, 2 * x + 2 * k * m + 4 * y, ph + n.name)
-    ntrain = sum(p.numel for p in graph.params.values() if p.trainable)
-    # fused optimizer: read g, w, m (fp32), write w, m (fp32) and the fp16 shadow
-    c.add("optimizer / all-reduce epilogue (W10/W11)", 0, ntrain * (4 * 5 + 2))
-    return c
-
-
-CLASS_OF = [
-    (r"gemm_tcgen05_kernel<\d+, 0,", "conv fprop (W1)"),
-    (r"gemm_tcgen05_kernel<\d+, 2,", "conv fprop (W1)"),
-    (r"im2col_small_c", "conv fprop (W1)"),
-    (r"gemm_tcgen05_kernel<\d+, 3,", "conv dgrad (W2)"),
-    (r"gemm_tcgen05_kernel<\d+, 5,", "conv dgrad (W2)"),
-    (r"gemm_tcgen05_kernel<\d+, [14],", "conv wgrad (W3)"),
-    (r"splitk_reduce", "conv wgrad (W3)"),
-    (r"channel_reduce_kernel<0>|bn_finalize", "BN fwd statistics (W4/W5)"),
-    (r"bn_apply_kernel", "BN fwd apply+ReLU+add (W5)"),
-    (r"channel_reduce_kernel<1>|bn_bwd_finalize", "BN bwd reduce (W5)"),
-    (r"bn_bwd_apply", "BN bwd apply (W5)"),
-    (r"pool_|spatial_mean", "pool fwd+bwd (W6)"),
-    (r"optimizer_step|allreduce_update", "optimizer / all-reduce epilogue (W10/W11)"),
-]
+from kf_benchmarks_b200.utils.roofline import CLASS_OF, model_costs, peaks  # noqa: E402
 
 
 def measured(path):
