@@ -2,7 +2,6 @@
 COCO metric (reference: T/ssd_dataloader.py, T/coco_metric.py)."""
 import io
 import json
-import os
 
 import numpy as np
 import pytest
@@ -224,7 +223,7 @@ def test_ssd_eval_hooks_on_the_cpu_executor(tmp_path):
 
 def test_backbone_loading_and_graph_dumps(tmp_path):
     import torch
-    from kf_benchmarks_b200 import benchmark, ckpt as ckpt_lib, datasets, params as P
+    from kf_benchmarks_b200 import benchmark, datasets, params as P
     from kf_benchmarks_b200.models import model_config
     from kf_benchmarks_b200.nn.params import ParameterStore
     ds = datasets.create_dataset(None, "coco")
