@@ -125,7 +125,7 @@ def _sanitizer_run(tmp_path, name, flags, env_extra):
     scratch = tmp_path / "data"
     scratch.mkdir()
     env = dict(os.environ, **env_extra)
-    run = subprocess.run([exe, str(scratch), "12"], capture_output=True, text=True, env=env,
+    run = subprocess.run([exe, str(scratch), "6"], capture_output=True, text=True, env=env,
                          timeout=600)
     report = run.stdout + run.stderr
     assert run.returncode == 0, report

@@ -425,11 +425,9 @@ def test_parameter_server_checkpoints_use_the_v_scope(tmp_path):
 
 
 @pytest.mark.parametrize("extra", [
-    dict(gradient_repacking=2),
-    dict(all_reduce_spec="xring"),
     dict(all_reduce_spec="pscpu:2k:xring", agg_small_grads_max_bytes=1024,
          agg_small_grads_max_group=10),
-    dict(all_reduce_spec="nccl", compact_gradient_transfer=False),
+    dict(all_reduce_spec="nccl", compact_gradient_transfer=False, gradient_repacking=2),
     dict(hierarchical_copy=True, gradient_repacking=3),
 ])
 def test_gradient_aggregation_matrix(extra, tmp_path):
