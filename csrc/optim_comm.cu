@@ -24,6 +24,8 @@
 // Synchronisation protocol: every rank owns a flag page in symmetric memory. Flags only ever
 // grow (per-call sequence numbers), are written with st.release.sys after a system fence and
 // polled with ld.acquire.sys, so there is no reset race. Waits are bounded (trap after 20 s).
+#include <stdlib.h>
+
 #include "kfb_common.cuh"
 #include "../include/kfb200.h"
 
@@ -713,8 +715,14 @@ extern "C" int kfb_allreduce_update(int mode, int rank, int nranks, void* const*
   PeerCtx c;
   if (fill_peer_ctx(&c, rank, nranks, src, reduced, flags)) return 2;
   if (blocks <= 0) {
-    // enough CTAs to keep the links busy, few enough to leave SMs to the backward kernels
-    blocks = count >= (4ll << 20) ? 96 : (count >= (1ll << 20) ? 64 : 32);
+    // enough CTAs to keep the links busy, few enough to leave SMs to the backward kernels;
+    // KFB_AR_BLOCKS overrides the choice for sweeps on the device (read once)
+    static const int forced = [] {
+      const char* e = getenv("KFB_AR_BLOCKS");
+      return (e != nullptr && *e != 0) ? atoi(e) : 0;
+    }();
+    blocks = forced > 0 ? forced
+                        : (count >= (4ll << 20) ? 96 : (count >= (1ll << 20) ? 64 : 32));
   }
   if (blocks > 148) blocks = 148;
   cudaStream_t st = (cudaStream_t)stream;
