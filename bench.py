@@ -212,6 +212,8 @@ def main() -> int:
     ap.add_argument("--kungfu_option", default="sync_sgd")
     ap.add_argument("--optimizer", default="momentum")
     ap.add_argument("--comm_impl", default="p2p")
+    ap.add_argument("--bucket_bytes", type=int, default=None,
+                    help="gradient bucket size of the overlapped exchange (default: the flag's)")
     ap.add_argument("--no_e2e", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -234,7 +236,7 @@ def main() -> int:
         variable_update=args.variable_update, kungfu_option=args.kungfu_option,
         num_gpus=1 if kungfu else args.gpus, optimizer=args.optimizer,
         comm_impl=args.comm_impl, num_batches=args.steps, num_warmup_batches=warmup,
-        data_format="NHWC")
+        data_format="NHWC", **({"bucket_bytes": args.bucket_bytes} if args.bucket_bytes else {}))
     p = benchmark.setup(p)
     bench = benchmark.BenchmarkCNN(p)
     rank = bench.rank
