@@ -377,3 +377,35 @@ def test_a_corrupt_image_fails_the_run_instead_of_hanging_it(tmp_path, monkeypat
     prod.start()
     with pytest.raises(RuntimeError, match="ZeroDivisionError"):
         prod.get()
+
+
+def test_native_image_transform_property_random_geometry():
+    """Random crops / virtual sizes / windows / methods / flips / jitter: the native transform
+    always equals the NumPy restatement (hypothesis drives the geometry)."""
+    from hypothesis import given, settings, strategies as st
+    ni = _native_image()
+    img = np.random.RandomState(9).randint(0, 256, (23, 31, 3)).astype(np.uint8)
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.data())
+    def check(data):
+        ch = data.draw(st.integers(1, 23))
+        cw = data.draw(st.integers(1, 31))
+        top = data.draw(st.integers(0, 23 - ch))
+        left = data.draw(st.integers(0, 31 - cw))
+        vh = data.draw(st.integers(1, 40))
+        vw = data.draw(st.integers(1, 40))
+        oh = data.draw(st.integers(1, vh))
+        ow = data.draw(st.integers(1, vw))
+        oy = data.draw(st.integers(0, vh - oh))
+        ox = data.draw(st.integers(0, vw - ow))
+        method = data.draw(st.sampled_from(sorted(ni.METHODS)))
+        flip = data.draw(st.booleans())
+        distort = data.draw(st.one_of(st.none(), st.tuples(
+            st.sampled_from([1, 2]), st.floats(-32, 32), st.floats(0.5, 1.5),
+            st.floats(-0.2, 0.2), st.floats(0.5, 1.5))))
+        op = ni.make_op(img, (top, left, ch, cw), (vh, vw), (oy, ox, oh, ow), method, flip, distort)
+        got, want = ni.transform(img, op), ni.transform_reference(img, op)
+        assert got.shape == (oh, ow, 3)
+        assert np.abs(got - want).max() < 2e-4
+    check()
