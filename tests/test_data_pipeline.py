@@ -386,7 +386,7 @@ def test_native_image_transform_property_random_geometry():
     ni = _native_image()
     img = np.random.RandomState(9).randint(0, 256, (23, 31, 3)).astype(np.uint8)
 
-    @settings(max_examples=60, deadline=None)
+    @settings(max_examples=60, deadline=None, derandomize=True, database=None)
     @given(st.data())
     def check(data):
         ch = data.draw(st.integers(1, 23))
