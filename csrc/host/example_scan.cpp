@@ -6,6 +6,8 @@
 #include <cstdint>
 #include <cstring>
 
+#include "../../include/kfb200_host.h"
+
 namespace {
 
 struct Span {

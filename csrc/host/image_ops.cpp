@@ -22,32 +22,7 @@
 #include <immintrin.h>
 #endif
 
-extern "C" {
-typedef struct {
-  int ih, iw, src_stride;  // source: uint8 RGB, ih x iw, row stride in bytes
-  int top, left, ch, cw;   // crop rectangle in source pixels
-  int vh, vw;              // size the crop is resized to
-  int oy, ox, oh, ow;      // window of that resized image which is produced (eval centre crop)
-  int method;              // 0 bilinear, 1 nearest, 2 bicubic, 3 area,
-                           // 4 tf.image.crop_and_resize (bilinear) of the float `box`
-  int flip;                // mirror the crop horizontally before it is resized
-  int distort_order;       // 0 none, 1 brightness - saturation/hue - contrast,
-                           // 2 brightness - contrast - saturation/hue (T/preprocessing.py:281-303)
-  float brightness;        // added (0..255 scale)
-  float saturation;        // HSV saturation factor (result clamped to [0, 1])
-  float hue;               // HSV hue shift in turns ([-0.2, 0.2] in the reference)
-  float contrast;          // factor around the per-channel image mean
-  float scale, bias;       // out = value * scale + bias
-  int out_f16;             // 0: float32 output, 1: IEEE binary16 output
-  // method 4: normalised (y0, x0, y1, x1) window of the whole image, sampled like
-  // tf.image.crop_and_resize: in = y0 (H-1) + i (y1-y0)(H-1)/(oh-1), zero outside the image;
-  // `flip` then mirrors the output. crop / resized / window fields are ignored except oh, ow.
-  float box[4];
-  int per_channel;         // 1: out = value * scale3[k] + bias3[k] instead of scale / bias
-  float scale3[3], bias3[3];
-  int no_clamp;            // 1: the colour jitter does not clamp to [0, 255] at the end
-} kfb_image_op;
-}
+#include "../../include/kfb200_host.h"
 
 namespace {
 

@@ -27,6 +27,8 @@
 #include <thread>
 #include <vector>
 
+#include "../../include/kfb200_host.h"
+
 #if defined(__SSE4_2__)
 #include <nmmintrin.h>
 #endif

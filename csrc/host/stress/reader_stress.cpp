@@ -14,30 +14,7 @@
 #include <thread>
 #include <vector>
 
-extern "C" {
-const char* kfb_host_last_error();
-uint32_t kfb_masked_crc32c(const void* data, uint64_t len);
-void* kfb_rr_open(const char* const* paths, int npaths, int num_threads, int capacity,
-                  int check_crc, int repeat, int shuffle_files, uint64_t seed);
-void* kfb_rr_open2(const char* const* paths, int npaths, int num_threads, int capacity,
-                   int check_crc, int repeat, int shuffle_files, uint64_t seed, int deterministic);
-int kfb_rr_next(void* handle, const uint8_t** data, uint64_t* len);
-void kfb_rr_close(void* handle);
-int kfb_example_get_bytes(const uint8_t* data, uint64_t len, const char* key, const uint8_t** out,
-                          uint64_t* out_len);
-int kfb_example_get_numbers(const uint8_t* data, uint64_t len, const char* key, double* out,
-                            int cap);
-typedef struct {
-  int ih, iw, src_stride, top, left, ch, cw, vh, vw, oy, ox, oh, ow, method, flip, distort_order;
-  float brightness, saturation, hue, contrast, scale, bias;
-  int out_f16;
-  float box[4];
-  int per_channel;
-  float scale3[3], bias3[3];
-  int no_clamp;
-} kfb_image_op;
-int kfb_image_transform(const uint8_t* src, const kfb_image_op* op, void* out);
-}
+#include "../../../include/kfb200_host.h"
 
 namespace {
 
