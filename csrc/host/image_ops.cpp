@@ -363,6 +363,8 @@ extern "C" {
 
 const char* kfb_image_last_error() { return g_err; }
 
+int kfb_image_op_bytes() { return static_cast<int>(sizeof(kfb_image_op)); }
+
 // 0 on success; -1 on invalid arguments (kfb_image_last_error()).
 int kfb_image_transform(const uint8_t* src, const kfb_image_op* opp, void* out) {
   if (src == nullptr || opp == nullptr || out == nullptr) {

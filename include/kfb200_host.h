@@ -90,6 +90,8 @@ typedef struct {
 /* 0 on success; -1 on invalid arguments (kfb_image_last_error). `out` holds oh * ow * 3 elements. */
 int kfb_image_transform(const uint8_t* src, const kfb_image_op* op, void* out);
 const char* kfb_image_last_error(void);
+/* sizeof(kfb_image_op) as this library was built (bindings check their mirror against it). */
+int kfb_image_op_bytes(void);
 
 #ifdef __cplusplus
 }

@@ -51,6 +51,13 @@ def _function():
         fn.restype = ctypes.c_int
         fn.argtypes = [ctypes.c_void_p, ctypes.POINTER(ImageOp), ctypes.c_void_p]
         lib.kfb_image_last_error.restype = ctypes.c_char_p
+        try:
+            size = int(lib.kfb_image_op_bytes())
+        except AttributeError:
+            size = ctypes.sizeof(ImageOp)
+        if size != ctypes.sizeof(ImageOp):
+            raise RuntimeError("kfb_image_op is %d bytes in the library but %d in the binding: "
+                               "rebuild the host library" % (size, ctypes.sizeof(ImageOp)))
         _fn = fn
     return _fn
 
