@@ -656,6 +656,17 @@ using namespace kfb;
 
 extern "C" int kfb_flag_page_bytes(void) { return 4096; }
 
+// sizeof of the structures that cross the C ABI (0 kfb_conv_desc, 1 kfb_hyper, 2 kfb_push_target);
+// bindings compare their mirrors against these. -1 for an unknown index.
+extern "C" int kfb_sizeof(int which) {
+  switch (which) {
+    case 0: return (int)sizeof(kfb_conv_desc);
+    case 1: return (int)sizeof(kfb_hyper);
+    case 2: return (int)sizeof(kfb_push_target);
+    default: return -1;
+  }
+}
+
 // Sequence numbers from device memory (multi-rank CUDA graphs): after kfb_set_seq_base(p) every
 // collective of this process adds *p (a uint32 in device memory, 0 at first) to the `seq` it is
 // given. A captured step ends with kfb_seq_advance(p, k), k = collectives per step, so each

@@ -212,6 +212,9 @@ int kfb_loss_scale_update(float* state, int* flag, int inc_every, float* dyn,
  * nranks device pointers (peer mappings); seq must increase by one per collective call and
  * be identical on every rank. */
 int kfb_flag_page_bytes(void);
+/* sizeof of the structures that cross this ABI as the library was built: 0 kfb_conv_desc,
+ * 1 kfb_hyper, 2 kfb_push_target (-1 otherwise). Bindings check their mirrors against it. */
+int kfb_sizeof(int which);
 /* Device-resident sequence offset for multi-rank CUDA graphs (B200 addition; the reference has no
  * graph replay): once set, every collective below adds the uint32 at `counter` (device memory)
  * to its `seq`; kfb_seq_advance bumps it on a stream (the last node of a captured step). */

@@ -121,3 +121,19 @@ def test_every_flag_is_either_used_or_declared_without_effect():
               if f not in declared and not re.search(r"\b%s\b" % re.escape(f), src)]
     assert silent == []
     assert not (set(P.IGNORED_ON_B200) - set(P.make_params()._fields))
+
+
+def test_ctypes_mirrors_match_the_built_library():
+    """The structures that cross the C ABI have the size the library was compiled with
+    (the library loads without a GPU)."""
+    import ctypes
+    from kf_benchmarks_b200 import build as build_lib
+    from kf_benchmarks_b200.ops import native
+    from kf_benchmarks_b200.parallel.strategy import Hyper, PushTarget
+    if not native.available():
+        build_lib.build()
+    lib = native.load()
+    assert lib.kfb_sizeof(0) == ctypes.sizeof(native.ConvDesc)
+    assert lib.kfb_sizeof(1) == ctypes.sizeof(Hyper)
+    assert lib.kfb_sizeof(2) == ctypes.sizeof(PushTarget)
+    assert lib.kfb_sizeof(99) == -1
