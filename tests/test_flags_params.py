@@ -137,3 +137,68 @@ def test_ctypes_mirrors_match_the_built_library():
     assert lib.kfb_sizeof(1) == ctypes.sizeof(Hyper)
     assert lib.kfb_sizeof(2) == ctypes.sizeof(PushTarget)
     assert lib.kfb_sizeof(99) == -1
+
+
+def test_every_native_call_site_names_an_exported_function_with_the_right_arity():
+    """Static check of the Python -> C ABI boundary: every ``native.call("name", ...)`` in the
+    package and the tools names a function the built library exports, and passes as many
+    arguments as the prototype in include/kfb200.h declares (sites with a starred argument are
+    checked for the minimum only)."""
+    import ast
+    import os
+    import re
+    from kf_benchmarks_b200 import build as build_lib
+    from kf_benchmarks_b200.ops import native
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not native.available():
+        build_lib.build()
+    lib = native.load()
+    header = open(os.path.join(root, "include", "kfb200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    arity = {}
+    for m in re.finditer(r"\b(?:int|long long|const char\*)\s+kfb_(\w+)\s*\(([^;{]*?)\)\s*;", header):
+        params = m.group(2).strip()
+        arity[m.group(1)] = 0 if params in ("", "void") else params.count(",") + 1
+    assert len(arity) > 60
+    sites = 0
+    for top in ("kf_benchmarks_b200", "tools"):
+        for d, _, fs in os.walk(os.path.join(root, top)):
+            for f in fs:
+                if not f.endswith(".py"):
+                    continue
+                tree = ast.parse(open(os.path.join(d, f)).read())
+                for node in ast.walk(tree):
+                    if not (isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute)
+                            and node.func.attr == "call" and isinstance(node.func.value, ast.Name)
+                            and node.func.value.id == "native" and node.args
+                            and isinstance(node.args[0], ast.Constant)
+                            and isinstance(node.args[0].value, str)):
+                        continue
+                    name = node.args[0].value
+                    where = "%s:%d native.call(%r)" % (f, node.lineno, name)
+                    assert hasattr(lib, "kfb_" + name), where + ": not exported"
+                    assert name in arity, where + ": no prototype in include/kfb200.h"
+                    given = len(node.args) - 1
+                    starred = any(isinstance(a, ast.Starred) for a in node.args)
+                    if starred:
+                        assert given - 1 <= arity[name], where
+                    else:
+                        assert given == arity[name], "%s: %d arguments, prototype has %d" % (
+                            where, given, arity[name])
+                    sites += 1
+    assert sites > 80
+    # direct calls through the ctypes handle (lib.kfb_xxx(...)) name exported functions too
+    host = None
+    for top in ("kf_benchmarks_b200", "tools", "tests"):
+        for d, _, fs in os.walk(os.path.join(root, top)):
+            for f in fs:
+                if not f.endswith(".py") or f == "test_flags_params.py":
+                    continue
+                for name in set(re.findall(r"\.kfb_(\w+)\b", open(os.path.join(d, f)).read())):
+                    if hasattr(lib, "kfb_" + name):
+                        continue
+                    if host is None:
+                        from kf_benchmarks_b200.data import native_reader
+                        build_lib.build_host()
+                        host = native_reader._load()
+                    assert hasattr(host, "kfb_" + name), "%s: kfb_%s is not exported" % (f, name)
