@@ -202,3 +202,77 @@ def test_every_native_call_site_names_an_exported_function_with_the_right_arity(
                         build_lib.build_host()
                         host = native_reader._load()
                     assert hasattr(host, "kfb_" + name), "%s: kfb_%s is not exported" % (f, name)
+
+
+def test_native_call_argument_types_match_the_prototypes():
+    """Static type check of the Python -> C boundary: where a call site builds an argument with
+    a recognisable constructor (i32 / i64 / f32 / u64 / c_uint / ptr / byref / None ...), its
+    kind must be the kind of the parameter in include/kfb200.h - an int passed for a long long
+    (or the reverse) leaves half a register undefined."""
+    import ast
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "kfb200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+
+    def kind_of_param(p):
+        p = p.strip()
+        if "*" in p:
+            return "ptr"
+        for prefix, kind in (("unsigned long long", "u64"), ("long long", "i64"),
+                             ("unsigned", "u32"), ("float", "f32"), ("int", "i32")):
+            if p.startswith(prefix):
+                return kind
+        return "?"
+
+    protos = {}
+    for m in re.finditer(r"\b(?:int|long long|const char\*)\s+kfb_(\w+)\s*\(([^;{]*?)\)\s*;", header):
+        ps = m.group(2).strip()
+        protos[m.group(1)] = [] if ps in ("", "void") else [kind_of_param(x) for x in ps.split(",")]
+    ctor = {"i32": "i32", "i64": "i64", "f32": "f32", "u64": "u64", "c_uint": "u32",
+            "c_int": "i32", "c_longlong": "i64", "c_ulonglong": "u64", "c_float": "f32",
+            "ptr": "ptr", "byref": "ptr", "c_void_p": "ptr", "_s": "ptr", "stream_ptr": "ptr",
+            "_w16": "ptr", "_w32": "ptr", "_g32": "ptr", "_ptr_at": "ptr"}
+
+    def kind_of_expr(e):
+        if isinstance(e, ast.Constant) and e.value is None:
+            return "ptr"
+        if isinstance(e, ast.Call):
+            f = e.func
+            name = f.id if isinstance(f, ast.Name) else (f.attr if isinstance(f, ast.Attribute)
+                                                         else None)
+            return ctor.get(name)
+        if isinstance(e, ast.Attribute) and e.attr == "p":
+            return "ptr"
+        if isinstance(e, ast.IfExp):
+            a, b = kind_of_expr(e.body), kind_of_expr(e.orelse)
+            return a if a == b else (a or b)
+        return None
+
+    bad, checked = [], 0
+    for top in ("kf_benchmarks_b200", "tools"):
+        for d, _, fs in os.walk(os.path.join(root, top)):
+            for f in fs:
+                if not f.endswith(".py"):
+                    continue
+                tree = ast.parse(open(os.path.join(d, f)).read())
+                for node in ast.walk(tree):
+                    if not (isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute)
+                            and node.func.attr == "call" and isinstance(node.func.value, ast.Name)
+                            and node.func.value.id == "native" and node.args
+                            and isinstance(node.args[0], ast.Constant)):
+                        continue
+                    name = node.args[0].value
+                    if name not in protos or any(isinstance(a, ast.Starred) for a in node.args):
+                        continue
+                    for i, (a, want) in enumerate(zip(node.args[1:], protos[name])):
+                        got = kind_of_expr(a)
+                        if got is None:
+                            continue
+                        checked += 1
+                        if got != want:
+                            bad.append("%s:%d %s arg %d: passes %s, prototype wants %s" %
+                                       (f, node.lineno, name, i, got, want))
+    assert checked > 600
+    assert not bad, "\n".join(bad)
