@@ -541,11 +541,13 @@ class BenchmarkCNN:
                                 ctypes.c_uint(self._graph_collectives), native.stream_ptr())
             if multi:
                 self.comm.seq = seq0              # nothing ran during capture
+            eng.step_count -= 1                   # finish_step counted the captured (not run) step
             self._graph = g
             _log("Captured the training step in a CUDA graph")
         eng.push_dynamic_hyper(lr)
         self._last_lr = lr
         self._graph.replay()
+        eng.step_count += 1                       # Adam's bias correction reads it (dyn[2])
         if self.world > 1:
             self.comm.graph_replayed(self._graph_collectives)
         self.global_step += 1
