@@ -171,3 +171,71 @@ def test_sequence_numbers_stay_consecutive_across_graph_replays():
     comm = types.SimpleNamespace(seq=2 ** 32 - 2, _dev_base=7)
     a, b, c = (P2PComm.next_seq(comm) for _ in range(3))
     assert ((b - a) & 0xFFFFFFFF) == 1 and ((c - b) & 0xFFFFFFFF) == 1
+
+
+def test_graphed_step_control_flow_with_two_ranks(monkeypatch):
+    """`BenchmarkCNN._step_graphed` for a multi-rank job, driven with stand-ins for the device
+    (no CUDA here): two eager steps, one capture, replays - the collectives' sequence numbers
+    and the optimizer step count stay in step with what an eager run would have used."""
+    import contextlib
+    import types
+
+    import torch
+    from kf_benchmarks_b200 import benchmark
+    from kf_benchmarks_b200.ops import native
+    from kf_benchmarks_b200.parallel.comm import P2PComm
+
+    calls = []
+    monkeypatch.setattr(native, "call", lambda name, *a: calls.append(name))
+    monkeypatch.setattr(native, "stream_ptr", lambda: None)
+    monkeypatch.setattr(native, "ptr", lambda t: None)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda dev=None: None)
+    monkeypatch.setattr(torch.cuda, "CUDAGraph", lambda: types.SimpleNamespace(
+        replay=lambda: calls.append("replay")))
+    monkeypatch.setattr(torch.cuda, "graph", lambda g: contextlib.nullcontext())
+
+    comm = types.SimpleNamespace(seq=0, _dev_base=0, barrier=lambda: None)
+    comm.enable_device_seq = lambda: "counter"
+    comm.graph_replayed = lambda k: P2PComm.graph_replayed(comm, k)
+    launched = []
+
+    class Engine:
+        step_count = 0
+        loss_scale = 1.0
+
+        def learning_rate(self, *a):
+            return 0.1
+
+        def enable_dynamic_hyper(self):
+            pass
+
+        def push_dynamic_hyper(self, lr):
+            self.pushed_t = self.step_count + 1
+
+        def begin_step(self, lr):
+            pass
+
+        def on_grads_ready(self, lo, hi):
+            pass
+
+        def finish_step(self):
+            for _ in range(3):                                   # three buckets per step
+                launched.append(P2PComm.next_seq(comm))
+            self.step_count += 1
+
+    ex = types.SimpleNamespace(set_inputs=lambda *a: None, forward=lambda train: None,
+                               loss_backward=lambda **kw: None)
+    b = types.SimpleNamespace(executor=ex, engine=Engine(), comm=comm, world=2, global_step=0,
+                              device=torch.device("cpu"), dataset=types.SimpleNamespace(
+                                  num_examples_per_epoch=lambda s: 1000),
+                              input_source=types.SimpleNamespace(next_batch=lambda: ()),
+                              _examples_per_step=lambda: 8)
+    for _ in range(6):
+        benchmark.BenchmarkCNN._step_graphed(b)
+    assert b.global_step == 6 and b.engine.step_count == 6
+    assert b._graph_collectives == 3 and calls.count("replay") == 4
+    assert calls.count("seq_advance") == 1                        # recorded once, in the capture
+    assert launched == [1, 2, 3, 4, 5, 6, 7, 8, 9]                # 2 eager steps + the capture
+    assert comm.seq == 6 + 4 * 3 and comm._dev_base == 4 * 3      # 4 replays moved the mirror
+    assert b.engine.pushed_t == 6                                 # Adam's t of the 6th step
+    assert P2PComm.next_seq(comm) == 19 - 12                      # an eager call afterwards
