@@ -239,3 +239,55 @@ def test_graphed_step_control_flow_with_two_ranks(monkeypatch):
     assert comm.seq == 6 + 4 * 3 and comm._dev_base == 4 * 3      # 4 replays moved the mirror
     assert b.engine.pushed_t == 6                                 # Adam's t of the 6th step
     assert P2PComm.next_seq(comm) == 19 - 12                      # an eager call afterwards
+
+
+def test_allreduce_call_passes_the_prototypes_argument_lists(monkeypatch):
+    """UpdateEngine._allreduce_call builds its argument list with a starred tail: run it with
+    stand-ins and compare the lists with the prototypes of include/kfb200.h (pull and NVLS)."""
+    import ctypes
+    import os
+    import re
+    import types
+
+    from kf_benchmarks_b200.ops import native
+    from kf_benchmarks_b200.parallel.strategy import Hyper, UpdateEngine
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = re.sub(r"/\*.*?\*/", "", open(os.path.join(root, "include", "kfb200.h")).read(),
+                    flags=re.S)
+
+    def arity(name):
+        m = re.search(r"\bint\s+kfb_%s\s*\(([^;{]*?)\)\s*;" % name, header)
+        return m.group(1).count(",") + 1
+
+    seen = {}
+    monkeypatch.setattr(native, "call", lambda name, *a: seen.__setitem__(name, a))
+
+    class T:                                    # stand-in for a device tensor
+        def __init__(self, addr):
+            self.addr = addr
+
+        def data_ptr(self):
+            return self.addr
+
+    store = types.SimpleNamespace(w32=T(0x1000), grad=T(0x2000), w16=T(0x3000))
+    comm = types.SimpleNamespace(rank=1, size=4, next_seq=lambda: 77)
+    eng = types.SimpleNamespace(
+        store=store, comm=comm, m=T(0x4000), v=None, dyn=None, reduced=T(0x5000),
+        params=types.SimpleNamespace(sma_alpha=0.25), nvls=False,
+        _w_ptrs="W", _grad_ptrs="G", _red_ptrs="R", _flag_ptrs="F",
+        _w_mc=ctypes.c_void_p(0x6000), _grad_mc=ctypes.c_void_p(0x7000),
+        _red_mc=ctypes.c_void_p(0x8000), _s=lambda stream=None: ctypes.c_void_p(9))
+    h = Hyper()
+    UpdateEngine._allreduce_call(eng, 0, 128, 4096, h, None, None)
+    a = seen["allreduce_update"]
+    assert len(a) == arity("allreduce_update") == 20
+    assert (a[0].value, a[1].value, a[2].value, a[3], a[4], a[5]) == (0, 1, 4, "G", "R", "F")
+    assert (a[6].value, a[7].value, a[8].value) == (128, 4096, 77)
+    assert [x.value for x in a[9:14]] == [0x1000, 0x2000, 0x4000, None, 0x3000]   # w g m v w16
+    assert a[17].value == 0.0 and a[18].value == 0 and a[19].value == 9
+    eng.nvls = True
+    UpdateEngine._allreduce_call(eng, 1, 0, 64, h, None, None)
+    b = seen["allreduce_update_nvls"]
+    assert len(b) == arity("allreduce_update_nvls") == 21
+    assert (b[0].value, b[3].value, b[4].value, b[5].value, b[6]) == (1, 0x6000, 0x8000, 0x5000, "F")
+    assert b[18].value == 0.25                                    # SMA blend factor, mode 1
