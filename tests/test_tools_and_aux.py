@@ -326,3 +326,24 @@ def test_analytic_roofline_of_the_headline_step():
     assert roofline.class_of("void kfb::gemm_tcgen05_kernel<64, 4, true>(...)") == "conv wgrad (W3)"
     assert roofline.class_of("void kfb::bn_bwd_apply_kernel(...)") == "BN bwd apply (W5)"
     assert roofline.class_of("at::native::vectorized_elementwise_kernel") is None
+
+
+def test_helper_scripts_parse_and_reference_existing_files():
+    """tools/*.sh are only ever run on a GPU box: at least make sure they parse, that every
+    repository path they mention exists and that the pytest -k expressions they use select
+    something."""
+    import glob
+    import re
+    scripts = sorted(glob.glob(os.path.join(ROOT, "tools", "*.sh")))
+    assert len(scripts) >= 6
+    test_src = "".join(open(p).read() for p in glob.glob(os.path.join(ROOT, "tests", "test_*.py")))
+    for path in scripts:
+        assert subprocess.run(["bash", "-n", path], capture_output=True).returncode == 0, path
+        text = open(path).read()
+        for rel in set(re.findall(r"\b((?:tools|tests|kf_benchmarks_b200)/[\w/]+\.(?:py|sh))\b", text)):
+            assert os.path.exists(os.path.join(ROOT, rel)), "%s mentions %s" % (path, rel)
+        for mod in set(re.findall(r"-m (kf_benchmarks_b200(?:\.\w+)+)", text)):
+            assert os.path.exists(os.path.join(ROOT, mod.replace(".", "/") + ".py")), (path, mod)
+        for expr in re.findall(r"-k (\w+)", text):
+            assert ("def test_" in test_src) and re.search(r"def test_\w*%s" % expr, test_src), \
+                "%s: -k %s selects nothing" % (path, expr)
