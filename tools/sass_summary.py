@@ -37,7 +37,8 @@ def main():
     out = ["# SASS evidence for libkfb200.so (cuobjdump -sass, sm_100a)", "",
            "Mnemonics that prove the Blackwell-native path (B200_PROFILING.md): UTCHMMA = "
            "tcgen05.mma, LDTM = tcgen05.ld, UTMALDG = TMA load (incl. .IM2COL), UTCBAR = "
-           "tcgen05.commit, SYNCS = mbarrier. In the weight-gradient variants (MODE 1 = GEMM_NT, "
+           "tcgen05.commit, SYNCS = mbarrier, UTMASTG = TMA tensor store (the opt-in KFB_TMA_STORE "
+           "epilogue of the FAST GEMM_TN / FPROP / DGRAD variants). In the weight-gradient variants (MODE 1 = GEMM_NT, "
            "MODE 4 = WGRAD) `MEMBAR.SC.SYS` is the system-scope fence that follows the epilogue's "
            "peer (NVLink) stores of the fused GEMM + reduce-scatter (--comm_impl=p2p_fused); no "
            "HMMA (legacy mma.sync) appears anywhere.", ""]
