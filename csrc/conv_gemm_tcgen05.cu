@@ -117,7 +117,9 @@ struct TileCfg {
 // MMA warp already fills accumulator `a^1` for the next tile.
 // FAST = every output piece is a full, 16-byte aligned vector (all conv layers): the scalar
 // fallbacks are compiled out, which shrinks the kernel below the instruction-cache size.
-template <int BN, int MODE, bool FAST>
+// TMA_ST = the opt-in TMA-store epilogue (KFB_TMA_STORE=1): a separate instantiation, so the
+// kernels of the default configuration carry none of its code.
+template <int BN, int MODE, bool FAST, bool TMA_ST = false>
 __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                         const __grid_constant__ CUtensorMap tmB,
@@ -354,8 +356,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     const int col_part = epi / 4;                  // which interleaved set of chunks is mine
     // TMA-store variant: dense 128-byte rows with the 128B swizzle of `tmC` (16-byte piece index
     // XOR row % 8), 4 KiB per warp, 1 KiB aligned (the staging area starts 1 KiB aligned)
-    constexpr bool kTmaStoreMode = FAST && (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD);
-    const bool tma_store = kTmaStoreMode && p.tma_store != 0;
+    constexpr bool kTmaStoreMode = TMA_ST;
+    constexpr bool tma_store = TMA_ST;
     bool store_pending = false;  // warp-uniform: a bulk store may still be reading stage_buf
     uint8_t* stage_buf = tma_store ? staging + epi * 4096 : staging + epi * (32 * kStageRowBytes);
     const int esize = p.out_fp32 ? 4 : 2;
@@ -852,6 +854,11 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
     KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE, true>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         Cfg::smem_bytes(Cfg::max_stages())));
+    if constexpr (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) {
+      KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE, true, true>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          Cfg::smem_bytes(Cfg::max_stages())));
+    }
     attr_set[dev] = true;
   }
   // every 16-byte piece of the output is full and aligned?
@@ -890,7 +897,12 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
     KFB_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, (size_t)kStatsRows * 2 * p.N * sizeof(float),
                                    stream));
   }
-  if (fast)
+  if (fast && p.tma_store) {
+    if constexpr (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) {
+      gemm_tcgen05_kernel<BN, MODE, true, true>
+          <<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(tmA, tmB, tmC, p);
+    }
+  } else if (fast)
     gemm_tcgen05_kernel<BN, MODE, true><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
         tmA, tmB, tmC, p);
   else
