@@ -68,6 +68,8 @@ class CudaExecutor:
         self.step_index = 0
         self._stream = None
         self._nvtx = os.environ.get("KFB_NVTX") == "1"
+        # tools/node_timing.py: when a list, every node appends (tag, node, start, end) events
+        self.node_events: Optional[list] = None
         # set by the benchmark driver when --comm_impl=p2p_fused: name -> kfb_push_target
         self.push_lookup: Optional[Callable[[str], object]] = None
         dev = self.device
@@ -98,7 +100,7 @@ class CudaExecutor:
         self._scratch_need = 0
         self._ws_need = 0
         self._stats_rows = int(native.load().kfb_gemm_stats_rows())
-        self.fuse_stats_min_k = int(os.environ.get("KFB_FUSE_STATS_MIN_K", "1000000000"))
+        self.fuse_stats_min_k = int(os.environ.get("KFB_FUSE_STATS_MIN_K", "0"))
         self._stats_for = None
         self.loss_rows = torch.zeros((2, n), dtype=torch.float32, device=dev)
         self.top = torch.zeros((4, n), dtype=torch.int32, device=dev)
@@ -236,11 +238,11 @@ class CudaExecutor:
             # conv -> bn adjacency: the conv epilogue can produce the BN statistics
             idx = self.graph.nodes.index(node)
             nxt = self.graph.nodes[idx + 1] if idx + 1 < len(self.graph.nodes) else None
-            # Measured on B200 (profiles/README.md): fusing the statistics doubles the epilogue's
-            # instruction count and the epilogue warps are the bottleneck of the store-bound
-            # layers, while the separate statistics pass streams at ~70% of HBM bandwidth - the
-            # fused variant was 0.4-0.7% slower end to end at every K threshold tried, so it is
-            # off by default (KFB_FUSE_STATS_MIN_K=<K> enables it for reductions >= K).
+            # Measured on B200 (profiles/README.md): with the per-lane store epilogue the fused
+            # statistics cost 0.4-0.7 % end to end (the epilogue warps were the bottleneck of the
+            # store-bound layers); with the TMA-store epilogue they gain 1.4 % on top of its
+            # 0.9 %, so they are on for every conv -> bn pair (KFB_FUSE_STATS_MIN_K=<K> restricts
+            # them to reductions >= K).
             k_reduction = a["kh"] * a["kw"] * c
             info["fuse_stats"] = bool(
                 nxt is not None and nxt.op == "bn" and nxt.inputs[0] is node.output and
@@ -380,7 +382,10 @@ class CudaExecutor:
     # ------------------------------------------------------------------ forward
     def forward(self, train: bool = True) -> None:
         s = self._s()
-        if self._nvtx:
+        if self.node_events is not None:
+            for node in self.graph.nodes:
+                self._timed_node("fwd", node, getattr(self, "_fwd_" + node.op), node, train, s)
+        elif self._nvtx:
             # KFB_NVTX=1: one NVTX range per node so that profilers attribute kernels to layers
             # (ncu --nvtx --nvtx-include "fwd/<node name>")
             for node in self.graph.nodes:
@@ -392,6 +397,14 @@ class CudaExecutor:
                 getattr(self, "_fwd_" + node.op)(node, train, s)
         # the image buffer is only read by the forward pass (backward uses saved activations)
         self._free[self._cur].record(torch.cuda.current_stream(self.device))
+
+    def _timed_node(self, tag, node, fn, *args):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        native.current_tag = tag + "/" + node.name
+        e0.record()
+        fn(*args)
+        e1.record()
+        self.node_events.append((tag, node, e0, e1))
 
     def _w16(self, name):
         return ctypes.c_void_p(self.store.view(name, "w16").data_ptr())
@@ -740,7 +753,9 @@ class CudaExecutor:
         for node in reversed(g.nodes):
             if not self.needs_grad[node.output.id]:
                 continue
-            if self._nvtx:
+            if self.node_events is not None:
+                self._timed_node("bwd", node, getattr(self, "_bwd_" + node.op), node, s)
+            elif self._nvtx:
                 torch.cuda.nvtx.range_push("bwd/" + node.name)
                 getattr(self, "_bwd_" + node.op)(node, s)
                 torch.cuda.nvtx.range_pop()

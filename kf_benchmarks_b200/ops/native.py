@@ -72,11 +72,24 @@ _LAUNCHES = {"gemm_nt": 2, "conv_wgrad": 2, "bn_forward_train": 3, "bn_forward_i
              "bn_backward": 3, "bias_act_backward": 2, "softmax_xent": 2, "dwconv_wgrad": 2, "ssd_loss": 4, "ctc_loss": 3, "gemm_nt_rs": 2, "conv_wgrad_rs": 2}
 
 
+# tools/node_timing.py: when a list, every call appends (entry point, start event, end event)
+call_events = None
+current_tag = ""
+
+
 def call(name: str, *args) -> None:
     """Call ``kfb_<name>`` and raise on a non-zero return code."""
     global launch_count
     fn = getattr(load(), "kfb_" + name)
-    rc = fn(*args)
+    if call_events is not None:
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = fn(*args)
+        e1.record()
+        call_events.append((name, current_tag, e0, e1))
+    else:
+        rc = fn(*args)
     launch_count += _LAUNCHES.get(name, 1)
     check(rc, name)
 
