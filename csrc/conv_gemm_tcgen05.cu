@@ -66,8 +66,13 @@ struct GemmParams {
   int m_tiles, n_tiles, splits;  // tile space walked by the persistent CTAs
   int wg_flat;             // WGRAD: N is the flattened (tap, channel) axis (C % 64 == 0)
   // optional fused batch-norm statistics of the (fp16-rounded) output: per-column sum and sum
-  // of squares, accumulated per epilogue warp into stats[(cta * epi_warps + warp)][2][N]
+  // of squares. Every (n-block, CTA slot, TMEM lane quarter) owns one row of [2][BN] floats:
+  // stats[((n_blk * stats_rpn + slot) * 4 + quarter)][2][BN], slot = position of the CTA among
+  // the stats_rpn = min(m_tiles, grid) CTAs that visit the n-block. The persistent tile order
+  // (m fastest) makes every CTA visit an n-block in one run, so each row is written exactly
+  // once with plain stores: no zero fill, no atomics, deterministic.
   float* stats;
+  int stats_rpn;
   // optional row scatter (strided dgrad): row (n,i,j) -> (n, h0 + i*sh, w0 + j*sw) of H x W
   int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw, sc_h0, sc_w0;
   // DGRAD: filter tap visited at (r, s) of this launch's (sub-)filter
@@ -92,7 +97,6 @@ constexpr int kTileABytes = kBlockM * kBlockK * 2;  // 16 KiB
 constexpr int kMaxStages = 8;
 constexpr int kStageRowBytes = 144;                 // 128 B payload + 16 B pad (conflict free)
 constexpr int kSmemBudget = 227 * 1024;
-constexpr int kStatsRows = 148 * 8;  // (max CTAs) x (max epilogue warps) partial rows
 
 template <int BN>
 struct TileCfg {
@@ -369,20 +373,22 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     for (int c = 0; c < kStatChunks; ++c) st_sum[c][0] = st_sum[c][1] = st_sq[c][0] = st_sq[c][1] = 0.f;
     int st_nblk = -1;
     const bool do_stats = p.stats != nullptr && !p.out_fp32;
-    float* st_row = do_stats ? p.stats + static_cast<long long>(blockIdx.x * Cfg::kEpiWarps + epi) *
-                                             2 * p.N
-                             : nullptr;
     auto flush_stats = [&](int nblk) {
-      // adds this warp's running sums of column block `nblk` into its private partial row
+      // stores this warp's sums of column block `nblk` into the row it owns (see GemmParams)
+      const int first = (nblk * p.m_tiles) % static_cast<int>(gridDim.x);
+      int slot = static_cast<int>(blockIdx.x) - first;
+      if (slot < 0) slot += gridDim.x;
+      float* st_row = p.stats +
+                      (static_cast<long long>(nblk * p.stats_rpn + slot) * 4 + quarter) * 2 * BN;
 #pragma unroll
       for (int c = 0; c < kStatChunks; ++c) {
-        const int col = nblk * BN + (col_part + c * kColSplit) * 64 + 2 * lane;
+        const int col = (col_part + c * kColSplit) * 64 + 2 * lane;  // column inside the tile
+        if (col < BN) {
+          *reinterpret_cast<float2*>(st_row + col) = make_float2(st_sum[c][0], st_sum[c][1]);
+          *reinterpret_cast<float2*>(st_row + BN + col) = make_float2(st_sq[c][0], st_sq[c][1]);
+        }
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-          if (col + e < p.N) {
-            st_row[col + e] += st_sum[c][e];
-            st_row[p.N + col + e] += st_sq[c][e];
-          }
           st_sum[c][e] = 0.f;
           st_sq[c][e] = 0.f;
         }
@@ -893,11 +899,7 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   const long long total = (long long)tiles.x * tiles.y * tiles.z;
   KFB_REQUIRE(total > 0 && total < (1ll << 31), "bad tile count %lld", total);
   const int ctas = total < sm_count() ? (int)total : sm_count();
-  if (p.stats != nullptr) {
-    // partial rows [kStatsRows][2][N]; rows of CTAs / warps that do not exist stay zero
-    KFB_CHECK_CUDA(cudaMemsetAsync(p.stats, 0, (size_t)kStatsRows * 2 * p.N * sizeof(float),
-                                   stream));
-  }
+  p.stats_rpn = (int)tiles.x < ctas ? (int)tiles.x : ctas;
   if (fast && p.tma_store) {
     if constexpr (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) {
       gemm_tcgen05_kernel<BN, MODE, true, true>
@@ -973,7 +975,19 @@ using namespace kfb;
 // ===========================================================================
 extern "C" const char* kfb_last_error(void) { return kfb::g_err; }
 
-extern "C" int kfb_gemm_stats_rows(void) { return kStatsRows; }
+// Layout of the fused statistics a GEMM with M rows, N columns and num_kb 64-wide K blocks
+// writes: `rows` partial rows of [2][bn] floats per bn-wide column block.
+extern "C" int kfb_gemm_stats_layout(int M, int N, int num_kb, int* rows, int* bn) {
+  KFB_REQUIRE(M > 0 && N > 0 && num_kb > 0 && rows != nullptr && bn != nullptr,
+              "gemm_stats_layout: bad arguments");
+  const int b = pick_bn_for(N, num_kb);
+  const long long m_tiles = (M + 127) / 128, n_tiles = (N + b - 1) / b;
+  const long long total = m_tiles * n_tiles;
+  const long long ctas = total < sm_count() ? total : sm_count();
+  *rows = (int)(m_tiles < ctas ? m_tiles : ctas) * 4;
+  *bn = b;
+  return 0;
+}
 
 extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, int K,
                            long long lda, long long ldb, long long ldc, const float* bias,
@@ -1002,8 +1016,7 @@ extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, 
   p.relu = relu;
   p.out_fp32 = out_fp32;
   p.stats = stats;
-  KFB_REQUIRE(stats == nullptr || (!out_fp32 && sm_count() <= 148),
-              "gemm_tn: fused statistics need fp16 output");
+  KFB_REQUIRE(stats == nullptr || !out_fp32, "gemm_tn: fused statistics need fp16 output");
   dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);
   return launch_mode<GEMM_TN>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
 }
@@ -1193,7 +1206,6 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   p.bias = bias;
   p.relu = relu;
   p.stats = stats;
-  KFB_REQUIRE(stats == nullptr || sm_count() <= 148, "conv_fprop: too many SMs for the stats rows");
   dim3 grid((M + 127) / 128, (d->k + bn - 1) / bn, 1);
   return launch_mode<FPROP>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
 }

@@ -1165,14 +1165,13 @@ extern "C" int kfb_bn_forward_train(const void* x, long long ldx, long long rows
                                     int stats_nblocks, const void* residual, long long ldr,
                                     int relu, void* y, long long ldy, void* stream) {
   KFB_REQ_C8(C, "bn_forward_train");
+  KFB_REQUIRE(stats_nblocks == 0,
+              "bn_forward_train: conv-epilogue statistics go through kfb_bn_forward_train_fused");
   cudaStream_t st = (cudaStream_t)stream;
-  int nb = stats_nblocks;
-  if (nb <= 0) {
-    nb = reduce_blocks(rows, C);
-    channel_reduce_kernel<0><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
-        (const __half*)x, ldx, nullptr, 0, nullptr, 0, nullptr, nullptr, nullptr, 0, rows, C,
-        scratch);
-  }
+  const int nb = reduce_blocks(rows, C);
+  channel_reduce_kernel<0><<<nb, kRedThreads, kRedThreads * 16 * sizeof(float), st>>>(
+      (const __half*)x, ldx, nullptr, 0, nullptr, 0, nullptr, nullptr, nullptr, 0, rows, C,
+      scratch);
   const float unbias = rows > 1 ? (float)((double)rows / (double)(rows - 1)) : 1.f;
   bn_finalize_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(
       scratch, nb, C, (float)(1.0 / (double)rows), unbias, eps, decay, gamma, beta, moving_mean,

@@ -36,11 +36,15 @@ typedef struct {
 int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
                 long long ldb, long long ldc, const float* bias, int relu, int out_fp32,
                 float* stats, void* stream);
-/* `stats` (optional, fp16 output only): fused batch-norm statistics of the output. The kernel
- * writes per-column partial sums / sums of squares as kfb_gemm_stats_rows() rows of [2][N]
- * floats (zero-filled first), in the format kfb_bn_forward_train consumes when
- * `stats_nblocks` > 0 - the separate statistics pass over the conv output disappears. */
-int kfb_gemm_stats_rows(void);
+/* `stats` (optional, fp16 output only): fused batch-norm statistics of the output. For every
+ * bn-wide column block the kernel writes `rows` partial rows of [2][bn] floats (per-column sum and
+ * sum of squares of the fp16-rounded output): stats[((block * rows + r) * 2 + s) * bn + j].
+ * kfb_gemm_stats_layout gives rows / bn for a shape (num_kb = 64-wide K blocks; a convolution has
+ * R*S*ceil(C/64)); every row is written exactly once with plain stores (no zero fill needed). The
+ * format is what kfb_bn_forward_train_fused consumes - the separate statistics pass over the conv
+ * output disappears (the reference gets this from cuDNN's fused batch norm,
+ * T/convnet_builder_legacy.py:418-431). */
+int kfb_gemm_stats_layout(int M, int N, int num_kb, int* rows, int* bn);
 
 /* C[M,N] (+)= A[M,K] * B[K,N]; B is consumed in place as an MN-major operand (FC dgrad). */
 int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, int K, long long lda,
@@ -95,14 +99,38 @@ int kfb_reduce_blocks(long long rows, int C);
 
 /* Training-mode batch norm fused with ReLU and residual add:
  * y = act(gamma * (x - mean) * rstd + beta (+ residual)); updates the moving statistics.
- * stats_nblocks > 0: `scratch` already holds that many rows of [2][C] partial sums (written by
- * the producing GEMM, see kfb_gemm_tn) and the statistics pass is skipped.
+ * stats_nblocks must be 0 (the conv-epilogue statistics are consumed by the single-launch form
+ * below).
  * T/convnet_builder_legacy.py:393-459 (fused_batch_norm + assign_moving_average). */
 int kfb_bn_forward_train(const void* x, long long ldx, long long rows, int C, const float* gamma,
                          const float* beta, float* moving_mean, float* moving_var, float eps,
                          float decay, int update_moving, float* mean_rstd, float* scale_shift,
                          float* scratch, int stats_nblocks, const void* residual, long long ldr,
                          int relu, void* y, long long ldy, void* stream);
+/* Single-launch forms (csrc/bn_fused.cu): one persistent kernel per direction whose phases
+ * (statistics fold / finalize / apply; reductions / coefficients / apply) are separated by
+ * grid-wide barriers instead of kernel boundaries. `sync`: two zero-initialised words owned by
+ * the caller (one pair per stream of such calls); `partial`: kfb_bn_fused_max_grid() * 2 * C
+ * floats of scratch. Forward: `stats` / `stats_rows` / `stats_bn` describe conv-epilogue
+ * statistics (kfb_gemm_stats_layout) or stats_rows = 0 to reduce x in the kernel; `bitmask`
+ * (optional, [rows][C/8] bytes) receives the packed ReLU mask of the output, which the backward
+ * accepts instead of `mask` (the forward output) - it spares two reads of the output tensor for
+ * residual blocks. T/convnet_builder_legacy.py:393-459. */
+int kfb_bn_fused_max_grid(void);
+int kfb_bn_forward_train_fused(const void* x, long long ldx, long long rows, int C,
+                               const float* gamma, const float* beta, float* moving_mean,
+                               float* moving_var, float eps, float decay, int update_moving,
+                               float* mean_rstd, float* scale_shift, const float* stats,
+                               int stats_rows, int stats_bn, float* partial, const void* residual,
+                               long long ldr, int relu, void* y, long long ldy,
+                               unsigned char* bitmask, unsigned* sync, void* stream);
+int kfb_bn_backward_fused(const void* dy, long long lddy, const void* mask, long long ldm,
+                          const unsigned char* bitmask, const float* relu_affine, const void* x,
+                          long long ldx, long long rows, int C, const float* gamma,
+                          const float* mean_rstd, float* dgamma, float* dbeta,
+                          int accumulate_param_grads, float grad_scale, float* coef,
+                          float* partial, void* dz, long long lddz, void* dres, long long lddr,
+                          int dres_accumulate, unsigned* sync, void* stream);
 int kfb_bn_forward_inference(const void* x, long long ldx, long long rows, int C,
                              const float* gamma, const float* beta, const float* moving_mean,
                              const float* moving_var, float eps, float* scale_shift,

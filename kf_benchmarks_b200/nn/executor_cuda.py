@@ -99,7 +99,11 @@ class CudaExecutor:
         # reductions / split-K scratch (sized below), loss outputs
         self._scratch_need = 0
         self._ws_need = 0
-        self._stats_rows = int(native.load().kfb_gemm_stats_rows())
+        # single-launch batch norm (csrc/bn_fused.cu); KFB_BN_FUSED=0 selects the three-kernel
+        # forms of nn_kernels.cu (then the conv epilogue does not produce the statistics either)
+        self.bn_fused = os.environ.get("KFB_BN_FUSED", "1") != "0"
+        self._bn_max_grid = int(native.load().kfb_bn_fused_max_grid())
+        self._stats_need = 0
         self.fuse_stats_min_k = int(os.environ.get("KFB_FUSE_STATS_MIN_K", "0"))
         self._stats_for = None
         self.loss_rows = torch.zeros((2, n), dtype=torch.float32, device=dev)
@@ -111,6 +115,9 @@ class CudaExecutor:
             self._prepare(node)
         self.scratch = torch.zeros((max(self._scratch_need, 1024),), dtype=torch.float32,
                                    device=dev)
+        self.stats_buf = torch.zeros((max(self._stats_need, 1024),), dtype=torch.float32,
+                                     device=dev)
+        self.bn_sync = torch.zeros((2,), dtype=torch.int32, device=dev)
         self.workspace = torch.zeros((max(self._ws_need // 4, 1024),), dtype=torch.float32,
                                      device=dev)
         self._plan_grad_writes()
@@ -245,11 +252,17 @@ class CudaExecutor:
             # them to reductions >= K).
             k_reduction = a["kh"] * a["kw"] * c
             info["fuse_stats"] = bool(
+                self.bn_fused and
                 nxt is not None and nxt.op == "bn" and nxt.inputs[0] is node.output and
                 len(node.output.consumers) == 1 and not a["has_bias"] and
                 a["activation"] == "linear" and k_reduction >= self.fuse_stats_min_k)
             if info["fuse_stats"]:
-                self._scratch_need = max(self._scratch_need, self._stats_rows * 2 * k)
+                from ..ops import gemm_conv
+                num_kb = ((info["kpad"] + 63) // 64) if info["flat"] else \
+                    a["kh"] * a["kw"] * ((c + 63) // 64)
+                rows_, bn_ = gemm_conv.stats_layout(node.output.rows, k, num_kb)
+                info["stats_layout"] = (rows_, bn_)
+                self._stats_need = max(self._stats_need, ((k + bn_ - 1) // bn_) * rows_ * 2 * bn_)
         elif node.op == "dwconv":
             x = node.inputs[0]
             n, h, w, c = x.shape
@@ -270,6 +283,12 @@ class CudaExecutor:
             info["scale_shift"] = torch.zeros((2 * c,), dtype=torch.float32, device=dev)
             info["coef"] = torch.zeros((3 * c,), dtype=torch.float32, device=dev)
             self._need_scratch(node.output.rows, c)
+            self._scratch_need = max(self._scratch_need, self._bn_max_grid * 2 * c)
+            if self.bn_fused and a["relu"] and len(node.inputs) > 1:
+                # packed ReLU mask of the block output: the backward reads one bit per element
+                # instead of the fp16 output (twice)
+                info["bitmask"] = torch.zeros((node.output.rows * (c // 8),), dtype=torch.uint8,
+                                              device=dev)
         elif node.op == "affine":
             spec = node.params["weights"]
             out, in_pad = spec.shape
@@ -424,7 +443,7 @@ class CudaExecutor:
         d = info["desc"]
         kname = node.params["kernel"].name
         # the batch-norm that immediately follows gets its statistics from the conv epilogue
-        stats = ptr(self.scratch) if (train and info.get("fuse_stats")) else None
+        stats = ptr(self.stats_buf) if (train and info.get("fuse_stats")) else None
         if info["flat"]:
             col = info["col"]
             native.call("im2col_small_c", x.p, ptr(col), i32(d.n), i32(d.h), i32(d.w), i32(d.c),
@@ -436,7 +455,7 @@ class CudaExecutor:
         else:
             native.call("conv_fprop", ctypes.byref(d), x.p, self._w16(kname), y.p, i64(y.ld),
                         bias, relu, stats, s)
-        self._stats_for = node.output.id if stats is not None else None
+        self._stats_for = (node.output.id,) + info["stats_layout"] if stats is not None else None
 
     def _fwd_bn(self, node, train, s):
         info = self._per_node[id(node)]
@@ -448,14 +467,22 @@ class CudaExecutor:
         mm = ptr(self.store.view(node.params["moving_mean"].name))
         mv = ptr(self.store.view(node.params["moving_variance"].name))
         c = y.cols
-        if train:
-            fused = self._stats_for == node.inputs[0].id
-            self._stats_for = None
+        if train and self.bn_fused:
+            sf, self._stats_for = self._stats_for, None
+            fused = sf is not None and sf[0] == node.inputs[0].id
+            native.call("bn_forward_train_fused", x.p, i64(x.ld), i64(x.rows), i32(c), gamma, beta,
+                        mm, mv, f32(a["epsilon"]), f32(a["decay"]), i32(1),
+                        ptr(info["mean_rstd"]), ptr(info["scale_shift"]),
+                        ptr(self.stats_buf) if fused else None, i32(sf[1] if fused else 0),
+                        i32(sf[2] if fused else 0), ptr(self.scratch), res.p if res else None,
+                        i64(res.ld if res else 0), i32(int(a["relu"])), y.p, i64(y.ld),
+                        ptr(info.get("bitmask")), ptr(self.bn_sync), s)
+        elif train:
             native.call("bn_forward_train", x.p, i64(x.ld), i64(x.rows), i32(c), gamma, beta, mm,
                         mv, f32(a["epsilon"]), f32(a["decay"]), i32(1), ptr(info["mean_rstd"]),
-                        ptr(info["scale_shift"]), ptr(self.scratch),
-                        i32(self._stats_rows if fused else 0), res.p if res else None,
-                        i64(res.ld if res else 0), i32(int(a["relu"])), y.p, i64(y.ld), s)
+                        ptr(info["scale_shift"]), ptr(self.scratch), i32(0),
+                        res.p if res else None, i64(res.ld if res else 0), i32(int(a["relu"])),
+                        y.p, i64(y.ld), s)
         else:
             native.call("bn_forward_inference", x.p, i64(x.ld), i64(x.rows), i32(c), gamma, beta,
                         mm, mv, f32(a["epsilon"]), ptr(info["scale_shift"]),
@@ -844,11 +871,20 @@ class CudaExecutor:
         # the stored output is the only source of the mask
         mask = y.p if (a["relu"] and has_res) else None
         affine = ptr(info["scale_shift"]) if (a["relu"] and not has_res) else None
-        native.call("bn_backward", gy.p, i64(gy.ld), mask, i64(y.ld), affine, z.p,
-                    i64(z.ld), i64(z.rows), i32(z.cols), gamma, ptr(info["mean_rstd"]), dgamma,
-                    dbeta, i32(0), f32(1.0), ptr(info["coef"]), ptr(self.scratch), gz.p,
-                    i64(gz.ld), gres.p if gres else None, i64(gres.ld if gres else 0),
-                    i32(res_acc), s)
+        if self.bn_fused:
+            bits = info.get("bitmask")
+            native.call("bn_backward_fused", gy.p, i64(gy.ld), None if bits is not None else mask,
+                        i64(y.ld), ptr(bits), affine, z.p, i64(z.ld), i64(z.rows), i32(z.cols),
+                        gamma, ptr(info["mean_rstd"]), dgamma, dbeta, i32(0), f32(1.0),
+                        ptr(info["coef"]), ptr(self.scratch), gz.p, i64(gz.ld),
+                        gres.p if gres else None, i64(gres.ld if gres else 0), i32(res_acc),
+                        ptr(self.bn_sync), s)
+        else:
+            native.call("bn_backward", gy.p, i64(gy.ld), mask, i64(y.ld), affine, z.p,
+                        i64(z.ld), i64(z.rows), i32(z.cols), gamma, ptr(info["mean_rstd"]),
+                        dgamma, dbeta, i32(0), f32(1.0), ptr(info["coef"]), ptr(self.scratch),
+                        gz.p, i64(gz.ld), gres.p if gres else None,
+                        i64(gres.ld if gres else 0), i32(res_acc), s)
         if need_dz and self._acc(node, 0):
             gdst = self._grad(zin)
             native.call("copy2d", gz.p, i64(gz.ld), gdst.p, i64(gdst.ld), i64(gz.rows),

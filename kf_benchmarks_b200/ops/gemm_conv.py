@@ -125,8 +125,30 @@ def get_workspace(device, nbytes: int) -> torch.Tensor:
     return ws
 
 
-def stats_rows() -> int:
-    return int(native.load().kfb_gemm_stats_rows())
+def stats_layout(m: int, n: int, num_kb: int):
+    """(rows, bn) of the fused BN statistics a GEMM of that shape writes: for every bn-wide
+    column block, `rows` partial rows of [2][bn] floats (sum, sum of squares)."""
+    rows, bn = ctypes.c_int(0), ctypes.c_int(0)
+    native.check(native.load().kfb_gemm_stats_layout(i32(m), i32(n), i32(num_kb),
+                                                     ctypes.byref(rows), ctypes.byref(bn)),
+                 "gemm_stats_layout")
+    return rows.value, bn.value
+
+
+def conv_stats_layout(d: ConvDesc):
+    return stats_layout(d.n * d.p * d.q, d.k, d.r * d.s * ((d.c + 63) // 64))
+
+
+def stats_buffer(m: int, n: int, num_kb: int, device) -> torch.Tensor:
+    """Buffer for the fused statistics, shaped [column blocks][rows][2][bn]."""
+    rows, bn = stats_layout(m, n, num_kb)
+    return torch.empty(((n + bn - 1) // bn, rows, 2, bn), device=device, dtype=torch.float32)
+
+
+def fold_stats(stats: torch.Tensor, n: int) -> torch.Tensor:
+    """[2][n] totals of a statistics buffer (what the fused BN forward kernel folds)."""
+    t = stats.sum(1)                                   # [blocks][2][bn]
+    return t.permute(1, 0, 2).reshape(2, -1)[:, :n]
 
 
 def conv_fprop(x, w, d: ConvDesc, bias=None, relu=False, out=None, ldy=None, stats=None):

@@ -22,11 +22,21 @@ def _scratch(rows, c):
     return torch.zeros(nb * 2 * c, device="cuda")
 
 
+@pytest.mark.parametrize("form", ["three_kernels", "single_launch", "single_launch_bitmask"])
 @pytest.mark.parametrize("rows,c,relu,res,scale", [(4 * 7 * 7, 64, True, False, True),
                                                    (3 * 14 * 14, 256, True, True, True),
                                                    (1000, 2048, False, False, False),
-                                                   (777, 24, True, True, True)])
-def test_bn_forward_backward(rows, c, relu, res, scale):
+                                                   (777, 24, True, True, True),
+                                                   (64 * 28 * 28, 128, True, True, True),
+                                                   (37, 4096, True, False, True)])
+def test_bn_forward_backward(rows, c, relu, res, scale, form):
+    """Both forms of the training batch norm (nn_kernels.cu: reduce / finalize / apply kernels;
+    bn_fused.cu: one persistent kernel per direction with grid barriers, optionally with the
+    packed ReLU mask) against the fp32 autograd restatement."""
+    fused = form != "three_kernels"
+    use_bits = form == "single_launch_bitmask" and relu
+    if form == "single_launch_bitmask" and not relu:
+        pytest.skip("no ReLU, no mask")
     g = torch.Generator(device="cuda").manual_seed(0)
     x = (torch.randn(rows, c, device="cuda", generator=g) * 2 + 0.5).half()
     r = torch.randn(rows, c, device="cuda", generator=g).half() if res else None
@@ -38,9 +48,18 @@ def test_bn_forward_backward(rows, c, relu, res, scale):
     y = torch.empty_like(x)
     eps, decay = 1e-5, 0.9
     scratch = _scratch(rows, c)
-    native.call("bn_forward_train", ptr(x), i64(c), i64(rows), i32(c), ptr(gamma), ptr(beta),
-                ptr(mm), ptr(mv), f32(eps), f32(decay), i32(1), ptr(mean_rstd), ptr(ss),
-                ptr(scratch), i32(0), ptr(r), i64(c), i32(int(relu)), ptr(y), i64(c), _s())
+    sync = torch.zeros(2, dtype=torch.int32, device="cuda")
+    bits = torch.zeros(rows * (c // 8), dtype=torch.uint8, device="cuda") if use_bits else None
+    if fused:
+        scratch = torch.zeros(int(native.load().kfb_bn_fused_max_grid()) * 2 * c, device="cuda")
+        native.call("bn_forward_train_fused", ptr(x), i64(c), i64(rows), i32(c), ptr(gamma),
+                    ptr(beta), ptr(mm), ptr(mv), f32(eps), f32(decay), i32(1), ptr(mean_rstd),
+                    ptr(ss), None, i32(0), i32(0), ptr(scratch), ptr(r), i64(c), i32(int(relu)),
+                    ptr(y), i64(c), ptr(bits), ptr(sync), _s())
+    else:
+        native.call("bn_forward_train", ptr(x), i64(c), i64(rows), i32(c), ptr(gamma), ptr(beta),
+                    ptr(mm), ptr(mv), f32(eps), f32(decay), i32(1), ptr(mean_rstd), ptr(ss),
+                    ptr(scratch), i32(0), ptr(r), i64(c), i32(int(relu)), ptr(y), i64(c), _s())
     # oracle
     xf = x.float().requires_grad_(True)
     gf = gamma.clone().requires_grad_(True) if scale else None
@@ -64,12 +83,21 @@ def test_bn_forward_backward(rows, c, relu, res, scale):
     dgamma = torch.zeros(c, device="cuda") if scale else None
     dbeta = torch.zeros(c, device="cuda")
     use_affine = relu and not res       # mask recomputed from x through the forward affine
-    native.call("bn_backward", ptr(dy), i64(c), ptr(y) if (relu and res) else None, i64(c),
-                ptr(ss) if use_affine else None, ptr(x), i64(c),
-                i64(rows), i32(c), ptr(gamma), ptr(mean_rstd), ptr(dgamma), ptr(dbeta), i32(0),
-                f32(1.0), ptr(coef), ptr(scratch), ptr(dz), i64(c), ptr(dres), i64(c), i32(0),
-                _s())
+    if fused:
+        mask = None if use_bits else (ptr(y) if (relu and res) else None)
+        native.call("bn_backward_fused", ptr(dy), i64(c), mask, i64(c), ptr(bits),
+                    ptr(ss) if (use_affine and not use_bits) else None, ptr(x), i64(c), i64(rows),
+                    i32(c), ptr(gamma), ptr(mean_rstd), ptr(dgamma), ptr(dbeta), i32(0), f32(1.0),
+                    ptr(coef), ptr(scratch), ptr(dz), i64(c), ptr(dres), i64(c), i32(0),
+                    ptr(sync), _s())
+    else:
+        native.call("bn_backward", ptr(dy), i64(c), ptr(y) if (relu and res) else None, i64(c),
+                    ptr(ss) if use_affine else None, ptr(x), i64(c),
+                    i64(rows), i32(c), ptr(gamma), ptr(mean_rstd), ptr(dgamma), ptr(dbeta), i32(0),
+                    f32(1.0), ptr(coef), ptr(scratch), ptr(dz), i64(c), ptr(dres), i64(c), i32(0),
+                    _s())
     torch.cuda.synchronize()
+    assert int(sync[0]) == 0      # the grid barrier leaves its arrival count at zero
     # the ReLU mask comes from the fp16 output; elements within rounding of zero may differ
     tol = dict(atol=3e-2, rtol=3e-2)
     assert torch.allclose(dbeta, bf.grad, atol=0.15, rtol=2e-2)

@@ -4,7 +4,8 @@
 #   KFB_REDUCE_BLOCKS_PER_SM grid cap of the channel reductions    (default 4)
 #   KFB_GEMM_MAX_BN          widest GEMM tile (64 | 128 | 256)     (default 256)
 #   KFB_SPLIT_ROUNDS         persistent-grid rounds split-K aims at (default 2)
-#   KFB_TMA_STORE            TMA-store GEMM epilogue               (default 0)
+#   KFB_TMA_STORE            TMA-store GEMM epilogue               (default 1)
+#   KFB_FUSE_STATS_MIN_K     smallest reduction whose conv epilogue produces the BN statistics (default 0)
 # Prints images/sec of the headline step per point; everything lands in gpurun_out/sweep_*.json.
 set -u
 cd "$(dirname "$0")/.."
@@ -30,6 +31,7 @@ for v in 4 8 32; do run apply_ctas_$v KFB_APPLY_CTAS_PER_SM=$v; done
 for v in 2 6 8; do run reduce_blocks_$v KFB_REDUCE_BLOCKS_PER_SM=$v; done
 run gemm_max_bn_128 KFB_GEMM_MAX_BN=128
 for v in 1 3 4; do run split_rounds_$v KFB_SPLIT_ROUNDS=$v; done
-run tma_store KFB_TMA_STORE=1
-run tma_store_bn128 KFB_TMA_STORE=1 KFB_GEMM_MAX_BN=128
+run per_lane_store KFB_TMA_STORE=0
+run no_fused_stats KFB_FUSE_STATS_MIN_K=1000000000
+run fused_stats_k512 KFB_FUSE_STATS_MIN_K=512
 run default_again KFB_DUMMY=0
