@@ -146,7 +146,13 @@ struct BnFwdArgs {
   const float* stats; int stats_rows, stats_bn;
   float* partial;
   unsigned* sync;
+  unsigned long long* dbg;   // optional: globaltimer stamps of CTA 0 at the phase boundaries
 };
+
+#define KFB_BN_STAMP(i)                                                     \
+  do {                                                                      \
+    if (p.dbg != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.dbg[i] = globaltimer_ns(); \
+  } while (0)
 
 __global__ void __launch_bounds__(kBnThreads)
     bn_fwd_fused_kernel(const BnFwdArgs p) {
@@ -323,6 +329,7 @@ struct BnBwdArgs {
   __half* dz; long long lddz;
   __half* dres; long long lddr; int dres_accumulate;
   unsigned* sync;
+  unsigned long long* dbg;
 };
 
 // g = dy masked by the ReLU of the forward output; MASK: 0 none, 1 from y, 2 from x, 3 bitmask
@@ -345,14 +352,15 @@ __device__ __forceinline__ void masked_grad(const Half8& gq, const Half8& mq, un
   }
 }
 
-template <int MASK>
-__global__ void __launch_bounds__(kBnThreads)
+template <int MASK, int KU, int MINB>
+__global__ void __launch_bounds__(kBnThreads, MINB)
     bn_bwd_fused_kernel(const BnBwdArgs p) {
   extern __shared__ float red[];
   const SlabMap m = make_slab_map(p.rows, p.C);
   const int C = p.C;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  constexpr int kU = 4;
+  constexpr int kU = KU;
+  KFB_BN_STAMP(0);
 
   // ---- phase 1: a = sum g, b = sum g * (x - mean) * rstd over this CTA's slab ----
   for (int cv0 = 0; cv0 < m.vpr; cv0 += m.cv_per_pass) {
@@ -418,17 +426,35 @@ __global__ void __launch_bounds__(kBnThreads)
       }
     }
   }
+  KFB_BN_STAMP(1);
   grid_barrier(p.sync, gridDim.x);
+  KFB_BN_STAMP(2);
 
   // ---- phase 2: one warp per channel: dbeta / dgamma and the coefficients of
   //      dz = A*g + B*x + D with A = gamma*rstd, B = -A*rstd*dgamma/M,
   //      D = A*(rstd*mean*dgamma/M - dbeta/M) ----
   for (int c = blockIdx.x * kBnWarps + warp; c < C; c += gridDim.x * kBnWarps) {
     float db = 0.f, dg = 0.f;
-    for (int b = lane; b < static_cast<int>(gridDim.x); b += 32) {
-      const float* q = p.partial + static_cast<long long>(b) * 2 * C + c;
-      db += __ldcg(q);
-      dg += __ldcg(q + C);
+    {
+      // all loads of a lane are issued before the first add (one L2 round trip, fixed order)
+      constexpr int kF = 8;
+      const int nb = static_cast<int>(gridDim.x);
+      for (int b0 = lane; b0 < nb; b0 += 32 * kF) {
+        float va[kF], vb[kF];
+#pragma unroll
+        for (int u = 0; u < kF; ++u) {
+          const int b = b0 + 32 * u;
+          const float* q = p.partial + static_cast<long long>(b < nb ? b : lane) * 2 * C + c;
+          va[u] = __ldcg(q);
+          vb[u] = __ldcg(q + C);
+          if (b >= nb) va[u] = vb[u] = 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < kF; ++u) {
+          db += va[u];
+          dg += vb[u];
+        }
+      }
     }
     db = warp_sum_det(db);
     dg = warp_sum_det(dg);
@@ -444,7 +470,9 @@ __global__ void __launch_bounds__(kBnThreads)
     }
   }
   if (p.dz == nullptr) return;  // only the parameter gradients were wanted
+  KFB_BN_STAMP(3);
   grid_barrier(p.sync, gridDim.x);
+  KFB_BN_STAMP(4);
 
   // ---- phase 3: dz = A*g + B*x + D (and d_res (+)= g); the slab is walked last-to-first so
   //      its tail, read last in phase 1, is served from L2 ----
@@ -515,6 +543,7 @@ __global__ void __launch_bounds__(kBnThreads)
       }
     }
   }
+  KFB_BN_STAMP(5);
 }
 
 // ---------------------------------------------------------------------------
@@ -536,7 +565,7 @@ static int resident_grid(K kernel, long long rows) {
   static int cap = -1;
   if (cap < 0) {
     const char* e = getenv("KFB_BN_CTAS_PER_SM");
-    cap = (e != nullptr && atoi(e) > 0) ? atoi(e) : 3;
+    cap = (e != nullptr && atoi(e) > 0) ? atoi(e) : 8;
   }
   if (per_sm > cap) per_sm = cap;
   long long g = static_cast<long long>(sms) * per_sm;
@@ -545,9 +574,18 @@ static int resident_grid(K kernel, long long rows) {
   return g < 1 ? 1 : static_cast<int>(g);
 }
 
+static unsigned long long* g_bn_dbg = nullptr;
+
 }  // namespace kfb
 
 using namespace kfb;
+
+// debugging aid (tools/bn_microbench.py --phases): six device words that receive the
+// globaltimer of CTA 0 at the phase boundaries of the next backward kernels; null disables
+extern "C" int kfb_bn_fused_debug_stamps(unsigned long long* dev_words) {
+  g_bn_dbg = dev_words;
+  return 0;
+}
 
 extern "C" int kfb_bn_fused_max_grid(void) {
   int dev = 0, sms = 0;
@@ -584,6 +622,7 @@ extern "C" int kfb_bn_forward_train_fused(
   a.stats = stats; a.stats_rows = stats_rows; a.stats_bn = stats_bn;
   a.partial = partial;
   a.sync = sync;
+  a.dbg = nullptr;
   KFB_REQUIRE(stats_rows > 0 || partial != nullptr,
               "bn_forward_train_fused: needs scratch for its own statistics pass");
   bn_fwd_fused_kernel<<<grid, kBnThreads, kBnSmemBytes, (cudaStream_t)stream>>>(a);
@@ -617,25 +656,21 @@ extern "C" int kfb_bn_backward_fused(
   a.dz = (__half*)dz; a.lddz = lddz;
   a.dres = (__half*)dres; a.lddr = lddr; a.dres_accumulate = dres_accumulate;
   a.sync = sync;
+  a.dbg = g_bn_dbg;
   cudaStream_t st = (cudaStream_t)stream;
   int grid = 0;
+  // 4 rows x 16 bytes per tensor in flight per thread at 2 CTAs per SM measured best (tools/
+  // bn_microbench.py: 1, 2, 6 and 8 rows and 1 / 3 / 4 / 6 CTAs per SM were all slower)
+#define KFB_BN_LAUNCH_V(MASK)                                                                  \
+  do {                                                                                         \
+    grid = resident_grid(bn_bwd_fused_kernel<MASK, 4, 2>, rows);                               \
+    if (grid > 0) bn_bwd_fused_kernel<MASK, 4, 2><<<grid, kBnThreads, kBnSmemBytes, st>>>(a);  \
+  } while (0)
   switch (mode) {
-    case 0:
-      grid = resident_grid(bn_bwd_fused_kernel<0>, rows);
-      if (grid > 0) bn_bwd_fused_kernel<0><<<grid, kBnThreads, kBnSmemBytes, st>>>(a);
-      break;
-    case 1:
-      grid = resident_grid(bn_bwd_fused_kernel<1>, rows);
-      if (grid > 0) bn_bwd_fused_kernel<1><<<grid, kBnThreads, kBnSmemBytes, st>>>(a);
-      break;
-    case 2:
-      grid = resident_grid(bn_bwd_fused_kernel<2>, rows);
-      if (grid > 0) bn_bwd_fused_kernel<2><<<grid, kBnThreads, kBnSmemBytes, st>>>(a);
-      break;
-    default:
-      grid = resident_grid(bn_bwd_fused_kernel<3>, rows);
-      if (grid > 0) bn_bwd_fused_kernel<3><<<grid, kBnThreads, kBnSmemBytes, st>>>(a);
-      break;
+    case 0: KFB_BN_LAUNCH_V(0); break;
+    case 1: KFB_BN_LAUNCH_V(1); break;
+    case 2: KFB_BN_LAUNCH_V(2); break;
+    default: KFB_BN_LAUNCH_V(3); break;
   }
   KFB_REQUIRE(grid > 0, "bn_backward_fused: occupancy query failed");
   KFB_CHECK_CUDA(cudaGetLastError());

@@ -930,8 +930,9 @@ static int launch_mode(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, c
 // Tile width: the widest tile that covers N (wider tiles amortise the A-operand smem reads);
 // short-K, wide-N problems keep 128-wide tiles so more tiles exist to balance across SMs.
 // Policy knobs for on-device sweeps without a rebuild (read once; defaults = measured setup):
-// KFB_GEMM_MAX_BN (64 | 128 | 256, default 256) caps the tile width, KFB_SPLIT_ROUNDS (default 2)
-// is the number of persistent-grid rounds the split-K count aims for.
+// KFB_GEMM_MAX_BN (64 | 128 | 256, default 256) caps the tile width, KFB_SPLIT_ROUNDS (default 1;
+// 2-4 measured 1-4 % slower on the headline step) is the number of persistent-grid rounds the
+// split-K count aims for.
 static int env_knob(const char* name, int dflt, int lo, int hi) {
   const char* e = getenv(name);
   if (e == nullptr || *e == 0) return dflt;
@@ -943,7 +944,7 @@ static int max_bn() {
   return v >= 256 ? 256 : (v >= 128 ? 128 : 64);
 }
 static int split_rounds() {
-  static const int v = env_knob("KFB_SPLIT_ROUNDS", 2, 1, 8);
+  static const int v = env_knob("KFB_SPLIT_ROUNDS", 1, 1, 8);
   return v;
 }
 static int pick_bn(int n) {

@@ -103,6 +103,12 @@ class CudaExecutor:
         # forms of nn_kernels.cu (then the conv epilogue does not produce the statistics either)
         self.bn_fused = os.environ.get("KFB_BN_FUSED", "1") != "0"
         self._bn_max_grid = int(native.load().kfb_bn_fused_max_grid())
+        # backward of layers smaller than this (bytes of one activation) and without a packed
+        # mask use the three-kernel form: below ~60 MB the single launch loses to it (its two
+        # CTAs per SM ramp up more slowly than the 4-8 of the separate kernels; measured on
+        # the headline step: 0 -> 11 051, 30 MB -> 11 163, 60 MB -> 11 197, 120 MB -> 11 194 img/s)
+        self.bn_fused_bwd_min_bytes = int(os.environ.get("KFB_BN_FUSED_BWD_MIN_BYTES",
+                                                         "60000000"))
         self._stats_need = 0
         self.fuse_stats_min_k = int(os.environ.get("KFB_FUSE_STATS_MIN_K", "0"))
         self._stats_for = None
@@ -871,8 +877,9 @@ class CudaExecutor:
         # the stored output is the only source of the mask
         mask = y.p if (a["relu"] and has_res) else None
         affine = ptr(info["scale_shift"]) if (a["relu"] and not has_res) else None
-        if self.bn_fused:
-            bits = info.get("bitmask")
+        bits = info.get("bitmask")
+        if self.bn_fused and (bits is not None or
+                              z.rows * z.cols * 2 >= self.bn_fused_bwd_min_bytes):
             native.call("bn_backward_fused", gy.p, i64(gy.ld), None if bits is not None else mask,
                         i64(y.ld), ptr(bits), affine, z.p, i64(z.ld), i64(z.rows), i32(z.cols),
                         gamma, ptr(info["mean_rstd"]), dgamma, dbeta, i32(0), f32(1.0),
