@@ -490,8 +490,8 @@ class BenchmarkCNN:
         and replayed, with device-resident inputs. Several ranks can do so when the gradient
         exchange is the overlapped P2P all-reduce: the kernels then take part of their per-call
         sequence number from a device counter that the captured step advances
-        (P2PComm.enable_device_seq). That path has not run on hardware yet and is switched on
-        with KFB_MULTI_RANK_GRAPH=1."""
+        (P2PComm.enable_device_seq; checked on hardware against the eager step,
+        tests/test_gpu_multi.py). KFB_MULTI_RANK_GRAPH=0 switches the multi-rank form off."""
         if not (self.params.cuda_graph and self.device.type == "cuda" and
                 not getattr(self.input_source, "host_resident", False) and
                 not self.engine.auto_loss_scale):
@@ -500,7 +500,7 @@ class BenchmarkCNN:
             return True
         from .parallel.comm import P2PComm
         eng = self.engine
-        return (os.environ.get("KFB_MULTI_RANK_GRAPH") == "1" and isinstance(self.comm, P2PComm)
+        return (os.environ.get("KFB_MULTI_RANK_GRAPH", "1") != "0" and isinstance(self.comm, P2PComm)
                 and eng._can_overlap() and not eng.fused_push)
 
     def _step_graphed(self) -> None:

@@ -102,9 +102,6 @@ def test_fused_wgrad_reduce_scatter_is_bit_identical_to_the_pull_path(tmp_path, 
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
-@pytest.mark.skipif(os.environ.get("KFB_TEST_NVLS") != "1",
-                    reason="--comm_impl=nvls was written without GPU time left in the round; set "
-                           "KFB_TEST_NVLS=1 to run it (tools/nvls_check.py does the same by hand)")
 @pytest.mark.parametrize("mode", [["--variable_update=replicated", "--num_gpus=2"],
                                   ["--variable_update=kungfu", "--kungfu_option=sma"]])
 def test_nvls_all_reduce_matches_the_pull_kernels(tmp_path, mode):
@@ -137,9 +134,6 @@ def test_nvls_all_reduce_matches_the_pull_kernels(tmp_path, mode):
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
-@pytest.mark.skipif(os.environ.get("KFB_MULTI_RANK_GRAPH") != "1",
-                    reason="multi-rank CUDA graphs were written without GPU time left in the "
-                           "round; set KFB_MULTI_RANK_GRAPH=1 to run (and to enable) them")
 def test_multi_rank_cuda_graph_matches_the_eager_step(tmp_path):
     """--cuda_graph on 2 ranks (device-resident sequence offset for the P2P flag protocol):
     same trained variables as the eager step, replicas bit-identical."""
