@@ -189,7 +189,8 @@ __global__ void __launch_bounds__(256)
   if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
 }
 
-// state = {loss_scale, normal_steps}; dyn[1] (grad_scale) is refreshed to base_grad_scale/scale.
+// state = {loss_scale, normal_steps, skipped steps so far, -}; dyn[1] (grad_scale) is refreshed
+// to base_grad_scale/scale and the flag is cleared for the next step.
 // Skip flag set: halve, reset counter. Else count up to inc_every clean steps, then double
 // (same transitions as T/variable_mgr_util.py:51-88).
 __global__ void loss_scale_update_kernel(float* state, int* flag, int inc_every, float* dyn,
@@ -200,6 +201,8 @@ __global__ void loss_scale_update_kernel(float* state, int* flag, int inc_every,
   if (*flag != 0) {
     scale *= 0.5f;
     steps = 0.f;
+    state[2] += 1.f;
+    *flag = 0;
   } else if (steps < static_cast<float>(inc_every)) {
     steps += 1.f;
   } else {
@@ -209,6 +212,19 @@ __global__ void loss_scale_update_kernel(float* state, int* flag, int inc_every,
   state[0] = scale;
   state[1] = steps;
   if (dyn != nullptr) dyn[1] = base_grad_scale / scale;
+}
+
+// dyn = {lr, grad_scale, adam_t, -}: the entries selected by `mask` (bit i = entry i) are set
+// from the arguments. Written by a kernel so that neither a pinned staging buffer (which a host
+// running ahead of the device could overwrite before its copy executes) nor a synchronisation
+// is needed, and so that a device-maintained entry (grad_scale under automatic loss scaling)
+// can be left alone.
+__global__ void set_hyper_dyn_kernel(float* dyn, float lr, float grad_scale, float adam_t,
+                                     int mask) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (mask & 1) dyn[0] = lr;
+  if (mask & 2) dyn[1] = grad_scale;
+  if (mask & 4) dyn[2] = adam_t;
 }
 
 // ---------------------------------------------------------------------------
@@ -508,6 +524,321 @@ __global__ void __launch_bounds__(512)
   }
 }
 
+// ---------------------------------------------------------------------------
+// Second generation of the fused all-reduce + update (kfb_allreduce_update2). Same two-shot
+// protocol and flags as above; what changed, and why (profiles/README.md, all_reduce_benchmark):
+//   * phase 2 (the optimizer over the whole bucket) keeps 4 x 16 bytes per array in flight per
+//     thread - with one vector per thread the few CTAs this kernel is allowed (the backward pass
+//     wants the SMs) reached ~2.3 TB/s and phase 2 was half of the kernel's time;
+//   * phase 1 keeps 4 vectors per peer in flight;
+//   * HALF = compact gradient transfer (--compact_gradient_transfer, T/batch_allreduce.py:429-453,
+//     T/variable_mgr.py:311-313): the sources are fp16 copies of the gradients and the reduced
+//     shard travels as fp16; the sum itself is taken in fp32 (by the owner, or inside the switch
+//     with .acc::f32), which the reference's fp16 NCCL all-reduce does not do;
+//   * NVLS = reduction and broadcast done by the NVSwitch on multicast addresses.
+// Requires offset and count to be multiples of 8 elements (arena slots are 128-aligned).
+// ---------------------------------------------------------------------------
+struct Ar2Args {
+  const void* src[kMaxRanks];  // pull: per-rank source arena (fp32 or fp16), element 0
+  void* red[kMaxRanks];        // pull: per-rank landing buffer, element 0
+  const void* src_mc;          // NVLS: multicast alias of the source arena
+  void* red_mc;                // NVLS: multicast alias of the landing buffer
+  const void* red_local;       // this rank's landing buffer
+  long long offset, count;
+  uint32_t seq;
+  float* w;
+  const float* g_local;
+  float* m;
+  float* v;
+  __half* w16;
+  const float* dyn;
+  const int* skip_flag;
+  float sma_alpha;
+  int reduce_only;
+};
+
+template <bool HALF>
+__device__ __forceinline__ void vec_unpack(const uint4& q, float* f) {
+  if (HALF) {
+    const __half2* h = reinterpret_cast<const __half2*>(&q);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 t = __half22float2(h[i]);
+      f[2 * i] = t.x;
+      f[2 * i + 1] = t.y;
+    }
+  } else {
+    f[0] = __uint_as_float(q.x);
+    f[1] = __uint_as_float(q.y);
+    f[2] = __uint_as_float(q.z);
+    f[3] = __uint_as_float(q.w);
+  }
+}
+template <bool HALF>
+__device__ __forceinline__ uint4 vec_pack(const float* f) {
+  uint4 q;
+  if (HALF) {
+    q.x = pack_half2(f[0], f[1]);
+    q.y = pack_half2(f[2], f[3]);
+    q.z = pack_half2(f[4], f[5]);
+    q.w = pack_half2(f[6], f[7]);
+  } else {
+    q.x = __float_as_uint(f[0]);
+    q.y = __float_as_uint(f[1]);
+    q.z = __float_as_uint(f[2]);
+    q.w = __float_as_uint(f[3]);
+  }
+  return q;
+}
+template <bool HALF>
+__device__ __forceinline__ uint4 multimem_ld_reduce_vec(const void* mc) {
+  uint4 q;
+  if (HALF) {
+    asm volatile(
+        "multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+        : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w)
+        : "l"(mc)
+        : "memory");
+  } else {
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w)
+                 : "l"(mc)
+                 : "memory");
+  }
+  return q;
+}
+template <bool HALF>
+__device__ __forceinline__ void multimem_st_vec(void* mc, const uint4& q) {
+  if (HALF) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc),
+                 "r"(q.x), "r"(q.y), "r"(q.z), "r"(q.w)
+                 : "memory");
+  } else {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc),
+                 "r"(q.x), "r"(q.y), "r"(q.z), "r"(q.w)
+                 : "memory");
+  }
+}
+
+// One optimizer step on E consecutive elements held in registers.
+template <int E>
+__device__ __forceinline__ void update_regs(const HyperParams& h, float (&wv)[E],
+                                            const float (&gv)[E], float (&mv)[E],
+                                            float (&vv)[E]) {
+#pragma unroll
+  for (int k = 0; k < E; ++k) {
+    float g = gv[k] * h.grad_scale + h.weight_decay * wv[k];
+    if (h.clip > 0.f) g = fminf(fmaxf(g, -h.clip), h.clip);
+    if (h.opt == 0) {
+      wv[k] -= h.lr * g;
+    } else if (h.opt == 1) {
+      mv[k] = mv[k] * h.momentum + g;
+      wv[k] -= h.lr * (g + h.momentum * mv[k]);
+    } else if (h.opt == 2) {
+      vv[k] = h.decay * vv[k] + (1.f - h.decay) * g * g;
+      mv[k] = h.momentum * mv[k] + h.lr * g * rsqrtf(vv[k] + h.epsilon);
+      wv[k] -= mv[k];
+    } else {
+      const float b1 = h.momentum, b2 = h.decay;
+      mv[k] = b1 * mv[k] + (1.f - b1) * g;
+      vv[k] = b2 * vv[k] + (1.f - b2) * g * g;
+      const float lr_t = h.lr * sqrtf(1.f - __powf(b2, h.adam_t)) / (1.f - __powf(b1, h.adam_t));
+      wv[k] -= lr_t * mv[k] / (sqrtf(vv[k]) + h.epsilon);
+    }
+  }
+}
+
+template <int E>
+__device__ __forceinline__ void load_f32(const float* p, float (&f)[E]) {
+#pragma unroll
+  for (int k = 0; k < E; k += 4) {
+    const float4 t = *reinterpret_cast<const float4*>(p + k);
+    f[k] = t.x; f[k + 1] = t.y; f[k + 2] = t.z; f[k + 3] = t.w;
+  }
+}
+template <int E>
+__device__ __forceinline__ void store_f32(float* p, const float (&f)[E]) {
+#pragma unroll
+  for (int k = 0; k < E; k += 4)
+    *reinterpret_cast<float4*>(p + k) = make_float4(f[k], f[k + 1], f[k + 2], f[k + 3]);
+}
+
+template <int MODE, bool NVLS, bool HALF>
+__global__ void __launch_bounds__(512)
+    allreduce_update2_kernel(PeerCtx c, Ar2Args a, HyperParams h) {
+  constexpr int E = HALF ? 8 : 4;             // elements per 16-byte vector on the wire
+  constexpr int ES = HALF ? 2 : 4;            // bytes per element on the wire
+  resolve_dyn(h, a.dyn);
+  const uint32_t seq = a.seq + seq_offset(c);
+  const int n = c.nranks;
+  // --- announce: my source data for [offset, offset+count) is final ---
+  if (blockIdx.x == 0 && threadIdx.x < n)
+    st_release_sys(c.flags[threadIdx.x] + FLAG_READY * kMaxRanks + c.rank, seq);
+  wait_flags(c, FLAG_READY, seq);
+
+  // --- phase 1: reduce my shard (pull from the peers, or in the switch), hand the result to
+  //     every rank ---
+  const long long per = ((a.count + n - 1) / n + 7) & ~7ll;  // shard length, multiple of 8
+  const long long s_begin = a.offset + per * c.rank;
+  long long s_end = s_begin + per;
+  if (s_end > a.offset + a.count) s_end = a.offset + a.count;
+  const long long nvec = s_end > s_begin ? (s_end - s_begin) / E : 0;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  const float inv_n = 1.f / static_cast<float>(n);
+  constexpr int kU = 4;
+  for (long long v0 = tid; v0 < nvec; v0 += nthreads * kU) {
+    uint4 out[kU];
+    bool ok[kU];
+    long long byte_off[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long vi = v0 + u * nthreads;
+      ok[u] = vi < nvec;
+      byte_off[u] = (s_begin + (ok[u] ? vi : v0) * E) * ES;
+    }
+    if (NVLS) {
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (ok[u])
+          out[u] = multimem_ld_reduce_vec<HALF>(static_cast<const char*>(a.src_mc) + byte_off[u]);
+      if (MODE == 1) {
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          float f[E];
+          vec_unpack<HALF>(out[u], f);
+#pragma unroll
+          for (int k = 0; k < E; ++k) f[k] *= inv_n;
+          out[u] = vec_pack<HALF>(f);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (ok[u]) multimem_st_vec<HALF>(static_cast<char*>(a.red_mc) + byte_off[u], out[u]);
+    } else {
+      float acc[kU][E];
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+#pragma unroll
+        for (int k = 0; k < E; ++k) acc[u][k] = 0.f;
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < n) {
+          uint4 x[kU];
+#pragma unroll
+          for (int u = 0; u < kU; ++u)
+            x[u] = *reinterpret_cast<const uint4*>(static_cast<const char*>(a.src[r]) +
+                                                   byte_off[u]);
+#pragma unroll
+          for (int u = 0; u < kU; ++u) {
+            float f[E];
+            vec_unpack<HALF>(x[u], f);
+#pragma unroll
+            for (int k = 0; k < E; ++k) acc[u][k] += f[k];
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        if (MODE == 1) {
+#pragma unroll
+          for (int k = 0; k < E; ++k) acc[u][k] *= inv_n;
+        }
+        out[u] = vec_pack<HALF>(acc[u]);
+      }
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < n) {
+#pragma unroll
+          for (int u = 0; u < kU; ++u)
+            if (ok[u])
+              *reinterpret_cast<uint4*>(static_cast<char*>(a.red[r]) + byte_off[u]) = out[u];
+        }
+      }
+    }
+  }
+  grid_arrive_and_signal(c, FLAG_REDUCED, seq, 0);
+  wait_flags(c, FLAG_REDUCED, seq);
+
+  // --- phase 2: every rank applies the identical update to its full replica ---
+  const bool skip = (a.skip_flag != nullptr && *a.skip_flag != 0) || a.reduce_only;
+  if (skip) return;
+  constexpr int kU2 = HALF ? 2 : 4;           // 4 x 16 bytes of w / m in flight per thread
+  const long long nv2 = a.count / E;
+  const char* red = static_cast<const char*>(a.red_local);
+  for (long long v0 = tid; v0 < nv2; v0 += nthreads * kU2) {
+    uint4 rq[kU2];
+    float wv[kU2][E], mv[kU2][E], vv[kU2][E], gl[kU2][E];
+    long long i[kU2];
+    bool ok[kU2];
+#pragma unroll
+    for (int u = 0; u < kU2; ++u) {
+      const long long vi = v0 + u * nthreads;
+      ok[u] = vi < nv2;
+      i[u] = a.offset + (ok[u] ? vi : v0) * E;
+      rq[u] = __ldcg(reinterpret_cast<const uint4*>(red + i[u] * ES));
+    }
+#pragma unroll
+    for (int u = 0; u < kU2; ++u) load_f32<E>(a.w + i[u], wv[u]);
+    if (h.opt != 0) {
+#pragma unroll
+      for (int u = 0; u < kU2; ++u) load_f32<E>(a.m + i[u], mv[u]);
+    }
+    if (h.opt >= 2) {
+#pragma unroll
+      for (int u = 0; u < kU2; ++u) load_f32<E>(a.v + i[u], vv[u]);
+    }
+    if (MODE == 1) {
+#pragma unroll
+      for (int u = 0; u < kU2; ++u) load_f32<E>(a.g_local + i[u], gl[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < kU2; ++u) {
+      float r[E];
+      vec_unpack<HALF>(rq[u], r);
+      if (MODE == 1) {
+        // SMA: w <- (1-a) w + a * avg(w); then the local gradient step
+#pragma unroll
+        for (int k = 0; k < E; ++k)
+          wv[u][k] = (1.f - a.sma_alpha) * wv[u][k] + a.sma_alpha * r[k];
+        update_regs<E>(h, wv[u], gl[u], mv[u], vv[u]);
+      } else {
+        update_regs<E>(h, wv[u], r, mv[u], vv[u]);
+      }
+      if (!ok[u]) continue;
+      store_f32<E>(a.w + i[u], wv[u]);
+      if (h.opt != 0) store_f32<E>(a.m + i[u], mv[u]);
+      if (h.opt >= 2) store_f32<E>(a.v + i[u], vv[u]);
+      if (a.w16 != nullptr) {
+#pragma unroll
+        for (int k = 0; k < E; k += 4) {
+          uint2 q;
+          q.x = pack_half2(wv[u][k], wv[u][k + 1]);
+          q.y = pack_half2(wv[u][k + 2], wv[u][k + 3]);
+          *reinterpret_cast<uint2*>(a.w16 + i[u] + k) = q;
+        }
+      }
+    }
+  }
+}
+
+// fp32 -> fp16 copy of a gradient range into the (symmetric) compact-transfer arena
+__global__ void __launch_bounds__(256)
+    cast_range_f16_kernel(const float* __restrict__ in, __half* __restrict__ out, long long n) {
+  const long long nv = n / 8;
+  for (long long v0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < nv;
+       v0 += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float4 a0 = *reinterpret_cast<const float4*>(in + v0 * 8);
+    const float4 a1 = *reinterpret_cast<const float4*>(in + v0 * 8 + 4);
+    uint4 q;
+    q.x = pack_half2(a0.x, a0.y);
+    q.y = pack_half2(a0.z, a0.w);
+    q.z = pack_half2(a1.x, a1.y);
+    q.w = pack_half2(a1.z, a1.w);
+    *reinterpret_cast<uint4*>(out + v0 * 8) = q;
+  }
+}
+
 // Pull `count` floats at `offset` from rank `root`'s arena into mine (+ fp16 shadow).
 __global__ void __launch_bounds__(512)
     broadcast_pull_kernel(PeerCtx c, int root, long long offset, long long count, uint32_t seq,
@@ -706,6 +1037,14 @@ extern "C" int kfb_check_finite(const float* g, long long n, int* flag, void* st
   return 0;
 }
 
+extern "C" int kfb_set_hyper_dyn(float* dyn, float lr, float grad_scale, float adam_t, int mask,
+                                 void* stream) {
+  KFB_REQUIRE(dyn != nullptr, "set_hyper_dyn: null dyn");
+  set_hyper_dyn_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(dyn, lr, grad_scale, adam_t, mask);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int kfb_loss_scale_update(float* state, int* flag, int inc_every, float* dyn,
                                      float base_grad_scale, void* stream) {
   loss_scale_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(state, flag, inc_every, dyn,
@@ -787,6 +1126,84 @@ extern "C" int kfb_allreduce_update_nvls(int mode, int rank, int nranks, const v
     allreduce_update_nvls_kernel<0><<<blocks, 512, 0, st>>>(
         c, (const float*)src_mc, (float*)reduced_mc, offset, count, seq, w, g_local, m, v,
         (__half*)w16, make_hyper(hp), dyn, skip_flag, sma_alpha, mode == 2 ? 1 : 0);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Second generation (see allreduce_update2_kernel). Pull form: `src` / `reduced` hold every
+// rank's arena / landing buffer addresses and src_mc = reduced_mc = null. NVLS form: src_mc /
+// reduced_mc are the multicast aliases and src / reduced may be null. `half` = 1: the source
+// arenas and the landing buffers hold fp16 (compact gradient transfer; mode 0 or 2 only).
+// `cast_from` (optional, with half): this rank's fp32 gradients of the range are first copied as
+// fp16 into `cast_to` (this rank's source arena) on the same stream.
+extern "C" int kfb_allreduce_update2(int mode, int rank, int nranks, void* const* src,
+                                     void* const* reduced, const void* src_mc, void* reduced_mc,
+                                     const void* reduced_local, void* const* flags, int half,
+                                     const float* cast_from, void* cast_to, long long offset,
+                                     long long count, unsigned seq, float* w,
+                                     const float* g_local, float* m, float* v, void* w16,
+                                     const kfb_hyper* hp, const float* dyn, const int* skip_flag,
+                                     float sma_alpha, int blocks, void* stream) {
+  KFB_REQUIRE(hp != nullptr && reduced_local != nullptr, "allreduce_update2: null argument");
+  KFB_REQUIRE(offset % 8 == 0 && count % 8 == 0,
+              "allreduce_update2: offset (%lld) and count (%lld) must be multiples of 8", offset,
+              count);
+  KFB_REQUIRE(!(half && mode == 1), "allreduce_update2: SMA averages the fp32 model");
+  const bool nvls = src_mc != nullptr;
+  KFB_REQUIRE(nvls ? reduced_mc != nullptr : (src != nullptr && reduced != nullptr),
+              "allreduce_update2: incomplete %s addresses", nvls ? "multicast" : "peer");
+  PeerCtx c;
+  if (fill_peer_ctx(&c, rank, nranks, flags, nullptr, flags)) return 2;
+  Ar2Args a;
+  for (int r = 0; r < kMaxRanks; ++r) {
+    a.src[r] = (!nvls && r < nranks) ? src[r] : nullptr;
+    a.red[r] = (!nvls && r < nranks) ? reduced[r] : nullptr;
+  }
+  a.src_mc = src_mc;
+  a.red_mc = reduced_mc;
+  a.red_local = reduced_local;
+  a.offset = offset;
+  a.count = count;
+  a.seq = seq;
+  a.w = w;
+  a.g_local = g_local;
+  a.m = m;
+  a.v = v;
+  a.w16 = (__half*)w16;
+  a.dyn = dyn;
+  a.skip_flag = skip_flag;
+  a.sma_alpha = sma_alpha;
+  a.reduce_only = mode == 2 ? 1 : 0;
+  if (blocks <= 0) {
+    static const int forced = [] {
+      const char* e = getenv("KFB_AR_BLOCKS");
+      return (e != nullptr && *e != 0) ? atoi(e) : 0;
+    }();
+    // measured on 2 B200s, 102 MB: 16 / 32 / 64 / 96 / 148 CTAs -> 710 / 376 / 298 / 259 / 263 us
+    blocks = forced > 0 ? forced
+                        : (count >= (4ll << 20) ? 96 : (count >= (1ll << 20) ? 64 : 32));
+  }
+  if (blocks > 148) blocks = 148;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (half && cast_from != nullptr) {
+    KFB_REQUIRE(cast_to != nullptr, "allreduce_update2: cast_to missing");
+    long long cb = (count / 8 + 255) / 256;
+    if (cb > 2 * blocks) cb = 2 * blocks;
+    if (cb < 1) cb = 1;
+    cast_range_f16_kernel<<<(unsigned)cb, 256, 0, st>>>(cast_from + offset,
+                                                       (__half*)cast_to + offset, count);
+  }
+  const HyperParams h = make_hyper(hp);
+#define KFB_AR2(MODE, NVLS, HALF) \
+  allreduce_update2_kernel<MODE, NVLS, HALF><<<blocks, 512, 0, st>>>(c, a, h)
+  if (mode == 1) {
+    if (nvls) KFB_AR2(1, true, false); else KFB_AR2(1, false, false);
+  } else if (half) {
+    if (nvls) KFB_AR2(0, true, true); else KFB_AR2(0, false, true);
+  } else {
+    if (nvls) KFB_AR2(0, true, false); else KFB_AR2(0, false, false);
+  }
+#undef KFB_AR2
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -231,6 +231,11 @@ typedef struct {
 int kfb_optimizer_step(float* w, const float* g, float* m, float* v, void* w16, long long n,
                        const kfb_hyper* hp, const float* dyn, const int* skip_flag, void* stream);
 int kfb_check_finite(const float* g, long long n, int* flag, void* stream);
+/* dyn[i] <- the argument for every bit i of `mask` (lr, grad_scale, adam_t), from a one-thread
+ * kernel on `stream`: per-step values for captured graphs / device-resident loss scaling without
+ * a pinned staging buffer. */
+int kfb_set_hyper_dyn(float* dyn, float lr, float grad_scale, float adam_t, int mask,
+                      void* stream);
 int kfb_loss_scale_update(float* state, int* flag, int inc_every, float* dyn,
                           float base_grad_scale, void* stream);
 
@@ -265,6 +270,22 @@ int kfb_allreduce_update_nvls(int mode, int rank, int nranks, const void* src_mc
                               const float* g_local, float* m, float* v, void* w16,
                               const kfb_hyper* hp, const float* dyn, const int* skip_flag,
                               float sma_alpha, int blocks, void* stream);
+/* Second generation of the two entry points above, one kernel template for both forms. Pull
+ * form: src / reduced = per-rank addresses, src_mc = reduced_mc = NULL. NVLS form: src_mc /
+ * reduced_mc = multicast aliases (src / reduced may be NULL). half = 1 is the compact gradient
+ * transfer of the reference (--compact_gradient_transfer: fp16 on the wire whenever use_fp16,
+ * T/variable_mgr.py:311-313, T/batch_allreduce.py:429-453): sources and landing buffers hold
+ * fp16, the sum is taken in fp32; with cast_from / cast_to this rank's fp32 gradients of the
+ * range are first copied as fp16 into its source arena on the same stream. offset and count
+ * must be multiples of 8. Phase 2 keeps four 16-byte vectors per array in flight per thread, so
+ * the few CTAs the kernel runs with (backward wants the SMs) still stream at HBM rate. */
+int kfb_allreduce_update2(int mode, int rank, int nranks, void* const* src, void* const* reduced,
+                          const void* src_mc, void* reduced_mc, const void* reduced_local,
+                          void* const* flags, int half, const float* cast_from, void* cast_to,
+                          long long offset, long long count, unsigned seq, float* w,
+                          const float* g_local, float* m, float* v, void* w16,
+                          const kfb_hyper* hp, const float* dyn, const int* skip_flag,
+                          float sma_alpha, int blocks, void* stream);
 /* Owner side of the fused weight-gradient reduce-scatter (see kfb_push_target): sums the nranks
  * local staging slots of this rank's shard of [offset, offset+count), pushes the sum to every
  * rank and applies the optimizer - kfb_allreduce_update with local instead of peer sources. */

@@ -190,6 +190,11 @@ class BenchmarkCNN:
                                  "variable_update=%s." % p.variable_update)
             if p.staged_vars:
                 raise ValueError("Automatic loss scaling is not supported with staged_vars.")
+            if p.variable_consistency == "relaxed":
+                # the deferred update would apply a sum whose finite check and loss scale
+                # belong to another step
+                raise ValueError("Automatic loss scaling is not supported with "
+                                 "variable_consistency=relaxed.")
         if p.debugger is not None and p.debugger != "cli" and ":" not in p.debugger:
             raise ValueError('--debugger must be "cli" or in the form host:port')
         if p.hierarchical_copy and p.num_gpus <= 1:
@@ -516,7 +521,7 @@ class BenchmarkCNN:
                 self._last_lr = lr
                 eng.begin_step(lr)
                 ex.forward(True)
-                ex.loss_backward(loss_scale=eng.loss_scale, on_grads_ready=eng.on_grads_ready)
+                ex.loss_backward(on_grads_ready=eng.on_grads_ready, **eng.loss_scale_kwargs())
                 eng.finish_step()
                 self.global_step += 1
                 return
@@ -530,7 +535,7 @@ class BenchmarkCNN:
             with torch.cuda.graph(g):
                 eng.begin_step(lr)
                 ex.forward(True)
-                ex.loss_backward(loss_scale=eng.loss_scale, on_grads_ready=eng.on_grads_ready)
+                ex.loss_backward(on_grads_ready=eng.on_grads_ready, **eng.loss_scale_kwargs())
                 eng.finish_step()
                 if multi:
                     # last node: move the device part of the sequence numbers past this step
@@ -574,7 +579,7 @@ class BenchmarkCNN:
                                self.dataset.num_examples_per_epoch("train"))
         self._last_lr = lr
         eng.begin_step(lr)
-        ex.loss_backward(loss_scale=eng.loss_scale, on_grads_ready=eng.on_grads_ready)
+        ex.loss_backward(on_grads_ready=eng.on_grads_ready, **eng.loss_scale_kwargs())
         eng.finish_step()
         self.global_step += 1
         if prefetch:

@@ -244,7 +244,10 @@ class RefExecutor:
 
     # -- loss / backward ------------------------------------------------------------
     def loss_backward(self, loss_scale: float = 1.0, backward: bool = True,
-                      on_grads_ready: Optional[Callable[[int, int], None]] = None) -> None:
+                      on_grads_ready: Optional[Callable[[int, int], None]] = None,
+                      dyn_scale=None) -> None:
+        if dyn_scale is not None:       # device-resident loss scale (CUDA executor only)
+            loss_scale = loss_scale * float(dyn_scale)
         g = self.graph
         logits = self._vals[g.logits.id].float() if g.logits is not None else None
         kind = g.loss["kind"]

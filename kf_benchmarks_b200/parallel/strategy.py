@@ -27,6 +27,7 @@ high-priority stream at once, overlapping the exchange with the rest of backward
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional, Tuple
 
 import numpy as np
@@ -120,10 +121,25 @@ class UpdateEngine:
             # tf.train.RMSPropOptimizer creates its "rms" slot filled with ones
             # (T/benchmark_cnn.py:1179-1185 uses it with momentum / decay / epsilon flags)
             self.v.fill_(1.0)
-        self.loss_scale = self._initial_loss_scale()
         self.auto_loss_scale = bool(params.use_fp16 and params.fp16_enable_auto_loss_scale)
-        self.loss_scale_normal_steps = 0
-        self.skipped_steps = 0
+        # Automatic loss scaling keeps its state machine on the device (T/variable_mgr_util.py:
+        # 91-139 takes the skip / apply decision inside the graph with tf.cond): ls_state =
+        # {scale, clean steps, skipped steps, -}; the loss kernels read the scale from it, the
+        # update kernels read grad_scale from dyn[1] and the skip decision from skip_flag, and
+        # kfb_loss_scale_update moves the state - no device->host read in the step. The host
+        # path (CPU replicas, torch.distributed, SMA / PairAveraging) keeps the Python mirror.
+        self.device_ls = bool(self.auto_loss_scale and self.device.type == "cuda" and
+                              self.algo in ("none", "allreduce") and
+                              not isinstance(comm, TorchDistComm) and
+                              params.variable_consistency != "relaxed" and
+                              not params.staged_vars)
+        self.ls_state = None
+        self._loss_scale = self._initial_loss_scale()
+        self._ls_normal_steps = 0
+        self._skipped_steps = 0
+        if self.device_ls:
+            self.ls_state = torch.tensor([self._loss_scale, 0.0, 0.0, 0.0], dtype=torch.float32,
+                                         device=self.device)
         # bucket size: --bucket_bytes, but never more than ~12 buckets for very large models (each
         # bucket costs two flag rounds across the ranks)
         bucket_elems = max(int(params.bucket_bytes) // 4, n // 12, 128)
@@ -152,6 +168,56 @@ class UpdateEngine:
         if self.fused_push:
             self.buckets = self._plan_buckets_on_slots(bucket_elems)
         self._setup_comm_buffers()
+
+    # ------------------------------------------------------------------ loss-scale state
+    def _ls_get(self, idx: int, host_value):
+        if self.ls_state is None:
+            return host_value
+        return float(self.ls_state[idx].item())      # synchronises; not used inside the step
+
+    def _ls_set(self, idx: int, value: float) -> None:
+        if self.ls_state is not None:
+            self.ls_state[idx] = float(value)
+            if idx == 0 and self.dyn is not None:
+                self.dyn[1] = self._base_grad_scale() / float(value)
+
+    @property
+    def loss_scale(self) -> float:
+        return self._ls_get(0, self._loss_scale)
+
+    @loss_scale.setter
+    def loss_scale(self, value: float) -> None:
+        self._loss_scale = float(value)
+        self._ls_set(0, value)
+
+    @property
+    def loss_scale_normal_steps(self) -> int:
+        return int(self._ls_get(1, self._ls_normal_steps))
+
+    @loss_scale_normal_steps.setter
+    def loss_scale_normal_steps(self, value: int) -> None:
+        self._ls_normal_steps = int(value)
+        self._ls_set(1, value)
+
+    @property
+    def skipped_steps(self) -> int:
+        return int(self._ls_get(2, self._skipped_steps))
+
+    @skipped_steps.setter
+    def skipped_steps(self, value: int) -> None:
+        self._skipped_steps = int(value)
+        self._ls_set(2, value)
+
+    def loss_scale_kwargs(self) -> dict:
+        """loss_scale / dyn_scale arguments of ``executor.loss_backward``: with the
+        device-resident state the loss kernels multiply by the scale they read from
+        ``ls_state``."""
+        if self.ls_state is not None:
+            return dict(loss_scale=1.0, dyn_scale=self.ls_state[0:1])
+        return dict(loss_scale=self._loss_scale, dyn_scale=None)
+
+    def _base_grad_scale(self) -> float:
+        return (1.0 / self.comm.size) if (self.algo == "allreduce" and self.average) else 1.0
 
     # ------------------------------------------------------------------ setup
     def _initial_loss_scale(self) -> float:
@@ -231,6 +297,23 @@ class UpdateEngine:
                 self._grad_mc = ctypes.c_void_p(c.mc_ptr(st.grad))
                 self._w_mc = ctypes.c_void_p(c.mc_ptr(st.w32))
                 self._red_mc = ctypes.c_void_p(c.mc_ptr(self.reduced))
+            # second-generation kernel (kfb_allreduce_update2); KFB_AR_V2=0 keeps the first
+            self.ar_v2 = os.environ.get("KFB_AR_V2", "1") != "0"
+            # --compact_gradient_transfer (T/variable_mgr.py:311-313: whenever use_fp16): the
+            # gradients cross NVLink as fp16 (summed in fp32); symmetric fp16 arenas for the
+            # sources and the reduced shards
+            p = self.params
+            self.compact = bool(self.ar_v2 and p.use_fp16 and p.compact_gradient_transfer and
+                                self.algo in ("allreduce", "ada") and not self.relaxed and
+                                not self.fused_push)
+            if self.compact:
+                self.g16 = c.symm_alloc(self.total, torch.float16)
+                self.r16 = c.symm_alloc(self.total, torch.float16)
+                self._g16_ptrs = c.ptr_array(self.g16)
+                self._r16_ptrs = c.ptr_array(self.r16)
+                if self.nvls:
+                    self._g16_mc = ctypes.c_void_p(c.mc_ptr(self.g16))
+                    self._r16_mc = ctypes.c_void_p(c.mc_ptr(self.r16))
             self.ready_event = torch.cuda.Event()
             self.done_event = torch.cuda.Event()
             if self.algo in ("pair", "ada"):
@@ -267,7 +350,7 @@ class UpdateEngine:
         h.weight_decay = p.weight_decay or 0.0
         if self._effective_algo() == "allreduce" and not self.average:
             h.weight_decay *= self.comm.size
-        scale = 1.0 / self.loss_scale
+        scale = 1.0 / self._loss_scale      # device-resident scaling: dyn[1] overrides this
         if self._effective_algo() == "allreduce" and self.average:
             scale /= self.comm.size
         h.grad_scale = scale
@@ -276,14 +359,21 @@ class UpdateEngine:
         return h
 
     def enable_dynamic_hyper(self) -> None:
-        self.dyn = torch.zeros(4, dtype=torch.float32, device=self.device)
-        self._dyn_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+        if self.dyn is None:
+            self.dyn = torch.zeros(4, dtype=torch.float32, device=self.device)
+            if self.ls_state is not None:
+                self.dyn[1] = self._base_grad_scale() / self._loss_scale
 
     def push_dynamic_hyper(self, lr: float) -> None:
-        """Uploads this step's learning rate / gradient scale / Adam step for graph replay."""
+        """This step's learning rate / gradient scale / Adam step count into the device-resident
+        hyper-parameters (graph replay, device-resident loss scaling). A one-thread kernel takes
+        the values by argument, so the host may run any number of steps ahead of the device;
+        under automatic loss scaling grad_scale belongs to kfb_loss_scale_update and is left
+        alone."""
         h = self._hyper(lr)
-        self._dyn_host[0], self._dyn_host[1], self._dyn_host[2] = h.lr, h.grad_scale, h.adam_t
-        self.dyn.copy_(self._dyn_host, non_blocking=True)
+        mask = 5 if self.ls_state is not None else 7
+        native.call("set_hyper_dyn", ptr(self.dyn), f32(h.lr), f32(h.grad_scale), f32(h.adam_t),
+                    i32(mask), self._s())
 
     def begin_step(self, lr: float) -> None:
         """Called before backward: arms the overlap scheduler."""
@@ -295,7 +385,12 @@ class UpdateEngine:
             torch.cuda.current_stream(self.device).wait_event(self.done_event)
         self._ready_hi = 0
         self._launched = 0
-        if self.cuda and self.auto_loss_scale:
+        if self.device_ls:
+            # the per-step values the update kernels read from device memory (the skip flag was
+            # cleared by the previous kfb_loss_scale_update)
+            self.enable_dynamic_hyper()
+            self.push_dynamic_hyper(lr)
+        elif self.cuda and self.auto_loss_scale:
             self.skip_flag.zero_()
 
     def _effective_algo(self) -> str:
@@ -316,13 +411,17 @@ class UpdateEngine:
 
     def _can_overlap(self) -> bool:
         return (self.cuda and isinstance(self.comm, P2PComm) and
-                self._effective_algo() == "allreduce" and not self.auto_loss_scale and
-                not self.relaxed)
+                self._effective_algo() == "allreduce" and
+                (not self.auto_loss_scale or self.device_ls) and not self.relaxed)
 
     def finish_step(self) -> None:
         """Called after backward: runs whatever has not been overlapped and makes the compute
         stream wait for the update."""
         algo = self._effective_algo()
+        if self.device_ls:
+            self._finish_device_loss_scale(algo)
+            self.step_count += 1
+            return
         if self.auto_loss_scale:
             self._check_finite()
         if self.relaxed and algo == "allreduce":
@@ -336,9 +435,12 @@ class UpdateEngine:
         elif algo == "pair":
             self._pair_update()
         else:
-            if self._launched == 0 and not self._can_overlap():
-                # nothing was overlapped (SMA, auto loss scale, micro-benchmark): one launch
-                self._launch_bucket((0, self.total), overlapped=False)
+            if self._launched == 0 and not self.fused_push:
+                # nothing was overlapped (SMA, auto loss scale, the all-reduce micro-benchmark,
+                # gradients that all became ready at once): one launch over the whole arena -
+                # every extra bucket costs ~55 us of flag rounds and ramp (2 B200s, 102 MB:
+                # 4 buckets 520 us, 1 launch 260 us)
+                self._launch_bucket((0, self.total), overlapped=self._can_overlap())
                 self._launched = len(self.buckets)
             while self._launched < len(self.buckets):
                 self._launch_bucket(self.buckets[self._launched], overlapped=self._can_overlap())
@@ -349,6 +451,34 @@ class UpdateEngine:
         if self.auto_loss_scale:
             self._update_loss_scale()
         self.step_count += 1
+
+    def _finish_device_loss_scale(self, algo: str) -> None:
+        """Automatic loss scaling without a host round trip. The buckets were summed (reduce
+        only) and checked for inf / nan on the exchange stream while backward ran - a non-finite
+        gradient on any rank makes the sum non-finite on every rank, so all ranks take the same
+        decision without exchanging it; the whole-arena update is predicated on the flag and
+        the state machine moves on the device."""
+        st, c = self.store, self.comm
+        flag = ptr(self.skip_flag)
+        if algo == "none" or not isinstance(c, P2PComm):
+            native.call("check_finite", ptr(st.grad), i64(self.total), flag, self._s())
+            src = st.grad
+        else:
+            if self._launched == 0:
+                self._launch_bucket((0, self.total), overlapped=True)
+                self._launched = len(self.buckets)
+            while self._launched < len(self.buckets):
+                self._launch_bucket(self.buckets[self._launched], overlapped=True)
+                self._launched += 1
+            self.done_event.record(c.comm_stream)
+            torch.cuda.current_stream(self.device).wait_event(self.done_event)
+            src = self.reduced
+        native.call("optimizer_step", ptr(st.w32), ptr(src), ptr(self.m), ptr(self.v),
+                    ptr(st.w16), i64(self.total), ctypes.byref(self._h), ptr(self.dyn), flag,
+                    self._s())
+        native.call("loss_scale_update", ptr(self.ls_state), flag,
+                    i32(int(self.params.fp16_inc_loss_scale_every_n)), ptr(self.dyn),
+                    f32(self._base_grad_scale()), self._s())
 
     def _finish_relaxed(self) -> None:
         """variable_consistency=relaxed (T/batch_allreduce.py:353-388): apply the all-reduced
@@ -405,6 +535,12 @@ class UpdateEngine:
             stream = c.comm_stream
         mode = 1 if algo == "sma" else 0
         h = self._h
+        if self.device_ls:
+            # reduce only + finite check of the sum; the update follows once every bucket is in
+            self._allreduce_call(2, lo, hi - lo, h, None, stream)
+            native.call("check_finite", self._ptr_at(self.reduced, lo), i64(hi - lo),
+                        ptr(self.skip_flag), self._s(stream))
+            return
         if self.fused_push and self._push_targets:
             per, ranges_dev, nranges, longest = self._bucket_push[self.buckets.index(bucket)]
             if nranges:
@@ -427,7 +563,22 @@ class UpdateEngine:
         tail = (i64(lo), i64(count), ctypes.c_uint(c.next_seq()), ptr(st.w32), ptr(st.grad),
                 ptr(self.m), ptr(self.v), ptr(st.w16), ctypes.byref(h), ptr(self.dyn), skip_flag,
                 f32(self.params.sma_alpha if mode == 1 else 0.0), i32(0), self._s(stream))
-        if self.nvls:
+        if self.ar_v2 and lo % 8 == 0 and count % 8 == 0:
+            half = self.compact and mode == 0
+            if half:
+                src, red, red_local = self._g16_ptrs, self._r16_ptrs, ptr(self.r16)
+                src_mc = self._g16_mc if self.nvls else None
+                red_mc = self._r16_mc if self.nvls else None
+            else:
+                src = self._w_ptrs if mode == 1 else self._grad_ptrs
+                red, red_local = self._red_ptrs, ptr(self.reduced)
+                src_mc = (self._w_mc if mode == 1 else self._grad_mc) if self.nvls else None
+                red_mc = self._red_mc if self.nvls else None
+            native.call("allreduce_update2", i32(mode), i32(c.rank), i32(c.size),
+                        None if self.nvls else src, None if self.nvls else red, src_mc, red_mc,
+                        red_local, self._flag_ptrs, i32(int(half)),
+                        ptr(st.grad) if half else None, ptr(self.g16) if half else None, *tail)
+        elif self.nvls:
             native.call("allreduce_update_nvls", i32(mode), i32(c.rank), i32(c.size),
                         self._w_mc if mode == 1 else self._grad_mc, self._red_mc,
                         ptr(self.reduced), self._flag_ptrs, *tail)
@@ -466,14 +617,15 @@ class UpdateEngine:
             self._cpu_skip = bad != 0
 
     def _update_loss_scale(self) -> None:
-        """Host mirror of the state machine (T/variable_mgr_util.py:51-88). The decision needs
-        the flag on the host; auto loss scaling therefore costs one small D2H per step."""
+        """Host mirror of the state machine (T/variable_mgr_util.py:51-88) for the paths without
+        the device-resident form (CPU replicas, torch.distributed, SMA / PairAveraging): the
+        decision needs the flag on the host, one small D2H per step."""
         skipped = bool(self.skip_flag.item()) if self.cuda else self._cpu_skip
-        self.loss_scale, self.loss_scale_normal_steps = next_loss_scale(
-            self.loss_scale, self.loss_scale_normal_steps, skipped,
+        self._loss_scale, self._ls_normal_steps = next_loss_scale(
+            self._loss_scale, self._ls_normal_steps, skipped,
             self.params.fp16_inc_loss_scale_every_n)
         if skipped:
-            self.skipped_steps += 1
+            self._skipped_steps += 1
 
     # ------------------------------------------------------------------ torch paths
     def _finish_torch(self, algo: str) -> None:

@@ -203,6 +203,9 @@ def test_graphed_step_control_flow_with_two_ranks(monkeypatch):
         step_count = 0
         loss_scale = 1.0
 
+        def loss_scale_kwargs(self):
+            return dict(loss_scale=1.0, dyn_scale=None)
+
         def learning_rate(self, *a):
             return 0.1
 
@@ -273,7 +276,7 @@ def test_allreduce_call_passes_the_prototypes_argument_lists(monkeypatch):
     comm = types.SimpleNamespace(rank=1, size=4, next_seq=lambda: 77)
     eng = types.SimpleNamespace(
         store=store, comm=comm, m=T(0x4000), v=None, dyn=None, reduced=T(0x5000),
-        params=types.SimpleNamespace(sma_alpha=0.25), nvls=False,
+        params=types.SimpleNamespace(sma_alpha=0.25), nvls=False, ar_v2=False, compact=False,
         _w_ptrs="W", _grad_ptrs="G", _red_ptrs="R", _flag_ptrs="F",
         _w_mc=ctypes.c_void_p(0x6000), _grad_mc=ctypes.c_void_p(0x7000),
         _red_mc=ctypes.c_void_p(0x8000), _s=lambda stream=None: ctypes.c_void_p(9))
@@ -291,3 +294,24 @@ def test_allreduce_call_passes_the_prototypes_argument_lists(monkeypatch):
     assert len(b) == arity("allreduce_update_nvls") == 21
     assert (b[0].value, b[3].value, b[4].value, b[5].value, b[6]) == (1, 0x6000, 0x8000, 0x5000, "F")
     assert b[18].value == 0.25                                    # SMA blend factor, mode 1
+    # second-generation entry point: pull form, compact (fp16) transfer of a gradient bucket
+    eng.nvls, eng.ar_v2, eng.compact = False, True, True
+    eng.g16, eng.r16 = T(0xA000), T(0xB000)
+    eng._g16_ptrs, eng._r16_ptrs = "G16", "R16"
+    UpdateEngine._allreduce_call(eng, 0, 128, 4096, h, None, None)
+    d = seen["allreduce_update2"]
+    assert len(d) == arity("allreduce_update2") == 26
+    assert (d[3], d[4], d[5], d[6], d[7].value, d[8], d[9].value) == \
+        ("G16", "R16", None, None, 0xB000, "F", 1)
+    assert (d[10].value, d[11].value, d[12].value, d[13].value, d[14].value) == \
+        (0x2000, 0xA000, 128, 4096, 77)
+    # NVLS form of SMA: fp32 weights through the multicast aliases, no compact transfer
+    eng.nvls = True
+    UpdateEngine._allreduce_call(eng, 1, 0, 64, h, None, None)
+    d = seen["allreduce_update2"]
+    assert (d[3], d[4], d[5].value, d[6].value, d[7].value, d[9].value) == \
+        (None, None, 0x6000, 0x8000, 0x5000, 0)
+    assert d[10] is None and d[11] is None and d[23].value == 0.25
+    # ranges that are not multiples of 8 elements stay on the first-generation kernels
+    UpdateEngine._allreduce_call(eng, 0, 4, 60, h, None, None)
+    assert seen["allreduce_update_nvls"][7].value == 4

@@ -60,20 +60,27 @@ def test_replicas_stay_bit_identical_and_match_nccl_baseline(tmp_path):
     import json
     import numpy as np
     outs = {}
-    for impl in ("p2p", "nccl"):
-        d = tmp_path / impl
+    for impl, compact in (("p2p", False), ("nccl", False), ("p2p", True)):
+        key = impl + ("_compact" if compact else "")
+        d = tmp_path / key
         d.mkdir()
         kw = dict(model="resnet20", data_name="cifar10", batch_size=32, use_fp16=True,
                   optimizer="momentum", init_learning_rate=0.05, num_batches=6,
-                  num_warmup_batches=0, variable_update="replicated", num_gpus=2, comm_impl=impl)
+                  num_warmup_batches=0, variable_update="replicated", num_gpus=2, comm_impl=impl,
+                  compact_gradient_transfer=compact)
         res = _launch(2, [os.path.join(ROOT, "tests", "helpers", "rank_worker.py"), json.dumps(kw),
                           str(d)])
         assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
-        outs[impl] = [np.load(str(d / ("rank%d.npz" % r)))["w"] for r in range(2)]
-        assert np.array_equal(outs[impl][0], outs[impl][1])
+        outs[key] = [np.load(str(d / ("rank%d.npz" % r)))["w"] for r in range(2)]
+        assert np.array_equal(outs[key][0], outs[key][1])
     a, b = outs["p2p"][0], outs["nccl"][0]
     cos = float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b)))
     assert cos > 0.9999 and np.abs(a - b).max() < 5e-2
+    # compact gradient transfer (the default, as in the reference): the gradients cross NVLink as
+    # fp16, so six steps at this learning rate drift from the fp32 exchange by fp16 rounding
+    c = outs["p2p_compact"][0]
+    cos = float((a * c).sum() / (np.linalg.norm(a) * np.linalg.norm(c)))
+    assert cos > 0.999 and np.isfinite(c).all()
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
@@ -91,7 +98,8 @@ def test_fused_wgrad_reduce_scatter_is_bit_identical_to_the_pull_path(tmp_path, 
         d.mkdir()
         kw = dict(model=model, data_name=data, batch_size=batch, use_fp16=True,
                   optimizer="momentum", init_learning_rate=1e-4, num_batches=5,
-                  num_warmup_batches=0, variable_update="replicated", num_gpus=2, comm_impl=impl)
+                  num_warmup_batches=0, variable_update="replicated", num_gpus=2, comm_impl=impl,
+                  compact_gradient_transfer=False)   # both paths with fp32 on the wire
         res = _launch(2, [os.path.join(ROOT, "tests", "helpers", "rank_worker.py"), json.dumps(kw),
                           str(d)])
         assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]

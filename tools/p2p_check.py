@@ -51,8 +51,19 @@ def main():
     gp, wp, rp, fp = (comm.ptr_array(grad), comm.ptr_array(w), comm.ptr_array(red),
                       comm.ptr_array(comm.flags))
 
+    # KFB_P2P_V1=1: the first-generation entry points (kfb_allreduce_update / _nvls); default is
+    # the second-generation kernel the engine uses (kfb_allreduce_update2), fp32 on the wire here
+    v1 = os.environ.get("KFB_P2P_V1") == "1"
+
     def ar(mode, src, *tail):
-        if nvls:
+        lo_, cnt_ = tail[0].value, tail[1].value
+        if not v1 and lo_ % 8 == 0 and cnt_ % 8 == 0:
+            native.call("allreduce_update2", i32(mode), i32(rank), i32(world),
+                        None if nvls else (gp if src is grad else wp), None if nvls else rp,
+                        ctypes.c_void_p(comm.mc_ptr(src)) if nvls else None,
+                        ctypes.c_void_p(comm.mc_ptr(red)) if nvls else None, ptr(red), fp,
+                        i32(0), None, None, *tail)
+        elif nvls:
             native.call("allreduce_update_nvls", i32(mode), i32(rank), i32(world),
                         ctypes.c_void_p(comm.mc_ptr(src)), ctypes.c_void_p(comm.mc_ptr(red)),
                         ptr(red), fp, *tail)
@@ -85,6 +96,37 @@ def main():
         optim_ref.apply_update(h, ref_w, gsum, ref_m, None)
         check("allreduce_update step %d (weights)" % step, w, ref_w, 2e-5)
         check("allreduce_update step %d (fp16 shadow)" % step, w16.float(), ref_w, 2e-3)
+    # ---- 1b. compact gradient transfer: fp16 on the wire, fp32 sum, two buckets ----
+    if not v1:
+        g16 = comm.symm_alloc(n, torch.float16)
+        r16 = comm.symm_alloc(n, torch.float16)
+        g16p, r16p = comm.ptr_array(g16), comm.ptr_array(r16)
+        w.copy_(w0)
+        m.zero_()
+        grad.copy_(rank_data(rank, n, 15))
+        comm.barrier()
+        h = make_hyper(1, scale=1.0 / 128)
+        cut = (n // 3) // 128 * 128
+        for lo, hi in [(0, cut), (cut, n)]:
+            native.call("allreduce_update2", i32(0), i32(rank), i32(world),
+                        None if nvls else g16p, None if nvls else r16p,
+                        ctypes.c_void_p(comm.mc_ptr(g16)) if nvls else None,
+                        ctypes.c_void_p(comm.mc_ptr(r16)) if nvls else None, ptr(r16), fp, i32(1),
+                        ptr(grad), ptr(g16), i64(lo), i64(hi - lo),
+                        ctypes.c_uint(comm.next_seq()), ptr(w), ptr(grad), ptr(m), None, ptr(w16),
+                        ctypes.byref(h), None, None, f32(0.0), i32(0), s)
+        torch.cuda.synchronize()
+        gsum = sum(rank_data(r, n, 15).half().float() for r in range(world)).half().float()
+        cw, cm = w0.clone(), torch.zeros(n)
+        optim_ref.apply_update(h, cw, gsum, cm, None)
+        # the switch may round the fp32 sum once more than the host model does: 1 fp16 ulp of
+        # the summed gradient times lr * scale
+        check("allreduce_update2 compact (fp16 wire, fp32 sum)", w, cw, 2e-5)
+        all_w = comm.allgather_object(w.cpu()[:: max(n // 65536, 1)].clone())
+        same = all(torch.equal(all_w[0], x) for x in all_w)
+        ok &= same
+        print("[rank %d] %s compact: replicas bit-identical" % (rank, "PASS" if same else "FAIL"),
+              flush=True)
     # ---- 2. SMA: average of the weight arenas, blend, local SGD ----
     wr = rank_data(rank, n, 20)
     w.copy_(wr)

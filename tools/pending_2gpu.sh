@@ -1,10 +1,24 @@
+# 2-GPU checks of the exchange kernels: host-simulation check (pull and NVLS forms), the
+# multi-GPU tests and the isolated all-reduce benchmark for every implementation.
 set -u
+N=${1:-2}
+MODEL=${2:-resnet50}
 mkdir -p gpurun_out
-echo "== multi tests (all, incl. gated) =="
-KFB_TEST_NVLS=1 KFB_MULTI_RANK_GRAPH=1 timeout 1200 python -m pytest tests/test_gpu_multi.py -q -m gpu -x 2>&1 | tail -15
-echo "== nvls_check 2 =="
-timeout 900 python tools/nvls_check.py 2 > gpurun_out/pending_nvls_check.log 2>&1
-grep -E "NVLS_CHECK|replicas|p2p_check|Average|per all-reduce|FAILED|==|Error|error" gpurun_out/pending_nvls_check.log | head -40
-echo "== devseq =="
-KFB_P2P_DEVSEQ=1 timeout 600 python -m kf_benchmarks_b200.parallel.launcher -np 2 -- tools/p2p_check.py > gpurun_out/pending_p2p_devseq.log 2>&1
-grep -E "device sequence|device counter|P2P_CHECK|FAIL" gpurun_out/pending_p2p_devseq.log | head
+echo "== p2p_check (pull) =="
+timeout 600 python -m kf_benchmarks_b200.parallel.launcher -np $N -- tools/p2p_check.py > gpurun_out/p2p_check_pull.log 2>&1
+grep -E "FAIL|P2P_CHECK|compact" gpurun_out/p2p_check_pull.log | head -20
+echo "== p2p_check (nvls) =="
+KFB_P2P_NVLS=1 timeout 600 python -m kf_benchmarks_b200.parallel.launcher -np $N -- tools/p2p_check.py > gpurun_out/p2p_check_nvls.log 2>&1
+grep -E "FAIL|P2P_CHECK|compact" gpurun_out/p2p_check_nvls.log | head -20
+echo "== all_reduce_benchmark =="
+for impl in p2p nvls nccl; do
+  for extra in "" "--compact_gradient_transfer=false"; do
+    if [ "$impl" = nccl ] && [ -n "$extra" ]; then continue; fi
+    timeout 600 python -m kf_benchmarks_b200.parallel.launcher -np $N -- -m kf_benchmarks_b200.all_reduce_benchmark \
+      --model=$MODEL --variable_update=replicated --num_gpus=$N --use_fp16 --optimizer=momentum \
+      --comm_impl=$impl --num_batches=20 --num_warmup_batches=5 $extra 2>&1 | grep -E "per all-reduce|Error|error" | sed "s/^/$impl $extra: /"
+  done
+done
+KFB_AR_V2=0 timeout 600 python -m kf_benchmarks_b200.parallel.launcher -np $N -- -m kf_benchmarks_b200.all_reduce_benchmark \
+      --model=$MODEL --variable_update=replicated --num_gpus=$N --use_fp16 --optimizer=momentum \
+      --comm_impl=p2p --num_batches=20 --num_warmup_batches=5 2>&1 | grep -E "per all-reduce" | sed "s/^/p2p first generation: /"
