@@ -215,8 +215,9 @@ def main() -> int:
     ap.add_argument("--bucket_bytes", type=int, default=None,
                     help="gradient bucket size of the overlapped exchange (default: the flag's)")
     ap.add_argument("--no_e2e", action="store_true")
-    ap.add_argument("--cuda_graph", type=int, default=0,
-                    help="capture the training step in a CUDA graph (device-resident inputs)")
+    ap.add_argument("--cuda_graph", type=int, default=-1,
+                    help="1 / 0 force the CUDA-graph replay of the step on / off; -1 (default) is "
+                         "the framework's automatic choice (on for ResNet-50)")
     args = ap.parse_args()
     if args.impl == "reference":
         return _reference_arm(args)
@@ -238,7 +239,7 @@ def main() -> int:
         variable_update=args.variable_update, kungfu_option=args.kungfu_option,
         num_gpus=1 if kungfu else args.gpus, optimizer=args.optimizer,
         comm_impl=args.comm_impl, num_batches=args.steps, num_warmup_batches=warmup,
-        cuda_graph=bool(args.cuda_graph),
+        cuda_graph=None if args.cuda_graph < 0 else bool(args.cuda_graph),
         data_format="NHWC", **({"bucket_bytes": args.bucket_bytes} if args.bucket_bytes else {}))
     p = benchmark.setup(p)
     bench = benchmark.BenchmarkCNN(p)

@@ -497,24 +497,48 @@ class BenchmarkCNN:
         sequence number from a device counter that the captured step advances
         (P2PComm.enable_device_seq; checked on hardware against the eager step,
         tests/test_gpu_multi.py). KFB_MULTI_RANK_GRAPH=0 switches the multi-rank form off."""
-        if not (self.params.cuda_graph and self.device.type == "cuda" and
-                not getattr(self.input_source, "host_resident", False) and
-                not self.engine.auto_loss_scale):
+        want = self.params.cuda_graph
+        if want is False or self.device.type != "cuda" or \
+                os.environ.get("KFB_CUDA_GRAPH", "1") == "0":
+            return False
+        eng = self.engine
+        if eng.auto_loss_scale and not eng.device_ls:
+            return False                        # the host mirror reads the skip flag every step
+        if want is None and not self._graph_safe_to_freeze():
             return False
         if self.world <= 1:
             return True
         from .parallel.comm import P2PComm
-        eng = self.engine
         return (os.environ.get("KFB_MULTI_RANK_GRAPH", "1") != "0" and isinstance(self.comm, P2PComm)
                 and eng._can_overlap() and not eng.fused_push)
+
+    def _graph_safe_to_freeze(self) -> bool:
+        """Automatic mode only captures steps whose replay is exactly the eager step: dropout /
+        drop-path take their per-step mask offsets by value (a replay would repeat the mask),
+        and only the softmax cross-entropy head is known to be free of per-step host work."""
+        cached = getattr(self, "_graph_safe", None)
+        if cached is None:
+            g = getattr(self.executor, "graph", None)
+            cached = bool(g is not None and g.loss["kind"] == "softmax_xent" and
+                          not any(n.op in ("dropout", "drop_path", "lstm", "embedding")
+                                  for n in g.nodes))
+            self._graph_safe = cached
+        return cached
 
     def _step_graphed(self) -> None:
         ex, eng = self.executor, self.engine
         lr = eng.learning_rate(self.global_step, self._examples_per_step(),
                                self.dataset.num_examples_per_epoch("train"))
+        src = self.input_source
+        host = getattr(src, "host_resident", False) and hasattr(ex, "stage_inputs")
+        if host and ex.has_staged_inputs():
+            # the batch staged on the copy stream during the previous step moves into the input
+            # buffers the captured kernels read (device-to-device, ~0.1 % of the step)
+            ex.adopt_staged_inputs()
+        else:
+            ex.set_inputs(*src.next_batch())
         if getattr(self, "_graph", None) is None:
             eng.enable_dynamic_hyper()
-            ex.set_inputs(*self.input_source.next_batch())
             self._graph_warm = getattr(self, "_graph_warm", 0) + 1
             eng.push_dynamic_hyper(lr)
             if self._graph_warm <= 2:            # eager steps: lazy inits happen outside capture
@@ -524,6 +548,8 @@ class BenchmarkCNN:
                 ex.loss_backward(on_grads_ready=eng.on_grads_ready, **eng.loss_scale_kwargs())
                 eng.finish_step()
                 self.global_step += 1
+                if host:
+                    ex.stage_inputs(*src.next_batch())
                 return
             multi = self.world > 1
             counter = self.comm.enable_device_seq() if multi else None
@@ -532,8 +558,10 @@ class BenchmarkCNN:
                 self.comm.barrier()               # every rank starts capturing at the same step
             seq0 = self.comm.seq if multi else 0
             g = torch.cuda.CUDAGraph()
+            from .ops import native as _native
+            launches0 = _native.launch_count
             with torch.cuda.graph(g):
-                eng.begin_step(lr)
+                eng.begin_step(lr, push_dyn=False)
                 ex.forward(True)
                 ex.loss_backward(on_grads_ready=eng.on_grads_ready, **eng.loss_scale_kwargs())
                 eng.finish_step()
@@ -547,15 +575,21 @@ class BenchmarkCNN:
             if multi:
                 self.comm.seq = seq0              # nothing ran during capture
             eng.step_count -= 1                   # finish_step counted the captured (not run) step
+            self._graph_launches = _native.launch_count - launches0   # kernels per replay
+            _native.launch_count = launches0
             self._graph = g
             _log("Captured the training step in a CUDA graph")
         eng.push_dynamic_hyper(lr)
         self._last_lr = lr
         self._graph.replay()
+        from .ops import native as _native
+        _native.launch_count += getattr(self, "_graph_launches", 0)
         eng.step_count += 1                       # Adam's bias correction reads it (dyn[2])
         if self.world > 1:
             self.comm.graph_replayed(self._graph_collectives)
         self.global_step += 1
+        if host:
+            ex.stage_inputs(*src.next_batch())
 
     def _step(self, train: bool = True, backward: bool = True) -> None:
         """One step on this rank: inputs -> forward -> loss/backward -> exchange + update."""

@@ -397,6 +397,18 @@ class CudaExecutor:
     def has_staged_inputs(self) -> bool:
         return self._staged
 
+    def adopt_staged_inputs(self) -> None:
+        """CUDA-graph mode: the captured kernels read fixed input buffers, so the staged batch
+        is copied device-to-device into the current set instead of swapping the sets."""
+        b = 1 - self._cur
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self._ready[b])
+        for m, t in zip(self._in_sets[self._cur], self._in_sets[b]):
+            m.copy_(t, non_blocking=True)
+        self._free[b].record(cur)       # the back set may be overwritten once this copy ran
+        self._staged = False
+        self._bind_inputs(self._in_sets[self._cur])
+
     def use_staged_inputs(self) -> None:
         b = 1 - self._cur
         torch.cuda.current_stream(self.device).wait_event(self._ready[b])

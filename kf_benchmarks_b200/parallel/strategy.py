@@ -375,8 +375,9 @@ class UpdateEngine:
         native.call("set_hyper_dyn", ptr(self.dyn), f32(h.lr), f32(h.grad_scale), f32(h.adam_t),
                     i32(mask), self._s())
 
-    def begin_step(self, lr: float) -> None:
-        """Called before backward: arms the overlap scheduler."""
+    def begin_step(self, lr: float, push_dyn: bool = True) -> None:
+        """Called before backward: arms the overlap scheduler. ``push_dyn=False`` while a CUDA
+        graph is being captured (the per-step values are pushed before every replay instead)."""
         self._h = self._hyper(lr)
         if self.relaxed and self.cuda and getattr(self, "_relaxed_pending", False) and \
                 isinstance(self.comm, P2PComm):
@@ -389,7 +390,8 @@ class UpdateEngine:
             # the per-step values the update kernels read from device memory (the skip flag was
             # cleared by the previous kfb_loss_scale_update)
             self.enable_dynamic_hyper()
-            self.push_dynamic_hyper(lr)
+            if push_dyn:
+                self.push_dynamic_hyper(lr)
         elif self.cuda and self.auto_loss_scale:
             self.skip_flag.zero_()
 

@@ -209,7 +209,10 @@ _D.DEFINE_enum("comm_impl", "p2p", ("p2p", "p2p_fused", "nvls", "nccl", "gloo"),
                "torch.distributed NCCL + separate update (comparison baseline). gloo: CPU ranks.")
 _D.DEFINE_float("sma_alpha", 0.1, "Blend factor of SynchronousAveraging.")
 _D.DEFINE_integer("bucket_bytes", 8 << 20, "Target gradient bucket size for overlap.")
-_D.DEFINE_boolean("cuda_graph", False, "Capture the training step in a CUDA graph.")
+_D.DEFINE_boolean("cuda_graph", None,
+                  "Capture the training step in a CUDA graph and replay it. Unset = automatic: "
+                  "on whenever the step is a fixed kernel sequence (GPU, no dropout / drop-path "
+                  "whose masks must change per step); true / false force it.")
 _D.DEFINE_integer("ada_sgd_switch_step", 0, "ada_sgd: step at which SMA hands over to S-SGD.")
 
 # Reference flags that configure TF/cuDNN/XLA/TRT/MKL internals: accepted, no effect here.

@@ -215,8 +215,8 @@ def test_graphed_step_control_flow_with_two_ranks(monkeypatch):
         def push_dynamic_hyper(self, lr):
             self.pushed_t = self.step_count + 1
 
-        def begin_step(self, lr):
-            pass
+        def begin_step(self, lr, push_dyn=True):
+            self.begin_push = getattr(self, "begin_push", []) + [push_dyn]
 
         def on_grads_ready(self, lo, hi):
             pass
@@ -241,6 +241,7 @@ def test_graphed_step_control_flow_with_two_ranks(monkeypatch):
     assert launched == [1, 2, 3, 4, 5, 6, 7, 8, 9]                # 2 eager steps + the capture
     assert comm.seq == 6 + 4 * 3 and comm._dev_base == 4 * 3      # 4 replays moved the mirror
     assert b.engine.pushed_t == 6                                 # Adam's t of the 6th step
+    assert b.engine.begin_push == [True, True, False]             # no push inside the capture
     assert P2PComm.next_seq(comm) == 19 - 12                      # an eager call afterwards
 
 

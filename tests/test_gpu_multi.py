@@ -110,21 +110,23 @@ def test_fused_wgrad_reduce_scatter_is_bit_identical_to_the_pull_path(tmp_path, 
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
-@pytest.mark.parametrize("mode", [["--variable_update=replicated", "--num_gpus=2"],
-                                  ["--variable_update=kungfu", "--kungfu_option=sma"]])
+@pytest.mark.parametrize("mode", ["replicated", "replicated_compact", "kungfu_sma"])
 def test_nvls_all_reduce_matches_the_pull_kernels(tmp_path, mode):
     """--comm_impl=nvls (multimem.ld_reduce / multimem.st on multicast-bound arenas): replicas
-    bit-identical to each other, variables equal to the pull path up to summation order."""
+    bit-identical to each other, variables equal to the pull path up to summation order. With
+    the compact (fp16) gradient transfer the switch and the pull kernel may round a sum
+    differently by one fp16 ulp, which six training steps amplify: the comparison is looser."""
     import json
     import numpy as np
     outs = {}
-    kung = "kungfu" in mode[0]
+    kung = mode == "kungfu_sma"
+    compact = mode == "replicated_compact"
     for impl in ("p2p", "nvls"):
         d = tmp_path / impl
         d.mkdir()
         kw = dict(model="resnet20", data_name="cifar10", batch_size=32, use_fp16=True,
                   optimizer="momentum", init_learning_rate=0.05, num_batches=6,
-                  num_warmup_batches=0, comm_impl=impl,
+                  num_warmup_batches=0, comm_impl=impl, compact_gradient_transfer=compact,
                   variable_update="kungfu" if kung else "replicated",
                   num_gpus=1 if kung else 2)
         if kung:
@@ -138,7 +140,10 @@ def test_nvls_all_reduce_matches_the_pull_kernels(tmp_path, mode):
             assert np.array_equal(outs[impl][0], outs[impl][1])
     a, b = outs["p2p"][0], outs["nvls"][0]
     cos = float((a * b).sum() / (np.linalg.norm(a) * np.linalg.norm(b)))
-    assert cos > 0.9999 and np.abs(a - b).max() < 5e-2
+    if compact:
+        assert cos > 0.999
+    else:
+        assert cos > 0.9999 and np.abs(a - b).max() < 5e-2
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs at least 2 GPUs")
