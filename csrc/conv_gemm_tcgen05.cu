@@ -113,6 +113,14 @@ struct TileCfg {
   static constexpr int kMaxFit = (kSmemBudget - kFixedBytes) / kStageBytes;
   static constexpr int max_stages() { return kMaxFit > kMaxStages ? kMaxStages : kMaxFit; }
   static constexpr int smem_bytes(int stages) { return stages * kStageBytes + kFixedBytes; }
+  // accumulating TMA-store epilogue: two 4 KiB tiles per epilogue warp receive the old values
+  // of the output (TMA loads, prefetched while the MMA of the tile still runs)
+  static constexpr int kOldBytes = kEpiWarps * 2 * 4096;
+  static constexpr int kMaxFitAcc = (kSmemBudget - kFixedBytes - kOldBytes - 512) / kStageBytes;
+  static constexpr int max_stages_acc() { return kMaxFitAcc > kMaxStages ? kMaxStages : kMaxFitAcc; }
+  static constexpr int smem_bytes_acc(int stages) {
+    return stages * kStageBytes + kFixedBytes + kOldBytes + 512;
+  }
 };
 
 // Persistent kernel: one CTA per SM walks the tile list (m fastest, then n, then split).
@@ -123,7 +131,10 @@ struct TileCfg {
 // fallbacks are compiled out, which shrinks the kernel below the instruction-cache size.
 // TMA_ST = the TMA-store epilogue (fp16 output without accumulate / scatter / split-K): a
 // separate instantiation, so the other variants carry none of its code.
-template <int BN, int MODE, bool FAST, bool TMA_ST = false>
+// ACC (with TMA_ST) = out += result: the old 32 x 64 chunks arrive by TMA load into shared memory
+// (issued before the wait for the accumulator, so their latency hides behind the MMA), are added
+// in fp32 and the sum leaves through the same TMA store; replaces the per-lane read-modify-write.
+template <int BN, int MODE, bool FAST, bool TMA_ST = false, bool ACC = false>
 __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                         const __grid_constant__ CUtensorMap tmB,
@@ -147,6 +158,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
   uint64_t* tmem_full_bar = empty_bar + kMaxStages;   // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;       // [2]
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  uint64_t* old_bar = tmem_empty_bar + 4;  // [kEpiWarps][2] (ACC only; inside the 512 B block)
+  uint8_t* old_area = staging + Cfg::kStagingBytes + 1024;  // 1 KiB aligned (ACC only)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -163,6 +176,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full_bar[a], 1);
       mbar_init(&tmem_empty_bar[a], Cfg::kEpiWarps);  // one arrive per epilogue warp
+    }
+    if (ACC) {
+      for (int i = 0; i < 2 * Cfg::kEpiWarps; ++i) mbar_init(&old_bar[i], 1);
     }
     mbar_fence_init();
     fence_proxy_async_smem();
@@ -364,6 +380,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     constexpr bool tma_store = TMA_ST;
     bool store_pending = false;  // warp-uniform: a bulk store may still be reading stage_buf
     uint8_t* stage_buf = tma_store ? staging + epi * 4096 : staging + epi * (32 * kStageRowBytes);
+    uint8_t* old_buf = old_area + epi * 8192;          // [2][4096] (ACC only)
+    uint64_t* my_old_bar = old_bar + epi * 2;
+    uint32_t old_issued = 0, old_used = 0;             // chunk loads issued / consumed so far
     const int esize = p.out_fp32 ? 4 : 2;
     const int cols_per_chunk = 128 / esize;  // 32 (fp32) or 64 (fp16)
     // fused BN statistics: lane owns columns (2*lane, 2*lane+1) of each 64-wide chunk it handles
@@ -431,11 +450,31 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       }
       if (row >= p.M) row_off = -1;  // marks an invalid row
       const long long base = static_cast<long long>(z) * p.split_stride + col_mem0;
+      const int c_step = cols_per_chunk * kColSplit;
+      const int c_first = col_part * cols_per_chunk;
+      // ACC: number of chunks this warp handles in this tile; the first two old tiles are
+      // requested now, while the MMA of this tile may still be running
+      int my_chunks = 0;
+      auto issue_old = [&](int k) {
+        // chunk k of this tile -> old_buf[old_issued & 1]
+        if (lane == 0) {
+          uint64_t* bar = &my_old_bar[old_issued & 1];
+          mbar_expect_tx(bar, 4096);
+          tma_load_2d(old_buf + (old_issued & 1) * 4096, &tmC, bar, col_mem0 + c_first + k * c_step,
+                      m0 + quarter * 32);
+        }
+        ++old_issued;
+      };
+      // rows of this warp beyond M are never stored: nothing is loaded for them either
+      const bool acc_on = ACC && (m0 + quarter * 32 < p.M);
+      if (acc_on) {
+        const int lim = n_limit < BN ? n_limit : BN;
+        if (c_first < lim) my_chunks = (lim - c_first + c_step - 1) / c_step;
+        for (int k = 0; k < my_chunks && k < 2; ++k) issue_old(k);
+      }
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t tmem_acc = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
-      const int c_step = cols_per_chunk * kColSplit;
-      const int c_first = col_part * cols_per_chunk;
       if (c_first >= n_limit || c_first >= BN) {
         // nothing to read for this warp in this tile: release the accumulator right away
         if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
@@ -471,14 +510,29 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
               __syncwarp();
             }
             uint8_t* srow = stage_buf + lane * 128;
+            const uint8_t* orow = old_buf + (old_used & 1) * 4096 + lane * 128;
+            if (acc_on && h == 0) {
+              // the old values of this chunk have landed (phase = use count of the buffer / 2)
+              mbar_wait(&my_old_bar[old_used & 1], (old_used >> 1) & 1);
+            }
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
+              const int piece = h * 4 + (j >> 3);
+              if (acc_on) {
+                const uint4 o = *reinterpret_cast<const uint4*>(orow + ((piece ^ (lane & 7)) << 4));
+                const __half2* o2 = reinterpret_cast<const __half2*>(&o);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const float2 t = __half22float2(o2[q]);
+                  f[j + 2 * q] += t.x;
+                  f[j + 2 * q + 1] += t.y;
+                }
+              }
               uint4 u;
               u.x = pack_half2(f[j], f[j + 1]);
               u.y = pack_half2(f[j + 2], f[j + 3]);
               u.z = pack_half2(f[j + 4], f[j + 5]);
               u.w = pack_half2(f[j + 6], f[j + 7]);
-              const int piece = h * 4 + (j >> 3);
               *reinterpret_cast<uint4*>(srow + ((piece ^ (lane & 7)) << 4)) = u;
             }
             continue;
@@ -541,6 +595,13 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           // stores the 32-row x 64-column box; rows >= M and columns >= N are clipped by TMA
           fence_proxy_async_smem();
           __syncwarp();
+          if (acc_on) {
+            // every lane has read the old tile (ordered by the fence + syncwarp above): its
+            // buffer takes the old values of the chunk after next
+            const int k_done = (c0 - c_first) / c_step;
+            ++old_used;
+            if (k_done + 2 < my_chunks) issue_old(k_done + 2);
+          }
           if (lane == 0 && m0 + quarter * 32 < p.M) {
             tma_store_2d(&tmC, smem_u32(stage_buf), col_mem0 + c0, m0 + quarter * 32);
             bulk_commit_group();
@@ -865,6 +926,11 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           Cfg::smem_bytes(Cfg::max_stages())));
     }
+    if constexpr (MODE == DGRAD) {
+      KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE, true, true, true>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          Cfg::smem_bytes_acc(Cfg::max_stages_acc())));
+    }
     attr_set[dev] = true;
   }
   // every 16-byte piece of the output is full and aligned?
@@ -883,8 +949,14 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   }
   CUtensorMap tmC = tmA;  // placeholder, only dereferenced when p.tma_store is set
   p.tma_store = 0;
+  static int tma_acc_env = -1;   // KFB_TMA_ACC=0: accumulating outputs keep the per-lane epilogue
+  if (tma_acc_env < 0) {
+    const char* e = getenv("KFB_TMA_ACC");
+    tma_acc_env = (e != nullptr && *e != 0 && atoi(e) == 0) ? 0 : 1;
+  }
+  const bool acc_ok = !p.accumulate || (tma_acc_env == 1 && MODE == DGRAD);
   if (tma_store_env == 1 && fast && (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) &&
-      !p.out_fp32 && !p.accumulate && p.sc_P == 0 && tiles.z == 1 && p.push_n <= 1 &&
+      !p.out_fp32 && acc_ok && p.sc_P == 0 && tiles.z == 1 && p.push_n <= 1 &&
       p.N >= 64 && p.M >= 32 && (p.ldc % 8) == 0) {
     const uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
     const uint64_t strides[1] = {(uint64_t)p.ldc * 2};
@@ -900,7 +972,13 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   KFB_REQUIRE(total > 0 && total < (1ll << 31), "bad tile count %lld", total);
   const int ctas = total < sm_count() ? (int)total : sm_count();
   p.stats_rpn = (int)tiles.x < ctas ? (int)tiles.x : ctas;
-  if (fast && p.tma_store) {
+  if (fast && p.tma_store && p.accumulate) {
+    if constexpr (MODE == DGRAD) {
+      p.stages = Cfg::max_stages_acc();
+      gemm_tcgen05_kernel<BN, MODE, true, true, true>
+          <<<ctas, Cfg::kThreads, Cfg::smem_bytes_acc(p.stages), stream>>>(tmA, tmB, tmC, p);
+    }
+  } else if (fast && p.tma_store) {
     if constexpr (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) {
       gemm_tcgen05_kernel<BN, MODE, true, true>
           <<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(tmA, tmB, tmC, p);

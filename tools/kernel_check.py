@@ -66,6 +66,40 @@ case("fprop_7x7_s2_c8_k64", "fprop", n=2, h=64, w=64, c=8, k=64, r=7, s=7, strid
 case("fprop_big_3x3_c256", "fprop", n=32, h=14, w=14, c=256, k=256, r=3, s=3, stride=1, pad="SAME")
 case("wgrad_big_3x3_c256", "wgrad", n=32, h=14, w=14, c=256, k=256, r=3, s=3, stride=1, pad="SAME")
 case("dgrad_big_3x3_c256", "dgrad", n=32, h=14, w=14, c=256, k=256, r=3, s=3, stride=1, pad="SAME")
+# dgrad accumulating into an existing gradient: TMA-prefetched old tiles (unit stride) and the
+# per-lane read-modify-write together with the row scatter (strided)
+case("dgrad_acc_1x1_c256_k64", "dgrad", n=4, h=14, w=14, c=256, k=64, r=1, s=1, stride=1,
+     pad="SAME", acc=True)
+case("dgrad_acc_1x1_c512_k128_tail", "dgrad", n=3, h=13, w=13, c=512, k=128, r=1, s=1, stride=1,
+     pad="SAME", acc=True)
+case("dgrad_acc_3x3_c128_k128", "dgrad", n=2, h=28, w=28, c=128, k=128, r=3, s=3, stride=1,
+     pad="SAME", acc=True)
+case("dgrad_acc_1x1_s2_c256_k512_scatter", "dgrad", n=4, h=28, w=28, c=256, k=512, r=1, s=1,
+     stride=2, pad="VALID", acc=True)
+case("dgrad_acc_3x3_s2_c64_k64_scatter", "dgrad", n=2, h=56, w=56, c=64, k=64, r=3, s=3,
+     stride=2, pad="SAME_RESNET", acc=True)
+# headline shapes (ResNet-50, batch 256; `--headline` runs them, they need ~6 GB)
+HEADLINE = []
+
+
+def hcase(name, kind, **kw):
+    CASES[name] = (kind, kw)
+    HEADLINE.append(name)
+
+
+for mode in ("fprop", "dgrad", "wgrad"):
+    hcase(f"{mode}_head_1x1_56_c64_k256", mode, n=256, h=56, w=56, c=64, k=256, r=1, s=1,
+          stride=1, pad="SAME")
+    hcase(f"{mode}_head_3x3_56_c64_k64", mode, n=256, h=56, w=56, c=64, k=64, r=3, s=3, stride=1,
+          pad="SAME")
+    hcase(f"{mode}_head_1x1_s2_56_c256_k512", mode, n=256, h=56, w=56, c=256, k=512, r=1, s=1,
+          stride=2, pad="VALID")
+hcase("dgrad_head_acc_1x1_56_c256_k64", "dgrad", n=256, h=56, w=56, c=256, k=64, r=1, s=1,
+      stride=1, pad="SAME", acc=True)
+hcase("dgrad_head_acc_1x1_s2_56_c256_k512_scatter", "dgrad", n=256, h=56, w=56, c=256, k=512,
+      r=1, s=1, stride=2, pad="VALID", acc=True)
+hcase("stem_head_7x7_s2_c3_k64", "stem", n=256, h=224, w=224, c=3, k=64, r=7, s=7, stride=2,
+      pad="SAME_RESNET")
 
 
 def run_case(name: str) -> dict:
@@ -96,6 +130,27 @@ def run_case(name: str) -> dict:
         a, b = rnd(kw["k"], kw["m"]), rnd(kw["k"], kw["n"])
         out = gc.gemm_nt(a, b)
         ref = a.float().t() @ b.float()
+    elif kind == "stem":
+        # the tiny-C stem: explicit im2col (kfb_im2col_small_c) + GEMM, as the executor runs it
+        from kf_benchmarks_b200.ops import native
+        from kf_benchmarks_b200.ops.native import i32, ptr
+        n, h, w, c, k, r, s = (kw[x] for x in ("n", "h", "w", "c", "k", "r", "s"))
+        st = kw["stride"]
+        ph = gc.resolve_padding(kw["pad"], h, r, st)
+        pw = gc.resolve_padding(kw["pad"], w, s, st)
+        p_, q_ = (h + ph[0] + ph[1] - r) // st + 1, (w + pw[0] + pw[1] - s) // st + 1
+        x = rnd(n, h, w, c)
+        kpad = (r * s * c + 7) // 8 * 8
+        wt = rnd(k, kpad, scale=(r * s * c) ** -0.5)
+        wt[:, r * s * c:] = 0
+        col = torch.zeros(n * p_ * q_, kpad, device=dev, dtype=torch.float16)
+        native.call("im2col_small_c", ptr(x), ptr(col), i32(n), i32(h), i32(w), i32(c), i32(p_),
+                    i32(q_), i32(r), i32(s), i32(st), i32(st), i32(ph[0]), i32(pw[0]), i32(kpad),
+                    native.stream_ptr())
+        out = gc.gemm_tn(col, wt).reshape(n, p_, q_, k)
+        w_oihw = wt[:, :r * s * c].float().reshape(k, r, s, c).permute(0, 3, 1, 2)
+        xp = F.pad(x.float().permute(0, 3, 1, 2), (pw[0], pw[1], ph[0], ph[1]))
+        ref = F.conv2d(xp, w_oihw, stride=st).permute(0, 2, 3, 1)
     else:
         n, h, w, c, k, r, s = (kw[x] for x in ("n", "h", "w", "c", "k", "r", "s"))
         st = kw["stride"]
@@ -116,9 +171,15 @@ def run_case(name: str) -> dict:
             dy = rnd(n, d.p, d.q, k)
             y_ref.backward(dy.float().permute(0, 3, 1, 2))
             if kind == "dgrad":
-                out = gc.conv_dgrad(dy, wt, d)
                 gx = xp.grad[:, :, ph[0]:ph[0] + h, pw[0]:pw[0] + w]
                 ref = gx.permute(0, 2, 3, 1)
+                if kw.get("acc"):
+                    prev = rnd(n, h, w, c)
+                    out = prev.clone()
+                    gc.conv_dgrad(dy, wt, d, out=out, accumulate=True)
+                    ref = ref + prev.float()
+                else:
+                    out = gc.conv_dgrad(dy, wt, d)
             else:
                 out = gc.conv_wgrad(x, dy, d)
                 ref = wv.grad.permute(0, 2, 3, 1)
@@ -137,6 +198,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--case", help="comma-separated cases to run in this process")
     ap.add_argument("--filter", default="")
+    ap.add_argument("--headline", action="store_true",
+                    help="run the ResNet-50 batch-256 shapes (skipped by default: ~6 GB, slower)")
     ap.add_argument("--timeout", type=int, default=180)
     args = ap.parse_args()
     if args.case:
@@ -149,7 +212,8 @@ def main():
                 sys.exit(3)
             print("RESULT " + json.dumps(r), flush=True)
         return
-    todo = [n for n in CASES if not args.filter or args.filter in n]
+    todo = [n for n in CASES if (not args.filter or args.filter in n) and
+            ((n in HEADLINE) == bool(args.headline))]
     results = []
     while todo:
         t0 = time.time()
