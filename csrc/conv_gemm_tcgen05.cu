@@ -106,9 +106,12 @@ struct TileCfg {
   // Narrow tiles are picked for short-K, store-bound problems: give them eight epilogue warps
   // (two per TMEM lane quarter, interleaving column chunks); 256-wide tiles keep four and a
   // deeper smem ring instead.
-  static constexpr int kEpiWarps = BN == 256 ? 4 : 8;
+  static constexpr int kEpiWarps = 8;
   static constexpr int kThreads = 64 + 32 * kEpiWarps;
-  static constexpr int kStagingBytes = kEpiWarps * 32 * kStageRowBytes;
+  // per epilogue warp: one 32-row tile with padded rows (per-lane store epilogue), or two dense
+  // swizzled 4 KiB tiles (TMA-store epilogue: the store of chunk k reads one tile while chunk
+  // k+1 is packed into the other)
+  static constexpr int kStagingBytes = kEpiWarps * 8192;
   static constexpr int kFixedBytes = kStagingBytes + 1024 /*align*/ + 512 /*barriers*/;
   static constexpr int kMaxFit = (kSmemBudget - kFixedBytes) / kStageBytes;
   static constexpr int max_stages() { return kMaxFit > kMaxStages ? kMaxStages : kMaxFit; }
@@ -379,7 +382,10 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     constexpr bool kTmaStoreMode = TMA_ST;
     constexpr bool tma_store = TMA_ST;
     bool store_pending = false;  // warp-uniform: a bulk store may still be reading stage_buf
-    uint8_t* stage_buf = tma_store ? staging + epi * 4096 : staging + epi * (32 * kStageRowBytes);
+    uint8_t* const stage_base = staging + epi * 8192;
+    uint8_t* stage_buf = stage_base;
+    constexpr bool kTwoStaging = TMA_ST && !ACC;   // the accumulating variant keeps one tile
+    uint32_t chunk_no = 0;
     uint8_t* old_buf = old_area + epi * 8192;          // [2][4096] (ACC only)
     uint64_t* my_old_bar = old_bar + epi * 2;
     uint32_t old_issued = 0, old_used = 0;             // chunk loads issued / consumed so far
@@ -503,11 +509,17 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
           }
           if (kTmaStoreMode && tma_store) {
-            if (h == 0 && store_pending) {
-              // the previous chunk's bulk store must have read the staging tile before it is
-              // overwritten (the wait overlapped the TMEM load above)
-              if (lane == 0) bulk_wait_group_read_all();
-              __syncwarp();
+            if (h == 0) {
+              if (kTwoStaging) stage_buf = stage_base + (chunk_no & 1) * 4096;
+              ++chunk_no;
+              if (store_pending) {
+                // the bulk store that last read this staging tile (the previous chunk's, or with
+                // two tiles the one before it) must be done reading before it is overwritten
+                if (lane == 0) {
+                  if (kTwoStaging) bulk_wait_group_read_1(); else bulk_wait_group_read_all();
+                }
+                __syncwarp();
+              }
             }
             uint8_t* srow = stage_buf + lane * 128;
             const uint8_t* orow = old_buf + (old_used & 1) * 4096 + lane * 128;

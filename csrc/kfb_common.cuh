@@ -146,6 +146,10 @@ __device__ __forceinline__ void bulk_commit_group() {
 __device__ __forceinline__ void bulk_wait_group_read_all() {
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
+// all but the most recent of this thread's bulk groups have finished READING shared memory
+__device__ __forceinline__ void bulk_wait_group_read_1() {
+  asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+}
 // all of this thread's bulk groups are complete (their global writes are performed)
 __device__ __forceinline__ void bulk_wait_group_all() {
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
