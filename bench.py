@@ -126,22 +126,15 @@ def _timed_steps(bench, steps, torch, e2e: bool):
     return start.elapsed_time(end), wall, last
 
 
-def _standin_arm(args, torch) -> int:
-    """Same metric for the conventional PyTorch stand-in (cuDNN/cuBLAS autocast + NCCL +
-    torch.optim), see kf_benchmarks_b200/baseline/torch_standin.py. Labelled impl=standin: it is
-    neither the reference nor the product."""
+def _run_standin(args, torch, dev, rank, world, group=None):
+    """Times the PyTorch stand-in (kf_benchmarks_b200/baseline/torch_standin.py: cuDNN / cuBLAS
+    fp16 model + fp32 master, NCCL all-reduce of a flat fp16 gradient buffer, CUDA-graphed
+    forward + backward) on the same config with the same harness; returns a dict for rank 0.
+    It is neither the reference nor the product."""
     import torch.distributed as dist
-    from kf_benchmarks_b200 import benchmark, datasets, lr as lr_mod, params as params_lib
+    from kf_benchmarks_b200 import datasets, lr as lr_mod, params as params_lib
     from kf_benchmarks_b200.baseline.torch_standin import StandinTrainer
     from kf_benchmarks_b200.models import model_config
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", str(rank)))
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     kungfu = args.variable_update in ("kungfu", "horovod")
     p = params_lib.make_params(model=args.model, batch_size=args.batch_size, use_fp16=True,
                                variable_update=args.variable_update,
@@ -152,7 +145,7 @@ def _standin_arm(args, torch) -> int:
     model = model_config.get_model_config(args.model, ds, p)
     model.set_batch_size(args.batch_size)
     graph = model.build_graph(ds.num_classes, batch_size=args.batch_size)
-    tr = StandinTrainer(p, model, graph, ds.num_classes, dev, world, rank)
+    tr = StandinTrainer(p, model, graph, ds.num_classes, dev, world, rank, group=group)
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
     h = model.image_size
     images = (torch.randn(args.batch_size, h, h, 3, device=dev, generator=gen) * 60 + 127).half()
@@ -160,13 +153,13 @@ def _standin_arm(args, torch) -> int:
     warmup = max(args.warmup, 3)
     lr = lr_mod.get_learning_rate(p, 1000, ds.num_examples_per_epoch("train"), model,
                                   args.batch_size * (world if kungfu else args.gpus))
-    for _ in range(warmup + 5):  # cudnn.benchmark needs a few extra steps
+    for _ in range(warmup + 6):  # cudnn.benchmark, then graph capture, then replays
         tr.step(images, labels, lr)
 
     def sync():
         torch.cuda.synchronize(dev)
         if world > 1:
-            dist.barrier()
+            dist.barrier(group=group)
         torch.cuda.synchronize(dev)
     sync()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -179,25 +172,52 @@ def _standin_arm(args, torch) -> int:
     ms = e0.elapsed_time(e1)
     if world > 1:
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         ms = float(t.item())
+    gb = args.batch_size * world
+    return {"impl": "eager-graphed torch cuDNN/cuBLAS + NCCL stand-in - NOT the reference",
+            "value": gb * args.steps / (ms / 1e3), "unit": "images/sec",
+            "ms_per_step": ms / args.steps, "steps": args.steps, "n_gpus": world,
+            "final_loss": float(tr.last_loss)}
+
+
+def _standin_arm(args, torch) -> int:
+    """--impl standin: the stand-in alone, as its own JSON line."""
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    out = _run_standin(args, torch, dev, rank, world)
     if rank == 0:
-        gb = args.batch_size * world
-        print(json.dumps({
-            "impl": "standin", "metric": "ResNet-50 fp16 synthetic-ImageNet training images/sec "
-            "(device-timed, max over ranks)", "value": gb * args.steps / (ms / 1e3),
-            "unit": "images/sec", "n_gpus": world, "steps": args.steps, "warmup": warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-            "dtype": "fp16 autocast", "data": "synthetic",
-            "config": {"model": args.model, "global_batch": gb,
-                       "variable_update": args.variable_update, "optimizer": args.optimizer,
-                       "kungfu_option": args.kungfu_option if args.variable_update == "kungfu"
-                       else "",
-                       "note": "PyTorch cuDNN/cuBLAS + NCCL stand-in (not the reference)"},
-            "final_loss": float(tr.last_loss)}))
+        out.update({"metric": "ResNet-50 fp16 synthetic-ImageNet training images/sec "
+                              "(device-timed, max over ranks)", "higher_is_better": True,
+                    "scaling": "weak", "dtype": "fp16", "data": "synthetic",
+                    "warmup": max(args.warmup, 3),
+                    "config": {"model": args.model, "global_batch": args.batch_size * world,
+                               "variable_update": args.variable_update,
+                               "optimizer": args.optimizer}})
+        out["impl"] = "standin"
+        print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def _replica_checksums_equal(bench, torch):
+    """64-bit checksum of every rank's fp32 master weights; True when all ranks hold the same
+    bits (what the synchronous modes guarantee), None for the asynchronous ones."""
+    eng = bench.engine
+    if getattr(eng, "algo", "none") in ("pair", "sma", "ada", "none") and bench.world > 1:
+        return None
+    w = bench.store.w32
+    chk = int(w.view(torch.int32).to(torch.int64).sum().item())
+    sums = bench.comm.allgather_object(chk) if bench.world > 1 else [chk]
+    return all(s == sums[0] for s in sums)
 
 
 def main() -> int:
@@ -215,6 +235,8 @@ def main() -> int:
     ap.add_argument("--bucket_bytes", type=int, default=None,
                     help="gradient bucket size of the overlapped exchange (default: the flag's)")
     ap.add_argument("--no_e2e", action="store_true")
+    ap.add_argument("--no_standin", action="store_true",
+                    help="skip the same-box PyTorch stand-in that is timed after the product")
     ap.add_argument("--cuda_graph", type=int, default=-1,
                     help="1 / 0 force the CUDA-graph replay of the step on / off; -1 (default) is "
                          "the framework's automatic choice (on for ResNet-50)")
@@ -275,14 +297,29 @@ def main() -> int:
         e2e = {"value": global_batch * args.steps / (ms_e / 1e3), "unit": "images/sec",
                "h2d_bytes_per_step": src.bytes_per_step * n_ranks,
                "d2h_bytes_per_step": 32 * n_ranks, "ms_per_step": ms_e / args.steps}
+    replicas_equal = _replica_checksums_equal(bench, torch)
+    standin = None
+    if not args.no_standin:
+        # the same-box comparison point, timed after the product's own regions with the same
+        # harness (the reference itself cannot be installed here, see --impl reference)
+        try:
+            group = None
+            if n_ranks > 1:
+                import torch.distributed as dist
+                group = dist.new_group(backend="nccl")
+            standin = _run_standin(args, torch, bench.device, rank, n_ranks, group=group)
+        except Exception as e:  # the product's numbers stand on their own
+            standin = {"error": repr(e)[:300]}
     if rank == 0:
-        pub = _PUBLISHED.get(n_ranks)
         out = {
             "metric": "ResNet-50 fp16 synthetic-ImageNet training images/sec "
                       "(device-timed, max over ranks)",
             "value": value, "unit": "images/sec", "n_gpus": n_ranks, "steps": args.steps,
             "warmup": warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": (value / pub) if pub else None,
+            "scaling": "weak",
+            # BASELINE.json publishes no number for this config (the reference's only figures are
+            # RTX 3090, fp32, parameter_server with a nan loss: 416 / 713 img/s on 1 / 2 GPUs)
+            "vs_baseline": None,
             "dtype": "fp16", "data": "synthetic",
             "config": {"model": args.model, "global_batch": global_batch, "seq_len": None,
                        "image_size": bench.model.image_size,
@@ -293,9 +330,10 @@ def main() -> int:
                        "comm_impl": args.comm_impl if n_ranks > 1 else "none",
                        "l2_hygiene": "per-step working set (>5 GB activations) exceeds the "
                                      "126 MB L2; no explicit flush",
-                       "baseline_note": "vs_baseline divides by the reference's only published "
-                                        "numbers (RTX 3090, fp32, nan loss; BASELINE.md)"},
+                       "cuda_graph": bool(getattr(bench, "_graph", None) is not None),
+                       "published_context": _PUBLISHED},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "replica_checksum_equal": replicas_equal, "standin": standin,
             "final_loss": loss, "wall_s_timed": wall,
         }
         print(json.dumps(out))

@@ -32,6 +32,9 @@ import executor_check  # noqa: E402
     ("official_resnet18", "imagenet", 2, 0.9, 5e-3),
     ("ncf", "imagenet", 512, 0.999, 5e-3),             # embeddings + GMF/MLP + [1, z] softmax
     ("ssd300", "coco", 2, 0.9, None),                  # multibox loss on the head convs
+    ("vgg16", "imagenet", 2, 0.99, 5e-3),              # BASELINE config #4
+    ("alexnet", "imagenet", 4, 0.99, 5e-3),
+    ("overfeat", "imagenet", 2, 0.99, 5e-3),
 ])
 def test_executor_matches_reference(model, data, batch, min_cos, max_logit_rel):
     r = executor_check.compare(model, data, batch)
@@ -40,6 +43,21 @@ def test_executor_matches_reference(model, data, batch, min_cos, max_logit_rel):
     assert r["grad_cosine"] > min_cos, r
     assert abs(r["loss_gpu"] - r["loss_ref"]) < 0.02 * abs(r["loss_ref"]), r
     assert r["moving_stats_rel"] < 2e-2, r
+
+
+@pytest.mark.parametrize("model,batch", [("resnet50", 32), ("inception3", 16), ("vgg16", 8),
+                                         ("inception4", 8), ("overfeat", 4), ("alexnet", 8)])
+def test_every_node_matches_the_oracle_teacher_forced(model, batch):
+    """tools/node_check.py: every node of the headline networks, forward and backward, gets the
+    oracle's own fp16-rounded inputs and output gradient and must reproduce the oracle's output,
+    input gradients and parameter gradients to 1e-2 of their maximum - no layer-to-layer
+    amplification, so the loose whole-network thresholds above are not the only line of defence.
+    (Inception-v4 has no whole-network case at all: at a batch that fits a test, two oracles -
+    fp32 and fp16-storage PyTorch - disagree on its gradient direction.)"""
+    import node_check
+    r = node_check.check(model, "imagenet", batch)
+    assert r["failed"] == 0, r
+    assert r["worst_fwd"] < 1e-2 and r["worst_dgrad"] < 1e-2 and r["worst_wgrad"] < 1e-2, r
 
 
 @pytest.mark.parametrize("data,batch,size,min_cos", [("cifar10", 8, None, 0.97),
