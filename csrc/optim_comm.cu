@@ -56,7 +56,15 @@ struct HyperParams {
   float grad_scale;    // multiplies the (reduced) gradient: 1/loss_scale, 1/N for means
   float clip;          // elementwise clip (<= 0: off)
   float adam_t;        // step count for Adam bias correction
+  // optional: one byte per 128-element arena block (slots are 128-aligned), 0 = this block is
+  // excluded from the L2 term (the SSD model decays no batch-norm variable,
+  // T/models/ssd_model.py:91-94); indexed like the kernel's element index
+  const unsigned char* decay_mask;
 };
+
+__device__ __forceinline__ float decay_at(const HyperParams& h, long long i) {
+  return (h.decay_mask != nullptr && h.decay_mask[i >> 7] == 0) ? 0.f : h.weight_decay;
+}
 
 // dyn (optional, device memory): {lr, grad_scale, adam_t, unused}. Lets a captured CUDA graph
 // see per-step values.
@@ -70,7 +78,7 @@ __device__ __forceinline__ void resolve_dyn(HyperParams& h, const float* dyn) {
 
 __device__ __forceinline__ float apply_update(const HyperParams& h, float w, float g_raw, float* m,
                                               float* v, long long i) {
-  float g = g_raw * h.grad_scale + h.weight_decay * w;
+  float g = g_raw * h.grad_scale + decay_at(h, i) * w;
   if (h.clip > 0.f) g = fminf(fmaxf(g, -h.clip), h.clip);
   switch (h.opt) {
     case 0:
@@ -123,9 +131,10 @@ __device__ __forceinline__ void apply_update4(const HyperParams& h, float* __res
     const float4 t = *reinterpret_cast<const float4*>(v + i);
     vv[0] = t.x; vv[1] = t.y; vv[2] = t.z; vv[3] = t.w;
   }
+  const float wd = decay_at(h, i);
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    float g = gv[k] * h.grad_scale + h.weight_decay * wv[k];
+    float g = gv[k] * h.grad_scale + wd * wv[k];
     if (h.clip > 0.f) g = fminf(fmaxf(g, -h.clip), h.clip);
     if (h.opt == 0) {
       wv[k] -= h.lr * g;
@@ -172,6 +181,29 @@ __global__ void __launch_bounds__(256)
     apply_update4(h, w, *reinterpret_cast<const float4*>(g + i), m, v, w16, i, nullptr, 0.f);
   for (long long i = n4 + tid; i < n; i += nthreads) {
     const float nw = apply_update(h, w[i], g[i], m, v, i);
+    w[i] = nw;
+    if (w16 != nullptr) w16[i] = __float2half_rn(nw);
+  }
+}
+
+// SMA applied from a local copy of the averaged model: w <- (1-a) w + a avg, then the local
+// gradient step (the average was all-reduced on the exchange stream while backward ran).
+__global__ void __launch_bounds__(256)
+    optimizer_step_blend_kernel(float* __restrict__ w, const float* __restrict__ avg,
+                                const float* __restrict__ g, float* __restrict__ m,
+                                float* __restrict__ v, __half* __restrict__ w16, long long n,
+                                HyperParams h, const float* __restrict__ dyn, float alpha) {
+  resolve_dyn(h, dyn);
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  const long long n4 = n & ~3ll;
+  for (long long i = tid * 4; i < n4; i += nthreads * 4) {
+    const float4 a4 = *reinterpret_cast<const float4*>(avg + i);
+    apply_update4(h, w, *reinterpret_cast<const float4*>(g + i), m, v, w16, i, &a4, alpha);
+  }
+  for (long long i = n4 + tid; i < n; i += nthreads) {
+    const float blended = (1.f - alpha) * w[i] + alpha * avg[i];
+    const float nw = apply_update(h, blended, g[i], m, v, i);
     w[i] = nw;
     if (w16 != nullptr) w16[i] = __float2half_rn(nw);
   }
@@ -622,12 +654,12 @@ __device__ __forceinline__ void multimem_st_vec(void* mc, const uint4& q) {
 
 // One optimizer step on E consecutive elements held in registers.
 template <int E>
-__device__ __forceinline__ void update_regs(const HyperParams& h, float (&wv)[E],
+__device__ __forceinline__ void update_regs(const HyperParams& h, float wd, float (&wv)[E],
                                             const float (&gv)[E], float (&mv)[E],
                                             float (&vv)[E]) {
 #pragma unroll
   for (int k = 0; k < E; ++k) {
-    float g = gv[k] * h.grad_scale + h.weight_decay * wv[k];
+    float g = gv[k] * h.grad_scale + wd * wv[k];
     if (h.clip > 0.f) g = fminf(fmaxf(g, -h.clip), h.clip);
     if (h.opt == 0) {
       wv[k] -= h.lr * g;
@@ -801,9 +833,9 @@ __global__ void __launch_bounds__(512)
 #pragma unroll
         for (int k = 0; k < E; ++k)
           wv[u][k] = (1.f - a.sma_alpha) * wv[u][k] + a.sma_alpha * r[k];
-        update_regs<E>(h, wv[u], gl[u], mv[u], vv[u]);
+        update_regs<E>(h, decay_at(h, i[u]), wv[u], gl[u], mv[u], vv[u]);
       } else {
-        update_regs<E>(h, wv[u], r, mv[u], vv[u]);
+        update_regs<E>(h, decay_at(h, i[u]), wv[u], r, mv[u], vv[u]);
       }
       if (!ok[u]) continue;
       store_f32<E>(a.w + i[u], wv[u]);
@@ -850,7 +882,31 @@ __global__ void __launch_bounds__(512)
   const float* src = c.src[root];
   const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = offset + tid; i < offset + count; i += nthreads) {
+  // 16-byte peer loads, four in flight per thread (offset is 4-aligned; scalar tail)
+  const long long end = offset + count, end4 = offset + (count & ~3ll);
+  const bool vec = (offset & 3) == 0;
+  constexpr int kU = 4;
+  for (long long i0 = offset + tid * 4; vec && i0 < end4; i0 += nthreads * 4 * kU) {
+    float4 x[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * nthreads * 4;
+      if (i < end4) x[u] = *reinterpret_cast<const float4*>(src + i);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const long long i = i0 + u * nthreads * 4;
+      if (i >= end4) continue;
+      if (c.rank != root) *reinterpret_cast<float4*>(dst + i) = x[u];
+      if (dst16 != nullptr) {
+        uint2 q;
+        q.x = pack_half2(x[u].x, x[u].y);
+        q.y = pack_half2(x[u].z, x[u].w);
+        *reinterpret_cast<uint2*>(dst16 + i) = q;
+      }
+    }
+  }
+  for (long long i = (vec ? end4 : offset) + tid; i < end; i += nthreads) {
     const float x = src[i];
     if (c.rank != root) dst[i] = x;
     if (dst16 != nullptr) dst16[i] = __float2half_rn(x);
@@ -872,7 +928,10 @@ __global__ void device_barrier_kernel(PeerCtx c, uint32_t seq) {
 // T/variable_mgr.py:321-332). Each rank posts its value into every page, then reads all.
 __global__ void flag_or_kernel(PeerCtx c, uint32_t seq, int* __restrict__ flag) {
   seq += seq_offset(c);
-  constexpr int kPostWord = kCounterWord + 8;  // [src_rank] words after the arrival counters
+  // [parity][src_rank] words after the arrival counters: two sets, chosen by the parity of the
+  // call's sequence number, so that a rank which already entered the next flag_or cannot
+  // overwrite a value a slower rank has not read yet
+  const int kPostWord = kCounterWord + 8 + static_cast<int>(seq & 1u) * kMaxRanks;
   if (threadIdx.x < c.nranks) {
     *reinterpret_cast<volatile uint32_t*>(c.flags[threadIdx.x] + kPostWord + c.rank) =
         static_cast<uint32_t>(*flag != 0);
@@ -902,35 +961,103 @@ struct PairCtx {
   long long stride;            // floats per slot
 };
 
+// Grid-wide barrier of a fully resident grid (the host clamps the grid): sync[0] counts
+// arrivals, sync[1] is the generation.
+__device__ __forceinline__ void pair_grid_barrier(unsigned* sync) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned gen = *reinterpret_cast<volatile unsigned*>(sync + 1);
+    __threadfence();
+    if (atomicAdd(sync, 1u) == gridDim.x - 1) {
+      atomicExch(sync, 0u);
+      __threadfence();
+      atomicAdd(sync + 1, 1u);
+    } else {
+      const uint64_t t0 = globaltimer_ns();
+      while (*reinterpret_cast<volatile unsigned*>(sync + 1) == gen) {
+        if (globaltimer_ns() - t0 > 20000000000ull) {
+          printf("kfb: pair_average grid barrier timeout (block %d)\n", blockIdx.x);
+          __trap();
+        }
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// Phase A pulls the peer's newest complete snapshot into a local buffer with 16-byte loads and
+// validates it afterwards (seqlock: the slot can only have been overwritten if the writer began
+// version k+3 meanwhile); a torn pull is REPEATED with the then-newest version (up to three
+// times) before anything is blended, so the model never mixes half-old and half-new weights.
+// Phase B blends from the local copy, applies the local gradient and publishes.
+// sync: {barrier count, barrier generation, retry flag, -}; torn_counter counts repeated pulls.
 __global__ void __launch_bounds__(512)
     pair_average_kernel(PairCtx pc, long long count, float* __restrict__ w,
                         const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                         __half* __restrict__ w16, HyperParams h, const float* __restrict__ dyn,
-                        uint32_t my_next_version, int has_peer, int* __restrict__ torn_counter) {
+                        uint32_t my_next_version, int has_peer, int* __restrict__ torn_counter,
+                        float* __restrict__ pulled, unsigned* __restrict__ sync) {
   resolve_dyn(h, dyn);
   __shared__ uint32_t s_ver;
-  if (threadIdx.x == 0) s_ver = has_peer ? ld_acquire_sys(pc.peer_ver + 1) : 0u;
-  __syncthreads();
-  const uint32_t ver = s_ver;
-  const bool blend = has_peer && ver > 0;  // version 0 = nothing published yet
-  const float* peer = pc.peer_pub + static_cast<long long>(ver % 3u) * pc.stride;
-  float* mine = pc.my_pub + static_cast<long long>(my_next_version % 3u) * pc.stride;
   const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  const long long n4 = count & ~3ll;
+  bool blend = false;
+  for (int attempt = 0; has_peer && attempt < 3; ++attempt) {
+    if (threadIdx.x == 0) s_ver = ld_acquire_sys(pc.peer_ver + 1);
+    __syncthreads();
+    const uint32_t ver = s_ver;
+    if (ver == 0) break;  // nothing published yet
+    const float* peer = pc.peer_pub + static_cast<long long>(ver % 3u) * pc.stride;
+    constexpr int kU = 4;
+    for (long long i0 = tid * 4; i0 < n4; i0 += nthreads * 4 * kU) {
+      float4 x[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = i0 + u * nthreads * 4;
+        if (i < n4) x[u] = *reinterpret_cast<const float4*>(peer + i);
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = i0 + u * nthreads * 4;
+        if (i < n4) *reinterpret_cast<float4*>(pulled + i) = x[u];
+      }
+    }
+    for (long long i = n4 + tid; i < count; i += nthreads) pulled[i] = peer[i];
+    // every block validates its own reads; one torn block makes the whole grid pull again
+    if (threadIdx.x == 0 && ld_acquire_sys(pc.peer_ver) >= ver + 3u) atomicExch(sync + 2, 1u);
+    pair_grid_barrier(sync);
+    const bool torn = *reinterpret_cast<volatile unsigned*>(sync + 2) != 0;
+    pair_grid_barrier(sync);               // everyone has read the flag
+    if (blockIdx.x == 0 && threadIdx.x == 0 && torn) {
+      atomicExch(sync + 2, 0u);
+      atomicAdd(torn_counter, 1);
+    }
+    if (!torn) {
+      blend = true;
+      break;
+    }
+    pair_grid_barrier(sync);               // flag cleared before the next attempt may set it
+  }
+  float* mine = pc.my_pub + static_cast<long long>(my_next_version % 3u) * pc.stride;
   // every block announces `begin` before its own first store into the slot
   if (threadIdx.x == 0) st_release_sys(pc.my_ver, my_next_version);
   __syncthreads();
-  for (long long i = tid; i < count; i += nthreads) {
+  for (long long i = tid * 4; i < n4; i += nthreads * 4) {
+    float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (blend) p4 = __ldcg(reinterpret_cast<const float4*>(pulled + i));
+    apply_update4(h, w, *reinterpret_cast<const float4*>(g + i), m, v, w16, i,
+                  blend ? &p4 : nullptr, 0.5f);
+    *reinterpret_cast<float4*>(mine + i) = *reinterpret_cast<const float4*>(w + i);
+  }
+  for (long long i = n4 + tid; i < count; i += nthreads) {
     float wi = w[i];
-    if (blend) wi = 0.5f * (wi + peer[i]);
+    if (blend) wi = 0.5f * (wi + pulled[i]);
     const float nw = apply_update(h, wi, g[i], m, v, i);
     w[i] = nw;
     if (w16 != nullptr) w16[i] = __float2half_rn(nw);
     mine[i] = nw;
-  }
-  if (blend && threadIdx.x == 0) {
-    const uint32_t begin_now = ld_acquire_sys(pc.peer_ver);
-    if (begin_now >= ver + 3u) atomicAdd(torn_counter, 1);
   }
   // publish: all blocks' stores must be visible before `end` moves
   __threadfence_system();
@@ -967,6 +1094,21 @@ static int fill_peer_ctx(PeerCtx* c, int rank, int nranks, void* const* src, voi
   return 0;
 }
 
+// The collectives publish a flag only after every CTA of the grid has arrived and then spin on
+// flags of the same launch: the whole grid must be resident at once. Clamps a requested CTA
+// count to what the device can hold for this kernel (queried, not assumed).
+template <typename K>
+static int clamp_resident(K kernel, int threads, int blocks) {
+  int dev = 0, sms = 0, per_sm = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess ||
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess ||
+      sms <= 0 || per_sm <= 0)
+    return blocks < 1 ? 1 : (blocks > 64 ? 64 : blocks);
+  const int cap = sms * per_sm;
+  return blocks < 1 ? 1 : (blocks > cap ? cap : blocks);
+}
+
 static HyperParams make_hyper(const kfb_hyper* hp) {
   HyperParams h;
   h.opt = hp->opt;
@@ -978,6 +1120,7 @@ static HyperParams make_hyper(const kfb_hyper* hp) {
   h.grad_scale = hp->grad_scale;
   h.clip = hp->clip;
   h.adam_t = hp->adam_t;
+  h.decay_mask = hp->decay_mask;
   return h;
 }
 
@@ -1028,6 +1171,19 @@ extern "C" int kfb_optimizer_step(float* w, const float* g, float* m, float* v, 
   return 0;
 }
 
+extern "C" int kfb_optimizer_step_blend(float* w, const float* avg, const float* g, float* m,
+                                        float* v, void* w16, long long n, const kfb_hyper* hp,
+                                        const float* dyn, float alpha, void* stream) {
+  KFB_REQUIRE(hp != nullptr && avg != nullptr, "optimizer_step_blend: null argument");
+  long long blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  optimizer_step_blend_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      w, avg, g, m, v, (__half*)w16, n, make_hyper(hp), dyn, alpha);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int kfb_check_finite(const float* g, long long n, int* flag, void* stream) {
   long long blocks = (n + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
@@ -1074,7 +1230,7 @@ extern "C" int kfb_allreduce_update(int mode, int rank, int nranks, void* const*
     blocks = forced > 0 ? forced
                         : (count >= (4ll << 20) ? 96 : (count >= (1ll << 20) ? 64 : 32));
   }
-  if (blocks > 148) blocks = 148;
+  blocks = clamp_resident(allreduce_update_kernel<0>, 512, blocks);
   cudaStream_t st = (cudaStream_t)stream;
   // mode 2: reduce only - the sum lands in every rank's `reduced` buffer and is applied later
   // (variable_consistency=relaxed: one-step-stale gradients, T/batch_allreduce.py:353-388)
@@ -1116,7 +1272,7 @@ extern "C" int kfb_allreduce_update_nvls(int mode, int rank, int nranks, const v
     // the switch does the adds: fewer CTAs than the pull kernel saturate the links
     blocks = count >= (4ll << 20) ? 64 : (count >= (1ll << 20) ? 48 : 24);
   }
-  if (blocks > 148) blocks = 148;
+  blocks = clamp_resident(allreduce_update_nvls_kernel<0>, 512, blocks);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 1)
     allreduce_update_nvls_kernel<1><<<blocks, 512, 0, st>>>(
@@ -1148,7 +1304,8 @@ extern "C" int kfb_allreduce_update2(int mode, int rank, int nranks, void* const
   KFB_REQUIRE(offset % 8 == 0 && count % 8 == 0,
               "allreduce_update2: offset (%lld) and count (%lld) must be multiples of 8", offset,
               count);
-  KFB_REQUIRE(!(half && mode == 1), "allreduce_update2: SMA averages the fp32 model");
+  KFB_REQUIRE(!(half && (mode == 1 || mode == 3)),
+              "allreduce_update2: SMA averages the fp32 model");
   const bool nvls = src_mc != nullptr;
   KFB_REQUIRE(nvls ? reduced_mc != nullptr : (src != nullptr && reduced != nullptr),
               "allreduce_update2: incomplete %s addresses", nvls ? "multicast" : "peer");
@@ -1173,7 +1330,7 @@ extern "C" int kfb_allreduce_update2(int mode, int rank, int nranks, void* const
   a.dyn = dyn;
   a.skip_flag = skip_flag;
   a.sma_alpha = sma_alpha;
-  a.reduce_only = mode == 2 ? 1 : 0;
+  a.reduce_only = (mode == 2 || mode == 3) ? 1 : 0;   // 3: average of the sources only (SMA)
   if (blocks <= 0) {
     static const int forced = [] {
       const char* e = getenv("KFB_AR_BLOCKS");
@@ -1183,7 +1340,7 @@ extern "C" int kfb_allreduce_update2(int mode, int rank, int nranks, void* const
     blocks = forced > 0 ? forced
                         : (count >= (4ll << 20) ? 96 : (count >= (1ll << 20) ? 64 : 32));
   }
-  if (blocks > 148) blocks = 148;
+  blocks = clamp_resident(allreduce_update2_kernel<0, false, true>, 512, blocks);
   cudaStream_t st = (cudaStream_t)stream;
   if (half && cast_from != nullptr) {
     KFB_REQUIRE(cast_to != nullptr, "allreduce_update2: cast_to missing");
@@ -1196,7 +1353,7 @@ extern "C" int kfb_allreduce_update2(int mode, int rank, int nranks, void* const
   const HyperParams h = make_hyper(hp);
 #define KFB_AR2(MODE, NVLS, HALF) \
   allreduce_update2_kernel<MODE, NVLS, HALF><<<blocks, 512, 0, st>>>(c, a, h)
-  if (mode == 1) {
+  if (mode == 1 || mode == 3) {
     if (nvls) KFB_AR2(1, true, false); else KFB_AR2(1, false, false);
   } else if (half) {
     if (nvls) KFB_AR2(0, true, true); else KFB_AR2(0, false, true);
@@ -1228,7 +1385,7 @@ extern "C" int kfb_allreduce_update_staged(int rank, int nranks, void* const* re
     blocks = static_cast<int>((count / 4 + 511) / 512);
     if (blocks < 8) blocks = 8;
   }
-  if (blocks > 148) blocks = 148;
+  blocks = clamp_resident(allreduce_update_kernel<0>, 512, blocks);
   allreduce_update_kernel<0><<<blocks, 512, 0, (cudaStream_t)stream>>>(
       c, offset, count, seq, w, nullptr, m, v, (__half*)w16, make_hyper(hp), dyn, skip_flag, 0.f,
       0, stage, stage_stride);
@@ -1281,6 +1438,7 @@ extern "C" int kfb_broadcast_pull(int rank, int nranks, void* const* src, void* 
   PeerCtx c;
   if (fill_peer_ctx(&c, rank, nranks, src, nullptr, flags)) return 2;
   if (blocks <= 0) blocks = 64;
+  blocks = clamp_resident(broadcast_pull_kernel, 512, blocks);
   broadcast_pull_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(c, root, offset, count, seq,
                                                                   dst, (__half*)dst16);
   KFB_CHECK_CUDA(cudaGetLastError());
@@ -1310,8 +1468,11 @@ extern "C" int kfb_pair_average_update(const float* peer_pub, const unsigned* pe
                                        long long count, float* w, const float* g, float* m,
                                        float* v, void* w16, const kfb_hyper* hp, const float* dyn,
                                        unsigned my_next_version, int has_peer, int* torn_counter,
-                                       int blocks, void* stream) {
+                                       float* pull_buf, unsigned* sync, int blocks,
+                                       void* stream) {
   KFB_REQUIRE(hp != nullptr, "pair_average_update: null hyper");
+  KFB_REQUIRE(!has_peer || (pull_buf != nullptr && sync != nullptr),
+              "pair_average_update: needs the pull buffer and four zeroed sync words");
   PairCtx pc;
   pc.peer_pub = peer_pub;
   pc.peer_ver = peer_ver;
@@ -1319,9 +1480,10 @@ extern "C" int kfb_pair_average_update(const float* peer_pub, const unsigned* pe
   pc.my_ver = my_ver;
   pc.stride = stride;
   if (blocks <= 0) blocks = 64;
+  blocks = clamp_resident(pair_average_kernel, 512, blocks);
   pair_average_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(
       pc, count, w, g, m, v, (__half*)w16, make_hyper(hp), dyn, my_next_version, has_peer,
-      torn_counter);
+      torn_counter, pull_buf, sync);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -224,12 +224,22 @@ typedef struct {
   float grad_scale;   /* multiplies the reduced gradient (1/loss_scale, 1/N for mean modes) */
   float clip;         /* elementwise clip_by_value bound, <= 0 disables */
   float adam_t;       /* step count for Adam bias correction */
+  /* optional (device): one byte per 128-element block of the arena range the call covers, 0 =
+   * no L2 term for that block (T/models/ssd_model.py:91-94: batch-norm variables are not
+   * decayed); NULL = every variable is decayed */
+  const unsigned char* decay_mask;
 } kfb_hyper;
 
 /* Fused optimizer over a flat arena; dyn (device, optional) = {lr, grad_scale, adam_t, -}
  * overrides the by-value fields; skip_flag (device, optional) != 0 skips the update. */
 int kfb_optimizer_step(float* w, const float* g, float* m, float* v, void* w16, long long n,
                        const kfb_hyper* hp, const float* dyn, const int* skip_flag, void* stream);
+/* SynchronousAveraging from a local copy of the averaged model (kfb_allreduce_update2 mode 3
+ * produced it on the exchange stream during backward): w <- (1-alpha) w + alpha avg, then the
+ * local gradient step. T/benchmark_cnn.py:1199-1201. */
+int kfb_optimizer_step_blend(float* w, const float* avg, const float* g, float* m, float* v,
+                             void* w16, long long n, const kfb_hyper* hp, const float* dyn,
+                             float alpha, void* stream);
 int kfb_check_finite(const float* g, long long n, int* flag, void* stream);
 /* dyn[i] <- the argument for every bit i of `mask` (lr, grad_scale, adam_t), from a one-thread
  * kernel on `stream`: per-step values for captured graphs / device-resident loss scaling without
@@ -272,8 +282,10 @@ int kfb_allreduce_update_nvls(int mode, int rank, int nranks, const void* src_mc
                               float sma_alpha, int blocks, void* stream);
 /* Second generation of the two entry points above, one kernel template for both forms. Pull
  * form: src / reduced = per-rank addresses, src_mc = reduced_mc = NULL. NVLS form: src_mc /
- * reduced_mc = multicast aliases (src / reduced may be NULL). half = 1 is the compact gradient
- * transfer of the reference (--compact_gradient_transfer: fp16 on the wire whenever use_fp16,
+ * reduced_mc = multicast aliases (src / reduced may be NULL). Modes: 0 gradients + optimizer,
+ * 1 SMA in one kernel, 2 reduce only (sum), 3 average only (the SMA weight exchange launched at
+ * the start of the step; kfb_optimizer_step_blend applies it after backward). half = 1 is the
+ * compact gradient transfer of the reference (--compact_gradient_transfer: fp16 whenever use_fp16,
  * T/variable_mgr.py:311-313, T/batch_allreduce.py:429-453): sources and landing buffers hold
  * fp16, the sum is taken in fp32; with cast_from / cast_to this rank's fp32 gradients of the
  * range are first copied as fp16 into its source arena on the same stream. offset and count
@@ -304,12 +316,17 @@ int kfb_broadcast_pull(int rank, int nranks, void* const* src, void* const* flag
                        int blocks, void* stream);
 int kfb_device_barrier(int rank, int nranks, void* const* flags, unsigned seq, void* stream);
 int kfb_flag_or(int rank, int nranks, void* const* flags, unsigned seq, int* flag, void* stream);
-/* PairAveraging (AD-PSGD): blend with one peer's published model, local step, publish. */
+/* PairAveraging (AD-PSGD, T/benchmark_cnn.py:1196-1198): pull one peer's newest published model
+ * into `pull_buf` (count floats, local) with 16-byte NVLink loads, validate the pull against the
+ * peer's version words and repeat it (up to three times; torn_counter counts the repeats) if the
+ * peer overwrote the slot meanwhile, then blend 1/2, apply the local gradient and publish.
+ * `sync`: four zero-initialised words owned by the caller (grid barrier + retry flag). */
 int kfb_pair_average_update(const float* peer_pub, const unsigned* peer_ver, float* my_pub,
                             unsigned* my_ver, long long stride, long long count, float* w,
                             const float* g, float* m, float* v, void* w16, const kfb_hyper* hp,
                             const float* dyn, unsigned my_next_version, int has_peer,
-                            int* torn_counter, int blocks, void* stream);
+                            int* torn_counter, float* pull_buf, unsigned* sync, int blocks,
+                            void* stream);
 
 /* Symmetric memory over CUDA IPC (cudaMalloc'd, zero-filled). */
 int kfb_symm_alloc(long long bytes, void** out);

@@ -784,8 +784,11 @@ class BenchmarkCNN:
         p = self.params
         if p.loss_type_to_report == "base_loss" or not p.weight_decay or p.forward_only:
             return base_loss
-        w = self.store.w32
-        l2 = 0.5 * float((w.double() ** 2).sum().item())
+        w = self.store.w32.double() ** 2
+        mask = getattr(self.engine, "decay_mask", None)
+        if mask is not None:        # variables the model keeps out of the L2 term (SSD: BN)
+            w = w * mask.to(w.dtype).repeat_interleave(128)[:w.numel()]
+        l2 = 0.5 * float(w.sum().item())
         return base_loss + p.weight_decay * l2
 
     def _sync(self) -> None:

@@ -69,6 +69,13 @@ class Model:
     def get_fp16_loss_scale(self):
         return self.fp16_loss_scale
 
+    def l2_decay_filter(self, var_name: str) -> bool:
+        """Whether variable ``var_name`` takes part in the L2 (weight decay) term. The default
+        decays every trainable variable (T/benchmark_cnn.py:3068-3099); models override it the
+        way the reference overrides ``custom_l2_loss`` (T/models/model.py:115-131)."""
+        del var_name
+        return True
+
     def get_learning_rate(self, global_step: int, batch_size: int) -> float:
         del global_step, batch_size
         return self.learning_rate

@@ -140,6 +140,10 @@ class SSD300Model(model.CNNModel):
             base_lr = self.learning_rate / self.params.num_gpus
         return base_lr * (batch_size / self.base_lr_batch_size)
 
+    def l2_decay_filter(self, var_name: str) -> bool:
+        """T/models/ssd_model.py:91-94: no variable whose name contains 'batchnorm' is decayed."""
+        return "batchnorm" not in var_name
+
     def get_learning_rate(self, global_step, batch_size):
         lr0 = self.get_scaled_base_learning_rate(batch_size)
         boundaries = [b * self.base_lr_batch_size // batch_size for b in (160000, 200000)]

@@ -10,9 +10,14 @@ from __future__ import annotations
 import torch
 
 
-def apply_update(h, w, grad, m=None, v=None, w16=None, blend=None):
-    """In-place update of the flat arena ``w``; ``h`` has the fields of ``kfb_hyper``."""
-    g = grad * h.grad_scale + h.weight_decay * w
+def apply_update(h, w, grad, m=None, v=None, w16=None, blend=None, decay_mask=None):
+    """In-place update of the flat arena ``w``; ``h`` has the fields of ``kfb_hyper``.
+    ``decay_mask`` (optional, one uint8 per 128-element block, 0 = no L2 term) is the torch form
+    of ``kfb_hyper.decay_mask``."""
+    wd = h.weight_decay
+    if decay_mask is not None:
+        wd = wd * decay_mask.to(w.dtype).repeat_interleave(128)[:w.numel()]
+    g = grad * h.grad_scale + wd * w
     if h.clip > 0:
         g = g.clamp(-h.clip, h.clip)
     if h.opt == 0:

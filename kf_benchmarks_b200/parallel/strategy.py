@@ -53,7 +53,8 @@ class Hyper(ctypes.Structure):
     _fields_ = [("opt", ctypes.c_int), ("lr", ctypes.c_float), ("momentum", ctypes.c_float),
                 ("decay", ctypes.c_float), ("epsilon", ctypes.c_float),
                 ("weight_decay", ctypes.c_float), ("grad_scale", ctypes.c_float),
-                ("clip", ctypes.c_float), ("adam_t", ctypes.c_float)]
+                ("clip", ctypes.c_float), ("adam_t", ctypes.c_float),
+                ("decay_mask", ctypes.c_void_p)]
 
 
 def reduction_semantics(params) -> Tuple[str, bool]:
@@ -147,6 +148,19 @@ class UpdateEngine:
         self._ready_hi = 0
         self._launched = 0
         self._rng = np.random.RandomState(seed + 7919 * comm.rank)
+        # variables a model excludes from the L2 term (SSD: batch norm): one byte per 128-element
+        # arena block, read by the update kernels; None when everything is decayed
+        self.decay_mask = None
+        flt = getattr(model, "l2_decay_filter", None)
+        if flt is not None and hasattr(store, "order") and (params.weight_decay or 0.0) > 0:
+            keep = torch.ones((n + 127) // 128, dtype=torch.uint8)
+            any_off = False
+            for slot in store.order:
+                if not flt(slot.spec.name):
+                    keep[slot.offset // 128:(slot.offset + slot.numel + 127) // 128] = 0
+                    any_off = True
+            if any_off:
+                self.decay_mask = keep.to(self.device)
         # --staged_vars (T/variable_mgr_util.py:236-393) software-pipelines the parameter-server
         # traffic by one step through StagingAreas: the step computes on variables that miss
         # the newest update. The deferred-exchange path below has the same one-step staleness
@@ -324,6 +338,8 @@ class UpdateEngine:
                 self._pub_peers = c.peers(self.pub)
                 self._ver_peers = c.peers(self.ver)
                 self.torn = torch.zeros(1, dtype=torch.int32, device=self.device)
+                self.pull_buf = torch.empty(self.total, dtype=torch.float32, device=self.device)
+                self.pair_sync = torch.zeros(4, dtype=torch.int32, device=self.device)
                 self.my_version = 0
 
     # ------------------------------------------------------------------ per-step
@@ -356,6 +372,8 @@ class UpdateEngine:
         h.grad_scale = scale
         h.clip = p.gradient_clip if p.gradient_clip else 0.0
         h.adam_t = float(self.step_count + 1)
+        h.decay_mask = self.decay_mask.data_ptr() if (self.decay_mask is not None and
+                                                      self.cuda) else None
         return h
 
     def enable_dynamic_hyper(self) -> None:
@@ -386,6 +404,16 @@ class UpdateEngine:
             torch.cuda.current_stream(self.device).wait_event(self.done_event)
         self._ready_hi = 0
         self._launched = 0
+        self._sma_prefetched = False
+        if self._effective_algo() == "sma" and self._sma_can_prefetch():
+            # SynchronousAveraging exchanges the *weights*, which are final now: their average
+            # is taken on the exchange stream while forward and backward run
+            c = self.comm
+            self.ready_event.record(torch.cuda.current_stream(self.device))
+            c.comm_stream.wait_event(self.ready_event)
+            self._allreduce_call(3, 0, self.total, self._h, None, c.comm_stream)
+            self.done_event.record(c.comm_stream)
+            self._sma_prefetched = True
         if self.device_ls:
             # the per-step values the update kernels read from device memory (the skip flag was
             # cleared by the previous kfb_loss_scale_update)
@@ -410,6 +438,11 @@ class UpdateEngine:
                 self.buckets[self._launched][1] <= self._ready_hi:
             self._launch_bucket(self.buckets[self._launched], overlapped=True)
             self._launched += 1
+
+    def _sma_can_prefetch(self) -> bool:
+        return (self.cuda and isinstance(self.comm, P2PComm) and self.ar_v2 and
+                not self.auto_loss_scale and not self.relaxed and self.total % 8 == 0 and
+                os.environ.get("KFB_SMA_OVERLAP", "1") != "0")
 
     def _can_overlap(self) -> bool:
         return (self.cuda and isinstance(self.comm, P2PComm) and
@@ -436,6 +469,13 @@ class UpdateEngine:
             self._local_update(0, self.total)
         elif algo == "pair":
             self._pair_update()
+        elif algo == "sma" and getattr(self, "_sma_prefetched", False):
+            st = self.store
+            torch.cuda.current_stream(self.device).wait_event(self.done_event)
+            native.call("optimizer_step_blend", ptr(st.w32), ptr(self.reduced), ptr(st.grad),
+                        ptr(self.m), ptr(self.v), ptr(st.w16), i64(self.total),
+                        ctypes.byref(self._h), ptr(self.dyn), f32(self.params.sma_alpha),
+                        self._s())
         else:
             if self._launched == 0 and not self.fused_push:
                 # nothing was overlapped (SMA, auto loss scale, the all-reduce micro-benchmark,
@@ -505,7 +545,8 @@ class UpdateEngine:
                                 ptr(self.v), ptr(st.w16), i64(self.total), ctypes.byref(self._h),
                                 None, None, self._s())
                 else:
-                    optim_ref.apply_update(self._h, st.w32, prev, self.m, self.v, st.w16)
+                    optim_ref.apply_update(self._h, st.w32, prev, self.m, self.v, st.w16,
+                                           decay_mask=self.decay_mask)
             cur = st.grad.clone()
             c.all_reduce_(cur)
             self._relaxed_prev = cur
@@ -521,9 +562,14 @@ class UpdateEngine:
 
     def _local_update(self, lo: int, hi: int) -> None:
         st = self.store
+        h = self._h
+        if lo and h.decay_mask:
+            # the kernel indexes the mask like its (offset) arrays: advance it with them
+            h = Hyper.from_buffer_copy(h)
+            h.decay_mask = self._h.decay_mask + lo // 128
         native.call("optimizer_step", self._ptr_at(st.w32, lo), self._ptr_at(st.grad, lo),
                     self._ptr_at(self.m, lo), self._ptr_at(self.v, lo), self._ptr_at(st.w16, lo),
-                    i64(hi - lo), ctypes.byref(self._h), ptr(self.dyn),
+                    i64(hi - lo), ctypes.byref(h), ptr(self.dyn),
                     ptr(self.skip_flag) if self.auto_loss_scale else None, self._s())
 
     def _launch_bucket(self, bucket, overlapped: bool) -> None:
@@ -564,7 +610,7 @@ class UpdateEngine:
         st, c = self.store, self.comm
         tail = (i64(lo), i64(count), ctypes.c_uint(c.next_seq()), ptr(st.w32), ptr(st.grad),
                 ptr(self.m), ptr(self.v), ptr(st.w16), ctypes.byref(h), ptr(self.dyn), skip_flag,
-                f32(self.params.sma_alpha if mode == 1 else 0.0), i32(0), self._s(stream))
+                f32(self.params.sma_alpha if mode in (1, 3) else 0.0), i32(0), self._s(stream))
         if self.ar_v2 and lo % 8 == 0 and count % 8 == 0:
             half = self.compact and mode == 0
             if half:
@@ -572,9 +618,9 @@ class UpdateEngine:
                 src_mc = self._g16_mc if self.nvls else None
                 red_mc = self._r16_mc if self.nvls else None
             else:
-                src = self._w_ptrs if mode == 1 else self._grad_ptrs
+                src = self._w_ptrs if mode in (1, 3) else self._grad_ptrs
                 red, red_local = self._red_ptrs, ptr(self.reduced)
-                src_mc = (self._w_mc if mode == 1 else self._grad_mc) if self.nvls else None
+                src_mc = (self._w_mc if mode in (1, 3) else self._grad_mc) if self.nvls else None
                 red_mc = self._red_mc if self.nvls else None
             native.call("allreduce_update2", i32(mode), i32(c.rank), i32(c.size),
                         None if self.nvls else src, None if self.nvls else red, src_mc, red_mc,
@@ -599,7 +645,8 @@ class UpdateEngine:
                     ctypes.c_void_p(self._ver_peers[peer]), ptr(self.pub), ptr(self.ver),
                     i64(self.total), i64(self.total), ptr(st.w32), ptr(st.grad), ptr(self.m),
                     ptr(self.v), ptr(st.w16), ctypes.byref(self._h), None,
-                    ctypes.c_uint(self.my_version), i32(1), ptr(self.torn), i32(0), self._s())
+                    ctypes.c_uint(self.my_version), i32(1), ptr(self.torn), ptr(self.pull_buf),
+                    ptr(self.pair_sync), i32(0), self._s())
 
     def _check_finite(self) -> None:
         st = self.store
@@ -655,7 +702,8 @@ class UpdateEngine:
         if self.cuda:
             self._local_update(0, self.total)
         else:
-            optim_ref.apply_update(h, st.w32, st.grad, self.m, self.v, st.w16)
+            optim_ref.apply_update(h, st.w32, st.grad, self.m, self.v, st.w16,
+                                   decay_mask=self.decay_mask)
 
     def _pair_pull_torch(self) -> torch.Tensor:
         """PairAveraging over torch.distributed: every rank draws a peer from a shared

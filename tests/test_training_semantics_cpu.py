@@ -445,3 +445,48 @@ def test_gradient_aggregation_matrix(extra, tmp_path):
     for r in range(2):
         assert np.allclose(results[r]["w"], sim.stores[r].w32.numpy(), rtol=2e-5, atol=2e-6)
     assert np.array_equal(results[0]["w"], results[1]["w"])
+
+
+def test_model_can_keep_variables_out_of_the_l2_term():
+    """The SSD model decays no batch-norm variable (T/models/ssd_model.py:91-94). The engine
+    turns the model's ``l2_decay_filter`` into a per-128-element-block mask that the update
+    (CPU restatement here, the CUDA kernels through ``kfb_hyper.decay_mask``) multiplies the
+    weight-decay coefficient with, and total_loss leaves the same variables out."""
+    import torch
+    from kf_benchmarks_b200 import datasets, params as params_lib
+    from kf_benchmarks_b200.models import model_config
+    from kf_benchmarks_b200.nn.params import ParameterStore
+    from kf_benchmarks_b200.parallel.comm import SingleComm
+    from kf_benchmarks_b200.parallel.strategy import UpdateEngine
+    p = params_lib.make_params(model="resnet20", data_name="cifar10", device="cpu",
+                               optimizer="sgd", weight_decay=0.1, variable_update="independent")
+    ds = datasets.create_dataset(None, "cifar10")
+    model = model_config.get_model_config("resnet20", ds, p)
+    g = model.build_graph(ds.num_classes, batch_size=2)
+    engines = {}
+    for name, flt in (("all", None), ("no_bn", lambda v: "batchnorm" not in v)):
+        store = ParameterStore(g, "cpu", fp16_shadow=False)
+        store.initialize(7)
+        if flt is not None:
+            model.l2_decay_filter = flt
+        eng = UpdateEngine(p, store, SingleComm(), model)
+        store.grad.zero_()                       # only the L2 term moves the weights
+        eng.begin_step(1.0)
+        w0 = store.w32.clone()
+        eng.finish_step()
+        engines[name] = (store, w0, eng)
+    store, w0, eng = engines["all"]
+    assert eng.decay_mask is None
+    assert torch.allclose(store.w32, w0 * 0.9)
+    store, w0, eng = engines["no_bn"]
+    assert eng.decay_mask is not None and int(eng.decay_mask.sum()) < eng.decay_mask.numel()
+    for slot in store.order:
+        a = store.view(slot.spec.name)
+        b = w0[slot.offset:slot.offset + slot.numel].view_as(a)
+        if "batchnorm" in slot.spec.name:
+            assert torch.equal(a, b), slot.spec.name
+        else:
+            assert torch.allclose(a, b * 0.9), slot.spec.name
+    from kf_benchmarks_b200.models import ssd_model
+    assert ssd_model.SSD300Model.l2_decay_filter(None, "ssd300/conv3/batchnorm3/gamma") is False
+    assert ssd_model.SSD300Model.l2_decay_filter(None, "ssd300/conv3/conv2d/kernel") is True

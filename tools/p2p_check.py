@@ -160,6 +160,8 @@ def main():
     pub = comm.symm_alloc(3 * n, torch.float32)
     ver = comm.symm_alloc(64, torch.int32)
     torn = torch.zeros(1, dtype=torch.int32, device=dev)
+    pull = torch.empty(n, device=dev)
+    psync = torch.zeros(4, dtype=torch.int32, device=dev)
     peer = (rank + 1) % world
     h = make_hyper(0, scale=1.0, wd=0.0)
     w.copy_(rank_data(rank, n, 40))
@@ -169,14 +171,14 @@ def main():
     native.call("pair_average_update", ctypes.c_void_p(comm.peers(pub)[peer]),
                 ctypes.c_void_p(comm.peers(ver)[peer]), ptr(pub), ptr(ver), i64(n), i64(n),
                 ptr(w), ptr(grad), None, None, ptr(w16), ctypes.byref(h), None, ctypes.c_uint(1),
-                i32(1), ptr(torn), i32(0), s)
+                i32(1), ptr(torn), ptr(pull), ptr(psync), i32(0), s)
     torch.cuda.synchronize()
     comm.barrier()
     # step 2: every rank now sees its peer's version 1
     native.call("pair_average_update", ctypes.c_void_p(comm.peers(pub)[peer]),
                 ctypes.c_void_p(comm.peers(ver)[peer]), ptr(pub), ptr(ver), i64(n), i64(n),
                 ptr(w), ptr(grad), None, None, ptr(w16), ctypes.byref(h), None, ctypes.c_uint(2),
-                i32(1), ptr(torn), i32(0), s)
+                i32(1), ptr(torn), ptr(pull), ptr(psync), i32(0), s)
     torch.cuda.synchronize()
     want = 0.5 * (rank_data(rank, n, 40) + rank_data(peer, n, 40))
     check("pair_average_update", w, want, 1e-6)
