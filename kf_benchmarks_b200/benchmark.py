@@ -129,6 +129,16 @@ class BenchmarkCNN:
         self.batch_size_per_device = self.model.get_batch_size()
         self.batch_size = self.batch_size_per_device * self.num_gpus  # per worker, as reference
         if self.device_kind == "gpu":
+            if not p.use_fp16:
+                # The reference's default precision (T/benchmark_cnn.py:464-466) has no device
+                # path here: every sm_100a kernel stores activations as fp16 and feeds the tensor
+                # cores fp16 operands (kind::f16). Running that under an fp32 label would make
+                # the numbers look like something they are not, so the combination is refused.
+                raise ValueError(
+                    "--use_fp16=false is not available with --device=gpu: the B200 kernels keep "
+                    "activations and tensor-core operands in fp16 (fp32 accumulation, fp32 master "
+                    "weights, optimizer state and batch-norm statistics). Pass --use_fp16, or "
+                    "--device=cpu --data_format=NHWC for full fp32 arithmetic.")
             if not torch.cuda.is_available():
                 raise RuntimeError("--device=gpu but no CUDA device is visible "
                                    "(use --device=cpu --data_format=NHWC for the CPU path)")
@@ -288,10 +298,6 @@ class BenchmarkCNN:
             from . import flags
             if getattr(p, name) != flags.param_specs[name].default_value:
                 _log("note: --%s has no effect on the B200-native runtime" % name)
-        if self.device.type == "cuda" and not p.use_fp16:
-            _log("note: --use_fp16=false: the CUDA executor keeps activations and the tensor-core "
-                 "operands in fp16 (fp32 accumulation, fp32 master weights, optimizer and batch-"
-                 "norm statistics); full fp32 arithmetic is available with --device=cpu")
 
     # ------------------------------------------------------------------ build
     def _build(self, phase_train: bool) -> None:

@@ -276,3 +276,19 @@ def test_native_call_argument_types_match_the_prototypes():
                                        (f, node.lineno, name, i, got, want))
     assert checked > 600
     assert not bad, "\n".join(bad)
+
+
+def test_fp32_on_the_gpu_is_refused_not_relabelled():
+    """--use_fp16 defaults to false in the reference (T/benchmark_cnn.py:464-466); the sm_100a
+    kernels are fp16-storage only, so the GPU path refuses the fp32 label instead of silently
+    computing in fp16 (the CPU path does full fp32)."""
+    import pytest
+    from kf_benchmarks_b200 import benchmark
+    p = P.make_params(model="trivial", device="gpu", num_batches=1)
+    with pytest.raises(ValueError, match="use_fp16=false is not available with --device=gpu"):
+        benchmark.BenchmarkCNN(benchmark.setup(p))
+    with pytest.raises(ValueError, match="variable_consistency=relaxed"):
+        benchmark.BenchmarkCNN(benchmark.setup(P.make_params(
+            model="trivial", device="cpu", data_format="NHWC", use_fp16=True,
+            fp16_enable_auto_loss_scale=True, variable_consistency="relaxed",
+            variable_update="replicated")))
