@@ -154,7 +154,8 @@ struct BnFwdArgs {
     if (p.dbg != nullptr && blockIdx.x == 0 && threadIdx.x == 0) p.dbg[i] = globaltimer_ns(); \
   } while (0)
 
-__global__ void __launch_bounds__(kBnThreads)
+template <int KU, int MINB>
+__global__ void __launch_bounds__(kBnThreads, MINB)
     bn_fwd_fused_kernel(const BnFwdArgs p) {
   extern __shared__ float red[];
   const SlabMap m = make_slab_map(p.rows, p.C);
@@ -262,7 +263,7 @@ __global__ void __launch_bounds__(kBnThreads)
       sc[i] = __ldcg(p.scale_shift + cv * 8 + i);
       sh[i] = __ldcg(p.scale_shift + C + cv * 8 + i);
     }
-    constexpr int kU = 4;
+    constexpr int kU = KU;
     const long long n_mine = m.r_end > m.r_begin + m.tr
                                  ? (m.r_end - m.r_begin - m.tr + m.row_lanes - 1) / m.row_lanes
                                  : 0;
@@ -604,7 +605,9 @@ extern "C" int kfb_bn_forward_train_fused(
   KFB_REQUIRE(sync != nullptr, "bn_forward_train_fused: needs the two barrier words");
   KFB_REQUIRE(stats_rows == 0 || (stats != nullptr && stats_bn > 0),
               "bn_forward_train_fused: bad statistics layout");
-  const int grid = resident_grid(bn_fwd_fused_kernel, rows);
+  // 4 rows in flight per thread at 2 CTAs per SM (tools/bn_microbench.py: 2 and 8 rows and
+  // 1 / 3 / 4 CTAs per SM were equal or slower)
+  const int grid = resident_grid(bn_fwd_fused_kernel<4, 2>, rows);
   KFB_REQUIRE(grid > 0, "bn_forward_train_fused: occupancy query failed");
   BnFwdArgs a;
   a.x = (const __half*)x; a.ldx = ldx;
@@ -625,7 +628,7 @@ extern "C" int kfb_bn_forward_train_fused(
   a.dbg = nullptr;
   KFB_REQUIRE(stats_rows > 0 || partial != nullptr,
               "bn_forward_train_fused: needs scratch for its own statistics pass");
-  bn_fwd_fused_kernel<<<grid, kBnThreads, kBnSmemBytes, (cudaStream_t)stream>>>(a);
+  bn_fwd_fused_kernel<4, 2><<<grid, kBnThreads, kBnSmemBytes, (cudaStream_t)stream>>>(a);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

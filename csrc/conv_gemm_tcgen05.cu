@@ -89,6 +89,14 @@ struct GemmParams {
   // through cp.async.bulk.tensor stores on `tmC` instead of per-lane 16-byte stores. Host-side
   // eligibility: fp16 output, no accumulate / row scatter / split-K / push.
   int tma_store;
+  // Accumulating TMA-store epilogue with a masked source (fused residual gradient): the values
+  // added to the result are acc_src * mask, acc_src being another [M][N] fp16 tensor read
+  // through tensor map D and mask one bit per element (byte (row, col / 8), bit col % 8) - the
+  // packed ReLU mask the batch-norm forward wrote. Null mask: plain out += result (D = C).
+  const unsigned char* acc_mask;
+  long long acc_mask_ld;  // bytes per row
+  const void* acc_src;    // host side only: the tensor map D is encoded over it
+  long long acc_src_ld;   // elements per row
 };
 
 constexpr int kBlockM = 128;
@@ -141,7 +149,8 @@ template <int BN, int MODE, bool FAST, bool TMA_ST = false, bool ACC = false>
 __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                         const __grid_constant__ CUtensorMap tmB,
-                        const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+                        const __grid_constant__ CUtensorMap tmC,
+                        const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
   using Cfg = TileCfg<BN>;
   const int kStages = p.stages;
   constexpr uint32_t kAMajor = (MODE == GEMM_NT || MODE == WGRAD) ? kMajorMN : kMajorK;
@@ -466,7 +475,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         if (lane == 0) {
           uint64_t* bar = &my_old_bar[old_issued & 1];
           mbar_expect_tx(bar, 4096);
-          tma_load_2d(old_buf + (old_issued & 1) * 4096, &tmC, bar, col_mem0 + c_first + k * c_step,
+          tma_load_2d(old_buf + (old_issued & 1) * 4096, &tmD, bar, col_mem0 + c_first + k * c_step,
                       m0 + quarter * 32);
         }
         ++old_issued;
@@ -527,17 +536,23 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
               // the old values of this chunk have landed (phase = use count of the buffer / 2)
               mbar_wait(&my_old_bar[old_used & 1], (old_used >> 1) & 1);
             }
+            // masked source: the 64 mask bits of this thread's row for the chunk (8 bytes)
+            unsigned long long mbits = ~0ull;
+            if (ACC && acc_on && p.acc_mask != nullptr && row < p.M)
+              mbits = *reinterpret_cast<const unsigned long long*>(
+                  p.acc_mask + static_cast<long long>(row) * p.acc_mask_ld + ((col_mem0 + c0) >> 3));
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
               const int piece = h * 4 + (j >> 3);
               if (acc_on) {
                 const uint4 o = *reinterpret_cast<const uint4*>(orow + ((piece ^ (lane & 7)) << 4));
                 const __half2* o2 = reinterpret_cast<const __half2*>(&o);
+                const unsigned mb = static_cast<unsigned>(mbits >> (8 * piece)) & 0xffu;
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                   const float2 t = __half22float2(o2[q]);
-                  f[j + 2 * q] += t.x;
-                  f[j + 2 * q + 1] += t.y;
+                  f[j + 2 * q] += ((mb >> (2 * q)) & 1u) ? t.x : 0.f;
+                  f[j + 2 * q + 1] += ((mb >> (2 * q + 1)) & 1u) ? t.y : 0.f;
                 }
               }
               uint4 u;
@@ -966,7 +981,8 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
     const char* e = getenv("KFB_TMA_ACC");
     tma_acc_env = (e != nullptr && *e != 0 && atoi(e) == 0) ? 0 : 1;
   }
-  const bool acc_ok = !p.accumulate || (tma_acc_env == 1 && MODE == DGRAD);
+  if (p.acc_src != nullptr) p.accumulate = 1;  // the masked source takes the accumulate path
+  const bool acc_ok = !p.accumulate || ((tma_acc_env == 1 || p.acc_src != nullptr) && MODE == DGRAD);
   if (tma_store_env == 1 && fast && (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) &&
       !p.out_fp32 && acc_ok && p.sc_P == 0 && tiles.z == 1 && p.push_n <= 1 &&
       p.N >= 64 && p.M >= 32 && (p.ldc % 8) == 0) {
@@ -975,6 +991,15 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
     const uint32_t box[2] = {64, 32};
     if (encode_tiled(&tmC, p.out, 2, dims, strides, box)) return 1;
     p.tma_store = 1;
+  }
+  CUtensorMap tmD = tmC;  // source of the values an accumulating epilogue adds (default: out)
+  if (p.acc_src != nullptr) {
+    KFB_REQUIRE(p.tma_store == 1,
+                "fused residual gradient: this shape does not take the TMA-store epilogue");
+    const uint64_t dims[2] = {(uint64_t)p.N, (uint64_t)p.M};
+    const uint64_t strides[1] = {(uint64_t)p.acc_src_ld * 2};
+    const uint32_t box[2] = {64, 32};
+    if (encode_tiled(&tmD, p.acc_src, 2, dims, strides, box)) return 1;
   }
   p.stages = Cfg::max_stages();
   p.m_tiles = (int)tiles.x;
@@ -988,19 +1013,19 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
     if constexpr (MODE == DGRAD) {
       p.stages = Cfg::max_stages_acc();
       gemm_tcgen05_kernel<BN, MODE, true, true, true>
-          <<<ctas, Cfg::kThreads, Cfg::smem_bytes_acc(p.stages), stream>>>(tmA, tmB, tmC, p);
+          <<<ctas, Cfg::kThreads, Cfg::smem_bytes_acc(p.stages), stream>>>(tmA, tmB, tmC, tmD, p);
     }
   } else if (fast && p.tma_store) {
     if constexpr (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) {
       gemm_tcgen05_kernel<BN, MODE, true, true>
-          <<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(tmA, tmB, tmC, p);
+          <<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(tmA, tmB, tmC, tmD, p);
     }
   } else if (fast)
     gemm_tcgen05_kernel<BN, MODE, true><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
-        tmA, tmB, tmC, p);
+        tmA, tmB, tmC, tmD, p);
   else
     gemm_tcgen05_kernel<BN, MODE, false><<<ctas, Cfg::kThreads, Cfg::smem_bytes(p.stages), stream>>>(
-        tmA, tmB, tmC, p);
+        tmA, tmB, tmC, tmD, p);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1327,8 +1352,39 @@ extern "C" int kfb_conv_dgrad_needs_zero_fill(const kfb_conv_desc* d) {
   return 0;
 }
 
+static int conv_dgrad_impl(const kfb_conv_desc* d, const void* dy, const void* w, void* dx,
+                           int accumulate, const void* res_src, long long res_ld,
+                           const unsigned char* res_mask, long long res_mask_ld, void* stream);
+
 extern "C" int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void* w, void* dx,
                               int accumulate, void* stream) {
+  return conv_dgrad_impl(d, dy, w, dx, accumulate, nullptr, 0, nullptr, 0, stream);
+}
+
+// dx = conv^T(dy, w) + res_src * mask: the data gradient of the first convolution of a residual
+// block together with the gradient that reaches the block input through the identity shortcut
+// (res_src = gradient of the block output, mask = packed ReLU mask of the block output, one bit
+// per element, as kfb_bn_forward_train_fused writes it). The separate "shortcut gradient" tensor
+// is then never written or read. Unit-stride convolutions whose output takes the TMA-store
+// epilogue only (kfb_conv_dgrad_residual_ok).
+extern "C" int kfb_conv_dgrad_residual_ok(const kfb_conv_desc* d) {
+  return d->stride_h == 1 && d->stride_w == 1 && d->c >= 64 && d->c % 8 == 0 &&
+         (long long)d->n * d->h * d->w >= 32;
+}
+
+extern "C" int kfb_conv_dgrad_residual(const kfb_conv_desc* d, const void* dy, const void* w,
+                                       void* dx, const void* res_src, long long res_ld,
+                                       const unsigned char* res_mask, long long res_mask_ld,
+                                       void* stream) {
+  KFB_REQUIRE(res_src != nullptr && kfb_conv_dgrad_residual_ok(d),
+              "conv_dgrad_residual: needs a unit-stride convolution with C >= 64");
+  KFB_REQUIRE(res_ld % 8 == 0, "conv_dgrad_residual: source row stride must be a multiple of 8");
+  return conv_dgrad_impl(d, dy, w, dx, 0, res_src, res_ld, res_mask, res_mask_ld, stream);
+}
+
+static int conv_dgrad_impl(const kfb_conv_desc* d, const void* dy, const void* w, void* dx,
+                           int accumulate, const void* res_src, long long res_ld,
+                           const unsigned char* res_mask, long long res_mask_ld, void* stream) {
   if (check_conv(d, "conv_dgrad")) return 2;
   if (load_driver_fns()) return 1;
   CUtensorMap tmB;
@@ -1381,6 +1437,10 @@ extern "C" int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void
       p.out = dx;
       p.ldc = d->c;
       p.accumulate = accumulate;
+      p.acc_src = res_src;
+      p.acc_src_ld = res_ld;
+      p.acc_mask = res_mask;
+      p.acc_mask_ld = res_mask_ld;
       if (strided) {
         p.sc_P = Hp;
         p.sc_Q = Wp;

@@ -1279,14 +1279,29 @@ static int fill_pool(PoolGeom* g, int n, int h, int w, int c, int p, int q, int 
   return 0;
 }
 
+// Grid of the pooling kernels: x = column / channel-vector chunks, y = rows, z = images, with the
+// loops of the kernels striding over what the grid does not cover. KFB_POOL_CTAS_PER_SM caps the
+// total number of CTAs (0 = one CTA per (chunk, row, image)).
+static dim3 pool_grid(int cols_x_vecs, int rows, int images) {
+  static const int per_sm = env_int("KFB_POOL_CTAS_PER_SM", 0, 0, 4096);
+  unsigned bx = (unsigned)((cols_x_vecs + 255) / 256);
+  unsigned by = (unsigned)(rows < 65535 ? rows : 65535);
+  unsigned bz = (unsigned)(images < 65535 ? images : 65535);
+  if (per_sm > 0) {
+    const unsigned long long target = 148ull * per_sm;
+    while ((unsigned long long)bx * by * bz > target && bz > 1) bz = (bz + 1) / 2;
+    while ((unsigned long long)bx * by * bz > target && by > 1) by = (by + 1) / 2;
+  }
+  return dim3(bx, by, bz);
+}
+
 extern "C" int kfb_pool_forward(const void* x, long long ldx, void* y, long long ldy,
                                 unsigned char* argmax, int n, int h, int w, int c, int p, int q,
                                 int kh, int kw, int sh, int sw, int pad_h, int pad_w, int is_max,
                                 void* stream) {
   PoolGeom g;
   if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
-  const dim3 blocks((unsigned)((q * (c / 8) + 255) / 256), (unsigned)(p < 65535 ? p : 65535),
-                    (unsigned)(n < 65535 ? n : 65535));
+  const dim3 blocks = pool_grid(q * (c / 8), p, n);
   cudaStream_t st = (cudaStream_t)stream;
   if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
     pool_fwd_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y, ldy, argmax,
@@ -1310,8 +1325,7 @@ extern "C" int kfb_pool_backward(const void* dy, long long lddy, const unsigned 
                                  int pad_w, int is_max, void* stream) {
   PoolGeom g;
   if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
-  const dim3 blocks((unsigned)((w * (c / 8) + 255) / 256), (unsigned)(h < 65535 ? h : 65535),
-                    (unsigned)(n < 65535 ? n : 65535));
+  const dim3 blocks = pool_grid(w * (c / 8), h, n);
   cudaStream_t st = (cudaStream_t)stream;
   if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
     pool_bwd_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)dy, lddy, argmax, (__half*)dx,

@@ -81,6 +81,17 @@ int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void* w, void* y
 int kfb_conv_dgrad_needs_zero_fill(const kfb_conv_desc* d);
 int kfb_conv_dgrad(const kfb_conv_desc* d, const void* dy, const void* w, void* dx,
                    int accumulate, void* stream);
+/* dx = conv^T(dy, w) + res_src * mask in one kernel: the data gradient of the first convolution
+ * of a residual block plus the gradient arriving through the identity shortcut (res_src =
+ * gradient of the block output [rows][C] with row stride res_ld, mask = packed ReLU mask of the
+ * block output, one bit per element, res_mask_ld bytes per row, NULL = unmasked). The old tiles
+ * arrive by TMA load while the MMA runs and the sum leaves by TMA store, so the separate shortcut
+ * gradient tensor of T/models/resnet_model.py:72-118's add + relu is never materialised.
+ * kfb_conv_dgrad_residual_ok tells whether the shape qualifies (unit stride, C >= 64). */
+int kfb_conv_dgrad_residual_ok(const kfb_conv_desc* d);
+int kfb_conv_dgrad_residual(const kfb_conv_desc* d, const void* dy, const void* w, void* dx,
+                            const void* res_src, long long res_ld,
+                            const unsigned char* res_mask, long long res_mask_ld, void* stream);
 
 /* dw (fp32, OHWI) (+)= scale * x^T (*) dy, split over pixels into `workspace`. */
 long long kfb_conv_wgrad_workspace_bytes(const kfb_conv_desc* d);

@@ -112,6 +112,10 @@ class CudaExecutor:
         self._stats_need = 0
         self.fuse_stats_min_k = int(os.environ.get("KFB_FUSE_STATS_MIN_K", "0"))
         self._stats_for = None
+        # fused residual gradient (kfb_conv_dgrad_residual): needs the packed masks of the
+        # single-launch BN and the TMA-store epilogue
+        self.fuse_res_grad = (self.bn_fused and os.environ.get("KFB_TMA_STORE", "1") != "0" and
+                              os.environ.get("KFB_FUSE_RESIDUAL_GRAD", "1") != "0")
         self.loss_rows = torch.zeros((2, n), dtype=torch.float32, device=dev)
         self.top = torch.zeros((4, n), dtype=torch.int32, device=dev)
         self.loss_out = torch.zeros((8,), dtype=torch.float32, device=dev)
@@ -127,6 +131,7 @@ class CudaExecutor:
         self.workspace = torch.zeros((max(self._ws_need // 4, 1024),), dtype=torch.float32,
                                      device=dev)
         self._plan_grad_writes()
+        self._plan_residual_grad_fusion()
         if graph.loss["kind"] not in ("softmax_xent", "ncf"):
             from . import losses_cuda
             losses_cuda.prepare(self)
@@ -205,6 +210,35 @@ class CudaExecutor:
             if self.needs_grad.get(t.id, False) and (t.consumers or t is self.graph.logits or
                                                      t is self.graph.aux_logits):
                 self._grad(t)
+
+    def _plan_residual_grad_fusion(self) -> None:
+        """Identity residual blocks: y = relu(bn(conv_k(...)) + r) with r also feeding the block's
+        first convolution. In backward the shortcut gradient dy * (y > 0) would be written by the
+        BN backward and then read-modify-written by that convolution's data gradient; instead
+        the convolution's dgrad epilogue adds dy * mask itself (kfb_conv_dgrad_residual) and the
+        tensor is written once. Conditions: r has exactly these two consumers, the convolution
+        is unit-stride with >= 64 input channels, the BN wrote a packed mask."""
+        if not self.fuse_res_grad:
+            return
+        order = {id(n): i for i, n in enumerate(self.graph.nodes)}
+        for node in self.graph.nodes:
+            info = self._per_node[id(node)]
+            if node.op != "bn" or "bitmask" not in info or len(node.inputs) < 2:
+                continue
+            r = node.inputs[1]
+            if not self.needs_grad.get(r.id, False) or r.id in self._alias or \
+                    len(r.consumers) != 2:
+                continue
+            others = [c for c in r.consumers if c is not node]
+            if len(others) != 1 or others[0].op != "conv" or others[0].inputs[0] is not r:
+                continue
+            conv = others[0]
+            cinfo = self._per_node[id(conv)]
+            if cinfo.get("flat") or order[id(conv)] > order[id(node)] or not bool(
+                    native.load().kfb_conv_dgrad_residual_ok(ctypes.byref(cinfo["desc"]))):
+                continue
+            info["res_grad_fused"] = True
+            cinfo["res_from"] = node
 
     def _acc(self, node: Node, idx: int) -> int:
         return 0 if self._first[(id(node), idx)] else 1
@@ -852,7 +886,15 @@ class CudaExecutor:
                         i32(gy.rows), i64(gy.ld), i64(info["kpad"]), i64(info["kpad"]),
                         ptr(self.workspace), i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
             return
-        if self.needs_grad[xin.id]:
+        if self.needs_grad[xin.id] and info.get("res_from") is not None:
+            # dx = dgrad + (gradient of the block output) * (packed ReLU mask of the block output)
+            bn = info["res_from"]
+            gout = self._grad(bn.output)
+            bits = self._per_node[id(bn)]["bitmask"]
+            gx = self._grad(xin)
+            native.call("conv_dgrad_residual", ctypes.byref(d), gy.p, self._w16(kname), gx.p,
+                        gout.p, i64(gout.ld), ptr(bits), i64(gout.cols // 8), s)
+        elif self.needs_grad[xin.id]:
             gx = self._grad(xin)
             acc = self._acc(node, 0)
             if info["dgrad_zero_fill"] and not acc:
@@ -879,6 +921,8 @@ class CudaExecutor:
         dbeta = self._g32(node.params["beta"].name)
         has_res = len(node.inputs) > 1
         gres = self._grad(node.inputs[1]) if has_res and self.needs_grad[node.inputs[1].id] else None
+        if info.get("res_grad_fused"):
+            gres = None        # the block's first convolution adds the shortcut gradient itself
         res_acc = self._acc(node, 1) if gres is not None else 0
         need_dz = self.needs_grad[zin.id]
         if need_dz and self._acc(node, 0):

@@ -78,6 +78,13 @@ case("dgrad_acc_1x1_s2_c256_k512_scatter", "dgrad", n=4, h=28, w=28, c=256, k=51
      stride=2, pad="VALID", acc=True)
 case("dgrad_acc_3x3_s2_c64_k64_scatter", "dgrad", n=2, h=56, w=56, c=64, k=64, r=3, s=3,
      stride=2, pad="SAME_RESNET", acc=True)
+# dgrad + shortcut gradient * packed ReLU mask in one kernel (kfb_conv_dgrad_residual)
+case("dgrad_res_1x1_c256_k64", "dgrad", n=4, h=14, w=14, c=256, k=64, r=1, s=1, stride=1,
+     pad="SAME", res=True)
+case("dgrad_res_1x1_c512_k128_tail", "dgrad", n=3, h=13, w=13, c=512, k=128, r=1, s=1, stride=1,
+     pad="SAME", res=True)
+case("dgrad_res_3x3_c64_k64", "dgrad", n=2, h=28, w=28, c=64, k=64, r=3, s=3, stride=1,
+     pad="SAME", res=True)
 # headline shapes (ResNet-50, batch 256; `--headline` runs them, they need ~6 GB)
 HEADLINE = []
 
@@ -98,6 +105,8 @@ hcase("dgrad_head_acc_1x1_56_c256_k64", "dgrad", n=256, h=56, w=56, c=256, k=64,
       stride=1, pad="SAME", acc=True)
 hcase("dgrad_head_acc_1x1_s2_56_c256_k512_scatter", "dgrad", n=256, h=56, w=56, c=256, k=512,
       r=1, s=1, stride=2, pad="VALID", acc=True)
+hcase("dgrad_head_res_1x1_56_c256_k64", "dgrad", n=256, h=56, w=56, c=256, k=64, r=1, s=1,
+      stride=1, pad="SAME", res=True)
 hcase("stem_head_7x7_s2_c3_k64", "stem", n=256, h=224, w=224, c=3, k=64, r=7, s=7, stride=2,
       pad="SAME_RESNET")
 
@@ -173,7 +182,21 @@ def run_case(name: str) -> dict:
             if kind == "dgrad":
                 gx = xp.grad[:, :, ph[0]:ph[0] + h, pw[0]:pw[0] + w]
                 ref = gx.permute(0, 2, 3, 1)
-                if kw.get("acc"):
+                if kw.get("res"):
+                    import ctypes
+                    from kf_benchmarks_b200.ops import native
+                    from kf_benchmarks_b200.ops.native import i64, ptr
+                    src = rnd(n, h, w, c)
+                    bits = torch.randint(0, 256, (n * h * w, c // 8), device=dev,
+                                         dtype=torch.uint8, generator=g)
+                    out = torch.full((n, h, w, c), 7.0, device=dev, dtype=torch.float16)
+                    native.call("conv_dgrad_residual", ctypes.byref(d), ptr(dy), ptr(wt),
+                                ptr(out), ptr(src), i64(c), ptr(bits), i64(c // 8),
+                                native.stream_ptr())
+                    shifts = torch.arange(8, device=dev, dtype=torch.uint8)
+                    mask = ((bits[:, :, None] >> shifts) & 1).reshape(n, h, w, c).float()
+                    ref = ref + src.float() * mask
+                elif kw.get("acc"):
                     prev = rnd(n, h, w, c)
                     out = prev.clone()
                     gc.conv_dgrad(dy, wt, d, out=out, accumulate=True)

@@ -72,7 +72,12 @@ def check(model_name, data_name, batch, image_size=None, tol=1e-2, verbose=False
     h = model.image_size
     images = (torch.randn(batch, h, h, 3, generator=gen) * 0.5).half()
     labels = torch.randint(0, nclass - 1, (batch,), generator=gen).int()
+    # the fused residual gradient couples two nodes (the block's first convolution adds the
+    # shortcut gradient of the block's last batch norm): checked on its own by
+    # tools/kernel_check.py (dgrad_res_*), switched off here so that every node stands alone
+    os.environ["KFB_FUSE_RESIDUAL_GRAD"] = "0"
     ex = CudaExecutor(g, st, nclass)
+    os.environ.pop("KFB_FUSE_RESIDUAL_GRAD", None)
     ex.set_inputs(images.cuda(), labels.cuda())
     ex.forward(True)
     ex.loss_backward(loss_scale=1.0)           # allocates every gradient buffer
@@ -133,6 +138,17 @@ def check(model_name, data_name, batch, image_size=None, tol=1e-2, verbose=False
             # element carrying a large gradient moves the max-norm comparison by percents. The
             # incoming gradient is zeroed at those few elements on both sides.
             flip = ((out > 0) != (y_ref.detach() > 0)).reshape(gy_h.shape)
+            if node.op == "bn" and node.attrs.get("relu"):
+                # the backward recomputes the ReLU mask from the input (x > -shift/scale), which
+                # can disagree with the forward's fma(x, scale, shift) > 0 for a value within an
+                # ulp of the threshold: such elements get no incoming gradient on either side
+                node.attrs["relu"] = False
+                with torch.no_grad():
+                    pre = ref._run(node, [x.detach() for x in xs], True)
+                node.attrs["relu"] = True
+                ref._leaves.clear()
+                y_ref = ref._run(node, xs, True)
+                flip = flip | (pre.abs() < 1e-4 * pre.abs().max()).reshape(gy_h.shape)
             r["sign_flips"] = int(flip.sum())
             gy_h = torch.where(flip, torch.zeros_like(gy_h), gy_h)
             put(ex.gbuf[node.output.id], gy_h)
