@@ -2,7 +2,8 @@
 
 For every node it counts the FLOPs of the forward / dgrad / wgrad GEMMs and the HBM bytes each
 kernel class has to move with the pass structure this framework uses (fp16 NHWC activations,
-fp32 weight gradients, two-pass batch norm forward and backward) and turns both into a time at
+fp32 weight gradients, batch-norm statistics from the conv epilogue, one apply pass forward, a
+reduce and an apply pass backward - the single-launch backward kernel is booked under "apply") and turns both into a time at
 the measured peaks of MEASURED_PEAKS.json: roof = max(FLOPs / tensor peak, bytes / copy
 bandwidth), summed kernel by kernel. ``CLASS_OF`` maps kernel names to those classes. Used by
 ``tools/roofline_model.py`` (against ncu launch lists) and by ``--tfprof_file`` (against the
@@ -71,12 +72,15 @@ def model_costs(graph, bw, fl):
             c.add("conv wgrad (W3)", 2.0 * macs, 2 * x + 2 * y + 4 * w, "bwd/" + n.name)
         elif n.op == "bn":
             res = len(n.inputs) > 1
-            # forward: statistics pass reads x; apply pass reads x (+ residual), writes y
-            c.add("BN fwd statistics (W4/W5)", 0, 2 * x, "fwd/" + n.name)
-            c.add("BN fwd apply+ReLU+add (W5)", 0, 2 * x * (3 if res else 2), "fwd/" + n.name)
-            # backward: reduce pass reads dy, x; apply pass reads dy, x, writes dx (+ d residual)
-            c.add("BN bwd reduce (W5)", 0, 2 * x * 2, "bwd/" + n.name)
-            c.add("BN bwd apply (W5)", 0, 2 * x * (4 if res else 3), "bwd/" + n.name)
+            # forward: the statistics come from the conv epilogue (no pass over x); the apply
+            # phase reads x (+ residual) and writes y (+ 1 bit per element of packed ReLU mask)
+            c.add("BN fwd apply+ReLU+add (W5)", 0, 2 * x * (3 if res else 2) + (x / 8 if res else 0),
+                  "fwd/" + n.name)
+            # backward: the reduce phase reads dy, x (+ mask bits); the apply phase reads them
+            # again and writes dx; the shortcut gradient of an identity block is added by the
+            # block's first convolution instead of being written here
+            c.add("BN bwd reduce (W5)", 0, 2 * x * 2 + (x / 8 if res else 0), "bwd/" + n.name)
+            c.add("BN bwd apply (W5)", 0, 2 * x * 3 + (x / 8 if res else 0), "bwd/" + n.name)
         elif n.op == "pool":
             c.add("pool fwd+bwd (W6)", 0, 2 * (x + y), "fwd/" + n.name)
             c.add("pool fwd+bwd (W6)", 0, 2 * (y + x), "bwd/" + n.name)
@@ -103,10 +107,10 @@ CLASS_OF = [
     (r"gemm_tcgen05_kernel<\d+, 5,", "conv dgrad (W2)"),
     (r"gemm_tcgen05_kernel<\d+, [14],", "conv wgrad (W3)"),
     (r"splitk_reduce", "conv wgrad (W3)"),
-    (r"channel_reduce_kernel<0>|bn_finalize", "BN fwd statistics (W4/W5)"),
-    (r"bn_apply_kernel", "BN fwd apply+ReLU+add (W5)"),
+    (r"channel_reduce_kernel<0>|bn_finalize", "BN fwd apply+ReLU+add (W5)"),
+    (r"bn_apply_kernel|bn_fwd_fused", "BN fwd apply+ReLU+add (W5)"),
     (r"channel_reduce_kernel<1>|bn_bwd_finalize", "BN bwd reduce (W5)"),
-    (r"bn_bwd_apply", "BN bwd apply (W5)"),
+    (r"bn_bwd_apply|bn_bwd_fused", "BN bwd apply (W5)"),
     (r"pool_|spatial_mean", "pool fwd+bwd (W6)"),
     (r"optimizer_step|allreduce_update", "optimizer / all-reduce epilogue (W10/W11)"),
 ]

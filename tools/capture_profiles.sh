@@ -14,7 +14,7 @@ mkdir -p gpurun_out profiles
 CMD="python tools/profile_step.py --model resnet50 --batch_size 256 --steps 3"
 
 echo "== 1. bench (plain) =="
-timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err || {
+timeout 900 python bench.py --steps 30 --warmup 5 > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err || {
   echo "bench failed"; tail -5 gpurun_out/bench_$TAG.err; exit 1; }
 tail -1 gpurun_out/bench_$TAG.json > profiles/bench_1gpu_$TAG.json
 python - "$TAG" <<'PY'
@@ -25,6 +25,7 @@ print("%.0f img/s, %.2f ms/step, e2e %s, clocks %s" %
 PY
 
 echo "== 2. launch list of one step =="
+export KFB_CUDA_GRAPH=0   # profiled runs launch kernel by kernel (a graph replay hides them)
 $CMD > gpurun_out/plain.log 2>&1 || { echo "profile_step failed"; tail -5 gpurun_out/plain.log; exit 1; }
 PER=$(grep -o "launches per step (approx): [0-9]*" gpurun_out/plain.log | grep -o "[0-9]*$")
 PER=${PER:-543}
@@ -51,8 +52,8 @@ KFB_NVTX=1 ncu --nvtx --print-nvtx-rename kernel \
   || echo "(per-layer list not produced; see gpurun_out/ncu_launches_nvtx.log)"
 
 echo "== 3. ncu --set full on the heaviest kernels =="
-for spec in "gemm:gemm_tcgen05_kernel" "bnbwd:bn_bwd_apply_kernel" "bnred:channel_reduce_kernel" \
-            "bnapply:bn_apply_kernel"; do
+for spec in "gemm:gemm_tcgen05_kernel" "bnbwd:bn_bwd_fused_kernel" "bnfwd:bn_fwd_fused_kernel" \
+            "bnred:channel_reduce_kernel"; do
   name=${spec%%:*}; pat=${spec##*:}
   ncu --set full --clock-control none --import-source on -k regex:$pat -s 60 -c 3 -f \
       -o gpurun_out/prof_${TAG}_$name $CMD > gpurun_out/ncu_$name.log 2>&1
