@@ -237,6 +237,9 @@ def main():
         return
     todo = [n for n in CASES if (not args.filter or args.filter in n) and
             ((n in HEADLINE) == bool(args.headline))]
+    if os.environ.get("KFB_TMA_STORE") == "0":
+        # the fused residual gradient exists only in the TMA-store epilogue
+        todo = [n for n in todo if not CASES[n][1].get("res")]
     results = []
     while todo:
         t0 = time.time()
