@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(256)
     bn_apply_kernel(const __half* __restrict__ x, long long ldx,
                     const float* __restrict__ scale_shift, const __half* __restrict__ res,
                     long long ldr, __half* __restrict__ y, long long ldy, long long rows, int C,
-                    int relu) {
+                    int relu, unsigned char* __restrict__ bitmask) {
   const int vpr = C >> 3;
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   if (cv >= vpr) return;
@@ -321,10 +321,77 @@ __global__ void __launch_bounds__(256)
       for (int k = 0; k < 8; ++k) v[k] += rr[k];
     }
     if (relu) {
+      unsigned bits = 0;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+      for (int k = 0; k < 8; ++k) {
+        bits |= (v[k] > 0.f ? 1u : 0u) << k;
+        v[k] = fmaxf(v[k], 0.f);
+      }
+      if (bitmask != nullptr) bitmask[r * vpr + cv] = static_cast<unsigned char>(bits);
     }
     store8(y + r * ldy + cv * 8, v);
+  }
+}
+
+// BN forward finalize from the conv-epilogue statistics (layout of kfb_gemm_stats_layout: for
+// channel c = nb*bn + j the partial rows are stats[((nb*nrows + r)*2 + s)*bn + j]). Block =
+// (32 channels, 32 row lanes), like fold_partials.
+__global__ void bn_finalize_stats_kernel(const float* __restrict__ stats, int nrows, int bn, int C,
+                                         float inv_count, float unbias, float eps, float decay,
+                                         const float* __restrict__ gamma,
+                                         const float* __restrict__ beta,
+                                         float* __restrict__ moving_mean,
+                                         float* __restrict__ moving_var,
+                                         float* __restrict__ mean_rstd,
+                                         float* __restrict__ scale_shift, int update_moving) {
+  __shared__ float sh[2][kFoldLanes][32];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int c = blockIdx.x * 32 + tx;
+  float a = 0.f, b = 0.f;
+  if (c < C) {
+    const int nb = c / bn, j = c - nb * bn;
+    const float* base = stats + static_cast<long long>(nb) * nrows * 2 * bn + j;
+    float a4[4] = {0.f, 0.f, 0.f, 0.f}, b4[4] = {0.f, 0.f, 0.f, 0.f};
+    int r = ty;
+    for (; r + 3 * kFoldLanes < nrows; r += 4 * kFoldLanes) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float* q = base + static_cast<long long>(r + u * kFoldLanes) * 2 * bn;
+        a4[u] += q[0];
+        b4[u] += q[bn];
+      }
+    }
+    for (int u = 0; r < nrows; r += kFoldLanes, ++u) {
+      const float* q = base + static_cast<long long>(r) * 2 * bn;
+      a4[u] += q[0];
+      b4[u] += q[bn];
+    }
+    a = (a4[0] + a4[1]) + (a4[2] + a4[3]);
+    b = (b4[0] + b4[1]) + (b4[2] + b4[3]);
+  }
+  sh[0][ty][tx] = a;
+  sh[1][ty][tx] = b;
+  __syncthreads();
+  if (ty != 0 || c >= C) return;
+  float s = 0.f, ss = 0.f;
+#pragma unroll
+  for (int l = 0; l < kFoldLanes; ++l) {
+    s += sh[0][l][tx];
+    ss += sh[1][l][tx];
+  }
+  const float mean = s * inv_count;
+  float var = ss * inv_count - mean * mean;
+  var = var < 0.f ? 0.f : var;
+  const float rstd = rsqrtf(var + eps);
+  mean_rstd[c] = mean;
+  mean_rstd[C + c] = rstd;
+  const float g = gamma ? gamma[c] : 1.f;
+  const float sc = g * rstd;
+  scale_shift[c] = sc;
+  scale_shift[C + c] = beta[c] - mean * sc;
+  if (update_moving) {
+    moving_mean[c] = moving_mean[c] * decay + mean * (1.f - decay);
+    moving_var[c] = moving_var[c] * decay + var * unbias * (1.f - decay);
   }
 }
 
@@ -1180,7 +1247,7 @@ extern "C" int kfb_bn_forward_train(const void* x, long long ldx, long long rows
   apply_launch_shape(rows, C, &ag, &ab);
   bn_apply_kernel<<<ag, ab, 0, st>>>((const __half*)x, ldx, scale_shift,
                                      (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
-                                     relu);
+                                     relu, nullptr);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1199,7 +1266,35 @@ extern "C" int kfb_bn_forward_inference(const void* x, long long ldx, long long 
   apply_launch_shape(rows, C, &ag, &ab);
   bn_apply_kernel<<<ag, ab, 0, st>>>((const __half*)x, ldx, scale_shift,
                                      (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
-                                     relu);
+                                     relu, nullptr);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Two-kernel training forward on conv-epilogue statistics: finalize (fold of the partial rows)
+// and apply. For small layers this beats the single-launch form, whose two CTAs per SM and grid
+// barrier cost more than the second launch (measured, profiles/README.md).
+extern "C" int kfb_bn_forward_train_stats(const void* x, long long ldx, long long rows, int C,
+                                          const float* gamma, const float* beta,
+                                          float* moving_mean, float* moving_var, float eps,
+                                          float decay, int update_moving, float* mean_rstd,
+                                          float* scale_shift, const float* stats, int stats_rows,
+                                          int stats_bn, const void* residual, long long ldr,
+                                          int relu, void* y, long long ldy,
+                                          unsigned char* bitmask, void* stream) {
+  KFB_REQ_C8(C, "bn_forward_train_stats");
+  KFB_REQUIRE(stats != nullptr && stats_rows > 0 && stats_bn > 0,
+              "bn_forward_train_stats: needs the conv-epilogue statistics");
+  cudaStream_t st = (cudaStream_t)stream;
+  const float unbias = rows > 1 ? (float)((double)rows / (double)(rows - 1)) : 1.f;
+  bn_finalize_stats_kernel<<<(C + 31) / 32, dim3(32, kFoldLanes), 0, st>>>(
+      stats, stats_rows, stats_bn, C, (float)(1.0 / (double)rows), unbias, eps, decay, gamma, beta,
+      moving_mean, moving_var, mean_rstd, scale_shift, update_moving);
+  dim3 ag, ab;
+  apply_launch_shape(rows, C, &ag, &ab);
+  bn_apply_kernel<<<ag, ab, 0, st>>>((const __half*)x, ldx, scale_shift,
+                                     (const __half*)residual, ldr, (__half*)y, ldy, rows, C,
+                                     relu, bitmask);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

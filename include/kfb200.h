@@ -142,6 +142,15 @@ int kfb_bn_backward_fused(const void* dy, long long lddy, const void* mask, long
                           int accumulate_param_grads, float grad_scale, float* coef,
                           float* partial, void* dz, long long lddz, void* dres, long long lddr,
                           int dres_accumulate, unsigned* sync, void* stream);
+/* Two-kernel training forward on conv-epilogue statistics (finalize + apply): the form small
+ * layers take, where the second launch costs less than the grid barrier of the single launch. */
+int kfb_bn_forward_train_stats(const void* x, long long ldx, long long rows, int C,
+                               const float* gamma, const float* beta, float* moving_mean,
+                               float* moving_var, float eps, float decay, int update_moving,
+                               float* mean_rstd, float* scale_shift, const float* stats,
+                               int stats_rows, int stats_bn, const void* residual, long long ldr,
+                               int relu, void* y, long long ldy, unsigned char* bitmask,
+                               void* stream);
 int kfb_bn_forward_inference(const void* x, long long ldx, long long rows, int C,
                              const float* gamma, const float* beta, const float* moving_mean,
                              const float* moving_var, float eps, float* scale_shift,

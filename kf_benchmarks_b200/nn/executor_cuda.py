@@ -109,6 +109,13 @@ class CudaExecutor:
         # the headline step: 0 -> 11 051, 30 MB -> 11 163, 60 MB -> 11 197, 120 MB -> 11 194 img/s)
         self.bn_fused_bwd_min_bytes = int(os.environ.get("KFB_BN_FUSED_BWD_MIN_BYTES",
                                                          "60000000"))
+        # forward with conv-epilogue statistics: layers smaller than this run finalize + apply as
+        # two launches instead of the single launch. Measured on the headline step (CUDA-graph
+        # replay): threshold 0 / 30 MB / 60 MB / 120 MB / 250 MB / all layers -> 11 773 / 11 945 /
+        # 12 034 / 12 144 / 12 180 / 12 237 img/s, so the two launches are the default for every
+        # size; the single launch remains for BN layers that reduce their own statistics
+        self.bn_fused_fwd_min_bytes = int(os.environ.get("KFB_BN_FUSED_FWD_MIN_BYTES",
+                                                         str(1 << 62)))
         self._stats_need = 0
         self.fuse_stats_min_k = int(os.environ.get("KFB_FUSE_STATS_MIN_K", "0"))
         self._stats_for = None
@@ -522,6 +529,14 @@ class CudaExecutor:
         if train and self.bn_fused:
             sf, self._stats_for = self._stats_for, None
             fused = sf is not None and sf[0] == node.inputs[0].id
+            if fused and x.rows * c * 2 < self.bn_fused_fwd_min_bytes:
+                native.call("bn_forward_train_stats", x.p, i64(x.ld), i64(x.rows), i32(c), gamma,
+                            beta, mm, mv, f32(a["epsilon"]), f32(a["decay"]), i32(1),
+                            ptr(info["mean_rstd"]), ptr(info["scale_shift"]),
+                            ptr(self.stats_buf), i32(sf[1]), i32(sf[2]), res.p if res else None,
+                            i64(res.ld if res else 0), i32(int(a["relu"])), y.p, i64(y.ld),
+                            ptr(info.get("bitmask")), s)
+                return
             native.call("bn_forward_train_fused", x.p, i64(x.ld), i64(x.rows), i32(c), gamma, beta,
                         mm, mv, f32(a["epsilon"]), f32(a["decay"]), i32(1),
                         ptr(info["mean_rstd"]), ptr(info["scale_shift"]),
