@@ -84,6 +84,24 @@ def test_fused_bn_statistics_from_conv_epilogue():
         ref = torch.relu((yf - yf.mean(0)) * torch.rsqrt(yf.var(0, unbiased=False) + 1e-5) * gamma
                          + beta)
         assert torch.allclose(z.float().reshape(-1, k), ref, atol=2e-2, rtol=2e-2)
+        # ... and so does the two-launch form (finalize + apply), the default in training; with a
+        # residual and the packed ReLU mask here
+        res = torch.randn_like(y)
+        z2 = torch.empty_like(y)
+        bits = torch.zeros(rows * (k // 8), dtype=torch.uint8, device="cuda")
+        mm2, mv2 = torch.zeros(k, device="cuda"), torch.ones(k, device="cuda")
+        native.call("bn_forward_train_stats", ptr(y), i64(k), i64(rows), i32(k), ptr(gamma),
+                    ptr(beta), ptr(mm2), ptr(mv2), f32(1e-5), f32(0.9), i32(1), ptr(mean_rstd),
+                    ptr(ss), ptr(stats), i32(srows), i32(sbn), ptr(res), i64(k), i32(1), ptr(z2),
+                    i64(k), ptr(bits), native.stream_ptr())
+        torch.cuda.synchronize()
+        pre = (yf - yf.mean(0)) * torch.rsqrt(yf.var(0, unbiased=False) + 1e-5) * gamma + beta \
+            + res.float().reshape(-1, k)
+        assert torch.allclose(z2.float().reshape(-1, k), torch.relu(pre), atol=2e-2, rtol=2e-2)
+        assert torch.allclose(mm2, mm) and torch.allclose(mv2, mv)
+        shifts = torch.arange(8, device="cuda", dtype=torch.uint8)
+        got_mask = ((bits.reshape(rows, k // 8, 1) >> shifts) & 1).reshape(rows, k).bool()
+        assert (got_mask != (z2.reshape(-1, k) > 0)).float().mean() < 1e-4
 
 
 def test_per_lane_store_epilogue_matches_the_references():
