@@ -231,7 +231,9 @@ def main() -> int:
     ap.add_argument("--variable_update", default="replicated")
     ap.add_argument("--kungfu_option", default="sync_sgd")
     ap.add_argument("--optimizer", default="momentum")
-    ap.add_argument("--comm_impl", default="p2p")
+    ap.add_argument("--comm_impl", default="auto",
+                    help="auto (NVLS from 4 ranks up where the multicast bind succeeds, else the "
+                         "pull kernel), p2p, nvls, p2p_fused, nccl")
     ap.add_argument("--bucket_bytes", type=int, default=None,
                     help="gradient bucket size of the overlapped exchange (default: the flag's)")
     ap.add_argument("--no_e2e", action="store_true")
@@ -336,8 +338,20 @@ def main() -> int:
             "replica_checksum_equal": replicas_equal, "standin": standin,
             "final_loss": loss, "wall_s_timed": wall,
         }
-        print(json.dumps(out))
     bench.comm.close()
+    if n_ranks > 1:
+        # tear the process groups down before the result line goes out, so that nothing (NCCL
+        # shutdown warnings of other ranks, for instance) follows it on the job's output
+        try:
+            import torch.distributed as dist
+            dist.barrier()
+            dist.destroy_process_group()
+        except Exception:
+            pass
+    if rank == 0:
+        sys.stdout.flush()
+        time.sleep(0.5 if n_ranks > 1 else 0.0)
+        print(json.dumps(out), flush=True)
     return 0
 
 

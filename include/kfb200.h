@@ -455,6 +455,20 @@ int kfb_ctc_loss(const float* z, long long ldz, int batch, int T, int C, const i
                  float scale, const float* dyn_scale, void* dz, long long lddz, float* workspace,
                  long long workspace_floats, float* out, void* stream);
 
+/* ------------------------------------------------------------------ */
+/* Input preprocessing on the device (csrc/image_ops.cu)               */
+/* ------------------------------------------------------------------ */
+/* Batch form of kfb_image_transform (include/kfb200_host.h, same kfb_image_op descriptor and
+ * arithmetic) as CUDA kernels: `srcs` = n device addresses of raw uint8 RGB images, `ops` = n
+ * descriptors in device memory (methods 0 bilinear, 1 nearest, 4 crop_and_resize; bicubic / area
+ * stay on the host), `means` = 3 n floats of scratch, `out` = n images `image_stride` elements
+ * apart. The host threads then only decode JPEG; crop / resize / mirror / colour jitter /
+ * normalise / fp16 happen where the batch is consumed (the reference runs this stage in tf.data,
+ * T/preprocessing.py:192-307). kfb_image_op_bytes_device = sizeof(kfb_image_op) in this library. */
+int kfb_image_op_bytes_device(void);
+int kfb_image_transform_batch(const void* srcs, const void* ops, int n, int max_pixels,
+                              float* means, void* out, long long image_stride, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -516,7 +516,9 @@ class BenchmarkCNN:
             return True
         from .parallel.comm import P2PComm
         return (os.environ.get("KFB_MULTI_RANK_GRAPH", "1") != "0" and isinstance(self.comm, P2PComm)
-                and eng._can_overlap() and not eng.fused_push)
+                and not eng.fused_push and
+                (eng._can_overlap() or
+                 (eng._effective_algo() == "sma" and eng._sma_can_prefetch())))
 
     def _graph_safe_to_freeze(self) -> bool:
         """Automatic mode only captures steps whose replay is exactly the eager step: dropout /
@@ -581,6 +583,7 @@ class BenchmarkCNN:
             if multi:
                 self.comm.seq = seq0              # nothing ran during capture
             eng.step_count -= 1                   # finish_step counted the captured (not run) step
+            ex.static_inputs = True               # later device batches are copied, not rebound
             self._graph_launches = _native.launch_count - launches0   # kernels per replay
             _native.launch_count = launches0
             self._graph = g

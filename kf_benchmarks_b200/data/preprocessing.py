@@ -212,6 +212,20 @@ class _BatchSource(InputSource):
         nthreads = _decode_workers(params)
         self._pool = ThreadPoolExecutor(nthreads, thread_name_prefix="kfb-decode") \
             if nthreads > 1 else None
+        # --gpu_preprocess: workers hand over (decoded image, descriptor) pairs and the batch is
+        # transformed by one CUDA kernel (data/gpu_image.py); the source then yields device
+        # tensors, one output buffer per ring slot
+        self._gpu = None
+        if getattr(params, "gpu_preprocess", False) and pin:
+            from . import gpu_image, native_image
+            if native_image.available():
+                self._gpu = gpu_image.GpuImageBatcher(self.device, batch, height, width,
+                                                      self.out_dtype, slots=len(self._ring))
+                self._gpu_stream = torch.cuda.Stream(device=self.device)
+                self._labels_dev = [torch.empty((batch,), dtype=torch.int32, device=self.device)
+                                    for _ in range(len(self._ring))]
+                self.host_resident = False
+                self._raw_jobs = [None] * batch
         self.producer = ImageProducer(self._make_batch, group)
         self.producer.start()
         self.bytes_per_step = batch * height * width * 3 * (2 if self.out_dtype ==
@@ -237,10 +251,43 @@ class _BatchSource(InputSource):
         else:
             for i, job in enumerate(jobs):
                 self._fill(images, labels, i, job)
+        if self._gpu is not None:
+            return self._finish_on_gpu(images, labels_t)
         return images, labels_t
 
+    def _finish_on_gpu(self, images, labels_t):
+        """Producer thread: positions whose descriptor the device kernel supports were left as
+        (image, descriptor) pairs by the workers; they are uploaded raw and transformed in one
+        launch on the source's own stream. Positions the host had to transform itself (bicubic /
+        area) are copied over from the pinned batch."""
+        slot = (self._ring_pos - 1) % len(self._ring)
+        idx = [i for i, j in enumerate(self._raw_jobs) if j is not None]
+        with torch.cuda.stream(self._gpu_stream):
+            out = self._gpu.run([self._raw_jobs[i][0] for i in idx],
+                                [self._raw_jobs[i][1] for i in idx], stream=self._gpu_stream) \
+                if idx else None
+            dev = self._gpu._out[(self._gpu._slot - 1) % self._gpu.slots]
+            if len(idx) != self.batch:
+                # some positions were transformed on the host: upload the pinned batch and
+                # overwrite the device-transformed positions
+                full = images.to(self.device, non_blocking=True)
+                if idx:
+                    full[torch.tensor(idx, device=self.device)] = out
+                dev = full
+            labels_dev = self._labels_dev[slot]
+            labels_dev.copy_(labels_t, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._gpu_stream)
+        self.bytes_per_step = self._gpu.h2d_bytes_last + self.batch * 4
+        self._raw_jobs = [None] * self.batch
+        return dev, labels_dev, ev
+
     def next_batch(self):
-        return self.producer.get()
+        out = self.producer.get()
+        if self._gpu is not None:
+            torch.cuda.current_stream(self.device).wait_event(out[2])
+            return out[0], out[1]
+        return out
 
     def close(self):
         self.producer.done()
@@ -359,6 +406,11 @@ class ImagenetSource(_BatchSource):
             resized, window = eval_geometry(img.shape[0], img.shape[1], self.h, self.w)
         op = ni.make_op(img, crop, resized, window, method, flip, distort,
                         out_f16=images.dtype == torch.float16)
+        if self._gpu is not None:
+            from . import gpu_image
+            if gpu_image.supports(op):
+                self._raw_jobs[position] = (np.ascontiguousarray(img), op)
+                return
         ni.transform_into(np.ascontiguousarray(img), op,
                           images.data_ptr() + position * images.stride(0) * images.element_size())
 

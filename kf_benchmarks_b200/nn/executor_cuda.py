@@ -90,6 +90,7 @@ class CudaExecutor:
         self._cur = 0
         self._bind_inputs(first)
         self._staged = False
+        self.static_inputs = False       # set once a CUDA graph has captured the input addresses
         self._copy_stream = None
         self._ready = [torch.cuda.Event(), torch.cuda.Event()]
         self._free = [torch.cuda.Event(), torch.cuda.Event()]
@@ -408,6 +409,14 @@ class CudaExecutor:
             raise ValueError("expected %d input tensors, got %d" % (len(mine), len(tensors)))
         if all(t.is_cuda and t.dtype == m.dtype and t.is_contiguous() and t.shape == m.shape
                for t, m in zip(tensors, mine)):
+            if self.static_inputs:
+                # a captured CUDA graph reads the buffers bound at capture time: device batches
+                # that live elsewhere (a ring of device-side preprocessing outputs) are copied in
+                bound = [self.buf[r.id].t for r in self._in_refs] + self.label_tensors
+                for t, b in zip(tensors, bound):
+                    if t.data_ptr() != b.data_ptr():
+                        b.copy_(t, non_blocking=True)
+                return
             self._bind_inputs(list(tensors))
             return
         for t, m in zip(tensors, mine):

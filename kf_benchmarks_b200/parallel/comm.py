@@ -313,4 +313,17 @@ def create_comm(params, device) -> Comm:
         return TorchDistComm("nccl", dev)
     if impl == "gloo":
         raise ValueError("--comm_impl=gloo needs --device=cpu")
+    if impl == "auto":
+        # the in-switch reduction pays from 4 ranks up; every rank takes the same decision and,
+        # should the multicast bind fail anywhere, all of them fall back to the pull kernels
+        if world >= 4 and os.environ.get("KFB_AUTO_NVLS", "1") != "0":
+            try:
+                return P2PComm(dev, nvls=True)
+            except Exception as e:  # noqa: BLE001 - any bind / rendezvous failure
+                import torch.distributed as dist
+                print("comm_impl=auto: NVLS unavailable (%s); using the pull kernels"
+                      % str(e).splitlines()[0][:160], flush=True)
+                if not dist.is_initialized():
+                    raise
+        return P2PComm(dev, nvls=False)
     return P2PComm(dev, nvls=impl == "nvls")      # p2p, p2p_fused, nvls
