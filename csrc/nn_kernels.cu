@@ -1619,6 +1619,14 @@ extern "C" int kfb_softmax_xent_static(const float* logits, long long ldl, const
   return 0;
 }
 
+// Zero fill of a device range on a stream (a memset node: nothing of the step goes through a
+// framework fill kernel).
+extern "C" int kfb_fill_zero(void* p, long long bytes, void* stream) {
+  KFB_REQUIRE(p != nullptr && bytes >= 0, "fill_zero: bad arguments");
+  KFB_CHECK_CUDA(cudaMemsetAsync(p, 0, (size_t)bytes, (cudaStream_t)stream));
+  return 0;
+}
+
 extern "C" int kfb_cast_f32_f16(const float* in, void* out, long long n, void* stream) {
   cast_f32_f16_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(in, (__half*)out, n);
   KFB_CHECK_CUDA(cudaGetLastError());

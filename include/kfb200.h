@@ -261,6 +261,9 @@ int kfb_optimizer_step_blend(float* w, const float* avg, const float* g, float* 
                              void* w16, long long n, const kfb_hyper* hp, const float* dyn,
                              float alpha, void* stream);
 int kfb_check_finite(const float* g, long long n, int* flag, void* stream);
+/* cudaMemsetAsync(p, 0, bytes) on `stream` (gradient buffers of strided 1x1 dgrads, scatter
+ * tables): the step issues no framework fill kernels. */
+int kfb_fill_zero(void* p, long long bytes, void* stream);
 /* dyn[i] <- the argument for every bit i of `mask` (lr, grad_scale, adam_t), from a one-thread
  * kernel on `stream`: per-step values for captured graphs / device-resident loss scaling without
  * a pinned staging buffer. */

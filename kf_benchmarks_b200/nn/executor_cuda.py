@@ -485,6 +485,10 @@ class CudaExecutor:
         # the image buffer is only read by the forward pass (backward uses saved activations)
         self._free[self._cur].record(torch.cuda.current_stream(self.device))
 
+    @staticmethod
+    def _zero(t: torch.Tensor, s) -> None:
+        native.call("fill_zero", ptr(t), i64(t.numel() * t.element_size()), s)
+
     def _timed_node(self, tag, node, fn, *args):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         native.current_tag = tag + "/" + node.name
@@ -728,7 +732,7 @@ class CudaExecutor:
             st = info[d]
             wx, wh, b = (node.params[d + k] for k in ("_wx", "_wh", "_b"))
             gates, cbuf, hprev = st["gates"], st["c"], st["hprev"]
-            info["dc"].zero_()
+            self._zero(info["dc"], s)
             step = 1 if d == "fw" else -1
             order = range(t_steps - 1, -1, -1) if d == "fw" else range(t_steps)
             gybase = gy.t.data_ptr() + di * hid * e2
@@ -852,7 +856,7 @@ class CudaExecutor:
         if not backward:
             return
         for name in getattr(self, "_scatter_tables", []):
-            self.store.view(name, "grad").zero_()
+            self._zero(self.store.view(name, "grad"), s)
         for node in reversed(g.nodes):
             if not self.needs_grad[node.output.id]:
                 continue
@@ -922,7 +926,7 @@ class CudaExecutor:
             gx = self._grad(xin)
             acc = self._acc(node, 0)
             if info["dgrad_zero_fill"] and not acc:
-                gx.t.zero_()
+                self._zero(gx.t, s)
             native.call("conv_dgrad", ctypes.byref(d), gy.p, self._w16(kname), gx.p, i32(acc), s)
         push = self.push_lookup(kname) if self.push_lookup else None
         if push is not None:
