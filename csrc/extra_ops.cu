@@ -249,7 +249,12 @@ __device__ __forceinline__ float sample_uniform(unsigned long long seed, unsigne
 __global__ void __launch_bounds__(256)
     drop_path_kernel(const __half* __restrict__ x, long long ldx, __half* __restrict__ y,
                      long long ldy, int accumulate, long long rows, long long rows_per_sample,
-                     int C, float keep_prob, unsigned long long seed, unsigned long long offset) {
+                     int C, float keep_prob, unsigned long long seed, unsigned long long offset,
+                     const unsigned long long* __restrict__ step, int step_shift,
+                     const float* __restrict__ keep_dev) {
+  // device-resident step counter / keep probability (CUDA-graph replay)
+  if (step != nullptr) offset += (*step) << step_shift;
+  if (keep_dev != nullptr) keep_prob = *keep_dev;
   const int vpr = C >> 3;
   const long long total = rows * vpr;
   const float inv = 1.f / keep_prob;
@@ -531,7 +536,23 @@ extern "C" int kfb_drop_path(const void* x, long long ldx, void* y, long long ld
   KFB_REQUIRE(rows_per_sample > 0 && rows % rows_per_sample == 0, "drop_path: bad row split");
   drop_path_kernel<<<xgrid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
       (const __half*)x, ldx, (__half*)y, ldy, accumulate, rows, rows_per_sample, C, keep_prob,
-      seed, offset);
+      seed, offset, nullptr, 0, nullptr);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// kfb_drop_path with the step part of the Philox offset (offset + (*step << step_shift)) and,
+// optionally, the keep probability read from device memory.
+extern "C" int kfb_drop_path_dev(const void* x, long long ldx, void* y, long long ldy,
+                                 int accumulate, long long rows, long long rows_per_sample, int C,
+                                 float keep_prob, unsigned long long seed,
+                                 unsigned long long offset, const unsigned long long* step,
+                                 int step_shift, const float* keep_dev, void* stream) {
+  KFB_REQ_C8(C, "drop_path");
+  KFB_REQUIRE(rows_per_sample > 0 && rows % rows_per_sample == 0, "drop_path: bad row split");
+  drop_path_kernel<<<xgrid_for(rows * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)x, ldx, (__half*)y, ldy, accumulate, rows, rows_per_sample, C, keep_prob,
+      seed, offset, step, step_shift, keep_dev);
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -949,7 +949,11 @@ __device__ __forceinline__ float u01(uint32_t r) { return (r >> 8) * (1.0f / 167
 // y = x * mask / keep, mask regenerated from (seed, offset) in backward (same kernel).
 __global__ void __launch_bounds__(256)
     dropout_kernel(const __half* __restrict__ x, __half* __restrict__ y, long long nvec,
-                   float keep_prob, unsigned long long seed, unsigned long long offset) {
+                   float keep_prob, unsigned long long seed, unsigned long long offset,
+                   const unsigned long long* __restrict__ step, int step_shift) {
+  // device-resident step counter (CUDA-graph replay): the Philox offset moves with the step
+  // although the by-value arguments of the captured launch stay the same
+  if (step != nullptr) offset += (*step) << step_shift;
   const float inv_keep = 1.f / keep_prob;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -1501,7 +1505,51 @@ extern "C" int kfb_dropout(const void* x, void* y, long long n, float keep_prob,
   KFB_REQUIRE(n % 8 == 0, "dropout: element count must be a multiple of 8");
   KFB_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "dropout: bad keep_prob %f", keep_prob);
   dropout_kernel<<<grid_for(n / 8), 256, 0, (cudaStream_t)stream>>>(
-      (const __half*)x, (__half*)y, n / 8, keep_prob, seed, offset);
+      (const __half*)x, (__half*)y, n / 8, keep_prob, seed, offset, nullptr, 0);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// kfb_dropout with the step part of the Philox offset taken from device memory:
+// offset + (*step << step_shift). The same call serves forward and backward of a step.
+extern "C" int kfb_dropout_dev(const void* x, void* y, long long n, float keep_prob,
+                               unsigned long long seed, unsigned long long offset,
+                               const unsigned long long* step, int step_shift, void* stream) {
+  KFB_REQUIRE(n % 8 == 0, "dropout: element count must be a multiple of 8");
+  KFB_REQUIRE(keep_prob > 0.f && keep_prob <= 1.f, "dropout: bad keep_prob %f", keep_prob);
+  dropout_kernel<<<grid_for(n / 8), 256, 0, (cudaStream_t)stream>>>(
+      (const __half*)x, (__half*)y, n / 8, keep_prob, seed, offset, step, step_shift);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+__global__ void step_advance_kernel(unsigned long long* step) { *step += 1ull; }
+
+// *step += 1 on `stream` (last node of a training step; captured with it in a CUDA graph)
+extern "C" int kfb_step_advance(unsigned long long* step, void* stream) {
+  KFB_REQUIRE(step != nullptr, "step_advance: null counter");
+  step_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+struct FloatPack {
+  float v[128];
+};
+__global__ void set_floats_kernel(float* dst, FloatPack pack, int n) {
+  if (threadIdx.x < n) dst[threadIdx.x] = pack.v[threadIdx.x];
+}
+
+// dst[0..n) <- host values, carried in kernel arguments (no pinned staging buffer that a host
+// running ahead of the device could overwrite): per-step scalars of captured graphs
+extern "C" int kfb_set_floats(float* dst, const float* host_values, int n, void* stream) {
+  KFB_REQUIRE(dst != nullptr && host_values != nullptr && n >= 0, "set_floats: bad arguments");
+  for (int i = 0; i < n; i += 128) {
+    FloatPack pack;
+    const int m = n - i < 128 ? n - i : 128;
+    for (int k = 0; k < m; ++k) pack.v[k] = host_values[i + k];
+    set_floats_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(dst + i, pack, m);
+  }
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -198,6 +198,15 @@ int kfb_im2col_small_c(const void* x, void* col, int n, int h, int w, int c, int
 /* Philox dropout; the backward pass calls it again on dy with the same (seed, offset). */
 int kfb_dropout(const void* x, void* y, long long n, float keep_prob, unsigned long long seed,
                 unsigned long long offset, void* stream);
+/* Device-resident step state for CUDA-graph replay of steps with dropout / drop-path: the Philox
+ * offset becomes offset + (*step << step_shift), so a captured launch draws a fresh mask in
+ * every replay; kfb_step_advance is the step's last node; kfb_set_floats writes per-step host
+ * scalars (drop-path keep probabilities) through kernel arguments. */
+int kfb_dropout_dev(const void* x, void* y, long long n, float keep_prob, unsigned long long seed,
+                    unsigned long long offset, const unsigned long long* step, int step_shift,
+                    void* stream);
+int kfb_step_advance(unsigned long long* step, void* stream);
+int kfb_set_floats(float* dst, const float* host_values, int n, void* stream);
 /* Synthetic inputs generated on the device (T/models/model.py:220-237). */
 int kfb_synth_images(void* out, long long n, float mean, float stddev, unsigned long long seed,
                      void* stream);
@@ -432,6 +441,11 @@ int kfb_channel_gather(const void* x, long long ldx, void* y, long long ldy, int
 int kfb_drop_path(const void* x, long long ldx, void* y, long long ldy, int accumulate,
                   long long rows, long long rows_per_sample, int C, float keep_prob,
                   unsigned long long seed, unsigned long long offset, void* stream);
+int kfb_drop_path_dev(const void* x, long long ldx, void* y, long long ldy, int accumulate,
+                      long long rows, long long rows_per_sample, int C, float keep_prob,
+                      unsigned long long seed, unsigned long long offset,
+                      const unsigned long long* step, int step_shift, const float* keep_dev,
+                      void* stream);
 
 /* ---- loss heads (csrc/loss_kernels.cu) ---------------------------------------------------- */
 /* SSD-300 multibox loss (T/models/ssd_model.py:299-384): smooth-L1 on matched anchors + softmax

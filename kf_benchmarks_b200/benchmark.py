@@ -521,15 +521,15 @@ class BenchmarkCNN:
                  (eng._effective_algo() == "sma" and eng._sma_can_prefetch())))
 
     def _graph_safe_to_freeze(self) -> bool:
-        """Automatic mode only captures steps whose replay is exactly the eager step: dropout /
-        drop-path take their per-step mask offsets by value (a replay would repeat the mask),
-        and only the softmax cross-entropy head is known to be free of per-step host work."""
+        """Automatic mode only captures steps whose replay is exactly the eager step. Dropout /
+        drop-path qualify: the step part of their mask offsets and the drop-path keep
+        probabilities are read from device memory (executor.step_dev, dp_keep). Only the
+        softmax cross-entropy head is known to be free of per-step host work."""
         cached = getattr(self, "_graph_safe", None)
         if cached is None:
             g = getattr(self.executor, "graph", None)
             cached = bool(g is not None and g.loss["kind"] == "softmax_xent" and
-                          not any(n.op in ("dropout", "drop_path", "lstm", "embedding")
-                                  for n in g.nodes))
+                          not any(n.op in ("lstm", "embedding") for n in g.nodes))
             self._graph_safe = cached
         return cached
 
@@ -589,8 +589,10 @@ class BenchmarkCNN:
             self._graph = g
             _log("Captured the training step in a CUDA graph")
         eng.push_dynamic_hyper(lr)
+        ex.push_step_values()                     # drop-path keep probabilities of this step
         self._last_lr = lr
         self._graph.replay()
+        ex.step_index += 1                        # host mirror of the device step counter
         from .ops import native as _native
         _native.launch_count += getattr(self, "_graph_launches", 0)
         eng.step_count += 1                       # Adam's bias correction reads it (dyn[2])

@@ -124,6 +124,14 @@ class CudaExecutor:
         # single-launch BN and the TMA-store epilogue
         self.fuse_res_grad = (self.bn_fused and os.environ.get("KFB_TMA_STORE", "1") != "0" and
                               os.environ.get("KFB_FUSE_RESIDUAL_GRAD", "1") != "0")
+        # device-resident training-step counter (mirrors step_index): dropout / drop-path take the
+        # step part of their Philox offset from it, so that a captured CUDA graph draws fresh
+        # masks in every replay; drop-path keep probabilities (a schedule over the step) live
+        # in a device array refreshed before each step
+        self.step_dev = torch.zeros((1,), dtype=torch.int64, device=dev)
+        self._dp_nodes = [nd for nd in graph.nodes if nd.op == "drop_path"]
+        self.dp_keep = torch.ones((max(len(self._dp_nodes), 1),), dtype=torch.float32, device=dev)
+        self._dp_slot = {id(nd): i for i, nd in enumerate(self._dp_nodes)}
         self.loss_rows = torch.zeros((2, n), dtype=torch.float32, device=dev)
         self.top = torch.zeros((4, n), dtype=torch.int32, device=dev)
         self.loss_out = torch.zeros((8,), dtype=torch.float32, device=dev)
@@ -469,6 +477,8 @@ class CudaExecutor:
     # ------------------------------------------------------------------ forward
     def forward(self, train: bool = True) -> None:
         s = self._s()
+        if train and self._dp_nodes and not torch.cuda.is_current_stream_capturing():
+            self.push_step_values()
         if self.node_events is not None:
             for node in self.graph.nodes:
                 self._timed_node("fwd", node, getattr(self, "_fwd_" + node.op), node, train, s)
@@ -587,12 +597,22 @@ class CudaExecutor:
         native.call("dwconv_fprop", ctypes.byref(d), x.p, i64(x.ld),
                     self._w16(node.params["kernel"].name), y.p, i64(y.ld), s)
 
+    def push_step_values(self) -> None:
+        """Per-step host scalars into device memory (before the step's first launch, outside a
+        captured graph): the drop-path keep probabilities of this step."""
+        if self._dp_nodes:
+            vals = (ctypes.c_float * len(self._dp_nodes))(
+                *[float(nd.attrs["keep_prob_fn"](self.step_index)) for nd in self._dp_nodes])
+            native.call("set_floats", ptr(self.dp_keep), vals, i32(len(self._dp_nodes)),
+                        self._s())
+
     def _drop_path_args(self, node):
         kp = float(node.attrs["keep_prob_fn"](self.step_index))
         idx = self.graph.nodes.index(node)
         b = self.buf[node.output.id]
+        keep = ctypes.c_void_p(self.dp_keep.data_ptr() + 4 * self._dp_slot[id(node)])
         return (i64(b.rows), i64(b.rows // self.graph.batch_size), i32(_pad8(b.cols)), f32(kp),
-                u64(self.dropout_seed), u64((self.step_index * 4096 + idx) * 65536))
+                u64(self.dropout_seed), u64(idx * 65536), ptr(self.step_dev), i32(28), keep)
 
     def _fwd_drop_path(self, node, train, s):
         x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
@@ -600,7 +620,7 @@ class CudaExecutor:
             native.call("copy2d", x.p, i64(x.ld), y.p, i64(y.ld), i64(x.rows), i32(x.cols),
                         i32(0), s)
             return
-        native.call("drop_path", x.p, i64(x.ld), y.p, i64(y.ld), i32(0),
+        native.call("drop_path_dev", x.p, i64(x.ld), y.p, i64(y.ld), i32(0),
                     *self._drop_path_args(node), s)
 
     def _fwd_add(self, node, train, s):
@@ -650,13 +670,13 @@ class CudaExecutor:
 
     def _dropout_offset(self, node) -> int:
         idx = self.graph.nodes.index(node)
-        return (self.step_index * 4096 + idx) * (1 << 32)
+        return idx * (1 << 32)      # the step part (step << 44) comes from step_dev
 
     def _fwd_dropout(self, node, train, s):
         x, y = self.buf[node.inputs[0].id], self.buf[node.output.id]
         kp = node.attrs["keep_prob"] if train else 1.0
-        native.call("dropout", x.p, y.p, i64(x.rows * x.ld), f32(kp), u64(self.dropout_seed),
-                    u64(self._dropout_offset(node)), s)
+        native.call("dropout_dev", x.p, y.p, i64(x.rows * x.ld), f32(kp), u64(self.dropout_seed),
+                    u64(self._dropout_offset(node)), ptr(self.step_dev), i32(44), s)
 
     def _fwd_lrn(self, node, train, s):
         a = node.attrs
@@ -872,6 +892,7 @@ class CudaExecutor:
                 lo, hi = self.store.span([p.name for p in node.params.values() if p.trainable])
                 if hi > lo:
                     on_grads_ready(lo, hi)
+        native.call("step_advance", ptr(self.step_dev), s)
         self.step_index += 1
 
     def read_loss(self):
@@ -1021,7 +1042,7 @@ class CudaExecutor:
         if not self.needs_grad[xin.id]:
             return
         gy, gx = self._grad(node.output), self._grad(xin)
-        native.call("drop_path", gy.p, i64(gy.ld), gx.p, i64(gx.ld), i32(self._acc(node, 0)),
+        native.call("drop_path_dev", gy.p, i64(gy.ld), gx.p, i64(gx.ld), i32(self._acc(node, 0)),
                     *self._drop_path_args(node), s)
 
     def _bwd_add(self, node, s):
@@ -1091,8 +1112,9 @@ class CudaExecutor:
             return
         gy, gx = self._grad(node.output), self._grad(xin)
         dst = gx if not self._acc(node, 0) else self._tmp_like(gy)
-        native.call("dropout", gy.p, dst.p, i64(gy.rows * gy.ld), f32(node.attrs["keep_prob"]),
-                    u64(self.dropout_seed), u64(self._dropout_offset(node)), s)
+        native.call("dropout_dev", gy.p, dst.p, i64(gy.rows * gy.ld),
+                    f32(node.attrs["keep_prob"]), u64(self.dropout_seed),
+                    u64(self._dropout_offset(node)), ptr(self.step_dev), i32(44), s)
         if dst is not gx:
             native.call("copy2d", dst.p, i64(dst.ld), gx.p, i64(gx.ld), i64(gx.rows),
                         i32(_pad8(gx.cols)), i32(1), s)

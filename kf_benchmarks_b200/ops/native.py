@@ -68,7 +68,7 @@ def check(rc: int, what: str) -> None:
 
 # kernels launched per entry point (used for the launch count bench.py reports; entry points
 # not listed launch one kernel; conv_dgrad launches one per stride phase and is counted once)
-_LAUNCHES = {"gemm_nt": 2, "conv_wgrad": 2, "bn_forward_train": 3, "bn_forward_train_stats": 2, "fill_zero": 0, "bn_forward_inference": 2,
+_LAUNCHES = {"gemm_nt": 2, "conv_wgrad": 2, "bn_forward_train": 3, "bn_forward_train_stats": 2, "fill_zero": 0, "step_advance": 1, "set_floats": 1, "bn_forward_inference": 2,
              "bn_backward": 3, "bias_act_backward": 2, "softmax_xent": 2, "dwconv_wgrad": 2, "ssd_loss": 4, "ctc_loss": 3, "gemm_nt_rs": 2, "conv_wgrad_rs": 2}
 # allreduce_update2 launches a second (cast) kernel with compact gradient transfer; counted once
 
