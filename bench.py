@@ -8,6 +8,9 @@ v1, fp16 compute / fp32 master weights, batch 256 per GPU, synthetic ImageNet,
 max over ranks. ``--impl reference`` reports that the TensorFlow/KungFu reference cannot be
 installed on this image.
 
+Defaults: 200 timed steps after 10 warm-up steps (~4 s per timed region, so the number is not a
+burst at boost clocks; profiles/sustained_1gpu.jsonl has a 600-step run).
+
 Timed region = exactly K full training steps (forward, loss, backward, gradient exchange,
 optimizer update, BN statistics) bracketed by barrier + synchronize on both sides and CUDA
 events on the launching stream. Every step touches > 5 GB of activations, far more than the
@@ -223,8 +226,8 @@ def _replica_checksums_equal(bench, torch):
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "standin"])
     ap.add_argument("--model", default="resnet50")
     ap.add_argument("--batch_size", type=int, default=256)

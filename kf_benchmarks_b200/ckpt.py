@@ -68,8 +68,10 @@ def _remove(base: str) -> None:
 def save_checkpoint(train_dir: str, global_step: int, store, extra: Optional[Dict] = None,
                     max_to_keep: int = 5, opt_slots: Optional[Dict] = None,
                     fmt: str = "npz", prefix: str = "v0/") -> str:
-    """``fmt="npz"`` (default) or ``"tf"``: a TensorFlow V2 bundle (``model.ckpt-N.index`` +
-    ``.data-00000-of-00001``, see tf_bundle.py) the reference's Saver can restore."""
+    """``fmt="npz"`` (this function's default; one ``.npz`` file) or ``"tf"``: a TensorFlow V2
+    bundle (``model.ckpt-N.index`` + ``.data-00000-of-00001``, see tf_bundle.py) the reference's
+    Saver can restore. The benchmark driver passes ``--checkpoint_format``, whose default is
+    ``tf`` - the files the reference's train_dir holds."""
     os.makedirs(train_dir, exist_ok=True)
     arrays = store.to_tf_arrays(prefix)
     if opt_slots:
