@@ -97,6 +97,8 @@ struct GemmParams {
   long long acc_mask_ld;  // bytes per row
   const void* acc_src;    // host side only: the tensor map D is encoded over it
   long long acc_src_ld;   // elements per row
+  // SV3: rows are virtual pixels of (sc_Q = Q + 1)-wide rows; column sc_Q - 1 is a dummy
+  int sv3;
 };
 
 constexpr int kBlockM = 128;
@@ -124,6 +126,13 @@ struct TileCfg {
   static constexpr int kMaxFit = (kSmemBudget - kFixedBytes) / kStageBytes;
   static constexpr int max_stages() { return kMaxFit > kMaxStages ? kMaxStages : kMaxFit; }
   static constexpr int smem_bytes(int stages) { return stages * kStageBytes + kFixedBytes; }
+  // SV3 (shifted-view 3-tap rows, see the kernel): one stage = a (128 + 2)-pixel A box (17
+  // swizzle atoms reserved) plus the three B tiles of a filter row
+  static constexpr int kSv3ABytes = 17 * 1024;
+  static constexpr int kSv3StageBytes = kSv3ABytes + 3 * kTileBBytes;
+  static constexpr int kSv3MaxFit = (kSmemBudget - kFixedBytes) / kSv3StageBytes;
+  static constexpr int max_stages_sv3() { return kSv3MaxFit > kMaxStages ? kMaxStages : kSv3MaxFit; }
+  static constexpr int smem_bytes_sv3(int stages) { return stages * kSv3StageBytes + kFixedBytes; }
   // accumulating TMA-store epilogue: two 4 KiB tiles per epilogue warp receive the old values
   // of the output (TMA loads, prefetched while the MMA of the tile still runs)
   static constexpr int kOldBytes = kEpiWarps * 2 * 4096;
@@ -145,7 +154,18 @@ struct TileCfg {
 // ACC (with TMA_ST) = out += result: the old 32 x 64 chunks arrive by TMA load into shared memory
 // (issued before the wait for the accumulator, so their latency hides behind the MMA), are added
 // in fp32 and the sum leaves through the same TMA store; replaces the per-lane read-modify-write.
-template <int BN, int MODE, bool FAST, bool TMA_ST = false, bool ACC = false>
+// SV3 (FPROP / DGRAD, unit stride, three taps per filter row, C % 64 == 0): the im2col re-read
+// of the input - nine boxes per 3x3 tile, the L2->SM traffic that bounds these layers - drops
+// to three. The output is traversed as rows of Q + 1 virtual pixels (one dummy column after the
+// last real one), for which tap s of virtual pixel m is tap 0 of virtual pixel m + s - also
+// across a row end, where the wrapped pixel is the left padding column of the next row, i.e.
+// the same zeros as the right padding it stands for. So ONE TMA im2col box of 128 + 2 pixels
+// per filter row serves all three taps: the MMA reads tap s through a descriptor whose start
+// address is s rows (s x 128 B) into the box (tcgen05 applies the 128B swizzle to absolute
+// address bits, so a row-shifted start needs no re-layout and no base offset; measured on
+// B200). The dummy column is computed and dropped by the epilogue (1.8 % at Q = 56, 3.5 % at
+// 28, 7 % at 14).
+template <int BN, int MODE, bool FAST, bool TMA_ST = false, bool ACC = false, bool SV3 = false>
 __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                         const __grid_constant__ CUtensorMap tmB,
@@ -162,9 +182,11 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
+  constexpr int kABytes = SV3 ? Cfg::kSv3ABytes : kTileABytes;
+  constexpr int kBBytes = SV3 ? 3 * Cfg::kTileBBytes : Cfg::kTileBBytes;   // per stage
   uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem + kStages * kTileABytes;
-  uint8_t* staging = smem + kStages * Cfg::kStageBytes;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  uint8_t* staging = smem + kStages * (kABytes + kBBytes);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
   uint64_t* empty_bar = full_bar + kMaxStages;
   uint64_t* tmem_full_bar = empty_bar + kMaxStages;   // [2]
@@ -230,7 +252,10 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         // ---- per-tile constants and incremental counters (no divisions inside the K loop) ----
         // FPROP/DGRAD: kb -> (r, s, cb)
         int it_r = 0, it_s = 0, it_cb = 0;
-        if (MODE == FPROP || MODE == DGRAD) {
+        if (SV3) {  // K blocks are (filter row, channel block); the taps of a row share a box
+          it_r = kb_begin / p.CB;
+          it_cb = kb_begin - it_r * p.CB;
+        } else if (MODE == FPROP || MODE == DGRAD) {
           const int tap = kb_begin / p.CB;
           it_cb = kb_begin - tap * p.CB;
           it_r = tap / p.S;
@@ -269,10 +294,34 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         }
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem_a + stage * kTileABytes;
-          uint8_t* sb = smem_b + stage * Cfg::kTileBBytes;
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          if (MODE == GEMM_TN) {
+          uint8_t* sa = smem_a + stage * kABytes;
+          uint8_t* sb = smem_b + stage * kBBytes;
+          mbar_expect_tx(&full_bar[stage], SV3 ? (kBlockM + 2) * 128 + kBBytes : Cfg::kStageBytes);
+          if (SV3) {
+            // one box of 128 + 2 virtual pixels (tap offset 0 along w) for the filter row, and
+            // the weight tiles of its three taps
+            tma_load_im2col_4d(sa, &tmA, &full_bar[stage], it_cb * kBlockK, px_w, px_h, px_n,
+                               static_cast<uint16_t>(0), static_cast<uint16_t>(it_r));
+#pragma unroll
+            for (int ts = 0; ts < 3; ++ts) {
+              uint8_t* sbt = sb + ts * Cfg::kTileBBytes;
+              if (MODE == FPROP) {
+                tma_load_2d(sbt, &tmB, &full_bar[stage],
+                            (it_r * p.S + ts) * p.Ck + it_cb * kBlockK, n0);
+              } else {
+                const int wtap = (p.wt_r0 + p.wt_rstep * (p.R - 1 - it_r)) * p.wt_S +
+                                 (p.wt_s0 + p.wt_sstep * (p.S - 1 - ts));
+#pragma unroll
+                for (int j = 0; j < BN / 64; ++j)
+                  tma_load_3d(sbt + j * 8192, &tmB, &full_bar[stage], n0 + 64 * j, wtap,
+                              it_cb * kBlockK);
+              }
+            }
+            if (++it_cb == p.CB) {
+              it_cb = 0;
+              ++it_r;
+            }
+          } else if (MODE == GEMM_TN) {
             tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBlockK, m0);
             tma_load_2d(sb, &tmB, &full_bar[stage], kb * kBlockK, n0);
           } else if (MODE == GEMM_NN) {
@@ -361,8 +410,22 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem_a + stage * kTileABytes);
-          const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::kTileBBytes);
+          const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
+          const uint32_t b_addr = smem_u32(smem_b + stage * kBBytes);
+          if (SV3) {
+            // tap ts reads the box through a start address ts rows (128 B each) further on
+#pragma unroll
+            for (int ts = 0; ts < 3; ++ts) {
+#pragma unroll
+              for (int k = 0; k < kBlockK / 16; ++k) {
+                const uint64_t da =
+                    make_smem_desc_sw128(a_addr + ts * 128 + k * a_kstep, a_lbo, 1024);
+                const uint64_t db = make_smem_desc_sw128(
+                    b_addr + ts * Cfg::kTileBBytes + k * b_kstep, b_lbo, 1024);
+                umma_f16_ss(tmem_d, da, db, idesc, (kb > kb_begin || ts > 0 || k > 0) ? 1u : 0u);
+              }
+            }
+          } else
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
             const uint64_t da = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
@@ -462,8 +525,11 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
                    static_cast<long long>(pp) * p.sc_sh) *
                       p.sc_W +
                   p.sc_w0 + static_cast<long long>(qq) * p.sc_sw;
+        if (SV3 && qq == p.sc_Q - 1) row_off = -1;  // dummy column
       }
       if (row >= p.M) row_off = -1;  // marks an invalid row
+      // SV3: the dummy rows hold real numbers (not zeros): they must stay out of the statistics
+      const unsigned valid_rows = SV3 ? __ballot_sync(0xffffffffu, row_off >= 0) : 0xffffffffu;
       const long long base = static_cast<long long>(z) * p.split_stride + col_mem0;
       const int c_step = cols_per_chunk * kColSplit;
       const int c_first = col_part * cols_per_chunk;
@@ -597,6 +663,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll 8
           for (int r = 0; r < 32; ++r) {
+            if (SV3 && !((valid_rows >> r) & 1u)) continue;
             // the lane's two columns of row r (swizzled 16-byte pieces in the TMA-store layout)
             const uint8_t* sp =
                 (kTmaStoreMode && tma_store)
@@ -1030,6 +1097,45 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
   return 0;
 }
 
+// SV3 launch (FPROP / DGRAD, BN <= 128): per-lane epilogue (the virtual rows scatter to real
+// pixels), the deepest pipeline its 17 KiB + 3 B-tile stages allow.
+template <int BN, int MODE>
+static int launch_sv3_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams p, dim3 tiles,
+                          cudaStream_t stream) {
+  using Cfg = TileCfg<BN>;
+  static bool attr_set[16] = {false};  // per device
+  int dev = 0;
+  KFB_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 16 && !attr_set[dev]) {
+    KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE, true, false, false, true>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::smem_bytes_sv3(Cfg::max_stages_sv3())));
+    attr_set[dev] = true;
+  }
+  p.tma_store = 0;
+  p.stages = Cfg::max_stages_sv3();
+  p.m_tiles = (int)tiles.x;
+  p.n_tiles = (int)tiles.y;
+  p.splits = 1;
+  const long long total = (long long)tiles.x * tiles.y;
+  KFB_REQUIRE(total > 0 && total < (1ll << 31), "bad tile count %lld", total);
+  const int ctas = total < sm_count() ? (int)total : sm_count();
+  p.stats_rpn = (int)tiles.x < ctas ? (int)tiles.x : ctas;
+  gemm_tcgen05_kernel<BN, MODE, true, false, false, true>
+      <<<ctas, Cfg::kThreads, Cfg::smem_bytes_sv3(p.stages), stream>>>(tmA, tmB, tmA, tmA, p);
+  KFB_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <int MODE>
+static int launch_sv3(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
+                      dim3 grid, cudaStream_t stream) {
+  if (bn == 64) return launch_sv3_cfg<64, MODE>(tmA, tmB, p, grid, stream);
+  if (bn == 128) return launch_sv3_cfg<128, MODE>(tmA, tmB, p, grid, stream);
+  set_error("SV3: unsupported BN %d", bn);
+  return 2;
+}
+
 template <int MODE>
 static int launch_mode(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
                        dim3 grid, cudaStream_t stream) {
@@ -1082,6 +1188,24 @@ static int balanced_splits(int tiles, int num_kb, int sms) {
 }
 static void init_params(GemmParams* p) { memset(p, 0, sizeof(*p)); }
 
+// SV3 eligibility (see the kernel): three taps per filter row at unit stride with one padding
+// column on each side, whole 64-channel K blocks, 16-byte output pieces, tiles of at most 128
+// columns (three B tiles per stage must fit). KFB_SV3=0 switches the variant off.
+static int sv3_enabled() {
+  static const int v = env_knob("KFB_SV3", 1, 0, 1);
+  return v;
+}
+static bool sv3_fprop_ok(const kfb_conv_desc* d, int bn, long long ldy, const void* y) {
+  return sv3_enabled() && d->s == 3 && d->stride_h == 1 && d->stride_w == 1 &&
+         d->pad_w_lo == 1 && d->pad_w_hi == 1 && d->q == d->w && d->c % 64 == 0 && bn <= 128 &&
+         d->k % 8 == 0 && ldy % 8 == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0;
+}
+static bool sv3_dgrad_ok(const kfb_conv_desc* d, int bn, const void* dx) {
+  return sv3_enabled() && d->s == 3 && d->stride_h == 1 && d->stride_w == 1 &&
+         d->pad_w_lo == 1 && d->pad_w_hi == 1 && d->q == d->w && d->k % 64 == 0 && bn <= 128 &&
+         d->c % 8 == 0 && (reinterpret_cast<uintptr_t>(dx) & 15) == 0;
+}
+
 }  // namespace kfb
 
 using namespace kfb;
@@ -1103,6 +1227,15 @@ extern "C" int kfb_gemm_stats_layout(int M, int N, int num_kb, int* rows, int* b
   *rows = (int)(m_tiles < ctas ? m_tiles : ctas) * 4;
   *bn = b;
   return 0;
+}
+
+// The same for a convolution's forward GEMM (which may traverse virtual rows, SV3).
+extern "C" int kfb_conv_stats_layout(const kfb_conv_desc* d, long long ldy, int* rows, int* bn) {
+  KFB_REQUIRE(d != nullptr && rows != nullptr && bn != nullptr, "conv_stats_layout: bad arguments");
+  const int num_kb = d->r * d->s * ((d->c + 63) / 64);
+  const int b = pick_bn_for(d->k, num_kb);
+  const int M = sv3_fprop_ok(d, b, ldy, nullptr) ? d->n * d->p * (d->q + 1) : d->n * d->p * d->q;
+  return kfb_gemm_stats_layout(M, d->k, num_kb, rows, bn);
 }
 
 extern "C" int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, int K,
@@ -1292,9 +1425,14 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   const int M = d->n * d->p * d->q;
   const int bn = pick_bn_for(d->k, d->r * d->s * ((d->c + 63) / 64));
   CUtensorMap tmA, tmB;
+  const bool sv3 = sv3_fprop_ok(d, bn, ldy, y);
+  // the statistics layout was sized by kfb_conv_stats_layout(d, K) without the pointer
+  KFB_REQUIRE(stats == nullptr || sv3 == sv3_fprop_ok(d, bn, d->k, nullptr),
+              "conv_fprop: fused statistics need a 16-byte aligned output with ldy % 8 == 0");
+  const int Mv = d->n * d->p * (d->q + 1);  // SV3: rows of Q + 1 virtual pixels
   if (encode_im2col(&tmA, x, d->n, d->h, d->w, d->c, -d->pad_w_lo, -d->pad_h_lo,
-                    d->pad_w_hi - (d->s - 1), d->pad_h_hi - (d->r - 1), 64, 128, d->stride_w,
-                    d->stride_h))
+                    d->pad_w_hi - (d->s - 1) + (sv3 ? 1 : 0), d->pad_h_hi - (d->r - 1), 64,
+                    sv3 ? 130 : 128, d->stride_w, d->stride_h))
     return 1;
   const uint64_t Kt = (uint64_t)d->r * d->s * d->c;
   uint64_t db[2] = {Kt, (uint64_t)d->k}, sb[1] = {Kt * 2};
@@ -1322,6 +1460,20 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   p.bias = bias;
   p.relu = relu;
   p.stats = stats;
+  if (sv3) {
+    p.M = Mv;
+    p.Q = d->q + 1;
+    p.num_kb = d->r * p.CB;
+    p.kb_per_split = p.num_kb;
+    p.sc_P = d->p;
+    p.sc_Q = d->q + 1;
+    p.sc_H = d->p;
+    p.sc_W = d->q;
+    p.sc_sh = p.sc_sw = 1;
+    p.sv3 = 1;
+    dim3 grid_v((Mv + 127) / 128, (d->k + bn - 1) / bn, 1);
+    return launch_sv3<FPROP>(bn, tmA, tmB, p, grid_v, (cudaStream_t)stream);
+  }
   dim3 grid((M + 127) / 128, (d->k + bn - 1) / bn, 1);
   return launch_mode<FPROP>(bn, tmA, tmB, p, grid, (cudaStream_t)stream);
 }
@@ -1407,9 +1559,12 @@ static int conv_dgrad_impl(const kfb_conv_desc* d, const void* dy, const void* w
       KFB_REQUIRE(lower_h >= -128 && lower_w >= -128 && upper_h <= 127 && upper_w <= 127 &&
                       lower_h <= 127 && lower_w <= 127 && upper_h >= -128 && upper_w >= -128,
                   "conv_dgrad: geometry exceeds the TMA im2col corner range");
+      const int num_kb_taps = nR * nS * ((d->k + 63) / 64);
+      const bool sv3 = !strided && res_src == nullptr && nS == 3 && lower_w == -1 &&
+                       upper_w == -1 && sv3_dgrad_ok(d, pick_bn_for(d->c, num_kb_taps), dx);
       CUtensorMap tmA;
-      if (encode_im2col(&tmA, dy, d->n, d->p, d->q, d->k, lower_w, lower_h, upper_w, upper_h, 64,
-                        128, 1, 1))
+      if (encode_im2col(&tmA, dy, d->n, d->p, d->q, d->k, lower_w, lower_h,
+                        upper_w + (sv3 ? 1 : 0), upper_h, 64, sv3 ? 130 : 128, 1, 1))
         return 1;
       GemmParams p;
       init_params(&p);
@@ -1423,7 +1578,7 @@ static int conv_dgrad_impl(const kfb_conv_desc* d, const void* dy, const void* w
       p.num_kb = nR * nS * p.CB;
       p.kb_per_split = p.num_kb;
       const int bn = pick_bn_for(d->c, p.num_kb);
-          p.P = Hp;
+      p.P = Hp;
       p.Q = Wp;
       p.lower_h = lower_h;
       p.lower_w = lower_w;
@@ -1450,6 +1605,21 @@ static int conv_dgrad_impl(const kfb_conv_desc* d, const void* dy, const void* w
         p.sc_sw = d->stride_w;
         p.sc_h0 = ph;
         p.sc_w0 = pw;
+      }
+      if (sv3) {
+        p.M = d->n * Hp * (Wp + 1);
+        p.Q = Wp + 1;
+        p.num_kb = nR * p.CB;
+        p.kb_per_split = p.num_kb;
+        p.sc_P = Hp;
+        p.sc_Q = Wp + 1;
+        p.sc_H = d->h;
+        p.sc_W = d->w;
+        p.sc_sh = p.sc_sw = 1;
+        p.sv3 = 1;
+        dim3 grid_v((p.M + 127) / 128, (d->c + bn - 1) / bn, 1);
+        if (launch_sv3<DGRAD>(bn, tmA, tmB, p, grid_v, (cudaStream_t)stream)) return 1;
+        continue;
       }
       dim3 grid((p.M + 127) / 128, (d->c + bn - 1) / bn, 1);
       if (launch_mode<DGRAD>(bn, tmA, tmB, p, grid, (cudaStream_t)stream)) return 1;

@@ -45,6 +45,9 @@ int kfb_gemm_tn(const void* A, const void* B, void* C, int M, int N, int K, long
  * output disappears (the reference gets this from cuDNN's fused batch norm,
  * T/convnet_builder_legacy.py:418-431). */
 int kfb_gemm_stats_layout(int M, int N, int num_kb, int* rows, int* bn);
+/* The same for the forward GEMM of a convolution writing rows of `ldy` elements (3x3 unit-stride
+ * layers traverse rows of Q + 1 virtual pixels, so their tile count is not that of N*P*Q rows). */
+int kfb_conv_stats_layout(const kfb_conv_desc* d, long long ldy, int* rows, int* bn);
 
 /* C[M,N] (+)= A[M,K] * B[K,N]; B is consumed in place as an MN-major operand (FC dgrad). */
 int kfb_gemm_nn(const void* A, const void* B, void* C, int M, int N, int K, long long lda,

@@ -316,7 +316,8 @@ class CudaExecutor:
                 from ..ops import gemm_conv
                 num_kb = ((info["kpad"] + 63) // 64) if info["flat"] else \
                     a["kh"] * a["kw"] * ((c + 63) // 64)
-                rows_, bn_ = gemm_conv.stats_layout(node.output.rows, k, num_kb)
+                rows_, bn_ = gemm_conv.stats_layout(node.output.rows, k, num_kb) \
+                    if info["flat"] else gemm_conv.conv_stats_layout(d)
                 info["stats_layout"] = (rows_, bn_)
                 self._stats_need = max(self._stats_need, ((k + bn_ - 1) // bn_) * rows_ * 2 * bn_)
         elif node.op == "dwconv":

@@ -135,8 +135,13 @@ def stats_layout(m: int, n: int, num_kb: int):
     return rows.value, bn.value
 
 
-def conv_stats_layout(d: ConvDesc):
-    return stats_layout(d.n * d.p * d.q, d.k, d.r * d.s * ((d.c + 63) // 64))
+def conv_stats_layout(d: ConvDesc, ldy=None):
+    """(rows, bn) of the statistics conv_fprop writes for `d` into rows of `ldy` elements."""
+    rows, bn = ctypes.c_int(0), ctypes.c_int(0)
+    native.check(native.load().kfb_conv_stats_layout(ctypes.byref(d), i64(ldy or d.k),
+                                                     ctypes.byref(rows), ctypes.byref(bn)),
+                 "conv_stats_layout")
+    return rows.value, bn.value
 
 
 def stats_buffer(m: int, n: int, num_kb: int, device) -> torch.Tensor:

@@ -227,7 +227,8 @@ def test_graphed_step_control_flow_with_two_ranks(monkeypatch):
             self.step_count += 1
 
     ex = types.SimpleNamespace(set_inputs=lambda *a: None, forward=lambda train: None,
-                               loss_backward=lambda **kw: None)
+                               loss_backward=lambda **kw: None,
+                               push_step_values=lambda: None, step_index=0)
     b = types.SimpleNamespace(executor=ex, engine=Engine(), comm=comm, world=2, global_step=0,
                               device=torch.device("cpu"), dataset=types.SimpleNamespace(
                                   num_examples_per_epoch=lambda s: 1000),

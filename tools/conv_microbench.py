@@ -1,0 +1,55 @@
+#!/usr/bin/env python
+"""Device time of the convolution kernels on ResNet-50's 3x3 layers (batch 256), one line per
+(layer, pass). Inputs are larger than L2 for stages 1-2 and rotated over four buffers otherwise.
+
+    KFB_SV3=0 python tools/conv_microbench.py      # nine im2col boxes per 3x3 tile
+    KFB_SV3=1 python tools/conv_microbench.py      # three (shifted-view rows)
+"""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+
+def main():
+    from kf_benchmarks_b200.ops import gemm_conv as gc
+    n = int(os.environ.get("BATCH", "256"))
+    shapes = [(56, 64), (28, 128), (14, 256), (7, 512)]
+    iters = 20
+    for hw, c in shapes:
+        xs = [torch.randn(n, hw, hw, c, device="cuda").half() for _ in range(4)]
+        dys = [torch.randn(n, hw, hw, c, device="cuda").half() for _ in range(4)]
+        w = (torch.randn(c, 3, 3, c, device="cuda") * (9 * c) ** -0.5).half()
+        d = gc.make_desc(xs[0].shape, w.shape, (1, 1), (1, 1), (1, 1))
+        out = torch.empty(n, hw, hw, c, device="cuda", dtype=torch.float16)
+        srows, sbn = gc.conv_stats_layout(d)
+        stats = torch.empty(((c + sbn - 1) // sbn, srows, 2, sbn), device="cuda")
+        passes = {
+            "fprop": lambda i: gc.conv_fprop(xs[i % 4], w, d, out=out),
+            "fprop+stats": lambda i: gc.conv_fprop(xs[i % 4], w, d, out=out, stats=stats),
+            "dgrad": lambda i: gc.conv_dgrad(dys[i % 4], w, d, out=out),
+            "wgrad": lambda i: gc.conv_wgrad(xs[i % 4], dys[i % 4], d),
+        }
+        flops = 2.0 * n * hw * hw * c * c * 9
+        for name, fn in passes.items():
+            for i in range(3):
+                fn(i)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(iters):
+                fn(i)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            print(json.dumps({"layer": f"3x3_{hw}_c{c}", "pass": name, "ms": round(ms, 4),
+                              "tflops": round(flops / ms / 1e9, 1),
+                              "sv3": os.environ.get("KFB_SV3", "1")}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
