@@ -463,6 +463,43 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     uint32_t old_issued = 0, old_used = 0;             // chunk loads issued / consumed so far
     const int esize = p.out_fp32 ? 4 : 2;
     const int cols_per_chunk = 128 / esize;  // 32 (fp32) or 64 (fp16)
+    // ACC: a prefetch cursor runs ahead of the chunk being processed - also into the next tiles
+    // of this CTA - so that the old values (TMA) and the mask words (one 8-byte load per lane)
+    // of a chunk are requested two chunks before they are used; tiles of one K block (1x1
+    // layers) have no main loop to hide that latency behind otherwise.
+    int pf_tile = blockIdx.x, pf_k = 0;
+    unsigned long long pf_mask0 = ~0ull, pf_mask1 = ~0ull;
+    auto pump_old = [&]() {
+      const int cstep = cols_per_chunk * kColSplit, cfirst = col_part * cols_per_chunk;
+      while (old_issued - old_used < 2u && pf_tile < total_tiles) {
+        const int nb = pf_tile / p.m_tiles;  // the accumulating epilogue has no K splits
+        const int pm0 = (pf_tile - nb * p.m_tiles) * kBlockM;
+        const int pcol0 = nb * BN;
+        int lim = p.N - pcol0;
+        if (lim > BN) lim = BN;
+        int chunks = 0;
+        if (pm0 + quarter * 32 < p.M && cfirst < lim) chunks = (lim - cfirst + cstep - 1) / cstep;
+        if (pf_k >= chunks) {
+          pf_tile += gridDim.x;
+          pf_k = 0;
+          continue;
+        }
+        const int slot = old_issued & 1;
+        const int ccol = pcol0 + cfirst + pf_k * cstep;
+        if (lane == 0) {
+          mbar_expect_tx(&my_old_bar[slot], 4096);
+          tma_load_2d(old_buf + slot * 4096, &tmD, &my_old_bar[slot], ccol, pm0 + quarter * 32);
+        }
+        unsigned long long mb = ~0ull;
+        const int prow = pm0 + quarter * 32 + lane;
+        if (p.acc_mask != nullptr && prow < p.M)
+          mb = *reinterpret_cast<const unsigned long long*>(
+              p.acc_mask + static_cast<long long>(prow) * p.acc_mask_ld + (ccol >> 3));
+        if (slot) pf_mask1 = mb; else pf_mask0 = mb;
+        ++old_issued;
+        ++pf_k;
+      }
+    };
     // fused BN statistics: lane owns columns (2*lane, 2*lane+1) of each 64-wide chunk it handles
     constexpr int kStatChunks = (BN / 64) / kColSplit > 0 ? (BN / 64) / kColSplit : 1;
     float st_sum[kStatChunks][2], st_sq[kStatChunks][2];
@@ -533,26 +570,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       const long long base = static_cast<long long>(z) * p.split_stride + col_mem0;
       const int c_step = cols_per_chunk * kColSplit;
       const int c_first = col_part * cols_per_chunk;
-      // ACC: number of chunks this warp handles in this tile; the first two old tiles are
-      // requested now, while the MMA of this tile may still be running
-      int my_chunks = 0;
-      auto issue_old = [&](int k) {
-        // chunk k of this tile -> old_buf[old_issued & 1]
-        if (lane == 0) {
-          uint64_t* bar = &my_old_bar[old_issued & 1];
-          mbar_expect_tx(bar, 4096);
-          tma_load_2d(old_buf + (old_issued & 1) * 4096, &tmD, bar, col_mem0 + c_first + k * c_step,
-                      m0 + quarter * 32);
-        }
-        ++old_issued;
-      };
       // rows of this warp beyond M are never stored: nothing is loaded for them either
       const bool acc_on = ACC && (m0 + quarter * 32 < p.M);
-      if (acc_on) {
-        const int lim = n_limit < BN ? n_limit : BN;
-        if (c_first < lim) my_chunks = (lim - c_first + c_step - 1) / c_step;
-        for (int k = 0; k < my_chunks && k < 2; ++k) issue_old(k);
-      }
+      if (ACC) pump_old();
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t tmem_acc = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -602,11 +622,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
               // the old values of this chunk have landed (phase = use count of the buffer / 2)
               mbar_wait(&my_old_bar[old_used & 1], (old_used >> 1) & 1);
             }
-            // masked source: the 64 mask bits of this thread's row for the chunk (8 bytes)
-            unsigned long long mbits = ~0ull;
-            if (ACC && acc_on && p.acc_mask != nullptr && row < p.M)
-              mbits = *reinterpret_cast<const unsigned long long*>(
-                  p.acc_mask + static_cast<long long>(row) * p.acc_mask_ld + ((col_mem0 + c0) >> 3));
+            // masked source: the 64 mask bits of this thread's row for the chunk (requested
+            // together with the old values)
+            const unsigned long long mbits = (old_used & 1) ? pf_mask1 : pf_mask0;
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
               const int piece = h * 4 + (j >> 3);
@@ -691,10 +709,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           __syncwarp();
           if (acc_on) {
             // every lane has read the old tile (ordered by the fence + syncwarp above): its
-            // buffer takes the old values of the chunk after next
-            const int k_done = (c0 - c_first) / c_step;
+            // buffer takes the old values of the chunk after next (of this or a later tile)
             ++old_used;
-            if (k_done + 2 < my_chunks) issue_old(k_done + 2);
+            pump_old();
           }
           if (lane == 0 && m0 + quarter * 32 < p.M) {
             tma_store_2d(&tmC, smem_u32(stage_buf), col_mem0 + c0, m0 + quarter * 32);
@@ -971,9 +988,12 @@ static int encode_tiled(CUtensorMap* m, const void* ptr, int rank, const uint64_
 // NHWC fp16 activation viewed as {C, W, H, N}; im2col traversal.
 static int encode_im2col(CUtensorMap* m, const void* ptr, int N, int H, int W, int C, int lower_w,
                          int lower_h, int upper_w, int upper_h, int channels_per_pixel,
-                         int pixels_per_column, int stride_w, int stride_h) {
+                         int pixels_per_column, int stride_w, int stride_h, int pix_stride = 0,
+                         int row_stride = 0) {
   cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t gstr[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  const cuuint64_t ps = pix_stride > 0 ? (cuuint64_t)pix_stride : (cuuint64_t)C;
+  const cuuint64_t rs = row_stride > 0 ? (cuuint64_t)row_stride : (cuuint64_t)W * ps;
+  cuuint64_t gstr[3] = {ps * 2, rs * 2, (cuuint64_t)H * rs * 2};
   int lower[2] = {lower_w, lower_h};
   int upper[2] = {upper_w, upper_h};
   cuuint32_t es[4] = {1, (cuuint32_t)stride_w, (cuuint32_t)stride_h, 1};
@@ -1407,6 +1427,9 @@ static int check_conv(const kfb_conv_desc* d, const char* who) {
   KFB_REQUIRE(d->c % 8 == 0 && d->k % 8 == 0, "%s: C (%d) and Cout (%d) must be multiples of 8",
               who, d->c, d->k);
   KFB_REQUIRE(d->n > 0 && d->h > 0 && d->w > 0 && d->p > 0 && d->q > 0, "%s: bad geometry", who);
+  KFB_REQUIRE(d->x_pix_stride >= 0 && d->x_row_stride >= 0 && d->x_pix_stride % 8 == 0 &&
+                  d->x_row_stride % 8 == 0,
+              "%s: input strides must be multiples of 8 elements", who);
   const int up_h = d->pad_h_hi - (d->r - 1), up_w = d->pad_w_hi - (d->s - 1);
   KFB_REQUIRE(d->pad_h_lo <= 127 && d->pad_w_lo <= 127 && up_h >= -128 && up_w >= -128,
               "%s: padding/filter exceed the TMA im2col corner range", who);
@@ -1432,7 +1455,7 @@ extern "C" int kfb_conv_fprop(const kfb_conv_desc* d, const void* x, const void*
   const int Mv = d->n * d->p * (d->q + 1);  // SV3: rows of Q + 1 virtual pixels
   if (encode_im2col(&tmA, x, d->n, d->h, d->w, d->c, -d->pad_w_lo, -d->pad_h_lo,
                     d->pad_w_hi - (d->s - 1) + (sv3 ? 1 : 0), d->pad_h_hi - (d->r - 1), 64,
-                    sv3 ? 130 : 128, d->stride_w, d->stride_h))
+                    sv3 ? 130 : 128, d->stride_w, d->stride_h, d->x_pix_stride, d->x_row_stride))
     return 1;
   const uint64_t Kt = (uint64_t)d->r * d->s * d->c;
   uint64_t db[2] = {Kt, (uint64_t)d->k}, sb[1] = {Kt * 2};
@@ -1538,6 +1561,8 @@ static int conv_dgrad_impl(const kfb_conv_desc* d, const void* dy, const void* w
                            int accumulate, const void* res_src, long long res_ld,
                            const unsigned char* res_mask, long long res_mask_ld, void* stream) {
   if (check_conv(d, "conv_dgrad")) return 2;
+  KFB_REQUIRE(d->x_pix_stride == 0 && d->x_row_stride == 0,
+              "conv_dgrad: a strided (overlapping) input view has no data gradient");
   if (load_driver_fns()) return 1;
   CUtensorMap tmB;
   uint64_t db[3] = {(uint64_t)d->c, (uint64_t)d->r * d->s, (uint64_t)d->k};
@@ -1675,7 +1700,7 @@ static int conv_wgrad_impl(const kfb_conv_desc* d, const void* x, const void* dy
   if (encode_tiled(&tmA, dy, 2, da, sa, bx)) return 1;
   if (encode_im2col(&tmB, x, d->n, d->h, d->w, d->c, -d->pad_w_lo, -d->pad_h_lo,
                     d->pad_w_hi - (d->s - 1), d->pad_h_hi - (d->r - 1), 64, 64, d->stride_w,
-                    d->stride_h))
+                    d->stride_h, d->x_pix_stride, d->x_row_stride))
     return 1;
   GemmParams p;
   init_params(&p);

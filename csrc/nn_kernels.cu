@@ -623,6 +623,68 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Max pooling forward with a compile-time window, packed: the eight channels of a vector stay
+// four half2 words - HSETP2 mask, HMNMX2 and one LOP3 for the arg-max lanes per tap and word,
+// no fp32 conversions. The scalar kernel above spends ~300 instructions per output vector of a
+// 3x3 window and is issue-bound at a third of the HBM roof on ResNet's stem pool.
+template <int TK, int TS>
+__global__ void __launch_bounds__(256)
+    pool_fwd_max_packed_kernel(const __half* __restrict__ x, long long ldx,
+                               __half* __restrict__ y, long long ldy,
+                               unsigned char* __restrict__ argmax, PoolGeom g) {
+  const int vpr = g.c >> 3;
+  for (int n = blockIdx.z; n < g.n; n += gridDim.z)
+  for (int p = blockIdx.y; p < g.p; p += gridDim.y)
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < g.q * vpr;
+       t += gridDim.x * blockDim.x) {
+    const int q = t / vpr;
+    const int cv = t - q * vpr;
+    const int h0 = p * TS - g.pad_h, w0 = q * TS - g.pad_w;
+    uint4 v[TK * TK];
+    bool ok[TK * TK];
+#pragma unroll
+    for (int r = 0; r < TK; ++r) {
+#pragma unroll
+      for (int s = 0; s < TK; ++s) {
+        const int hh = h0 + r, ww = w0 + s;
+        ok[r * TK + s] = hh >= 0 && hh < g.h && ww >= 0 && ww < g.w;
+        if (ok[r * TK + s])
+          v[r * TK + s] = *reinterpret_cast<const uint4*>(
+              x + ((static_cast<long long>(n) * g.h + hh) * g.w + ww) * ldx + cv * 8);
+      }
+    }
+    unsigned acc[4], arg[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      acc[k] = 0xFC00FC00u;  // -inf, -inf
+      arg[k] = 0u;
+    }
+    unsigned first = 0xFFFFFFFFu;  // the first in-bounds tap always wins (as the scalar kernel)
+#pragma unroll
+    for (int tap = 0; tap < TK * TK; ++tap) {
+      if (!ok[tap]) continue;
+      const unsigned w4[4] = {v[tap].x, v[tap].y, v[tap].z, v[tap].w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const __half2 a = *reinterpret_cast<const __half2*>(&acc[k]);
+        const __half2 b = *reinterpret_cast<const __half2*>(&w4[k]);
+        const unsigned m = __hgt2_mask(b, a) | first;
+        acc[k] = (acc[k] & ~m) | (w4[k] & m);
+        arg[k] = (arg[k] & ~m) | ((static_cast<unsigned>(tap) * 0x00010001u) & m);
+      }
+      first = 0u;
+    }
+    const long long orow = (static_cast<long long>(n) * g.p + p) * g.q + q;
+    *reinterpret_cast<uint4*>(y + orow * ldy + cv * 8) = make_uint4(acc[0], acc[1], acc[2], acc[3]);
+    if (argmax != nullptr) {
+      uint2 packed;
+      packed.x = __byte_perm(arg[0], arg[1], 0x6420);
+      packed.y = __byte_perm(arg[2], arg[3], 0x6420);
+      *reinterpret_cast<uint2*>(argmax + orow * g.c + cv * 8) = packed;
+    }
+  }
+}
+
 // Gather formulation: one thread per input vector visits the output windows that cover it.
 template <int TK, int TS>
 __global__ void __launch_bounds__(256)
@@ -784,6 +846,89 @@ __global__ void __launch_bounds__(256)
       for (int k = 0; k < 8; ++k) acc[k] += old[k];
     }
     store8(o, acc);
+  }
+}
+
+// 3x3 / 2 max-pool backward, one thread per 2x2 block of input pixels and channel vector. The
+// gather kernel above loads up to four windows (gradient + arg-max, 24 B each) for every input
+// pixel - 2.25 valid ones on average, 2.4 GB of L2 -> SM traffic for ResNet's stem pool at batch
+// 256, which is what bounded it. The four pixels of a block (padded coordinates 2a..2a+1,
+// 2b..2b+1) are covered by the same four windows (a-1..a, b-1..b): they are loaded once, and
+// the nine (window, pixel) pairs are resolved in registers with the same SWAR byte compare.
+__global__ void __launch_bounds__(256)
+    pool_bwd_max3s2_block_kernel(const __half* __restrict__ dy, long long lddy,
+                                 const unsigned char* __restrict__ argmax,
+                                 __half* __restrict__ dx, long long lddx, int accumulate,
+                                 PoolGeom g) {
+  const int vpr = g.c >> 3;
+  const int nb_w = (g.w + g.pad_w + 1) >> 1, nb_h = (g.h + g.pad_h + 1) >> 1;
+  for (int n = blockIdx.z; n < g.n; n += gridDim.z)
+  for (int a = blockIdx.y; a < nb_h; a += gridDim.y)
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nb_w * vpr;
+       t += gridDim.x * blockDim.x) {
+    const int b = t / vpr;
+    const int cv = t - b * vpr;
+    uint4 dv[4];
+    uint2 am[4];
+#pragma unroll
+    for (int jp = 0; jp < 2; ++jp) {
+#pragma unroll
+      for (int jq = 0; jq < 2; ++jq) {
+        const int p = a - jp, q = b - jq;
+        const int idx = jp * 2 + jq;
+        dv[idx] = make_uint4(0u, 0u, 0u, 0u);
+        am[idx] = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);  // matches no tap
+        if (p >= 0 && p < g.p && q >= 0 && q < g.q) {
+          const long long orow = (static_cast<long long>(n) * g.p + p) * g.q + q;
+          dv[idx] = *reinterpret_cast<const uint4*>(dy + orow * lddy + cv * 8);
+          am[idx] = *reinterpret_cast<const uint2*>(argmax + orow * g.c + cv * 8);
+        }
+      }
+    }
+#pragma unroll
+    for (int dh = 0; dh < 2; ++dh) {
+      const int hh = 2 * a + dh - g.pad_h;
+      if (hh < 0 || hh >= g.h) continue;
+#pragma unroll
+      for (int dw = 0; dw < 2; ++dw) {
+        const int ww = 2 * b + dw - g.pad_w;
+        if (ww < 0 || ww >= g.w) continue;
+        __half2 hacc[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) hacc[k] = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+        for (int jp = 0; jp < 2 - dh; ++jp) {
+#pragma unroll
+          for (int jq = 0; jq < 2 - dw; ++jq) {
+            const int idx = jp * 2 + jq;
+            const unsigned tapv =
+                static_cast<unsigned>((dh + 2 * jp) * 3 + dw + 2 * jq) * 0x01010101u;
+            const unsigned e0 = am[idx].x ^ tapv, e1 = am[idx].y ^ tapv;
+            const unsigned z0 = ~(((e0 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | e0 | 0x7F7F7F7Fu);
+            const unsigned z1 = ~(((e1 & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | e1 | 0x7F7F7F7Fu);
+            const unsigned b0 = (z0 >> 7) * 0xFFu, b1 = (z1 >> 7) * 0xFFu;
+            unsigned w[4];
+            w[0] = dv[idx].x & __byte_perm(b0, 0, 0x1100);
+            w[1] = dv[idx].y & __byte_perm(b0, 0, 0x3322);
+            w[2] = dv[idx].z & __byte_perm(b1, 0, 0x1100);
+            w[3] = dv[idx].w & __byte_perm(b1, 0, 0x3322);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              hacc[k] = __hadd2(hacc[k], *reinterpret_cast<const __half2*>(&w[k]));
+          }
+        }
+        __half* o = dx + ((static_cast<long long>(n) * g.h + hh) * g.w + ww) * lddx + cv * 8;
+        if (accumulate) {
+          const Half8 old = *reinterpret_cast<const Half8*>(o);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) hacc[k] = __hadd2(hacc[k], old.h[k]);
+        }
+        Half8 outv;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) outv.h[k] = hacc[k];
+        *reinterpret_cast<Half8*>(o) = outv;
+      }
+    }
   }
 }
 
@@ -1402,7 +1547,19 @@ extern "C" int kfb_pool_forward(const void* x, long long ldx, void* y, long long
   if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
   const dim3 blocks = pool_grid(q * (c / 8), p, n);
   cudaStream_t st = (cudaStream_t)stream;
-  if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
+  static const int packed_form = env_int("KFB_POOL_FWD_PACKED", 1, 0, 1);
+  if (is_max && packed_form && kh == kw && sh == sw &&
+      ((kh == 3 && sh == 2) || (kh == 2 && sh == 2) || (kh == 3 && sh == 1))) {
+    if (kh == 3 && sh == 2)
+      pool_fwd_max_packed_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y,
+                                                               ldy, argmax, g);
+    else if (kh == 2)
+      pool_fwd_max_packed_kernel<2, 2><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y,
+                                                               ldy, argmax, g);
+    else
+      pool_fwd_max_packed_kernel<3, 1><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y,
+                                                               ldy, argmax, g);
+  } else if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
     pool_fwd_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)x, ldx, (__half*)y, ldy, argmax,
                                                   g, is_max);
   else if (kh == 2 && kw == 2 && sh == 2 && sw == 2)
@@ -1426,7 +1583,13 @@ extern "C" int kfb_pool_backward(const void* dy, long long lddy, const unsigned 
   if (fill_pool(&g, n, h, w, c, p, q, kh, kw, sh, sw, pad_h, pad_w)) return 2;
   const dim3 blocks = pool_grid(w * (c / 8), h, n);
   cudaStream_t st = (cudaStream_t)stream;
-  if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
+  static const int block_form = env_int("KFB_POOL_BWD_BLOCK", 1, 0, 1);
+  if (kh == 3 && kw == 3 && sh == 2 && sw == 2 && is_max && pad_h >= 0 && pad_w >= 0 &&
+      block_form) {
+    const dim3 bb = pool_grid(((w + pad_w + 1) / 2) * (c / 8), (h + pad_h + 1) / 2, n);
+    pool_bwd_max3s2_block_kernel<<<bb, 256, 0, st>>>((const __half*)dy, lddy, argmax,
+                                                      (__half*)dx, lddx, accumulate, g);
+  } else if (kh == 3 && kw == 3 && sh == 2 && sw == 2)
     pool_bwd_kernel<3, 2><<<blocks, 256, 0, st>>>((const __half*)dy, lddy, argmax, (__half*)dx,
                                                   lddx, accumulate, g, is_max);
   else if (kh == 2 && kw == 2 && sh == 2 && sw == 2)

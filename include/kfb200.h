@@ -29,6 +29,10 @@ typedef struct {
   int pad_w_lo, pad_w_hi;
   int stride_h, stride_w;
   int p, q;                /* output spatial size */
+  /* element strides of the input between neighbouring pixels / rows; 0 = dense (c and w*c). A
+   * pixel stride smaller than c makes neighbouring pixels overlap: the space-to-depth stem reads
+   * four 16-channel pixels as one 64-channel pixel this way (kfb_stem_s2d). fprop / wgrad only. */
+  int x_pix_stride, x_row_stride;
 } kfb_conv_desc;
 
 /* C[M,N] = A[M,K] * B[N,K]^T (+bias[N]) (ReLU). fp16 in, fp16 or fp32 out.
@@ -198,6 +202,19 @@ int kfb_copy_rows(const void* src, long long lds, void* dst, long long ldd, long
 /* Explicit im2col for stems whose input channel count is not a multiple of 8. */
 int kfb_im2col_small_c(const void* x, void* col, int n, int h, int w, int c, int p, int q, int kh,
                        int kw, int sh, int sw, int pad_h, int pad_w, int kpad, void* stream);
+/* Space-to-depth stem (csrc/stem_s2d.cu): a stride-2 convolution on C <= 4 channels with
+ * ceil(S/2) == 4 runs as a ceil(R/2) x 1 unit-stride convolution over 64-"channel" pixels that
+ * are four overlapping 16-channel pixels of the regrouped image (kfb_conv_desc.x_pix_stride = 16).
+ * kfb_stem_s2d writes y[n, h2, w2p, 16] (expand = 0; eh / ew = parity of the low padding, lw =
+ * zero pixels on the left) or the materialised [n, h2, q, 64] form (expand = 1);
+ * kfb_stem_pack_w / kfb_stem_unpack_dw convert [K, kpad] weights / gradients (columns
+ * (r*S + s)*C + c) to and from [K, ceil(R/2), 64]. */
+int kfb_stem_s2d(const void* x, void* y, int n, int h, int w, int c, int h2, int w2p, int eh,
+                 int ew, int lw, int expand, int q, void* stream);
+int kfb_stem_pack_w(const void* w, void* w4, int k, int kpad, int r, int s, int c, int ta,
+                    void* stream);
+int kfb_stem_unpack_dw(const float* dw4, float* dw, int k, int kpad, int r, int s, int c, int ta,
+                       int accumulate, float scale, void* stream);
 /* Philox dropout; the backward pass calls it again on dy with the same (seed, offset). */
 int kfb_dropout(const void* x, void* y, long long n, float keep_prob, unsigned long long seed,
                 unsigned long long offset, void* stream);

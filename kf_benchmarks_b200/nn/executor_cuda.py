@@ -285,12 +285,26 @@ class CudaExecutor:
             info["dgrad_zero_fill"] = bool(
                 native.load().kfb_conv_dgrad_needs_zero_fill(ctypes.byref(d)))
             info["flat"] = spec.kind == "conv_kernel_flat"
+            info["s2d"] = None
             if info["flat"]:
+                from ..ops import stem
                 kpad = spec.shape[1]
                 info["kpad"] = kpad
-                info["col"] = torch.zeros((n * d.p * d.q, kpad), dtype=torch.float16, device=dev)
-                m_rows = n * d.p * d.q
-                self._ws_need = max(self._ws_need, self._nt_ws(k, kpad))
+                if stem.eligible(d) and not self.needs_grad.get(x.id, False):
+                    # 7x7/2 stems: space-to-depth + overlapping-pixel TMA view (ops/stem.py)
+                    # instead of the explicit column buffer (976 MB at batch 256)
+                    pl = stem.plan(d, kpad)
+                    info["s2d"] = pl
+                    info["s2d_x"] = torch.zeros(pl.s2d_shape(), dtype=torch.float16, device=dev)
+                    info["s2d_w"] = torch.zeros((k, pl.ta, 64), dtype=torch.float16, device=dev)
+                    info["s2d_dw"] = torch.zeros((k, pl.ta, 64), dtype=torch.float32, device=dev)
+                    fn = native.load().kfb_conv_wgrad_workspace_bytes
+                    fn.restype = ctypes.c_longlong
+                    self._ws_need = max(self._ws_need, int(fn(ctypes.byref(pl.desc))))
+                else:
+                    info["col"] = torch.zeros((n * d.p * d.q, kpad), dtype=torch.float16,
+                                              device=dev)
+                    self._ws_need = max(self._ws_need, self._nt_ws(k, kpad))
             else:
                 fn = native.load().kfb_conv_wgrad_workspace_bytes
                 fn.restype = ctypes.c_longlong
@@ -316,8 +330,12 @@ class CudaExecutor:
                 from ..ops import gemm_conv
                 num_kb = ((info["kpad"] + 63) // 64) if info["flat"] else \
                     a["kh"] * a["kw"] * ((c + 63) // 64)
-                rows_, bn_ = gemm_conv.stats_layout(node.output.rows, k, num_kb) \
-                    if info["flat"] else gemm_conv.conv_stats_layout(d)
+                if info["s2d"] is not None:
+                    rows_, bn_ = gemm_conv.conv_stats_layout(info["s2d"].desc)
+                elif info["flat"]:
+                    rows_, bn_ = gemm_conv.stats_layout(node.output.rows, k, num_kb)
+                else:
+                    rows_, bn_ = gemm_conv.conv_stats_layout(d)
                 info["stats_layout"] = (rows_, bn_)
                 self._stats_need = max(self._stats_need, ((k + bn_ - 1) // bn_) * rows_ * 2 * bn_)
         elif node.op == "dwconv":
@@ -527,7 +545,14 @@ class CudaExecutor:
         kname = node.params["kernel"].name
         # the batch-norm that immediately follows gets its statistics from the conv epilogue
         stats = ptr(self.stats_buf) if (train and info.get("fuse_stats")) else None
-        if info["flat"]:
+        if info["s2d"] is not None:
+            from ..ops import stem
+            pl = info["s2d"]
+            stem.regroup(pl, x.t, info["s2d_x"], s)
+            stem.pack_weights(pl, self.store.view(kname, "w16"), info["s2d_w"], s)
+            native.call("conv_fprop", ctypes.byref(pl.desc), ptr(info["s2d_x"]),
+                        ptr(info["s2d_w"]), y.p, i64(y.ld), bias, relu, stats, s)
+        elif info["flat"]:
             col = info["col"]
             native.call("im2col_small_c", x.p, ptr(col), i32(d.n), i32(d.h), i32(d.w), i32(d.c),
                         i32(d.p), i32(d.q), i32(d.r), i32(d.s), i32(d.stride_h), i32(d.stride_w),
@@ -925,6 +950,14 @@ class CudaExecutor:
         if info["flat"]:
             if self.needs_grad[xin.id]:
                 raise NotImplementedError("input gradient of a tiny-C stem conv is not built")
+            if info["s2d"] is not None:
+                from ..ops import stem
+                pl = info["s2d"]
+                native.call("conv_wgrad", ctypes.byref(pl.desc), ptr(info["s2d_x"]), gy.p,
+                            i64(gy.ld), ptr(info["s2d_dw"]), ptr(self.workspace),
+                            i64(self.workspace.numel() * 4), i32(0), f32(1.0), s)
+                stem.unpack_grad(pl, info["s2d_dw"], self.store.view(kname, "grad"), False, 1.0, s)
+                return
             col = info["col"]
             push = self.push_lookup(kname) if self.push_lookup else None
             if push is not None:
@@ -1157,7 +1190,8 @@ class CudaExecutor:
         names = []
         for node in self.graph.nodes:
             if node.op == "conv":
-                names.append(node.params["kernel"].name)
+                if self._per_node[id(node)].get("s2d") is None:   # the s2d stem unpacks locally
+                    names.append(node.params["kernel"].name)
             elif node.op == "affine":
                 names.append(node.params["weights"].name)
         return names

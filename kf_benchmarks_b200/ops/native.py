@@ -32,7 +32,7 @@ class ConvDesc(ctypes.Structure):
     """Mirror of ``kfb_conv_desc`` in include/kfb200.h."""
     _fields_ = [(name, ctypes.c_int) for name in (
         "n", "h", "w", "c", "k", "r", "s", "pad_h_lo", "pad_h_hi", "pad_w_lo", "pad_w_hi",
-        "stride_h", "stride_w", "p", "q")]
+        "stride_h", "stride_w", "p", "q", "x_pix_stride", "x_row_stride")]
 
 
 def lib_path() -> str:

@@ -112,10 +112,12 @@ def test_bn_forward_backward(rows, c, relu, res, scale, form):
 
 @pytest.mark.parametrize("kind,k,s,pad", [("max", 3, 2, "SAME"), ("max", 2, 2, "VALID"),
                                           ("avg", 3, 1, "SAME"), ("avg", 2, 2, "VALID"),
-                                          ("max", 3, 2, "VALID"), ("avg", 1, 2, "VALID")])
-def test_pool(kind, k, s, pad):
+                                          ("max", 3, 2, "VALID"), ("avg", 1, 2, "VALID"),
+                                          ("max", 3, 1, "SAME")])
+@pytest.mark.parametrize("hw", [(15, 15), (16, 22)])
+def test_pool(kind, k, s, pad, hw):
     from kf_benchmarks_b200.nn.builder import out_size, resolve_padding
-    n, h, w, c = 2, 15, 15, 24
+    n, (h, w), c = 2, hw, 24
     g = torch.Generator(device="cuda").manual_seed(1)
     x = torch.randn(n, h, w, c, device="cuda", generator=g).half()
     ph, pw = resolve_padding(pad, h, k, s), resolve_padding(pad, w, k, s)

@@ -85,6 +85,21 @@ case("dgrad_res_1x1_c512_k128_tail", "dgrad", n=3, h=13, w=13, c=512, k=128, r=1
      pad="SAME", res=True)
 case("dgrad_res_3x3_c64_k64", "dgrad", n=2, h=28, w=28, c=64, k=64, r=3, s=3, stride=1,
      pad="SAME", res=True)
+# space-to-depth stem (ops/stem.py): forward and weight gradient against conv2d
+case("stem_s2d_fprop_7x7_s2_c3_k64", "stem_s2d", n=2, h=64, w=64, c=3, k=64, r=7, s=7, stride=2,
+     pad="SAME_RESNET")
+case("stem_s2d_wgrad_7x7_s2_c3_k64", "stem_s2d", n=2, h=64, w=64, c=3, k=64, r=7, s=7, stride=2,
+     pad="SAME_RESNET", wgrad=True)
+case("stem_s2d_fprop_7x7_s2_c3_k32_odd_same", "stem_s2d", n=3, h=45, w=51, c=3, k=32, r=7, s=7,
+     stride=2, pad="SAME")
+case("stem_s2d_wgrad_7x7_s2_c3_k32_odd_same", "stem_s2d", n=3, h=45, w=51, c=3, k=32, r=7, s=7,
+     stride=2, pad="SAME", wgrad=True)
+case("stem_s2d_fprop_7x7_s2_c3_k64_same_even_pad", "stem_s2d", n=2, h=32, w=32, c=3, k=64, r=7,
+     s=7, stride=2, pad="SAME")
+case("stem_s2d_wgrad_7x7_s2_c3_k64_same_even_pad", "stem_s2d", n=2, h=32, w=32, c=3, k=64, r=7,
+     s=7, stride=2, pad="SAME", wgrad=True)
+case("stem_s2d_wgrad_5x7_s2_c4_k64_valid", "stem_s2d", n=2, h=40, w=40, c=4, k=64, r=5, s=7,
+     stride=2, pad="VALID", wgrad=True)
 # headline shapes (ResNet-50, batch 256; `--headline` runs them, they need ~6 GB)
 HEADLINE = []
 
@@ -109,6 +124,10 @@ hcase("dgrad_head_res_1x1_56_c256_k64", "dgrad", n=256, h=56, w=56, c=256, k=64,
       stride=1, pad="SAME", res=True)
 hcase("stem_head_7x7_s2_c3_k64", "stem", n=256, h=224, w=224, c=3, k=64, r=7, s=7, stride=2,
       pad="SAME_RESNET")
+hcase("stem_s2d_head_fprop", "stem_s2d", n=256, h=224, w=224, c=3, k=64, r=7, s=7, stride=2,
+      pad="SAME_RESNET")
+hcase("stem_s2d_head_wgrad", "stem_s2d", n=256, h=224, w=224, c=3, k=64, r=7, s=7, stride=2,
+      pad="SAME_RESNET", wgrad=True)
 
 
 def run_case(name: str) -> dict:
@@ -139,6 +158,35 @@ def run_case(name: str) -> dict:
         a, b = rnd(kw["k"], kw["m"]), rnd(kw["k"], kw["n"])
         out = gc.gemm_nt(a, b)
         ref = a.float().t() @ b.float()
+    elif kind == "stem_s2d":
+        from kf_benchmarks_b200.ops import stem
+        n, h, w, c, k, r, s = (kw[x] for x in ("n", "h", "w", "c", "k", "r", "s"))
+        st = kw["stride"]
+        ph = gc.resolve_padding(kw["pad"], h, r, st)
+        pw = gc.resolve_padding(kw["pad"], w, s, st)
+        x = rnd(n, h, w, c)
+        kpad = (r * s * c + 7) // 8 * 8
+        wt = rnd(k, kpad, scale=(r * s * c) ** -0.5)
+        wt[:, r * s * c:] = 0
+        d = gc.ConvDesc()
+        d.n, d.h, d.w, d.c, d.k, d.r, d.s = n, h, w, c, k, r, s
+        d.pad_h_lo, d.pad_h_hi, d.pad_w_lo, d.pad_w_hi = ph[0], ph[1], pw[0], pw[1]
+        d.stride_h = d.stride_w = st
+        d.p, d.q = (h + ph[0] + ph[1] - r) // st + 1, (w + pw[0] + pw[1] - s) // st + 1
+        pl = stem.plan(d, kpad)
+        y, s2d = stem.forward(pl, x, wt)
+        w_oihw = wt[:, :r * s * c].float().reshape(k, r, s, c).permute(0, 3, 1, 2).contiguous()
+        w_oihw.requires_grad_(True)
+        xp = F.pad(x.float().permute(0, 3, 1, 2), (pw[0], pw[1], ph[0], ph[1]))
+        y_ref = F.conv2d(xp, w_oihw, stride=st)
+        if kw.get("wgrad"):
+            dy = rnd(n, d.p, d.q, k)
+            y_ref.backward(dy.float().permute(0, 3, 1, 2))
+            out = stem.weight_grad(pl, s2d, dy)[:, :r * s * c]
+            ref = w_oihw.grad.permute(0, 2, 3, 1).reshape(k, r * s * c)
+        else:
+            out = y
+            ref = y_ref.detach().permute(0, 2, 3, 1)
     elif kind == "stem":
         # the tiny-C stem: explicit im2col (kfb_im2col_small_c) + GEMM, as the executor runs it
         from kf_benchmarks_b200.ops import native

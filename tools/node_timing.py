@@ -32,9 +32,10 @@ def main():
     from kf_benchmarks_b200 import benchmark, params as params_lib
     from kf_benchmarks_b200.ops import native
     from kf_benchmarks_b200.utils import roofline
+    # node by node: a graph replay would hide the calls the events bracket
     p = params_lib.make_params(model=a.model, batch_size=a.batch_size, use_fp16=True,
                                variable_update="replicated", optimizer="momentum",
-                               data_format="NHWC")
+                               data_format="NHWC", cuda_graph=False)
     bench = benchmark.BenchmarkCNN(benchmark.setup(p))
     bench._build(phase_train=True)
     ex = bench.executor
