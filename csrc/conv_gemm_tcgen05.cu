@@ -99,6 +99,7 @@ struct GemmParams {
   long long acc_src_ld;   // elements per row
   // SV3: rows are virtual pixels of (sc_Q = Q + 1)-wide rows; column sc_Q - 1 is a dummy
   int sv3;
+  int bres_bytes;  // BRES: size of the resident B operand (all K blocks)
 };
 
 constexpr int kBlockM = 128;
@@ -133,6 +134,15 @@ struct TileCfg {
   static constexpr int kSv3MaxFit = (kSmemBudget - kFixedBytes) / kSv3StageBytes;
   static constexpr int max_stages_sv3() { return kSv3MaxFit > kMaxStages ? kMaxStages : kSv3MaxFit; }
   static constexpr int smem_bytes_sv3(int stages) { return stages * kSv3StageBytes + kFixedBytes; }
+  // BRES: `bres` bytes of resident B; the ring holds A tiles only
+  static constexpr int kBresMax = 72 * 1024;
+  static constexpr int stages_bres(int a_bytes, int bres) {
+    const int fit = (kSmemBudget - kFixedBytes - bres) / a_bytes;
+    return fit > kMaxStages ? kMaxStages : fit;
+  }
+  static constexpr int smem_bytes_bres(int a_bytes, int bres, int stages) {
+    return stages * a_bytes + bres + kFixedBytes;
+  }
   // accumulating TMA-store epilogue: two 4 KiB tiles per epilogue warp receive the old values
   // of the output (TMA loads, prefetched while the MMA of the tile still runs)
   static constexpr int kOldBytes = kEpiWarps * 2 * 4096;
@@ -165,7 +175,12 @@ struct TileCfg {
 // address bits, so a row-shifted start needs no re-layout and no base offset; measured on
 // B200). The dummy column is computed and dropped by the epilogue (1.8 % at Q = 56, 3.5 % at
 // 28, 7 % at 14).
-template <int BN, int MODE, bool FAST, bool TMA_ST = false, bool ACC = false, bool SV3 = false>
+// BRES (FPROP / DGRAD with one column tile, i.e. N <= BN): the whole B operand (all K blocks of
+// the weights, p.bres_bytes <= 72 KiB) is loaded once per CTA and stays resident in shared
+// memory; the ring stages carry A only. For the 64-channel layers the weight tiles are 60 % of
+// the L2 -> SM traffic of a tile (72 of 122 KiB for a 3x3), and that traffic is their bound.
+template <int BN, int MODE, bool FAST, bool TMA_ST = false, bool ACC = false, bool SV3 = false,
+          bool BRES = false>
 __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                         const __grid_constant__ CUtensorMap tmB,
@@ -185,8 +200,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
   constexpr int kABytes = SV3 ? Cfg::kSv3ABytes : kTileABytes;
   constexpr int kBBytes = SV3 ? 3 * Cfg::kTileBBytes : Cfg::kTileBBytes;   // per stage
   uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem + kStages * kABytes;
-  uint8_t* staging = smem + kStages * (kABytes + kBBytes);
+  uint8_t* smem_b = smem + kStages * kABytes;   // BRES: the resident operand, p.bres_bytes
+  uint8_t* staging = BRES ? smem_b + p.bres_bytes : smem + kStages * (kABytes + kBBytes);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
   uint64_t* empty_bar = full_bar + kMaxStages;
   uint64_t* tmem_full_bar = empty_bar + kMaxStages;   // [2]
@@ -194,6 +209,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
   uint64_t* old_bar = tmem_empty_bar + 4;  // [kEpiWarps][2] (ACC only; inside the 512 B block)
   uint8_t* old_area = staging + Cfg::kStagingBytes + 1024;  // 1 KiB aligned (ACC only)
+  uint64_t* bres_bar = tmem_empty_bar + 20;                 // (BRES only)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -214,6 +230,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     if (ACC) {
       for (int i = 0; i < 2 * Cfg::kEpiWarps; ++i) mbar_init(&old_bar[i], 1);
     }
+    if (BRES) mbar_init(bres_bar, 1);
     mbar_fence_init();
     fence_proxy_async_smem();
   }
@@ -230,6 +247,41 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      if (BRES && static_cast<int>(blockIdx.x) < total_tiles) {
+        // every K block of the weights, once (n0 = 0: one column tile)
+        mbar_expect_tx(bres_bar, static_cast<uint32_t>(p.bres_bytes));
+        // in the order the MMA warp walks them: SV3 (r, cb, tap); otherwise (r, s, cb)
+        uint8_t* dst = smem_b;
+        if (SV3) {
+          for (int r = 0; r < p.R; ++r)
+            for (int cb = 0; cb < p.CB; ++cb)
+              for (int ts = 0; ts < 3; ++ts, dst += Cfg::kTileBBytes) {
+                if (MODE == FPROP) {
+                  tma_load_2d(dst, &tmB, bres_bar, (r * p.S + ts) * p.Ck + cb * kBlockK, 0);
+                } else {
+                  const int wtap = (p.wt_r0 + p.wt_rstep * (p.R - 1 - r)) * p.wt_S +
+                                   (p.wt_s0 + p.wt_sstep * (p.S - 1 - ts));
+#pragma unroll
+                  for (int j = 0; j < BN / 64; ++j)
+                    tma_load_3d(dst + j * 8192, &tmB, bres_bar, 64 * j, wtap, cb * kBlockK);
+                }
+              }
+        } else {
+          for (int r = 0; r < p.R; ++r)
+            for (int ss = 0; ss < p.S; ++ss)
+              for (int cb = 0; cb < p.CB; ++cb, dst += Cfg::kTileBBytes) {
+                if (MODE == FPROP) {
+                  tma_load_2d(dst, &tmB, bres_bar, (r * p.S + ss) * p.Ck + cb * kBlockK, 0);
+                } else {
+                  const int wtap = (p.wt_r0 + p.wt_rstep * (p.R - 1 - r)) * p.wt_S +
+                                   (p.wt_s0 + p.wt_sstep * (p.S - 1 - ss));
+#pragma unroll
+                  for (int j = 0; j < BN / 64; ++j)
+                    tma_load_3d(dst + j * 8192, &tmB, bres_bar, 64 * j, wtap, cb * kBlockK);
+                }
+              }
+        }
+      }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int z = tile / tiles_mn;
         const int rem_t = tile - z * tiles_mn;
@@ -296,7 +348,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem_a + stage * kABytes;
           uint8_t* sb = smem_b + stage * kBBytes;
-          mbar_expect_tx(&full_bar[stage], SV3 ? (kBlockM + 2) * 128 + kBBytes : Cfg::kStageBytes);
+          mbar_expect_tx(&full_bar[stage], (SV3 ? (kBlockM + 2) * 128 : kTileABytes) +
+                                               (BRES ? 0 : kBBytes));
           if (SV3) {
             // one box of 128 + 2 virtual pixels (tap offset 0 along w) for the filter row, and
             // the weight tiles of its three taps
@@ -304,6 +357,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
                                static_cast<uint16_t>(0), static_cast<uint16_t>(it_r));
 #pragma unroll
             for (int ts = 0; ts < 3; ++ts) {
+              if (BRES) break;
               uint8_t* sbt = sb + ts * Cfg::kTileBBytes;
               if (MODE == FPROP) {
                 tma_load_2d(sbt, &tmB, &full_bar[stage],
@@ -339,7 +393,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           } else if (MODE == FPROP || MODE == DGRAD) {
             tma_load_im2col_4d(sa, &tmA, &full_bar[stage], it_cb * kBlockK, px_w, px_h, px_n,
                                static_cast<uint16_t>(it_s), static_cast<uint16_t>(it_r));
-            if (MODE == FPROP) {
+            if (BRES) {
+            } else if (MODE == FPROP) {
               tma_load_2d(sb, &tmB, &full_bar[stage],
                           (it_r * p.S + it_s) * p.Ck + it_cb * kBlockK, n0);
             } else {
@@ -385,7 +440,12 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // All 32 lanes walk the loops: with warp-uniform control flow the shared-memory descriptors
+    // live in uniform registers and advance with one add per operand; one elected lane issues
+    // the MMAs and the commits. (Issued from inside an `if (lane == 0)` region every
+    // tcgen05.mma cost ~17 dependent instructions - 125 cycles, four times the duration of an
+    // N = 64 MMA - and the tensor pipe idled 70 % of the time on narrow tiles.)
+    {
       constexpr uint32_t idesc = make_idesc_f16(kBlockM, BN, kAMajor, kBMajor);
       // K-major: 8-row groups 1024 B apart; +32 B per UMMA_K(16) inside the swizzle atom.
       // MN-major: 64-element column groups 8192 B apart (LBO), 8-row K groups 1024 B apart
@@ -397,6 +457,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      if (BRES && static_cast<int>(blockIdx.x) < total_tiles) mbar_wait(bres_bar, 0);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
         const int z = tile / tiles_mn;
         const int kb_begin = z * p.kb_per_split;
@@ -411,34 +472,39 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
-          const uint32_t b_addr = smem_u32(smem_b + stage * kBBytes);
-          if (SV3) {
-            // tap ts reads the box through a start address ts rows (128 B each) further on
+          const uint32_t b_addr = smem_u32(smem_b + (BRES ? kb : stage) * kBBytes);
+          // descriptors of the stage; the start-address field (bits 0-13, units of 16 bytes)
+          // takes the per-MMA offsets - it cannot carry out of the field below 256 KiB
+          const uint64_t da0 = make_smem_desc_sw128(a_addr, a_lbo, 1024);
+          const uint64_t db0 = make_smem_desc_sw128(b_addr, b_lbo, 1024);
+          const uint32_t first = kb > kb_begin ? 1u : 0u;
+          if (elect_one_sync()) {
+            if (SV3) {
+              // tap ts reads the box through a start address ts rows (128 B each) further on
 #pragma unroll
-            for (int ts = 0; ts < 3; ++ts) {
+              for (int ts = 0; ts < 3; ++ts) {
 #pragma unroll
-              for (int k = 0; k < kBlockK / 16; ++k) {
-                const uint64_t da =
-                    make_smem_desc_sw128(a_addr + ts * 128 + k * a_kstep, a_lbo, 1024);
-                const uint64_t db = make_smem_desc_sw128(
-                    b_addr + ts * Cfg::kTileBBytes + k * b_kstep, b_lbo, 1024);
-                umma_f16_ss(tmem_d, da, db, idesc, (kb > kb_begin || ts > 0 || k > 0) ? 1u : 0u);
+                for (int k = 0; k < kBlockK / 16; ++k)
+                  umma_f16_ss(tmem_d, da0 + ((ts * 128 + k * a_kstep) >> 4),
+                              db0 + ((ts * Cfg::kTileBBytes + k * b_kstep) >> 4), idesc,
+                              (ts > 0 || k > 0) ? 1u : first);
               }
-            }
-          } else
+            } else {
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k) {
-            const uint64_t da = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
-            const uint64_t db = make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, 1024);
-            umma_f16_ss(tmem_d, da, db, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+              for (int k = 0; k < kBlockK / 16; ++k)
+                umma_f16_ss(tmem_d, da0 + ((k * a_kstep) >> 4), db0 + ((k * b_kstep) >> 4), idesc,
+                            k > 0 ? 1u : first);
+            }
+            umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          __syncwarp();
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tmem_full_bar[acc]);
+        if (elect_one_sync()) umma_commit(&tmem_full_bar[acc]);
+        __syncwarp();
       }
     }
   } else {
@@ -1021,6 +1087,16 @@ static int sm_count() {
   return g_sm_count;
 }
 
+// KFB_BRES=0 switches the resident-weights variants off
+static int bres_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("KFB_BRES");
+    v = (e != nullptr && *e != 0 && atoi(e) == 0) ? 0 : 1;
+  }
+  return v;
+}
+
 template <int BN, int MODE>
 static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams p, dim3 tiles,
                       cudaStream_t stream) {
@@ -1044,6 +1120,11 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
       KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE, true, true, true>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           Cfg::smem_bytes_acc(Cfg::max_stages_acc())));
+    }
+    if constexpr (BN == 64 && (MODE == FPROP || MODE == DGRAD)) {
+      KFB_CHECK_CUDA(cudaFuncSetAttribute(
+          gemm_tcgen05_kernel<BN, MODE, true, true, false, false, true>,
+          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
     }
     attr_set[dev] = true;
   }
@@ -1102,6 +1183,16 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
       gemm_tcgen05_kernel<BN, MODE, true, true, true>
           <<<ctas, Cfg::kThreads, Cfg::smem_bytes_acc(p.stages), stream>>>(tmA, tmB, tmC, tmD, p);
     }
+  } else if (BN == 64 && (MODE == FPROP || MODE == DGRAD) && fast && p.tma_store &&
+             bres_enabled() && tiles.y == 1 && tiles.z == 1 &&
+             p.num_kb * Cfg::kTileBBytes <= Cfg::kBresMax) {
+    if constexpr (BN == 64 && (MODE == FPROP || MODE == DGRAD)) {
+      p.bres_bytes = p.num_kb * Cfg::kTileBBytes;
+      p.stages = Cfg::stages_bres(kTileABytes, p.bres_bytes);
+      gemm_tcgen05_kernel<BN, MODE, true, true, false, false, true>
+          <<<ctas, Cfg::kThreads, Cfg::smem_bytes_bres(kTileABytes, p.bres_bytes, p.stages),
+             stream>>>(tmA, tmB, tmC, tmD, p);
+    }
   } else if (fast && p.tma_store) {
     if constexpr (MODE == GEMM_TN || MODE == FPROP || MODE == DGRAD) {
       gemm_tcgen05_kernel<BN, MODE, true, true>
@@ -1130,6 +1221,11 @@ static int launch_sv3_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmPa
     KFB_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, MODE, true, false, false, true>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         Cfg::smem_bytes_sv3(Cfg::max_stages_sv3())));
+    if constexpr (BN == 64) {
+      KFB_CHECK_CUDA(cudaFuncSetAttribute(
+          gemm_tcgen05_kernel<BN, MODE, true, false, false, true, true>,
+          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget));
+    }
     attr_set[dev] = true;
   }
   p.tma_store = 0;
@@ -1141,8 +1237,19 @@ static int launch_sv3_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmPa
   KFB_REQUIRE(total > 0 && total < (1ll << 31), "bad tile count %lld", total);
   const int ctas = total < sm_count() ? (int)total : sm_count();
   p.stats_rpn = (int)tiles.x < ctas ? (int)tiles.x : ctas;
-  gemm_tcgen05_kernel<BN, MODE, true, false, false, true>
-      <<<ctas, Cfg::kThreads, Cfg::smem_bytes_sv3(p.stages), stream>>>(tmA, tmB, tmA, tmA, p);
+  if (BN == 64 && bres_enabled() && tiles.y == 1 &&
+      p.num_kb * 3 * Cfg::kTileBBytes <= Cfg::kBresMax) {
+    if constexpr (BN == 64) {
+      p.bres_bytes = p.num_kb * 3 * Cfg::kTileBBytes;
+      p.stages = Cfg::stages_bres(Cfg::kSv3ABytes, p.bres_bytes);
+      gemm_tcgen05_kernel<BN, MODE, true, false, false, true, true>
+          <<<ctas, Cfg::kThreads, Cfg::smem_bytes_bres(Cfg::kSv3ABytes, p.bres_bytes, p.stages),
+             stream>>>(tmA, tmB, tmA, tmA, p);
+    }
+  } else {
+    gemm_tcgen05_kernel<BN, MODE, true, false, false, true>
+        <<<ctas, Cfg::kThreads, Cfg::smem_bytes_sv3(p.stages), stream>>>(tmA, tmB, tmA, tmA, p);
+  }
   KFB_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

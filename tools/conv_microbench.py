@@ -19,7 +19,11 @@ def main():
     from kf_benchmarks_b200.ops import gemm_conv as gc
     n = int(os.environ.get("BATCH", "256"))
     shapes = [(56, 64), (28, 128), (14, 256), (7, 512)]
-    iters = 20
+    only = os.environ.get("LAYERS")            # e.g. LAYERS=56 PASSES=fprop for a profiler run
+    if only:
+        shapes = [sh for sh in shapes if str(sh[0]) in only.split(",")]
+    only_pass = os.environ.get("PASSES")
+    iters = int(os.environ.get("ITERS", "20"))
     for hw, c in shapes:
         xs = [torch.randn(n, hw, hw, c, device="cuda").half() for _ in range(4)]
         dys = [torch.randn(n, hw, hw, c, device="cuda").half() for _ in range(4)]
@@ -36,6 +40,8 @@ def main():
         }
         flops = 2.0 * n * hw * hw * c * c * 9
         for name, fn in passes.items():
+            if only_pass and name not in only_pass.split(","):
+                continue
             for i in range(3):
                 fn(i)
             torch.cuda.synchronize()
