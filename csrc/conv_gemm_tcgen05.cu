@@ -70,7 +70,8 @@ struct GemmParams {
   // stats[((n_blk * stats_rpn + slot) * 4 + quarter)][2][BN], slot = position of the CTA among
   // the stats_rpn = min(m_tiles, grid) CTAs that visit the n-block. The persistent tile order
   // (m fastest) makes every CTA visit an n-block in one run, so each row is written exactly
-  // once with plain stores: no zero fill, no atomics, deterministic.
+  // once with plain stores: no zero fill, no atomics, deterministic. BN = 64: eight rows per
+  // slot (the two warps of a quarter take alternate tiles and own a row each).
   float* stats;
   int stats_rpn;
   // optional row scatter (strided dgrad): row (n,i,j) -> (n, h0 + i*sh, w0 + j*sw) of H x W
@@ -213,6 +214,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // 64-wide fp16 tiles are one column chunk: instead of leaving half of the epilogue warps idle,
+  // the two warps of a TMEM lane quarter take alternate tiles (= alternate accumulator stages)
+  const bool alt_tiles = (BN == 64) && !p.out_fp32;
   const int tiles_mn = p.m_tiles * p.n_tiles;
   const int total_tiles = tiles_mn * p.splits;
 
@@ -225,7 +229,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full_bar[a], 1);
-      mbar_init(&tmem_empty_bar[a], Cfg::kEpiWarps);  // one arrive per epilogue warp
+      // one arrive per epilogue warp that reads the stage
+      mbar_init(&tmem_empty_bar[a], alt_tiles ? Cfg::kEpiWarps / 2 : Cfg::kEpiWarps);
     }
     if (ACC) {
       for (int i = 0; i < 2 * Cfg::kEpiWarps; ++i) mbar_init(&old_bar[i], 1);
@@ -533,10 +538,11 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     // of this CTA - so that the old values (TMA) and the mask words (one 8-byte load per lane)
     // of a chunk are requested two chunks before they are used; tiles of one K block (1x1
     // layers) have no main loop to hide that latency behind otherwise.
-    int pf_tile = blockIdx.x, pf_k = 0;
+    int pf_tile = blockIdx.x, pf_k = 0, pf_it = 0;
     unsigned long long pf_mask0 = ~0ull, pf_mask1 = ~0ull;
     auto pump_old = [&]() {
-      const int cstep = cols_per_chunk * kColSplit, cfirst = col_part * cols_per_chunk;
+      const int cstep = alt_tiles ? 64 : cols_per_chunk * kColSplit;
+      const int cfirst = alt_tiles ? 0 : col_part * cols_per_chunk;
       while (old_issued - old_used < 2u && pf_tile < total_tiles) {
         const int nb = pf_tile / p.m_tiles;  // the accumulating epilogue has no K splits
         const int pm0 = (pf_tile - nb * p.m_tiles) * kBlockM;
@@ -545,8 +551,10 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         if (lim > BN) lim = BN;
         int chunks = 0;
         if (pm0 + quarter * 32 < p.M && cfirst < lim) chunks = (lim - cfirst + cstep - 1) / cstep;
+        if (alt_tiles && (pf_it & 1) != col_part) chunks = 0;  // the other warp's tile
         if (pf_k >= chunks) {
           pf_tile += gridDim.x;
+          ++pf_it;
           pf_k = 0;
           continue;
         }
@@ -578,11 +586,13 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       const int first = (nblk * p.m_tiles) % static_cast<int>(gridDim.x);
       int slot = static_cast<int>(blockIdx.x) - first;
       if (slot < 0) slot += gridDim.x;
-      float* st_row = p.stats +
-                      (static_cast<long long>(nblk * p.stats_rpn + slot) * 4 + quarter) * 2 * BN;
+      const int sub = alt_tiles ? col_part * 4 + quarter : quarter;
+      float* st_row = p.stats + (static_cast<long long>(nblk * p.stats_rpn + slot) *
+                                     (alt_tiles ? 8 : 4) + sub) * 2 * BN;
 #pragma unroll
       for (int c = 0; c < kStatChunks; ++c) {
-        const int col = (col_part + c * kColSplit) * 64 + 2 * lane;  // column inside the tile
+        // column inside the tile
+        const int col = (alt_tiles ? 0 : (col_part + c * kColSplit)) * 64 + 2 * lane;
         if (col < BN) {
           *reinterpret_cast<float2*>(st_row + col) = make_float2(st_sum[c][0], st_sum[c][1]);
           *reinterpret_cast<float2*>(st_row + BN + col) = make_float2(st_sq[c][0], st_sq[c][1]);
@@ -603,6 +613,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         if (st_nblk >= 0) flush_stats(st_nblk);
         st_nblk = n_blk;
       }
+      if (alt_tiles && (it & 1) != col_part) continue;  // the other warp of the quarter's tile
       const int m0 = (rem_t - n_blk * p.m_tiles) * kBlockM;
       int n0 = n_blk * BN;
       int col_mem0 = n0;       // first memory column of this tile
@@ -634,8 +645,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       // SV3: the dummy rows hold real numbers (not zeros): they must stay out of the statistics
       const unsigned valid_rows = SV3 ? __ballot_sync(0xffffffffu, row_off >= 0) : 0xffffffffu;
       const long long base = static_cast<long long>(z) * p.split_stride + col_mem0;
-      const int c_step = cols_per_chunk * kColSplit;
-      const int c_first = col_part * cols_per_chunk;
+      const int c_step = alt_tiles ? 64 : cols_per_chunk * kColSplit;
+      const int c_first = alt_tiles ? 0 : col_part * cols_per_chunk;
       // rows of this warp beyond M are never stored: nothing is loaded for them either
       const bool acc_on = ACC && (m0 + quarter * 32 < p.M);
       if (ACC) pump_old();
@@ -743,7 +754,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         if (do_stats) {
           // column sums of the staged (already fp16-rounded) 32 x 64 chunk; rows beyond M and
           // columns beyond N hold exact zeros (zero-filled operands), so no masking is needed
-          const int sc = (c0 / 64 - col_part) / kColSplit;
+          const int sc = alt_tiles ? 0 : (c0 / 64 - col_part) / kColSplit;
           float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll 8
           for (int r = 0; r < 32; ++r) {
@@ -1351,7 +1362,8 @@ extern "C" int kfb_gemm_stats_layout(int M, int N, int num_kb, int* rows, int* b
   const long long m_tiles = (M + 127) / 128, n_tiles = (N + b - 1) / b;
   const long long total = m_tiles * n_tiles;
   const long long ctas = total < sm_count() ? total : sm_count();
-  *rows = (int)(m_tiles < ctas ? m_tiles : ctas) * 4;
+  // 64-wide tiles: the two epilogue warps of a lane quarter take alternate tiles, a row each
+  *rows = (int)(m_tiles < ctas ? m_tiles : ctas) * (b == 64 ? 8 : 4);
   *bn = b;
   return 0;
 }
