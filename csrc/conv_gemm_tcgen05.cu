@@ -25,6 +25,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+#include <unordered_map>
+
 namespace kfb {
 
 // ---------------------------------------------------------------------------
@@ -1052,6 +1055,45 @@ static int load_driver_fns() {
   return 0;
 }
 
+// Tensor maps are pure functions of (pointer, geometry): a training step launches the same few
+// hundred GEMMs on the same static buffers every step, so the encoded maps are kept in a small
+// host-side table and a launch outside a CUDA graph costs one hash lookup per operand instead of
+// a driver call (KFB_TMAP_CACHE=0 encodes every time).
+struct TmapKey {
+  uint64_t v[20];
+  bool operator==(const TmapKey& o) const { return memcmp(v, o.v, sizeof(v)) == 0; }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    uint64_t h = 1469598103934665603ull;
+    for (uint64_t x : k.v) h = (h ^ x) * 1099511628211ull;
+    return (size_t)h;
+  }
+};
+static std::mutex g_tmap_mu;
+static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
+static bool tmap_cache_on() {
+  static const bool on = [] {
+    const char* e = getenv("KFB_TMAP_CACHE");
+    return !(e != nullptr && *e != 0 && atoi(e) == 0);
+  }();
+  return on;
+}
+static bool tmap_lookup(const TmapKey& k, CUtensorMap* m) {
+  if (!tmap_cache_on()) return false;
+  std::lock_guard<std::mutex> lock(g_tmap_mu);
+  auto it = g_tmap_cache.find(k);
+  if (it == g_tmap_cache.end()) return false;
+  *m = it->second;
+  return true;
+}
+static void tmap_store(const TmapKey& k, const CUtensorMap& m) {
+  if (!tmap_cache_on()) return;
+  std::lock_guard<std::mutex> lock(g_tmap_mu);
+  if (g_tmap_cache.size() > 8192) g_tmap_cache.clear();
+  g_tmap_cache.emplace(k, m);
+}
+
 // fp16 tensor, rank 2 or 3 (dims innermost first), 128B swizzle, zero OOB fill.
 static int encode_tiled(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims,
                         const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box) {
@@ -1065,6 +1107,17 @@ static int encode_tiled(CUtensorMap* m, const void* ptr, int rank, const uint64_
     es[i] = 1;
   }
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
+  TmapKey key;
+  memset(&key, 0, sizeof(key));
+  key.v[0] = 1;
+  key.v[1] = (uint64_t)(uintptr_t)ptr;
+  key.v[2] = (uint64_t)rank;
+  for (int i = 0; i < rank; ++i) {
+    key.v[3 + i] = dims[i];
+    key.v[8 + i] = box[i];
+  }
+  for (int i = 0; i + 1 < rank; ++i) key.v[13 + i] = strides_bytes[i];
+  if (tmap_lookup(key, m)) return 0;
   CUresult r = g_encodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, rank, const_cast<void*>(ptr),
                              gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1075,6 +1128,7 @@ static int encode_tiled(CUtensorMap* m, const void* ptr, int rank, const uint64_
               (int)r, rank, (unsigned long long)dims[0], (unsigned long long)dims[1],
               (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], box[1], rank > 2 ? box[2] : 0,
               (unsigned long long)strides_bytes[0], ptr);
+  tmap_store(key, *m);
   return 0;
 }
 
@@ -1090,6 +1144,18 @@ static int encode_im2col(CUtensorMap* m, const void* ptr, int N, int H, int W, i
   int lower[2] = {lower_w, lower_h};
   int upper[2] = {upper_w, upper_h};
   cuuint32_t es[4] = {1, (cuuint32_t)stride_w, (cuuint32_t)stride_h, 1};
+  TmapKey key;
+  memset(&key, 0, sizeof(key));
+  key.v[0] = 2;
+  key.v[1] = (uint64_t)(uintptr_t)ptr;
+  key.v[2] = ((uint64_t)(uint32_t)N << 32) | (uint32_t)H;
+  key.v[3] = ((uint64_t)(uint32_t)W << 32) | (uint32_t)C;
+  key.v[4] = ((uint64_t)(uint32_t)lower_w << 32) | (uint32_t)lower_h;
+  key.v[5] = ((uint64_t)(uint32_t)upper_w << 32) | (uint32_t)upper_h;
+  key.v[6] = ((uint64_t)(uint32_t)channels_per_pixel << 32) | (uint32_t)pixels_per_column;
+  key.v[7] = ((uint64_t)(uint32_t)stride_w << 32) | (uint32_t)stride_h;
+  key.v[8] = ((uint64_t)(uint32_t)pix_stride << 32) | (uint32_t)row_stride;
+  if (tmap_lookup(key, m)) return 0;
   CUresult r = g_encodeIm2col(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(ptr), gdim,
                               gstr, lower, upper, (cuuint32_t)channels_per_pixel,
                               (cuuint32_t)pixels_per_column, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -1100,6 +1166,7 @@ static int encode_im2col(CUtensorMap* m, const void* ptr, int N, int H, int W, i
               "[%d,%d] cpp %d ppc %d stride [%d,%d]",
               (int)r, N, H, W, C, lower_w, lower_h, upper_w, upper_h, channels_per_pixel,
               pixels_per_column, stride_w, stride_h);
+  tmap_store(key, *m);
   return 0;
 }
 

@@ -95,6 +95,8 @@ class CudaExecutor:
         self._ready = [torch.cuda.Event(), torch.cuda.Event()]
         self._free = [torch.cuda.Event(), torch.cuda.Event()]
         self.needs_grad = self._mark_needs_grad(need_input_grad)
+        self._slice_of: Dict[int, tuple] = {}
+        self._plan_concat_slices()
         for node in graph.nodes:
             self._alloc_output(node)
         # reductions / split-K scratch (sized below), loss outputs
@@ -166,9 +168,49 @@ class CudaExecutor:
             need[node.output.id] = has_param or any(need[t.id] for t in node.inputs)
         return need
 
+    def _plan_concat_slices(self) -> None:
+        """Concat inputs that can be produced in place: a 4-D tensor written by a batch norm or a
+        pooling layer (kernels that take the row stride of their output and of the incoming
+        gradient) whose only consumer is the concat becomes a column slice of the concat
+        buffer, forward and backward - no copy2d in either direction (the reference's concat is
+        a real copy too, T/convnet_builder_legacy.py inception modules -> tf.concat; here the
+        branch simply stores into its channel slice). KFB_CONCAT_INPLACE=0 keeps the copies."""
+        if os.environ.get("KFB_CONCAT_INPLACE", "1") == "0":
+            return
+        producer = {node.output.id: node for node in self.graph.nodes}
+        for node in self.graph.nodes:
+            if node.op != "concat" or len(node.output.shape) != 4 or \
+                    node.output.id in self._slice_of:
+                continue
+            off = 0
+            for t in node.inputs:
+                src = producer.get(t.id)
+                if (src is not None and src.op in ("bn", "pool") and len(t.consumers) == 1 and
+                        len(t.shape) == 4 and t.shape[-1] % 8 == 0 and off % 8 == 0 and
+                        t is not self.graph.logits and t is not self.graph.aux_logits and
+                        node.inputs.count(t) == 1):
+                    self._slice_of[t.id] = (node.output.id, off)
+                off += t.shape[-1]
+
+    def _concat_buffer(self, tid: int) -> "_Buf":
+        if tid not in self.buf:
+            t = self.graph.tensors[tid]
+            rows, cols = t.rows, t.shape[-1]
+            self.buf[tid] = _Buf(torch.zeros((rows, cols), dtype=torch.float16,
+                                             device=self.device), rows, cols, cols)
+        return self.buf[tid]
+
     def _alloc_output(self, node: Node) -> None:
         t = node.output
         dev = self.device
+        if t.id in self._slice_of:
+            parent, off = self._slice_of[t.id]
+            y = self._concat_buffer(parent)
+            cols = t.shape[-1]
+            self.buf[t.id] = _Buf(y.t[:, off:off + cols], y.rows, cols, y.ld)
+            return
+        if node.op == "concat" and t.id in self.buf:
+            return                       # allocated early for its in-place inputs
         if len(t.shape) == 4:
             rows, cols = t.rows, t.shape[-1]
             if cols % 8 != 0:
@@ -200,6 +242,13 @@ class CudaExecutor:
             g = _Buf(base.t.view(b.rows, b.ld), b.rows, b.cols, b.ld)
             self.gbuf[t.id] = g
             return g
+        if t.id in self._slice_of:
+            if t.id not in self.gbuf:
+                parent, off = self._slice_of[t.id]
+                base = self._grad(self.graph.tensors[parent])
+                b = self.buf[t.id]
+                self.gbuf[t.id] = _Buf(base.t[:, off:off + b.cols], b.rows, b.cols, base.ld)
+            return self.gbuf[t.id]
         if t.id not in self.gbuf:
             b = self.buf[t.id]
             self.gbuf[t.id] = _Buf(torch.zeros((b.rows, b.ld), dtype=torch.float16,
@@ -715,8 +764,10 @@ class CudaExecutor:
         off = 0
         for t in node.inputs:
             x = self.buf[t.id]
-            native.call("copy2d", x.p, i64(x.ld), ctypes.c_void_p(y.t.data_ptr() + off * 2),
-                        i64(y.ld), i64(x.rows), i32(x.cols), i32(0), s)
+            if t.id not in self._slice_of:       # in-place inputs already sit in their slice
+                native.call("copy2d", x.p, i64(x.ld),
+                            ctypes.c_void_p(y.t.data_ptr() + off * 2), i64(y.ld), i64(x.rows),
+                            i32(x.cols), i32(0), s)
             off += x.cols
 
     # LSTM layer = one big input-projection GEMM per direction, then per time step a small
@@ -1168,7 +1219,7 @@ class CudaExecutor:
         off = 0
         for idx, t in enumerate(node.inputs):
             cols = self.buf[t.id].cols
-            if self.needs_grad[t.id]:
+            if self.needs_grad[t.id] and t.id not in self._slice_of:
                 gx = self._grad(t)
                 native.call("copy2d", ctypes.c_void_p(gy.t.data_ptr() + off * 2), i64(gy.ld),
                             gx.p, i64(gx.ld), i64(gx.rows), i32(cols),

@@ -15,8 +15,9 @@ import ctypes
 import os
 import threading
 
+# KFB_LIB_NAME selects another build of the library in _lib/ (A/B measurements of build flags)
 _LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "_lib",
-                         "libkfb200.so")
+                         os.environ.get("KFB_LIB_NAME", "libkfb200.so"))
 _lib = None
 _lock = threading.Lock()
 

@@ -52,40 +52,25 @@ KFB_NVTX=1 ncu --nvtx --print-nvtx-rename kernel \
   || echo "(per-layer list not produced; see gpurun_out/ncu_launches_nvtx.log)"
 
 echo "== 3. ncu --set full on the heaviest kernels =="
-for spec in "gemm:gemm_tcgen05_kernel" "bnbwd:bn_bwd_fused_kernel" "bnfwd:bn_fwd_fused_kernel" \
-            "bnred:channel_reduce_kernel"; do
+for spec in "gemm:gemm_tcgen05_kernel" "bnbwd:bn_bwd_fused_kernel" "bnapply:bn_apply_kernel" \
+            "poolbwd:pool_bwd_max3s2_block_kernel"; do
   name=${spec%%:*}; pat=${spec##*:}
-  ncu --set full --clock-control none --import-source on -k regex:$pat -s 60 -c 3 -f \
+  skip=60; [ "$name" = poolbwd ] && skip=2
+  ncu --set full --clock-control none --import-source on -k regex:$pat -s $skip -c 3 -f \
       -o gpurun_out/prof_${TAG}_$name $CMD > gpurun_out/ncu_$name.log 2>&1
   if [ -f gpurun_out/prof_${TAG}_$name.ncu-rep ]; then
-    ncu -i gpurun_out/prof_${TAG}_$name.ncu-rep --page raw --csv 2>/dev/null | python - "$TAG" "$name" <<'PY'
-import csv, sys
-tag, name = sys.argv[1], sys.argv[2]
-keep = ("gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
-        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
-        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
-        "sm__pipe_tensor_subpipe_hmma_cycles_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
-        "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
-        "lts__t_sector_hit_rate.pct", "sm__inst_executed_pipe_uniform", "smsp__issue_active.avg.pct_of_peak_sustained_active")
-rows = list(csv.reader(sys.stdin))
-if len(rows) > 2:
-    hdr = rows[0]
-    cols = [i for i, h in enumerate(hdr) if h in ("ID", "Kernel Name") or any(h.startswith(k) for k in keep)]
-    with open("profiles/ncu_%s_%s.csv" % (tag, name), "w", newline="") as f:
-        w = csv.writer(f)
-        for r in rows:
-            w.writerow([r[i][:120] for i in cols if i < len(r)])
-    print("profiles/ncu_%s_%s.csv: %d launches, %d metrics" % (tag, name, len(rows) - 2, len(cols)))
-else:
-    print("no rows for", name)
-PY
+    ncu -i gpurun_out/prof_${TAG}_$name.ncu-rep --page raw --csv > gpurun_out/raw_${TAG}_$name.csv 2>/dev/null
+    python tools/ncu_select.py gpurun_out/raw_${TAG}_$name.csv gpurun_out/ncu_${TAG}_$name.csv
+    cp gpurun_out/ncu_${TAG}_$name.csv profiles/ 2>/dev/null
   else
     echo "no report for $name"; tail -3 gpurun_out/ncu_$name.log
   fi
 done
 
 echo "== 4. roofline =="
+# (only gpurun_out/ travels back from a gpurun box: everything under profiles/ is mirrored there)
 MS=$(python -c "import json;print(json.loads(open('profiles/bench_1gpu_$TAG.json').read())['ms_per_step'])")
 python tools/roofline_model.py --launches profiles/resnet50_bs256_launches_$TAG.txt --step_ms "$MS" \
     --by_layer profiles/resnet50_bs256_launches_by_layer_$TAG.txt \
     > profiles/roofline_resnet50_bs256_$TAG.md && tail -14 profiles/roofline_resnet50_bs256_$TAG.md
+mkdir -p gpurun_out/profiles_$TAG && cp profiles/*_$TAG* gpurun_out/profiles_$TAG/ 2>/dev/null

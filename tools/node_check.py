@@ -153,7 +153,8 @@ def check(model_name, data_name, batch, image_size=None, tol=1e-2, verbose=False
             gy_h = torch.where(flip, torch.zeros_like(gy_h), gy_h)
             put(ex.gbuf[node.output.id], gy_h)
             for t in node.inputs:
-                if ex.needs_grad.get(t.id, False):
+                # (an in-place concat input's gradient IS a slice of the gradient just put)
+                if ex.needs_grad.get(t.id, False) and t.id not in ex._slice_of:
                     ex._grad(t).t.zero_()
             for spec in node.params.values():
                 if spec.trainable:
