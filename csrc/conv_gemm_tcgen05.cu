@@ -79,6 +79,9 @@ struct GemmParams {
   int stats_rpn;
   // optional row scatter (strided dgrad): row (n,i,j) -> (n, h0 + i*sh, w0 + j*sw) of H x W
   int sc_P, sc_Q, sc_H, sc_W, sc_sh, sc_sw, sc_h0, sc_w0;
+  // n / d == (n * mul) >> sh for 0 <= n < 2^31 (filled by the launcher from sc_P, sc_Q)
+  unsigned long long sc_pq_mul, sc_q_mul;
+  int sc_pq_sh, sc_q_sh;
   // DGRAD: filter tap visited at (r, s) of this launch's (sub-)filter
   int wt_r0, wt_rstep, wt_s0, wt_sstep, wt_S;
   // Fused reduce-scatter (weight gradients, data-parallel training): when push_n > 1 the
@@ -130,7 +133,11 @@ template <int BN>
 struct TileCfg {
   static constexpr int kTileBBytes = BN * kBlockK * 2;
   static constexpr int kStageBytes = kTileABytes + kTileBBytes;
-  static constexpr int kTmemCols = 2 * BN;  // two accumulator stages (power of two >= 128)
+  // Accumulator stages in TMEM (512 columns): four for tiles of at most 128 columns, so that the
+  // MMA warp runs up to three tiles ahead of the epilogue (with two stages the tile time of the
+  // short-K 64-channel layers was (MMA + epilogue) / 2: each stage's cycle is fill -> drain)
+  static constexpr int kAccStages = BN <= 128 ? 4 : 2;
+  static constexpr int kTmemCols = kAccStages * BN;  // a power of two >= 128
   // Narrow tiles are picked for short-K, store-bound problems: give them eight epilogue warps
   // (two per TMEM lane quarter, interleaving column chunks); 256-wide tiles keep four and a
   // deeper smem ring instead.
@@ -212,8 +219,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       (MODE == GEMM_NT || MODE == WGRAD || MODE == DGRAD || MODE == GEMM_NN) ? kMajorMN : kMajorK;
 
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // 1 KiB aligned; pointer arithmetic on the array (not an integer round trip) so that the
+  // compiler keeps the shared address space and emits LDS / STS for the staging tiles
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   constexpr int kABytes = SV3 ? Cfg::kSv3ABytes : kTileABytes;
   constexpr int kBBytes = SV3 ? 3 * Cfg::kTileBBytes : Cfg::kTileBBytes;   // per stage
   uint8_t* smem_a = smem;
@@ -221,12 +229,13 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
   uint8_t* staging = BRES ? smem_b + p.bres_bytes : smem + kStages * (kABytes + kBBytes);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
   uint64_t* empty_bar = full_bar + kMaxStages;
-  uint64_t* tmem_full_bar = empty_bar + kMaxStages;   // [2]
-  uint64_t* tmem_empty_bar = tmem_full_bar + 2;       // [2]
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
-  uint64_t* old_bar = tmem_empty_bar + 4;  // [kEpiWarps][2] (ACC only; inside the 512 B block)
+  constexpr int kAcc = Cfg::kAccStages;
+  uint64_t* tmem_full_bar = empty_bar + kMaxStages;   // [4]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 4;       // [4]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 4);
+  uint64_t* old_bar = tmem_empty_bar + 6;  // [kEpiWarps][2] (ACC only; inside the 512 B block)
   uint8_t* old_area = staging + Cfg::kStagingBytes + 1024;  // 1 KiB aligned (ACC only)
-  uint64_t* bres_bar = tmem_empty_bar + 20;                 // (BRES only)
+  uint64_t* bres_bar = tmem_empty_bar + 22;                 // (BRES only)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -243,7 +252,7 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < kAcc; ++a) {
       mbar_init(&tmem_full_bar[a], 1);
       // one arrive per epilogue warp that reads the stage
       mbar_init(&tmem_empty_bar[a], alt_tiles ? Cfg::kEpiWarps / 2 : Cfg::kEpiWarps);
@@ -304,9 +313,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         }
       }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int z = tile / tiles_mn;
+        const int z = p.splits == 1 ? 0 : tile / tiles_mn;
         const int rem_t = tile - z * tiles_mn;
-        const int n_blk = rem_t / p.m_tiles;
+        const int n_blk = p.n_tiles == 1 ? 0 : rem_t / p.m_tiles;
         const int m0 = (rem_t - n_blk * p.m_tiles) * kBlockM;
         const int n0 = n_blk * BN;
         const int kb_begin = z * p.kb_per_split;
@@ -480,12 +489,12 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       int it = 0;
       if (BRES && static_cast<int>(blockIdx.x) < total_tiles) mbar_wait(bres_bar, 0);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const int z = tile / tiles_mn;
+        const int z = p.splits == 1 ? 0 : tile / tiles_mn;
         const int kb_begin = z * p.kb_per_split;
         int kb_end = kb_begin + p.kb_per_split;
         if (kb_end > p.num_kb) kb_end = p.num_kb;
-        const int acc = it & 1;
-        const uint32_t acc_phase = (it >> 1) & 1;
+        const int acc = it % kAcc;
+        const uint32_t acc_phase = (it / kAcc) & 1;
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
@@ -560,7 +569,8 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
       const int cstep = alt_tiles ? 64 : cols_per_chunk * kColSplit;
       const int cfirst = alt_tiles ? 0 : col_part * cols_per_chunk;
       while (old_issued - old_used < 2u && pf_tile < total_tiles) {
-        const int nb = pf_tile / p.m_tiles;  // the accumulating epilogue has no K splits
+        // (the accumulating epilogue has no K splits)
+        const int nb = p.n_tiles == 1 ? 0 : pf_tile / p.m_tiles;
         const int pm0 = (pf_tile - nb * p.m_tiles) * kBlockM;
         const int pcol0 = nb * BN;
         int lim = p.N - pcol0;
@@ -622,9 +632,9 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
     };
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int z = tile / tiles_mn;
+      const int z = p.splits == 1 ? 0 : tile / tiles_mn;
       const int rem_t = tile - z * tiles_mn;
-      const int n_blk = rem_t / p.m_tiles;
+      const int n_blk = p.n_tiles == 1 ? 0 : rem_t / p.m_tiles;
       if (do_stats && n_blk != st_nblk) {
         if (st_nblk >= 0) flush_stats(st_nblk);
         st_nblk = n_blk;
@@ -641,15 +651,18 @@ __global__ void __launch_bounds__(TileCfg<BN>::kThreads, 1)
         n_limit = p.Cn - n0;
       }
       if (n_limit > BN) n_limit = BN;
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
+      const int acc = it % kAcc;
+      const uint32_t acc_phase = (it / kAcc) & 1;
       const int row = m0 + quarter * 32 + lane;
       long long row_off = row;
       if (p.sc_P > 0) {
+        // exact division by multiply-high (host-computed constants; row < 2^31)
         const int pq = p.sc_P * p.sc_Q;
-        const int n_img = row / pq;
+        const int n_img = static_cast<int>(
+            (static_cast<unsigned long long>(static_cast<unsigned>(row)) * p.sc_pq_mul) >> p.sc_pq_sh);
         const int rem = row - n_img * pq;
-        const int pp = rem / p.sc_Q;
+        const int pp = static_cast<int>(
+            (static_cast<unsigned long long>(static_cast<unsigned>(rem)) * p.sc_q_mul) >> p.sc_q_sh);
         const int qq = rem - pp * p.sc_Q;
         row_off = (static_cast<long long>(n_img) * p.sc_H + p.sc_h0 +
                    static_cast<long long>(pp) * p.sc_sh) *
@@ -1181,6 +1194,19 @@ static int sm_count() {
   return g_sm_count;
 }
 
+// n / d == (n * mul) >> sh for 0 <= n < 2^31: mul = floor(2^(32+s) / d) + 1, s = floor(log2 d)
+static void magic_div(unsigned d, unsigned long long* mul, int* sh) {
+  int s = 0;
+  while (s < 30 && (2u << s) <= d) ++s;
+  *sh = 32 + s;
+  *mul = ((1ull << (32 + s)) / d) + 1;
+}
+static void fill_scatter_magic(GemmParams* p) {
+  if (p->sc_P <= 0) return;
+  magic_div((unsigned)(p->sc_P * p->sc_Q), &p->sc_pq_mul, &p->sc_pq_sh);
+  magic_div((unsigned)p->sc_Q, &p->sc_q_mul, &p->sc_q_sh);
+}
+
 // KFB_BRES=0 switches the resident-weights variants off
 static int bres_enabled() {
   static int v = -1;
@@ -1264,6 +1290,7 @@ static int launch_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams
     if (encode_tiled(&tmD, p.acc_src, 2, dims, strides, box)) return 1;
   }
   p.stages = Cfg::max_stages();
+  fill_scatter_magic(&p);
   p.m_tiles = (int)tiles.x;
   p.n_tiles = (int)tiles.y;
   p.splits = (int)tiles.z;
@@ -1323,6 +1350,7 @@ static int launch_sv3_cfg(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmPa
     attr_set[dev] = true;
   }
   p.tma_store = 0;
+  fill_scatter_magic(&p);
   p.stages = Cfg::max_stages_sv3();
   p.m_tiles = (int)tiles.x;
   p.n_tiles = (int)tiles.y;
