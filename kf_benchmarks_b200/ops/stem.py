@@ -115,6 +115,64 @@ def weight_grad(pl: StemPlan, s2d, dy):
     return unpack_grad(pl, dw4, out)
 
 
+# ---------------------------------------------------------------- PyTorch restatements
+# The index arithmetic of csrc/stem_s2d.cu in plain tensor ops: the CPU tests check the plan's
+# geometry with them (regroup + pack + a ceil(R/2) x 4 convolution == the original convolution)
+# and the GPU tests compare the kernels against them.
+def regroup_ref(pl: StemPlan, x: torch.Tensor) -> torch.Tensor:
+    """x[n, h, w, c] -> the padded regrouped image [n, h2, w2p, 16] (same dtype)."""
+    out = torch.zeros((pl.n, pl.h2, pl.w2p, 16), dtype=x.dtype, device=x.device)
+    for a in range(pl.h2):
+        for bh in range(2):
+            i = 2 * a - pl.eh + bh
+            if not 0 <= i < pl.h:
+                continue
+            for jp in range(pl.w2p):
+                for bw in range(2):
+                    j = 2 * (jp - pl.lw) - pl.ew + bw
+                    if 0 <= j < pl.w:
+                        c0 = (bh * 2 + bw) * pl.c
+                        out[:, a, jp, c0:c0 + pl.c] = x[:, i, j, :]
+    return out
+
+
+def pack_weights_ref(pl: StemPlan, w_flat: torch.Tensor) -> torch.Tensor:
+    """w_flat[k, kpad] (columns (r*S + s)*C + c) -> [k, ta, 4, 16] (vertical tap, horizontal
+    tap, regrouped channel)."""
+    w4 = torch.zeros((pl.k, pl.ta, 4, 16), dtype=w_flat.dtype, device=w_flat.device)
+    for r in range(pl.r):
+        for s in range(pl.s):
+            ch = ((r & 1) * 2 + (s & 1)) * pl.c
+            col = (r * pl.s + s) * pl.c
+            w4[:, r >> 1, s >> 1, ch:ch + pl.c] = w_flat[:, col:col + pl.c]
+    return w4
+
+
+def unpack_grad_ref(pl: StemPlan, dw4: torch.Tensor) -> torch.Tensor:
+    """Inverse gather of pack_weights_ref: [k, ta, 4, 16] -> [k, kpad] (pad columns zero)."""
+    dw4 = dw4.reshape(pl.k, pl.ta, 4, 16)
+    out = torch.zeros((pl.k, pl.kpad), dtype=dw4.dtype, device=dw4.device)
+    for r in range(pl.r):
+        for s in range(pl.s):
+            ch = ((r & 1) * 2 + (s & 1)) * pl.c
+            col = (r * pl.s + s) * pl.c
+            out[:, col:col + pl.c] = dw4[:, r >> 1, s >> 1, ch:ch + pl.c]
+    return out
+
+
+def forward_ref(pl: StemPlan, x: torch.Tensor, w_flat: torch.Tensor) -> torch.Tensor:
+    """The convolution as the kernels run it, in fp32 tensor ops: returns y[n, p, q, k]."""
+    import torch.nn.functional as F
+    s2d = regroup_ref(pl, x.float())                       # [n, h2, w2p, 16]
+    w4 = pack_weights_ref(pl, w_flat.float())              # [k, ta, 4, 16]
+    d = pl.desc
+    xin = F.pad(s2d.permute(0, 3, 1, 2), (0, 0, d.pad_h_lo, max(d.pad_h_hi, 0)))
+    if d.pad_h_hi < 0:
+        xin = xin[:, :, :xin.shape[2] + d.pad_h_hi, :]
+    y = F.conv2d(xin, w4.permute(0, 3, 1, 2))              # 4 horizontal taps = 4 pixels
+    return y.permute(0, 2, 3, 1)[:, :pl.p, :pl.q, :]
+
+
 __all__ = ["StemPlan", "eligible", "plan", "regroup", "pack_weights", "unpack_grad", "forward",
-           "weight_grad"]
+           "weight_grad", "regroup_ref", "pack_weights_ref", "unpack_grad_ref", "forward_ref"]
 _ = ctypes
