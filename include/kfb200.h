@@ -202,6 +202,20 @@ int kfb_copy_rows(const void* src, long long lds, void* dst, long long ldd, long
 /* Explicit im2col for stems whose input channel count is not a multiple of 8. */
 int kfb_im2col_small_c(const void* x, void* col, int n, int h, int w, int c, int p, int q, int kh,
                        int kw, int sh, int sw, int pad_h, int pad_w, int kpad, void* stream);
+/* Batched JPEG decode on the device through nvJPEG (csrc/jpeg_decode.cu; libnvjpeg is loaded with
+ * dlopen: kfb_jpeg_available() == 0 when it is missing). backend: 0 = hardware engine if the GPU
+ * has one, else GPU-assisted Huffman; 1 = hardware only; 2 = GPU-assisted; 3 = nvJPEG's default.
+ * kfb_jpeg_image_info reads the frame header on the host; kfb_jpeg_decode_batch decodes n host
+ * bitstreams into n interleaved-RGB device buffers (row pitch >= 3 * width bytes) on `stream`. */
+int kfb_jpeg_available(void);
+int kfb_jpeg_create(int backend, int cpu_threads, void** handle);
+int kfb_jpeg_backend(void* handle);
+int kfb_jpeg_destroy(void* handle);
+int kfb_jpeg_image_info(void* handle, const unsigned char* data, unsigned long long len, int* width,
+                        int* height, int* components);
+int kfb_jpeg_decode_batch(void* handle, const unsigned char* const* data,
+                          const unsigned long long* lens, int n, unsigned char* const* dst,
+                          const int* pitch, void* stream);
 /* Space-to-depth stem (csrc/stem_s2d.cu): a stride-2 convolution on C <= 4 channels with
  * ceil(S/2) == 4 runs as a ceil(R/2) x 1 unit-stride convolution over 64-"channel" pixels that
  * are four overlapping 16-channel pixels of the regrouped image (kfb_conv_desc.x_pix_stride = 16).

@@ -106,3 +106,36 @@ class GpuImageBatcher:
                         i64(self.oh * self.ow * 3), ctypes.c_void_p(s.cuda_stream))
         self.h2d_bytes_last = total + n * (size + 8)
         return out[:n]
+
+    def run_device(self, dev_ptrs: Sequence[int], pitches: Sequence[int], ops: Sequence[ImageOp],
+                   stream=None) -> torch.Tensor:
+        """The same transform on images that are already on the device (decoded there by
+        data/nvjpeg.py): ``dev_ptrs[k]`` is interleaved RGB with row pitch ``pitches[k]`` bytes.
+        Only the descriptors and pointers are uploaded."""
+        n = len(dev_ptrs)
+        if n != len(ops) or n > self.batch:
+            raise ValueError("gpu_image: %d images, %d descriptors, batch %d"
+                             % (n, len(ops), self.batch))
+        slot = self._slot
+        self._slot = (slot + 1) % self.slots
+        ops_bytes = self._ops_host[slot].numpy()
+        ptrs = self._ptr_host[slot].numpy()
+        size = ctypes.sizeof(ImageOp)
+        for k, (dp, pitch, op) in enumerate(zip(dev_ptrs, pitches, ops)):
+            if not supports(op):
+                raise ValueError("gpu_image: resize method %d runs on the host path" % op.method)
+            dop = ImageOp.from_buffer_copy(op)
+            dop.src_stride = int(pitch)
+            dop.out_f16 = int(self.out_dtype == torch.float16)
+            ops_bytes[k * size:(k + 1) * size] = np.frombuffer(bytes(dop), dtype=np.uint8)
+            ptrs[k] = dp
+        s = stream or torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(s):
+            self._ops_dev[slot].copy_(self._ops_host[slot], non_blocking=True)
+            self._ptr_dev[slot].copy_(self._ptr_host[slot], non_blocking=True)
+            out = self._out[slot]
+            native.call("image_transform_batch", ptr(self._ptr_dev[slot]), ptr(self._ops_dev[slot]),
+                        i32(n), i32(self.oh * self.ow), ptr(self._means), ptr(out),
+                        i64(self.oh * self.ow * 3), ctypes.c_void_p(s.cuda_stream))
+        self.h2d_bytes_last = n * (size + 8)
+        return out[:n]

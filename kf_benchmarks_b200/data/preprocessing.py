@@ -132,6 +132,15 @@ def train_image(img: np.ndarray, height: int, width: int, bbox, batch_position: 
     return np.ascontiguousarray(img)
 
 
+class _ImageDims:
+    """Stand-in for a decoded image where only its geometry is needed (the pixels are decoded
+    on the device): what ``native_image.make_op`` and the crop samplers read."""
+
+    def __init__(self, h: int, w: int):
+        self.shape = (h, w, 3)
+        self.strides = (w * 3, 3, 1)
+
+
 def decode_jpeg(buf: bytes) -> np.ndarray:
     from PIL import Image
     return np.asarray(Image.open(io.BytesIO(buf)).convert("RGB"))
@@ -226,6 +235,21 @@ class _BatchSource(InputSource):
                                     for _ in range(len(self._ring))]
                 self.host_resident = False
                 self._raw_jobs = [None] * batch
+                # JPEG decode on the device as well (data/nvjpeg.py): workers then hand over
+                # (bitstream, descriptor, dims) for baseline JPEGs; KFB_NVJPEG=0 keeps Pillow
+                self._jpeg = None
+                self._final = {}
+                if os.environ.get("KFB_NVJPEG", "1") != "0":
+                    from . import nvjpeg
+                    if nvjpeg.available():
+                        try:
+                            self._jpeg = nvjpeg.NvJpegDecoder(
+                                self.device, int(os.environ.get("KFB_NVJPEG_BACKEND", "0")),
+                                cpu_threads=max(nthreads, 1), slots=len(self._ring))
+                            _log_once("JPEG decode on the GPU: nvJPEG backend '%s'"
+                                      % self._jpeg.backend)
+                        except Exception as e:  # no usable backend on this GPU
+                            _log_once("nvJPEG unavailable (%s): decoding with Pillow" % e)
         self.producer = ImageProducer(self._make_batch, group)
         self.producer.start()
         self.bytes_per_step = batch * height * width * 3 * (2 if self.out_dtype ==
@@ -261,19 +285,42 @@ class _BatchSource(InputSource):
         launch on the source's own stream. Positions the host had to transform itself (bicubic /
         area) are copied over from the pinned batch."""
         slot = (self._ring_pos - 1) % len(self._ring)
-        idx = [i for i, j in enumerate(self._raw_jobs) if j is not None]
+        jobs = self._raw_jobs
+        jidx = [i for i, j in enumerate(jobs) if j is not None and len(j) == 3]   # bitstreams
+        if jidx:
+            try:
+                _, ptrs, pitches = self._jpeg.decode([jobs[i][0] for i in jidx],
+                                                     [jobs[i][2] for i in jidx],
+                                                     stream=self._gpu_stream)
+            except Exception as e:
+                # a bitstream nvJPEG rejects: this batch is decoded on the host instead
+                _log_once("nvJPEG decode failed (%s): batch decoded with Pillow" % e)
+                for i in jidx:
+                    jobs[i] = (np.ascontiguousarray(decode_jpeg(jobs[i][0])), jobs[i][1])
+                jidx = []
+        idx = [i for i, j in enumerate(jobs) if j is not None and len(j) == 2]    # decoded
         with torch.cuda.stream(self._gpu_stream):
-            out = self._gpu.run([self._raw_jobs[i][0] for i in idx],
-                                [self._raw_jobs[i][1] for i in idx], stream=self._gpu_stream) \
-                if idx else None
-            dev = self._gpu._out[(self._gpu._slot - 1) % self._gpu.slots]
-            if len(idx) != self.batch:
-                # some positions were transformed on the host: upload the pinned batch and
-                # overwrite the device-transformed positions
-                full = images.to(self.device, non_blocking=True)
+            out_j = self._gpu.run_device(ptrs, pitches, [jobs[i][1] for i in jidx],
+                                         stream=self._gpu_stream) if jidx else None
+            out = self._gpu.run([jobs[i][0] for i in idx], [jobs[i][1] for i in idx],
+                                stream=self._gpu_stream) if idx else None
+            if len(jidx) == self.batch:
+                dev = out_j
+            elif len(idx) == self.batch:
+                dev = out
+            else:
+                # mixed batch (device-decoded, host-decoded, host-transformed positions): the
+                # pieces are gathered into a batch buffer of this ring slot
+                dev = self._final.get(slot)
+                if dev is None:
+                    dev = self._final[slot] = torch.empty(
+                        (self.batch, self.h, self.w, 3), dtype=self.out_dtype, device=self.device)
+                if len(jidx) + len(idx) != self.batch:
+                    dev.copy_(images, non_blocking=True)      # host-transformed positions
+                if jidx:
+                    dev.index_copy_(0, torch.tensor(jidx, device=self.device), out_j)
                 if idx:
-                    full[torch.tensor(idx, device=self.device)] = out
-                dev = full
+                    dev.index_copy_(0, torch.tensor(idx, device=self.device), out)
             labels_dev = self._labels_dev[slot]
             labels_dev.copy_(labels_t, non_blocking=True)
             ev = torch.cuda.Event()
@@ -382,7 +429,12 @@ class ImagenetSource(_BatchSource):
         record, seed = job
         p = self.p
         buf, label, bbox, _ = parse_example_proto(record)
-        img = decode_jpeg(buf)
+        dims = None
+        if self._gpu is not None and self._jpeg is not None and self._native is not None:
+            from . import nvjpeg
+            dims = nvjpeg.device_decodable(buf)
+        # with a device decode only the geometry of the image is needed on the host
+        img = _ImageDims(dims[0], dims[1]) if dims is not None else decode_jpeg(buf)
         rng = random.Random(seed)
         labels[position] = label
         if self._native is None:
@@ -409,8 +461,11 @@ class ImagenetSource(_BatchSource):
         if self._gpu is not None:
             from . import gpu_image
             if gpu_image.supports(op):
-                self._raw_jobs[position] = (np.ascontiguousarray(img), op)
+                self._raw_jobs[position] = (buf, op, dims) if dims is not None else \
+                    (np.ascontiguousarray(img), op)
                 return
+        if dims is not None:                      # (resize method the device kernel lacks)
+            img = decode_jpeg(buf)
         ni.transform_into(np.ascontiguousarray(img), op,
                           images.data_ptr() + position * images.stride(0) * images.element_size())
 
