@@ -568,7 +568,10 @@ class BenchmarkCNN:
             g = torch.cuda.CUDAGraph()
             from .ops import native as _native
             launches0 = _native.launch_count
-            with torch.cuda.graph(g):
+            # thread-local capture: the input pipeline's producer thread allocates, copies and
+            # launches (nvJPEG, the transform kernel) on its own stream while this thread
+            # captures; in the default global mode its calls would fail and invalidate the capture
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 eng.begin_step(lr, push_dyn=False)
                 ex.forward(True)
                 ex.loss_backward(on_grads_ready=eng.on_grads_ready, **eng.loss_scale_kwargs())

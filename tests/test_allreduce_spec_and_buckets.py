@@ -192,7 +192,7 @@ def test_graphed_step_control_flow_with_two_ranks(monkeypatch):
     monkeypatch.setattr(torch.cuda, "synchronize", lambda dev=None: None)
     monkeypatch.setattr(torch.cuda, "CUDAGraph", lambda: types.SimpleNamespace(
         replay=lambda: calls.append("replay")))
-    monkeypatch.setattr(torch.cuda, "graph", lambda g: contextlib.nullcontext())
+    monkeypatch.setattr(torch.cuda, "graph", lambda g, **kw: contextlib.nullcontext())
 
     comm = types.SimpleNamespace(seq=0, _dev_base=0, barrier=lambda: None)
     comm.enable_device_seq = lambda: "counter"
