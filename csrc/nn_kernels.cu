@@ -1354,7 +1354,7 @@ static int env_int(const char* name, int dflt, int lo, int hi) {
   return v < lo ? lo : (v > hi ? hi : v);
 }
 static int apply_ctas_per_sm() {
-  static const int v = env_int("KFB_APPLY_CTAS_PER_SM", 16, 1, 64);
+  static const int v = env_int("KFB_APPLY_CTAS_PER_SM", 4, 1, 64);  // one resident wave (measured: 4 > 8 > 16 > 6)
   return v;
 }
 static int apply_unroll() {
