@@ -111,7 +111,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         objs = list(ex.map(lambda s: _compile_one(s, verbose), srcs))
     newest_obj = max(os.path.getmtime(o) for o in objs)
     if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < newest_obj:
-        cmd = [_nvcc(), "-shared", "-o", LIB] + objs
+        # the arch at link time too: without it nvcc adds an (empty) sm_52 device-link stub
+        cmd = [_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
