@@ -568,10 +568,14 @@ class BenchmarkCNN:
             g = torch.cuda.CUDAGraph()
             from .ops import native as _native
             launches0 = _native.launch_count
-            # thread-local capture: the input pipeline's producer thread allocates, copies and
-            # launches (nvJPEG, the transform kernel) on its own stream while this thread
-            # captures; in the default global mode its calls would fail and invalidate the capture
-            with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            # A device-side input pipeline (--gpu_preprocess) has a producer thread that
+            # allocates, copies and launches (nvJPEG, the transform kernel) on its own stream
+            # while this thread captures: in the default global mode its calls would fail and
+            # invalidate the capture, so the capture is thread-local then. Every other source
+            # keeps the global mode (the one the multi-rank captures were validated with).
+            busy_producer = getattr(self.input_source, "_gpu", None) is not None
+            mode = {"capture_error_mode": "thread_local"} if busy_producer else {}
+            with torch.cuda.graph(g, **mode):
                 eng.begin_step(lr, push_dyn=False)
                 ex.forward(True)
                 ex.loss_backward(on_grads_ready=eng.on_grads_ready, **eng.loss_scale_kwargs())
